@@ -1,0 +1,258 @@
+"""oracle/pyoracle.py -- TEST INFRASTRUCTURE ONLY.
+
+Python face of the CPU oracle for the gr-filter / gr-fft hot path.  Only ``tests/``,
+``__graft_entry__.smoke()`` and ``bench.py``'s cpu_baseline / ``--impl reference`` legs may import
+this module; the product package ``gnuradio_b200`` never does.
+
+Three layers, from most to least authoritative:
+
+* ``Ref``   -- oracle/_ref/libgrref.so: the reference's OWN kernel sources (fir_filter.cc,
+  fft_filter.cc, polyphase_filterbank.cc, firdes.cc, window.cc) compiled unmodified from
+  /root/reference against oracle/shim by oracle/Makefile (block shells restated in oracle/ref_capi.cc).
+* ``Port``  -- oracle/libgrb_oracle.so: the plain-C restatement oracle/port.c.
+* ``f64_*`` -- float64 numpy closed forms.
+
+Both C layers expose the same calls through ``_CLib`` so tests can run either against the other.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_SO = os.path.join(HERE, "_ref", "libgrref.so")
+PORT_SO = os.path.join(HERE, "libgrb_oracle.so")
+
+
+def build(ref=True, port=True):
+    """Compile the checker libraries (building the checker is not using it)."""
+    if port:
+        subprocess.check_call(["make", "-s", "-C", HERE, "port"])
+    if ref and os.path.isdir("/root/reference/gr-filter"):
+        subprocess.check_call(["make", "-s", "-C", HERE, "ref"])
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _c64(a):
+    return np.ascontiguousarray(a, dtype=np.complex64)
+
+
+class _CLib:
+    """Uniform wrapper over libgrref.so (prefix grref_) and libgrb_oracle.so (prefix grbo_)."""
+
+    def __init__(self, path, prefix, kind):
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        self.lib = C.CDLL(path)
+        self.prefix = prefix
+        self.kind = kind  # "reference" | "port"
+
+    def _f(self, name):
+        return getattr(self.lib, self.prefix + name)
+
+    # -- fir_filter_ccf / ccc work(): xin carries ntaps-1 history items in front ------------------
+    def fir(self, decim, taps, xin, nout):
+        taps = np.ascontiguousarray(taps)
+        xin = _c64(xin)
+        ntaps = len(taps)
+        assert len(xin) >= nout * decim + ntaps - 1
+        out = np.empty(nout, np.complex64)
+        if np.iscomplexobj(taps):
+            t = _c64(taps)
+            rc = self._f("fir_ccc")(decim, _p(t), ntaps, _p(xin), _p(out), C.c_long(nout))
+        else:
+            t = np.ascontiguousarray(taps, np.float32)
+            rc = self._f("fir_ccf")(decim, _p(t), ntaps, _p(xin), _p(out), C.c_long(nout))
+        assert rc == 0
+        return out
+
+    def fir_stream(self, decim, taps, x):
+        """Whole finite stream as a flowgraph would see it: ntaps-1 zeros preloaded."""
+        ntaps = len(taps)
+        xin = np.concatenate([np.zeros(ntaps - 1, np.complex64), _c64(x)])
+        return self.fir(decim, taps, xin, len(x) // decim)
+
+    # -- fft_filter_ccc ---------------------------------------------------------------------------
+    def fft_filter_nsamples(self, ntaps):
+        return int(self._f("fft_filter_nsamples")(int(ntaps)))
+
+    def fft_filter_ccc(self, decim, taps, x, chunk_out=0):
+        t = _c64(taps)
+        x = _c64(x)
+        ns = self.fft_filter_nsamples(len(t))
+        nitems = (len(x) // decim // ns) * ns
+        out = np.empty(nitems, np.complex64)
+        if nitems == 0:
+            return out
+        rc = self._f("fft_filter_ccc")(decim, _p(t), len(t), _p(x), _p(out), C.c_long(nitems),
+                                       C.c_long(chunk_out))
+        assert rc == ns, rc
+        return out
+
+    # -- pfb_channelizer_ccf: one general_work() call ---------------------------------------------
+    def pfb_taps_per_filter(self, nfilts, ntaps):
+        return int(self._f("pfb_taps_per_filter")(C.c_uint(nfilts), int(ntaps)))
+
+    def pfb_channelizer(self, nfilts, taps, osr, in_streams, noutput, channel_map=None, nouts=None):
+        """in_streams: [nfilts, consumed + T] complex64 (T history items first).
+        Returns ([nouts, noutput] complex64, consumed) or raises ValueError."""
+        t = np.ascontiguousarray(taps, np.float32)
+        ins = _c64(in_streams)
+        assert ins.shape[0] == nfilts
+        nouts = nfilts if nouts is None else nouts
+        outs = np.zeros((nouts, noutput), np.complex64)
+        inp = (C.c_void_p * nfilts)(*[ins[j].ctypes.data for j in range(nfilts)])
+        outp = (C.c_void_p * nouts)(*[outs[j].ctypes.data for j in range(nouts)])
+        if channel_map is None:
+            cm, ncm = None, 0
+        else:
+            cma = np.ascontiguousarray(channel_map, np.int32)
+            cm, ncm = _p(cma), len(cma)
+        rc = self._f("pfb_channelizer_ccf")(C.c_uint(nfilts), _p(t), len(t), C.c_float(osr), cm, ncm,
+                                            inp, outp, nouts, int(noutput))
+        if rc < 0:
+            raise ValueError("pfb_channelizer_ccf oracle error %d" % rc)
+        return outs, rc
+
+    # -- fft_vcc -----------------------------------------------------------------------------------
+    def fft_vcc(self, fft_size, forward, window, shift, x):
+        x = _c64(x)
+        nvec = len(x) // fft_size
+        out = np.empty(nvec * fft_size, np.complex64)
+        if window is None or len(window) == 0:
+            w, nw = None, 0
+        else:
+            wa = np.ascontiguousarray(window, np.float32)
+            w, nw = _p(wa), len(wa)
+        rc = self._f("fft_vcc")(int(fft_size), int(bool(forward)), w, nw, int(bool(shift)), _p(x),
+                                _p(out), C.c_long(nvec))
+        if rc != 0:
+            raise RuntimeError("fft_vcc: window not the same length as fft_size")
+        return out
+
+    def mag_squared(self, x):
+        x = _c64(x)
+        out = np.empty(len(x), np.float32)
+        self._f("mag_squared")(_p(x), _p(out), C.c_long(len(x)))
+        return out
+
+    # -- window / firdes ---------------------------------------------------------------------------
+    def window(self, wtype, ntaps, beta=6.76):
+        out = np.empty(ntaps, np.float32)
+        if self.kind == "reference":
+            rc = self._f("window_build")(int(wtype), int(ntaps), C.c_double(beta), _p(out))
+        else:
+            rc = self._f("window_build")(int(wtype), int(ntaps), _p(out))
+        if rc < 0:
+            raise ValueError("window type %d not available in %s oracle" % (wtype, self.kind))
+        return out
+
+    def low_pass_2(self, gain, fs, cutoff, tw, atten_db, wtype=0, beta=6.76):
+        buf = np.empty(1 << 16, np.float32)
+        if self.kind == "reference":
+            n = self._f("firdes_low_pass_2")(C.c_double(gain), C.c_double(fs), C.c_double(cutoff),
+                                             C.c_double(tw), C.c_double(atten_db), int(wtype),
+                                             C.c_double(beta), _p(buf), len(buf))
+        else:
+            n = self._f("firdes_low_pass_2")(C.c_double(gain), C.c_double(fs), C.c_double(cutoff),
+                                             C.c_double(tw), C.c_double(atten_db), int(wtype),
+                                             _p(buf), len(buf))
+        if n < 0:
+            raise ValueError("firdes error %d" % n)
+        return buf[:n].copy()
+
+
+_cache = {}
+
+
+def Ref():
+    if "ref" not in _cache:
+        _cache["ref"] = _CLib(REF_SO, "grref_", "reference")
+    return _cache["ref"]
+
+
+def Port():
+    if "port" not in _cache:
+        if not os.path.exists(PORT_SO):
+            build(ref=False)
+        _cache["port"] = _CLib(PORT_SO, "grbo_", "port")
+    return _cache["port"]
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+def best():
+    """The most authoritative C oracle available on this machine."""
+    return Ref() if have_ref() else Port()
+
+
+# ------------------------------------------------------------------------------------------------
+# float64 closed forms
+# ------------------------------------------------------------------------------------------------
+def f64_fir(decim, taps, x):
+    """out[i] = sum_k taps[k] x[i*D-k], x[<0]=0 (gr-filter/python/filter/qa_fir_filter.py:14-22)."""
+    x = np.asarray(x, np.complex128)
+    t = np.asarray(taps, np.complex128 if np.iscomplexobj(taps) else np.float64)
+    n = (len(x) // decim)
+    return np.convolve(x, t)[: n * decim: decim][:n]
+
+
+def f64_fft_filter(decim, taps, x, nsamples):
+    x = np.asarray(x, np.complex128)
+    t = np.asarray(taps, np.complex128)
+    nitems = (len(x) // decim // nsamples) * nsamples
+    return np.convolve(x[: nitems * decim], t)[: nitems * decim: decim][:nitems]
+
+
+def f64_channelizer(nfilts, taps, x, nout, osr=1.0):
+    """Closed form of pfb_channelizer_ccf for an interleaved input stream x (zeros before t=0).
+
+    out_c[o] = rot(c,o) * (x conv g_c)[P(o)],  g_c[n] = h[n] e^{+j2pi c n/M},
+    P(o) = (o+1)*R - 1, R = M/osr, rot = e^{-j2pi c (o+2) R / M}   (==1 when osr == 1).
+    Derived from gr-filter/lib/pfb_channelizer_ccf_impl.cc:73-77,157-189."""
+    M = int(nfilts)
+    R = int(round(M / osr))
+    h = np.asarray(taps, np.float64)
+    x = np.asarray(x, np.complex128)
+    n = np.arange(len(h))
+    out = np.zeros((M, nout), np.complex128)
+    o = np.arange(nout)
+    P = (o + 1) * R - 1
+    assert P.max() < len(x) + 0 or nout == 0
+    for c in range(M):
+        g = h * np.exp(2j * np.pi * c * n / M)
+        y = np.convolve(x, g)[: len(x)]
+        out[c] = y[P] * np.exp(-2j * np.pi * c * ((o + 2) * R % M) / M)
+    return out
+
+
+def f64_fft_vcc(fft_size, forward, window, shift, x):
+    N = fft_size
+    v = np.asarray(x, np.complex128)[: (len(x) // N) * N].reshape(-1, N)
+    if window is not None and len(window):
+        v = v * np.asarray(window, np.float64)[None, :]
+    if forward:
+        y = np.fft.fft(v, axis=1)
+        if shift:
+            y = np.fft.fftshift(y, axes=1)
+    else:
+        if shift:
+            v = np.fft.ifftshift(v, axes=1)
+        y = np.fft.ifft(v, axis=1) * N
+    return y.reshape(-1)
+
+
+def nrms(a, ref):
+    """Normalised RMS error and max-abs error relative to the reference RMS (north_star tolerance)."""
+    a = np.asarray(a)
+    ref = np.asarray(ref)
+    rms = np.sqrt(np.mean(np.abs(ref) ** 2)) if ref.size else 1.0
+    rms = rms if rms > 0 else 1.0
+    d = np.abs(a - ref)
+    return float(np.sqrt(np.mean(d ** 2)) / rms) if ref.size else 0.0, float(d.max() / rms) if ref.size else 0.0

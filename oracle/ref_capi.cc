@@ -1,0 +1,311 @@
+/* oracle/ref_capi.cc -- TEST INFRASTRUCTURE ONLY (never on the product path).
+ *
+ * C entry points around the REAL reference kernel classes, which oracle/Makefile compiles
+ * unmodified from /root/reference into oracle/_ref/libgrref.so:
+ *   gr-filter/lib/fir_filter.cc, gr-filter/lib/fft_filter.cc, gr-filter/lib/polyphase_filterbank.cc,
+ *   gr-filter/lib/firdes.cc, gr-fft/lib/window.cc.
+ * The block shells (work()/general_work()) depend on gr::block (Boost/PMT/GMP, absent here) and are
+ * restated below next to the reference file:line each loop follows.  Third-party arithmetic comes
+ * from oracle/shim (generic-C VOLK stand-ins, own FFT engine in place of FFTW3f).
+ */
+#include <gnuradio/fft/fft.h>
+#include <gnuradio/fft/window.h>
+#include <gnuradio/filter/fft_filter.h>
+#include <gnuradio/filter/fir_filter.h>
+#include <gnuradio/filter/firdes.h>
+#include <gnuradio/filter/polyphase_filterbank.h>
+#include <volk/volk.h>
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+#include <vector>
+
+using gr::filter::kernel::fft_filter_ccc;
+using gr::filter::kernel::fir_filter_ccc;
+using gr::filter::kernel::fir_filter_ccf;
+
+namespace {
+
+/* Restatement of pfb_channelizer_ccf_impl (gr-filter/lib/pfb_channelizer_ccf_impl.cc:34-193) on
+ * top of the real kernel::polyphase_filterbank. */
+class channelizer_shell : public gr::filter::kernel::polyphase_filterbank
+{
+public:
+    float d_osr;
+    int d_rate_ratio;
+    int d_output_multiple;
+    std::vector<int> d_idxlut;
+    std::vector<int> d_channel_map;
+
+    channelizer_shell(unsigned int nfilts, const std::vector<float>& taps, float osr)
+        : polyphase_filterbank(nfilts, taps, false), d_osr(osr)
+    {
+        /* ctor checks: pfb_channelizer_ccf_impl.cc:49-53 */
+        const double srate = nfilts / osr;
+        const double rsrate = round(srate);
+        if (fabs(srate - rsrate) > 0.00001)
+            throw std::invalid_argument(
+                "pfb_channelizer: oversample rate must be N/i for i in [1, N]");
+        d_channel_map.resize(nfilts);
+        for (unsigned int i = 0; i < nfilts; i++)
+            d_channel_map[i] = i;
+        /* LUT: :72-77 */
+        d_rate_ratio = (int)rintf(nfilts / osr);
+        d_idxlut.resize(nfilts);
+        for (unsigned int i = 0; i < nfilts; i++)
+            d_idxlut[i] = nfilts - ((i + d_rate_ratio) % nfilts) - 1;
+        /* output multiple: :81-84 */
+        d_output_multiple = 1;
+        while ((d_output_multiple * d_rate_ratio) % nfilts != 0)
+            d_output_multiple++;
+    }
+
+    /* general_work body: :157-192.  in[j] points at the oldest history item of stream j
+     * (history = taps_per_filter + 1).  Returns items consumed per input stream. */
+    int work(int noutput_items,
+             const gr_complex* const* input_items,
+             gr_complex* const* output_items,
+             size_t noutputs)
+    {
+        const int nfilts = (int)d_nfilts;
+        int n = 1, i = -1, j = 0, oo = 0, last;
+        int toconsume = (int)rintf(noutput_items / d_osr);
+        while (n <= toconsume) {
+            j = 0;
+            i = (i + d_rate_ratio) % nfilts;
+            last = i;
+            while (i >= 0) {
+                const gr_complex* in = input_items[j];
+                d_fft->get_inbuf()[d_idxlut[j]] = d_fir_filters[i]->filter(&in[n]);
+                j++;
+                i--;
+            }
+            i = nfilts - 1;
+            while (i > last) {
+                const gr_complex* in = input_items[j];
+                d_fft->get_inbuf()[d_idxlut[j]] = d_fir_filters[i]->filter(&in[n - 1]);
+                j++;
+                i--;
+            }
+            n += (i + d_rate_ratio) >= nfilts;
+            d_fft->execute();
+            for (size_t nn = 0; nn < noutputs; nn++)
+                output_items[nn][oo] = d_fft->get_outbuf()[d_channel_map[nn]];
+            oo++;
+        }
+        return toconsume;
+    }
+};
+
+} // namespace
+
+extern "C" {
+
+/* fir_filter_blk_impl<gr_complex,gr_complex,float>::work (gr-filter/lib/fir_filter_blk_impl.cc:67-90):
+ * in[] holds nout*decim + ntaps-1 items, in[0] = oldest history item. */
+int grref_fir_ccf(int decim, const float* taps, int ntaps, const void* in, void* out, long nout)
+{
+    std::vector<float> t(taps, taps + ntaps);
+    fir_filter_ccf fir(decim, t);
+    if (decim == 1)
+        fir.filterN((gr_complex*)out, (const gr_complex*)in, (unsigned long)nout);
+    else
+        fir.filterNdec((gr_complex*)out, (const gr_complex*)in, (unsigned long)nout, decim);
+    return 0;
+}
+
+int grref_fir_ccc(int decim, const void* taps, int ntaps, const void* in, void* out, long nout)
+{
+    const gr_complex* tp = (const gr_complex*)taps;
+    std::vector<gr_complex> t(tp, tp + ntaps);
+    fir_filter_ccc fir(decim, t);
+    if (decim == 1)
+        fir.filterN((gr_complex*)out, (const gr_complex*)in, (unsigned long)nout);
+    else
+        fir.filterNdec((gr_complex*)out, (const gr_complex*)in, (unsigned long)nout, decim);
+    return 0;
+}
+
+/* fft_filter_ccc_impl::work driven like the scheduler does (gr-filter/lib/fft_filter_ccc_impl.cc:61-78):
+ * one filter() call per chunk of `chunk_out` output items (rounded down to a multiple of nsamples,
+ * at least one block).  nitems must be a multiple of nsamples; consumes nitems*decim inputs.
+ * Returns nsamples, or -1 on a bad nitems. */
+int grref_fft_filter_ccc(int decim,
+                         const void* taps,
+                         int ntaps,
+                         const void* in,
+                         void* out,
+                         long nitems,
+                         long chunk_out)
+{
+    const gr_complex* tp = (const gr_complex*)taps;
+    std::vector<gr_complex> t(tp, tp + ntaps);
+    fft_filter_ccc filt(decim, t, 1);
+    const int nsamples = filt.set_taps(t);
+    if (nitems % nsamples != 0)
+        return -1;
+    long chunk = (chunk_out / nsamples) * nsamples;
+    if (chunk <= 0)
+        chunk = nsamples;
+    const gr_complex* ip = (const gr_complex*)in;
+    gr_complex* op = (gr_complex*)out;
+    for (long done = 0; done < nitems;) {
+        long n = std::min(chunk, nitems - done);
+        filt.filter((int)n, ip, op);
+        ip += n * decim;
+        op += n;
+        done += n;
+    }
+    return nsamples;
+}
+
+int grref_fft_filter_nsamples(int ntaps)
+{
+    std::vector<gr_complex> t(ntaps, gr_complex(1.0f, 0.0f));
+    fft_filter_ccc filt(1, t, 1);
+    return filt.set_taps(t);
+}
+
+/* One pfb_channelizer_ccf general_work() call.  in_streams[j] -> consumed + taps_per_filter items
+ * (the first taps_per_filter being history).  Returns items consumed per stream, <0 on ctor error. */
+int grref_pfb_channelizer_ccf(unsigned int nfilts,
+                              const float* taps,
+                              int ntaps,
+                              float osr,
+                              const int* channel_map,
+                              int nmap,
+                              const void* const* in_streams,
+                              void* const* out_streams,
+                              int nouts,
+                              int noutput)
+{
+    try {
+        std::vector<float> t(taps, taps + ntaps);
+        channelizer_shell ch(nfilts, t, osr);
+        if (nmap > 0) {
+            /* set_channel_map: pfb_channelizer_ccf_impl.cc:112-124 */
+            std::vector<int> map(channel_map, channel_map + nmap);
+            unsigned int mx = 0;
+            for (int v : map)
+                mx = std::max(mx, (unsigned int)v);
+            if (mx >= nfilts)
+                return -2;
+            ch.d_channel_map = map;
+        }
+        if (noutput % ch.d_output_multiple != 0)
+            return -3;
+        return ch.work(noutput,
+                       (const gr_complex* const*)in_streams,
+                       (gr_complex* const*)out_streams,
+                       (size_t)nouts);
+    } catch (const std::invalid_argument&) {
+        return -1;
+    }
+}
+
+int grref_pfb_taps_per_filter(unsigned int nfilts, int ntaps)
+{
+    return (int)ceil((double)ntaps / (double)nfilts);
+}
+
+/* fft_vcc_fftw::work (gr-fft/lib/fft_vcc_fftw.cc:63-122) restated over the shim fft_complex. */
+int grref_fft_vcc(int fft_size,
+                  int forward,
+                  const float* window,
+                  int nwindow,
+                  int shift,
+                  const void* in_,
+                  void* out_,
+                  long nvec)
+{
+    if (!(nwindow == 0 || nwindow == fft_size))
+        return -1; /* ctor throws std::runtime_error: fft_vcc_fftw.cc:46-47 */
+    gr::fft::fft_complex fft(fft_size, forward != 0, 1);
+    const gr_complex* in = (const gr_complex*)in_;
+    gr_complex* out = (gr_complex*)out_;
+    const unsigned int N = (unsigned int)fft_size;
+    for (long count = 0; count < nvec; count++) {
+        gr_complex* dst = fft.get_inbuf();
+        if (nwindow) {
+            if (!forward && shift) {
+                unsigned int offset = N / 2;
+                int fft_m_offset = N - offset;
+                volk_32fc_32f_multiply_32fc(&dst[fft_m_offset], &in[0], &window[0], offset);
+                volk_32fc_32f_multiply_32fc(&dst[0], &in[offset], &window[offset], N - offset);
+            } else {
+                volk_32fc_32f_multiply_32fc(&dst[0], in, &window[0], N);
+            }
+        } else {
+            if (!forward && shift) {
+                unsigned int len = (unsigned int)(floor(N / 2.0));
+                memcpy(&dst[0], &in[len], sizeof(gr_complex) * (N - len));
+                memcpy(&dst[N - len], &in[0], sizeof(gr_complex) * len);
+            } else {
+                memcpy(dst, in, sizeof(gr_complex) * N);
+            }
+        }
+        fft.execute();
+        if (forward && shift) {
+            unsigned int len = (unsigned int)(ceil(N / 2.0));
+            memcpy(&out[0], &fft.get_outbuf()[len], sizeof(gr_complex) * (N - len));
+            memcpy(&out[N - len], &fft.get_outbuf()[0], sizeof(gr_complex) * len);
+        } else {
+            memcpy(out, fft.get_outbuf(), sizeof(gr_complex) * N);
+        }
+        in += N;
+        out += N;
+    }
+    return 0;
+}
+
+/* complex_to_mag_squared_impl::work (gr-blocks/lib/complex_to_mag_squared_impl.cc:37-48) */
+int grref_mag_squared(const void* in, float* out, long n)
+{
+    volk_32fc_magnitude_squared_32f(out, (const gr_complex*)in, (unsigned int)n);
+    return 0;
+}
+
+/* gr::fft::window::build (gr-fft/lib/window.cc) -- real reference code. */
+int grref_window_build(int type, int ntaps, double beta, float* out)
+{
+    try {
+        std::vector<float> w =
+            gr::fft::window::build((gr::fft::window::win_type)type, ntaps, beta);
+        memcpy(out, w.data(), sizeof(float) * w.size());
+        return (int)w.size();
+    } catch (...) {
+        return -1;
+    }
+}
+
+/* gr::filter::firdes::low_pass / low_pass_2 (gr-filter/lib/firdes.cc:33-119) -- real reference code.
+ * Returns the tap count (writes at most maxn taps), <0 on error. */
+int grref_firdes_low_pass(double gain, double fs, double cutoff, double tw, int win, double beta,
+                          float* out, int maxn)
+{
+    try {
+        std::vector<float> t = gr::filter::firdes::low_pass(
+            gain, fs, cutoff, tw, (gr::filter::firdes::win_type)win, beta);
+        for (int i = 0; i < (int)t.size() && i < maxn; i++)
+            out[i] = t[i];
+        return (int)t.size();
+    } catch (...) {
+        return -1;
+    }
+}
+
+int grref_firdes_low_pass_2(double gain, double fs, double cutoff, double tw, double atten_db,
+                            int win, double beta, float* out, int maxn)
+{
+    try {
+        std::vector<float> t = gr::filter::firdes::low_pass_2(
+            gain, fs, cutoff, tw, atten_db, (gr::filter::firdes::win_type)win, beta);
+        for (int i = 0; i < (int)t.size() && i < maxn; i++)
+            out[i] = t[i];
+        return (int)t.size();
+    } catch (...) {
+        return -1;
+    }
+}
+
+} /* extern "C" */
