@@ -1,0 +1,72 @@
+// capi_common.cuh -- declarations shared by the C-ABI translation units.
+#pragma once
+#include <cmath>
+#include <memory>
+#include "staging.cuh"
+
+namespace grb {
+// kernels' host launchers (fir.cu, fftvcc.cu, fftfilt.cu, pfb.cu)
+int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, const void* in, void* out,
+               long long nout, cudaStream_t st);
+int fir_upad(int D, int ntaps);
+bool fft_size_is_fast(int N);
+int fft_direct_max();
+int fft_vcc_launch(int N, bool fwd, const void* in, void* out, long long nvec, const float* window, int shift,
+                   int magsq, const float2* tw, int nsm, cudaStream_t st);
+int magsq_launch(const void* in, float* out, long long n, int nsm, cudaStream_t st);
+int fftfilt_device_fftsize(int ntaps);
+int fftfilt_launch(int L, const void* in, void* out, long long nout, int ntaps, int D, const float2* H,
+                   const float2* tw, int nsm, cudaStream_t st);
+int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stride, int nouts, const int* cmap,
+               int identity, long long noutput, const float* h, const float2* wM, int nsm, bool allow_fast,
+               cudaStream_t st);
+int streams_to_interleaved_launch(const void* in, long long in_stride, void* out, int M, long long nrows,
+                                  cudaStream_t st);
+
+static const size_t kChunkBytes = 32u << 20; // staging granularity (input bytes per chunk)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int upload(const void* host, size_t bytes)
+    {
+        if (bytes > cap) {
+            if (p)
+                cudaFree(p);
+            p = nullptr;
+            cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+            if (e != cudaSuccess) {
+                cap = 0;
+                return fail(GRB200_ENOMEM, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+            }
+            cap = bytes;
+        }
+        if (bytes)
+            GRB_CUDA(cudaMemcpy(p, host, bytes, cudaMemcpyHostToDevice));
+        return 0;
+    }
+    void release()
+    {
+        if (p)
+            cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+// forward twiddle table e^{-j 2 pi k / N} (or e^{+...} with sign=+1), evaluated in double
+inline std::vector<float2> make_roots(int N, int sign)
+{
+    std::vector<float2> w((size_t)N);
+    const double two_pi = 6.283185307179586476925286766559;
+    for (int k = 0; k < N; k++) {
+        const double a = two_pi * k / N;
+        w[k] = make_float2((float)cos(a), (float)(sign * sin(a)));
+    }
+    return w;
+}
+
+inline cudaStream_t pick_stream(void* user, Stager& sg) { return user ? (cudaStream_t)user : sg.s_exec; }
+
+} // namespace grb
+

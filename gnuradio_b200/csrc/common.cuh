@@ -1,0 +1,70 @@
+// common.cuh -- shared host/device helpers for libgrb200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/grb200.h"
+
+namespace grb {
+
+// ---- error plumbing ---------------------------------------------------------------------------
+extern thread_local char g_err[512];
+extern std::atomic<unsigned long long> g_launches;
+
+inline int fail(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define GRB_CUDA(expr)                                                                      \
+    do {                                                                                    \
+        cudaError_t _e = (expr);                                                            \
+        if (_e != cudaSuccess)                                                              \
+            return grb::fail(GRB200_ECUDA, "%s failed: %s (%s:%d)", #expr,                  \
+                             cudaGetErrorString(_e), __FILE__, __LINE__);                   \
+    } while (0)
+
+#define GRB_LAUNCH_CHECK()                                                                  \
+    do {                                                                                    \
+        grb::g_launches.fetch_add(1, std::memory_order_relaxed);                            \
+        cudaError_t _e = cudaGetLastError();                                                \
+        if (_e != cudaSuccess)                                                              \
+            return grb::fail(GRB200_ECUDA, "kernel launch failed: %s (%s:%d)",              \
+                             cudaGetErrorString(_e), __FILE__, __LINE__);                   \
+    } while (0)
+
+// Select a device and check that it is a Blackwell (sm_100) part: there is no other code path.
+int use_device(int device);
+int sm_count(int device);
+
+// ---- device-side complex helpers --------------------------------------------------------------
+__device__ __forceinline__ float2 cmul(float2 a, float2 b)
+{
+    return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cconj(float2 a) { return make_float2(a.x, -a.y); }
+// multiply by -j (forward) / +j (inverse)
+template <bool FWD>
+__device__ __forceinline__ float2 cmulj(float2 a)
+{
+    return FWD ? make_float2(a.y, -a.x) : make_float2(-a.y, a.x);
+}
+
+// ---- staging: pinned double-buffered host<->device pipeline (K8 in SURVEY.md section 2a) --------
+// A Stager owns three streams (h2d, compute, d2h), NSLOT pinned bounce slots per direction and
+// device slots.  Callers describe a job as a sequence of chunks; see staging.cu.
+struct Stager;
+
+} // namespace grb

@@ -1,0 +1,232 @@
+// staging.cu -- library globals, device selection and the pinned double-buffered staging pipeline (K8).
+#include "staging.cuh"
+
+namespace grb {
+
+thread_local char g_err[512] = "";
+std::atomic<unsigned long long> g_launches{ 0 };
+
+static std::mutex g_dev_mutex;
+static int g_dev_checked[64];
+static int g_dev_sms[64];
+
+int use_device(int device)
+{
+    if (device < 0 || device >= 64)
+        return fail(GRB200_EINVAL, "invalid device index %d", device);
+    GRB_CUDA(cudaSetDevice(device));
+    std::lock_guard<std::mutex> lk(g_dev_mutex);
+    if (!g_dev_checked[device]) {
+        cudaDeviceProp prop;
+        GRB_CUDA(cudaGetDeviceProperties(&prop, device));
+        if (prop.major != 10)
+            return fail(GRB200_ECUDA,
+                        "device %d is sm_%d%d; libgrb200 is built for sm_100a (B200) only and has no fallback",
+                        device, prop.major, prop.minor);
+        g_dev_sms[device] = prop.multiProcessorCount;
+        g_dev_checked[device] = 1;
+    }
+    return 0;
+}
+
+int sm_count(int device) { return (device >= 0 && device < 64 && g_dev_checked[device]) ? g_dev_sms[device] : 148; }
+
+// ---- Stager ----------------------------------------------------------------------------------------
+int Stager::init(int dev_id)
+{
+    if (ready)
+        return 0;
+    device = dev_id;
+    int rc = use_device(device);
+    if (rc)
+        return rc;
+    GRB_CUDA(cudaStreamCreateWithFlags(&s_h2d, cudaStreamNonBlocking));
+    GRB_CUDA(cudaStreamCreateWithFlags(&s_exec, cudaStreamNonBlocking));
+    GRB_CUDA(cudaStreamCreateWithFlags(&s_d2h, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) {
+        GRB_CUDA(cudaEventCreateWithFlags(&ev_h2d[i], cudaEventDisableTiming));
+        GRB_CUDA(cudaEventCreateWithFlags(&ev_exec[i], cudaEventDisableTiming));
+        GRB_CUDA(cudaEventCreateWithFlags(&ev_d2h[i], cudaEventDisableTiming));
+    }
+    ready = true;
+    return 0;
+}
+
+void Stager::destroy()
+{
+    if (!ready)
+        return;
+    cudaSetDevice(device);
+    cudaStreamSynchronize(s_h2d);
+    cudaStreamSynchronize(s_exec);
+    cudaStreamSynchronize(s_d2h);
+    for (int i = 0; i < 2; i++) {
+        cudaEventDestroy(ev_h2d[i]);
+        cudaEventDestroy(ev_exec[i]);
+        cudaEventDestroy(ev_d2h[i]);
+        if (pin_in[i])
+            cudaFreeHost(pin_in[i]);
+        if (pin_out[i])
+            cudaFreeHost(pin_out[i]);
+        for (int k = 0; k < 3; k++)
+            if (dev[i][k])
+                cudaFree(dev[i][k]);
+    }
+    cudaStreamDestroy(s_h2d);
+    cudaStreamDestroy(s_exec);
+    cudaStreamDestroy(s_d2h);
+    ready = false;
+}
+
+int Stager::reserve_dev(int which, size_t bytes)
+{
+    if (bytes <= dev_cap[which])
+        return 0;
+    size_t cap = bytes + bytes / 8 + 256;
+    for (int i = 0; i < 2; i++) {
+        if (dev[i][which]) {
+            GRB_CUDA(cudaStreamSynchronize(s_exec));
+            GRB_CUDA(cudaFree(dev[i][which]));
+            dev[i][which] = nullptr;
+        }
+        cudaError_t e = cudaMalloc(&dev[i][which], cap);
+        if (e != cudaSuccess) {
+            dev_cap[which] = 0;
+            return fail(GRB200_ENOMEM, "cudaMalloc(%zu) failed: %s", cap, cudaGetErrorString(e));
+        }
+    }
+    dev_cap[which] = cap;
+    return 0;
+}
+
+int Stager::reserve_pin(bool in, size_t bytes)
+{
+    size_t& cap = in ? pin_in_cap : pin_out_cap;
+    void** p = in ? pin_in : pin_out;
+    if (bytes <= cap)
+        return 0;
+    size_t ncap = bytes + bytes / 8 + 256;
+    for (int i = 0; i < 2; i++) {
+        if (p[i]) {
+            GRB_CUDA(cudaFreeHost(p[i]));
+            p[i] = nullptr;
+        }
+        cudaError_t e = cudaHostAlloc(&p[i], ncap, cudaHostAllocDefault);
+        if (e != cudaSuccess) {
+            cap = 0;
+            return fail(GRB200_ENOMEM, "cudaHostAlloc(%zu) failed: %s", ncap, cudaGetErrorString(e));
+        }
+    }
+    cap = ncap;
+    return 0;
+}
+
+bool Stager::is_pinned(const void* p)
+{
+    cudaPointerAttributes attr;
+    cudaError_t e = cudaPointerGetAttributes(&attr, p);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return attr.type == cudaMemoryTypeHost;
+}
+
+int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
+{
+    struct Bounce {
+        void* host_dst;
+        const void* pin_src;
+        size_t bytes;
+    };
+    std::vector<Bounce> bounce[2];
+    bool pending[2] = { false, false };
+    Chunk ch;
+    auto retire = [&](int slot) -> int {
+        if (!pending[slot])
+            return 0;
+        GRB_CUDA(cudaEventSynchronize(ev_d2h[slot]));
+        for (auto& b : bounce[slot])
+            memcpy(b.host_dst, b.pin_src, b.bytes);
+        bounce[slot].clear();
+        pending[slot] = false;
+        return 0;
+    };
+    for (long long c = 0; c < nchunks; c++) {
+        const int slot = (int)(c & 1);
+        int rc = retire(slot);
+        if (rc)
+            return rc;
+        ch.h2d.clear();
+        ch.d2h.clear();
+        rc = plan(c, slot, ch);
+        if (rc)
+            return rc;
+        // pageable pieces need bounce space
+        size_t need_in = 0, need_out = 0;
+        std::vector<char> pinned_in(ch.h2d.size()), pinned_out(ch.d2h.size());
+        for (size_t k = 0; k < ch.h2d.size(); k++) {
+            pinned_in[k] = is_pinned(ch.h2d[k].src);
+            if (!pinned_in[k])
+                need_in += (ch.h2d[k].bytes + 255) & ~(size_t)255;
+        }
+        for (size_t k = 0; k < ch.d2h.size(); k++) {
+            pinned_out[k] = is_pinned(ch.d2h[k].dst);
+            if (!pinned_out[k])
+                need_out += (ch.d2h[k].bytes + 255) & ~(size_t)255;
+        }
+        if (need_in > pin_in_cap || need_out > pin_out_cap) {
+            // growing the bounce slots invalidates in-flight copies: drain first
+            for (int s = 0; s < 2; s++)
+                if ((rc = retire(s)))
+                    return rc;
+            if ((rc = reserve_pin(true, need_in)) || (rc = reserve_pin(false, need_out)))
+                return rc;
+        }
+        size_t off = 0;
+        for (size_t k = 0; k < ch.h2d.size(); k++) {
+            const Piece& p = ch.h2d[k];
+            if (p.bytes == 0)
+                continue;
+            if (pinned_in[k]) {
+                GRB_CUDA(cudaMemcpyAsync(p.dst, p.src, p.bytes, cudaMemcpyHostToDevice, s_h2d));
+            } else {
+                char* b = (char*)pin_in[slot] + off;
+                memcpy(b, p.src, p.bytes);
+                GRB_CUDA(cudaMemcpyAsync(p.dst, b, p.bytes, cudaMemcpyHostToDevice, s_h2d));
+                off += (p.bytes + 255) & ~(size_t)255;
+            }
+        }
+        GRB_CUDA(cudaEventRecord(ev_h2d[slot], s_h2d));
+        GRB_CUDA(cudaStreamWaitEvent(s_exec, ev_h2d[slot], 0));
+        rc = launch(c, slot, s_exec);
+        if (rc)
+            return rc;
+        GRB_CUDA(cudaEventRecord(ev_exec[slot], s_exec));
+        GRB_CUDA(cudaStreamWaitEvent(s_d2h, ev_exec[slot], 0));
+        off = 0;
+        for (size_t k = 0; k < ch.d2h.size(); k++) {
+            const Piece& p = ch.d2h[k];
+            if (p.bytes == 0)
+                continue;
+            if (pinned_out[k]) {
+                GRB_CUDA(cudaMemcpyAsync(p.dst, p.src, p.bytes, cudaMemcpyDeviceToHost, s_d2h));
+            } else {
+                char* b = (char*)pin_out[slot] + off;
+                GRB_CUDA(cudaMemcpyAsync(b, p.src, p.bytes, cudaMemcpyDeviceToHost, s_d2h));
+                bounce[slot].push_back({ p.dst, b, p.bytes });
+                off += (p.bytes + 255) & ~(size_t)255;
+            }
+        }
+        GRB_CUDA(cudaEventRecord(ev_d2h[slot], s_d2h));
+        pending[slot] = true;
+    }
+    // drain in submission order
+    const int first = (int)(nchunks & 1);
+    int rc = retire(first);
+    if (rc)
+        return rc;
+    return retire(first ^ 1);
+}
+
+} // namespace grb

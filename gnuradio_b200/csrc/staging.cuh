@@ -1,0 +1,49 @@
+// staging.cuh -- K8: the gr::buffer chunk staged through pinned, double-buffered cudaMemcpyAsync.
+//
+// The scheduler hands work() borrowed HOST pointers into its circular buffers (reference
+// gnuradio-runtime/lib/buffer.cc:101-140, block.h:176-179).  A Stager splits one work() call into chunks and
+// runs  H2D(chunk c+1) | kernel(chunk c) | D2H(chunk c-1)  concurrently on three streams with two device
+// slots.  Host memory that is already page-locked (grb200_host_alloc, cudaHostRegister, torch pinned
+// tensors) is copied from/to directly; pageable memory goes through pinned bounce slots owned by the Stager.
+#pragma once
+#include <functional>
+#include "common.cuh"
+
+namespace grb {
+
+struct Piece {
+    const void* src; // H2D: host source / D2H: device source (offset within the slot is in dst/src below)
+    void* dst;
+    size_t bytes;
+};
+
+struct Stager {
+    int device = 0;
+    cudaStream_t s_h2d = nullptr, s_exec = nullptr, s_d2h = nullptr;
+    cudaEvent_t ev_h2d[2] = { nullptr, nullptr }, ev_exec[2] = { nullptr, nullptr }, ev_d2h[2] = { nullptr, nullptr };
+    void* pin_in[2] = { nullptr, nullptr };
+    void* pin_out[2] = { nullptr, nullptr };
+    size_t pin_in_cap = 0, pin_out_cap = 0;
+    void* dev[2][3] = { { nullptr, nullptr, nullptr }, { nullptr, nullptr, nullptr } }; // [slot][in, out, scratch]
+    size_t dev_cap[3] = { 0, 0, 0 };
+    bool ready = false;
+
+    int init(int dev_id);
+    void destroy();
+    int reserve_dev(int which, size_t bytes);  // both slots
+    int reserve_pin(bool in, size_t bytes);    // both slots
+    static bool is_pinned(const void* p);
+
+    // One chunk's description, filled by the `plan` callback:
+    //   h2d : pieces {host src, device dst (inside dev[slot][0]), bytes}
+    //   d2h : pieces {device src (inside dev[slot][1]), host dst, bytes}
+    // `launch` enqueues the chunk's kernels on s_exec.
+    struct Chunk {
+        std::vector<Piece> h2d, d2h;
+    };
+    using PlanFn = std::function<int(long long c, int slot, Chunk& ch)>;
+    using LaunchFn = std::function<int(long long c, int slot, cudaStream_t st)>;
+    int run(long long nchunks, const PlanFn& plan, const LaunchFn& launch);
+};
+
+} // namespace grb

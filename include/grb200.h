@@ -1,0 +1,146 @@
+/* grb200.h -- C-ABI of libgrb200: B200-native (sm_100a) kernels for the GNU Radio filtering hot path.
+ *
+ * This is the drop-in boundary: the re-hosted GNU Radio block classes (include/grb200/blocks.hpp, and
+ * the bindings shown in INTEGRATION.md) call ONLY these functions.  Plain pointers and sizes, no CUDA
+ * or torch types.  Every entry point names the reference interface it replaces (paths relative to the
+ * reference tree, GNU Radio 3.9.0-git).
+ *
+ * Conventions
+ *  - complex64 items are interleaved float pairs (gr_complex, gnuradio-runtime/include/gnuradio/gr_complex.h:15).
+ *  - Every function returns 0 (GRB200_OK) or a negative grb200_status; grb200_last_error() gives the
+ *    message of the calling thread's last failure.  The block wrappers turn GRB200_EINVAL into
+ *    std::invalid_argument, GRB200_ERANGE into std::out_of_range and the rest into std::runtime_error,
+ *    matching the exceptions of the reference blocks.
+ *  - `*_work`     : HOST buffers borrowed for the duration of the call (what gr::block::general_work hands
+ *                   over, gnuradio-runtime/include/gnuradio/block.h:176-179); blocks until the outputs are valid.
+ *                   Inputs are staged through pinned double-buffered async copies on the handle's streams.
+ *  - `*_work_dev` : DEVICE buffers (device-resident chaining mode); asynchronous on `stream`
+ *                   (a cudaStream_t passed as void*, NULL = the handle's own stream).
+ *  - One handle <-> one calling thread for work(); set_* may come from any thread (internally serialised,
+ *    mirroring d_setlock / d_mutex in the reference blocks).
+ *  - There is no CPU fallback: every call fails with GRB200_ECUDA when no sm_100 device is usable.
+ */
+#ifndef GRB200_H
+#define GRB200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    GRB200_OK = 0,
+    GRB200_EINVAL = -1, /* bad argument            -> std::invalid_argument */
+    GRB200_ERANGE = -2, /* size out of range       -> std::out_of_range     */
+    GRB200_ECUDA = -3,  /* CUDA runtime failure    -> std::runtime_error    */
+    GRB200_ENOMEM = -4, /* allocation failure      -> std::runtime_error    */
+    GRB200_EWINDOW = -5 /* window length mismatch  -> std::runtime_error ("fft_vcc: window not the same length as fft_size") */
+} grb200_status;
+
+/* ---- library / device ------------------------------------------------------------------------- */
+const char* grb200_last_error(void);
+const char* grb200_version(void);
+int grb200_device_count(void);
+/* Number of kernels this library has launched so far in the process (all handles). */
+unsigned long long grb200_launch_count(void);
+/* Pinned host buffers for callers that want zero-bounce staging (optional). */
+int grb200_host_alloc(void** ptr, unsigned long long bytes);
+int grb200_host_free(void* ptr);
+/* Device buffers for the device-resident mode (thin cudaMalloc/cudaFree/cudaMemcpy wrappers, so a C++
+ * block can chain handles without linking the CUDA runtime itself). */
+int grb200_dev_alloc(int device, void** ptr, unsigned long long bytes);
+int grb200_dev_free(int device, void* ptr);
+int grb200_memcpy_h2d(int device, void* dst_dev, const void* src_host, unsigned long long bytes);
+int grb200_memcpy_d2h(int device, void* dst_host, const void* src_dev, unsigned long long bytes);
+int grb200_dev_sync(int device);
+
+/* ---- fir_filter_ccf / fir_filter_ccc -----------------------------------------------------------
+ * Replaces gr::filter::kernel::fir_filter<gr_complex,gr_complex,float|gr_complex>
+ *   ctor/set_taps  gr-filter/lib/fir_filter.cc:21-75
+ *   filterN        gr-filter/lib/fir_filter.cc:101-108
+ *   filterNdec     gr-filter/lib/fir_filter.cc:111-121
+ * as called from fir_filter_blk_impl::work, gr-filter/lib/fir_filter_blk_impl.cc:67-90.
+ * work(): `in` holds noutput*decim + ntaps-1 items, in[0] being the oldest history item
+ * (history = ntaps, fir_filter_blk_impl.cc:41);  out[i] = sum_k taps[k] * in[i*decim + ntaps-1-k]. */
+typedef struct grb200_fir grb200_fir;
+int grb200_fir_ccf_create(int decim, const float* taps, int ntaps, int device, grb200_fir** out);
+int grb200_fir_ccc_create(int decim, const float* taps_re_im, int ntaps, int device, grb200_fir** out);
+int grb200_fir_set_taps(grb200_fir* h, const float* taps, int ntaps); /* re/im pairs for ccc */
+int grb200_fir_ntaps(const grb200_fir* h);
+int grb200_fir_decimation(const grb200_fir* h);
+int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long long noutput);
+int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long long noutput, void* stream);
+void grb200_fir_destroy(grb200_fir* h);
+
+/* ---- fft_filter_ccc ----------------------------------------------------------------------------
+ * Replaces gr::filter::kernel::fft_filter_ccc
+ *   compute_sizes  gr-filter/lib/fft_filter.cc:204-224   (fftsize = 2*2^ceil(log2 ntaps), nsamples = fftsize-ntaps+1)
+ *   set_taps       gr-filter/lib/fft_filter.cc:171-201   (zeroes the overlap state)
+ *   filter         gr-filter/lib/fft_filter.cc:241-285
+ * as called from fft_filter_ccc_impl::work, gr-filter/lib/fft_filter_ccc_impl.cc:61-78.
+ * work(): consumes noutput*decim input items (history 1) and carries the ntaps-1 item overlap between
+ * calls like the reference's d_tail; noutput must be a multiple of nsamples() (the block's output_multiple).
+ * The device computes the same linear convolution by overlap-save; the FFT length used on the device may be
+ * larger than the reference's (parity is on outputs, not on block structure). */
+typedef struct grb200_fftfilt grb200_fftfilt;
+int grb200_fftfilt_ccc_create(int decim, const float* taps_re_im, int ntaps, int device, grb200_fftfilt** out);
+int grb200_fftfilt_set_taps(grb200_fftfilt* h, const float* taps_re_im, int ntaps);
+int grb200_fftfilt_nsamples(const grb200_fftfilt* h);
+int grb200_fftfilt_ntaps(const grb200_fftfilt* h);
+int grb200_fftfilt_work(grb200_fftfilt* h, const void* in_host, void* out_host, long long noutput);
+/* Stateless device form: in_dev[0] is the oldest of ntaps-1 history items (caller supplies the halo),
+ * noutput*decim + ntaps-1 items readable. */
+int grb200_fftfilt_work_dev(grb200_fftfilt* h, const void* in_dev, void* out_dev, long long noutput, void* stream);
+void grb200_fftfilt_destroy(grb200_fftfilt* h);
+
+/* ---- pfb_channelizer_ccf -----------------------------------------------------------------------
+ * Replaces gr::filter::kernel::polyphase_filterbank (ctor/set_taps, gr-filter/lib/polyphase_filterbank.cc:22-81)
+ * and pfb_channelizer_ccf_impl: ctor checks/LUT/output multiple gr-filter/lib/pfb_channelizer_ccf_impl.cc:49-84,
+ * set_channel_map :112-124, general_work :128-193.
+ * work(): in_streams[j] (j < numchans) points at consumed + taps_per_filter items of input stream j, the first
+ * taps_per_filter being history (history = taps_per_filter+1, :101); out_streams[n] (n < nout_streams <= numchans)
+ * receives noutput items of FFT bin channel_map[n].  noutput must be a multiple of output_multiple();
+ * consumed = noutput / oversample_rate is returned through *consumed.
+ * work_interleaved_dev(): the stream_to_streams step (gr-blocks/lib/stream_to_streams_impl.cc:35-54) absorbed:
+ * `in_dev` is ONE interleaved stream (sample n of stream j at in_dev[n*numchans + j]) with
+ * taps_per_filter*numchans history items in front; `out_dev` is channel-major [nout_streams][out_stride]. */
+typedef struct grb200_pfb grb200_pfb;
+int grb200_pfb_chan_ccf_create(unsigned int numchans, const float* taps, int ntaps, float oversample_rate,
+                               int device, grb200_pfb** out);
+int grb200_pfb_chan_set_taps(grb200_pfb* h, const float* taps, int ntaps);
+int grb200_pfb_chan_set_channel_map(grb200_pfb* h, const int* map, int n);
+int grb200_pfb_chan_get_channel_map(const grb200_pfb* h, int* map, int n);
+int grb200_pfb_chan_taps_per_filter(const grb200_pfb* h);
+int grb200_pfb_chan_output_multiple(const grb200_pfb* h);
+/* branch taps d_taps[i][j] = padded[i + j*numchans]; `out` holds numchans*taps_per_filter floats */
+int grb200_pfb_chan_branch_taps(const grb200_pfb* h, float* out);
+int grb200_pfb_chan_work(grb200_pfb* h, const void* const* in_streams, void* const* out_streams,
+                         int nout_streams, long long noutput, long long* consumed);
+int grb200_pfb_chan_work_interleaved_dev(grb200_pfb* h, const void* in_dev, void* out_dev,
+                                         long long out_stride, int nout_streams, long long noutput,
+                                         void* stream);
+void grb200_pfb_chan_destroy(grb200_pfb* h);
+
+/* ---- fft_vcc (+ complex_to_mag_squared) --------------------------------------------------------
+ * Replaces gr::fft::fft_complex (gr-fft/lib/fft.cc:151-203) and fft_vcc_fftw: ctor/set_window
+ * gr-fft/lib/fft_vcc_fftw.cc:33-61, work :63-122; and complex_to_mag_squared_impl::work
+ * (gr-blocks/lib/complex_to_mag_squared_impl.cc:37-48), standalone or fused behind the FFT.
+ * Items are vectors of fft_size complex64.  Unnormalised; forward e^{-j..}, reverse e^{+j..}. */
+typedef struct grb200_fftvcc grb200_fftvcc;
+int grb200_fft_vcc_create(int fft_size, int forward, const float* window, int nwindow, int shift,
+                          int device, grb200_fftvcc** out);
+int grb200_fft_vcc_set_window(grb200_fftvcc* h, const float* window, int nwindow); /* GRB200_EWINDOW if bad */
+int grb200_fft_vcc_fft_size(const grb200_fftvcc* h);
+int grb200_fft_vcc_work(grb200_fftvcc* h, const void* in_host, void* out_host, long long nvectors);
+int grb200_fft_vcc_work_dev(grb200_fftvcc* h, const void* in_dev, void* out_dev, long long nvectors, void* stream);
+/* fused fft_vcc -> complex_to_mag_squared(vlen=fft_size): out is float32 */
+int grb200_fft_vcc_work_magsq(grb200_fftvcc* h, const void* in_host, float* out_host, long long nvectors);
+int grb200_fft_vcc_work_magsq_dev(grb200_fftvcc* h, const void* in_dev, float* out_dev, long long nvectors, void* stream);
+void grb200_fft_vcc_destroy(grb200_fftvcc* h);
+
+int grb200_magsq_work(int device, const void* in_host, float* out_host, long long nitems);
+int grb200_magsq_work_dev(int device, const void* in_dev, float* out_dev, long long nitems, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRB200_H */
