@@ -1,0 +1,107 @@
+"""ctypes binding of the C-ABI library libgrb200.so (include/grb200.h).
+
+There is no CPU fallback: if the library is missing or no sm_100 device is usable every call raises.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgrb200.so")
+
+OK, EINVAL, ERANGE, ECUDA, ENOMEM, EWINDOW = 0, -1, -2, -3, -4, -5
+
+_lib = None
+
+vp, i32, i64, u64, f32 = C.c_void_p, C.c_int, C.c_longlong, C.c_ulonglong, C.c_float
+pvp = C.POINTER(C.c_void_p)
+
+# name -> (restype, argtypes); every symbol include/grb200.h declares
+SIGNATURES = {
+    "grb200_last_error": (C.c_char_p, []),
+    "grb200_version": (C.c_char_p, []),
+    "grb200_device_count": (i32, []),
+    "grb200_launch_count": (u64, []),
+    "grb200_host_alloc": (i32, [pvp, u64]),
+    "grb200_host_free": (i32, [vp]),
+    "grb200_dev_alloc": (i32, [i32, pvp, u64]),
+    "grb200_dev_free": (i32, [i32, vp]),
+    "grb200_memcpy_h2d": (i32, [i32, vp, vp, u64]),
+    "grb200_memcpy_d2h": (i32, [i32, vp, vp, u64]),
+    "grb200_dev_sync": (i32, [i32]),
+    "grb200_fir_ccf_create": (i32, [i32, vp, i32, i32, pvp]),
+    "grb200_fir_ccc_create": (i32, [i32, vp, i32, i32, pvp]),
+    "grb200_fir_set_taps": (i32, [vp, vp, i32]),
+    "grb200_fir_ntaps": (i32, [vp]),
+    "grb200_fir_decimation": (i32, [vp]),
+    "grb200_fir_work": (i32, [vp, vp, vp, i64]),
+    "grb200_fir_work_dev": (i32, [vp, vp, vp, i64, vp]),
+    "grb200_fir_destroy": (None, [vp]),
+    "grb200_fftfilt_ccc_create": (i32, [i32, vp, i32, i32, pvp]),
+    "grb200_fftfilt_set_taps": (i32, [vp, vp, i32]),
+    "grb200_fftfilt_nsamples": (i32, [vp]),
+    "grb200_fftfilt_ntaps": (i32, [vp]),
+    "grb200_fftfilt_work": (i32, [vp, vp, vp, i64]),
+    "grb200_fftfilt_work_dev": (i32, [vp, vp, vp, i64, vp]),
+    "grb200_fftfilt_destroy": (None, [vp]),
+    "grb200_pfb_chan_ccf_create": (i32, [C.c_uint, vp, i32, f32, i32, pvp]),
+    "grb200_pfb_chan_set_taps": (i32, [vp, vp, i32]),
+    "grb200_pfb_chan_set_channel_map": (i32, [vp, vp, i32]),
+    "grb200_pfb_chan_get_channel_map": (i32, [vp, vp, i32]),
+    "grb200_pfb_chan_taps_per_filter": (i32, [vp]),
+    "grb200_pfb_chan_output_multiple": (i32, [vp]),
+    "grb200_pfb_chan_branch_taps": (i32, [vp, vp]),
+    "grb200_pfb_chan_work": (i32, [vp, pvp, pvp, i32, i64, C.POINTER(i64)]),
+    "grb200_pfb_chan_work_interleaved": (i32, [vp, vp, pvp, i32, i64, C.POINTER(i64)]),
+    "grb200_pfb_chan_work_interleaved_dev": (i32, [vp, vp, vp, i64, i32, i64, vp]),
+    "grb200_pfb_chan_destroy": (None, [vp]),
+    "grb200_fft_vcc_create": (i32, [i32, i32, vp, i32, i32, i32, pvp]),
+    "grb200_fft_vcc_set_window": (i32, [vp, vp, i32]),
+    "grb200_fft_vcc_fft_size": (i32, [vp]),
+    "grb200_fft_vcc_work": (i32, [vp, vp, vp, i64]),
+    "grb200_fft_vcc_work_dev": (i32, [vp, vp, vp, i64, vp]),
+    "grb200_fft_vcc_work_magsq": (i32, [vp, vp, vp, i64]),
+    "grb200_fft_vcc_work_magsq_dev": (i32, [vp, vp, vp, i64, vp]),
+    "grb200_fft_vcc_destroy": (None, [vp]),
+    "grb200_magsq_work": (i32, [i32, vp, vp, i64]),
+    "grb200_magsq_work_dev": (i32, [i32, vp, vp, i64, vp]),
+}
+
+
+def load_library():
+    """Load libgrb200.so and bind every declared symbol.  Raises if the CUDA extension is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "gnuradio_b200: %s is missing -- run `python __graft_entry__.py` (nvcc, sm_100a) first; "
+            "there is no CPU fallback" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def lib():
+    return load_library()
+
+
+def last_error():
+    return lib().grb200_last_error().decode("utf-8", "replace")
+
+
+def check(rc):
+    """Status -> the exception the reference block would raise."""
+    if rc == OK:
+        return
+    msg = last_error()
+    if rc == EINVAL:
+        raise ValueError(msg)  # std::invalid_argument
+    if rc == ERANGE:
+        raise IndexError(msg)  # std::out_of_range
+    if rc == ENOMEM:
+        raise MemoryError(msg)
+    raise RuntimeError(msg)  # std::runtime_error (CUDA failure, window mismatch)

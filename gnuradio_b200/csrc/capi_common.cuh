@@ -1,5 +1,6 @@
 // capi_common.cuh -- declarations shared by the C-ABI translation units.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <memory>
 #include "staging.cuh"

@@ -1,0 +1,157 @@
+// blocks_capi.cc -- drives the C++ block wrappers of include/grb200/blocks.hpp the way block_executor would
+// (general_work in chunks, the d_updated "return 0 once" protocol, consume/produce bookkeeping), behind a
+// few extern "C" entry points so tests/ can reach the C++ host side through ctypes.
+// Built into gnuradio_b200/cxx/libgrb200_blocks.so by the Makefile next to this file.
+#include <cstring>
+#include <grb200/blocks.hpp>
+
+static thread_local std::string g_what;
+
+template <class F>
+static long long guarded(F&& f)
+{
+    try {
+        return f();
+    } catch (const std::invalid_argument& e) {
+        g_what = e.what();
+        return -1;
+    } catch (const std::out_of_range& e) {
+        g_what = e.what();
+        return -2;
+    } catch (const std::runtime_error& e) {
+        g_what = e.what();
+        return -3;
+    } catch (const std::exception& e) {
+        g_what = e.what();
+        return -4;
+    }
+}
+
+// sync blocks: input holds (history-1) + consumed items; chunked like the scheduler (max `chunk` outputs per call,
+// rounded down to the output multiple)
+template <class BLK>
+static long long run_sync(BLK& blk, const char* in, char* out, long long nout, int chunk, size_t in_item, size_t out_item)
+{
+    long long produced = 0;
+    int zero_calls = 0;
+    const int D = (int)blk.decimation();
+    while (produced < nout) {
+        long long n = std::min<long long>(chunk, nout - produced);
+        n = n / blk.output_multiple() * blk.output_multiple();
+        if (n == 0)
+            break;
+        gr_vector_const_void_star ii(1, in + (size_t)produced * D * in_item);
+        gr_vector_void_star oo(1, out + (size_t)produced * out_item);
+        gr_vector_int ni(1, (int)(n * D + blk.history() - 1));
+        int r = blk.general_work((int)n, ni, ii, oo);
+        if (r < 0)
+            break;
+        if (r == 0 && ++zero_calls > 4)
+            break;
+        produced += r;
+    }
+    return produced;
+}
+
+extern "C" {
+
+const char* grbx_what(void) { return g_what.c_str(); }
+
+long long grbx_fir_run(int complex_taps, int decim, const float* taps, int ntaps, const void* in, void* out,
+                       long long nout, int chunk, int retap_after_first)
+{
+    return guarded([&]() -> long long {
+        if (complex_taps) {
+            std::vector<gr_complex> t((const gr_complex*)taps, (const gr_complex*)taps + ntaps);
+            auto b = gr::filter::fir_filter_ccc::make(decim, t);
+            if (b->history() != (unsigned)ntaps || b->taps() != t)
+                throw std::logic_error("fir_filter_ccc: history/taps accessor mismatch");
+            return run_sync(*b, (const char*)in, (char*)out, nout, chunk, 8, 8);
+        }
+        std::vector<float> t(taps, taps + ntaps);
+        auto b = gr::filter::fir_filter_ccf::make(decim, t);
+        if (b->history() != (unsigned)ntaps || b->taps() != t)
+            throw std::logic_error("fir_filter_ccf: history/taps accessor mismatch");
+        if (retap_after_first) { // set_taps mid-stream: the next work() returns 0 once, then carries on
+            b->set_taps(t);
+            gr_vector_const_void_star ii(1, in);
+            gr_vector_void_star oo(1, out);
+            if (b->work(1, ii, oo) != 0)
+                throw std::logic_error("fir_filter_ccf: work() after set_taps() must return 0 once");
+        }
+        return run_sync(*b, (const char*)in, (char*)out, nout, chunk, 8, 8);
+    });
+}
+
+long long grbx_fft_filter_run(int decim, const float* taps_re_im, int ntaps, const void* in, void* out, long long nout,
+                              int chunk, int* nsamples)
+{
+    return guarded([&]() -> long long {
+        std::vector<gr_complex> t((const gr_complex*)taps_re_im, (const gr_complex*)taps_re_im + ntaps);
+        auto b = gr::filter::fft_filter_ccc::make(decim, t, 1);
+        if (nsamples)
+            *nsamples = b->output_multiple();
+        return run_sync(*b, (const char*)in, (char*)out, nout, chunk, 8, 8);
+    });
+}
+
+long long grbx_fft_vcc_run(int fft_size, int forward, const float* window, int nwindow, int shift, const void* in,
+                           void* out, long long nvec, int chunk)
+{
+    return guarded([&]() -> long long {
+        std::vector<float> w(window, window + nwindow);
+        auto b = gr::fft::fft_vcc::make(fft_size, forward != 0, w, shift != 0, 1);
+        return run_sync(*b, (const char*)in, (char*)out, nvec, chunk, (size_t)fft_size * 8, (size_t)fft_size * 8);
+    });
+}
+
+long long grbx_magsq_run(int vlen, const void* in, float* out, long long nitems, int chunk)
+{
+    return guarded([&]() -> long long {
+        auto b = gr::blocks::complex_to_mag_squared::make((size_t)vlen);
+        return run_sync(*b, (const char*)in, (char*)out, nitems, chunk, (size_t)vlen * 8, (size_t)vlen * 4);
+    });
+}
+
+// channelizer: in_streams[j] holds T history items + consumed items; outputs written to out_streams[k][0..nout)
+long long grbx_pfb_run(unsigned nfilts, const float* taps, int ntaps, float osr, const int* cmap, int ncmap,
+                       const void* const* in_streams, void* const* out_streams, int nouts, long long nout, int chunk,
+                       long long* consumed_total)
+{
+    return guarded([&]() -> long long {
+        std::vector<float> t(taps, taps + ntaps);
+        auto b = gr::filter::pfb_channelizer_ccf::make(nfilts, t, osr);
+        if (ncmap > 0)
+            b->set_channel_map(std::vector<int>(cmap, cmap + ncmap));
+        long long produced = 0, consumed = 0;
+        int zero_calls = 0;
+        while (produced < nout) {
+            long long n = std::min<long long>(chunk, nout - produced);
+            n = n / b->output_multiple() * b->output_multiple();
+            if (n == 0)
+                break;
+            gr_vector_const_void_star ii(nfilts);
+            gr_vector_void_star oo(nouts);
+            for (unsigned j = 0; j < nfilts; j++)
+                ii[j] = (const gr_complex*)in_streams[j] + consumed;
+            for (int k = 0; k < nouts; k++)
+                oo[k] = (gr_complex*)out_streams[k] + produced;
+            gr_vector_int ni(nfilts, 0);
+            int r = b->general_work((int)n, ni, ii, oo);
+            if (r < 0)
+                break;
+            if (r == 0) {
+                if (++zero_calls > 4)
+                    break;
+                continue;
+            }
+            produced += r;
+            consumed += b->nitems_consumed_last();
+        }
+        if (consumed_total)
+            *consumed_total = consumed;
+        return produced;
+    });
+}
+
+} // extern "C"

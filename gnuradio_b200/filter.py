@@ -1,0 +1,371 @@
+"""gr-filter hot-path blocks re-hosted on libgrb200 (same names, arguments and error behaviour as the reference).
+
+  fir_filter_ccf / fir_filter_ccc   gr-filter/include/gnuradio/filter/fir_filter_blk.h:46-68,
+                                    gr-filter/lib/fir_filter_blk_impl.cc:22-90
+  fft_filter_ccc                    gr-filter/include/gnuradio/filter/fft_filter_ccc.h:43-70,
+                                    gr-filter/lib/fft_filter_ccc_impl.cc:22-78
+  pfb_channelizer_ccf               gr-filter/include/gnuradio/filter/pfb_channelizer_ccf.h:100-192,
+                                    gr-filter/lib/pfb_channelizer_ccf_impl.cc:34-193
+  pfb.channelizer_ccf               gr-filter/python/filter/pfb.py:23-50 (hier block; stream_to_streams absorbed)
+
+work()/general_work() take borrowed HOST numpy buffers like the scheduler's; *_dev variants take raw
+device pointers (ints, e.g. torch.Tensor.data_ptr()) for chained GPU blocks.  All arithmetic runs in the
+CUDA library; this module holds no compute.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .runtime import as_items, block, io_signature, sync_decimator
+
+_c64 = np.dtype(np.complex64)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class _fir_filter_blk(sync_decimator):
+    _complex_taps = False
+    _name = "fir_filter"
+
+    def __init__(self, decimation, taps, device=0):
+        L = _lib.lib()
+        if int(decimation) < 1:
+            raise ValueError("fir_filter: decimation must be >= 1")
+        sync_decimator.__init__(self, self._name, io_signature.make(1, 1, 8), io_signature.make(1, 1, 8), decimation)
+        self._device = int(device)
+        self._h = C.c_void_p()
+        t = self._conv_taps(taps)
+        create = L.grb200_fir_ccc_create if self._complex_taps else L.grb200_fir_ccf_create
+        _lib.check(create(int(decimation), _ptr(t), len(t), self._device, C.byref(self._h)))
+        self._taps = t.copy()
+        self.d_updated = False
+        self.set_history(len(t))  # fir_filter_blk_impl.cc:41
+
+    @classmethod
+    def make(cls, decimation, taps, device=0):
+        return cls(decimation, taps, device)
+
+    def _conv_taps(self, taps):
+        t = np.ascontiguousarray(taps, np.complex64 if self._complex_taps else np.float32)
+        if t.ndim != 1 or t.size < 1:
+            raise ValueError("fir_filter: at least one tap is required")
+        return t
+
+    def set_taps(self, taps):
+        t = self._conv_taps(taps)
+        with self.d_setlock:  # fir_filter_blk_impl.cc:53-59
+            _lib.check(_lib.lib().grb200_fir_set_taps(self._h, _ptr(t), len(t)))
+            self._taps = t.copy()
+            self.d_updated = True
+
+    def taps(self):
+        return self._taps.tolist()
+
+    def work(self, noutput_items, input_items, output_items):
+        with self.d_setlock:
+            if self.d_updated:  # fir_filter_blk_impl.cc:77-81
+                self.set_history(len(self._taps))
+                self.d_updated = False
+                return 0
+            n = int(noutput_items)
+            need = n * self.decimation() + len(self._taps) - 1
+            xin = as_items(input_items[0], _c64, need if n else 0, "input_items[0]")
+            out = as_items(output_items[0], _c64, n, "output_items[0]")
+            _lib.check(_lib.lib().grb200_fir_work(self._h, _ptr(xin), _ptr(out), n))
+            return n
+
+    def work_dev(self, in_dev, out_dev, noutput_items, stream=0):
+        """Device-resident mode: in_dev/out_dev are device addresses; asynchronous on `stream`."""
+        _lib.check(_lib.lib().grb200_fir_work_dev(self._h, C.c_void_p(in_dev), C.c_void_p(out_dev),
+                                                  int(noutput_items), C.c_void_p(stream)))
+        return int(noutput_items)
+
+    def process(self, xin, noutput_items):
+        """Convenience: one work() call on `xin` (history items first); returns the output array."""
+        xin = np.ascontiguousarray(xin, np.complex64)
+        out = np.empty(int(noutput_items), np.complex64)
+        if self.d_updated:
+            self.work(0, [xin], [out])
+        r = self.work(noutput_items, [xin], [out])
+        return out[:r]
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().grb200_fir_destroy(h)
+            except Exception:
+                pass
+
+
+class fir_filter_ccf(_fir_filter_blk):
+    _complex_taps = False
+    _name = "fir_filter_ccf"
+
+
+class fir_filter_ccc(_fir_filter_blk):
+    _complex_taps = True
+    _name = "fir_filter_ccc"
+
+
+class fft_filter_ccc(sync_decimator):
+    def __init__(self, decimation, taps, nthreads=1, device=0):
+        L = _lib.lib()
+        if int(decimation) < 1:
+            raise ValueError("fft_filter_ccc: decimation must be >= 1")
+        sync_decimator.__init__(self, "fft_filter_ccc", io_signature.make(1, 1, 8), io_signature.make(1, 1, 8),
+                                decimation)
+        self._h = C.c_void_p()
+        t = self._conv_taps(taps)
+        _lib.check(L.grb200_fftfilt_ccc_create(int(decimation), _ptr(t), len(t), int(device), C.byref(self._h)))
+        self._taps = t.copy()
+        self._new_taps = t.copy()
+        self._nthreads = int(nthreads)
+        self.d_updated = False
+        self.set_history(1)  # fft_filter_ccc_impl.cc:42
+        self.d_nsamples = L.grb200_fftfilt_nsamples(self._h)
+        self.set_output_multiple(self.d_nsamples)  # :46
+
+    @classmethod
+    def make(cls, decimation, taps, nthreads=1, device=0):
+        return cls(decimation, taps, nthreads, device)
+
+    @staticmethod
+    def _conv_taps(taps):
+        t = np.ascontiguousarray(taps, np.complex64)
+        if t.ndim != 1 or t.size < 1:
+            raise ValueError("fft_filter_ccc: at least one tap is required")
+        return t
+
+    def set_taps(self, taps):  # fft_filter_ccc_impl.cc:49-53: deferred to the next work()
+        self._new_taps = self._conv_taps(taps).copy()
+        self.d_updated = True
+
+    def taps(self):
+        return self._new_taps.tolist()
+
+    def set_nthreads(self, n):  # FFTW threads in the reference; the device transform has no such knob
+        self._nthreads = int(n)
+
+    def nthreads(self):
+        return self._nthreads
+
+    def nsamples(self):
+        return self.d_nsamples
+
+    def work(self, noutput_items, input_items, output_items):
+        L = _lib.lib()
+        if self.d_updated:  # fft_filter_ccc_impl.cc:68-73
+            t = self._new_taps
+            _lib.check(L.grb200_fftfilt_set_taps(self._h, _ptr(t), len(t)))
+            self._taps = t.copy()
+            self.d_nsamples = L.grb200_fftfilt_nsamples(self._h)
+            self.d_updated = False
+            self.set_output_multiple(self.d_nsamples)
+            return 0
+        n = int(noutput_items)
+        xin = as_items(input_items[0], _c64, n * self.decimation(), "input_items[0]")
+        out = as_items(output_items[0], _c64, n, "output_items[0]")
+        _lib.check(L.grb200_fftfilt_work(self._h, _ptr(xin), _ptr(out), n))
+        return n
+
+    def work_dev(self, in_dev, out_dev, noutput_items, stream=0):
+        """Stateless device form: in_dev[0] is the oldest of ntaps-1 history items."""
+        _lib.check(_lib.lib().grb200_fftfilt_work_dev(self._h, C.c_void_p(in_dev), C.c_void_p(out_dev),
+                                                      int(noutput_items), C.c_void_p(stream)))
+        return int(noutput_items)
+
+    def process(self, x, noutput_items):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.empty(int(noutput_items), np.complex64)
+        if self.d_updated:
+            self.work(0, [x], [out])
+        r = self.work(noutput_items, [x], [out])
+        return out[:r]
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().grb200_fftfilt_destroy(h)
+            except Exception:
+                pass
+
+
+class pfb_channelizer_ccf(block):
+    def __init__(self, numchans, taps, oversample_rate=1.0, device=0):
+        L = _lib.lib()
+        numchans = int(numchans)
+        block.__init__(self, "pfb_channelizer_ccf", io_signature.make(numchans, numchans, 8),
+                       io_signature.make(1, numchans, 8))
+        self._h = C.c_void_p()
+        self._M = numchans
+        t = self._conv_taps(taps)
+        _lib.check(L.grb200_pfb_chan_ccf_create(numchans, _ptr(t), len(t), float(oversample_rate), int(device),
+                                                C.byref(self._h)))
+        self.d_oversample_rate = float(oversample_rate)
+        self.set_relative_rate(self.d_oversample_rate)  # pfb_channelizer_ccf_impl.cc:55
+        self.set_output_multiple(L.grb200_pfb_chan_output_multiple(self._h))  # :81-84
+        self.d_taps_per_filter = L.grb200_pfb_chan_taps_per_filter(self._h)
+        self.set_history(self.d_taps_per_filter + 1)  # :101
+        self.d_updated = True  # the constructor goes through set_taps (:87, :102)
+
+    @classmethod
+    def make(cls, numchans, taps, oversample_rate=1.0, device=0):
+        return cls(numchans, taps, oversample_rate, device)
+
+    @staticmethod
+    def _conv_taps(taps):
+        t = np.ascontiguousarray(taps, np.float32)
+        if t.ndim != 1 or t.size < 1:
+            raise ValueError("pfb_channelizer_ccf: at least one tap is required")
+        return t
+
+    def set_taps(self, taps):
+        t = self._conv_taps(taps)
+        with self.d_setlock:  # :96-103
+            L = _lib.lib()
+            _lib.check(L.grb200_pfb_chan_set_taps(self._h, _ptr(t), len(t)))
+            self.d_taps_per_filter = L.grb200_pfb_chan_taps_per_filter(self._h)
+            self.set_history(self.d_taps_per_filter + 1)
+            self.d_updated = True
+
+    def taps(self):
+        out = np.empty((self._M, self.d_taps_per_filter), np.float32)
+        _lib.check(_lib.lib().grb200_pfb_chan_branch_taps(self._h, _ptr(out)))
+        return out.tolist()
+
+    def print_taps(self):  # polyphase_filterbank::print_taps
+        for i, row in enumerate(self.taps()):
+            print("filter[%d]: [%s]" % (i, " ".join("%.4e" % v for v in row)))
+
+    def set_channel_map(self, chan_map):
+        m = np.ascontiguousarray(chan_map, np.int32)
+        with self.d_setlock:
+            _lib.check(_lib.lib().grb200_pfb_chan_set_channel_map(self._h, _ptr(m), len(m)))
+
+    def channel_map(self):
+        m = np.empty(self._M, np.int32)
+        n = _lib.lib().grb200_pfb_chan_get_channel_map(self._h, _ptr(m), self._M)
+        return m[:n].tolist()
+
+    def taps_per_filter(self):
+        return self.d_taps_per_filter
+
+    def _toconsume(self, noutput_items):
+        return int(np.rint(np.float32(noutput_items) / np.float32(self.d_oversample_rate)))  # :158
+
+    def forecast(self, noutput_items, ninputs):
+        return [self._toconsume(noutput_items) + self.history() - 1] * ninputs
+
+    def general_work(self, noutput_items, ninput_items, input_items, output_items):
+        with self.d_setlock:
+            if self.d_updated:  # :140-143
+                self.d_updated = False
+                self.consume_each(0)
+                return 0
+            n = int(noutput_items)
+            M, T = self._M, self.d_taps_per_filter
+            if len(input_items) != M:
+                raise ValueError("pfb_channelizer_ccf: %d input streams, %d needed" % (len(input_items), M))
+            nouts = len(output_items)
+            need = self._toconsume(n) + T
+            ins = [as_items(a, _c64, need if n else 0, "input_items[%d]" % j) for j, a in enumerate(input_items)]
+            outs = [as_items(a, _c64, n, "output_items[%d]" % j) for j, a in enumerate(output_items)]
+            inp = (C.c_void_p * M)(*[a.ctypes.data for a in ins])
+            outp = (C.c_void_p * nouts)(*[a.ctypes.data for a in outs])
+            consumed = C.c_longlong(0)
+            _lib.check(_lib.lib().grb200_pfb_chan_work(self._h, inp, outp, nouts, n, C.byref(consumed)))
+            self.consume_each(consumed.value)
+            return n
+
+    def work_interleaved(self, in_interleaved, output_items, noutput_items):
+        """Host form with stream_to_streams absorbed (see pfb.channelizer_ccf)."""
+        n = int(noutput_items)
+        M, T = self._M, self.d_taps_per_filter
+        need = (self._toconsume(n) + T) * M
+        xin = as_items(in_interleaved, _c64, need if n else 0, "input")
+        nouts = len(output_items)
+        outs = [as_items(a, _c64, n, "output_items[%d]" % j) for j, a in enumerate(output_items)]
+        outp = (C.c_void_p * nouts)(*[a.ctypes.data for a in outs])
+        consumed = C.c_longlong(0)
+        with self.d_setlock:
+            self.d_updated = False
+            _lib.check(_lib.lib().grb200_pfb_chan_work_interleaved(self._h, _ptr(xin), outp, nouts, n,
+                                                                  C.byref(consumed)))
+        self.consume_each(consumed.value)
+        return n
+
+    def work_interleaved_dev(self, in_dev, out_dev, out_stride, nout_streams, noutput_items, stream=0):
+        _lib.check(_lib.lib().grb200_pfb_chan_work_interleaved_dev(
+            self._h, C.c_void_p(in_dev), C.c_void_p(out_dev), int(out_stride), int(nout_streams),
+            int(noutput_items), C.c_void_p(stream)))
+        return int(noutput_items)
+
+    def process(self, in_streams, noutput_items, nouts=None):
+        """Convenience: in_streams [M, consumed+T] (history first) -> [nouts, noutput] array."""
+        ins = np.ascontiguousarray(in_streams, np.complex64)
+        nouts = self._M if nouts is None else int(nouts)
+        outs = np.zeros((nouts, int(noutput_items)), np.complex64)
+        il, ol = [ins[j] for j in range(self._M)], [outs[j] for j in range(nouts)]
+        if self.d_updated:
+            self.general_work(0, [], il, ol)
+        r = self.general_work(noutput_items, [], il, ol)
+        return outs[:, :r]
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().grb200_pfb_chan_destroy(h)
+            except Exception:
+                pass
+
+
+class _pfb_namespace:
+    """gnuradio.filter.pfb: the Python hier blocks of gr-filter/python/filter/pfb.py."""
+
+    class channelizer_ccf:
+        """pfb.channelizer_ccf(numchans, taps, oversample_rate): ONE interleaved input stream -> numchans
+        outputs (pfb.py:30-50).  stream_to_streams + pfb_channelizer_ccf collapse into one device pass."""
+
+        def __init__(self, numchans, taps=None, oversample_rate=1, atten=100, device=0):
+            if taps is None or len(taps) == 0:
+                # pfb.py:65-72 would design taps with optfir; out of scope here
+                raise ValueError("pfb.channelizer_ccf: taps must be supplied")
+            self._numchans = int(numchans)
+            self._oversample_rate = oversample_rate
+            self.pfb = pfb_channelizer_ccf(numchans, taps, float(oversample_rate), device)
+            self.pfb.d_updated = False  # the hier block is driven whole; no first-call skip
+            self._hist = None
+
+        def set_channel_map(self, newmap):
+            self.pfb.set_channel_map(newmap)
+
+        def set_taps(self, taps):
+            self.pfb.set_taps(taps)
+            self.pfb.d_updated = False
+            self._hist = None
+
+        def taps(self):
+            return self.pfb.taps()
+
+        def run(self, x, nouts=None):
+            """Whole finite interleaved stream, zeros before t=0 (what tb.run() delivers)."""
+            M, T = self._numchans, self.pfb.taps_per_filter()
+            x = np.ascontiguousarray(x, np.complex64)
+            rows = len(x) // M
+            om = self.pfb.output_multiple()
+            R = int(round(M / float(self._oversample_rate)))
+            noutput = (rows * M // R) // om * om
+            xin = np.concatenate([np.zeros(T * M, np.complex64), x[: rows * M]])
+            nouts = M if nouts is None else int(nouts)
+            outs = np.zeros((nouts, noutput), np.complex64)
+            self.pfb.work_interleaved(xin, [outs[j] for j in range(nouts)], noutput)
+            return outs
+
+
+pfb = _pfb_namespace()

@@ -115,6 +115,11 @@ int grb200_pfb_chan_output_multiple(const grb200_pfb* h);
 int grb200_pfb_chan_branch_taps(const grb200_pfb* h, float* out);
 int grb200_pfb_chan_work(grb200_pfb* h, const void* const* in_streams, void* const* out_streams,
                          int nout_streams, long long noutput, long long* consumed);
+/* Host form of the same absorbed stream_to_streams step -- what the hier block pfb.channelizer_ccf
+ * (gr-filter/python/filter/pfb.py:43-50) computes from its single input: `in_host` holds
+ * (taps_per_filter + consumed) * numchans interleaved items, history rows first. */
+int grb200_pfb_chan_work_interleaved(grb200_pfb* h, const void* in_host, void* const* out_streams,
+                                     int nout_streams, long long noutput, long long* consumed);
 int grb200_pfb_chan_work_interleaved_dev(grb200_pfb* h, const void* in_dev, void* out_dev,
                                          long long out_stride, int nout_streams, long long noutput,
                                          void* stream);

@@ -1,0 +1,438 @@
+// grb200/blocks.hpp -- the reference's block classes re-hosted on the C-ABI (include/grb200.h).
+//
+// Host side of the drop-in boundary, C++ like the reference.  Each class keeps the reference's name,
+// make()/set_taps()/taps()/work() signatures, io_signature, history / output_multiple / relative_rate
+// declarations, locking and exception types; only the body of work() changed: it hands the scheduler's
+// borrowed buffers to libgrb200.
+//
+//   gr::filter::fir_filter_blk<IN,OUT,TAP>  gr-filter/include/gnuradio/filter/fir_filter_blk.h:46-68
+//                                           gr-filter/lib/fir_filter_blk_impl.{h,cc}
+//   gr::filter::fft_filter_ccc              gr-filter/include/gnuradio/filter/fft_filter_ccc.h:43-70
+//                                           gr-filter/lib/fft_filter_ccc_impl.{h,cc}
+//   gr::filter::pfb_channelizer_ccf         gr-filter/include/gnuradio/filter/pfb_channelizer_ccf.h:100-192
+//                                           gr-filter/lib/pfb_channelizer_ccf_impl.{h,cc}
+//   gr::fft::fft_vcc                        gr-fft/include/gnuradio/fft/fft_vcc.h:47-70, gr-fft/lib/fft_vcc_fftw.{h,cc}
+//   gr::blocks::complex_to_mag_squared      gr-blocks/lib/complex_to_mag_squared_impl.{h,cc}
+//
+// Build modes
+//   -DGRB200_WITH_GNURADIO : include the real <gnuradio/sync_decimator.h> etc. and derive from gr::block
+//                            (what a maintainer compiles inside gr-filter / gr-fft).
+//   default                : a ~60-line stand-in of the gr::block surface these classes touch
+//                            (grb200::rt below), so the wrappers compile and are unit-tested where GNU Radio
+//                            cannot be built (no Boost/VOLK/FFTW in this image).
+#ifndef GRB200_BLOCKS_HPP
+#define GRB200_BLOCKS_HPP
+
+#include <cmath>
+#include <complex>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <type_traits>
+#include <vector>
+
+#include "../grb200.h"
+
+#ifdef GRB200_WITH_GNURADIO
+#include <gnuradio/block.h>
+#include <gnuradio/io_signature.h>
+#include <gnuradio/sync_block.h>
+#include <gnuradio/sync_decimator.h>
+namespace grb200 {
+namespace rt = ::gr;
+}
+#else
+typedef std::complex<float> gr_complex;
+typedef std::vector<int> gr_vector_int;
+typedef std::vector<void*> gr_vector_void_star;
+typedef std::vector<const void*> gr_vector_const_void_star;
+namespace grb200 {
+namespace rt {
+struct io_signature {
+    int min_streams, max_streams, item_size;
+    static io_signature make(int mn, int mx, int sz) { return io_signature{ mn, mx, sz }; }
+};
+class block
+{
+public:
+    enum { WORK_CALLED_PRODUCE = -2, WORK_DONE = -1 };
+    enum tag_propagation_policy_t { TPP_DONT = 0, TPP_ALL_TO_ALL = 1, TPP_ONE_TO_ONE = 2 };
+    block(const std::string& name, io_signature in, io_signature out) : d_name(name), d_in(in), d_out(out) {}
+    virtual ~block() {}
+    const std::string& name() const { return d_name; }
+    const io_signature& input_signature() const { return d_in; }
+    const io_signature& output_signature() const { return d_out; }
+    unsigned history() const { return d_history; }
+    void set_history(unsigned h) { d_history = h; }
+    int output_multiple() const { return d_output_multiple; }
+    void set_output_multiple(int m)
+    {
+        if (m < 1)
+            throw std::invalid_argument("block::set_output_multiple");
+        d_output_multiple = m;
+    }
+    double relative_rate() const { return d_relative_rate; }
+    void set_relative_rate(double r)
+    {
+        if (r <= 0.0)
+            throw std::invalid_argument("block::set_relative_rate: relative rate must be > 0.0");
+        d_relative_rate = r;
+    }
+    void set_tag_propagation_policy(tag_propagation_policy_t p) { d_tpp = p; }
+    void consume_each(int n) { d_consumed = n; }
+    int nitems_consumed_last() const { return d_consumed; }
+    virtual int general_work(int noutput_items, gr_vector_int& ninput_items, gr_vector_const_void_star& input_items,
+                             gr_vector_void_star& output_items) = 0;
+
+protected:
+    std::mutex d_setlock;
+
+private:
+    std::string d_name;
+    io_signature d_in, d_out;
+    unsigned d_history = 1;
+    int d_output_multiple = 1;
+    double d_relative_rate = 1.0;
+    tag_propagation_policy_t d_tpp = TPP_ALL_TO_ALL;
+    int d_consumed = 0;
+};
+class sync_block : public block
+{
+public:
+    using block::block;
+    virtual int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) = 0;
+    virtual unsigned decimation() const { return 1; }
+    int general_work(int noutput_items, gr_vector_int&, gr_vector_const_void_star& input_items,
+                     gr_vector_void_star& output_items) override
+    {
+        int r = work(noutput_items, input_items, output_items); // sync_decimator.cc:45-54
+        consume_each(r > 0 ? r * (int)decimation() : 0);
+        return r;
+    }
+};
+class sync_decimator : public sync_block
+{
+public:
+    sync_decimator(const std::string& name, io_signature in, io_signature out, unsigned decimation)
+        : sync_block(name, in, out), d_decimation(decimation)
+    {
+        set_relative_rate(1.0 / decimation);
+    }
+    unsigned decimation() const override { return d_decimation; }
+
+private:
+    unsigned d_decimation;
+};
+} // namespace rt
+} // namespace grb200
+#endif
+
+namespace grb200 {
+
+// status -> the exception type the reference block throws at the same site
+inline void check(int rc)
+{
+    if (rc == GRB200_OK)
+        return;
+    const std::string msg = grb200_last_error();
+    if (rc == GRB200_EINVAL)
+        throw std::invalid_argument(msg);
+    if (rc == GRB200_ERANGE)
+        throw std::out_of_range(msg);
+    throw std::runtime_error(msg);
+}
+
+inline int default_device() { return 0; }
+
+} // namespace grb200
+
+namespace gr {
+namespace filter {
+
+// ---------------------------------------------------------------------------------------------------
+// fir_filter_blk<gr_complex, gr_complex, float|gr_complex>  (fir_filter_ccf / fir_filter_ccc)
+// ---------------------------------------------------------------------------------------------------
+template <class IN_T, class OUT_T, class TAP_T>
+class fir_filter_blk : public grb200::rt::sync_decimator
+{
+    static_assert(std::is_same<IN_T, gr_complex>::value && std::is_same<OUT_T, gr_complex>::value &&
+                      (std::is_same<TAP_T, float>::value || std::is_same<TAP_T, gr_complex>::value),
+                  "libgrb200 re-hosts the ccf and ccc instantiations (SURVEY.md section 8)");
+
+public:
+    typedef std::shared_ptr<fir_filter_blk<IN_T, OUT_T, TAP_T>> sptr;
+
+    static sptr make(int decimation, const std::vector<TAP_T>& taps)
+    {
+        return sptr(new fir_filter_blk<IN_T, OUT_T, TAP_T>(decimation, taps));
+    }
+
+    ~fir_filter_blk() override { grb200_fir_destroy(d_h); }
+
+    void set_taps(const std::vector<TAP_T>& taps)
+    {
+        std::lock_guard<std::mutex> l(d_setlock); // fir_filter_blk_impl.cc:56
+        grb200::check(grb200_fir_set_taps(d_h, reinterpret_cast<const float*>(taps.data()), (int)taps.size()));
+        d_taps = taps;
+        d_updated = true;
+    }
+    std::vector<TAP_T> taps() const { return d_taps; }
+
+    int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
+    {
+        std::lock_guard<std::mutex> l(d_setlock); // fir_filter_blk_impl.cc:72
+        if (d_updated) {                           // :77-81
+            set_history(d_taps.size());
+            d_updated = false;
+            return 0; // history requirements may have changed
+        }
+        grb200::check(grb200_fir_work(d_h, input_items[0], output_items[0], noutput_items));
+        return noutput_items;
+    }
+
+    grb200_fir* handle() { return d_h; } // device-resident chaining (grb200_fir_work_dev)
+
+private:
+    fir_filter_blk(int decimation, const std::vector<TAP_T>& taps)
+        : sync_decimator(std::is_same<TAP_T, float>::value ? "fir_filter_ccf" : "fir_filter_ccc",
+                         grb200::rt::io_signature::make(1, 1, sizeof(IN_T)),
+                         grb200::rt::io_signature::make(1, 1, sizeof(OUT_T)), decimation),
+          d_taps(taps)
+    {
+        const float* t = reinterpret_cast<const float*>(taps.data());
+        if (std::is_same<TAP_T, float>::value)
+            grb200::check(grb200_fir_ccf_create(decimation, t, (int)taps.size(), grb200::default_device(), &d_h));
+        else
+            grb200::check(grb200_fir_ccc_create(decimation, t, (int)taps.size(), grb200::default_device(), &d_h));
+        set_history(taps.size()); // fir_filter_blk_impl.cc:41
+    }
+    grb200_fir* d_h = nullptr;
+    std::vector<TAP_T> d_taps;
+    bool d_updated = false;
+};
+typedef fir_filter_blk<gr_complex, gr_complex, float> fir_filter_ccf;
+typedef fir_filter_blk<gr_complex, gr_complex, gr_complex> fir_filter_ccc;
+
+// ---------------------------------------------------------------------------------------------------
+// fft_filter_ccc
+// ---------------------------------------------------------------------------------------------------
+class fft_filter_ccc : public grb200::rt::sync_decimator
+{
+public:
+    typedef std::shared_ptr<fft_filter_ccc> sptr;
+    static sptr make(int decimation, const std::vector<gr_complex>& taps, int nthreads = 1)
+    {
+        return sptr(new fft_filter_ccc(decimation, taps, nthreads));
+    }
+    ~fft_filter_ccc() override { grb200_fftfilt_destroy(d_h); }
+
+    void set_taps(const std::vector<gr_complex>& taps) // fft_filter_ccc_impl.cc:49-53
+    {
+        d_new_taps = taps;
+        d_updated = true;
+    }
+    std::vector<gr_complex> taps() const { return d_new_taps; }
+    void set_nthreads(int n) { d_nthreads = n; } // FFTW knob; the device transform has none
+    int nthreads() const { return d_nthreads; }
+
+    int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
+    {
+        if (d_updated) { // fft_filter_ccc_impl.cc:68-73
+            grb200::check(grb200_fftfilt_set_taps(d_h, reinterpret_cast<const float*>(d_new_taps.data()),
+                                                  (int)d_new_taps.size()));
+            d_nsamples = grb200_fftfilt_nsamples(d_h);
+            d_updated = false;
+            set_output_multiple(d_nsamples);
+            return 0; // output multiple may have changed
+        }
+        grb200::check(grb200_fftfilt_work(d_h, input_items[0], output_items[0], noutput_items));
+        return noutput_items;
+    }
+    grb200_fftfilt* handle() { return d_h; }
+
+private:
+    fft_filter_ccc(int decimation, const std::vector<gr_complex>& taps, int nthreads)
+        : sync_decimator("fft_filter_ccc", grb200::rt::io_signature::make(1, 1, sizeof(gr_complex)),
+                         grb200::rt::io_signature::make(1, 1, sizeof(gr_complex)), decimation),
+          d_new_taps(taps), d_nthreads(nthreads)
+    {
+        set_history(1);
+        grb200::check(grb200_fftfilt_ccc_create(decimation, reinterpret_cast<const float*>(taps.data()),
+                                                (int)taps.size(), grb200::default_device(), &d_h));
+        d_nsamples = grb200_fftfilt_nsamples(d_h);
+        set_output_multiple(d_nsamples);
+    }
+    grb200_fftfilt* d_h = nullptr;
+    std::vector<gr_complex> d_new_taps;
+    int d_nsamples = 0, d_nthreads = 1;
+    bool d_updated = false;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// pfb_channelizer_ccf
+// ---------------------------------------------------------------------------------------------------
+class pfb_channelizer_ccf : public grb200::rt::block
+{
+public:
+    typedef std::shared_ptr<pfb_channelizer_ccf> sptr;
+    static sptr make(unsigned int numchans, const std::vector<float>& taps, float oversample_rate)
+    {
+        return sptr(new pfb_channelizer_ccf(numchans, taps, oversample_rate));
+    }
+    ~pfb_channelizer_ccf() override { grb200_pfb_chan_destroy(d_h); }
+
+    void set_taps(const std::vector<float>& taps) // pfb_channelizer_ccf_impl.cc:96-103
+    {
+        std::lock_guard<std::mutex> l(d_setlock);
+        grb200::check(grb200_pfb_chan_set_taps(d_h, taps.data(), (int)taps.size()));
+        set_history(grb200_pfb_chan_taps_per_filter(d_h) + 1);
+        d_updated = true;
+    }
+    std::vector<std::vector<float>> taps() const
+    {
+        const int T = grb200_pfb_chan_taps_per_filter(d_h);
+        std::vector<float> flat((size_t)d_nfilts * T);
+        grb200::check(grb200_pfb_chan_branch_taps(d_h, flat.data()));
+        std::vector<std::vector<float>> out(d_nfilts);
+        for (unsigned i = 0; i < d_nfilts; i++)
+            out[i].assign(flat.begin() + (size_t)i * T, flat.begin() + (size_t)(i + 1) * T);
+        return out;
+    }
+    void print_taps()
+    {
+        auto t = taps();
+        for (unsigned i = 0; i < d_nfilts; i++) {
+            printf("filter[%u]: [", i);
+            for (float v : t[i])
+                printf(" %.4e", v);
+            printf("]\n\n");
+        }
+    }
+    void set_channel_map(const std::vector<int>& map) // :112-124
+    {
+        std::lock_guard<std::mutex> l(d_setlock);
+        grb200::check(grb200_pfb_chan_set_channel_map(d_h, map.data(), (int)map.size()));
+    }
+    std::vector<int> channel_map() const
+    {
+        std::vector<int> m(d_nfilts);
+        int n = grb200_pfb_chan_get_channel_map(d_h, m.data(), (int)m.size());
+        m.resize(n < 0 ? 0 : n);
+        return m;
+    }
+
+    int general_work(int noutput_items, gr_vector_int&, gr_vector_const_void_star& input_items,
+                     gr_vector_void_star& output_items) override
+    {
+        std::lock_guard<std::mutex> l(d_setlock); // :133
+        if (d_updated) {                           // :140-143
+            d_updated = false;
+            return 0; // history requirements may have changed
+        }
+        long long consumed = 0;
+        grb200::check(grb200_pfb_chan_work(d_h, input_items.data(), output_items.data(), (int)output_items.size(),
+                                           noutput_items, &consumed));
+        consume_each((int)consumed); // :191
+        return noutput_items;
+    }
+    grb200_pfb* handle() { return d_h; }
+
+private:
+    pfb_channelizer_ccf(unsigned int nfilts, const std::vector<float>& taps, float oversample_rate)
+        : block("pfb_channelizer_ccf", grb200::rt::io_signature::make(nfilts, nfilts, sizeof(gr_complex)),
+                grb200::rt::io_signature::make(1, nfilts, sizeof(gr_complex))),
+          d_nfilts(nfilts)
+    {
+        grb200::check(grb200_pfb_chan_ccf_create(nfilts, taps.data(), (int)taps.size(), oversample_rate,
+                                                 grb200::default_device(), &d_h)); // throws invalid_argument (:49-53)
+        set_relative_rate(oversample_rate);                               // :55
+        set_output_multiple(grb200_pfb_chan_output_multiple(d_h));        // :81-84
+        set_history(grb200_pfb_chan_taps_per_filter(d_h) + 1);            // :101
+        d_updated = true;                                                 // ctor goes through set_taps (:87)
+        set_tag_propagation_policy(TPP_ONE_TO_ONE);                       // :91
+    }
+    grb200_pfb* d_h = nullptr;
+    unsigned d_nfilts;
+    bool d_updated = false;
+};
+
+} // namespace filter
+
+namespace fft {
+
+// ---------------------------------------------------------------------------------------------------
+// fft_vcc
+// ---------------------------------------------------------------------------------------------------
+class fft_vcc : public grb200::rt::sync_block
+{
+public:
+    typedef std::shared_ptr<fft_vcc> sptr;
+    static sptr make(int fft_size, bool forward, const std::vector<float>& window, bool shift = false,
+                     int nthreads = 1)
+    {
+        return sptr(new fft_vcc(fft_size, forward, window, shift, nthreads));
+    }
+    ~fft_vcc() override { grb200_fft_vcc_destroy(d_h); }
+    void set_nthreads(int n) { d_nthreads = n; }
+    int nthreads() const { return d_nthreads; }
+    bool set_window(const std::vector<float>& window) // fft_vcc_fftw.cc:54-61
+    {
+        if (window.empty() || window.size() == d_fft_size) {
+            grb200::check(grb200_fft_vcc_set_window(d_h, window.data(), (int)window.size()));
+            return true;
+        }
+        return false;
+    }
+    int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
+    {
+        grb200::check(grb200_fft_vcc_work(d_h, input_items[0], output_items[0], noutput_items));
+        return noutput_items;
+    }
+    grb200_fftvcc* handle() { return d_h; }
+
+private:
+    fft_vcc(int fft_size, bool forward, const std::vector<float>& window, bool shift, int nthreads)
+        : sync_block("fft_vcc_fftw", grb200::rt::io_signature::make(1, 1, fft_size * sizeof(gr_complex)),
+                     grb200::rt::io_signature::make(1, 1, fft_size * sizeof(gr_complex))),
+          d_fft_size(fft_size > 0 ? fft_size : 0), d_nthreads(nthreads)
+    {
+        // wrong window length -> std::runtime_error("fft_vcc: window not the same length as fft_size"), :46-47
+        grb200::check(grb200_fft_vcc_create(fft_size, forward ? 1 : 0, window.data(), (int)window.size(), shift ? 1 : 0,
+                                            grb200::default_device(), &d_h));
+    }
+    grb200_fftvcc* d_h = nullptr;
+    size_t d_fft_size;
+    int d_nthreads;
+};
+
+} // namespace fft
+
+namespace blocks {
+
+class complex_to_mag_squared : public grb200::rt::sync_block
+{
+public:
+    typedef std::shared_ptr<complex_to_mag_squared> sptr;
+    static sptr make(size_t vlen = 1) { return sptr(new complex_to_mag_squared(vlen)); }
+    int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
+    {
+        grb200::check(grb200_magsq_work(grb200::default_device(), input_items[0], (float*)output_items[0],
+                                        (long long)noutput_items * (long long)d_vlen));
+        return noutput_items;
+    }
+
+private:
+    explicit complex_to_mag_squared(size_t vlen)
+        : sync_block("complex_to_mag_squared", grb200::rt::io_signature::make(1, 1, sizeof(gr_complex) * vlen),
+                     grb200::rt::io_signature::make(1, 1, sizeof(float) * vlen)),
+          d_vlen(vlen)
+    {
+    }
+    size_t d_vlen;
+};
+
+} // namespace blocks
+} // namespace gr
+
+#endif // GRB200_BLOCKS_HPP

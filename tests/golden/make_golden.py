@@ -1,0 +1,128 @@
+#!/usr/bin/env python
+"""Regenerates the committed fixtures of tests/golden/ -- run in the BUILD container only (needs /root/reference).
+
+  qa_vectors.json    golden vectors lifted (by ast, nothing retyped) from the reference's own QA files:
+                     gr-fft/python/fft/qa_fft.py (32-point primes FFT, Hamming-windowed, reverse+window+shift),
+                     gr-blocks/python/blocks/qa_type_conversions.py:129-137 (complex_to_mag_squared).
+  ref_fixtures.npz   outputs of oracle/_ref/libgrref.so -- the reference's OWN fir_filter.cc, fft_filter.cc,
+                     polyphase_filterbank.cc, firdes.cc, window.cc compiled unmodified -- on seeded inputs.
+                     Inputs are stored next to the outputs so the fixtures stand alone on the GPU box.
+
+    python tests/golden/make_golden.py
+"""
+import ast
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+REF = "/root/reference"
+
+
+def _c(v):
+    return [complex(x).real for x in v], [complex(x).imag for x in v]
+
+
+def lift_qa_vectors():
+    out = {}
+    tree = ast.parse(open(os.path.join(REF, "gr-fft/python/fft/qa_fft.py")).read())
+    for node in ast.walk(tree):
+        if isinstance(node, ast.Assign) and isinstance(node.targets[0], ast.Name):
+            name = node.targets[0].id
+            if name in ("primes", "primes_transformed"):
+                out[name] = ast.literal_eval(node.value)
+        if isinstance(node, ast.FunctionDef) and node.name in ("test_window", "test_reverse_window_shift"):
+            for sub in ast.walk(node):
+                if isinstance(sub, ast.Assign) and getattr(sub.targets[0], "id", "") == "expected_result":
+                    out[node.name] = ast.literal_eval(sub.value)
+    res = {"primes": list(out["primes"])}
+    for k in ("primes_transformed", "test_window", "test_reverse_window_shift"):
+        re, im = _c(out[k])
+        res[k] = {"re": re, "im": im}
+    tree = ast.parse(open(os.path.join(REF, "gr-blocks/python/blocks/qa_type_conversions.py")).read())
+    for node in ast.walk(tree):
+        if isinstance(node, ast.FunctionDef) and node.name == "test_complex_to_mag_squared":
+            for sub in ast.walk(node):
+                if isinstance(sub, ast.Assign) and getattr(sub.targets[0], "id", "") in ("src_data", "expected_data"):
+                    v = ast.literal_eval(sub.value)
+                    if sub.targets[0].id == "src_data":
+                        re, im = _c(v)
+                        res["magsq_src"] = {"re": re, "im": im}
+                    else:
+                        res["magsq_expected"] = [float(x) for x in v]
+    return res
+
+
+def crand(rng, n):
+    return (rng.uniform(-1, 1, n) + 1j * rng.uniform(-1, 1, n)).astype(np.complex64)
+
+
+def ref_fixtures():
+    from oracle import pyoracle as po
+
+    po.build()
+    R = po.Ref()
+    rng = np.random.default_rng(20261104)
+    fx = {}
+    # ---- fir_filter_ccf / ccc ----
+    x = crand(rng, 3000)
+    fx["fir_x"] = x
+    fx["fir_taps_f"] = rng.uniform(-1, 1, 64).astype(np.float32)
+    fx["fir_taps_c"] = crand(rng, 37)
+    for D in (1, 4):
+        fx["fir_ccf_d%d" % D] = R.fir_stream(D, fx["fir_taps_f"], x)
+        fx["fir_ccc_d%d" % D] = R.fir_stream(D, fx["fir_taps_c"], x)
+    # ---- fft_filter_ccc ----
+    fx["fftfilt_x"] = crand(rng, 5000)
+    fx["fftfilt_taps"] = crand(rng, 300)
+    for D in (1, 3):
+        fx["fftfilt_d%d" % D] = R.fft_filter_ccc(D, fx["fftfilt_taps"], fx["fftfilt_x"])
+    fx["fftfilt_nsamples_300"] = np.int64(R.fft_filter_nsamples(300))
+    # ---- firdes / window (host-side tap and window generators feeding the path) ----
+    fx["lp2_qa_taps"] = R.low_pass_2(1, 25000, 2500, 500, 80, 5)  # qa_pfb_channelizer.py:37-40
+    fx["win_hamming_32"] = R.window(0, 32)
+    fx["win_bh_64"] = R.window(5, 64)
+    fx["win_bh_4096"] = R.window(5, 4096)
+    # ---- pfb_channelizer_ccf ----
+    for tag, M, nt, osr in (("a", 5, len(fx["lp2_qa_taps"]), 1.0), ("b", 8, 50, 2.0), ("c", 6, 31, 1.5)):
+        taps = fx["lp2_qa_taps"] if tag == "a" else rng.uniform(-1, 1, nt).astype(np.float32)
+        T = R.pfb_taps_per_filter(M, len(taps))
+        Rr = int(round(M / osr))
+        om = 1
+        while (om * Rr) % M:
+            om += 1
+        nout = om * 40
+        cons = nout * Rr // M
+        ins = np.concatenate([np.zeros((M, T), np.complex64), crand(rng, M * cons).reshape(M, cons)], axis=1)
+        cmap = np.arange(M, dtype=np.int32) if tag == "a" else rng.permutation(M).astype(np.int32)
+        nouts = M if tag != "c" else 4
+        y, c = R.pfb_channelizer(M, taps, osr, ins, nout, channel_map=cmap, nouts=nouts)
+        assert c == cons
+        fx["pfb_%s_taps" % tag] = taps
+        fx["pfb_%s_in" % tag] = ins
+        fx["pfb_%s_map" % tag] = cmap
+        fx["pfb_%s_out" % tag] = y
+        fx["pfb_%s_meta" % tag] = np.array([M, osr, nout, cons, T, nouts], np.float64)
+    # ---- fft_vcc ----
+    fx["vcc_x"] = crand(rng, 64 * 6)
+    w = fx["win_bh_64"]
+    for fwd in (0, 1):
+        for sh in (0, 1):
+            fx["vcc64_f%d_s%d_w" % (fwd, sh)] = R.fft_vcc(64, fwd, w, sh, fx["vcc_x"])
+            fx["vcc64_f%d_s%d" % (fwd, sh)] = R.fft_vcc(64, fwd, None, sh, fx["vcc_x"])
+    fx["vcc_x15"] = crand(rng, 15 * 3)  # odd length: ceil/floor halves of the shift differ (fft_vcc_fftw.cc:79,107)
+    for fwd in (0, 1):
+        fx["vcc15_f%d_s1" % fwd] = R.fft_vcc(15, fwd, None, 1, fx["vcc_x15"])
+    fx["magsq"] = R.mag_squared(fx["vcc_x"])
+    return fx
+
+
+if __name__ == "__main__":
+    json.dump(lift_qa_vectors(), open(os.path.join(HERE, "qa_vectors.json"), "w"), indent=0)
+    fx = ref_fixtures()
+    np.savez_compressed(os.path.join(HERE, "ref_fixtures.npz"), **fx)
+    print("wrote", len(fx), "arrays,", os.path.getsize(os.path.join(HERE, "ref_fixtures.npz")), "bytes")

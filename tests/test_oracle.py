@@ -1,0 +1,185 @@
+"""CPU: pins the oracle.  Both C layers -- the reference's own compiled sources (oracle/_ref, build container
+only) and the plain-C port (travels) -- against the committed fixtures generated from the reference sources,
+the reference QA's golden vectors, and float64 closed forms."""
+import random
+
+import numpy as np
+import pytest
+
+from common import (assert_parity, assert_tuples_almost_equal2, crand, fixtures, make_random_complex_tuple,
+                    qa_vectors, sig_source_c)
+from oracle import pyoracle as po
+
+
+def layers():
+    out = [po.Port()]
+    if po.have_ref():
+        out.append(po.Ref())
+    return out
+
+
+@pytest.fixture(params=["port", "reference"])
+def lay(request):
+    if request.param == "reference":
+        if not po.have_ref():
+            pytest.skip("oracle/_ref not built on this machine (needs /root/reference)")
+        return po.Ref()
+    return po.Port()
+
+
+def test_fir_against_reference_fixtures(lay):
+    fx = fixtures()
+    for D in (1, 4):
+        assert_parity(lay.fir_stream(D, fx["fir_taps_f"], fx["fir_x"]), fx["fir_ccf_d%d" % D], "ccf", 1e-6, 1e-5)
+        assert_parity(lay.fir_stream(D, fx["fir_taps_c"], fx["fir_x"]), fx["fir_ccc_d%d" % D], "ccc", 1e-6, 1e-5)
+        assert_parity(fx["fir_ccf_d%d" % D], po.f64_fir(D, fx["fir_taps_f"], fx["fir_x"]), "ccf f64", 1e-6, 1e-5)
+
+
+def test_fir_qa_cases(lay):
+    # gr-filter/python/filter/qa_fir_filter.py:60-129: ccf_001/002, ccc_001/003 inputs; 5 places
+    src = np.array(40 * [1 + 1j, 2 + 2j, 3 + 3j, 4 + 4j], np.complex64)
+    for taps, decs in ((np.array(20 * [0.5, 0.5], np.float32), (1, 4)),
+                       (np.array(20 * [0.5 + 1j, 0.5 + 1j], np.complex64), (1, 4))):
+        for D in decs:
+            got = lay.fir_stream(D, taps, src)
+            exp = po.f64_fir(D, taps, src)
+            assert len(got) == len(src) // D
+            np.testing.assert_allclose(got, exp, atol=0.5e-5 * 80, rtol=0)  # values reach ~80: 5 places relative
+
+
+def test_fft_filter_against_fixtures_and_f64(lay):
+    fx = fixtures()
+    assert lay.fft_filter_nsamples(300) == int(fx["fftfilt_nsamples_300"]) == 1024 - 300 + 1
+    for nt, ns in ((1, 2), (2, 3), (64, 65), (1024, 1025), (4096, 4097), (5, 12)):
+        assert lay.fft_filter_nsamples(nt) == ns  # gr-filter/lib/fft_filter.cc:208-209
+    for D in (1, 3):
+        got = lay.fft_filter_ccc(D, fx["fftfilt_taps"], fx["fftfilt_x"])
+        assert_parity(got, fx["fftfilt_d%d" % D], "fixture", 2e-6, 2e-5)
+        assert_parity(got, po.f64_fft_filter(D, fx["fftfilt_taps"], fx["fftfilt_x"], 725), "f64", 2e-6, 2e-5)
+
+
+def test_fft_filter_qa_random_trials(lay):
+    # qa_fft_filter.py:144-184 (test_ccc_004/005): seed 0, 4096 samples, fft filter vs fir filter, rel_eps 4e-4
+    random.seed(0)
+    for i in range(6):
+        src = np.array(make_random_complex_tuple(4096), np.complex64)
+        ntaps = int(random.uniform(2, 1000))
+        taps = np.array(make_random_complex_tuple(ntaps), np.complex64)
+        exp = lay.fir_stream(1, taps, src)
+        got = lay.fft_filter_ccc(1, taps, src)
+        assert_tuples_almost_equal2(exp[: len(got)], got, abs_eps=1e-9, rel_eps=4e-4 * 50)
+        assert_parity(got, exp[: len(got)], "trial %d" % i, 2e-6, 4e-5)
+    random.seed(0)
+    for i in range(6):
+        dec = i + 1
+        src = np.array(make_random_complex_tuple(4096), np.complex64)
+        taps = np.array(make_random_complex_tuple(int(random.uniform(2, 100))), np.complex64)
+        exp = lay.fir_stream(dec, taps, src)
+        got = lay.fft_filter_ccc(dec, taps, src)
+        assert_parity(got, exp[: len(got)], "dec %d" % dec, 2e-6, 4e-5)
+
+
+def test_fft_filter_chunked_state(lay):
+    # the OLA tail (d_tail) carries between filter() calls: one call == many calls
+    rng = np.random.default_rng(5)
+    x, taps = crand(rng, 7000), crand(rng, 100)
+    ns = lay.fft_filter_nsamples(100)
+    whole = lay.fft_filter_ccc(1, taps, x)
+    parts = lay.fft_filter_ccc(1, taps, x, chunk_out=ns)
+    np.testing.assert_array_equal(whole, parts)
+
+
+def test_fft_golden_vectors(lay):
+    # gr-fft/python/fft/qa_fft.py: 32-point golden vectors (Octave), abs_eps 1e-9 rel_eps 4e-4
+    q = qa_vectors()
+    primes = q["primes"]
+    src = np.array([complex(primes[2 * i], primes[2 * i + 1]) for i in range(32)], np.complex64)
+    assert_tuples_almost_equal2(q["primes_transformed"], lay.fft_vcc(32, 1, None, 0, src), 1e-9, 4e-4)
+    rev_in = (q["primes_transformed"] / 32).astype(np.complex64)
+    assert_tuples_almost_equal2(src, lay.fft_vcc(32, 0, None, 0, rev_in), 1e-9, 4e-4)
+    ham = lay.window(0, 32)
+    assert_tuples_almost_equal2(q["test_window"], lay.fft_vcc(32, 1, ham, 0, src), 1e-9, 4e-4)
+    assert_tuples_almost_equal2(q["test_reverse_window_shift"], lay.fft_vcc(32, 0, ham, 1, rev_in), 1e-9, 4e-4)
+
+
+def test_fft_vcc_fixtures_and_f64(lay):
+    fx = fixtures()
+    w = fx["win_bh_64"]
+    for fwd in (0, 1):
+        for sh in (0, 1):
+            assert_parity(lay.fft_vcc(64, fwd, w, sh, fx["vcc_x"]), fx["vcc64_f%d_s%d_w" % (fwd, sh)], "w", 2e-6, 2e-5)
+            assert_parity(lay.fft_vcc(64, fwd, None, sh, fx["vcc_x"]), fx["vcc64_f%d_s%d" % (fwd, sh)], "", 2e-6, 2e-5)
+            assert_parity(fx["vcc64_f%d_s%d_w" % (fwd, sh)], po.f64_fft_vcc(64, fwd, w, sh, fx["vcc_x"]), "f64", 2e-6, 2e-5)
+        assert_parity(lay.fft_vcc(15, fwd, None, 1, fx["vcc_x15"]), fx["vcc15_f%d_s1" % fwd], "odd", 2e-6, 2e-5)
+    with pytest.raises(RuntimeError):
+        lay.fft_vcc(64, 1, np.ones(63, np.float32), 0, fx["vcc_x"])  # fft_vcc_fftw.cc:46-47
+
+
+def test_windows_and_firdes(lay):
+    fx = fixtures()
+    np.testing.assert_allclose(lay.window(0, 32), fx["win_hamming_32"], atol=2e-7)
+    np.testing.assert_allclose(lay.window(5, 64), fx["win_bh_64"], atol=5e-7)
+    np.testing.assert_allclose(lay.window(5, 4096), fx["win_bh_4096"], atol=5e-7)
+    taps = lay.low_pass_2(1, 25000, 2500, 500, 80, 5)
+    assert len(taps) == len(fx["lp2_qa_taps"])
+    np.testing.assert_allclose(taps, fx["lp2_qa_taps"], atol=1e-7)
+
+
+def test_mag_squared(lay):
+    q, fx = qa_vectors(), fixtures()
+    np.testing.assert_allclose(lay.mag_squared(q["magsq_src"].astype(np.complex64)), q["magsq_expected"], rtol=1e-6)
+    np.testing.assert_allclose(lay.mag_squared(fx["vcc_x"]), fx["magsq"], rtol=1e-6)
+
+
+def test_channelizer_fixtures_and_closed_form(lay):
+    fx = fixtures()
+    for tag in "abc":
+        M, osr, nout, cons, T, nouts = fx["pfb_%s_meta" % tag]
+        M, nout, cons, T, nouts = int(M), int(nout), int(cons), int(T), int(nouts)
+        taps, ins, cmap = fx["pfb_%s_taps" % tag], fx["pfb_%s_in" % tag], fx["pfb_%s_map" % tag]
+        assert lay.pfb_taps_per_filter(M, len(taps)) == T
+        got, c = lay.pfb_channelizer(M, taps, float(osr), ins, nout, channel_map=cmap, nouts=nouts)
+        assert c == cons
+        assert_parity(got, fx["pfb_%s_out" % tag], "fixture " + tag, 2e-6, 2e-5)
+        # float64 closed form, channel map applied afterwards
+        hp = np.concatenate([taps, np.zeros(M * T - len(taps), np.float32)])
+        x = ins[:, T:].T.reshape(-1)
+        f64 = po.f64_channelizer(M, hp, x, nout, float(osr))[cmap[:nouts]]
+        assert_parity(got, f64, "f64 " + tag, 2e-6, 2e-5)
+    with pytest.raises(ValueError):
+        lay.pfb_channelizer(36, fx["pfb_a_taps"], 10.1334, np.zeros((36, 64), np.complex64), 4)  # :49-53
+
+
+def test_channelizer_qa_tones(lay):
+    # qa_pfb_channelizer.py:25-153: 5 tones, low_pass_2 taps, last 50 samples normalised, 3 places
+    freqs, fs, N = [110., -513., 203., -230, 121], 5000, 1000
+    M = len(freqs)
+    ifs = M * fs
+    taps = lay.low_pass_2(1, ifs, fs / 2, fs / 10, 80, 5)
+    x = np.sum([sig_source_c(ifs, f + i * fs, 1, N) for i, f in enumerate(freqs)], axis=0).astype(np.complex64)
+    T = lay.pfb_taps_per_filter(M, len(taps))
+    rows = N // M
+    ins = np.concatenate([np.zeros((M, T), np.complex64), x[: rows * M].reshape(rows, M).T], axis=1)
+    got, _ = lay.pfb_channelizer(M, taps, 1.0, ins, rows)
+    L = rows
+    delay = int(-(np.ceil(len(taps) / float(M)) - 1.0) / 2.0)
+    t = np.arange(delay, L + delay) / fs
+    for i, f in enumerate(freqs):
+        exp = np.exp(2j * np.pi * f * t)[-50:]
+        rec = got[i][-50:]
+        np.testing.assert_allclose(rec / rec[0], exp / exp[0], atol=0.5e-3 * 2)
+
+
+def test_port_matches_reference_layer_on_fresh_data():
+    if not po.have_ref():
+        pytest.skip("oracle/_ref not built here")
+    R, P = po.Ref(), po.Port()
+    rng = np.random.default_rng(99)
+    x = crand(rng, 9000)
+    for nt, D in ((1, 1), (7, 2), (64, 1), (1024, 8)):
+        t = rng.uniform(-1, 1, nt).astype(np.float32)
+        assert_parity(P.fir_stream(D, t, x), R.fir_stream(D, t, x), "fir %d/%d" % (nt, D), 1e-6, 1e-5)
+    for N in (2, 4, 8, 16, 64, 100, 4096):
+        v = crand(rng, N * 2)
+        for fwd in (0, 1):
+            assert_parity(P.fft_vcc(N, fwd, None, 1, v), R.fft_vcc(N, fwd, None, 1, v), "fft %d" % N, 2e-6, 2e-5)
