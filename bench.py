@@ -1,0 +1,570 @@
+#!/usr/bin/env python
+"""bench.py -- complex Msps of the gr-filter / gr-fft hot path on B200, with roofline and CPU baseline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+One "step" = one pass of the hot path over one batch of synthetic complex64 input that is already resident
+in HBM (`value`), launched through the C-ABI device entry points on torch's current stream and timed with CUDA
+events.  `e2e` is the same metric through the host-buffer C-ABI call (pinned host buffers, H2D + kernel + D2H
+inside the timed region).  Headline workload (BASELINE.json metric "fir_filter_ccf/pfb_channelizer_ccf at 1-8
+B200"): configs[2], pfb_channelizer_ccf 64 channels x 16 taps/branch over 2^30 samples per GPU; the other four
+configs are measured at N=1 and attached under "other_configs".  Multi-GPU: one process per GPU (torchrun),
+time-sharded stream, weak scaling; the only exchange is the taps_per_filter*numchans-sample history halo sent
+to the right neighbour over NCCL.
+
+`--impl reference` times the reference's own CPU kernels (oracle/_ref/libgrref.so = the reference sources
+compiled unmodified; the C port when that file is absent) on the host cores, for the same workload.
+"""
+import argparse
+import concurrent.futures as cf
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+HBM_FALLBACK_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md fallback
+
+
+def measured_peaks():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    except Exception:
+        return HBM_FALLBACK_GBS, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------------------------------------
+# synthetic taps / windows (host side, float64 formulas of gr-filter/lib/firdes.cc:77-119 and gr-fft/lib/window.cc:94-104)
+# ---------------------------------------------------------------------------------------------------------
+def coswindow(n, c0, c1, c2, c3=0.0):
+    M = n - 1
+    k = np.arange(n)
+    return (c0 - c1 * np.cos(2 * np.pi * k / M) + c2 * np.cos(4 * np.pi * k / M) - c3 * np.cos(6 * np.pi * k / M))
+
+
+def blackman_harris(n):
+    return coswindow(n, 0.35875, 0.48829, 0.14128, 0.01168).astype(np.float32)
+
+
+def hamming(n):
+    return coswindow(n, 0.54, 0.46, 0.0).astype(np.float32)
+
+
+def lowpass(ntaps, cutoff, window):
+    n = np.arange(ntaps) - (ntaps - 1) / 2.0
+    h = 2 * cutoff * np.sinc(2 * cutoff * n) * window.astype(np.float64)
+    return (h / h.sum()).astype(np.float32)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# workloads: each builds its device state lazily and exposes step() (device-resident) and, for the headline,
+# e2e_step() (host buffers).  alg_bytes = SURVEY.md section 8(d) algorithmic bytes per input sample.
+# ---------------------------------------------------------------------------------------------------------
+class Workload:
+    name = ""
+    block = ""
+    alg_bytes = 16.0
+    flops = 0.0
+    log2n = 30
+    kernel = ""
+    launches_per_step = 1
+    seed = 0
+
+    def __init__(self, torch, grb, device, log2n=None):
+        self.torch, self.grb, self.device = torch, grb, device
+        if log2n is not None:
+            self.log2n = log2n
+        self.n = 1 << self.log2n
+        self.stream = torch.cuda.current_stream().cuda_stream
+
+    def rand_c64(self, nitems, seed):
+        g = self.torch.Generator(device="cuda")
+        g.manual_seed(seed)
+        x = self.torch.empty(2 * nitems, dtype=self.torch.float32, device="cuda")
+        x.uniform_(-1.0, 1.0, generator=g)
+        return x
+
+    def describe(self):
+        return self.name
+
+    def free(self):
+        for k in list(self.__dict__):
+            if k.startswith("d_"):
+                delattr(self, k)
+        self.torch.cuda.empty_cache()
+
+
+class PfbChannelizer(Workload):
+    """configs[2]: pfb_channelizer_ccf 64 channels x 16 taps/branch, 2^30 samples (per GPU)."""
+    name = "pfb_channelizer_ccf 64ch x 16 taps/branch, 2^%d complex64 samples per GPU (BASELINE configs[2])"
+    block = "pfb_channelizer_ccf"
+    alg_bytes, flops, log2n, seed = 16.0, 94.0, 30, 3
+    kernel = "pfb_fast_kernel"
+    M, T = 64, 16
+
+    def setup(self):
+        M, T = self.M, self.T
+        self.taps = lowpass(M * T, 0.5 / M, blackman_harris(M * T)) * np.float32(M)
+        self.blk = self.grb.filter.pfb_channelizer_ccf(M, self.taps, 1.0, device=self.device)
+        self.nout = self.n // M
+        self.d_in = self.rand_c64(self.n + T * M, self.seed)  # history rows in front
+        self.d_out = self.torch.empty(2 * self.n, dtype=self.torch.float32, device="cuda")
+        self.halo_items = T * M
+
+    def step(self):
+        self.blk.work_interleaved_dev(self.d_in.data_ptr(), self.d_out.data_ptr(), self.nout, self.M, self.nout,
+                                      self.stream)
+
+    def describe(self):
+        return self.name % self.log2n
+
+    # -- multi-GPU: the segment's history comes from the left neighbour's tail ---------------------------
+    def halo_views(self):
+        h = 2 * self.halo_items
+        return self.d_in[:h], self.d_in[-h:]
+
+    # -- e2e through host buffers ---------------------------------------------------------------------
+    def e2e_setup(self, log2n):
+        t, M, T = self.torch, self.M, self.T
+        self.e2e_n = 1 << log2n
+        self.e2e_nout = self.e2e_n // M
+        self.h_in = t.empty(2 * (self.e2e_n + T * M), dtype=t.float32).pin_memory()
+        self.h_in.uniform_(-1, 1)
+        self.h_out = t.empty((M, 2 * self.e2e_nout), dtype=t.float32).pin_memory()
+        self.h_in_np = self.h_in.numpy().view(np.complex64)
+        self.h_out_np = [self.h_out[j].numpy().view(np.complex64) for j in range(M)]
+        self.blk_e2e = self.grb.filter.pfb_channelizer_ccf(M, self.taps, 1.0, device=self.device)
+        return 8 * (self.e2e_n + T * M), 8 * self.e2e_n
+
+    def e2e_step(self):
+        self.blk_e2e.work_interleaved(self.h_in_np, self.h_out_np, self.e2e_nout)
+
+    # -- CPU leg: one bounded slice of the same workload per thread --------------------------------------
+    def cpu_setup(self, lay, log2n):
+        rng = np.random.default_rng(self.seed)
+        M, T = self.M, self.T
+        n = 1 << log2n
+        self.cpu_nout = n // M
+        self.cpu_ins = (rng.uniform(-1, 1, (M, self.cpu_nout + T)) + 1j * rng.uniform(-1, 1, (M, self.cpu_nout + T))
+                        ).astype(np.complex64)
+        self.cpu_taps = lowpass(M * T, 0.5 / M, blackman_harris(M * T)) * np.float32(M)
+        self.cpu_lay = lay
+        return n
+
+    def cpu_call(self):
+        self.cpu_lay.pfb_channelizer(self.M, self.cpu_taps, 1.0, self.cpu_ins, self.cpu_nout)
+
+
+class FirCcf(Workload):
+    """configs[0]: fir_filter_ccf 64 taps, decim 1, 2^24 samples (4 rotating buffer sets so no step re-reads L2)."""
+    name = "fir_filter_ccf 64 taps decim 1, 2^%d samples x %d rotating buffer sets (BASELINE configs[0])"
+    block = "fir_filter_ccf"
+    alg_bytes, flops, log2n, seed = 16.0, 256.0, 24, 1
+    kernel = "fir_tiled_kernel"
+    ntaps, decim, nsets = 64, 1, 4
+
+    def setup(self):
+        self.taps = lowpass(self.ntaps, 0.1, hamming(self.ntaps))
+        self.blk = self.grb.filter.fir_filter_ccf(self.decim, self.taps, device=self.device)
+        self.nout = self.n // self.decim
+        self.d_in = [self.rand_c64(self.n + self.ntaps - 1, self.seed + i) for i in range(self.nsets)]
+        self.d_out = [self.torch.empty(2 * self.nout, dtype=self.torch.float32, device="cuda") for _ in range(self.nsets)]
+        self.launches_per_step = self.nsets
+        self.samples_per_step = self.n * self.nsets
+
+    def step(self):
+        for i in range(self.nsets):
+            self.blk.work_dev(self.d_in[i].data_ptr(), self.d_out[i].data_ptr(), self.nout, self.stream)
+
+    def describe(self):
+        return self.name % (self.log2n, self.nsets)
+
+    def cpu_setup(self, lay, log2n):
+        rng = np.random.default_rng(self.seed)
+        n = 1 << log2n
+        self.cpu_x = (rng.uniform(-1, 1, n + self.ntaps - 1) + 1j * rng.uniform(-1, 1, n + self.ntaps - 1)).astype(np.complex64)
+        self.cpu_lay, self.cpu_nout = lay, n // self.decim
+        self.cpu_taps = lowpass(self.ntaps, 0.1, hamming(self.ntaps))
+        return n
+
+    def cpu_call(self):
+        self.cpu_lay.fir(self.decim, self.cpu_taps, self.cpu_x, self.cpu_nout)
+
+
+class FirLongDecim(FirCcf):
+    """configs[3]: fir_filter_ccf 1024 taps, decim 8 (2^27 input samples per GPU)."""
+    name = "fir_filter_ccf 1024 taps decim 8, 2^%d input samples per GPU x %d set(s) (BASELINE configs[3])"
+    alg_bytes, flops, log2n, seed = 9.0, 512.0, 27, 4
+    ntaps, decim, nsets = 1024, 8, 1
+
+    def setup(self):
+        self.taps = lowpass(self.ntaps, 1.0 / 32, blackman_harris(self.ntaps))
+        self.blk = self.grb.filter.fir_filter_ccf(self.decim, self.taps, device=self.device)
+        self.nout = self.n // self.decim
+        self.d_in = [self.rand_c64(self.n + self.ntaps - 1, self.seed)]
+        self.d_out = [self.torch.empty(2 * self.nout, dtype=self.torch.float32, device="cuda")]
+        self.launches_per_step = 1
+        self.samples_per_step = self.n
+
+    def cpu_setup(self, lay, log2n):
+        n = FirCcf.cpu_setup(self, lay, log2n)
+        self.cpu_taps = lowpass(self.ntaps, 1.0 / 32, blackman_harris(self.ntaps))
+        return n
+
+
+class FftFilter(Workload):
+    """configs[1]: fft_filter_ccc 4096-tap low-pass, 2^28 samples on 1 B200."""
+    name = "fft_filter_ccc 4096 taps, 2^%d samples (BASELINE configs[1])"
+    block = "fft_filter_ccc"
+    alg_bytes, flops, log2n, seed = 16.0, 272.0, 28, 2
+    kernel = "fftfilt_ols_kernel"
+    ntaps = 4096
+
+    def setup(self):
+        self.taps = lowpass(self.ntaps, 0.05, blackman_harris(self.ntaps)).astype(np.complex64)
+        self.blk = self.grb.filter.fft_filter_ccc(1, self.taps, device=self.device)
+        ns = self.blk.nsamples()
+        self.nout = (self.n // ns) * ns  # 65520 x 4097: the block only emits whole multiples of nsamples
+        self.d_in = self.rand_c64(self.n + self.ntaps - 1, self.seed)
+        self.d_out = self.torch.empty(2 * self.nout, dtype=self.torch.float32, device="cuda")
+        self.samples_per_step = self.nout
+
+    def step(self):
+        self.blk.work_dev(self.d_in.data_ptr(), self.d_out.data_ptr(), self.nout, self.stream)
+
+    def describe(self):
+        return self.name % self.log2n
+
+    def cpu_setup(self, lay, log2n):
+        rng = np.random.default_rng(self.seed)
+        n = 1 << log2n
+        self.cpu_x = (rng.uniform(-1, 1, n) + 1j * rng.uniform(-1, 1, n)).astype(np.complex64)
+        self.cpu_taps = lowpass(self.ntaps, 0.05, blackman_harris(self.ntaps)).astype(np.complex64)
+        self.cpu_lay = lay
+        ns = lay.fft_filter_nsamples(self.ntaps)
+        return (n // ns) * ns
+
+    def cpu_call(self):
+        self.cpu_lay.fft_filter_ccc(1, self.cpu_taps, self.cpu_x)
+
+
+class FftVccMagSq(Workload):
+    """configs[4]: fft_vcc 4096-point Blackman-Harris (shift) + complex_to_mag_squared, 2^30 samples, fused."""
+    name = "fft_vcc 4096 Blackman-Harris fwd shift + complex_to_mag_squared fused, 2^%d samples (BASELINE configs[4])"
+    block = "fft_vcc+complex_to_mag_squared"
+    alg_bytes, flops, log2n, seed = 12.0, 65.0, 30, 5
+    kernel = "fft_vcc_kernel"
+    N = 4096
+
+    def setup(self):
+        self.win = blackman_harris(self.N)
+        self.blk = self.grb.fft.fft_vcc(self.N, True, self.win, True, device=self.device)
+        self.nvec = self.n // self.N
+        self.d_in = self.rand_c64(self.n, self.seed)
+        self.d_out = self.torch.empty(self.n, dtype=self.torch.float32, device="cuda")
+
+    def step(self):
+        self.blk.work_dev(self.d_in.data_ptr(), self.d_out.data_ptr(), self.nvec, self.stream, magsq=True)
+
+    def describe(self):
+        return self.name % self.log2n
+
+    def cpu_setup(self, lay, log2n):
+        rng = np.random.default_rng(self.seed)
+        n = 1 << log2n
+        self.cpu_x = (rng.uniform(-1, 1, n) + 1j * rng.uniform(-1, 1, n)).astype(np.complex64)
+        self.cpu_lay, self.cpu_win = lay, blackman_harris(self.N)
+        return n
+
+    def cpu_call(self):
+        self.cpu_lay.mag_squared(self.cpu_lay.fft_vcc(self.N, True, self.cpu_win, True, self.cpu_x))
+
+
+WORKLOADS = {"pfb": PfbChannelizer, "fir": FirCcf, "fftfilt": FftFilter, "firdec": FirLongDecim, "fftvcc": FftVccMagSq}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# clocks during the timed region (NVML; the recipe's nvidia-smi line, sampled in-process)
+# ---------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                r = int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                for bit, name in self.REASONS.items():
+                    if r & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU legs (the ONLY place bench.py touches oracle/)
+# ---------------------------------------------------------------------------------------------------------
+def cpu_layer():
+    from oracle import pyoracle as po
+
+    lay = po.best()
+    return lay, lay.kind
+
+
+def cpu_run(wl_cls, threads, log2n_per_thread, reps):
+    """`threads` host threads each run the reference kernel over its own 2^log2n-sample slice, `reps` times."""
+    lay, kind = cpu_layer()
+    wl = wl_cls.__new__(wl_cls)
+    n = wl.cpu_setup(lay, log2n_per_thread)
+    wl.cpu_call()  # warm
+    t0 = time.perf_counter()
+    if threads == 1:
+        for _ in range(reps):
+            wl.cpu_call()
+    else:
+        with cf.ThreadPoolExecutor(max_workers=threads) as ex:
+            list(ex.map(lambda _: [wl.cpu_call() for _ in range(reps)], range(threads)))
+    dt = time.perf_counter() - t0
+    return n * reps * threads / dt / 1e6, kind, n * reps * threads, dt
+
+
+def run_reference_arm(args, wl_cls):
+    """--impl reference: the reference's own CPU kernels on all host cores, same workload and metric."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    threads = os.cpu_count() or 1
+    log2n = 22
+    msps_list = []
+    for _ in range(args.warmup):
+        cpu_run(wl_cls, threads, log2n, 1)
+    t_all = 0.0
+    nsamp = 0
+    for _ in range(args.steps):
+        msps, kind, n, dt = cpu_run(wl_cls, threads, log2n, 1)
+        msps_list.append(msps)
+        t_all += dt
+        nsamp += n
+    value = nsamp / t_all / 1e6
+    wl = wl_cls.__new__(wl_cls)
+    sample = "%d host threads x 2^%d-sample slices of the workload per step" % (threads, log2n)
+    line = {
+        "impl": "reference", "metric": "complex Msps (%s)" % wl_cls.block, "value": value, "unit": "Msps",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_all / max(1, args.steps),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl_cls.name.replace("%d", "n") if "%" in wl_cls.name else wl_cls.name,
+                   "cpu_impl": "oracle/_ref/libgrref.so (reference sources compiled unmodified against a VOLK/FFTW shim)"
+                   if kind == "reference" else "oracle/libgrb_oracle.so (plain-C port of the reference)"},
+        "cpu_baseline": {"value": value, "unit": "Msps", "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "Msps", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------
+def timed_steps(torch, dist, wl, steps, warmup, halo=None):
+    def one():
+        if halo is not None:
+            halo()
+        wl.step()
+
+    for _ in range(warmup):
+        one()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+        torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    ev[0].record()
+    for i in range(steps):
+        one()
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    per = [ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]
+    total = ev[0].elapsed_time(ev[steps])
+    return total, per
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="pfb", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="grb200", choices=["grb200", "reference"])
+    ap.add_argument("--log2n", type=int, default=None, help="override the workload's per-GPU sample count")
+    ap.add_argument("--no-others", action="store_true", help="skip the other BASELINE configs at N=1")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "grb200" else args.warmup
+    wl_cls = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        return run_reference_arm(args, wl_cls)
+
+    import torch
+
+    import gnuradio_b200 as grb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; libgrb200 has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    launches0 = grb.launch_count()
+
+    wl = wl_cls(torch, grb, local, args.log2n)
+    wl.setup()
+    samples_per_step = getattr(wl, "samples_per_step", wl.n)
+
+    halo = None
+    if dist is not None and hasattr(wl, "halo_views"):
+        head, tail = wl.halo_views()
+        right, left = (rank + 1) % world, (rank - 1) % world
+
+        def halo():  # the segment's history = the left neighbour's newest T*M samples (ring; rank 0 keeps zeros in a real stream)
+            ops = [dist.P2POp(dist.isend, tail, right), dist.P2POp(dist.irecv, head, left)]
+            for r in dist.batch_isend_irecv(ops):
+                r.wait()
+
+    with ClockSampler(local) as clk:
+        total_ms, per = timed_steps(torch, dist, wl, args.steps, args.warmup, halo)
+    t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    launches = grb.launch_count() - launches0
+    launches_timed = wl.launches_per_step * args.steps
+    value = samples_per_step * world * args.steps / (total_ms * 1e-3) / 1e6
+
+    peak, peak_src = measured_peaks()
+    kernel_ms = float(np.mean(per)) / wl.launches_per_step  # one dominant kernel per launch, no other work in a step
+    alg_bytes_launch = wl.alg_bytes * samples_per_step / wl.launches_per_step
+    achieved = alg_bytes_launch / (kernel_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": wl.kernel, "peak_source": peak_src,
+                "alg_bytes_per_sample": wl.alg_bytes, "alg_flops_per_sample": wl.flops,
+                "fp32_tflops": wl.flops * samples_per_step / wl.launches_per_step / (kernel_ms * 1e-3) / 1e12}
+
+    line = {
+        "metric": "complex Msps (%s)" % wl.block, "value": value, "unit": "Msps", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic (uniform complex64 in [-1,1)^2, seeded torch Philox on device)",
+        "config": {"workload": wl.describe(), "samples_per_step_per_gpu": samples_per_step,
+                   "l2": "inputs larger than L2 (%.1f GiB read per step)" % (8.0 * samples_per_step / 2 ** 30),
+                   "parallelism": "time-sharded x%d, weak scaling, %d-sample history halo over NCCL send/recv" % (
+                       world, getattr(wl, "halo_items", 0)) if world > 1 else "single GPU"},
+        "roofline": roofline, "gpu_launches": launches_timed, "gpu_launches_total_process": launches,
+    }
+
+    if rank == 0 and world == 1 and not args.no_e2e and hasattr(wl, "e2e_setup"):
+        bi, bo = wl.e2e_setup(28)
+        for _ in range(2):
+            wl.e2e_step()
+        t0 = time.perf_counter()
+        ksteps = max(3, min(args.steps, 8))
+        for _ in range(ksteps):
+            wl.e2e_step()  # blocking: returns when the host output buffers are valid
+        dt = time.perf_counter() - t0
+        line["e2e"] = {"value": wl.e2e_n * ksteps / dt / 1e6, "unit": "Msps", "h2d_bytes_per_step": bi,
+                       "d2h_bytes_per_step": bo, "steps": ksteps,
+                       "call": "grb200_pfb_chan_work_interleaved (pinned host in/out, 2^28 samples per step)",
+                       "pcie_gbs_each_way": bi * ksteps / dt / 1e9}
+        line["gpu_launches_e2e"] = grb.launch_count() - launches0 - launches
+
+    with ClockSampler(local) as _:
+        pass
+    line["clocks"] = clk.summary()
+
+    if rank == 0 and world == 1 and not args.no_others:
+        others = {}
+        wl.free()
+        for key, cls in WORKLOADS.items():
+            if key == args.workload:
+                continue
+            try:
+                o = cls(torch, grb, local)
+                o.setup()
+                sps = getattr(o, "samples_per_step", o.n)
+                tot, pr = timed_steps(torch, None, o, max(5, args.steps // 2), 3)
+                kms = float(np.mean(pr)) / o.launches_per_step
+                ach = o.alg_bytes * sps / o.launches_per_step / (kms * 1e-3) / 1e9
+                others[key] = {"workload": o.describe(), "msps": sps * len(pr) / (tot * 1e-3) / 1e6,
+                               "hbm_gbs": ach, "hbm_frac": ach / peak, "kernel_ms": kms,
+                               "fp32_tflops": o.flops * sps / o.launches_per_step / (kms * 1e-3) / 1e12}
+                o.free()
+                del o
+            except Exception as e:  # a failing side config must not hide the headline
+                others[key] = {"error": repr(e)[:200]}
+        line["other_configs"] = others
+
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        v1, kind, n1, dt1 = cpu_run(wl_cls, 1, 22, 2)
+        vN, kind, nN, dtN = cpu_run(wl_cls, cores, 22, 2)
+        line["cpu_baseline"] = {"value": vN, "unit": "Msps", "cores": cores, "kind": kind,
+                                "sample": "2 passes over a 2^22-sample slice of the workload per thread (%d threads, %.1f s); "
+                                          "1 thread = %.2f Msps (what one GNU Radio block thread delivers)" % (cores, dtN, v1),
+                                "value_1core": v1}
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -3,8 +3,8 @@
 // Replaces pfb_channelizer_ccf_impl::general_work (reference gr-filter/lib/pfb_channelizer_ccf_impl.cc:128-193)
 // on top of kernel::polyphase_filterbank (gr-filter/lib/polyphase_filterbank.cc:53-81).
 //
-// Closed form used on the device (derived from :73-77 and :157-189, checked against the literal loop in
-// tests/test_oracle.py).  With the M input streams seen as ONE interleaved stream x (stream j, item n at
+// Closed form used on the device (derived from :73-77 and :157-189, checked against the literal loop by the
+// parity tests).  With the M input streams seen as ONE interleaved stream x (stream j, item n at
 // x[n*M + j]; what stream_to_streams split apart, gr-blocks/lib/stream_to_streams_impl.cc:35-54),
 // R = M/oversample_rate, h = prototype taps zero-padded to T*M, for output index oo:
 //     P      = (oo+1)*R - 1                                   (newest interleaved sample used)

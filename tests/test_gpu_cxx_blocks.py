@@ -1,0 +1,88 @@
+"""GPU: the C++ block classes of include/grb200/blocks.hpp (make/set_taps/work, the host side a GNU Radio
+maintainer compiles) driven in scheduler-sized chunks through gnuradio_b200/cxx/libgrb200_blocks.so."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from common import assert_parity, crand
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+LL = C.c_longlong
+
+
+@pytest.fixture(scope="module")
+def drv():
+    lib = C.CDLL(os.path.join(ROOT, "gnuradio_b200", "cxx", "libgrb200_blocks.so"))
+    for f in ("grbx_fir_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run"):
+        getattr(lib, f).restype = LL
+    lib.grbx_what.restype = C.c_char_p
+    return lib
+
+
+def p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def test_cxx_fir(drv, orc):
+    rng = np.random.default_rng(1)
+    x = crand(rng, 30000)
+    for ct, nt, D in ((0, 64, 1), (0, 1024, 8), (1, 33, 2)):
+        taps = crand(rng, nt) if ct else rng.uniform(-1, 1, nt).astype(np.float32)
+        xin = np.concatenate([np.zeros(nt - 1, np.complex64), x])
+        nout = len(x) // D
+        out = np.zeros(nout, np.complex64)
+        rc = drv.grbx_fir_run(ct, D, p(taps), nt, p(xin), p(out), LL(nout), 4096, 0 if ct else 1)
+        assert rc == nout, drv.grbx_what()
+        assert_parity(out, orc.fir(D, taps, xin, nout), "c++ fir ct=%d %d/%d" % (ct, nt, D))
+    rc = drv.grbx_fir_run(0, 0, p(taps), 4, p(xin), p(out), LL(10), 4096, 0)
+    assert rc == -1  # std::invalid_argument
+
+
+def test_cxx_fft_filter(drv, orc):
+    rng = np.random.default_rng(2)
+    x, taps = crand(rng, 50000), crand(rng, 200)
+    ns = C.c_int(0)
+    nout = (len(x) // 313) * 313
+    out = np.zeros(nout, np.complex64)
+    rc = drv.grbx_fft_filter_run(1, p(taps), 200, p(x), p(out), LL(nout), 4096, C.byref(ns))
+    assert ns.value == 313 and rc == nout, drv.grbx_what()
+    assert_parity(out, orc.fft_filter_ccc(1, taps, x), "c++ fft_filter")
+
+
+def test_cxx_fft_vcc_and_magsq(drv, orc):
+    rng = np.random.default_rng(3)
+    N, nvec = 4096, 50
+    x = crand(rng, N * nvec)
+    w = orc.window(5, N)
+    out = np.zeros(N * nvec, np.complex64)
+    rc = drv.grbx_fft_vcc_run(N, 1, p(w), N, 1, p(x), p(out), LL(nvec), 1)  # one vector per work(), as in SURVEY 3.4
+    assert rc == nvec, drv.grbx_what()
+    assert_parity(out, orc.fft_vcc(N, 1, w, 1, x), "c++ fft_vcc")
+    assert drv.grbx_fft_vcc_run(N, 1, p(w), N - 1, 1, p(x), p(out), LL(nvec), 1) == -3  # std::runtime_error
+    assert drv.grbx_fft_vcc_run(0, 1, p(w), 0, 1, p(x), p(out), LL(nvec), 1) == -2      # std::out_of_range
+    m = np.zeros(N * nvec, np.float32)
+    assert drv.grbx_magsq_run(N, p(out), p(m), LL(nvec), 8) == nvec
+    assert_parity(m, orc.mag_squared(out), "c++ mag^2", 1e-6, 1e-5)
+
+
+def test_cxx_pfb(drv, orc):
+    rng = np.random.default_rng(4)
+    for M, nt, osr, nouts in ((64, 1024, 1.0, 64), (8, 50, 2.0, 5)):
+        taps = rng.uniform(-1, 1, nt).astype(np.float32)
+        T = orc.pfb_taps_per_filter(M, nt)
+        cons = 4000
+        nout = int(cons * osr)
+        ins = np.concatenate([np.zeros((M, T), np.complex64), crand(rng, M * cons).reshape(M, cons)], axis=1)
+        outs = np.zeros((nouts, nout), np.complex64)
+        cmap = rng.permutation(M).astype(np.int32)
+        inp = (C.c_void_p * M)(*[ins[j].ctypes.data for j in range(M)])
+        outp = (C.c_void_p * nouts)(*[outs[j].ctypes.data for j in range(nouts)])
+        ctot = LL(0)
+        rc = drv.grbx_pfb_run(M, p(taps), nt, C.c_float(osr), p(cmap), M, inp, outp, nouts, LL(nout), 1000, C.byref(ctot))
+        assert rc == nout and ctot.value == cons, drv.grbx_what()
+        ref, _ = orc.pfb_channelizer(M, taps, osr, ins, nout, channel_map=cmap, nouts=nouts)
+        assert_parity(outs, ref, "c++ pfb M=%d" % M)
+    assert drv.grbx_pfb_run(36, p(taps), nt, C.c_float(10.1334), None, 0, inp, outp, 1, LL(0), 10, None) == -1

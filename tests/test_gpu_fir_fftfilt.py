@@ -1,0 +1,190 @@
+"""GPU parity (through the C-ABI): fir_filter_ccf/ccc and fft_filter_ccc against the oracle, the committed
+reference fixtures and the reference QA cases.  Tolerance: north_star (NRMS <= 1e-5, max-abs <= 1e-4 x RMS)."""
+import random
+
+import numpy as np
+import pytest
+
+import sched_mock
+from common import assert_parity, assert_tuples_almost_equal2, crand, fixtures, make_random_complex_tuple
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def grb():
+    import gnuradio_b200 as g
+
+    assert g.device_count() > 0, "no CUDA device: libgrb200 has no CPU fallback"
+    return g
+
+
+def test_fir_reference_fixtures(grb):
+    fx = fixtures()
+    for D in (1, 4):
+        for kind, cls in (("ccf", grb.filter.fir_filter_ccf), ("ccc", grb.filter.fir_filter_ccc)):
+            taps = fx["fir_taps_f"] if kind == "ccf" else fx["fir_taps_c"]
+            got = sched_mock.run_sync(cls(D, taps), fx["fir_x"], max_noutput=700)
+            assert_parity(got, fx["fir_%s_d%d" % (kind, D)], "%s d%d" % (kind, D))
+
+
+def test_fir_qa_cases(grb):
+    # qa_fir_filter.py:60-129
+    src = np.array(40 * [1 + 1j, 2 + 2j, 3 + 3j, 4 + 4j], np.complex64)
+    for D in (1, 4):
+        taps = np.array(20 * [0.5, 0.5], np.float32)
+        got = sched_mock.run_sync(grb.filter.fir_filter_ccf(D, taps), src)
+        np.testing.assert_allclose(got, po.f64_fir(D, taps, src), atol=0.5e-5 * 80)
+        tc = np.array(20 * [0.5 + 1j, 0.5 + 1j], np.complex64)
+        got = sched_mock.run_sync(grb.filter.fir_filter_ccc(D, tc), src)
+        np.testing.assert_allclose(got, po.f64_fir(D, tc, src), atol=0.5e-5 * 200)
+
+
+@pytest.mark.parametrize("ntaps", [1, 2, 7, 63, 64, 65, 200, 1024, 3001])
+@pytest.mark.parametrize("decim", [1, 2, 3, 8, 25])
+def test_fir_ccf_sweep(grb, orc, ntaps, decim):
+    rng = np.random.default_rng(ntaps * 100 + decim)
+    x = crand(rng, 40000 + 13)
+    taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
+    got = sched_mock.run_sync(grb.filter.fir_filter_ccf(decim, taps), x, max_noutput=100000)
+    ref = orc.fir_stream(decim, taps, x)
+    assert_parity(got, ref, "ccf %d/%d" % (ntaps, decim))
+    assert_parity(got, po.f64_fir(decim, taps, x), "ccf f64 %d/%d" % (ntaps, decim))
+
+
+@pytest.mark.parametrize("ntaps,decim", [(1, 1), (5, 1), (64, 1), (64, 4), (257, 3), (1024, 8), (2500, 1)])
+def test_fir_ccc_sweep(grb, orc, ntaps, decim):
+    rng = np.random.default_rng(ntaps * 7 + decim)
+    x = crand(rng, 30000 + 5)
+    taps = crand(rng, ntaps)
+    got = sched_mock.run_sync(grb.filter.fir_filter_ccc(decim, taps), x, max_noutput=100000)
+    assert_parity(got, orc.fir_stream(decim, taps, x), "ccc %d/%d" % (ntaps, decim))
+    assert_parity(got, po.f64_fir(decim, taps, x), "ccc f64")
+
+
+def test_fir_scheduler_sized_chunks_equal_one_call(grb):
+    rng = np.random.default_rng(3)
+    x, taps = crand(rng, 50000), rng.uniform(-1, 1, 64).astype(np.float32)
+    a = sched_mock.run_sync(grb.filter.fir_filter_ccf(1, taps), x, max_noutput=4096)
+    b = sched_mock.run_sync(grb.filter.fir_filter_ccf(1, taps), x, max_noutput=1 << 20)
+    c = sched_mock.run_sync(grb.filter.fir_filter_ccf(1, taps), x, max_noutput=1)[:64]
+    np.testing.assert_array_equal(a, b)
+    np.testing.assert_array_equal(a[:64], c)
+
+
+def test_fir_empty_and_errors(grb):
+    blk = grb.filter.fir_filter_ccf(1, [1.0, 2.0])
+    out = np.empty(0, np.complex64)
+    assert blk.work(0, [np.zeros(1, np.complex64)], [out]) == 0
+    with pytest.raises(ValueError):
+        grb.filter.fir_filter_ccf(0, [1.0])
+    with pytest.raises(ValueError):
+        grb.filter.fir_filter_ccf(1, [])
+    with pytest.raises(ValueError):  # too few input items for the request
+        blk.work(10, [np.zeros(5, np.complex64)], [np.empty(10, np.complex64)])
+
+
+def test_fir_set_taps_midstream(grb, orc):
+    # fir_filter_blk_impl.cc:53-59,77-81: next work() returns 0 once and re-declares history
+    rng = np.random.default_rng(4)
+    x = crand(rng, 6000)
+    t1, t2 = rng.uniform(-1, 1, 16).astype(np.float32), rng.uniform(-1, 1, 40).astype(np.float32)
+    blk = grb.filter.fir_filter_ccf(1, t1)
+    xin = np.concatenate([np.zeros(15, np.complex64), x])
+    out1 = np.empty(3000, np.complex64)
+    assert blk.work(3000, [xin], [out1]) == 3000
+    blk.set_taps(t2)
+    assert blk.taps() == t2.tolist()
+    assert blk.work(100, [xin], [np.empty(100, np.complex64)]) == 0
+    assert blk.history() == 40
+    xin2 = x[3000 - 39:]  # the scheduler now presents 39 history items
+    out2 = np.empty(3000, np.complex64)
+    assert blk.work(3000, [xin2], [out2]) == 3000
+    assert_parity(out1, orc.fir_stream(1, t1, x)[:3000], "before")
+    assert_parity(out2, orc.fir_stream(1, t2, x)[3000:], "after")
+
+
+def test_fir_large_device_resident(grb, orc):
+    import torch
+
+    rng = np.random.default_rng(5)
+    n = 1 << 22
+    x = crand(rng, n + 63)
+    taps = rng.uniform(-1, 1, 64).astype(np.float32)
+    blk = grb.filter.fir_filter_ccf(1, taps)
+    xd = torch.from_numpy(x.view(np.float32)).cuda()
+    yd = torch.empty(2 * n, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    blk.work_dev(xd.data_ptr(), yd.data_ptr(), n, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    got = yd.cpu().numpy().view(np.complex64)
+    assert_parity(got, orc.fir(1, taps, x, n), "2^22 device-resident")
+
+
+# ---------------------------------------------------------------------------------------------------
+def test_fft_filter_fixtures(grb):
+    fx = fixtures()
+    for D in (1, 3):
+        blk = grb.filter.fft_filter_ccc(D, fx["fftfilt_taps"])
+        assert blk.nsamples() == 725 and blk.output_multiple() == 725
+        got = sched_mock.run_sync(blk, fx["fftfilt_x"], max_noutput=725 * 2)
+        assert_parity(got, fx["fftfilt_d%d" % D], "fixture d%d" % D)
+
+
+def test_fft_filter_qa_random_trials(grb, orc):
+    # qa_fft_filter.py:144-184: seeded random data, fft_filter_ccc against fir_filter_ccc, rel_eps 4e-4
+    random.seed(0)
+    for i in range(25):
+        src = np.array(make_random_complex_tuple(4096), np.complex64)
+        ntaps = int(random.uniform(2, 1000))
+        taps = np.array(make_random_complex_tuple(ntaps), np.complex64)
+        exp_gpu = sched_mock.run_sync(grb.filter.fir_filter_ccc(1, taps), src)
+        got = sched_mock.run_sync(grb.filter.fft_filter_ccc(1, taps), src)
+        assert len(got) == (4096 // orc.fft_filter_nsamples(ntaps)) * orc.fft_filter_nsamples(ntaps)
+        assert_parity(got, exp_gpu[: len(got)], "trial %d vs gpu fir" % i)
+        assert_parity(got, orc.fft_filter_ccc(1, taps, src), "trial %d vs oracle" % i)
+    random.seed(0)
+    for i in range(25):
+        dec = i + 1
+        src = np.array(make_random_complex_tuple(4096), np.complex64)
+        taps = np.array(make_random_complex_tuple(int(random.uniform(2, 100))), np.complex64)
+        got = sched_mock.run_sync(grb.filter.fft_filter_ccc(dec, taps, 2), src)
+        ref = orc.fft_filter_ccc(dec, taps, src)
+        assert_parity(got, ref, "dec %d" % dec)
+
+
+@pytest.mark.parametrize("ntaps", [1, 2, 31, 1024, 4096, 6000])
+def test_fft_filter_sizes(grb, orc, ntaps):
+    rng = np.random.default_rng(ntaps)
+    x, taps = crand(rng, 60000), crand(rng, ntaps) * np.float32(4.0 / max(ntaps, 4))
+    blk = grb.filter.fft_filter_ccc(1, taps)
+    assert blk.nsamples() == orc.fft_filter_nsamples(ntaps)
+    got = sched_mock.run_sync(blk, x, max_noutput=1 << 20)
+    ref = orc.fft_filter_ccc(1, taps, x)
+    assert_parity(got, ref, "ntaps %d" % ntaps)
+    assert_parity(got, po.f64_fft_filter(1, taps, x, blk.nsamples()), "f64 ntaps %d" % ntaps)
+
+
+def test_fft_filter_state_across_calls_and_set_taps(grb, orc):
+    rng = np.random.default_rng(8)
+    x, taps = crand(rng, 20000), crand(rng, 100)
+    a = sched_mock.run_sync(grb.filter.fft_filter_ccc(1, taps), x, max_noutput=157)       # one block per call
+    b = sched_mock.run_sync(grb.filter.fft_filter_ccc(1, taps), x, max_noutput=1 << 20)   # one call
+    np.testing.assert_allclose(a, b, atol=1e-5)
+    # set_taps is deferred to the next work(), which returns 0, and it zeroes the overlap state (fft_filter.cc:177-179)
+    blk = grb.filter.fft_filter_ccc(1, taps)
+    ns = blk.nsamples()
+    out = np.empty(ns * 10, np.complex64)
+    assert blk.work(ns * 10, [x], [out]) == ns * 10
+    t2 = crand(rng, 300)
+    blk.set_taps(t2)
+    assert blk.work(ns, [x], [out]) == 0
+    ns2 = blk.nsamples()
+    assert ns2 == orc.fft_filter_nsamples(300) == blk.output_multiple()
+    seg = x[ns * 10: ns * 10 + ns2 * 5]
+    out2 = np.empty(ns2 * 5, np.complex64)
+    assert blk.work(ns2 * 5, [seg], [out2]) == ns2 * 5
+    assert_parity(out2, orc.fft_filter_ccc(1, t2, seg), "fresh state after set_taps")
+    with pytest.raises(ValueError):
+        blk.work(ns2 + 1, [x], [np.empty(ns2 + 1, np.complex64)])
