@@ -82,6 +82,7 @@ class Workload:
             self.log2n = log2n
         self.n = 1 << self.log2n
         self.stream = torch.cuda.current_stream().cuda_stream
+        assert self.stream != 0, "bench needs a non-default stream (NULL selects the handle's own stream)"
 
     def rand_c64(self, nitems, seed):
         g = self.torch.Generator(device="cuda")
@@ -465,6 +466,10 @@ def main():
         dist = dist_mod
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     launches0 = grb.launch_count()
+    # a real (non-default) stream: the C-ABI treats a NULL stream as "the handle's own stream", and the CUDA
+    # events below must sit on the stream the kernels are launched on
+    bench_stream = torch.cuda.Stream()
+    torch.cuda.set_stream(bench_stream)
 
     wl = wl_cls(torch, grb, local, args.log2n)
     wl.setup()

@@ -2,6 +2,7 @@
 #pragma once
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <memory>
 #include "staging.cuh"
 
@@ -24,7 +25,19 @@ int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stri
 int streams_to_interleaved_launch(const void* in, long long in_stride, void* out, int M, long long nrows,
                                   cudaStream_t st);
 
-static const size_t kChunkBytes = 32u << 20; // staging granularity (input bytes per chunk)
+// staging granularity (input bytes per chunk); GRB200_CHUNK_MB overrides it (tuning knob, 1..1024)
+inline size_t chunk_bytes()
+{
+    static const size_t v = [] {
+        const char* e = getenv("GRB200_CHUNK_MB");
+        long mb = e ? atol(e) : 0;
+        if (mb < 1 || mb > 1024)
+            mb = 64;
+        return (size_t)mb << 20;
+    }();
+    return v;
+}
+#define kChunkBytes (grb::chunk_bytes())
 
 struct DevBuf {
     void* p = nullptr;

@@ -1,4 +1,5 @@
 // staging.cu -- library globals, device selection and the pinned double-buffered staging pipeline (K8).
+#include <algorithm>
 #include "staging.cuh"
 
 namespace grb {
@@ -43,7 +44,7 @@ int Stager::init(int dev_id)
     GRB_CUDA(cudaStreamCreateWithFlags(&s_h2d, cudaStreamNonBlocking));
     GRB_CUDA(cudaStreamCreateWithFlags(&s_exec, cudaStreamNonBlocking));
     GRB_CUDA(cudaStreamCreateWithFlags(&s_d2h, cudaStreamNonBlocking));
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < NSLOT; i++) {
         GRB_CUDA(cudaEventCreateWithFlags(&ev_h2d[i], cudaEventDisableTiming));
         GRB_CUDA(cudaEventCreateWithFlags(&ev_exec[i], cudaEventDisableTiming));
         GRB_CUDA(cudaEventCreateWithFlags(&ev_d2h[i], cudaEventDisableTiming));
@@ -60,7 +61,7 @@ void Stager::destroy()
     cudaStreamSynchronize(s_h2d);
     cudaStreamSynchronize(s_exec);
     cudaStreamSynchronize(s_d2h);
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < NSLOT; i++) {
         cudaEventDestroy(ev_h2d[i]);
         cudaEventDestroy(ev_exec[i]);
         cudaEventDestroy(ev_d2h[i]);
@@ -83,7 +84,7 @@ int Stager::reserve_dev(int which, size_t bytes)
     if (bytes <= dev_cap[which])
         return 0;
     size_t cap = bytes + bytes / 8 + 256;
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < NSLOT; i++) {
         if (dev[i][which]) {
             GRB_CUDA(cudaStreamSynchronize(s_exec));
             GRB_CUDA(cudaFree(dev[i][which]));
@@ -106,7 +107,7 @@ int Stager::reserve_pin(bool in, size_t bytes)
     if (bytes <= cap)
         return 0;
     size_t ncap = bytes + bytes / 8 + 256;
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < NSLOT; i++) {
         if (p[i]) {
             GRB_CUDA(cudaFreeHost(p[i]));
             p[i] = nullptr;
@@ -139,8 +140,8 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
         const void* pin_src;
         size_t bytes;
     };
-    std::vector<Bounce> bounce[2];
-    bool pending[2] = { false, false };
+    std::vector<Bounce> bounce[NSLOT];
+    bool pending[NSLOT] = {};
     Chunk ch;
     auto retire = [&](int slot) -> int {
         if (!pending[slot])
@@ -153,7 +154,7 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
         return 0;
     };
     for (long long c = 0; c < nchunks; c++) {
-        const int slot = (int)(c & 1);
+        const int slot = (int)(c % NSLOT);
         int rc = retire(slot);
         if (rc)
             return rc;
@@ -177,8 +178,8 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
         }
         if (need_in > pin_in_cap || need_out > pin_out_cap) {
             // growing the bounce slots invalidates in-flight copies: drain first
-            for (int s = 0; s < 2; s++)
-                if ((rc = retire(s)))
+            for (long long k = c - NSLOT + 1; k < c; k++)
+                if (k >= 0 && (rc = retire((int)(k % NSLOT))))
                     return rc;
             if ((rc = reserve_pin(true, need_in)) || (rc = reserve_pin(false, need_out)))
                 return rc;
@@ -222,11 +223,12 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
         pending[slot] = true;
     }
     // drain in submission order
-    const int first = (int)(nchunks & 1);
-    int rc = retire(first);
-    if (rc)
-        return rc;
-    return retire(first ^ 1);
+    for (long long k = std::max<long long>(0, nchunks - NSLOT); k < nchunks; k++) {
+        int rc = retire((int)(k % NSLOT));
+        if (rc)
+            return rc;
+    }
+    return 0;
 }
 
 } // namespace grb

@@ -2,7 +2,7 @@
 //
 // The scheduler hands work() borrowed HOST pointers into its circular buffers (reference
 // gnuradio-runtime/lib/buffer.cc:101-140, block.h:176-179).  A Stager splits one work() call into chunks and
-// runs  H2D(chunk c+1) | kernel(chunk c) | D2H(chunk c-1)  concurrently on three streams with two device
+// runs  H2D(chunk c+1) | kernel(chunk c) | D2H(chunk c-1)  concurrently on three streams with three device
 // slots.  Host memory that is already page-locked (grb200_host_alloc, cudaHostRegister, torch pinned
 // tensors) is copied from/to directly; pageable memory goes through pinned bounce slots owned by the Stager.
 #pragma once
@@ -20,11 +20,12 @@ struct Piece {
 struct Stager {
     int device = 0;
     cudaStream_t s_h2d = nullptr, s_exec = nullptr, s_d2h = nullptr;
-    cudaEvent_t ev_h2d[2] = { nullptr, nullptr }, ev_exec[2] = { nullptr, nullptr }, ev_d2h[2] = { nullptr, nullptr };
-    void* pin_in[2] = { nullptr, nullptr };
-    void* pin_out[2] = { nullptr, nullptr };
+    static constexpr int NSLOT = 3; // one slot in H2D, one in D2H, one of slack so neither engine waits on the host
+    cudaEvent_t ev_h2d[NSLOT] = {}, ev_exec[NSLOT] = {}, ev_d2h[NSLOT] = {};
+    void* pin_in[NSLOT] = {};
+    void* pin_out[NSLOT] = {};
     size_t pin_in_cap = 0, pin_out_cap = 0;
-    void* dev[2][3] = { { nullptr, nullptr, nullptr }, { nullptr, nullptr, nullptr } }; // [slot][in, out, scratch]
+    void* dev[NSLOT][3] = {}; // [slot][in, out, scratch]
     size_t dev_cap[3] = { 0, 0, 0 };
     bool ready = false;
 
