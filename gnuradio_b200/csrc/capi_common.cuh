@@ -22,6 +22,9 @@ int fftfilt_launch(int L, const void* in, void* out, long long nout, int ntaps, 
 int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stride, int nouts, const int* cmap,
                int identity, long long noutput, const float* h, const float2* wM, int nsm, bool allow_fast,
                cudaStream_t st);
+bool pfb_stream_supported(int M, int T, int R, const void* x);
+int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                      const float* h, const float2* wM, int nsm, cudaStream_t st);
 int streams_to_interleaved_launch(const void* in, long long in_stride, void* out, int M, long long nrows,
                                   cudaStream_t st);
 

@@ -19,9 +19,14 @@
 // [time][branch].  Phase 2: thread (time o, j) runs a two-pass radix-sqrt(M) inverse FFT over the branches
 // with lanes running over TIME, so the final stores are 256-byte runs per channel: the channel-major
 // transpose costs nothing extra.  HBM traffic is the compulsory 8 B in + 8 B out per input sample.
+#include <cstdlib>
 #include "fft.cuh"
 
 namespace grb {
+
+bool pfb_stream_supported(int M, int T, int R, const void* x);
+int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                      const float* h, const float2* wM, int nsm, cudaStream_t st);
 
 // ---- generic kernel: any M, T, rate ratio, channel map -------------------------------------------------
 __global__ void __launch_bounds__(256)
@@ -295,6 +300,8 @@ int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stri
     if (noutput <= 0)
         return 0;
     const long long nrows = T + (noutput * R) / M; // history rows + consumed rows
+    if (allow_fast && identity && pfb_stream_supported(M, T, R, x) && !getenv("GRB200_PFB_V1"))
+        return pfb_stream_launch(M, T, x, out, out_stride, nouts, noutput, h, wM, nsm, st);
     if (allow_fast && R == M && T <= 32 && (M == 16 || M == 64 || M == 256)) {
         if (M == 16)
             return launch_fast_tp<16>(T, x, out, out_stride, nouts, cmap, identity, noutput, nrows, h, wM, nsm, st);

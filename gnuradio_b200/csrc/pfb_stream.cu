@@ -1,0 +1,279 @@
+// pfb_stream.cu -- pfb_channelizer_ccf streaming kernel (K4, second generation; oversample_rate 1, identity map).
+//
+// Same closed form as pfb.cu (reference gr-filter/lib/pfb_channelizer_ccf_impl.cc:128-193 over
+// gr-filter/lib/polyphase_filterbank.cc:53-81):  v_i[o] = sum_u h[i + u*M] * x[(o + T - u)*M + (M-1-i)],
+// out_c[o] = sum_i v_i[o] e^{+j 2 pi i c / M}.
+//
+// What changed against pfb_fast_kernel, driven by its ncu capture (profiles/r1_pfb_fast_kernel_v1_ncu.txt:
+// 2x redundant L1 loads, 25 % occupancy, long-scoreboard + barrier stalls):
+//  * persistent CTAs that own a CONTIGUOUS run of output times, split into NG group runs; thread (branch i,
+//    group g) walks down its run with the last TP input samples of its branch in a register ring, so every
+//    input sample is fetched exactly once and the FIR is TP packed FFMA2 per output;
+//  * the KT x M input rows each group needs per iteration are one contiguous block of the interleaved
+//    stream: a single TMA bulk copy (cp.async.bulk, mbarrier completion) per group, issued one iteration
+//    ahead right after the FIR phase has drained the staging buffer, so HBM latency hides behind the FFT;
+//  * the M-point inverse DFT runs in place in ONE shared buffer (pass 1 writes back to the slots it read),
+//    lanes over time, so channel stores are contiguous 128-byte runs.
+// HBM traffic stays the compulsory 8 B in + 8 B out per input sample (16 B/sample, the roofline figure).
+#include <cstdlib>
+#include <type_traits>
+#include "fft.cuh"
+
+namespace grb {
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity)
+{
+    unsigned done = 0;
+    while (!done) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    }
+}
+// 1-D TMA bulk copy global -> shared, completion counted in bytes on `bar`
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+template <int M, int NT>
+struct PfbStreamGeom {
+    static constexpr int RDX = M == 16 ? 4 : (M == 64 ? 8 : 16); // sqrt(M)
+    static constexpr int NG = NT / M;                            // group runs per CTA
+    static constexpr int KT = 16;                                // output times per group per iteration
+    static constexpr int OT = NG * KT;                           // output times per CTA per iteration
+    static constexpr int LD = M + 1;                             // padded row of the [time][branch] buffer
+    static constexpr int NI = OT * RDX / NT;                     // DFT items per thread and pass
+    static constexpr int XS_BYTES = NG * KT * M * 8;
+    static constexpr int VB_BYTES = OT * LD * 8;
+    static constexpr int SMEM = XS_BYTES + VB_BYTES + M * 8 + 16;
+    static_assert(NT % M == 0 && (OT * RDX) % NT == 0, "geometry");
+};
+
+template <int M, int TP, int NT>
+__global__ void __launch_bounds__(NT)
+pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long long out_stride, int nouts,
+                  long long noutput, int T, long long nrows, const float* __restrict__ h,
+                  const float2* __restrict__ wM, int iters)
+{
+    using Geo = PfbStreamGeom<M, NT>;
+    constexpr int NG = Geo::NG, KT = Geo::KT, OT = Geo::OT, LD = Geo::LD, RDX = Geo::RDX, NI = Geo::NI;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float2* xs = reinterpret_cast<float2*>(smem_raw);                     // [NG][KT][M]
+    float2* vbuf = reinterpret_cast<float2*>(smem_raw + Geo::XS_BYTES);   // [OT][LD]
+    float2* wtab = vbuf + OT * LD;                                        // [M] e^{+j 2 pi k / M}
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(wtab + M);
+
+    const int tid = threadIdx.x;
+    const int bi = tid % M, bg = tid / M;
+    const int col = M - 1 - bi;                       // input stream feeding branch bi
+    const long long region = (long long)iters * KT;   // output times per group run
+    const long long cta0 = (long long)blockIdx.x * NG * region;
+    const long long gs = cta0 + (long long)bg * region; // this thread's first output time
+
+    for (int k = tid; k < M; k += NT)
+        wtab[k] = wM[k];
+    if (tid == 0)
+        mbar_init(bar, 1);
+
+    float taps[TP];
+#pragma unroll
+    for (int u = 0; u < TP; u++)
+        taps[u] = (u < T) ? __ldg(h + u * M + bi) : 0.f;
+
+    // register ring: after the row of output o is in, ring[(n - u) mod TP] = row (o + T - u), n = o - gs
+    float2 ring[TP];
+#pragma unroll
+    for (int u = 1; u < TP; u++) {
+        const long long r = gs + T - u;
+        ring[(TP - u) % TP] = (r >= 0 && r < nrows) ? x[r * M + col] : make_float2(0.f, 0.f);
+    }
+    ring[0] = make_float2(0.f, 0.f);
+    __syncthreads(); // barrier initialised, twiddle table written
+
+    // one elected thread streams the input: NG contiguous blocks of KT rows per iteration
+    auto issue = [&](int it) {
+        unsigned total = 0;
+        unsigned bytes[NG];
+#pragma unroll
+        for (int g = 0; g < NG; g++) {
+            const long long r0 = cta0 + (long long)g * region + (long long)it * KT + T;
+            long long nv = nrows - r0;
+            nv = nv < 0 ? 0 : (nv > KT ? KT : nv);
+            bytes[g] = (unsigned)(nv * M * 8);
+            total += bytes[g];
+        }
+        mbar_expect_tx(bar, total);
+#pragma unroll
+        for (int g = 0; g < NG; g++) {
+            const long long r0 = cta0 + (long long)g * region + (long long)it * KT + T;
+            if (bytes[g])
+                bulk_g2s(xs + g * KT * M, x + r0 * M, bytes[g], bar);
+        }
+    };
+    if (tid == 0)
+        issue(0);
+
+    auto iteration = [&](int it, auto phc) {
+        constexpr int PH = decltype(phc)::value; // ring position of this iteration's first row
+        mbar_wait(bar, it & 1);
+        // ---------------- FIR: one new row per output, TP packed FMAs ----------------
+#pragma unroll
+        for (int k = 0; k < KT; k++) {
+            ring[(PH + k) % TP] = xs[(bg * KT + k) * M + col];
+            float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int u = 0; u < TP; u += 2) {
+                a0 = __ffma2_rn(make_float2(taps[u], taps[u]), ring[(PH + k - u + 2 * TP) % TP], a0);
+                a1 = __ffma2_rn(make_float2(taps[u + 1], taps[u + 1]), ring[(PH + k - u - 1 + 2 * TP) % TP], a1);
+            }
+            vbuf[(bg * KT + k) * LD + bi] = __fadd2_rn(a0, a1);
+        }
+        __syncthreads(); // vbuf complete; xs drained
+        if (tid == 0 && it + 1 < iters)
+            issue(it + 1);
+        // ---------------- inverse DFT pass 1 (in place): y[j][k1] -> slot j + RDX*k1 ----------------
+#pragma unroll
+        for (int n = 0; n < NI; n++) {
+            const int idx = tid + n * NT;
+            const int o = idx % OT, j = idx / OT;
+            float2 v[RDX];
+#pragma unroll
+            for (int q = 0; q < RDX; q++)
+                v[q] = vbuf[o * LD + j + q * RDX];
+            dft_r<RDX, false>(v);
+#pragma unroll
+            for (int q = 0; q < RDX; q++)
+                vbuf[o * LD + j + q * RDX] = v[q];
+        }
+        __syncthreads();
+        // ---------------- pass 2: twiddle, DFT over j, channel-major stores ----------------
+#pragma unroll
+        for (int n = 0; n < NI; n++) {
+            const int idx = tid + n * NT;
+            const int o = idx % OT, k1 = idx / OT;
+            float2 a[RDX];
+#pragma unroll
+            for (int j = 0; j < RDX; j++) {
+                a[j] = vbuf[o * LD + k1 * RDX + j];
+                if (j > 0)
+                    a[j] = cmul(a[j], wtab[j * k1]);
+            }
+            dft_r<RDX, false>(a);
+            const int g = o / KT, k = o % KT;
+            const long long t = cta0 + (long long)g * region + (long long)it * KT + k;
+            if (t < noutput) {
+#pragma unroll
+                for (int k2 = 0; k2 < RDX; k2++) {
+                    const int c = k1 + RDX * k2;
+                    if (c < nouts)
+                        out[(long long)c * out_stride + t] = a[k2];
+                }
+            }
+        }
+        __syncthreads(); // pass-2 reads of vbuf are done before the next FIR phase overwrites it
+    };
+
+    if constexpr (TP <= KT) {
+        for (int it = 0; it < iters; it++)
+            iteration(it, std::integral_constant<int, 0>{});
+    } else { // TP == 2*KT: the ring position alternates between 0 and KT
+        for (int it = 0; it < iters; it += 2) {
+            iteration(it, std::integral_constant<int, 0>{});
+            if (it + 1 < iters)
+                iteration(it + 1, std::integral_constant<int, KT>{});
+        }
+    }
+}
+
+// ---- host launcher ------------------------------------------------------------------------------------
+template <int M, int TP, int NT>
+static int launch_stream(const void* x, void* out, long long out_stride, int nouts, long long noutput, int T,
+                         long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st)
+{
+    using Geo = PfbStreamGeom<M, NT>;
+    auto kern = pfb_stream_kernel<M, TP, NT>;
+    static thread_local bool configured[16] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 15]) {
+        GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo::SMEM));
+        configured[dev & 15] = true;
+    }
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, Geo::SMEM));
+    if (occ < 1)
+        occ = 1;
+    long long grid = (long long)nsm * occ;
+    const long long need = (noutput + Geo::OT - 1) / Geo::OT;
+    if (grid > need)
+        grid = need;
+    long long iters = (noutput + grid * Geo::OT - 1) / (grid * Geo::OT);
+    if (TP > Geo::KT && (iters & 1))
+        iters++;
+    grid = (noutput + iters * Geo::OT - 1) / (iters * Geo::OT); // drop CTAs the rounding left without work
+    if (iters > 0x7fffffffLL / Geo::KT)
+        return fail(GRB200_ERANGE, "pfb_channelizer: work() call too long for one launch");
+    kern<<<(unsigned)grid, NT, Geo::SMEM, st>>>((const float2*)x, (float2*)out, out_stride, nouts, noutput, T, nrows,
+                                                 h, wM, (int)iters);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+template <int M, int NT>
+static int launch_stream_tp(int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                            long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st)
+{
+    if (T <= 8)
+        return launch_stream<M, 8, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st);
+    if (T <= 16)
+        return launch_stream<M, 16, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st);
+    return launch_stream<M, 32, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st);
+}
+
+bool pfb_stream_supported(int M, int T, int R, const void* x)
+{
+    return R == M && T >= 1 && T <= 32 && (M == 16 || M == 64 || M == 256) && ((uintptr_t)x & 15) == 0;
+}
+
+// x: interleaved input with T*M history items in front (16-byte aligned); identity channel map.
+int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                      const float* h, const float2* wM, int nsm, cudaStream_t st)
+{
+    if (noutput <= 0)
+        return 0;
+    const long long nrows = T + noutput;
+    static const int nt_small = [] {
+        const char* e = getenv("GRB200_PFB_NT");
+        return (e && atoi(e) == 128) ? 128 : 256;
+    }();
+    if (M == 16)
+        return nt_small == 128 ? launch_stream_tp<16, 128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st)
+                               : launch_stream_tp<16, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+    if (M == 64)
+        return nt_small == 128 ? launch_stream_tp<64, 128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st)
+                               : launch_stream_tp<64, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+    return launch_stream_tp<256, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+}
+
+} // namespace grb
