@@ -6,15 +6,18 @@
 //
 // B200 mapping.  Writing t = D*u + p splits the decimating FIR into D undecimated correlations
 //   out[i] = sum_p sum_u g_p[u] * x_p[i+u],   x_p[m] = in[D*m + p],   g_p[u] = rev[D*u + p],
-// so every decimation uses the same sliding-window inner loop.  A CTA owns TILE = NT*R consecutive
-// outputs; it stages the D*(TILE+Upad) input samples it needs (tile + halo) into shared memory with
-// coalesced 8-byte loads, de-interleaved by phase, and the phase-major taps next to them.  Each thread
-// keeps R complex accumulators and an R-deep register ring of the input window: per tap it issues
-// 2R (ccf) or 4R (ccc) FFMA against ONE new 8-byte shared load, i.e. 4/R bytes of shared-memory traffic
-// per FFMA, which keeps the kernel on the FP32 pipe (the roofline that bounds it: 2*ntaps/D FFMA per
-// input sample vs 8+8/D HBM bytes).  Rows are padded by 2 complex every R so the 16-byte window loads of
-// a quarter-warp fall in distinct banks.  Results are transposed through shared memory so the global
-// stores are coalesced.
+// so every decimation uses the same sliding-window inner loop.  Persistent CTAs walk over tiles of
+// TILE = NT*R consecutive outputs.  A tile's D*(TILE+Upad) input samples (tile + ntaps-1 halo) are staged
+// into shared memory with cp.async (16-byte when the stream is 16-byte aligned), de-interleaved by phase;
+// with two buffers the next tile streams in while the current one is being filtered, so the FP32 pipe
+// never waits on HBM.  Each thread keeps R complex accumulators and an R-deep register ring of its input
+// window: per tap it issues R packed FFMA2 (ccf; 2R for ccc) against ONE new 8-byte shared load, i.e.
+// 4/R bytes of shared-memory traffic per FMA, which keeps the kernel on the FP32 pipe -- the roofline that
+// bounds it: 2*ntaps/D (ccf) FMA per input sample against 8+8/D HBM bytes.  Rows are padded by 2 complex
+// every R so the 16-byte window loads of a quarter-warp fall in distinct banks.  Results go through a
+// per-warp shared staging area (no CTA barrier) so the global stores are coalesced.
+#include <cstdint>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace grb {
@@ -28,56 +31,65 @@ struct TapT<true> {
     using type = float2;
 };
 
-__device__ __forceinline__ void mac(float2& acc, float h, float2 x)
+// acc += h * x on the packed pipe.  ccc: (hr + j hi)(xr + j xi) = hr*(xr, xi) + hi*(-xi, xr)
+__device__ __forceinline__ void mac2(float2& acc, float h, float2 x, float2)
 {
-    acc.x = fmaf(h, x.x, acc.x);
-    acc.y = fmaf(h, x.y, acc.y);
+    acc = __ffma2_rn(make_float2(h, h), x, acc);
 }
-__device__ __forceinline__ void mac(float2& acc, float2 h, float2 x)
+__device__ __forceinline__ void mac2(float2& acc, float2 h, float2 x, float2 xswap)
 {
-    acc.x = fmaf(h.x, x.x, acc.x);
-    acc.x = fmaf(-h.y, x.y, acc.x);
-    acc.y = fmaf(h.x, x.y, acc.y);
-    acc.y = fmaf(h.y, x.x, acc.y);
+    acc = __ffma2_rn(make_float2(h.x, h.x), x, acc);
+    acc = __ffma2_rn(make_float2(h.y, h.y), xswap, acc);
 }
 
-template <int R, bool CT>
-__global__ void __launch_bounds__(256)
-fir_tiled_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout,
-                 long long nin, int D, int Upad, const typename TapT<CT>::type* __restrict__ gtaps,
-                 int ldrow)
+__device__ __forceinline__ void cp_async8(void* dst, const void* src, unsigned src_bytes)
 {
-    using tap_t = typename TapT<CT>::type;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    float2* xs = reinterpret_cast<float2*>(smem_raw);
-    tap_t* gs = reinterpret_cast<tap_t*>(xs + (size_t)D * ldrow);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"((unsigned)__cvta_generic_to_shared(dst)),
+                 "l"(src), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, unsigned src_bytes)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"((unsigned)__cvta_generic_to_shared(dst)),
+                 "l"(src), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait()
+{
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
 
-    const int NT = blockDim.x;
-    const int tid = threadIdx.x;
-    const int TILE = NT * R;
-    const int Lm = TILE + Upad; // window positions staged per phase
-    const long long i0 = (long long)blockIdx.x * TILE;
-    const long long g0 = i0 * D;
-
-    // ---- stage taps (phase-major, zero padded on the host) ----
-    for (int e = tid; e < D * Upad; e += NT)
-        gs[e] = gtaps[e];
-
-    // ---- stage input tile + halo, de-interleaved by phase ----
+// Stage one tile (+halo) into `xs`, de-interleaved by phase and skewed by 2 complex every R.
+// Items at or beyond `nin` read as zero (cp.async src-size 0 zero-fills).
+template <int R>
+__device__ __forceinline__ void fir_stage_tile(float2* xs, const float2* __restrict__ in, long long g0, long long nin,
+                                               int D, int Lm, int ldrow, int tid, int NT, bool aligned16)
+{
     if (D == 1) {
-        for (int m = tid; m < Lm; m += NT) {
-            long long g = g0 + m;
-            float2 v = (g < nin) ? in[g] : make_float2(0.f, 0.f);
-            xs[m + 2 * (m / R)] = v;
+        if (aligned16) {
+            for (int m = 2 * tid; m < Lm; m += 2 * NT) {
+                const long long g = g0 + m;
+                long long left = nin - g;
+                left = left < 0 ? 0 : (left > 2 ? 2 : left);
+                cp_async16(xs + m + 2 * (m / R), in + (left ? g : 0), (unsigned)left * 8);
+            }
+        } else {
+            for (int m = tid; m < Lm; m += NT) {
+                const long long g = g0 + m;
+                const bool ok = g < nin;
+                cp_async8(xs + m + 2 * (m / R), in + (ok ? g : 0), ok ? 8u : 0u);
+            }
         }
     } else {
         const int total = D * Lm;
         int p = tid % D, m = tid / D;
         const int dp = NT % D, dm = NT / D;
         for (int e = tid; e < total; e += NT) {
-            long long g = g0 + e;
-            float2 v = (g < nin) ? in[g] : make_float2(0.f, 0.f);
-            xs[p * ldrow + m + 2 * (m / R)] = v;
+            const long long g = g0 + e;
+            const bool ok = g < nin;
+            cp_async8(xs + p * ldrow + m + 2 * (m / R), in + (ok ? g : 0), ok ? 8u : 0u);
             p += dp;
             m += dm;
             if (p >= D) {
@@ -86,73 +98,139 @@ fir_tiled_kernel(const float2* __restrict__ in, float2* __restrict__ out, long l
             }
         }
     }
-    __syncthreads();
+}
 
-    // ---- sliding-window multiply-accumulate ----
-    float2 acc[R];
-#pragma unroll
-    for (int r = 0; r < R; r++)
-        acc[r] = make_float2(0.f, 0.f);
+// NBUF = 2: double-buffered staging (prefetch the next tile during compute); NBUF = 1: single buffer.
+template <int R, bool CT, int NBUF>
+__global__ void __launch_bounds__(256)
+fir_tiled_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int D,
+                 int Upad, const typename TapT<CT>::type* __restrict__ gtaps, int ldrow, int aligned16)
+{
+    using tap_t = typename TapT<CT>::type;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int NT = blockDim.x;
+    const int tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5;
+    const int TILE = NT * R;
+    const int Lm = TILE + Upad; // window positions staged per phase
+    const size_t bufelems = (size_t)D * ldrow;
+    float2* xbuf = reinterpret_cast<float2*>(smem_raw);                      // [NBUF][D][ldrow]
+    float2* stage = xbuf + NBUF * bufelems + (size_t)warp * 32 * (R + 2);    // per-warp output staging
+    tap_t* gs = reinterpret_cast<tap_t*>(xbuf + NBUF * bufelems + (size_t)(NT / 32) * 32 * (R + 2));
 
-    for (int p = 0; p < D; p++) {
-        const float2* row = xs + p * ldrow + tid * (R + 2);
-        const tap_t* gp = gs + p * Upad;
-        float2 ring[R];
-#pragma unroll
-        for (int k = 0; k < R; k += 2) {
-            float4 v = *reinterpret_cast<const float4*>(row + k);
-            ring[k] = make_float2(v.x, v.y);
-            ring[k + 1] = make_float2(v.z, v.w);
+    const long long ntiles = (nout + TILE - 1) / TILE;
+    long long tile = blockIdx.x;
+    if (tile >= ntiles)
+        return;
+
+    // ---- taps (phase-major, zero padded on the host), once per CTA ----
+    for (int e = tid; e < D * Upad; e += NT)
+        gs[e] = gtaps[e];
+    fir_stage_tile<R>(xbuf, in, tile * TILE * D, nin, D, Lm, ldrow, tid, NT, aligned16 != 0);
+    cp_async_commit();
+
+    int b = 0;
+    for (; tile < ntiles; tile += gridDim.x) {
+        float2* xs = xbuf + (size_t)b * bufelems;
+        if (NBUF == 2) {
+            const long long next = tile + gridDim.x;
+            if (next < ntiles)
+                fir_stage_tile<R>(xbuf + (size_t)(b ^ 1) * bufelems, in, next * TILE * D, nin, D, Lm, ldrow, tid, NT,
+                                  aligned16 != 0);
+            cp_async_commit();
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
         }
-        for (int u0 = 0; u0 < Upad; u0 += R) {
-            const float2* nx = row + (u0 / R + 1) * (R + 2);
-            float2 xn[R];
+        __syncthreads();
+
+        // ---- sliding-window multiply-accumulate ----
+        float2 acc[R];
+#pragma unroll
+        for (int r = 0; r < R; r++)
+            acc[r] = make_float2(0.f, 0.f);
+
+        for (int p = 0; p < D; p++) {
+            const float2* row = xs + p * ldrow + tid * (R + 2);
+            const tap_t* gp = gs + p * Upad;
+            float2 ring[R], rsw[CT ? R : 1];
 #pragma unroll
             for (int k = 0; k < R; k += 2) {
-                float4 v = *reinterpret_cast<const float4*>(nx + k);
-                xn[k] = make_float2(v.x, v.y);
-                xn[k + 1] = make_float2(v.z, v.w);
+                float4 v = *reinterpret_cast<const float4*>(row + k);
+                ring[k] = make_float2(v.x, v.y);
+                ring[k + 1] = make_float2(v.z, v.w);
+                if (CT) {
+                    rsw[k] = make_float2(-v.y, v.x);
+                    rsw[k + 1] = make_float2(-v.w, v.z);
+                }
             }
-            tap_t h[R];
-            if (CT) {
+            for (int u0 = 0; u0 < Upad; u0 += R) {
+                const float2* nx = row + (u0 / R + 1) * (R + 2);
+                float2 xn[R];
 #pragma unroll
                 for (int k = 0; k < R; k += 2) {
-                    float4 v = *reinterpret_cast<const float4*>(gp + u0 + k);
-                    reinterpret_cast<float2*>(h)[k] = make_float2(v.x, v.y);
-                    reinterpret_cast<float2*>(h)[k + 1] = make_float2(v.z, v.w);
+                    float4 v = *reinterpret_cast<const float4*>(nx + k);
+                    xn[k] = make_float2(v.x, v.y);
+                    xn[k + 1] = make_float2(v.z, v.w);
                 }
-            } else {
+                tap_t hh[R];
+                if (CT) {
 #pragma unroll
-                for (int k = 0; k < R; k += 4) {
-                    float4 v = *reinterpret_cast<const float4*>(gp + u0 + k);
-                    reinterpret_cast<float*>(h)[k] = v.x;
-                    reinterpret_cast<float*>(h)[k + 1] = v.y;
-                    reinterpret_cast<float*>(h)[k + 2] = v.z;
-                    reinterpret_cast<float*>(h)[k + 3] = v.w;
+                    for (int k = 0; k < R; k += 2) {
+                        float4 v = *reinterpret_cast<const float4*>(gp + u0 + k);
+                        reinterpret_cast<float2*>(hh)[k] = make_float2(v.x, v.y);
+                        reinterpret_cast<float2*>(hh)[k + 1] = make_float2(v.z, v.w);
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < R; k += 4) {
+                        float4 v = *reinterpret_cast<const float4*>(gp + u0 + k);
+                        reinterpret_cast<float*>(hh)[k] = v.x;
+                        reinterpret_cast<float*>(hh)[k + 1] = v.y;
+                        reinterpret_cast<float*>(hh)[k + 2] = v.z;
+                        reinterpret_cast<float*>(hh)[k + 3] = v.w;
+                    }
                 }
-            }
 #pragma unroll
-            for (int uu = 0; uu < R; uu++) {
+                for (int uu = 0; uu < R; uu++) {
 #pragma unroll
-                for (int r = 0; r < R; r++)
-                    mac(acc[r], h[uu], ring[(uu + r) % R]);
-                ring[uu] = xn[uu];
+                    for (int r = 0; r < R; r++)
+                        mac2(acc[r], hh[uu], ring[(uu + r) % R], rsw[CT ? (uu + r) % R : 0]);
+                    ring[uu] = xn[uu];
+                    if (CT)
+                        rsw[uu] = make_float2(-xn[uu].y, xn[uu].x);
+                }
             }
         }
-    }
-    __syncthreads();
 
-    // ---- transpose through shared memory, coalesced store ----
-    float2* os = xs + tid * (R + 2);
+        // ---- per-warp transpose through shared staging, coalesced stores ----
+        {
+            float2* os = stage + lane * (R + 2);
 #pragma unroll
-    for (int r = 0; r < R; r += 2)
-        *reinterpret_cast<float4*>(os + r) = make_float4(acc[r].x, acc[r].y, acc[r + 1].x, acc[r + 1].y);
-    __syncthreads();
-    for (int m = tid; m < TILE; m += NT) {
-        long long i = i0 + m;
-        if (i < nout)
-            out[i] = xs[m + 2 * (m / R)];
+            for (int r = 0; r < R; r += 2)
+                *reinterpret_cast<float4*>(os + r) = make_float4(acc[r].x, acc[r].y, acc[r + 1].x, acc[r + 1].y);
+            __syncwarp();
+            const long long w0 = tile * TILE + (long long)warp * 32 * R;
+#pragma unroll
+            for (int j = 0; j < R; j++) {
+                const int m = lane + 32 * j;
+                const long long i = w0 + m;
+                if (i < nout)
+                    out[i] = stage[m + 2 * (m / R)];
+            }
+            __syncwarp();
+        }
+        __syncthreads(); // every warp is done with this buffer before it is refilled
+        if (NBUF == 2) {
+            b ^= 1;
+        } else {
+            const long long next = tile + gridDim.x;
+            if (next < ntiles)
+                fir_stage_tile<R>(xbuf, in, next * TILE * D, nin, D, Lm, ldrow, tid, NT, aligned16 != 0);
+            cp_async_commit();
+        }
     }
+    cp_async_wait<0>();
 }
 
 // Fallback for geometries whose tile does not fit shared memory (very large decimation or tap count):
@@ -169,7 +247,7 @@ fir_warp_kernel(const float2* __restrict__ in, float2* __restrict__ out, long lo
     const float2* x = in + w * D;
     float2 acc = make_float2(0.f, 0.f);
     for (int t = lane; t < ntaps; t += 32)
-        mac(acc, rev[t], x[t]);
+        mac2(acc, rev[t], x[t], make_float2(-x[t].y, x[t].x));
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) {
         acc.x += __shfl_xor_sync(0xffffffffu, acc.x, s);
@@ -181,61 +259,89 @@ fir_warp_kernel(const float2* __restrict__ in, float2* __restrict__ out, long lo
 
 // ---- host-side launch ---------------------------------------------------------------------------
 struct FirPlan {
-    int R = 0, NT = 0, Upad = 0, ldrow = 0;
+    int R = 0, NT = 0, NBUF = 0, Upad = 0, ldrow = 0;
     size_t smem = 0;
     bool tiled = false;
 };
+
+static size_t fir_smem(int D, int Upad, bool ct, int R, int NT, int NBUF, int* ldrow_out)
+{
+    const int Lm = NT * R + Upad;
+    const int ldrow = Lm / R * (R + 2);
+    if (ldrow_out)
+        *ldrow_out = ldrow;
+    return (size_t)NBUF * D * ldrow * 8 + (size_t)NT * (R + 2) * 8 + (size_t)D * Upad * (ct ? 8 : 4);
+}
 
 static FirPlan plan_fir(int D, int ntaps, bool ct)
 {
     FirPlan best;
     const int U = (ntaps + D - 1) / D;
-    const int Upad = ((U + 15) / 16) * 16;
-    const size_t tapsz = ct ? 8 : 4;
-    const int cand[6][2] = { { 16, 256 }, { 16, 128 }, { 8, 256 }, { 8, 128 }, { 8, 64 }, { 8, 32 } };
-    for (int pass = 0; pass < 2 && !best.tiled; pass++) {
-        const size_t limit = pass == 0 ? 110 * 1024 : 220 * 1024;
-        for (auto& c : cand) {
-            const int R = c[0], NT = c[1];
-            const int Lm = NT * R + Upad;
-            const int ldrow = Lm / R * (R + 2);
-            const size_t smem = (size_t)D * ldrow * 8 + (size_t)D * Upad * tapsz;
-            if (smem <= limit) {
-                best.R = R;
-                best.NT = NT;
-                best.Upad = Upad;
-                best.ldrow = ldrow;
-                best.smem = smem;
-                best.tiled = true;
-                break;
-            }
+    best.Upad = ((U + 15) / 16) * 16;
+    const size_t two_per_sm = 113 * 1024, one_per_sm = 226 * 1024;
+    auto take = [&](int R, int NT, int NBUF, size_t limit) {
+        if (best.tiled || (ct && R == 16))
+            return;
+        int ld = 0;
+        const size_t s = fir_smem(D, best.Upad, ct, R, NT, NBUF, &ld);
+        if (s <= limit) {
+            best.R = R, best.NT = NT, best.NBUF = NBUF, best.ldrow = ld, best.smem = s, best.tiled = true;
         }
+    };
+    if (const char* e = getenv("GRB200_FIR_PLAN")) { // tuning knob: "R,NT,NBUF"
+        int R = 0, NT = 0, NB = 0;
+        if (sscanf(e, "%d,%d,%d", &R, &NT, &NB) == 3 && (R == 8 || R == 16) && NT >= 32 && NT <= 256 && NT % 32 == 0 &&
+            (NB == 1 || NB == 2))
+            take(R, NT, NB, one_per_sm);
     }
-    if (!best.tiled)
-        best.Upad = Upad;
+    const int cand[4][2] = { { 16, 256 }, { 16, 128 }, { 8, 256 }, { 8, 128 } };
+    for (auto& c : cand)
+        take(c[0], c[1], 2, two_per_sm);
+    for (auto& c : cand)
+        take(c[0], c[1], 1, two_per_sm);
+    take(8, 64, 2, two_per_sm);
+    take(8, 64, 1, two_per_sm);
+    for (auto& c : cand)
+        take(c[0], c[1], 1, one_per_sm);
+    take(8, 64, 1, one_per_sm);
+    take(8, 32, 1, one_per_sm);
     return best;
 }
 
-template <int R, bool CT>
-static int launch_tiled(const FirPlan& pl, const void* in, void* out, long long nout, long long nin,
-                        int D, const void* gtaps, cudaStream_t st)
+template <int R, bool CT, int NBUF>
+static int launch_tiled(const FirPlan& pl, const void* in, void* out, long long nout, long long nin, int D,
+                        const void* gtaps, int nsm, cudaStream_t st)
 {
-    auto kern = fir_tiled_kernel<R, CT>;
-    static thread_local size_t configured[16] = { 0 };
+    auto kern = fir_tiled_kernel<R, CT, NBUF>;
+    static thread_local bool configured[16] = {};
     int dev = 0;
     cudaGetDevice(&dev);
-    if (pl.smem > 48 * 1024 && configured[dev & 15] < pl.smem) {
-        GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(220 * 1024)));
-        configured[dev & 15] = 220 * 1024;
+    if (!configured[dev & 15]) {
+        GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(226 * 1024)));
+        configured[dev & 15] = true;
     }
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, pl.NT, pl.smem));
+    if (occ < 1)
+        occ = 1;
     const long long tile = (long long)pl.NT * R;
-    const long long nblk = (nout + tile - 1) / tile;
-    if (nblk > 0x7fffffffLL)
-        return fail(GRB200_ERANGE, "fir: too many tiles");
-    kern<<<(unsigned)nblk, pl.NT, pl.smem, st>>>((const float2*)in, (float2*)out, nout, nin, D, pl.Upad,
-                                                 (const typename TapT<CT>::type*)gtaps, pl.ldrow);
+    const long long ntiles = (nout + tile - 1) / tile;
+    long long grid = (long long)nsm * occ;
+    if (grid > ntiles)
+        grid = ntiles;
+    const int aligned16 = (((uintptr_t)in) & 15) == 0;
+    kern<<<(unsigned)grid, pl.NT, pl.smem, st>>>((const float2*)in, (float2*)out, nout, nin, D, pl.Upad,
+                                                 (const typename TapT<CT>::type*)gtaps, pl.ldrow, aligned16);
     GRB_LAUNCH_CHECK();
     return 0;
+}
+
+template <int R, bool CT>
+static int launch_tiled_nb(const FirPlan& pl, const void* in, void* out, long long nout, long long nin, int D,
+                           const void* gtaps, int nsm, cudaStream_t st)
+{
+    return pl.NBUF == 2 ? launch_tiled<R, CT, 2>(pl, in, out, nout, nin, D, gtaps, nsm, st)
+                        : launch_tiled<R, CT, 1>(pl, in, out, nout, nin, D, gtaps, nsm, st);
 }
 
 // gtaps: phase-major padded taps [D][Upad]; rev: reversed taps [ntaps] (both on the device).
@@ -246,12 +352,14 @@ int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, co
         return 0;
     const long long nin = nout * D + ntaps - 1; // readable items behind `in` (block contract)
     FirPlan pl = plan_fir(D, ntaps, ct);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const int nsm = sm_count(dev);
     if (pl.tiled) {
-        if (pl.R == 16)
-            return ct ? launch_tiled<16, true>(pl, in, out, nout, nin, D, gtaps, st)
-                      : launch_tiled<16, false>(pl, in, out, nout, nin, D, gtaps, st);
-        return ct ? launch_tiled<8, true>(pl, in, out, nout, nin, D, gtaps, st)
-                  : launch_tiled<8, false>(pl, in, out, nout, nin, D, gtaps, st);
+        if (ct)
+            return launch_tiled_nb<8, true>(pl, in, out, nout, nin, D, gtaps, nsm, st);
+        return pl.R == 16 ? launch_tiled_nb<16, false>(pl, in, out, nout, nin, D, gtaps, nsm, st)
+                          : launch_tiled_nb<8, false>(pl, in, out, nout, nin, D, gtaps, nsm, st);
     }
     const long long nthreads = nout * 32;
     const long long nblk = (nthreads + 255) / 256;
