@@ -48,18 +48,32 @@ int use_device(int device);
 int sm_count(int device);
 
 // ---- device-side complex helpers --------------------------------------------------------------
+// Packed FP32 (sm_100 FADD2/FMUL2/FFMA2): a complex add is ONE instruction, a complex multiply TWO; the
+// swaps and sign flips below fold into the instructions' operand modifiers (.LO_HI, .NP), they cost nothing.
 __device__ __forceinline__ float2 cmul(float2 a, float2 b)
 {
-    return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+    const float2 t = __fmul2_rn(make_float2(a.y, a.y), make_float2(b.y, b.x)); // (a.y b.y, a.y b.x)
+    return __ffma2_rn(make_float2(a.x, a.x), b, make_float2(-t.x, t.y));
 }
-__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return __fadd2_rn(a, make_float2(-b.x, -b.y)); }
 __device__ __forceinline__ float2 cconj(float2 a) { return make_float2(a.x, -a.y); }
 // multiply by -j (forward) / +j (inverse)
 template <bool FWD>
 __device__ __forceinline__ float2 cmulj(float2 a)
 {
     return FWD ? make_float2(a.y, -a.x) : make_float2(-a.y, a.x);
+}
+// a + (-+j) b and a - (-+j) b without materialising the rotation
+template <bool FWD>
+__device__ __forceinline__ float2 cadd_mulj(float2 a, float2 b)
+{
+    return __fadd2_rn(a, FWD ? make_float2(b.y, -b.x) : make_float2(-b.y, b.x));
+}
+template <bool FWD>
+__device__ __forceinline__ float2 csub_mulj(float2 a, float2 b)
+{
+    return __fadd2_rn(a, FWD ? make_float2(-b.y, b.x) : make_float2(b.y, -b.x));
 }
 
 // ---- staging: pinned double-buffered host<->device pipeline (K8 in SURVEY.md section 2a) --------

@@ -38,25 +38,25 @@ __device__ __forceinline__ void dft2(float2& a, float2& b)
 template <bool FWD>
 __device__ __forceinline__ void dft4(float2& v0, float2& v1, float2& v2, float2& v3)
 {
-    float2 a0 = cadd(v0, v2), a1 = csub(v0, v2), a2 = cadd(v1, v3), a3 = cmulj<FWD>(csub(v1, v3));
+    const float2 a0 = cadd(v0, v2), a1 = csub(v0, v2), a2 = cadd(v1, v3), a3 = csub(v1, v3);
     v0 = cadd(a0, a2);
-    v1 = cadd(a1, a3);
+    v1 = cadd_mulj<FWD>(a1, a3);
     v2 = csub(a0, a2);
-    v3 = csub(a1, a3);
+    v3 = csub_mulj<FWD>(a1, a3);
 }
 
 // multiply by e^{-+j pi/4 * m}, m = 1 or 3 (sign by FWD)
 template <bool FWD>
 __device__ __forceinline__ float2 cmul_w8_1(float2 a)
 {
-    const float s = 0.70710678118654752440f;
-    return FWD ? make_float2((a.x + a.y) * s, (a.y - a.x) * s) : make_float2((a.x - a.y) * s, (a.x + a.y) * s);
+    const float s = 0.70710678118654752440f; // (1 -+ j)/sqrt2 * a = s * (a + (-+j) a)
+    return __fmul2_rn(make_float2(s, s), cadd_mulj<FWD>(a, a));
 }
 template <bool FWD>
 __device__ __forceinline__ float2 cmul_w8_3(float2 a)
 {
-    const float s = 0.70710678118654752440f;
-    return FWD ? make_float2((a.y - a.x) * s, -(a.x + a.y) * s) : make_float2(-(a.x + a.y) * s, (a.x - a.y) * s);
+    const float s = 0.70710678118654752440f; // (-1 -+ j)/sqrt2 * a = s * ((-+j) a - a)
+    return __fmul2_rn(make_float2(-s, -s), csub_mulj<FWD>(a, a));
 }
 
 template <bool FWD>
@@ -83,9 +83,9 @@ __device__ __forceinline__ void dft8(float2* v)
 template <bool FWD>
 __device__ __forceinline__ float2 cmul_const(float2 a, float c, float s)
 {
-    // multiply by (c - j s) forward, (c + j s) inverse
-    return FWD ? make_float2(fmaf(a.x, c, a.y * s), fmaf(a.y, c, -a.x * s))
-               : make_float2(fmaf(a.x, c, -a.y * s), fmaf(a.y, c, a.x * s));
+    // multiply by (c - j s) forward, (c + j s) inverse:  c*a + s*((-+j) a)
+    const float2 t = __fmul2_rn(make_float2(s, s), cmulj<FWD>(a));
+    return __ffma2_rn(make_float2(c, c), a, t);
 }
 
 template <bool FWD>

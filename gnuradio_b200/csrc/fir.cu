@@ -68,7 +68,21 @@ __device__ __forceinline__ void fir_stage_tile(float2* xs, const float2* __restr
                                                int D, int Lm, int ldrow, int tid, int NT, bool aligned16)
 {
     if (D == 1) {
-        if (aligned16) {
+        if (g0 + Lm <= nin) { // interior tile: no bounds, pure pointer increments (NT*2 is a multiple of R)
+            if (aligned16) {
+                const float2* src = in + g0 + 2 * tid;
+                float2* dst = xs + 2 * tid + 2 * ((2 * tid) / R);
+                const int dstep = 2 * NT + 2 * (2 * NT / R);
+                for (int m = 2 * tid; m < Lm; m += 2 * NT, src += 2 * NT, dst += dstep)
+                    cp_async16(dst, src, 16u);
+            } else {
+                const float2* src = in + g0 + tid;
+                float2* dst = xs + tid + 2 * (tid / R);
+                const int dstep = NT + 2 * (NT / R);
+                for (int m = tid; m < Lm; m += NT, src += NT, dst += dstep)
+                    cp_async8(dst, src, 8u);
+            }
+        } else if (aligned16) {
             for (int m = 2 * tid; m < Lm; m += 2 * NT) {
                 const long long g = g0 + m;
                 long long left = nin - g;
@@ -211,12 +225,20 @@ fir_tiled_kernel(const float2* __restrict__ in, float2* __restrict__ out, long l
                 *reinterpret_cast<float4*>(os + r) = make_float4(acc[r].x, acc[r].y, acc[r + 1].x, acc[r + 1].y);
             __syncwarp();
             const long long w0 = tile * TILE + (long long)warp * 32 * R;
+            if (w0 + 32 * R <= nout) {
+                float2* o = out + w0 + lane;
+                const float2* sp = stage + lane + 2 * (lane / R);
 #pragma unroll
-            for (int j = 0; j < R; j++) {
-                const int m = lane + 32 * j;
-                const long long i = w0 + m;
-                if (i < nout)
-                    out[i] = stage[m + 2 * (m / R)];
+                for (int j = 0; j < R; j++) // 32*j advances the skewed index by 32 + 2*(32/R)
+                    o[32 * j] = sp[j * (32 + 2 * (32 / R))];
+            } else {
+#pragma unroll
+                for (int j = 0; j < R; j++) {
+                    const int m = lane + 32 * j;
+                    const long long i = w0 + m;
+                    if (i < nout)
+                        out[i] = stage[m + 2 * (m / R)];
+                }
             }
             __syncwarp();
         }
@@ -229,6 +251,118 @@ fir_tiled_kernel(const float2* __restrict__ in, float2* __restrict__ out, long l
                 fir_stage_tile<R>(xbuf, in, next * TILE * D, nin, D, Lm, ldrow, tid, NT, aligned16 != 0);
             cp_async_commit();
         }
+    }
+    cp_async_wait<0>();
+}
+
+// Warp-private pipelines: every warp owns its own double-buffered window (32*R outputs + halo) and output
+// staging, so after the one-time tap load there is NO CTA barrier: warps drift freely and the scheduler
+// always finds FFMA2 work.  Costs Upad/(32*R) extra staged samples per tile; chosen when that is small.
+template <int R, bool CT>
+__global__ void __launch_bounds__(256)
+fir_warptile_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int D,
+                    int Upad, const typename TapT<CT>::type* __restrict__ gtaps, int ldrow, int aligned16)
+{
+    using tap_t = typename TapT<CT>::type;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+    constexpr int WT = 32 * R;          // outputs per warp tile
+    const int Lm = WT + Upad;           // window positions staged per phase
+    const size_t bufelems = (size_t)D * ldrow;
+    const size_t per_warp = 2 * bufelems + 32 * (R + 2);
+    float2* xbuf = reinterpret_cast<float2*>(smem_raw) + (size_t)warp * per_warp; // [2][D][ldrow]
+    float2* stage = xbuf + 2 * bufelems;
+    tap_t* gs = reinterpret_cast<tap_t*>(reinterpret_cast<float2*>(smem_raw) + (size_t)nwarp * per_warp);
+
+    for (int e = tid; e < D * Upad; e += blockDim.x)
+        gs[e] = gtaps[e];
+    __syncthreads();
+
+    const long long ntiles = (nout + WT - 1) / WT;
+    const long long stride = (long long)gridDim.x * nwarp;
+    long long tile = (long long)blockIdx.x * nwarp + warp;
+    if (tile >= ntiles)
+        return;
+    fir_stage_tile<R>(xbuf, in, tile * WT * D, nin, D, Lm, ldrow, lane, 32, aligned16 != 0);
+    cp_async_commit();
+    int b = 0;
+    for (; tile < ntiles; tile += stride, b ^= 1) {
+        const float2* xs = xbuf + (size_t)b * bufelems;
+        const long long next = tile + stride;
+        if (next < ntiles)
+            fir_stage_tile<R>(xbuf + (size_t)(b ^ 1) * bufelems, in, next * WT * D, nin, D, Lm, ldrow, lane, 32,
+                              aligned16 != 0);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncwarp();
+
+        float2 acc[R];
+#pragma unroll
+        for (int r = 0; r < R; r++)
+            acc[r] = make_float2(0.f, 0.f);
+        for (int p = 0; p < D; p++) {
+            const float2* row = xs + p * ldrow + lane * (R + 2);
+            const tap_t* gp = gs + p * Upad;
+            float2 ring[R], rsw[CT ? R : 1];
+#pragma unroll
+            for (int k = 0; k < R; k += 2) {
+                float4 v = *reinterpret_cast<const float4*>(row + k);
+                ring[k] = make_float2(v.x, v.y);
+                ring[k + 1] = make_float2(v.z, v.w);
+                if (CT) {
+                    rsw[k] = make_float2(-v.y, v.x);
+                    rsw[k + 1] = make_float2(-v.w, v.z);
+                }
+            }
+            for (int u0 = 0; u0 < Upad; u0 += R) {
+                const float2* nx = row + (u0 / R + 1) * (R + 2);
+                float2 xn[R];
+#pragma unroll
+                for (int k = 0; k < R; k += 2) {
+                    float4 v = *reinterpret_cast<const float4*>(nx + k);
+                    xn[k] = make_float2(v.x, v.y);
+                    xn[k + 1] = make_float2(v.z, v.w);
+                }
+                __align__(16) tap_t hh[R];
+                constexpr int TPV = CT ? 2 : 4; // taps per 16-byte load
+#pragma unroll
+                for (int k = 0; k < R; k += TPV) {
+                    float4 v = *reinterpret_cast<const float4*>(gp + u0 + k);
+                    reinterpret_cast<float4*>(hh)[k / TPV] = v;
+                }
+#pragma unroll
+                for (int uu = 0; uu < R; uu++) {
+#pragma unroll
+                    for (int r = 0; r < R; r++)
+                        mac2(acc[r], hh[uu], ring[(uu + r) % R], rsw[CT ? (uu + r) % R : 0]);
+                    ring[uu] = xn[uu];
+                    if (CT)
+                        rsw[uu] = make_float2(-xn[uu].y, xn[uu].x);
+                }
+            }
+        }
+        // ---- transpose through the warp's staging area, coalesced stores ----
+        float2* os = stage + lane * (R + 2);
+#pragma unroll
+        for (int r = 0; r < R; r += 2)
+            *reinterpret_cast<float4*>(os + r) = make_float4(acc[r].x, acc[r].y, acc[r + 1].x, acc[r + 1].y);
+        __syncwarp();
+        const long long w0 = tile * WT;
+        if (w0 + WT <= nout) {
+            float2* o = out + w0 + lane;
+            const float2* sp = stage + lane + 2 * (lane / R);
+#pragma unroll
+            for (int j = 0; j < R; j++)
+                o[32 * j] = sp[j * (32 + 2 * (32 / R))];
+        } else {
+#pragma unroll
+            for (int j = 0; j < R; j++) {
+                const int m = lane + 32 * j;
+                if (w0 + m < nout)
+                    out[w0 + m] = stage[m + 2 * (m / R)];
+            }
+        }
+        __syncwarp(); // staging and this buffer are free again
     }
     cp_async_wait<0>();
 }
@@ -261,7 +395,7 @@ fir_warp_kernel(const float2* __restrict__ in, float2* __restrict__ out, long lo
 struct FirPlan {
     int R = 0, NT = 0, NBUF = 0, Upad = 0, ldrow = 0;
     size_t smem = 0;
-    bool tiled = false;
+    bool tiled = false, warptile = false;
 };
 
 static size_t fir_smem(int D, int Upad, bool ct, int R, int NT, int NBUF, int* ldrow_out)
@@ -288,12 +422,29 @@ static FirPlan plan_fir(int D, int ntaps, bool ct)
             best.R = R, best.NT = NT, best.NBUF = NBUF, best.ldrow = ld, best.smem = s, best.tiled = true;
         }
     };
-    if (const char* e = getenv("GRB200_FIR_PLAN")) { // tuning knob: "R,NT,NBUF"
+    // warp-private pipelines when a warp's double-buffered window is small (short filters)
+    auto take_warptile = [&](int R, int NT) {
+        if (best.tiled || (ct && R == 16))
+            return;
+        const int Lm = 32 * R + best.Upad;
+        const int ld = Lm / R * (R + 2);
+        const size_t per_warp = ((size_t)2 * D * ld + 32 * (R + 2)) * 8;
+        if (per_warp <= 16 * 1024) {
+            best.R = R, best.NT = NT, best.NBUF = 2, best.ldrow = ld, best.tiled = true, best.warptile = true;
+            best.smem = per_warp * (NT / 32) + (size_t)D * best.Upad * (ct ? 8 : 4);
+        }
+    };
+    if (const char* e = getenv("GRB200_FIR_PLAN")) { // tuning knob: "R,NT,NBUF" (NBUF 3 = warp-private pipelines)
         int R = 0, NT = 0, NB = 0;
-        if (sscanf(e, "%d,%d,%d", &R, &NT, &NB) == 3 && (R == 8 || R == 16) && NT >= 32 && NT <= 256 && NT % 32 == 0 &&
-            (NB == 1 || NB == 2))
-            take(R, NT, NB, one_per_sm);
+        if (sscanf(e, "%d,%d,%d", &R, &NT, &NB) == 3 && (R == 8 || R == 16) && NT >= 32 && NT <= 256 && NT % 32 == 0) {
+            if (NB == 1 || NB == 2)
+                take(R, NT, NB, one_per_sm);
+            else if (NB == 3)
+                take_warptile(R, NT);
+        }
     }
+    take_warptile(16, 128);
+    take_warptile(8, 128);
     const int cand[4][2] = { { 16, 256 }, { 16, 128 }, { 8, 256 }, { 8, 128 } };
     for (auto& c : cand)
         take(c[0], c[1], 2, two_per_sm);
@@ -337,9 +488,39 @@ static int launch_tiled(const FirPlan& pl, const void* in, void* out, long long 
 }
 
 template <int R, bool CT>
+static int launch_warptile(const FirPlan& pl, const void* in, void* out, long long nout, long long nin, int D,
+                           const void* gtaps, int nsm, cudaStream_t st)
+{
+    auto kern = fir_warptile_kernel<R, CT>;
+    static thread_local bool configured[16] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 15]) {
+        GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(226 * 1024)));
+        configured[dev & 15] = true;
+    }
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, pl.NT, pl.smem));
+    if (occ < 1)
+        occ = 1;
+    const long long ntiles = (nout + 32 * R - 1) / (32 * R);
+    const long long wpc = pl.NT / 32;
+    long long grid = (long long)nsm * occ;
+    if (grid > (ntiles + wpc - 1) / wpc)
+        grid = (ntiles + wpc - 1) / wpc;
+    const int aligned16 = (((uintptr_t)in) & 15) == 0;
+    kern<<<(unsigned)grid, pl.NT, pl.smem, st>>>((const float2*)in, (float2*)out, nout, nin, D, pl.Upad,
+                                                 (const typename TapT<CT>::type*)gtaps, pl.ldrow, aligned16);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+template <int R, bool CT>
 static int launch_tiled_nb(const FirPlan& pl, const void* in, void* out, long long nout, long long nin, int D,
                            const void* gtaps, int nsm, cudaStream_t st)
 {
+    if (pl.warptile)
+        return launch_warptile<R, CT>(pl, in, out, nout, nin, D, gtaps, nsm, st);
     return pl.NBUF == 2 ? launch_tiled<R, CT, 2>(pl, in, out, nout, nin, D, gtaps, nsm, st)
                         : launch_tiled<R, CT, 1>(pl, in, out, nout, nin, D, gtaps, nsm, st);
 }
