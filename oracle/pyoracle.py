@@ -41,6 +41,21 @@ def _c64(a):
     return np.ascontiguousarray(a, dtype=np.complex64)
 
 
+def _headroom(a):
+    """Copy of 1-D/2-D complex64 ``a`` whose every row is preceded by 64 zero bytes of the same allocation.
+    kernel::fir_filter::filter() (gr-filter/lib/fir_filter.cc:133-141) rounds the input pointer DOWN to the
+    VOLK alignment and multiplies what lies in front by zero taps; inside a gr::buffer that memory is always
+    finite, in a bare numpy allocation it may hold NaN bit patterns (0*NaN = NaN)."""
+    a = _c64(a)
+    if a.ndim == 1:
+        buf = np.zeros(len(a) + 8, np.complex64)
+        buf[8:] = a
+        return buf[8:]
+    buf = np.zeros((a.shape[0], a.shape[1] + 8), np.complex64)
+    buf[:, 8:] = a
+    return buf[:, 8:]
+
+
 class _CLib:
     """Uniform wrapper over libgrref.so (prefix grref_) and libgrb_oracle.so (prefix grbo_)."""
 
@@ -57,7 +72,7 @@ class _CLib:
     # -- fir_filter_ccf / ccc work(): xin carries ntaps-1 history items in front ------------------
     def fir(self, decim, taps, xin, nout):
         taps = np.ascontiguousarray(taps)
-        xin = _c64(xin)
+        xin = _headroom(xin)
         ntaps = len(taps)
         assert len(xin) >= nout * decim + ntaps - 1
         out = np.empty(nout, np.complex64)
@@ -101,7 +116,7 @@ class _CLib:
         """in_streams: [nfilts, consumed + T] complex64 (T history items first).
         Returns ([nouts, noutput] complex64, consumed) or raises ValueError."""
         t = np.ascontiguousarray(taps, np.float32)
-        ins = _c64(in_streams)
+        ins = _headroom(in_streams)
         assert ins.shape[0] == nfilts
         nouts = nfilts if nouts is None else nouts
         outs = np.zeros((nouts, noutput), np.complex64)
