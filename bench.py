@@ -106,7 +106,7 @@ class PfbChannelizer(Workload):
     name = "pfb_channelizer_ccf 64ch x 16 taps/branch, 2^%d complex64 samples per GPU (BASELINE configs[2])"
     block = "pfb_channelizer_ccf"
     alg_bytes, flops, log2n, seed = 16.0, 94.0, 30, 3
-    kernel = "pfb_fast_kernel"
+    kernel = "pfb_stream_kernel"
     M, T = 64, 16
 
     def setup(self):
@@ -167,7 +167,7 @@ class FirCcf(Workload):
     name = "fir_filter_ccf 64 taps decim 1, 2^%d samples x %d rotating buffer sets (BASELINE configs[0])"
     block = "fir_filter_ccf"
     alg_bytes, flops, log2n, seed = 16.0, 256.0, 24, 1
-    kernel = "fir_tiled_kernel"
+    kernel = "fir_warptile_kernel"
     ntaps, decim, nsets = 64, 1, 4
 
     def setup(self):
