@@ -128,7 +128,7 @@ class PfbChannelizer(Workload):
     # -- multi-GPU: the segment's history comes from the left neighbour's tail ---------------------------
     def halo_views(self):
         h = 2 * self.halo_items
-        return self.d_in[:h], self.d_in[-h:]
+        return [(self.d_in[:h], self.d_in[-h:])]
 
     # -- e2e through host buffers ---------------------------------------------------------------------
     def e2e_setup(self, log2n):
@@ -183,6 +183,11 @@ class FirCcf(Workload):
         for i in range(self.nsets):
             self.blk.work_dev(self.d_in[i].data_ptr(), self.d_out[i].data_ptr(), self.nout, self.stream)
 
+    def halo_views(self):  # ntaps-1 history items in front of every segment
+        h = 2 * (self.ntaps - 1)
+        self.halo_items = self.ntaps - 1
+        return [(d[:h], d[-h:]) for d in self.d_in]
+
     def describe(self):
         return self.name % (self.log2n, self.nsets)
 
@@ -202,6 +207,7 @@ class FirLongDecim(FirCcf):
     """configs[3]: fir_filter_ccf 1024 taps, decim 8 (2^27 input samples per GPU)."""
     name = "fir_filter_ccf 1024 taps decim 8, 2^%d input samples per GPU x %d set(s) (BASELINE configs[3])"
     alg_bytes, flops, log2n, seed = 9.0, 512.0, 27, 4
+    kernel = "fir_tiled_kernel"
     ntaps, decim, nsets = 1024, 8, 1
 
     def setup(self):
@@ -477,13 +483,13 @@ def main():
 
     halo = None
     if dist is not None and hasattr(wl, "halo_views"):
-        head, tail = wl.halo_views()
-        right, left = (rank + 1) % world, (rank - 1) % world
+        from gnuradio_b200 import sharding
 
-        def halo():  # the segment's history = the left neighbour's newest T*M samples (ring; rank 0 keeps zeros in a real stream)
-            ops = [dist.P2POp(dist.isend, tail, right), dist.P2POp(dist.irecv, head, left)]
-            for r in dist.batch_isend_irecv(ops):
-                r.wait()
+        views = wl.halo_views()
+
+        def halo():  # the segment's history = the left neighbour's newest items (ring: every rank does equal work)
+            for head, tail in views:
+                sharding.exchange_halo(dist, head, tail, rank, world, ring=True)
 
     with ClockSampler(local) as clk:
         total_ms, per = timed_steps(torch, dist, wl, args.steps, args.warmup, halo)
@@ -558,11 +564,17 @@ def main():
 
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
-        v1, kind, n1, dt1 = cpu_run(wl_cls, 1, 22, 2)
-        vN, kind, nN, dtN = cpu_run(wl_cls, cores, 22, 2)
+        # bounded sample: ~3 s on one core, then ~1.5 s wall on all cores (about 25-30 core-seconds in total)
+        _, kind, n0, dt0 = cpu_run(wl_cls, 1, 22, 1)
+        r1 = max(1, int(round(3.0 / dt0)))
+        v1, kind, n1, dt1 = cpu_run(wl_cls, 1, 22, r1)
+        _, kind, n0, dtp = cpu_run(wl_cls, cores, 22, 1)
+        rN = max(1, int(round(1.5 / dtp)))
+        vN, kind, nN, dtN = cpu_run(wl_cls, cores, 22, rN)
         line["cpu_baseline"] = {"value": vN, "unit": "Msps", "cores": cores, "kind": kind,
-                                "sample": "2 passes over a 2^22-sample slice of the workload per thread (%d threads, %.1f s); "
-                                          "1 thread = %.2f Msps (what one GNU Radio block thread delivers)" % (cores, dtN, v1),
+                                "sample": "%d passes over a 2^22-sample slice of the workload per thread (%d threads, %.1f s "
+                                          "wall = %.0f core-seconds); 1 thread = %.2f Msps over %.1f s (what one GNU Radio block "
+                                          "thread delivers)" % (rN, cores, dtN, dtN * cores, v1, dt1),
                                 "value_1core": v1}
     if rank == 0:
         print(json.dumps(line))

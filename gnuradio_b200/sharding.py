@@ -1,0 +1,74 @@
+"""Time-segment sharding of the hot-path blocks across the GPUs of one box (host logic, no compute).
+
+SURVEY.md section 8(e): every block on the path shards by time segment.  Rank g owns a contiguous run of
+OUTPUT items; the input it needs is its own segment plus a history halo that is the left neighbour's newest
+items (fir: ntaps-1, gr-filter/lib/fir_filter_blk_impl.cc:41; channelizer: taps_per_filter rows of numchans
+items, gr-filter/lib/pfb_channelizer_ccf_impl.cc:101; fft_filter: ntaps-1, the d_tail of
+gr-filter/lib/fft_filter.cc:262-267; fft_vcc: none).  The halo is the only exchange step the path has:
+one send/recv pair per rank and step over NCCL (gloo in the CPU tests).
+"""
+from dataclasses import dataclass
+
+
+@dataclass(frozen=True)
+class Segment:
+    rank: int
+    world: int
+    out_begin: int   # first output item owned
+    out_end: int     # one past the last output item owned
+    in_begin: int    # first NEW input item consumed (halo excluded)
+    in_end: int
+    halo: int        # history items in front of in_begin that come from the left neighbour (zeros for rank 0)
+
+    @property
+    def noutput(self):
+        return self.out_end - self.out_begin
+
+    @property
+    def ninput(self):
+        return self.in_end - self.in_begin
+
+
+def split_outputs(noutput_total, world, multiple=1):
+    """Cut [0, noutput_total) into `world` contiguous runs whose lengths are multiples of `multiple`
+    (the block's output_multiple); the remainder units go to the lowest ranks."""
+    if world < 1 or multiple < 1:
+        raise ValueError("split_outputs: world and multiple must be >= 1")
+    if noutput_total % multiple:
+        raise ValueError("split_outputs: %d outputs is not a multiple of %d" % (noutput_total, multiple))
+    units = noutput_total // multiple
+    base, extra = divmod(units, world)
+    bounds = [0]
+    for r in range(world):
+        bounds.append(bounds[-1] + (base + (1 if r < extra else 0)) * multiple)
+    return bounds
+
+
+def segment(rank, world, noutput_total, decimation=1, history=1, multiple=1, items_per_output=1):
+    """Segment of a sync_decimator-like block: output i consumes input items
+    [i*decimation*items_per_output, ...) plus (history-1)*items_per_output items of history.
+    items_per_output = numchans for the interleaved channelizer stream, fft_size is NOT used here
+    (fft_vcc items are whole vectors)."""
+    b = split_outputs(noutput_total, world, multiple)
+    step = decimation * items_per_output
+    return Segment(rank, world, b[rank], b[rank + 1], b[rank] * step, b[rank + 1] * step,
+                   (history - 1) * items_per_output)
+
+
+def exchange_halo(dist, head, tail, rank, world, ring=False):
+    """Fill `head` (this rank's halo region, in front of its segment) with the left neighbour's `tail`
+    (its newest halo-many items).  Rank 0 keeps what it has (zeros = the scheduler's preloaded history)
+    unless ring=True (bench: every rank does the same work).  Tensors may be CUDA (nccl) or CPU (gloo)."""
+    if world == 1 or head.numel() == 0:
+        return
+    right, left = rank + 1, rank - 1
+    ops = []
+    if ring:
+        right, left = right % world, left % world
+    if right < world:
+        ops.append(dist.P2POp(dist.isend, tail, right))
+    if left >= 0:
+        ops.append(dist.P2POp(dist.irecv, head, left))
+    if ops:
+        for r in dist.batch_isend_irecv(ops):
+            r.wait()

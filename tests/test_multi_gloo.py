@@ -1,0 +1,96 @@
+"""N>1 host logic on CPU: time-segment sharding + history halo exchange (gnuradio_b200/sharding.py),
+world_size 2 and 3 over gloo.  The per-rank "block" is the CPU oracle (tests may call it): what is under test is
+that segments + halo reproduce the single-stream result item for item, i.e. the arithmetic bench.py and a
+multi-GPU flowgraph rely on."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from gnuradio_b200 import sharding  # noqa: E402
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _c64_to_t(a):
+    return torch.from_numpy(np.ascontiguousarray(a).view(np.float32).copy())
+
+
+def _worker(rank, world, port, case, outdir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import pyoracle as po
+
+        orc = po.Port()
+        rng = np.random.default_rng(1234)  # every rank draws the same whole stream, then keeps its segment only
+        if case == "fir":
+            ntaps, D, nout_total = 37, 3, 6000
+            taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
+            x = (rng.uniform(-1, 1, nout_total * D) + 1j * rng.uniform(-1, 1, nout_total * D)).astype(np.complex64)
+            seg = sharding.segment(rank, world, nout_total, decimation=D, history=ntaps)
+            buf = np.zeros(seg.halo + seg.ninput, np.complex64)  # rank 0: zeros = preloaded history
+            buf[seg.halo:] = x[seg.in_begin:seg.in_end]
+            tbuf = _c64_to_t(buf)
+            head, tail = tbuf[: 2 * seg.halo], tbuf[-2 * seg.halo:].clone()
+            sharding.exchange_halo(dist, head, tail, rank, world)
+            y = orc.fir(D, taps, tbuf.numpy().view(np.complex64), seg.noutput)
+            full = orc.fir_stream(D, taps, x)
+        elif case == "pfb":
+            M, T, nout_total = 8, 5, 900
+            taps = rng.uniform(-1, 1, M * T).astype(np.float32)
+            x = (rng.uniform(-1, 1, nout_total * M) + 1j * rng.uniform(-1, 1, nout_total * M)).astype(np.complex64)
+            seg = sharding.segment(rank, world, nout_total, history=T + 1, items_per_output=M)
+            buf = np.zeros(seg.halo + seg.ninput, np.complex64)
+            buf[seg.halo:] = x[seg.in_begin:seg.in_end]
+            tbuf = _c64_to_t(buf)
+            head, tail = tbuf[: 2 * seg.halo], tbuf[-2 * seg.halo:].clone()
+            sharding.exchange_halo(dist, head, tail, rank, world)
+            ins = np.ascontiguousarray(tbuf.numpy().view(np.complex64).reshape(-1, M).T)
+            y, consumed = orc.pfb_channelizer(M, taps, 1.0, ins, seg.noutput)
+            assert consumed == seg.noutput
+            xf = np.concatenate([np.zeros(T * M, np.complex64), x])
+            full, _ = orc.pfb_channelizer(M, taps, 1.0, np.ascontiguousarray(xf.reshape(-1, M).T), nout_total)
+            full = full[:, seg.out_begin:seg.out_end]
+            np.save(os.path.join(outdir, "ok_%d.npy" % rank), np.array([np.array_equal(y, full)]))
+            return
+        else:
+            raise AssertionError(case)
+        np.save(os.path.join(outdir, "ok_%d.npy" % rank),
+                np.array([np.array_equal(y, full[seg.out_begin:seg.out_end])]))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("case", ["fir", "pfb"])
+def test_segments_plus_halo_equal_single_stream(tmp_path, world, case):
+    mp.spawn(_worker, args=(world, _free_port(), case, str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        assert bool(np.load(tmp_path / ("ok_%d.npy" % r))[0]), "rank %d differs from the single-stream result" % r
+
+
+def test_split_outputs_respects_multiples():
+    b = sharding.split_outputs(4097 * 10, 4, multiple=4097)
+    assert b == [0, 3 * 4097, 6 * 4097, 8 * 4097, 10 * 4097]
+    with pytest.raises(ValueError):
+        sharding.split_outputs(100, 3, multiple=7)
+    s = sharding.segment(1, 2, 1000, decimation=8, history=1024)
+    assert (s.out_begin, s.out_end, s.in_begin, s.in_end, s.halo) == (500, 1000, 4000, 8000, 1023)
+    s = sharding.segment(0, 8, 1 << 24, history=17, items_per_output=64)
+    assert s.halo == 16 * 64 and s.ninput == (1 << 27)
