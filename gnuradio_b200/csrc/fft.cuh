@@ -137,31 +137,26 @@ __device__ __forceinline__ void dft_r(float2* v)
         dft16<FWD>(v);
 }
 
-// ---- twiddles: v[q] *= W_N^{q*m}, tw = forward table of N entries --------------------------------
-template <int R, int N, bool FWD>
-__device__ __forceinline__ void apply_twiddles(float2* v, int m, const float2* __restrict__ tw)
+// ---- twiddles: v[q] *= W^{q}, the powers 1,2,4,8 of W come from look(0..3), the rest are products ----
+template <int R, class Look>
+__device__ __forceinline__ void apply_twiddles_l(float2* v, Look look)
 {
-    // m = (j mod Ns) * N/(Ns*R); q*m < N for every q < R
-    auto look = [&](int idx) {
-        float2 w = __ldg(tw + idx);
-        return FWD ? w : cconj(w);
-    };
-    float2 w1 = look(m);
+    float2 w1 = look(0);
     v[1] = cmul(v[1], w1);
     if constexpr (R >= 4) {
-        float2 w2 = look(2 * m);
+        float2 w2 = look(1);
         float2 w3 = cmul(w2, w1);
         v[2] = cmul(v[2], w2);
         v[3] = cmul(v[3], w3);
         if constexpr (R >= 8) {
-            float2 w4 = look(4 * m);
+            float2 w4 = look(2);
             float2 w5 = cmul(w4, w1), w6 = cmul(w4, w2), w7 = cmul(w4, w3);
             v[4] = cmul(v[4], w4);
             v[5] = cmul(v[5], w5);
             v[6] = cmul(v[6], w6);
             v[7] = cmul(v[7], w7);
             if constexpr (R >= 16) {
-                float2 w8 = look(8 * m);
+                float2 w8 = look(3);
                 v[8] = cmul(v[8], w8);
                 v[9] = cmul(v[9], cmul(w8, w1));
                 v[10] = cmul(v[10], cmul(w8, w2));
@@ -173,6 +168,17 @@ __device__ __forceinline__ void apply_twiddles(float2* v, int m, const float2* _
             }
         }
     }
+}
+
+// v[q] *= W_N^{q*m}, tw = forward table of N entries in global memory
+template <int R, int N, bool FWD>
+__device__ __forceinline__ void apply_twiddles(float2* v, int m, const float2* __restrict__ tw)
+{
+    // m = (j mod Ns) * N/(Ns*R); q*m < N for every q < R
+    apply_twiddles_l<R>(v, [&](int k) {
+        float2 w = __ldg(tw + (m << k));
+        return FWD ? w : cconj(w);
+    });
 }
 
 // ---- radix schedule ------------------------------------------------------------------------------------
@@ -254,6 +260,113 @@ __device__ __forceinline__ void cta_fft(float2 (&v)[fft_elems(N)], float2* S, in
         }
         __syncthreads();
         cta_fft<N, FWD, REV, PASS + 1, NS * R>(v, S, t, tw);
+    }
+}
+
+// ---- variant with per-thread twiddles precomputed in shared memory -----------------------------------
+// In a persistent kernel thread t meets the same butterflies for every vector, so the base twiddles
+// (powers 1,2,4,8 of W^m per butterfly) are loop invariant: cta_fft_tws_init() writes them once to
+// TW[slot][TPV] (column t, conflict-free), cta_fft_tws() reads them back with LDS instead of going to
+// the global table every pass.  A pass whose butterflies of one thread all share m (TPV % NS == 0, true
+// for every pass but the small-radix tail of the big sizes) takes log2(R) slots; the others keep the
+// global table.  `after_first` runs once, right after the barrier that follows the first pass's writes
+// (all threads have consumed their input by then).
+__host__ __device__ constexpr int fft_ilog2(int r) { return r == 16 ? 4 : (r == 8 ? 3 : (r == 4 ? 2 : (r == 2 ? 1 : 0))); }
+__host__ __device__ constexpr int fft_ns_at(int N, bool rev, int pass)
+{
+    int ns = 1;
+    for (int p = 0; p < pass; p++)
+        ns *= fft_radix_at(N, rev, p);
+    return ns;
+}
+__host__ __device__ constexpr bool fft_tws_pass_in_smem(int N, bool rev, int pass)
+{
+    return pass >= 1 && ((N / fft_elems(N)) % fft_ns_at(N, rev, pass)) == 0;
+}
+__host__ __device__ constexpr int fft_tws_offset(int N, bool rev, int pass)
+{
+    int off = 0;
+    for (int p = 1; p < pass; p++)
+        if (fft_tws_pass_in_smem(N, rev, p))
+            off += fft_ilog2(fft_radix_at(N, rev, p));
+    return off;
+}
+__host__ __device__ constexpr int fft_tws_slots(int N, bool rev = false)
+{
+    return fft_tws_offset(N, rev, fft_num_passes(N));
+}
+
+template <int N, bool FWD, bool REV = false, int PASS = 1>
+__device__ __forceinline__ void cta_fft_tws_init(float2* TW, int t, const float2* __restrict__ tw)
+{
+    if constexpr (PASS < fft_num_passes(N)) {
+        constexpr int E = fft_elems(N), TPV = N / E;
+        constexpr int R = fft_radix_at(N, REV, PASS), LG = fft_ilog2(R);
+        constexpr int NS = fft_ns_at(N, REV, PASS);
+        constexpr int OFF = fft_tws_offset(N, REV, PASS);
+        if constexpr (fft_tws_pass_in_smem(N, REV, PASS)) {
+            const int m = (t % NS) * (N / (NS * R));
+#pragma unroll
+            for (int k = 0; k < LG; k++) {
+                const float2 w = tw[m << k];
+                TW[(OFF + k) * TPV + t] = FWD ? w : cconj(w);
+            }
+        }
+        cta_fft_tws_init<N, FWD, REV, PASS + 1>(TW, t, tw);
+    }
+}
+
+template <int N, bool FWD, bool REV = false, int PASS = 0, int NS = 1, class After>
+__device__ __forceinline__ void cta_fft_tws(float2 (&v)[fft_elems(N)], float2* S, int t, const float2* TW,
+                                            const float2* __restrict__ tw, After after_first)
+{
+    constexpr int E = fft_elems(N);
+    constexpr int TPV = N / E;
+    constexpr int R = fft_radix_at(N, REV, PASS);
+    constexpr int NB = E / R;
+    if constexpr (NS > 1) {
+        constexpr int LG = fft_ilog2(R), OFF = fft_tws_offset(N, REV, PASS);
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+            const int j = t + b * TPV;
+#pragma unroll
+            for (int q = 0; q < R; q++)
+                v[b * R + q] = S[fft_pad(j + q * (N / R))];
+        }
+        if constexpr (fft_tws_pass_in_smem(N, REV, PASS)) {
+            float2 base[LG];
+#pragma unroll
+            for (int k = 0; k < LG; k++)
+                base[k] = TW[(OFF + k) * TPV + t];
+#pragma unroll
+            for (int b = 0; b < NB; b++)
+                apply_twiddles_l<R>(v + b * R, [&](int k) { return base[k]; });
+        } else {
+#pragma unroll
+            for (int b = 0; b < NB; b++) {
+                const int j = t + b * TPV;
+                apply_twiddles<R, N, FWD>(v + b * R, (j % NS) * (N / (NS * R)), tw);
+            }
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < NB; b++)
+        dft_r<R, FWD>(v + b * R);
+    if constexpr (NS * R < N) {
+        if constexpr (NS > 1)
+            __syncthreads();
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+            const int j = t + b * TPV;
+            const int base = (j / NS) * (NS * R) + (j % NS);
+#pragma unroll
+            for (int q = 0; q < R; q++)
+                S[fft_pad(base + q * NS)] = v[b * R + q];
+        }
+        __syncthreads();
+        if constexpr (PASS == 0)
+            after_first();
+        cta_fft_tws<N, FWD, REV, PASS + 1, NS * R>(v, S, t, TW, tw, after_first);
     }
 }
 

@@ -8,7 +8,10 @@
 // One kernel per launch does load (+window, +input swap) -> cta_fft -> (+output rotate, +|.|^2) -> store,
 // so a vector crosses HBM exactly once in each direction: 16 B per complex sample (12 B with the fused
 // magnitude-squared), the figure the HBM roofline is taken against.  Persistent CTAs loop over vectors.
+#include <cstdint>
+#include <cstdlib>
 #include "fft.cuh"
+#include "tma.cuh"
 
 namespace grb {
 
@@ -80,6 +83,115 @@ fft_vcc_kernel(const float2* __restrict__ in, void* __restrict__ out, long long 
         }
         if (N > E)
             __syncthreads(); // the next iteration's first pass overwrites S
+    }
+}
+
+// ---- streaming variant (1024 <= N <= 8192) ----------------------------------------------------------
+// ncu on the kernel above (profiles/r1_fftvcc_ncu.txt): 2 CTAs/SM at 127 registers, long-scoreboard stalls
+// 2.9 per issue -- every vector's loads are exposed, and window + twiddle lookups add 2.7x the input's L1
+// sectors.  Here a persistent CTA keeps ONE TMA bulk copy (its next VPC vectors, contiguous in the stream)
+// in flight while it transforms the current ones: the copy is issued as soon as the first pass has drained
+// the landing buffer, and completes behind passes 2..n and the stores.  The window sits in shared memory,
+// the loop-invariant base twiddles too (cta_fft_tws), so the only global loads left are the bulk copies.
+template <int N>
+struct VccStreamGeom {
+    using G = VccGeom<N>;
+    static constexpr int XIN_BYTES = G::VPC * N * 8;
+    static constexpr int S_BYTES = G::VPC * fft_smem_elems(N) * 8;
+    static constexpr int TW_BYTES = fft_tws_slots(N) * G::TPV * 8;
+    static constexpr int WIN_BYTES = N * 4;
+    static constexpr int SMEM = XIN_BYTES + S_BYTES + TW_BYTES + WIN_BYTES + 16;
+};
+
+template <int N, bool FWD>
+__global__ void __launch_bounds__(VccGeom<N>::NT)
+fft_vcc_stream_kernel(const float2* __restrict__ in, void* __restrict__ out, long long nvec,
+                      const float* __restrict__ window, int shift, int magsq, const float2* __restrict__ tw)
+{
+    using G = VccGeom<N>;
+    using SG = VccStreamGeom<N>;
+    constexpr int E = G::E, TPV = G::TPV, VPC = G::VPC;
+    constexpr int R0 = fft_first_radix(N, false);
+    constexpr int RL = fft_last_radix(N, false);
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float2* XIN = reinterpret_cast<float2*>(smem_raw);
+    float2* Sall = reinterpret_cast<float2*>(smem_raw + SG::XIN_BYTES);
+    float2* TW = reinterpret_cast<float2*>(smem_raw + SG::XIN_BYTES + SG::S_BYTES);
+    float* WIN = reinterpret_cast<float*>(smem_raw + SG::XIN_BYTES + SG::S_BYTES + SG::TW_BYTES);
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem_raw + SG::XIN_BYTES + SG::S_BYTES +
+                                                                    SG::TW_BYTES + SG::WIN_BYTES);
+    const int vl = threadIdx.x / TPV;
+    const int t = threadIdx.x % TPV;
+    float2* S = Sall + vl * fft_smem_elems(N);
+    const float2* X = XIN + vl * N;
+    const bool in_swap = (!FWD) && shift;
+    const bool out_rot = FWD && shift;
+    const bool has_win = window != nullptr;
+    const long long vstep = (long long)gridDim.x * VPC;
+
+    auto issue = [&](long long vbase) {
+        long long nv = nvec - vbase;
+        nv = nv > VPC ? VPC : nv;
+        const unsigned bytes = (unsigned)(nv * N * 8);
+        mbar_expect_tx(bar, bytes);
+        bulk_g2s(XIN, in + vbase * N, bytes, bar);
+    };
+
+    if (threadIdx.x == 0)
+        mbar_init(bar, 1);
+    if (vl == 0)
+        cta_fft_tws_init<N, FWD>(TW, t, tw);
+    if (has_win)
+        for (int i = threadIdx.x; i < N; i += G::NT)
+            WIN[i] = window[i];
+    __syncthreads();
+    long long vbase = (long long)blockIdx.x * VPC;
+    if (threadIdx.x == 0 && vbase < nvec)
+        issue(vbase);
+
+    unsigned phase = 0;
+    for (; vbase < nvec; vbase += vstep, phase ^= 1) {
+        const long long vec = vbase + vl;
+        const bool valid = vec < nvec;
+        mbar_wait(bar, phase);
+        float2 v[E];
+#pragma unroll
+        for (int b = 0; b < E / R0; b++) {
+#pragma unroll
+            for (int q = 0; q < R0; q++) {
+                int d = (t + b * TPV) + q * (N / R0);
+                if (in_swap)
+                    d = (d + N / 2) & (N - 1);
+                float2 x = valid ? X[d] : make_float2(0.f, 0.f);
+                if (has_win) {
+                    const float w = WIN[d];
+                    x = __fmul2_rn(x, make_float2(w, w));
+                }
+                v[b * R0 + q] = x;
+            }
+        }
+        const long long vnext = vbase + vstep;
+        cta_fft_tws<N, FWD>(v, S, t, TW, tw, [&]() {
+            if (threadIdx.x == 0 && vnext < nvec)
+                issue(vnext); // every thread has read XIN (barrier after the first pass)
+        });
+        if (valid) {
+#pragma unroll
+            for (int b = 0; b < E / RL; b++) {
+#pragma unroll
+                for (int q = 0; q < RL; q++) {
+                    int k = (t + b * TPV) + q * (N / RL);
+                    if (out_rot)
+                        k = (k + N / 2) & (N - 1);
+                    const float2 Xk = v[b * RL + q];
+                    if (magsq)
+                        reinterpret_cast<float*>(out)[vec * N + k] = fmaf(Xk.x, Xk.x, Xk.y * Xk.y);
+                    else
+                        reinterpret_cast<float2*>(out)[vec * N + k] = Xk;
+                }
+            }
+        }
+        __syncthreads(); // the next iteration's first pass overwrites S
     }
 }
 
@@ -168,10 +280,41 @@ static int launch_vcc(const void* in, void* out, long long nvec, const float* wi
     return 0;
 }
 
+template <int N, bool FWD>
+static int launch_vcc_stream(const void* in, void* out, long long nvec, const float* window, int shift, int magsq,
+                             const float2* tw, int nsm, cudaStream_t st)
+{
+    using G = VccGeom<N>;
+    using SG = VccStreamGeom<N>;
+    auto kern = fft_vcc_stream_kernel<N, FWD>;
+    GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::SMEM));
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, G::NT, SG::SMEM));
+    if (occ < 1)
+        occ = 1;
+    long long need = (nvec + G::VPC - 1) / G::VPC;
+    long long grid = (long long)nsm * occ;
+    if (grid > need)
+        grid = need;
+    kern<<<(unsigned)grid, G::NT, SG::SMEM, st>>>((const float2*)in, out, nvec, window, shift, magsq, tw);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
 template <int N>
 static int launch_vcc_dir(bool fwd, const void* in, void* out, long long nvec, const float* window, int shift,
                           int magsq, const float2* tw, int nsm, cudaStream_t st)
 {
+    if constexpr (N >= 1024 && N <= 8192) {
+        static const bool use_stream = [] {
+            const char* e = getenv("GRB200_FFT_STREAM");
+            return !(e && e[0] == '0');
+        }();
+        // TMA source must be 16-byte aligned; a few vectors are not worth a persistent pipeline
+        if (use_stream && (((uintptr_t)in) & 15) == 0 && nvec >= 64)
+            return fwd ? launch_vcc_stream<N, true>(in, out, nvec, window, shift, magsq, tw, nsm, st)
+                       : launch_vcc_stream<N, false>(in, out, nvec, window, shift, magsq, tw, nsm, st);
+    }
     return fwd ? launch_vcc<N, true>(in, out, nvec, window, shift, magsq, tw, nsm, st)
                : launch_vcc<N, false>(in, out, nvec, window, shift, magsq, tw, nsm, st);
 }

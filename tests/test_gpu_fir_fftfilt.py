@@ -166,6 +166,25 @@ def test_fft_filter_sizes(grb, orc, ntaps):
     assert_parity(got, po.f64_fft_filter(1, taps, x, blk.nsamples()), "f64 ntaps %d" % ntaps)
 
 
+@pytest.mark.parametrize("ntaps,decim", [(31, 1), (1500, 1), (4096, 1), (4096, 3)])
+def test_fft_filter_many_blocks_per_cta(grb, orc, ntaps, decim):
+    """2^22 samples: more overlap-save blocks than persistent CTAs, so the streaming kernel's TMA prefetch
+    chain (odd and even block bases, clipped last copy) is exercised end to end."""
+    import scipy.signal
+
+    rng = np.random.default_rng(77 + ntaps)
+    x, taps = crand(rng, (1 << 22) + 1234), crand(rng, ntaps) * np.float32(4.0 / max(ntaps, 4))
+    blk = grb.filter.fft_filter_ccc(decim, taps)
+    ns = blk.nsamples()
+    got = sched_mock.run_sync(blk, x, max_noutput=1 << 23)
+    nitems = (len(x) // decim // ns) * ns
+    assert len(got) == nitems
+    ref64 = scipy.signal.fftconvolve(x.astype(np.complex128), taps.astype(np.complex128))[: nitems * decim: decim]
+    assert_parity(got, ref64, "f64 ntaps %d decim %d" % (ntaps, decim))
+    n_c = (200000 // decim // ns) * ns  # the C oracle on a prefix
+    assert_parity(got[:n_c], orc.fft_filter_ccc(decim, taps, x[: n_c * decim]), "oracle prefix")
+
+
 def test_fft_filter_state_across_calls_and_set_taps(grb, orc):
     rng = np.random.default_rng(8)
     x, taps = crand(rng, 20000), crand(rng, 100)

@@ -165,6 +165,25 @@ def test_fft_vcc_sizes(grb, orc, N):
             assert_parity(got, po.f64_fft_vcc(N, fwd, w, sh, x), "f64 N=%d f%d s%d" % (N, fwd, sh))
 
 
+@pytest.mark.parametrize("N", [1024, 2048, 4096, 8192])
+def test_fft_vcc_streaming_kernel(grb, orc, N):
+    """>= 64 vectors per work() call take the persistent TMA-prefetch kernel (fft_vcc_stream_kernel);
+    odd vector counts exercise the clipped last bulk copy."""
+    rng = np.random.default_rng(1000 + N)
+    nvec = 701 if N <= 2048 else 333
+    x = crand(rng, N * nvec)
+    w = rng.uniform(0.1, 1, N).astype(np.float32)
+    for fwd in (True, False):
+        for sh in (False, True):
+            for win in (w, []):
+                got = grb.fft.fft_vcc(N, fwd, win, sh).process(x)
+                wl = win if len(win) else None
+                assert_parity(got, orc.fft_vcc(N, fwd, wl, sh, x), "N=%d f%d s%d" % (N, fwd, sh))
+                assert_parity(got, po.f64_fft_vcc(N, fwd, wl, sh, x), "f64 N=%d f%d s%d" % (N, fwd, sh))
+    P = grb.fft.fft_vcc(N, True, w, True).process(x, magsq=True)
+    assert_parity(P, orc.mag_squared(orc.fft_vcc(N, True, w, True, x)), "fused mag^2 N=%d" % N)
+
+
 def test_fft_vcc_config5_window_and_magsq(grb, orc):
     # BASELINE config 5 geometry: 4096-point Blackman-Harris, forward, + complex_to_mag_squared
     rng = np.random.default_rng(21)
