@@ -256,7 +256,7 @@ fir_tiled_kernel(const float2* __restrict__ in, float2* __restrict__ out, long l
 }
 
 // Warp-private pipelines: every warp owns its own double-buffered window (32*R outputs + halo) and output
-// staging, so after the one-time tap load there is NO CTA barrier: warps drift freely and the scheduler
+// staging (the consumed window buffer), so after the one-time tap load there is NO CTA barrier: warps drift freely and the scheduler
 // always finds FFMA2 work.  Costs Upad/(32*R) extra staged samples per tile; chosen when that is small.
 template <int R, bool CT>
 __global__ void __launch_bounds__(256)
@@ -269,9 +269,8 @@ fir_warptile_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
     constexpr int WT = 32 * R;          // outputs per warp tile
     const int Lm = WT + Upad;           // window positions staged per phase
     const size_t bufelems = (size_t)D * ldrow;
-    const size_t per_warp = 2 * bufelems + 32 * (R + 2);
+    const size_t per_warp = 2 * bufelems; // output staging reuses the window buffer just consumed
     float2* xbuf = reinterpret_cast<float2*>(smem_raw) + (size_t)warp * per_warp; // [2][D][ldrow]
-    float2* stage = xbuf + 2 * bufelems;
     tap_t* gs = reinterpret_cast<tap_t*>(reinterpret_cast<float2*>(smem_raw) + (size_t)nwarp * per_warp);
 
     for (int e = tid; e < D * Upad; e += blockDim.x)
@@ -341,7 +340,9 @@ fir_warptile_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
                 }
             }
         }
-        // ---- transpose through the warp's staging area, coalesced stores ----
+        // ---- transpose through the consumed window buffer (>= 32*(R+2) items), coalesced stores ----
+        __syncwarp(); // every lane is done reading the window
+        float2* stage = xbuf + (size_t)b * bufelems;
         float2* os = stage + lane * (R + 2);
 #pragma unroll
         for (int r = 0; r < R; r += 2)
@@ -363,6 +364,122 @@ fir_warptile_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
             }
         }
         __syncwarp(); // staging and this buffer are free again
+    }
+    cp_async_wait<0>();
+}
+
+// Long filters: split the TAPS across the warps of a CTA instead of the outputs.  Every warp works on the same
+// 32*R outputs and owns a contiguous range of tap chunks (a chunk = R taps of one decimation phase); the W
+// partial sums meet in shared memory.  The staged window is then only D*(32*R + Upad) items however long the
+// filter is, so it can be double buffered with 2 CTAs (16 warps) per SM, where the output-tiled kernel above
+// fits one single-buffered 4-warp CTA and leaves the FP32 pipe idle while it stages (ncu, profiles/
+// r1_firdec_ncu.txt: 10 % occupancy, FMA pipe 63 % active, 27 % of shared wavefronts are staging conflicts).
+template <int R, bool CT>
+__global__ void __launch_bounds__(256)
+fir_splitk_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int D,
+                  int Upad, const typename TapT<CT>::type* __restrict__ gtaps, int ldrow, int aligned16)
+{
+    using tap_t = typename TapT<CT>::type;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int W = 8;               // warps per CTA
+    constexpr int WT = 32 * R;         // outputs per tile
+    constexpr int RS = 32 * (R + 2);   // one warp's partial sums (skewed like the input rows)
+    const int Lm = WT + Upad;
+    const size_t bufelems = (size_t)D * ldrow; // >= W*RS (host checks): the partial sums reuse the consumed buffer
+    float2* xbuf = reinterpret_cast<float2*>(smem_raw); // [2][D][ldrow]
+    tap_t* gs = reinterpret_cast<tap_t*>(xbuf + 2 * bufelems);
+
+    const int UB = Upad / R;           // chunks per phase
+    const int C = D * UB;
+    const int per = (C + W - 1) / W;
+    const int c_begin = warp * per, c_end = min(C, c_begin + per);
+
+    for (int e = tid; e < D * Upad; e += 256)
+        gs[e] = gtaps[e];
+    const long long ntiles = (nout + WT - 1) / WT;
+    long long tile = blockIdx.x;
+    if (tile >= ntiles)
+        return;
+    fir_stage_tile<R>(xbuf, in, tile * WT * D, nin, D, Lm, ldrow, tid, 256, aligned16 != 0);
+    cp_async_commit();
+
+    int b = 0;
+    for (; tile < ntiles; tile += gridDim.x, b ^= 1) {
+        float2* xs = xbuf + (size_t)b * bufelems;
+        cp_async_wait<0>();
+        __syncthreads(); // this tile has landed for everyone; the previous tile's reduction is over
+        const long long next = tile + gridDim.x;
+        if (next < ntiles)
+            fir_stage_tile<R>(xbuf + (size_t)(b ^ 1) * bufelems, in, next * WT * D, nin, D, Lm, ldrow, tid, 256,
+                              aligned16 != 0);
+        cp_async_commit();
+
+        float2 acc[R];
+#pragma unroll
+        for (int r = 0; r < R; r++)
+            acc[r] = make_float2(0.f, 0.f);
+        float2 ring[R], rsw[CT ? R : 1];
+        int p_cur = -1;
+        for (int c = c_begin; c < c_end; c++) {
+            const int p = c / UB, ub = c - p * UB;
+            const float2* row = xs + p * ldrow + lane * (R + 2) + ub * (R + 2);
+            if (p != p_cur) { // first chunk of a phase for this warp: load the window afresh
+                p_cur = p;
+#pragma unroll
+                for (int k = 0; k < R; k += 2) {
+                    float4 v = *reinterpret_cast<const float4*>(row + k);
+                    ring[k] = make_float2(v.x, v.y);
+                    ring[k + 1] = make_float2(v.z, v.w);
+                    if (CT) {
+                        rsw[k] = make_float2(-v.y, v.x);
+                        rsw[k + 1] = make_float2(-v.w, v.z);
+                    }
+                }
+            }
+            const float2* nx = row + (R + 2);
+            float2 xn[R];
+#pragma unroll
+            for (int k = 0; k < R; k += 2) {
+                float4 v = *reinterpret_cast<const float4*>(nx + k);
+                xn[k] = make_float2(v.x, v.y);
+                xn[k + 1] = make_float2(v.z, v.w);
+            }
+            __align__(16) tap_t hh[R];
+            constexpr int TPV = CT ? 2 : 4; // taps per 16-byte load
+            const tap_t* gp = gs + p * Upad + ub * R;
+#pragma unroll
+            for (int k = 0; k < R; k += TPV)
+                reinterpret_cast<float4*>(hh)[k / TPV] = *reinterpret_cast<const float4*>(gp + k);
+#pragma unroll
+            for (int uu = 0; uu < R; uu++) {
+#pragma unroll
+                for (int r = 0; r < R; r++)
+                    mac2(acc[r], hh[uu], ring[(uu + r) % R], rsw[CT ? (uu + r) % R : 0]);
+                ring[uu] = xn[uu];
+                if (CT)
+                    rsw[uu] = make_float2(-xn[uu].y, xn[uu].x);
+            }
+        }
+        __syncthreads(); // every warp is done reading this buffer
+        {
+            float2* os = xs + warp * RS + lane * (R + 2);
+#pragma unroll
+            for (int r = 0; r < R; r += 2)
+                *reinterpret_cast<float4*>(os + r) = make_float4(acc[r].x, acc[r].y, acc[r + 1].x, acc[r + 1].y);
+        }
+        __syncthreads();
+        const long long w0 = tile * WT;
+#pragma unroll
+        for (int o = tid; o < WT; o += 256) {
+            const float2* rp = xs + o + 2 * (o / R);
+            float2 sum = rp[0];
+#pragma unroll
+            for (int w = 1; w < W; w++)
+                sum = __fadd2_rn(sum, rp[w * RS]);
+            if (w0 + o < nout)
+                out[w0 + o] = sum;
+        }
     }
     cp_async_wait<0>();
 }
@@ -395,7 +512,7 @@ fir_warp_kernel(const float2* __restrict__ in, float2* __restrict__ out, long lo
 struct FirPlan {
     int R = 0, NT = 0, NBUF = 0, Upad = 0, ldrow = 0;
     size_t smem = 0;
-    bool tiled = false, warptile = false;
+    bool tiled = false, warptile = false, splitk = false;
 };
 
 static size_t fir_smem(int D, int Upad, bool ct, int R, int NT, int NBUF, int* ldrow_out)
@@ -428,8 +545,8 @@ static FirPlan plan_fir(int D, int ntaps, bool ct)
             return;
         const int Lm = 32 * R + best.Upad;
         const int ld = Lm / R * (R + 2);
-        const size_t per_warp = ((size_t)2 * D * ld + 32 * (R + 2)) * 8;
-        if (per_warp <= 16 * 1024) {
+        const size_t per_warp = (size_t)2 * D * ld * 8;
+        if (per_warp <= 12 * 1024) {
             best.R = R, best.NT = NT, best.NBUF = 2, best.ldrow = ld, best.tiled = true, best.warptile = true;
             best.smem = per_warp * (NT / 32) + (size_t)D * best.Upad * (ct ? 8 : 4);
         }
@@ -443,8 +560,34 @@ static FirPlan plan_fir(int D, int ntaps, bool ct)
                 take_warptile(R, NT);
         }
     }
+    if (best.tiled)
+        return best;
     take_warptile(16, 128);
     take_warptile(8, 128);
+    // long filters: taps split across the 8 warps of a CTA, double-buffered window, 2 CTAs per SM
+    auto take_splitk = [&](int R) {
+        if (best.tiled || (ct && R == 16))
+            return;
+        const int Lm = 32 * R + best.Upad;
+        int ld = Lm / R * (R + 2);
+        if (D > 1) // phase rows 16 bytes apart modulo 128: the D-strided staging stores spread over all banks
+            while (ld % 16 != 2)
+                ld += 2;
+        const size_t buf = (size_t)D * ld * 8;
+        const size_t s = 2 * buf + (size_t)D * best.Upad * (ct ? 8 : 4);
+        const int chunks = D * (best.Upad / R);
+        if (chunks >= 16 && buf >= (size_t)8 * 32 * (R + 2) * 8 && s <= two_per_sm) {
+            best.R = R, best.NT = 256, best.NBUF = 2, best.ldrow = ld, best.smem = s, best.tiled = true, best.splitk = true;
+        }
+    };
+    static const bool allow_splitk = [] {
+        const char* e = getenv("GRB200_FIR_SPLITK");
+        return !(e && e[0] == '0');
+    }();
+    if (allow_splitk) {
+        take_splitk(16);
+        take_splitk(8);
+    }
     const int cand[4][2] = { { 16, 256 }, { 16, 128 }, { 8, 256 }, { 8, 128 } };
     for (auto& c : cand)
         take(c[0], c[1], 2, two_per_sm);
@@ -516,9 +659,38 @@ static int launch_warptile(const FirPlan& pl, const void* in, void* out, long lo
 }
 
 template <int R, bool CT>
+static int launch_splitk(const FirPlan& pl, const void* in, void* out, long long nout, long long nin, int D,
+                         const void* gtaps, int nsm, cudaStream_t st)
+{
+    auto kern = fir_splitk_kernel<R, CT>;
+    static thread_local bool configured[16] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 15]) {
+        GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(226 * 1024)));
+        configured[dev & 15] = true;
+    }
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, pl.smem));
+    if (occ < 1)
+        occ = 1;
+    const long long ntiles = (nout + 32 * R - 1) / (32 * R);
+    long long grid = (long long)nsm * occ;
+    if (grid > ntiles)
+        grid = ntiles;
+    const int aligned16 = (((uintptr_t)in) & 15) == 0;
+    kern<<<(unsigned)grid, 256, pl.smem, st>>>((const float2*)in, (float2*)out, nout, nin, D, pl.Upad,
+                                               (const typename TapT<CT>::type*)gtaps, pl.ldrow, aligned16);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+template <int R, bool CT>
 static int launch_tiled_nb(const FirPlan& pl, const void* in, void* out, long long nout, long long nin, int D,
                            const void* gtaps, int nsm, cudaStream_t st)
 {
+    if (pl.splitk)
+        return launch_splitk<R, CT>(pl, in, out, nout, nin, D, gtaps, nsm, st);
     if (pl.warptile)
         return launch_warptile<R, CT>(pl, in, out, nout, nin, D, gtaps, nsm, st);
     return pl.NBUF == 2 ? launch_tiled<R, CT, 2>(pl, in, out, nout, nin, D, gtaps, nsm, st)

@@ -63,6 +63,27 @@ def test_fir_ccc_sweep(grb, orc, ntaps, decim):
     assert_parity(got, po.f64_fir(decim, taps, x), "ccc f64")
 
 
+@pytest.mark.parametrize("ntaps,decim,cplx", [(1024, 8, False), (1000, 1, False), (777, 3, False), (600, 2, True), (2048, 5, True)])
+def test_fir_long_taps_many_tiles(grb, orc, ntaps, decim, cplx):
+    """Long filters take the split-tap kernel (taps spread over the warps of a CTA, partial sums reduced in
+    shared memory); enough outputs that every persistent CTA walks several double-buffered tiles."""
+    rng = np.random.default_rng(ntaps + decim)
+    nout = 296 * 512 * 3 + 777
+    x = crand(rng, nout * decim)
+    taps = crand(rng, ntaps) if cplx else rng.uniform(-1, 1, ntaps).astype(np.float32)
+    blk = (grb.filter.fir_filter_ccc if cplx else grb.filter.fir_filter_ccf)(decim, taps)
+    got = sched_mock.run_sync(blk, x, max_noutput=1 << 24)
+    assert len(got) == nout
+    # float64 check on three windows (a full float64 convolution of this size would take minutes)
+    xin = np.concatenate([np.zeros(ntaps - 1, np.complex64), x])
+    for o0 in (0, nout // 2 - 100, nout - 3000):
+        seg = xin[o0 * decim: (o0 + 3000) * decim + ntaps - 1]
+        assert_parity(got[o0:o0 + 3000], orc.fir(decim, taps, seg, 3000), "oracle window %d" % o0)
+        ref64 = po.f64_fir(decim, taps, seg[ntaps - 1:] if o0 == 0 else seg)
+        if o0 == 0:
+            assert_parity(got[:3000], ref64[:3000], "f64 window 0")
+
+
 def test_fir_scheduler_sized_chunks_equal_one_call(grb):
     rng = np.random.default_rng(3)
     x, taps = crand(rng, 50000), rng.uniform(-1, 1, 64).astype(np.float32)
