@@ -455,6 +455,11 @@ def main():
     if args.impl == "reference":
         return run_reference_arm(args, wl_cls)
 
+    # library chatter on fd 1 (e.g. NCCL's version banner) goes to stderr; stdout carries the ONE JSON line
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
 
     import gnuradio_b200 as grb
@@ -470,6 +475,8 @@ def main():
         import torch.distributed as dist_mod
 
         dist = dist_mod
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # the version banner goes to stdout and would precede the JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     launches0 = grb.launch_count()
     # a real (non-default) stream: the C-ABI treats a NULL stream as "the handle's own stream", and the CUDA
@@ -521,19 +528,28 @@ def main():
         "roofline": roofline, "gpu_launches": launches_timed, "gpu_launches_total_process": launches,
     }
 
-    if rank == 0 and world == 1 and not args.no_e2e and hasattr(wl, "e2e_setup"):
+    if not args.no_e2e and hasattr(wl, "e2e_setup"):
+        # every rank pushes its own host-resident segment through the host-buffer C-ABI call (its own PCIe link);
+        # barrier on both sides, max over ranks
         bi, bo = wl.e2e_setup(28)
         for _ in range(2):
             wl.e2e_step()
-        t0 = time.perf_counter()
         ksteps = max(3, min(args.steps, 8))
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
         for _ in range(ksteps):
             wl.e2e_step()  # blocking: returns when the host output buffers are valid
-        dt = time.perf_counter() - t0
-        line["e2e"] = {"value": wl.e2e_n * ksteps / dt / 1e6, "unit": "Msps", "h2d_bytes_per_step": bi,
-                       "d2h_bytes_per_step": bo, "steps": ksteps,
-                       "call": "grb200_pfb_chan_work_interleaved (pinned host in/out, 2^28 samples per step)",
-                       "pcie_gbs_each_way": bi * ksteps / dt / 1e9}
+        torch.cuda.synchronize()
+        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        dt = float(te.item())
+        line["e2e"] = {"value": wl.e2e_n * world * ksteps / dt / 1e6, "unit": "Msps", "h2d_bytes_per_step": bi * world,
+                       "d2h_bytes_per_step": bo * world, "steps": ksteps,
+                       "call": "grb200_pfb_chan_work_interleaved (pinned host in/out, 2^28 samples per step per GPU)",
+                       "pcie_gbs_each_way": bi * world * ksteps / dt / 1e9}
         line["gpu_launches_e2e"] = grb.launch_count() - launches0 - launches
 
     with ClockSampler(local) as _:
@@ -576,10 +592,12 @@ def main():
                                           "wall = %.0f core-seconds); 1 thread = %.2f Msps over %.1f s (what one GNU Radio block "
                                           "thread delivers)" % (rN, cores, dtN, dtN * cores, v1, dt1),
                                 "value_1core": v1}
-    if rank == 0:
-        print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
     return 0
 
 
