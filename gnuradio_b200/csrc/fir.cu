@@ -697,6 +697,10 @@ static int launch_tiled_nb(const FirPlan& pl, const void* in, void* out, long lo
                         : launch_tiled<R, CT, 1>(pl, in, out, nout, nin, D, gtaps, nsm, st);
 }
 
+bool fir_tc_eligible(bool ct, int D, int ntaps, const void* in, long long nout);
+int fir_tc_launch(int ntaps, const float* rev, const void* in, void* out, long long nout, long long nin, int nsm,
+                  cudaStream_t st);
+
 // gtaps: phase-major padded taps [D][Upad]; rev: reversed taps [ntaps] (both on the device).
 int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, const void* in, void* out,
                long long nout, cudaStream_t st)
@@ -708,6 +712,8 @@ int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, co
     int dev = 0;
     cudaGetDevice(&dev);
     const int nsm = sm_count(dev);
+    if (fir_tc_eligible(ct, D, ntaps, in, nout)) // tcgen05 block-Toeplitz path (fir_tc.cu)
+        return fir_tc_launch(ntaps, (const float*)rev, in, out, nout, nin, nsm, st);
     if (pl.tiled) {
         if (ct)
             return launch_tiled_nb<8, true>(pl, in, out, nout, nin, D, gtaps, nsm, st);

@@ -1,0 +1,406 @@
+// fir_tc.cu -- fir_filter_ccf (decimation 1, <= 64 real taps) on the 5th-generation tensor cores (tcgen05, sm_100a).
+//
+// Why: the CUDA-core kernel (fir.cu) sits on the FP32 pipe (ncu: FMA pipe 70 % busy, 47 of 66.6 TFLOP/s measured
+// peak) at 45 % of the HBM roofline; 256 flop per complex sample cannot reach the 16 B/sample HBM bound on that pipe.
+// The FIR is a block-Toeplitz product, which the tensor cores evaluate at fp32 accuracy with a 3-term TF32 split.
+//
+// Math (reference: kernel::fir_filter<gr_complex,gr_complex,float>::filterN, gr-filter/lib/fir_filter.cc:101-141):
+//   out[i] = sum_t h[t] * in[i+t],  h = reversed taps zero-padded to 64.
+// Cut the input into rows of 64 complex items, X_r[k] = in[64 r + k].  Then for j in [0,64)
+//   out[64 r + j] = sum_k T0[j][k] X_r[k] + sum_k T1[j][k] X_{r+1}[k],
+//   T0[j][k] = h[k-j] (k >= j),  T1[j][k] = h[64+k-j] (k < j)        (two triangular Toeplitz blocks).
+// Real taps act on re and im separately, so the de-interleaved re / im rows are just 2 columns of the B operand:
+//   D[m][n] = sum_k A[m][k] B[n][k],  A = [T0; T1] (M = 128 TMEM lanes), n = 2 r + c (N = 128 per tile), K = 64,
+// and out = D[T0 lanes][n] + D[T1 lanes][n + 2] is formed in the epilogue.  The A rows are permuted so that both
+// halves of an output position sit in the SAME 32-lane TMEM sub-partition (lanes 0-15: T0 rows, lanes 16-31: T1 rows
+// of 16 positions): one thread reads both with two tcgen05.ld.16x256b (second one 2 columns to the right) and adds them.
+//
+// Precision: kind::tf32 truncates the low 13 mantissa bits of an fp32 operand (measured: tools/tc_probe.cu), so
+// x_hi is the raw value and x_lo = x - trunc(x) is exact; D = A_hi B_hi + A_lo B_hi + A_hi B_lo leaves an error of
+// ~2^-21 per product (fp32 accumulation in TMEM).
+//
+// Pipeline per CTA (persistent, 1 CTA/SM), warp-specialised:
+//   1 TMA warp      : cp.async.bulk of the raw 32 KiB input tile into a 3-deep shared-memory ring (3 tiles in flight)
+//   8 converter warps: raw tile -> (hi, lo) split, re/im de-interleaved -> swizzled K-major B tiles (2 stages)
+//   1 MMA warp      : 24 tcgen05.mma per tile from one elected thread; the Toeplitz operand A lives in TENSOR MEMORY
+//                     (hi + lo = 128 columns, written once per CTA), so only B is read from shared memory
+//   4 epilogue warps : TMEM -> registers -> add the two halves -> 64-byte-run global stores (3 accumulator stages)
+// mbarriers: raw_full/raw_empty, b_full/b_empty, d_full/d_empty.  A tile = 64 input rows -> 63 output rows (tiles
+// overlap by one row, so no tile depends on another).
+#include "common.cuh"
+#include "tma.cuh"
+
+namespace grb {
+
+namespace tc {
+
+constexpr int ROWS = 64;        // input rows per tile (N = 2*ROWS columns)
+constexpr int OROWS = ROWS - 1; // output rows per tile
+constexpr int NCOL = 2 * ROWS;  // 128
+constexpr int NCONV = 8;        // converter warps
+constexpr int NEPI = 4;         // epilogue warps (one per TMEM sub-partition)
+constexpr int W_TMA = NCONV, W_MMA = NCONV + 1, W_EPI = NCONV + 2;
+constexpr int NTHREADS = (NCONV + 2 + NEPI) * 32;
+constexpr int RSTAGES = 3; // raw input ring
+constexpr int BSTAGES = 2; // converted operand ring
+constexpr int DSTAGES = 3; // TMEM accumulator ring
+constexpr int RAW_BYTES = ROWS * 64 * 8;     // 32 KiB
+constexpr int KBLK_BYTES = 128 * 128;        // one 32-float K block of a 128-row operand, SW128
+constexpr int OPER_BYTES = 2 * KBLK_BYTES;   // K = 64 floats: 32 KiB
+constexpr int BSTAGE_BYTES = 2 * OPER_BYTES; // hi + lo
+constexpr int NBARS = 2 * RSTAGES + 2 * BSTAGES + 2 * DSTAGES;
+constexpr int SMEM_BYTES = BSTAGES * BSTAGE_BYTES + RSTAGES * RAW_BYTES + 256 + 1024;
+static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+constexpr unsigned TMEM_A_HI = DSTAGES * NCOL; // columns 384..447
+constexpr unsigned TMEM_A_LO = TMEM_A_HI + 64; // columns 448..511
+
+__device__ __forceinline__ unsigned long long desc_sw128(unsigned saddr)
+{
+    unsigned long long d = 0;
+    d |= (unsigned long long)((saddr & 0x3FFFF) >> 4);
+    d |= (unsigned long long)1 << 16;           // leading byte offset: unused for swizzled K-major
+    d |= (unsigned long long)(1024 >> 4) << 32; // stride byte offset: 8 rows x 128 B
+    d |= (unsigned long long)1 << 46;           // descriptor version (sm_100)
+    d |= (unsigned long long)2 << 61;           // SWIZZLE_128B
+    return d;
+}
+// D[tmem] (+)= A[tmem] * B[smem]^T, A: lane = row, one 32-bit column per k
+__device__ __forceinline__ void mma_tf32_ts(unsigned tmem_d, unsigned tmem_a, unsigned long long bdesc, unsigned idesc,
+                                            unsigned accumulate)
+{
+    asm volatile(
+        "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n}\n" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(unsigned long long* bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_init_nofence(unsigned long long* bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void sts128(unsigned saddr, float4 v)
+{
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 lds128(unsigned saddr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr) : "memory");
+    return v;
+}
+__device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
+
+#define GRB_TMEM_LD_16x256_X4(r, taddr)                                                                                   \
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x4.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];" \
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),        \
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])   \
+                 : "r"(taddr))
+#define GRB_TMEM_ST_32x32_X8(taddr, r)                                                                                    \
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(r[0]), "r"(r[1]), \
+                 "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])                                         \
+                 : "memory")
+
+} // namespace tc
+
+template <bool TRACE>
+__global__ void __launch_bounds__(tc::NTHREADS, 1)
+    fir_tc_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int ntaps,
+                  const float* __restrict__ rev, long long ntiles, long long* __restrict__ trace)
+{
+    using namespace tc;
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    unsigned char* sB = smem;                            // BSTAGES x [B_hi | B_lo]
+    unsigned char* sR = smem + BSTAGES * BSTAGE_BYTES;   // RSTAGES raw tiles
+    unsigned long long* bars = (unsigned long long*)(sR + RSTAGES * RAW_BYTES);
+    unsigned long long* raw_full = bars;
+    unsigned long long* raw_empty = raw_full + RSTAGES;
+    unsigned long long* b_full = raw_empty + RSTAGES;
+    unsigned long long* b_empty = b_full + BSTAGES;
+    unsigned long long* d_full = b_empty + BSTAGES;
+    unsigned long long* d_empty = d_full + DSTAGES;
+    unsigned long long* a_ready = bars + NBARS;
+    unsigned* tmem_ptr = (unsigned*)(bars + NBARS + 1);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long G = gridDim.x;
+
+    if (warp == W_MMA) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (tid == 0) {
+        for (int i = 0; i < RSTAGES; ++i) {
+            mbar_init_nofence(&raw_full[i], 1);
+            mbar_init_nofence(&raw_empty[i], NCONV);
+        }
+        for (int i = 0; i < BSTAGES; ++i) {
+            mbar_init_nofence(&b_full[i], NCONV);
+            mbar_init_nofence(&b_empty[i], 1);
+        }
+        for (int i = 0; i < DSTAGES; ++i) {
+            mbar_init_nofence(&d_full[i], 1);
+            mbar_init_nofence(&d_empty[i], NEPI);
+        }
+        mbar_init_nofence(a_ready, NEPI);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem = *tmem_ptr;
+
+    if (warp == W_TMA) {
+        // ================= loader: one bulk copy per tile, up to RSTAGES tiles ahead of the converters =================
+        if (lane == 0) {
+            int it = 0;
+#pragma unroll 1
+            for (long long tile = blockIdx.x; tile < ntiles; tile += G, ++it) {
+                const int rs = it % RSTAGES, use = it / RSTAGES;
+                if (use > 0)
+                    mbar_wait(&raw_empty[rs], (use - 1) & 1);
+                const long long e0 = tile * (long long)(OROWS * 64);
+                if (e0 + ROWS * 64 <= nin) {
+                    mbar_expect_tx(&raw_full[rs], RAW_BYTES);
+                    bulk_g2s(sR + rs * RAW_BYTES, in + e0, RAW_BYTES, &raw_full[rs]);
+                } else {
+                    mbar_arrive(&raw_full[rs]); // ragged last tile: the converters read global memory with bounds checks
+                }
+            }
+        }
+    } else if (warp < NCONV) {
+        // ================= converters: raw tile -> (hi, lo), re/im de-interleaved, swizzled K-major B operand =================
+        const int p = tid;
+        const unsigned sB_u32 = smem_u32(sB), sR_u32 = smem_u32(sR);
+        const int hsel = (lane >> 2) & 1; // which 16-byte half of its 32-byte chunk a lane reads first (bank-conflict free)
+        int it = 0;
+#pragma unroll 1
+        for (long long tile = blockIdx.x; tile < ntiles; tile += G, ++it) {
+            const int rs = it % RSTAGES, ruse = it / RSTAGES;
+            const int stage = it % BSTAGES, buse = it / BSTAGES;
+            const bool tr = TRACE && p == 0 && blockIdx.x == 0 && it < 64;
+            const long long e0 = tile * (long long)(OROWS * 64);
+            if (tr) trace[it * 16 + 0] = clock64();
+            mbar_wait(&raw_full[rs], ruse & 1);
+            if (tr) trace[it * 16 + 1] = clock64();
+            float4 v[4][2];
+            if (e0 + ROWS * 64 <= nin) {
+                const unsigned rb = sR_u32 + rs * RAW_BYTES + 32 * p;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float4 x = lds128(rb + 8192 * i + 16 * hsel);
+                    const float4 y = lds128(rb + 8192 * i + 16 * (1 - hsel));
+                    v[i][0] = hsel ? y : x;
+                    v[i][1] = hsel ? x : y;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const long long e = e0 + 4 * (p + 256 * i);
+                    float2 z[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) z[u] = (e + u < nin) ? in[e + u] : make_float2(0.f, 0.f);
+                    v[i][0] = make_float4(z[0].x, z[0].y, z[1].x, z[1].y);
+                    v[i][1] = make_float4(z[2].x, z[2].y, z[3].x, z[3].y);
+                }
+            }
+            if (buse > 0)
+                mbar_wait(&b_empty[stage], (buse - 1) & 1);
+            if (tr) trace[it * 16 + 2] = clock64();
+            const unsigned bh = sB_u32 + stage * BSTAGE_BYTES;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int c = p + 256 * i;
+                const int n0 = 2 * (c >> 4), q = c & 15;
+                const unsigned base = (unsigned)((q >> 3) * KBLK_BYTES + (n0 >> 3) * 1024 + (n0 & 7) * 128);
+                const unsigned off_re = base + (((q & 7) ^ (n0 & 7)) << 4);
+                const unsigned off_im = base + 128 + (((q & 7) ^ ((n0 & 7) + 1)) << 4);
+                const float4 a = v[i][0], b = v[i][1];
+                const float4 re = make_float4(a.x, a.z, b.x, b.z), im = make_float4(a.y, a.w, b.y, b.w);
+                const float4 rl = make_float4(re.x - trunc_tf32(re.x), re.y - trunc_tf32(re.y), re.z - trunc_tf32(re.z),
+                                              re.w - trunc_tf32(re.w));
+                const float4 il = make_float4(im.x - trunc_tf32(im.x), im.y - trunc_tf32(im.y), im.z - trunc_tf32(im.z),
+                                              im.w - trunc_tf32(im.w));
+                sts128(bh + off_re, re); // the tensor core ignores the low 13 bits: raw value = hi part
+                sts128(bh + off_im, im);
+                sts128(bh + OPER_BYTES + off_re, rl);
+                sts128(bh + OPER_BYTES + off_im, il);
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&b_full[stage]);
+                mbar_arrive(&raw_empty[rs]); // the stores above depend on every raw read of this warp
+            }
+            if (tr) trace[it * 16 + 3] = clock64();
+        }
+    }
+    else if (warp == W_MMA) {
+        // ================= MMA issuer: one thread, 3 split terms x 8 K steps per tile, A from tensor memory =================
+        if (lane == 0) {
+            const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(NCOL >> 3) << 17) | ((128u >> 4) << 24);
+            mbar_wait(a_ready, 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            int it = 0;
+#pragma unroll 1
+            for (long long tile = blockIdx.x; tile < ntiles; tile += G, ++it) {
+                const int stage = it % BSTAGES, buse = it / BSTAGES;
+                const int acc = it % DSTAGES, duse = it / DSTAGES;
+                const bool tr = TRACE && blockIdx.x == 0 && it < 64;
+                if (tr) trace[it * 16 + 4] = clock64();
+                mbar_wait(&b_full[stage], buse & 1);
+                if (tr) trace[it * 16 + 5] = clock64();
+                if (duse > 0)
+                    mbar_wait(&d_empty[acc], (duse - 1) & 1);
+                if (tr) trace[it * 16 + 6] = clock64();
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const unsigned d = tmem + acc * NCOL;
+                const unsigned b_addr = smem_u32(sB + stage * BSTAGE_BYTES);
+                unsigned n = 0;
+#pragma unroll
+                for (int term = 0; term < 3; ++term) { // A_hi B_hi + A_lo B_hi + A_hi B_lo
+                    const unsigned ta = tmem + (term == 1 ? TMEM_A_LO : TMEM_A_HI);
+                    const unsigned bo = b_addr + (term == 2 ? OPER_BYTES : 0);
+#pragma unroll
+                    for (int kk = 0; kk < 8; ++kk)
+                        mma_tf32_ts(d, ta + 8 * kk, desc_sw128(bo + (kk >> 2) * KBLK_BYTES + (kk & 3) * 32), idesc, n++);
+                }
+                umma_commit(&b_empty[stage]); // shared-memory stage may be refilled once these MMAs retire
+                umma_commit(&d_full[acc]);    // accumulator ready for the epilogue
+                if (tr) trace[it * 16 + 7] = clock64();
+            }
+        }
+    } else if (warp >= W_EPI) {
+        const int s = warp & 3; // the TMEM sub-partition (lanes 32 s .. 32 s + 31) this warp can access
+        // ---- one-time: Toeplitz operand A = [T0; T1] into tensor memory.  Lane l < 16 of sub-partition s holds the T0 row
+        //      of output position j = 16 s + l, lane 16 + l the T1 row of the same position (so one thread can add them) ----
+        {
+            const int j = 16 * s + (lane & 15);
+            const bool lowhalf = lane < 16;
+            const unsigned trow = tmem + ((unsigned)(32 * s) << 16);
+#pragma unroll 1
+            for (int k0 = 0; k0 < 64; k0 += 8) {
+                unsigned hi[8], lo[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int k = k0 + i;
+                    const int t = lowhalf ? (k - j) : (64 + k - j);
+                    const bool nz = lowhalf ? (k >= j) : (k < j);
+                    const float v = (nz && t < ntaps) ? __ldg(rev + t) : 0.f;
+                    const float h = trunc_tf32(v);
+                    hi[i] = __float_as_uint(h);
+                    lo[i] = __float_as_uint(v - h);
+                }
+                GRB_TMEM_ST_32x32_X8(trow + TMEM_A_HI + k0, hi);
+                GRB_TMEM_ST_32x32_X8(trow + TMEM_A_LO + k0, lo);
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(a_ready);
+        }
+        // ================= epilogue: out = D[T0 lanes][n] + D[T1 lanes][n+2] -> global =================
+        int it = 0;
+#pragma unroll 1
+        for (long long tile = blockIdx.x; tile < ntiles; tile += G, ++it) {
+            const int acc = it % DSTAGES, duse = it / DSTAGES;
+            const bool tr = TRACE && blockIdx.x == 0 && it < 64 && warp == W_EPI && lane == 0;
+            if (tr) trace[it * 16 + 8] = clock64();
+            mbar_wait(&d_full[acc], duse & 1);
+            if (tr) trace[it * 16 + 9] = clock64();
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const unsigned t0 = tmem + ((unsigned)(32 * s) << 16) + acc * NCOL;
+            const unsigned t1 = t0 + (16u << 16) + 2;
+            const long long row0 = tile * OROWS;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                unsigned a[16], b[16];
+                GRB_TMEM_LD_16x256_X4(a, t0 + 32 * g);
+                GRB_TMEM_LD_16x256_X4(b, t1 + 32 * g); // g == 3 reads 2 columns past the stage: discarded (row 63)
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (g == 3) {
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive(&d_empty[acc]);
+                    if (tr) trace[it * 16 + 10] = clock64();
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int r = 16 * g + 4 * i + (lane & 3);
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) {
+                        const int j = 16 * s + (lane >> 2) + 8 * hh;
+                        const float re = __uint_as_float(a[4 * i + 2 * hh]) + __uint_as_float(b[4 * i + 2 * hh]);
+                        const float im = __uint_as_float(a[4 * i + 2 * hh + 1]) + __uint_as_float(b[4 * i + 2 * hh + 1]);
+                        const long long idx = (row0 + r) * 64 + j;
+                        if (r < OROWS && idx < nout)
+                            out[idx] = make_float2(re, im);
+                    }
+                }
+            }
+            if (tr) trace[it * 16 + 11] = clock64();
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == W_MMA)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
+// Tensor-core path for fir_filter_ccf: decimation 1, ntaps <= 64, `in` 16-byte aligned.  `rev` = reversed taps (device).
+bool fir_tc_eligible(bool ct, int D, int ntaps, const void* in, long long nout)
+{
+    if (ct || D != 1 || ntaps > 64 || ((uintptr_t)in & 15) != 0)
+        return false;
+    if (const char* e = getenv("GRB200_FIR_TC"))
+        return atoi(e) != 0;
+    return nout >= 64 * tc::OROWS; // below one tile the CUDA-core kernel's launch is cheaper
+}
+
+int fir_tc_launch(int ntaps, const float* rev, const void* in, void* out, long long nout, long long nin, int nsm,
+                  cudaStream_t st)
+{
+    static std::atomic<int> configured{0};
+    if (!configured.load(std::memory_order_acquire)) {
+        GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        configured.store(1, std::memory_order_release);
+    }
+    const long long rows = (nout + 63) / 64;
+    const long long ntiles = (rows + tc::OROWS - 1) / tc::OROWS;
+    const unsigned grid = (unsigned)(ntiles < nsm ? ntiles : nsm);
+    if (const char* path = getenv("GRB200_FIR_TC_TRACE")) { // developer aid: per-tile clock64() stamps of CTA 0
+        long long* dtrace = nullptr;
+        GRB_CUDA(cudaMalloc(&dtrace, 64 * 16 * sizeof(long long)));
+        GRB_CUDA(cudaMemsetAsync(dtrace, 0, 64 * 16 * sizeof(long long), st));
+        fir_tc_kernel<true><<<grid, tc::NTHREADS, tc::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps, rev,
+                                                                       ntiles, dtrace);
+        GRB_LAUNCH_CHECK();
+        std::vector<long long> h(64 * 16);
+        GRB_CUDA(cudaMemcpyAsync(h.data(), dtrace, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
+        GRB_CUDA(cudaStreamSynchronize(st));
+        cudaFree(dtrace);
+        if (FILE* f = fopen(path, "w")) {
+            for (int i = 0; i < 64; ++i) {
+                for (int j = 0; j < 12; ++j) fprintf(f, "%lld ", h[i * 16 + j] ? h[i * 16 + j] - h[0] : -1LL);
+                fprintf(f, "\n");
+            }
+            fclose(f);
+        }
+        return 0;
+    }
+    fir_tc_kernel<false><<<grid, tc::NTHREADS, tc::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps, rev,
+                                                                    ntiles, nullptr);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+} // namespace grb

@@ -84,14 +84,68 @@ def test_fir_long_taps_many_tiles(grb, orc, ntaps, decim, cplx):
             assert_parity(got[:3000], ref64[:3000], "f64 window 0")
 
 
-def test_fir_scheduler_sized_chunks_equal_one_call(grb):
+def test_fir_scheduler_sized_chunks_equal_one_call(grb, monkeypatch):
+    """Chunking must not change the result.  On the CUDA-core kernels that holds bit for bit; the tcgen05 path
+    (large, 16-byte aligned calls) sums each output in an order that depends on its position inside a 64-item row,
+    so there the invariant is the parity tolerance (the reference's VOLK kernels are alignment dependent too:
+    gr-filter/lib/fir_filter.cc:67-74,133-141)."""
     rng = np.random.default_rng(3)
     x, taps = crand(rng, 50000), rng.uniform(-1, 1, 64).astype(np.float32)
+    monkeypatch.setenv("GRB200_FIR_TC", "0")
     a = sched_mock.run_sync(grb.filter.fir_filter_ccf(1, taps), x, max_noutput=4096)
     b = sched_mock.run_sync(grb.filter.fir_filter_ccf(1, taps), x, max_noutput=1 << 20)
     c = sched_mock.run_sync(grb.filter.fir_filter_ccf(1, taps), x, max_noutput=1)[:64]
     np.testing.assert_array_equal(a, b)
     np.testing.assert_array_equal(a[:64], c)
+    monkeypatch.delenv("GRB200_FIR_TC")
+    d = sched_mock.run_sync(grb.filter.fir_filter_ccf(1, taps), x, max_noutput=1 << 20)
+    assert_parity(d, a, "tensor-core path vs chunked CUDA-core path")
+    assert_parity(d, po.f64_fir(1, taps, x), "tensor-core path vs float64")
+
+
+@pytest.mark.parametrize("ntaps,nout", [(64, 64 * 63), (64, 64 * 63 + 1), (64, 64 * 63 * 148 * 2 + 4095), (63, 100001),
+                                        (37, 250000), (2, 8191), (1, 70000), (64, 1 << 21)])
+def test_fir_tensor_core_path(grb, orc, monkeypatch, ntaps, nout):
+    """fir_tc_kernel (tcgen05 block-Toeplitz FIR, 3xTF32): ragged last tile, short filters (zero-padded Toeplitz),
+    one tile, several tiles per CTA; against the C oracle and float64, and against the CUDA-core kernel."""
+    monkeypatch.setenv("GRB200_FIR_TC", "1")
+    rng = np.random.default_rng(1000 * ntaps + nout % 997)
+    x = crand(rng, nout)
+    taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
+    xin = np.concatenate([np.zeros(ntaps - 1, np.complex64), x])
+    got = grb.filter.fir_filter_ccf(1, taps).process(xin, nout)
+    assert len(got) == nout and np.isfinite(got.view(np.float32)).all()
+    assert_parity(got, po.f64_fir(1, taps, x), "tc f64 %d/%d" % (ntaps, nout))
+    n0 = min(nout, 200000)
+    assert_parity(got[:n0], orc.fir(1, taps, xin[:n0 + ntaps - 1], n0), "tc oracle")
+    monkeypatch.setenv("GRB200_FIR_TC", "0")
+    ref = grb.filter.fir_filter_ccf(1, taps).process(xin, nout)
+    assert_parity(got, ref, "tc vs cuda-core")
+
+
+def test_fir_tensor_core_linearity_and_impulse(grb, monkeypatch):
+    """Size-independent properties at a BASELINE-sized call (2^24): impulse -> taps, linearity, shift invariance."""
+    monkeypatch.setenv("GRB200_FIR_TC", "1")
+    rng = np.random.default_rng(77)
+    n, ntaps = 1 << 24, 64
+    taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
+    blk = grb.filter.fir_filter_ccf(1, taps)
+    imp = np.zeros(n + ntaps - 1, np.complex64)
+    pos = [ntaps - 1, ntaps - 1 + 4031, ntaps - 1 + 64 * 63 * 148 + 5, n - 100]
+    for q in pos:
+        imp[q] = 1.0 + 2.0j
+    y = blk.process(imp, n)
+    for q in pos:
+        o = q - (ntaps - 1)
+        seg = y[o:o + ntaps]
+        assert_parity(seg, (taps * np.complex64(1 + 2j))[:len(seg)], "impulse at %d" % q)
+    y[np.concatenate([np.arange(q - (ntaps - 1), min(q + 1, n)) for q in pos])] = 0
+    assert not y.any()
+    a, b = crand(rng, n + ntaps - 1), crand(rng, n + ntaps - 1)
+    ya, yb, yab = blk.process(a, n), blk.process(b, n), blk.process((a + np.complex64(0.5) * b).astype(np.complex64), n)
+    assert_parity(yab, ya + np.complex64(0.5) * yb, "linearity")
+    ys = blk.process(a[64 * 7:], n - 64 * 7)
+    assert_parity(ys, ya[64 * 7:], "shift by 7 rows")
 
 
 def test_fir_empty_and_errors(grb):
