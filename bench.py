@@ -167,7 +167,7 @@ class FirCcf(Workload):
     name = "fir_filter_ccf 64 taps decim 1, 2^%d samples x %d rotating buffer sets (BASELINE configs[0])"
     block = "fir_filter_ccf"
     alg_bytes, flops, log2n, seed = 16.0, 256.0, 24, 1
-    kernel = "fir_warptile_kernel"
+    kernel = "fir_tc_kernel"
     ntaps, decim, nsets = 64, 1, 4
 
     def setup(self):
