@@ -235,6 +235,13 @@ int fftfilt_device_fftsize(int ntaps)
     int L = 4096;
     while (L < 2 * ntaps && L < 16384)
         L *= 2;
+    if (L == 8192 && ntaps - 1 > L / 4)
+        L = 16384; // > 25 % of every block would be overlap: the longer transform wins (cfg2: 70 -> 78 Gsps)
+    if (const char* e = getenv("GRB200_FFTFILT_L")) { // tuning knob: a longer transform wastes less on the overlap
+        const int v = atoi(e);
+        if ((v == 4096 || v == 8192 || v == 16384) && v >= L)
+            L = v;
+    }
     if (L - (ntaps - 1) < L / 4)
         return -1; // too many taps for a single-CTA transform
     return L;

@@ -55,6 +55,27 @@ def segment(rank, world, noutput_total, decimation=1, history=1, multiple=1, ite
                    (history - 1) * items_per_output)
 
 
+def exchange_halos(dist, pairs, rank, world, ring=False):
+    """exchange_halo for several (head, tail) pairs of one step in ONE batched send/recv group (one NCCL group launch
+    instead of len(pairs): the host-side cost of a halo exchange is per group, not per byte)."""
+    if world == 1:
+        return
+    right, left = rank + 1, rank - 1
+    if ring:
+        right, left = right % world, left % world
+    ops = []
+    for head, tail in pairs:
+        if head.numel() == 0:
+            continue
+        if right < world:
+            ops.append(dist.P2POp(dist.isend, tail, right))
+        if left >= 0:
+            ops.append(dist.P2POp(dist.irecv, head, left))
+    if ops:
+        for r in dist.batch_isend_irecv(ops):
+            r.wait()
+
+
 def exchange_halo(dist, head, tail, rank, world, ring=False):
     """Fill `head` (this rank's halo region, in front of its segment) with the left neighbour's `tail`
     (its newest halo-many items).  Rank 0 keeps what it has (zeros = the scheduler's preloaded history)

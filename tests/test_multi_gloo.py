@@ -60,7 +60,9 @@ def _worker(rank, world, port, case, outdir):
             buf[seg.halo:] = x[seg.in_begin:seg.in_end]
             tbuf = _c64_to_t(buf)
             head, tail = tbuf[: 2 * seg.halo], tbuf[-2 * seg.halo:].clone()
-            sharding.exchange_halo(dist, head, tail, rank, world)
+            # batched variant, the halo cut in two pairs (what bench.py does for several buffer sets per step)
+            h = seg.halo
+            sharding.exchange_halos(dist, [(head[:h], tail[:h]), (head[h:], tail[h:])], rank, world)
             ins = np.ascontiguousarray(tbuf.numpy().view(np.complex64).reshape(-1, M).T)
             y, consumed = orc.pfb_channelizer(M, taps, 1.0, ins, seg.noutput)
             assert consumed == seg.noutput

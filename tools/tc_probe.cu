@@ -129,7 +129,7 @@ __device__ __forceinline__ void mma_tf32_ts(unsigned tmem_d, unsigned tmem_a, un
         "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
-__global__ void __launch_bounds__(128) probe_ts(const float* A, const float* B, float* D)
+__global__ void __launch_bounds__(128) probe_ts(const float* A, const float* B, float* D, int shift)
 {
     extern __shared__ unsigned char smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -172,6 +172,9 @@ __global__ void __launch_bounds__(128) probe_ts(const float* A, const float* B, 
         const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(N >> 3) << 17) | ((unsigned)(M >> 4) << 24);
         for (int k = 0; k < K / 8; ++k)
             mma_tf32_ts(tmem, tmem + 128 + k * 8, make_desc_sw128(smem_u32(sB) + k * 32), idesc, k > 0);
+        if (shift) // accumulate the same product again, `shift` columns to the right: D'[m][n] = D[m][n] + D[m][n-shift]
+            for (int k = 0; k < K / 8; ++k)
+                mma_tf32_ts(tmem + shift, tmem + 128 + k * 8, make_desc_sw128(smem_u32(sB) + k * 32), idesc, 1);
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                      : "memory");
     }
@@ -267,7 +270,7 @@ int main()
         std::vector<float> D2(M * N);
         cudaMemset(dD, 0, D.size() * 4);
         cudaFuncSetAttribute(probe_ts, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        probe_ts<<<1, 128, smem>>>(dA, dB, dD);
+        probe_ts<<<1, 128, smem>>>(dA, dB, dD, 0);
         e = cudaDeviceSynchronize();
         printf("probe_ts: %s\n", cudaGetErrorString(e));
         if (e != cudaSuccess) return 1;
@@ -275,6 +278,22 @@ int main()
         double err = 0, ref = 0;
         for (int i = 0; i < M * N; ++i) { err += (double)(D2[i] - D[i]) * (D2[i] - D[i]); ref += (double)D[i] * D[i]; }
         printf("A-from-TMEM vs A-from-smem: nrms %.3e\n", sqrt(err / ref));
+        for (int shift : {4, 2, 6}) {
+            std::vector<float> D3(M * N);
+            probe_ts<<<1, 128, smem>>>(dA, dB, dD, shift);
+            e = cudaDeviceSynchronize();
+            printf("probe_ts shift %d: %s\n", shift, cudaGetErrorString(e));
+            if (e != cudaSuccess) return 1;
+            cudaMemcpy(D3.data(), dD, D3.size() * 4, cudaMemcpyDeviceToHost);
+            double err3 = 0, ref3 = 0;
+            for (int m = 0; m < M; ++m)
+                for (int n = shift; n < N; ++n) {
+                    const double want = (double)D[m * N + n] + D[m * N + n - shift];
+                    err3 += (D3[m * N + n] - want) * (D3[m * N + n] - want);
+                    ref3 += want * want;
+                }
+            printf("accumulate with D column base +%d: nrms vs D[n] + D[n-%d] = %.3e\n", shift, shift, sqrt(err3 / ref3));
+        }
     }
     return 0;
 }
