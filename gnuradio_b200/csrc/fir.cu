@@ -698,7 +698,7 @@ static int launch_tiled_nb(const FirPlan& pl, const void* in, void* out, long lo
 }
 
 bool fir_tc_eligible(bool ct, int D, int ntaps, const void* in, long long nout);
-int fir_tc_launch(int ntaps, const float* rev, const void* in, void* out, long long nout, long long nin, int nsm,
+int fir_tc_launch(bool ct, int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
                   cudaStream_t st);
 
 // gtaps: phase-major padded taps [D][Upad]; rev: reversed taps [ntaps] (both on the device).
@@ -713,7 +713,7 @@ int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, co
     cudaGetDevice(&dev);
     const int nsm = sm_count(dev);
     if (fir_tc_eligible(ct, D, ntaps, in, nout)) // tcgen05 block-Toeplitz path (fir_tc.cu)
-        return fir_tc_launch(ntaps, (const float*)rev, in, out, nout, nin, nsm, st);
+        return fir_tc_launch(ct, ntaps, rev, in, out, nout, nin, nsm, st);
     if (pl.tiled) {
         if (ct)
             return launch_tiled_nb<8, true>(pl, in, out, nout, nin, D, gtaps, nsm, st);

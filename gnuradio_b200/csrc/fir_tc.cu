@@ -1,4 +1,4 @@
-// fir_tc.cu -- fir_filter_ccf (decimation 1, <= 64 real taps) on the 5th-generation tensor cores (tcgen05, sm_100a).
+// fir_tc.cu -- fir_filter_ccf / fir_filter_ccc (decimation 1, <= 64 taps) on the 5th-generation tensor cores (tcgen05, sm_100a).
 //
 // Why: the CUDA-core kernel (fir.cu) sits on the FP32 pipe (ncu: FMA pipe 70 % busy, 47 of 66.6 TFLOP/s measured
 // peak) at 45 % of the HBM roofline; 256 flop per complex sample cannot reach the 16 B/sample HBM bound on that pipe.
@@ -14,6 +14,10 @@
 // and out = D[T0 lanes][n] + D[T1 lanes][n + 2] is formed in the epilogue.  The A rows are permuted so that both
 // halves of an output position sit in the SAME 32-lane TMEM sub-partition (lanes 0-15: T0 rows, lanes 16-31: T1 rows
 // of 16 positions): one thread reads both with two tcgen05.ld.16x256b (second one 2 columns to the right) and adds them.
+//
+// Complex taps (fir_filter_ccc, fir_filter.cc:153-162): two such products per tile, Dr = A(Re h) B and Di = A(Im h) B on
+// the same B operand; the (re, im) columns of an input row are adjacent registers of the epilogue thread, which forms
+// out = (Dr.re - Di.im, Dr.im + Di.re).  A then takes 256 TMEM columns, so a tile is 32 rows (Cfg<true>).
 //
 // Precision: kind::tf32 truncates the low 13 mantissa bits of an fp32 operand (measured: tools/tc_probe.cu), so
 // x_hi is the raw value and x_lo = x - trunc(x) is exact; D = A_hi B_hi + A_lo B_hi + A_hi B_lo leaves an error of
@@ -34,25 +38,35 @@ namespace grb {
 
 namespace tc {
 
-constexpr int ROWS = 64;        // input rows per tile (N = 2*ROWS columns)
-constexpr int OROWS = ROWS - 1; // output rows per tile
-constexpr int NCOL = 2 * ROWS;  // 128
-constexpr int NCONV = 8;        // converter warps
-constexpr int NEPI = 4;         // epilogue warps (one per TMEM sub-partition)
+constexpr int NCONV = 8; // converter warps
+constexpr int NEPI = 4;  // epilogue warps (one per TMEM sub-partition)
 constexpr int W_TMA = NCONV, W_MMA = NCONV + 1, W_EPI = NCONV + 2;
 constexpr int NTHREADS = (NCONV + 2 + NEPI) * 32;
-constexpr int RSTAGES = 3; // raw input ring
-constexpr int BSTAGES = 2; // converted operand ring
-constexpr int DSTAGES = 3; // TMEM accumulator ring
-constexpr int RAW_BYTES = ROWS * 64 * 8;     // 32 KiB
-constexpr int KBLK_BYTES = 128 * 128;        // one 32-float K block of a 128-row operand, SW128
-constexpr int OPER_BYTES = 2 * KBLK_BYTES;   // K = 64 floats: 32 KiB
-constexpr int BSTAGE_BYTES = 2 * OPER_BYTES; // hi + lo
-constexpr int NBARS = 2 * RSTAGES + 2 * BSTAGES + 2 * DSTAGES;
-constexpr int SMEM_BYTES = BSTAGES * BSTAGE_BYTES + RSTAGES * RAW_BYTES + 256 + 1024;
-static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
-constexpr unsigned TMEM_A_HI = DSTAGES * NCOL; // columns 384..447
-constexpr unsigned TMEM_A_LO = TMEM_A_HI + 64; // columns 448..511
+
+// Tile geometry.  ccf: 64 input rows (N = 128), one accumulator of 128 columns per stage, A = [hi | lo] (128 columns).
+// ccc: taps hr + j hi need TWO products per tile, Dr = A(hr) B and Di = A(hi) B (out = (Dr.re - Di.im, Dr.im + Di.re)), and
+// A = [hr_hi | hr_lo | hi_hi | hi_lo] takes 256 of the 512 TMEM columns, so a tile is 32 rows (N = 64): Dr | Di = 128 columns
+// per stage, two stages.
+template <bool CT>
+struct Cfg {
+    static constexpr int ROWS = CT ? 32 : 64;  // input rows per tile
+    static constexpr int OROWS = ROWS - 1;     // output rows per tile (tiles overlap by one row)
+    static constexpr int NCOL = 2 * ROWS;      // MMA N: (row, re|im)
+    static constexpr int RSTAGES = CT ? 4 : 3; // raw input ring
+    static constexpr int BSTAGES = CT ? 3 : 2; // converted operand ring
+    static constexpr int DSTAGES = CT ? 2 : 3; // TMEM accumulator ring
+    static constexpr int RAW_BYTES = ROWS * 64 * 8;
+    static constexpr int KBLK_BYTES = NCOL * 128;        // one 32-float K block of the B tile, 128-byte swizzle
+    static constexpr int OPER_BYTES = 2 * KBLK_BYTES;    // K = 64 floats
+    static constexpr int BSTAGE_BYTES = 2 * OPER_BYTES;  // hi + lo
+    static constexpr int DSTRIDE = 128;                  // TMEM columns per accumulator stage
+    static constexpr unsigned TMEM_A = DSTAGES * DSTRIDE; // ccf 384, ccc 256; 64-column blocks follow
+    static constexpr int CHUNKS = ROWS * 16 / (NCONV * 32); // 32-byte chunks per converter thread and tile
+    static constexpr int NBARS = 2 * RSTAGES + 2 * BSTAGES + 2 * DSTAGES + 1;
+    static constexpr int SMEM_BYTES = BSTAGES * BSTAGE_BYTES + RSTAGES * RAW_BYTES + 256 + 1024;
+    static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+    static_assert(NBARS * 8 + 8 <= 256, "barrier block");
+};
 
 __device__ __forceinline__ unsigned long long desc_sw128(unsigned saddr)
 {
@@ -109,16 +123,21 @@ __device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__
 
 } // namespace tc
 
-template <bool TRACE>
+template <bool CT, bool TRACE>
 __global__ void __launch_bounds__(tc::NTHREADS, 1)
     fir_tc_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int ntaps,
-                  const float* __restrict__ rev, long long ntiles, long long* __restrict__ trace)
+                  const void* __restrict__ rev_, long long ntiles, long long* __restrict__ trace)
 {
     using namespace tc;
+    using C = Cfg<CT>;
+    constexpr int ROWS = C::ROWS, OROWS = C::OROWS, NCOL = C::NCOL;
+    constexpr int RSTAGES = C::RSTAGES, BSTAGES = C::BSTAGES, DSTAGES = C::DSTAGES;
+    constexpr int RAW_BYTES = C::RAW_BYTES, KBLK_BYTES = C::KBLK_BYTES, OPER_BYTES = C::OPER_BYTES,
+                  BSTAGE_BYTES = C::BSTAGE_BYTES;
     extern __shared__ unsigned char smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    unsigned char* sB = smem;                            // BSTAGES x [B_hi | B_lo]
-    unsigned char* sR = smem + BSTAGES * BSTAGE_BYTES;   // RSTAGES raw tiles
+    unsigned char* sB = smem;                          // BSTAGES x [B_hi | B_lo]
+    unsigned char* sR = smem + BSTAGES * BSTAGE_BYTES; // RSTAGES raw tiles
     unsigned long long* bars = (unsigned long long*)(sR + RSTAGES * RAW_BYTES);
     unsigned long long* raw_full = bars;
     unsigned long long* raw_empty = raw_full + RSTAGES;
@@ -126,8 +145,8 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
     unsigned long long* b_empty = b_full + BSTAGES;
     unsigned long long* d_full = b_empty + BSTAGES;
     unsigned long long* d_empty = d_full + DSTAGES;
-    unsigned long long* a_ready = bars + NBARS;
-    unsigned* tmem_ptr = (unsigned*)(bars + NBARS + 1);
+    unsigned long long* a_ready = d_empty + DSTAGES;
+    unsigned* tmem_ptr = (unsigned*)(bars + C::NBARS);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const long long G = gridDim.x;
 
@@ -189,11 +208,11 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
             if (tr) trace[it * 16 + 0] = clock64();
             mbar_wait(&raw_full[rs], ruse & 1);
             if (tr) trace[it * 16 + 1] = clock64();
-            float4 v[4][2];
+            float4 v[C::CHUNKS][2];
             if (e0 + ROWS * 64 <= nin) {
                 const unsigned rb = sR_u32 + rs * RAW_BYTES + 32 * p;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
+                for (int i = 0; i < C::CHUNKS; ++i) {
                     const float4 x = lds128(rb + 8192 * i + 16 * hsel);
                     const float4 y = lds128(rb + 8192 * i + 16 * (1 - hsel));
                     v[i][0] = hsel ? y : x;
@@ -201,7 +220,7 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                 }
             } else {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
+                for (int i = 0; i < C::CHUNKS; ++i) {
                     const long long e = e0 + 4 * (p + 256 * i);
                     float2 z[4];
 #pragma unroll
@@ -215,7 +234,7 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
             if (tr) trace[it * 16 + 2] = clock64();
             const unsigned bh = sB_u32 + stage * BSTAGE_BYTES;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < C::CHUNKS; ++i) {
                 const int c = p + 256 * i;
                 const int n0 = 2 * (c >> 4), q = c & 15;
                 const unsigned base = (unsigned)((q >> 3) * KBLK_BYTES + (n0 >> 3) * 1024 + (n0 & 7) * 128);
@@ -240,9 +259,8 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
             }
             if (tr) trace[it * 16 + 3] = clock64();
         }
-    }
-    else if (warp == W_MMA) {
-        // ================= MMA issuer: one thread, 3 split terms x 8 K steps per tile, A from tensor memory =================
+    } else if (warp == W_MMA) {
+        // ================= MMA issuer: one thread; per product 3 split terms x 8 K steps, A from tensor memory =================
         if (lane == 0) {
             const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(NCOL >> 3) << 17) | ((128u >> 4) << 24);
             mbar_wait(a_ready, 0);
@@ -260,45 +278,61 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                     mbar_wait(&d_empty[acc], (duse - 1) & 1);
                 if (tr) trace[it * 16 + 6] = clock64();
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const unsigned d = tmem + acc * NCOL;
                 const unsigned b_addr = smem_u32(sB + stage * BSTAGE_BYTES);
-                unsigned n = 0;
 #pragma unroll
-                for (int term = 0; term < 3; ++term) { // A_hi B_hi + A_lo B_hi + A_hi B_lo
-                    const unsigned ta = tmem + (term == 1 ? TMEM_A_LO : TMEM_A_HI);
-                    const unsigned bo = b_addr + (term == 2 ? OPER_BYTES : 0);
+                for (int part = 0; part < (CT ? 2 : 1); ++part) { // ccc: Dr = A(hr) B, Di = A(hi) B
+                    const unsigned d = tmem + acc * C::DSTRIDE + part * NCOL;
+                    const unsigned a_hi = tmem + C::TMEM_A + part * 128, a_lo = a_hi + 64;
+                    unsigned n = 0;
 #pragma unroll
-                    for (int kk = 0; kk < 8; ++kk)
-                        mma_tf32_ts(d, ta + 8 * kk, desc_sw128(bo + (kk >> 2) * KBLK_BYTES + (kk & 3) * 32), idesc, n++);
+                    for (int term = 0; term < 3; ++term) { // A_hi B_hi + A_lo B_hi + A_hi B_lo
+                        const unsigned ta = term == 1 ? a_lo : a_hi;
+                        const unsigned bo = b_addr + (term == 2 ? OPER_BYTES : 0);
+#pragma unroll
+                        for (int kk = 0; kk < 8; ++kk)
+                            mma_tf32_ts(d, ta + 8 * kk, desc_sw128(bo + (kk >> 2) * KBLK_BYTES + (kk & 3) * 32), idesc, n++);
+                    }
                 }
                 umma_commit(&b_empty[stage]); // shared-memory stage may be refilled once these MMAs retire
                 umma_commit(&d_full[acc]);    // accumulator ready for the epilogue
                 if (tr) trace[it * 16 + 7] = clock64();
             }
         }
-    } else if (warp >= W_EPI) {
+    }
+    else if (warp >= W_EPI) {
         const int s = warp & 3; // the TMEM sub-partition (lanes 32 s .. 32 s + 31) this warp can access
         // ---- one-time: Toeplitz operand A = [T0; T1] into tensor memory.  Lane l < 16 of sub-partition s holds the T0 row
         //      of output position j = 16 s + l, lane 16 + l the T1 row of the same position (so one thread can add them) ----
         {
             const int j = 16 * s + (lane & 15);
             const bool lowhalf = lane < 16;
-            const unsigned trow = tmem + ((unsigned)(32 * s) << 16);
+            const unsigned trow = tmem + ((unsigned)(32 * s) << 16) + C::TMEM_A;
 #pragma unroll 1
-            for (int k0 = 0; k0 < 64; k0 += 8) {
-                unsigned hi[8], lo[8];
+            for (int part = 0; part < (CT ? 2 : 1); ++part) {
+#pragma unroll 1
+                for (int k0 = 0; k0 < 64; k0 += 8) {
+                    unsigned hi[8], lo[8];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int k = k0 + i;
-                    const int t = lowhalf ? (k - j) : (64 + k - j);
-                    const bool nz = lowhalf ? (k >= j) : (k < j);
-                    const float v = (nz && t < ntaps) ? __ldg(rev + t) : 0.f;
-                    const float h = trunc_tf32(v);
-                    hi[i] = __float_as_uint(h);
-                    lo[i] = __float_as_uint(v - h);
+                    for (int i = 0; i < 8; ++i) {
+                        const int k = k0 + i;
+                        const int t = lowhalf ? (k - j) : (64 + k - j);
+                        const bool nz = (lowhalf ? (k >= j) : (k < j)) && t < ntaps;
+                        float v = 0.f;
+                        if (nz) {
+                            if (CT) {
+                                const float2 h2 = __ldg((const float2*)rev_ + t);
+                                v = part ? h2.y : h2.x;
+                            } else {
+                                v = __ldg((const float*)rev_ + t);
+                            }
+                        }
+                        const float h = trunc_tf32(v);
+                        hi[i] = __float_as_uint(h);
+                        lo[i] = __float_as_uint(v - h);
+                    }
+                    GRB_TMEM_ST_32x32_X8(trow + part * 128 + k0, hi);
+                    GRB_TMEM_ST_32x32_X8(trow + part * 128 + 64 + k0, lo);
                 }
-                GRB_TMEM_ST_32x32_X8(trow + TMEM_A_HI + k0, hi);
-                GRB_TMEM_ST_32x32_X8(trow + TMEM_A_LO + k0, lo);
             }
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -306,7 +340,7 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
             if (lane == 0)
                 mbar_arrive(a_ready);
         }
-        // ================= epilogue: out = D[T0 lanes][n] + D[T1 lanes][n+2] -> global =================
+        // ================= epilogue: D[T0 lanes][n] + D[T1 lanes][n+2] (+ the complex combination) -> global =================
         int it = 0;
 #pragma unroll 1
         for (long long tile = blockIdx.x; tile < ntiles; tile += G, ++it) {
@@ -316,16 +350,21 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
             mbar_wait(&d_full[acc], duse & 1);
             if (tr) trace[it * 16 + 9] = clock64();
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const unsigned t0 = tmem + ((unsigned)(32 * s) << 16) + acc * NCOL;
-            const unsigned t1 = t0 + (16u << 16) + 2;
+            const unsigned t0 = tmem + ((unsigned)(32 * s) << 16) + acc * C::DSTRIDE;
+            const unsigned t1 = t0 + (16u << 16) + 2; // T1 lanes, one input row (2 columns) to the right
             const long long row0 = tile * OROWS;
+            constexpr int NG = NCOL / 32;
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                unsigned a[16], b[16];
+            for (int g = 0; g < NG; ++g) {
+                unsigned a[16], b[16], c[CT ? 16 : 1], d[CT ? 16 : 1];
                 GRB_TMEM_LD_16x256_X4(a, t0 + 32 * g);
-                GRB_TMEM_LD_16x256_X4(b, t1 + 32 * g); // g == 3 reads 2 columns past the stage: discarded (row 63)
+                GRB_TMEM_LD_16x256_X4(b, t1 + 32 * g); // the last group reads 2 columns past the tile: discarded (row OROWS)
+                if (CT) {
+                    GRB_TMEM_LD_16x256_X4(c, t0 + NCOL + 32 * g);
+                    GRB_TMEM_LD_16x256_X4(d, t1 + NCOL + 32 * g);
+                }
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (g == 3) {
+                if (g == NG - 1) {
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     __syncwarp();
                     if (lane == 0)
@@ -338,8 +377,15 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
 #pragma unroll
                     for (int hh = 0; hh < 2; ++hh) {
                         const int j = 16 * s + (lane >> 2) + 8 * hh;
-                        const float re = __uint_as_float(a[4 * i + 2 * hh]) + __uint_as_float(b[4 * i + 2 * hh]);
-                        const float im = __uint_as_float(a[4 * i + 2 * hh + 1]) + __uint_as_float(b[4 * i + 2 * hh + 1]);
+                        const int e = 4 * i + 2 * hh;
+                        float re = __uint_as_float(a[e]) + __uint_as_float(b[e]);
+                        float im = __uint_as_float(a[e + 1]) + __uint_as_float(b[e + 1]);
+                        if (CT) { // (Dr.re - Di.im, Dr.im + Di.re)
+                            const float ire = __uint_as_float(c[e]) + __uint_as_float(d[e]);
+                            const float iim = __uint_as_float(c[e + 1]) + __uint_as_float(d[e + 1]);
+                            re -= iim;
+                            im += ire;
+                        }
                         const long long idx = (row0 + r) * 64 + j;
                         if (r < OROWS && idx < nout)
                             out[idx] = make_float2(re, im);
@@ -355,34 +401,38 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
 }
 
-// Tensor-core path for fir_filter_ccf: decimation 1, ntaps <= 64, `in` 16-byte aligned.  `rev` = reversed taps (device).
+// Tensor-core path for fir_filter_ccf / fir_filter_ccc: decimation 1, ntaps <= 64, `in` 16-byte aligned.
 bool fir_tc_eligible(bool ct, int D, int ntaps, const void* in, long long nout)
 {
-    if (ct || D != 1 || ntaps > 64 || ((uintptr_t)in & 15) != 0)
+    if (D != 1 || ntaps > 64 || ((uintptr_t)in & 15) != 0)
         return false;
     if (const char* e = getenv("GRB200_FIR_TC"))
         return atoi(e) != 0;
-    return nout >= 64 * tc::OROWS; // below one tile the CUDA-core kernel's launch is cheaper
+    if (ct && ntaps < 20) // measured: the CUDA-core ccc kernel is as fast below ~20 taps (137 vs 154 Gsps at 21)
+        return false;
+    return nout >= 64 * 63; // below a tile or two the CUDA-core kernel's launch is cheaper
 }
 
-int fir_tc_launch(int ntaps, const float* rev, const void* in, void* out, long long nout, long long nin, int nsm,
-                  cudaStream_t st)
+template <bool CT>
+static int fir_tc_launch_t(int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
+                           cudaStream_t st)
 {
+    using C = tc::Cfg<CT>;
     static std::atomic<int> configured{0};
     if (!configured.load(std::memory_order_acquire)) {
-        GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
-        GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<CT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<CT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
         configured.store(1, std::memory_order_release);
     }
     const long long rows = (nout + 63) / 64;
-    const long long ntiles = (rows + tc::OROWS - 1) / tc::OROWS;
+    const long long ntiles = (rows + C::OROWS - 1) / C::OROWS;
     const unsigned grid = (unsigned)(ntiles < nsm ? ntiles : nsm);
     if (const char* path = getenv("GRB200_FIR_TC_TRACE")) { // developer aid: per-tile clock64() stamps of CTA 0
         long long* dtrace = nullptr;
         GRB_CUDA(cudaMalloc(&dtrace, 64 * 16 * sizeof(long long)));
         GRB_CUDA(cudaMemsetAsync(dtrace, 0, 64 * 16 * sizeof(long long), st));
-        fir_tc_kernel<true><<<grid, tc::NTHREADS, tc::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps, rev,
-                                                                       ntiles, dtrace);
+        fir_tc_kernel<CT, true><<<grid, tc::NTHREADS, C::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps,
+                                                                          rev, ntiles, dtrace);
         GRB_LAUNCH_CHECK();
         std::vector<long long> h(64 * 16);
         GRB_CUDA(cudaMemcpyAsync(h.data(), dtrace, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
@@ -397,10 +447,17 @@ int fir_tc_launch(int ntaps, const float* rev, const void* in, void* out, long l
         }
         return 0;
     }
-    fir_tc_kernel<false><<<grid, tc::NTHREADS, tc::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps, rev,
-                                                                    ntiles, nullptr);
+    fir_tc_kernel<CT, false><<<grid, tc::NTHREADS, C::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps, rev,
+                                                                       ntiles, nullptr);
     GRB_LAUNCH_CHECK();
     return 0;
+}
+
+int fir_tc_launch(bool ct, int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
+                  cudaStream_t st)
+{
+    return ct ? fir_tc_launch_t<true>(ntaps, rev, in, out, nout, nin, nsm, st)
+              : fir_tc_launch_t<false>(ntaps, rev, in, out, nout, nin, nsm, st);
 }
 
 } // namespace grb

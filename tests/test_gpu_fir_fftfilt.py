@@ -103,23 +103,26 @@ def test_fir_scheduler_sized_chunks_equal_one_call(grb, monkeypatch):
     assert_parity(d, po.f64_fir(1, taps, x), "tensor-core path vs float64")
 
 
+@pytest.mark.parametrize("cplx", [False, True])
 @pytest.mark.parametrize("ntaps,nout", [(64, 64 * 63), (64, 64 * 63 + 1), (64, 64 * 63 * 148 * 2 + 4095), (63, 100001),
                                         (37, 250000), (2, 8191), (1, 70000), (64, 1 << 21)])
-def test_fir_tensor_core_path(grb, orc, monkeypatch, ntaps, nout):
-    """fir_tc_kernel (tcgen05 block-Toeplitz FIR, 3xTF32): ragged last tile, short filters (zero-padded Toeplitz),
-    one tile, several tiles per CTA; against the C oracle and float64, and against the CUDA-core kernel."""
+def test_fir_tensor_core_path(grb, orc, monkeypatch, ntaps, nout, cplx):
+    """fir_tc_kernel (tcgen05 block-Toeplitz FIR, 3xTF32), real and complex taps: ragged last tile, short filters
+    (zero-padded Toeplitz), one tile, several tiles per CTA; against the C oracle and float64, and against the
+    CUDA-core kernel."""
     monkeypatch.setenv("GRB200_FIR_TC", "1")
-    rng = np.random.default_rng(1000 * ntaps + nout % 997)
+    rng = np.random.default_rng(1000 * ntaps + nout % 997 + cplx)
     x = crand(rng, nout)
-    taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
+    taps = crand(rng, ntaps) if cplx else rng.uniform(-1, 1, ntaps).astype(np.float32)
+    cls = grb.filter.fir_filter_ccc if cplx else grb.filter.fir_filter_ccf
     xin = np.concatenate([np.zeros(ntaps - 1, np.complex64), x])
-    got = grb.filter.fir_filter_ccf(1, taps).process(xin, nout)
+    got = cls(1, taps).process(xin, nout)
     assert len(got) == nout and np.isfinite(got.view(np.float32)).all()
     assert_parity(got, po.f64_fir(1, taps, x), "tc f64 %d/%d" % (ntaps, nout))
     n0 = min(nout, 200000)
     assert_parity(got[:n0], orc.fir(1, taps, xin[:n0 + ntaps - 1], n0), "tc oracle")
     monkeypatch.setenv("GRB200_FIR_TC", "0")
-    ref = grb.filter.fir_filter_ccf(1, taps).process(xin, nout)
+    ref = cls(1, taps).process(xin, nout)
     assert_parity(got, ref, "tc vs cuda-core")
 
 
