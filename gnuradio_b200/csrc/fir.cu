@@ -697,8 +697,8 @@ static int launch_tiled_nb(const FirPlan& pl, const void* in, void* out, long lo
                         : launch_tiled<R, CT, 1>(pl, in, out, nout, nin, D, gtaps, nsm, st);
 }
 
-bool fir_tc_eligible(bool ct, int D, int ntaps, const void* in, long long nout);
-int fir_tc_launch(bool ct, int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
+int fir_tc_mode(bool ct, int D, int ntaps, const void* in, long long nout);
+int fir_tc_launch(int mode, int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
                   cudaStream_t st);
 
 // gtaps: phase-major padded taps [D][Upad]; rev: reversed taps [ntaps] (both on the device).
@@ -712,8 +712,9 @@ int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, co
     int dev = 0;
     cudaGetDevice(&dev);
     const int nsm = sm_count(dev);
-    if (fir_tc_eligible(ct, D, ntaps, in, nout)) // tcgen05 block-Toeplitz path (fir_tc.cu)
-        return fir_tc_launch(ct, ntaps, rev, in, out, nout, nin, nsm, st);
+    const int tc_mode = fir_tc_mode(ct, D, ntaps, in, nout); // tcgen05 block-Toeplitz paths (fir_tc.cu)
+    if (tc_mode >= 0)
+        return fir_tc_launch(tc_mode, ntaps, rev, in, out, nout, nin, nsm, st);
     if (pl.tiled) {
         if (ct)
             return launch_tiled_nb<8, true>(pl, in, out, nout, nin, D, gtaps, nsm, st);

@@ -43,27 +43,40 @@ constexpr int NEPI = 4;  // epilogue warps (one per TMEM sub-partition)
 constexpr int W_TMA = NCONV, W_MMA = NCONV + 1, W_EPI = NCONV + 2;
 constexpr int NTHREADS = (NCONV + 2 + NEPI) * 32;
 
-// Tile geometry.  ccf: 64 input rows (N = 128), one accumulator of 128 columns per stage, A = [hi | lo] (128 columns).
-// ccc: taps hr + j hi need TWO products per tile, Dr = A(hr) B and Di = A(hi) B (out = (Dr.re - Di.im, Dr.im + Di.re)), and
-// A = [hr_hi | hr_lo | hi_hi | hi_lo] takes 256 of the 512 TMEM columns, so a tile is 32 rows (N = 64): Dr | Di = 128 columns
-// per stage, two stages.
-template <bool CT>
+// Tile geometry per MODE.
+// M_CCF: 64 input rows (N = 128), one accumulator of 128 columns per stage, A = [hi | lo] (128 TMEM columns).
+// M_CCC: taps hr + j hi need TWO products per tile, Dr = A(hr) B and Di = A(hi) B (out = (Dr.re - Di.im, Dr.im + Di.re)), and
+//        A = [hr_hi | hr_lo | hi_hi | hi_lo] takes 256 of the 512 TMEM columns, so a tile is 32 rows (N = 64): Dr | Di = 128
+//        columns per stage, two stages.
+// M_DEC8: fir_filter_ccf with decimation 8 and up to 1024 taps (BASELINE configs[3]).  A row of 64 inputs yields 8 outputs
+//        j; out[8r + j] = sum_{d=0..16} sum_k h[64 d + k - 8 j] X_{r+d}[k].  The 16 blocks d = 0..15 are STACKED in the 128
+//        lanes of one A operand (lane group (d, j)), so the MMA work per input sample equals the 64-tap case; block 16
+//        (only k < 8 j, taps 968..1023) is a second, narrower MMA (N = 96, B rows 32.. of the same tile) accumulating into
+//        the d = 0 lanes.  The epilogue sums the 16 lane groups with their row shifts: four per thread in registers
+//        (tcgen05.ld column offsets are free), the last four across the epilogue warps through shared memory.
+//        A tile = 64 input rows -> 48 output rows x 8 (tiles overlap by 16 rows).
+enum { M_CCF = 0, M_CCC = 1, M_DEC8 = 2 };
+
+template <int MODE>
 struct Cfg {
-    static constexpr int ROWS = CT ? 32 : 64;  // input rows per tile
-    static constexpr int OROWS = ROWS - 1;     // output rows per tile (tiles overlap by one row)
-    static constexpr int NCOL = 2 * ROWS;      // MMA N: (row, re|im)
-    static constexpr int RSTAGES = CT ? 4 : 3; // raw input ring
-    static constexpr int BSTAGES = CT ? 3 : 2; // converted operand ring
-    static constexpr int DSTAGES = CT ? 2 : 3; // TMEM accumulator ring
+    static constexpr bool CT = MODE == M_CCC;
+    static constexpr int ROWS = CT ? 32 : 64;                  // input rows per tile
+    static constexpr int OROWS = MODE == M_DEC8 ? 48 : ROWS - 1; // rows of the tile that produce output
+    static constexpr int OUT_PER_ROW = MODE == M_DEC8 ? 8 : 64;
+    static constexpr int NCOL = 2 * ROWS;                      // MMA N: (row, re|im)
+    static constexpr int RSTAGES = CT ? 4 : (MODE == M_DEC8 ? 2 : 3); // raw input ring
+    static constexpr int BSTAGES = CT ? 3 : 2;                 // converted operand ring
+    static constexpr int DSTAGES = MODE == M_CCF ? 3 : 2;      // TMEM accumulator ring
     static constexpr int RAW_BYTES = ROWS * 64 * 8;
     static constexpr int KBLK_BYTES = NCOL * 128;        // one 32-float K block of the B tile, 128-byte swizzle
     static constexpr int OPER_BYTES = 2 * KBLK_BYTES;    // K = 64 floats
     static constexpr int BSTAGE_BYTES = 2 * OPER_BYTES;  // hi + lo
     static constexpr int DSTRIDE = 128;                  // TMEM columns per accumulator stage
-    static constexpr unsigned TMEM_A = DSTAGES * DSTRIDE; // ccf 384, ccc 256; 64-column blocks follow
+    static constexpr unsigned TMEM_A = DSTAGES * DSTRIDE; // ccf 384, ccc/dec8 256; 64-column blocks follow
     static constexpr int CHUNKS = ROWS * 16 / (NCONV * 32); // 32-byte chunks per converter thread and tile
     static constexpr int NBARS = 2 * RSTAGES + 2 * BSTAGES + 2 * DSTAGES + 1;
-    static constexpr int SMEM_BYTES = BSTAGES * BSTAGE_BYTES + RSTAGES * RAW_BYTES + 256 + 1024;
+    static constexpr int RED_BYTES = MODE == M_DEC8 ? 2 * 4 * 384 * 8 : 0; // 2 buffers x 4 partial sums x 384 outputs
+    static constexpr int SMEM_BYTES = BSTAGES * BSTAGE_BYTES + RSTAGES * RAW_BYTES + RED_BYTES + 256 + 1024;
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
     static_assert(NBARS * 8 + 8 <= 256, "barrier block");
 };
@@ -116,6 +129,10 @@ __device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),        \
                    "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])   \
                  : "r"(taddr))
+#define GRB_TMEM_LD_16x256_X1(r, taddr)                                                                                   \
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0,%1,%2,%3}, [%4];"                                            \
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])                                                         \
+                 : "r"(taddr))
 #define GRB_TMEM_ST_32x32_X8(taddr, r)                                                                                    \
     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(r[0]), "r"(r[1]), \
                  "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])                                         \
@@ -123,13 +140,14 @@ __device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__
 
 } // namespace tc
 
-template <bool CT, bool TRACE>
+template <int MODE, bool TRACE>
 __global__ void __launch_bounds__(tc::NTHREADS, 1)
     fir_tc_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int ntaps,
                   const void* __restrict__ rev_, long long ntiles, long long* __restrict__ trace)
 {
     using namespace tc;
-    using C = Cfg<CT>;
+    using C = Cfg<MODE>;
+    constexpr bool CT = C::CT;
     constexpr int ROWS = C::ROWS, OROWS = C::OROWS, NCOL = C::NCOL;
     constexpr int RSTAGES = C::RSTAGES, BSTAGES = C::BSTAGES, DSTAGES = C::DSTAGES;
     constexpr int RAW_BYTES = C::RAW_BYTES, KBLK_BYTES = C::KBLK_BYTES, OPER_BYTES = C::OPER_BYTES,
@@ -138,7 +156,8 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     unsigned char* sB = smem;                          // BSTAGES x [B_hi | B_lo]
     unsigned char* sR = smem + BSTAGES * BSTAGE_BYTES; // RSTAGES raw tiles
-    unsigned long long* bars = (unsigned long long*)(sR + RSTAGES * RAW_BYTES);
+    float2* sRed = (float2*)(sR + RSTAGES * RAW_BYTES); // M_DEC8: cross-warp partial sums
+    unsigned long long* bars = (unsigned long long*)(sR + RSTAGES * RAW_BYTES + C::RED_BYTES);
     unsigned long long* raw_full = bars;
     unsigned long long* raw_empty = raw_full + RSTAGES;
     unsigned long long* b_full = raw_empty + RSTAGES;
@@ -293,6 +312,19 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                             mma_tf32_ts(d, ta + 8 * kk, desc_sw128(bo + (kk >> 2) * KBLK_BYTES + (kk & 3) * 32), idesc, n++);
                     }
                 }
+                if (MODE == M_DEC8 && ntaps > 968) { // block 16 (taps 968..1023): B rows 32.. (input rows 16..), N = 96, k < 56
+                    const unsigned idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((96u >> 3) << 17) | ((128u >> 4) << 24);
+                    const unsigned d = tmem + acc * C::DSTRIDE;
+                    const unsigned a_hi = tmem + C::TMEM_A + 128, a_lo = a_hi + 64;
+#pragma unroll
+                    for (int term = 0; term < 3; ++term) {
+                        const unsigned ta = term == 1 ? a_lo : a_hi;
+                        const unsigned bo = b_addr + (term == 2 ? OPER_BYTES : 0) + 4 * 1024;
+#pragma unroll
+                        for (int kk = 0; kk < 7; ++kk)
+                            mma_tf32_ts(d, ta + 8 * kk, desc_sw128(bo + (kk >> 2) * KBLK_BYTES + (kk & 3) * 32), idesc2, 1);
+                    }
+                }
                 umma_commit(&b_empty[stage]); // shared-memory stage may be refilled once these MMAs retire
                 umma_commit(&d_full[acc]);    // accumulator ready for the epilogue
                 if (tr) trace[it * 16 + 7] = clock64();
@@ -304,21 +336,27 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
         // ---- one-time: Toeplitz operand A = [T0; T1] into tensor memory.  Lane l < 16 of sub-partition s holds the T0 row
         //      of output position j = 16 s + l, lane 16 + l the T1 row of the same position (so one thread can add them) ----
         {
-            const int j = 16 * s + (lane & 15);
-            const bool lowhalf = lane < 16;
             const unsigned trow = tmem + ((unsigned)(32 * s) << 16) + C::TMEM_A;
 #pragma unroll 1
-            for (int part = 0; part < (CT ? 2 : 1); ++part) {
+            for (int part = 0; part < (MODE == M_CCF ? 1 : 2); ++part) {
 #pragma unroll 1
                 for (int k0 = 0; k0 < 64; k0 += 8) {
                     unsigned hi[8], lo[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         const int k = k0 + i;
-                        const int t = lowhalf ? (k - j) : (64 + k - j);
-                        const bool nz = (lowhalf ? (k >= j) : (k < j)) && t < ntaps;
+                        int t; // tap index this (lane, k) element multiplies, < 0: structural zero
+                        if (MODE == M_DEC8) {
+                            // lane = j + 8 m holds block d = s + 4 m (part 0); block 16 sits in lanes 0..7 of sub-partition 0
+                            const int j = lane & 7, m = lane >> 3;
+                            const int d = part ? ((s == 0 && m == 0) ? 16 : -1) : s + 4 * m;
+                            t = d < 0 ? -1 : 64 * d + k - 8 * j;
+                        } else {
+                            const int j = 16 * s + (lane & 15);
+                            t = lane < 16 ? (k >= j ? k - j : -1) : (k < j ? 64 + k - j : -1);
+                        }
                         float v = 0.f;
-                        if (nz) {
+                        if (t >= 0 && t < ntaps) {
                             if (CT) {
                                 const float2 h2 = __ldg((const float2*)rev_ + t);
                                 v = part ? h2.y : h2.x;
@@ -350,45 +388,90 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
             mbar_wait(&d_full[acc], duse & 1);
             if (tr) trace[it * 16 + 9] = clock64();
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const unsigned t0 = tmem + ((unsigned)(32 * s) << 16) + acc * C::DSTRIDE;
-            const unsigned t1 = t0 + (16u << 16) + 2; // T1 lanes, one input row (2 columns) to the right
-            const long long row0 = tile * OROWS;
-            constexpr int NG = NCOL / 32;
+            if constexpr (MODE == M_DEC8) {
+                // thread (sub-partition s, lane): output phase j = lane / 4; lanes j + 8 m of sub-partition s hold blocks
+                // d = s + 4 m.  One .16x256b load returns lanes (j, j + 8): blocks d and d + 4, whose 4-row shift is the
+                // next x1 repeat (8 columns), so register index i + 1; the second load (lane base 16) holds d + 8, d + 12.
+                const unsigned tA = tmem + ((unsigned)(32 * s) << 16) + acc * C::DSTRIDE + 2 * s;
+                const unsigned tB = tA + (16u << 16) + 16;
+                float2* red = sRed + (it & 1) * (4 * 384) + s * 384;
+                const int j = lane >> 2, q = lane & 3;
 #pragma unroll
-            for (int g = 0; g < NG; ++g) {
-                unsigned a[16], b[16], c[CT ? 16 : 1], d[CT ? 16 : 1];
-                GRB_TMEM_LD_16x256_X4(a, t0 + 32 * g);
-                GRB_TMEM_LD_16x256_X4(b, t1 + 32 * g); // the last group reads 2 columns past the tile: discarded (row OROWS)
-                if (CT) {
-                    GRB_TMEM_LD_16x256_X4(c, t0 + NCOL + 32 * g);
-                    GRB_TMEM_LD_16x256_X4(d, t1 + NCOL + 32 * g);
+                for (int g = 0; g < 3; ++g) {
+                    unsigned a[20], b[20];
+                    GRB_TMEM_LD_16x256_X4(a, tA + 32 * g);
+                    GRB_TMEM_LD_16x256_X1((a + 16), tA + 32 * g + 32);
+                    GRB_TMEM_LD_16x256_X4(b, tB + 32 * g);
+                    GRB_TMEM_LD_16x256_X1((b + 16), tB + 32 * g + 32);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (g == 2) {
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        __syncwarp();
+                        if (lane == 0)
+                            mbar_arrive(&d_empty[acc]);
+                        if (tr) trace[it * 16 + 10] = clock64();
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float re = __uint_as_float(a[4 * i]) + __uint_as_float(a[4 * i + 6]) + __uint_as_float(b[4 * i]) +
+                                         __uint_as_float(b[4 * i + 6]);
+                        const float im = __uint_as_float(a[4 * i + 1]) + __uint_as_float(a[4 * i + 7]) +
+                                         __uint_as_float(b[4 * i + 1]) + __uint_as_float(b[4 * i + 7]);
+                        red[(16 * g + 4 * i + q) * 8 + j] = make_float2(re, im);
+                    }
                 }
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (g == NG - 1) {
-                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                    __syncwarp();
-                    if (lane == 0)
-                        mbar_arrive(&d_empty[acc]);
-                    if (tr) trace[it * 16 + 10] = clock64();
+                asm volatile("bar.sync 1, 128;" ::: "memory"); // the four epilogue warps: partial sums of this tile are in place
+                const float2* r4 = sRed + (it & 1) * (4 * 384);
+                const int e = (warp - W_EPI) * 32 + lane;
+#pragma unroll
+                for (int u = 0; u < 3; ++u) {
+                    const int o = e + 128 * u;
+                    const float2 p0 = r4[o], p1 = r4[384 + o], p2 = r4[768 + o], p3 = r4[1152 + o];
+                    const long long idx = tile * 384 + o;
+                    if (idx < nout)
+                        out[idx] = make_float2((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y));
                 }
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int r = 16 * g + 4 * i + (lane & 3);
-#pragma unroll
-                    for (int hh = 0; hh < 2; ++hh) {
-                        const int j = 16 * s + (lane >> 2) + 8 * hh;
-                        const int e = 4 * i + 2 * hh;
-                        float re = __uint_as_float(a[e]) + __uint_as_float(b[e]);
-                        float im = __uint_as_float(a[e + 1]) + __uint_as_float(b[e + 1]);
-                        if (CT) { // (Dr.re - Di.im, Dr.im + Di.re)
-                            const float ire = __uint_as_float(c[e]) + __uint_as_float(d[e]);
-                            const float iim = __uint_as_float(c[e + 1]) + __uint_as_float(d[e + 1]);
-                            re -= iim;
-                            im += ire;
+            } else {
+                const unsigned t0 = tmem + ((unsigned)(32 * s) << 16) + acc * C::DSTRIDE;
+                const unsigned t1 = t0 + (16u << 16) + 2; // T1 lanes, one input row (2 columns) to the right
+                const long long row0 = tile * OROWS;
+                constexpr int NG = NCOL / 32;
+    #pragma unroll
+                for (int g = 0; g < NG; ++g) {
+                    unsigned a[16], b[16], c[CT ? 16 : 1], d[CT ? 16 : 1];
+                    GRB_TMEM_LD_16x256_X4(a, t0 + 32 * g);
+                    GRB_TMEM_LD_16x256_X4(b, t1 + 32 * g); // the last group reads 2 columns past the tile: discarded (row OROWS)
+                    if (CT) {
+                        GRB_TMEM_LD_16x256_X4(c, t0 + NCOL + 32 * g);
+                        GRB_TMEM_LD_16x256_X4(d, t1 + NCOL + 32 * g);
+                    }
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (g == NG - 1) {
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        __syncwarp();
+                        if (lane == 0)
+                            mbar_arrive(&d_empty[acc]);
+                        if (tr) trace[it * 16 + 10] = clock64();
+                    }
+    #pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int r = 16 * g + 4 * i + (lane & 3);
+    #pragma unroll
+                        for (int hh = 0; hh < 2; ++hh) {
+                            const int j = 16 * s + (lane >> 2) + 8 * hh;
+                            const int e = 4 * i + 2 * hh;
+                            float re = __uint_as_float(a[e]) + __uint_as_float(b[e]);
+                            float im = __uint_as_float(a[e + 1]) + __uint_as_float(b[e + 1]);
+                            if (CT) { // (Dr.re - Di.im, Dr.im + Di.re)
+                                const float ire = __uint_as_float(c[e]) + __uint_as_float(d[e]);
+                                const float iim = __uint_as_float(c[e + 1]) + __uint_as_float(d[e + 1]);
+                                re -= iim;
+                                im += ire;
+                            }
+                            const long long idx = (row0 + r) * 64 + j;
+                            if (r < OROWS && idx < nout)
+                                out[idx] = make_float2(re, im);
                         }
-                        const long long idx = (row0 + r) * 64 + j;
-                        if (r < OROWS && idx < nout)
-                            out[idx] = make_float2(re, im);
                     }
                 }
             }
@@ -401,38 +484,46 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
 }
 
-// Tensor-core path for fir_filter_ccf / fir_filter_ccc: decimation 1, ntaps <= 64, `in` 16-byte aligned.
-bool fir_tc_eligible(bool ct, int D, int ntaps, const void* in, long long nout)
+// Which tensor-core mode serves this call, or -1 (CUDA-core kernels).  `in` must be 16-byte aligned (TMA bulk copies).
+//   M_CCF / M_CCC: decimation 1, ntaps <= 64.   M_DEC8: real taps, decimation 8, ntaps <= 1024.
+int fir_tc_mode(bool ct, int D, int ntaps, const void* in, long long nout)
 {
-    if (D != 1 || ntaps > 64 || ((uintptr_t)in & 15) != 0)
-        return false;
+    int mode = -1;
+    if (D == 1 && ntaps <= 64)
+        mode = ct ? tc::M_CCC : tc::M_CCF;
+    else if (D == 8 && !ct && ntaps <= 1024)
+        mode = tc::M_DEC8;
+    if (mode < 0 || ((uintptr_t)in & 15) != 0)
+        return -1;
     if (const char* e = getenv("GRB200_FIR_TC"))
-        return atoi(e) != 0;
-    if (ct && ntaps < 20) // measured: the CUDA-core ccc kernel is as fast below ~20 taps (137 vs 154 Gsps at 21)
-        return false;
-    return nout >= 64 * 63; // below a tile or two the CUDA-core kernel's launch is cheaper
+        return atoi(e) != 0 ? mode : -1;
+    if (mode == tc::M_CCC && ntaps < 20) // measured: the CUDA-core ccc kernel is as fast below ~20 taps (137 vs 154 Gsps at 21)
+        return -1;
+    if (mode == tc::M_DEC8 && ntaps < 256) // short decimators are already HBM-bound on the CUDA cores
+        return -1;
+    return nout >= 64 * 63 ? mode : -1; // below a tile or two the CUDA-core kernel's launch is cheaper
 }
 
-template <bool CT>
+template <int MODE>
 static int fir_tc_launch_t(int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
                            cudaStream_t st)
 {
-    using C = tc::Cfg<CT>;
+    using C = tc::Cfg<MODE>;
     static std::atomic<int> configured{0};
     if (!configured.load(std::memory_order_acquire)) {
-        GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<CT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-        GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<CT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
         configured.store(1, std::memory_order_release);
     }
-    const long long rows = (nout + 63) / 64;
-    const long long ntiles = (rows + C::OROWS - 1) / C::OROWS;
+    const long long orows = (nout + C::OUT_PER_ROW - 1) / C::OUT_PER_ROW;
+    const long long ntiles = (orows + C::OROWS - 1) / C::OROWS;
     const unsigned grid = (unsigned)(ntiles < nsm ? ntiles : nsm);
     if (const char* path = getenv("GRB200_FIR_TC_TRACE")) { // developer aid: per-tile clock64() stamps of CTA 0
         long long* dtrace = nullptr;
         GRB_CUDA(cudaMalloc(&dtrace, 64 * 16 * sizeof(long long)));
         GRB_CUDA(cudaMemsetAsync(dtrace, 0, 64 * 16 * sizeof(long long), st));
-        fir_tc_kernel<CT, true><<<grid, tc::NTHREADS, C::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps,
-                                                                          rev, ntiles, dtrace);
+        fir_tc_kernel<MODE, true><<<grid, tc::NTHREADS, C::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps,
+                                                                            rev, ntiles, dtrace);
         GRB_LAUNCH_CHECK();
         std::vector<long long> h(64 * 16);
         GRB_CUDA(cudaMemcpyAsync(h.data(), dtrace, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
@@ -447,17 +538,24 @@ static int fir_tc_launch_t(int ntaps, const void* rev, const void* in, void* out
         }
         return 0;
     }
-    fir_tc_kernel<CT, false><<<grid, tc::NTHREADS, C::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps, rev,
-                                                                       ntiles, nullptr);
+    fir_tc_kernel<MODE, false><<<grid, tc::NTHREADS, C::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps,
+                                                                         rev, ntiles, nullptr);
     GRB_LAUNCH_CHECK();
     return 0;
 }
 
-int fir_tc_launch(bool ct, int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
+int fir_tc_launch(int mode, int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
                   cudaStream_t st)
 {
-    return ct ? fir_tc_launch_t<true>(ntaps, rev, in, out, nout, nin, nsm, st)
-              : fir_tc_launch_t<false>(ntaps, rev, in, out, nout, nin, nsm, st);
+    switch (mode) {
+    case tc::M_CCF:
+        return fir_tc_launch_t<tc::M_CCF>(ntaps, rev, in, out, nout, nin, nsm, st);
+    case tc::M_CCC:
+        return fir_tc_launch_t<tc::M_CCC>(ntaps, rev, in, out, nout, nin, nsm, st);
+    case tc::M_DEC8:
+        return fir_tc_launch_t<tc::M_DEC8>(ntaps, rev, in, out, nout, nin, nsm, st);
+    }
+    return fail(GRB200_ERANGE, "fir: no tensor-core mode %d", mode);
 }
 
 } // namespace grb
