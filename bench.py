@@ -207,7 +207,7 @@ class FirLongDecim(FirCcf):
     """configs[3]: fir_filter_ccf 1024 taps, decim 8 (2^27 input samples per GPU)."""
     name = "fir_filter_ccf 1024 taps decim 8, 2^%d input samples per GPU x %d set(s) (BASELINE configs[3])"
     alg_bytes, flops, log2n, seed = 9.0, 512.0, 27, 4
-    kernel = "fir_splitk_kernel"
+    kernel = "fir_tc_kernel<M_DEC8>"
     ntaps, decim, nsets = 1024, 8, 1
 
     def setup(self):
