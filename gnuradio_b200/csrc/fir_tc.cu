@@ -51,8 +51,9 @@ constexpr int NTHREADS = (NCONV + 2 + NEPI) * 32;
 // M_DEC8: fir_filter_ccf with decimation 8 and up to 1024 taps (BASELINE configs[3]).  A row of 64 inputs yields 8 outputs
 //        j; out[8r + j] = sum_{d=0..16} sum_k h[64 d + k - 8 j] X_{r+d}[k].  The 16 blocks d = 0..15 are STACKED in the 128
 //        lanes of one A operand (lane group (d, j)), so the MMA work per input sample equals the 64-tap case; block 16
-//        (only k < 8 j, taps 968..1023) is a second, narrower MMA (N = 96, B rows 32.. of the same tile) accumulating into
-//        the d = 0 lanes.  The epilogue sums the 16 lane groups with their row shifts: four per thread in registers
+//        (only k < 8 j, taps 968..1023: 28 multiply-adds per output) does not fit the 128 lanes and is evaluated on the CUDA
+//        cores by the converter warps straight from the raw tile, after they have handed the B tile to the MMA warp (a second
+//        MMA for it cost 44 %, two dedicated warps were too slow).  The epilogue sums the 16 lane groups with their row shifts: four per thread in registers
 //        (tcgen05.ld column offsets are free), the last four across the epilogue warps through shared memory.
 //        A tile = 64 input rows -> 48 output rows x 8 (tiles overlap by 16 rows).
 enum { M_CCF = 0, M_CCC = 1, M_DEC8 = 2 };
@@ -66,7 +67,7 @@ struct Cfg {
     static constexpr int NCOL = 2 * ROWS;                      // MMA N: (row, re|im)
     static constexpr int RSTAGES = CT ? 4 : (MODE == M_DEC8 ? 2 : 3); // raw input ring
     static constexpr int BSTAGES = CT ? 3 : 2;                 // converted operand ring
-    static constexpr int DSTAGES = MODE == M_CCF ? 3 : 2;      // TMEM accumulator ring
+    static constexpr int DSTAGES = CT ? 2 : 3;                 // TMEM accumulator ring
     static constexpr int RAW_BYTES = ROWS * 64 * 8;
     static constexpr int KBLK_BYTES = NCOL * 128;        // one 32-float K block of the B tile, 128-byte swizzle
     static constexpr int OPER_BYTES = 2 * KBLK_BYTES;    // K = 64 floats
@@ -74,9 +75,13 @@ struct Cfg {
     static constexpr int DSTRIDE = 128;                  // TMEM columns per accumulator stage
     static constexpr unsigned TMEM_A = DSTAGES * DSTRIDE; // ccf 384, ccc/dec8 256; 64-column blocks follow
     static constexpr int CHUNKS = ROWS * 16 / (NCONV * 32); // 32-byte chunks per converter thread and tile
-    static constexpr int NBARS = 2 * RSTAGES + 2 * BSTAGES + 2 * DSTAGES + 1;
-    static constexpr int RED_BYTES = MODE == M_DEC8 ? 2 * 4 * 384 * 8 : 0; // 2 buffers x 4 partial sums x 384 outputs
-    static constexpr int SMEM_BYTES = BSTAGES * BSTAGE_BYTES + RSTAGES * RAW_BYTES + RED_BYTES + 256 + 1024;
+    static constexpr int TSTAGES = 4;                    // M_DEC8: ring of 17th-block results (tail warps -> epilogue)
+    static constexpr int NBARS = 2 * RSTAGES + 2 * BSTAGES + 2 * DSTAGES + 1 + (MODE == M_DEC8 ? 2 * TSTAGES : 0);
+    static constexpr int RED_BYTES = MODE == M_DEC8 ? 4 * 384 * 8 : 0;            // 4 partial sums x 384 outputs
+    static constexpr int TAIL_BYTES = MODE == M_DEC8 ? TSTAGES * 384 * 8 : 0;     // 17th-block sums per tile
+    static constexpr int COEF_BYTES = MODE == M_DEC8 ? 8 * 56 * 4 : 0;            // 17th-block taps [j][k]
+    static constexpr int SMEM_BYTES =
+        BSTAGES * BSTAGE_BYTES + RSTAGES * RAW_BYTES + RED_BYTES + TAIL_BYTES + COEF_BYTES + 256 + 1024;
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
     static_assert(NBARS * 8 + 8 <= 256, "barrier block");
 };
@@ -156,8 +161,10 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     unsigned char* sB = smem;                          // BSTAGES x [B_hi | B_lo]
     unsigned char* sR = smem + BSTAGES * BSTAGE_BYTES; // RSTAGES raw tiles
-    float2* sRed = (float2*)(sR + RSTAGES * RAW_BYTES); // M_DEC8: cross-warp partial sums
-    unsigned long long* bars = (unsigned long long*)(sR + RSTAGES * RAW_BYTES + C::RED_BYTES);
+    float2* sRed = (float2*)(sR + RSTAGES * RAW_BYTES);                       // M_DEC8: cross-warp partial sums
+    float2* sTail = (float2*)(sR + RSTAGES * RAW_BYTES + C::RED_BYTES);        // M_DEC8: 17th-block sums, TSTAGES x 384
+    unsigned char* sCoef = sR + RSTAGES * RAW_BYTES + C::RED_BYTES + C::TAIL_BYTES;
+    unsigned long long* bars = (unsigned long long*)(sCoef + C::COEF_BYTES);
     unsigned long long* raw_full = bars;
     unsigned long long* raw_empty = raw_full + RSTAGES;
     unsigned long long* b_full = raw_empty + RSTAGES;
@@ -165,6 +172,9 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
     unsigned long long* d_full = b_empty + BSTAGES;
     unsigned long long* d_empty = d_full + DSTAGES;
     unsigned long long* a_ready = d_empty + DSTAGES;
+    unsigned long long* t_full = a_ready + 1;          // M_DEC8
+    unsigned long long* t_empty = t_full + C::TSTAGES; // M_DEC8
+    const bool have_tail = MODE == M_DEC8 && ntaps > 968;
     unsigned* tmem_ptr = (unsigned*)(bars + C::NBARS);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const long long G = gridDim.x;
@@ -187,6 +197,11 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
             mbar_init_nofence(&d_empty[i], NEPI);
         }
         mbar_init_nofence(a_ready, NEPI);
+        if (MODE == M_DEC8)
+            for (int i = 0; i < C::TSTAGES; ++i) {
+                mbar_init_nofence(&t_full[i], NCONV);
+                mbar_init_nofence(&t_empty[i], NEPI);
+            }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -217,6 +232,14 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
         const int p = tid;
         const unsigned sB_u32 = smem_u32(sB), sR_u32 = smem_u32(sR);
         const int hsel = (lane >> 2) & 1; // which 16-byte half of its 32-byte chunk a lane reads first (bank-conflict free)
+        if (have_tail) { // taps of the partial 17th block: coef[j][k] = h[1024 + k - 8 j] for k < 8 j
+            float* coef = (float*)sCoef;
+            for (int idx = p; idx < 8 * 56; idx += NCONV * 32) {
+                const int j = idx / 56, k = idx % 56, t = 1024 + k - 8 * j;
+                coef[idx] = (k < 8 * j && t < ntaps) ? __ldg((const float*)rev_ + t) : 0.f;
+            }
+            asm volatile("bar.sync 2, 256;" ::: "memory");
+        }
         int it = 0;
 #pragma unroll 1
         for (long long tile = blockIdx.x; tile < ntiles; tile += G, ++it) {
@@ -276,6 +299,44 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                 mbar_arrive(&b_full[stage]);
                 mbar_arrive(&raw_empty[rs]); // the stores above depend on every raw read of this warp
             }
+            if (have_tail) {
+                // 17th tap block on the CUDA cores: out[8 r + j] += sum_{k < 8 j} h[1024 + k - 8 j] X_{r+16}[k], X read back from
+                // the B_hi tile just written (rows 2 (r + 16) and + 1: re and im, zero-filled past the end of the input).
+                // thread = (output row r = p / 4, phase pair (jq + 1, 7 - jq)): 64 / 64 / 64 / 32 multiply-adds, balanced
+                asm volatile("bar.sync 2, 256;" ::: "memory"); // every converter warp has written its part of the tile
+                const int ts = it % C::TSTAGES, tuse = it / C::TSTAGES;
+                const int r = p >> 2, jq = p & 3, jA = jq + 1, jB = 7 - jq;
+                float2 accA = make_float2(0.f, 0.f), accB = accA;
+                if (r < OROWS) {
+                    const int n = 2 * (r + 16);
+                    const unsigned rowre = bh + (n >> 3) * 1024 + (n & 7) * 128, rowim = rowre + 128;
+                    const unsigned cA = smem_u32(sCoef) + jA * 56 * 4, cB = smem_u32(sCoef) + jB * 56 * 4;
+#pragma unroll
+                    for (int ch = 0; ch < 14; ++ch) { // k = 4 ch .. 4 ch + 3 < 56
+                        const unsigned ko = (ch >> 3) * KBLK_BYTES;
+                        const float4 xr = lds128(rowre + ko + (((ch & 7) ^ (n & 7)) << 4));
+                        const float4 xi = lds128(rowim + ko + (((ch & 7) ^ ((n & 7) + 1)) << 4));
+                        const float4 a = lds128(cA + 16 * ch), b = lds128(cB + 16 * ch);
+                        accA.x = fmaf(a.x, xr.x, accA.x), accA.y = fmaf(a.x, xi.x, accA.y);
+                        accA.x = fmaf(a.y, xr.y, accA.x), accA.y = fmaf(a.y, xi.y, accA.y);
+                        accA.x = fmaf(a.z, xr.z, accA.x), accA.y = fmaf(a.z, xi.z, accA.y);
+                        accA.x = fmaf(a.w, xr.w, accA.x), accA.y = fmaf(a.w, xi.w, accA.y);
+                        accB.x = fmaf(b.x, xr.x, accB.x), accB.y = fmaf(b.x, xi.x, accB.y);
+                        accB.x = fmaf(b.y, xr.y, accB.x), accB.y = fmaf(b.y, xi.y, accB.y);
+                        accB.x = fmaf(b.z, xr.z, accB.x), accB.y = fmaf(b.z, xi.z, accB.y);
+                        accB.x = fmaf(b.w, xr.w, accB.x), accB.y = fmaf(b.w, xi.w, accB.y);
+                    }
+                }
+                if (tuse > 0)
+                    mbar_wait(&t_empty[ts], (tuse - 1) & 1);
+                if (r < OROWS) {
+                    sTail[ts * 384 + r * 8 + jA] = accA;
+                    sTail[ts * 384 + r * 8 + jB] = accB;
+                }
+                asm volatile("bar.sync 2, 256;" ::: "memory"); // all tail reads of this B stage are done before anyone refills it
+                if (lane == 0)
+                    mbar_arrive(&t_full[ts]);
+            }
             if (tr) trace[it * 16 + 3] = clock64();
         }
     } else if (warp == W_MMA) {
@@ -312,19 +373,6 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                             mma_tf32_ts(d, ta + 8 * kk, desc_sw128(bo + (kk >> 2) * KBLK_BYTES + (kk & 3) * 32), idesc, n++);
                     }
                 }
-                if (MODE == M_DEC8 && ntaps > 968) { // block 16 (taps 968..1023): B rows 32.. (input rows 16..), N = 96, k < 56
-                    const unsigned idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((96u >> 3) << 17) | ((128u >> 4) << 24);
-                    const unsigned d = tmem + acc * C::DSTRIDE;
-                    const unsigned a_hi = tmem + C::TMEM_A + 128, a_lo = a_hi + 64;
-#pragma unroll
-                    for (int term = 0; term < 3; ++term) {
-                        const unsigned ta = term == 1 ? a_lo : a_hi;
-                        const unsigned bo = b_addr + (term == 2 ? OPER_BYTES : 0) + 4 * 1024;
-#pragma unroll
-                        for (int kk = 0; kk < 7; ++kk)
-                            mma_tf32_ts(d, ta + 8 * kk, desc_sw128(bo + (kk >> 2) * KBLK_BYTES + (kk & 3) * 32), idesc2, 1);
-                    }
-                }
                 umma_commit(&b_empty[stage]); // shared-memory stage may be refilled once these MMAs retire
                 umma_commit(&d_full[acc]);    // accumulator ready for the epilogue
                 if (tr) trace[it * 16 + 7] = clock64();
@@ -338,7 +386,7 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
         {
             const unsigned trow = tmem + ((unsigned)(32 * s) << 16) + C::TMEM_A;
 #pragma unroll 1
-            for (int part = 0; part < (MODE == M_CCF ? 1 : 2); ++part) {
+            for (int part = 0; part < (CT ? 2 : 1); ++part) {
 #pragma unroll 1
                 for (int k0 = 0; k0 < 64; k0 += 8) {
                     unsigned hi[8], lo[8];
@@ -347,10 +395,9 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                         const int k = k0 + i;
                         int t; // tap index this (lane, k) element multiplies, < 0: structural zero
                         if (MODE == M_DEC8) {
-                            // lane = j + 8 m holds block d = s + 4 m (part 0); block 16 sits in lanes 0..7 of sub-partition 0
+                            // lane = j + 8 m holds block d = s + 4 m
                             const int j = lane & 7, m = lane >> 3;
-                            const int d = part ? ((s == 0 && m == 0) ? 16 : -1) : s + 4 * m;
-                            t = d < 0 ? -1 : 64 * d + k - 8 * j;
+                            t = 64 * (s + 4 * m) + k - 8 * j;
                         } else {
                             const int j = 16 * s + (lane & 15);
                             t = lane < 16 ? (k >= j ? k - j : -1) : (k < j ? 64 + k - j : -1);
@@ -394,7 +441,7 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                 // next x1 repeat (8 columns), so register index i + 1; the second load (lane base 16) holds d + 8, d + 12.
                 const unsigned tA = tmem + ((unsigned)(32 * s) << 16) + acc * C::DSTRIDE + 2 * s;
                 const unsigned tB = tA + (16u << 16) + 16;
-                float2* red = sRed + (it & 1) * (4 * 384) + s * 384;
+                float2* red = sRed + s * 384;
                 const int j = lane >> 2, q = lane & 3;
 #pragma unroll
                 for (int g = 0; g < 3; ++g) {
@@ -420,17 +467,28 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                         red[(16 * g + 4 * i + q) * 8 + j] = make_float2(re, im);
                     }
                 }
+                const int ts = it % C::TSTAGES, tuse = it / C::TSTAGES;
+                if (have_tail)
+                    mbar_wait(&t_full[ts], tuse & 1);
                 asm volatile("bar.sync 1, 128;" ::: "memory"); // the four epilogue warps: partial sums of this tile are in place
-                const float2* r4 = sRed + (it & 1) * (4 * 384);
                 const int e = (warp - W_EPI) * 32 + lane;
 #pragma unroll
                 for (int u = 0; u < 3; ++u) {
                     const int o = e + 128 * u;
-                    const float2 p0 = r4[o], p1 = r4[384 + o], p2 = r4[768 + o], p3 = r4[1152 + o];
+                    const float2 p0 = sRed[o], p1 = sRed[384 + o], p2 = sRed[768 + o], p3 = sRed[1152 + o];
+                    float2 y = make_float2((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y));
+                    if (have_tail && (o & 7) != 0) { // phase 0 has no 17th-block term
+                        const float2 tl = sTail[ts * 384 + o];
+                        y.x += tl.x;
+                        y.y += tl.y;
+                    }
                     const long long idx = tile * 384 + o;
                     if (idx < nout)
-                        out[idx] = make_float2((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y));
+                        out[idx] = y;
                 }
+                asm volatile("bar.sync 1, 128;" ::: "memory"); // everyone has read sRed / sTail[ts]: they may be rewritten
+                if (have_tail && lane == 0)
+                    mbar_arrive(&t_empty[ts]);
             } else {
                 const unsigned t0 = tmem + ((unsigned)(32 * s) << 16) + acc * C::DSTRIDE;
                 const unsigned t1 = t0 + (16u << 16) + 2; // T1 lanes, one input row (2 columns) to the right

@@ -3,15 +3,17 @@ import os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import gnuradio_b200 as grb
-n = 1 << 24
+ntaps = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+D = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+n = 1 << 23
 rng = np.random.default_rng(1)
-x = (rng.uniform(-1, 1, n + 63) + 1j * rng.uniform(-1, 1, n + 63)).astype(np.complex64)
-blk = grb.filter.fir_filter_ccf(1, rng.uniform(-1, 1, 64).astype(np.float32))
-blk.process(x, n)
+x = (rng.uniform(-1, 1, n + ntaps - 1) + 1j * rng.uniform(-1, 1, n + ntaps - 1)).astype(np.complex64)
+blk = grb.filter.fir_filter_ccf(D, rng.uniform(-1, 1, ntaps).astype(np.float32))
+blk.process(x, n // D)
 os.environ["GRB200_FIR_TC_TRACE"] = "gpurun_out/fir_tc_trace.txt"
-blk.process(x, n)
+blk.process(x, n // D)
 rows = [list(map(int, l.split())) for l in open("gpurun_out/fir_tc_trace.txt") if l.strip()]
 names = "P.start P.gotEmpty P.sts0 P.arrived | M.start M.gotB M.gotD M.issued | E.start E.gotD E.ldDone E.stored".replace("| ", "").split()
 print(" it " + " ".join("%10s" % s for s in names))
-for i, r in enumerate(rows[:32]):
+for i, r in enumerate(rows[:20]):
     print("%3d " % i + " ".join("%10d" % v for v in r))
