@@ -126,6 +126,30 @@ def test_fir_tensor_core_path(grb, orc, monkeypatch, ntaps, nout, cplx):
     assert_parity(got, ref, "tc vs cuda-core")
 
 
+@pytest.mark.parametrize("ntaps,nout", [(1024, 384 * 148 * 2 + 5), (1024, 4032), (1023, 9999), (969, 50000), (968, 50000),
+                                        (513, 70001), (256, 40000), (1000, 384 * 3 + 1 + 4032)])
+def test_fir_tensor_core_decimate_by_8(grb, orc, monkeypatch, ntaps, nout):
+    """fir_tc_kernel<M_DEC8> (BASELINE configs[3] geometry: decimation 8, up to 1024 real taps): 16 tap blocks stacked in the
+    MMA lanes, the partial 17th block (taps 968..) on the CUDA cores; ragged last tile, tap counts either side of 968."""
+    monkeypatch.setenv("GRB200_FIR_TC", "1")
+    rng = np.random.default_rng(ntaps + nout % 1009)
+    D = 8
+    x = crand(rng, nout * D)
+    taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
+    xin = np.concatenate([np.zeros(ntaps - 1, np.complex64), x])
+    got = grb.filter.fir_filter_ccf(D, taps).process(xin, nout)
+    assert len(got) == nout and np.isfinite(got.view(np.float32)).all()
+    for o0 in sorted({0, max(0, nout // 2 - 500), max(0, nout - 2000)}):
+        n0 = min(2000, nout - o0)
+        seg = xin[o0 * D: (o0 + n0) * D + ntaps - 1]
+        assert_parity(got[o0:o0 + n0], orc.fir(D, taps, seg, n0), "dec8 oracle window %d" % o0)
+        if o0 == 0:
+            assert_parity(got[:n0], po.f64_fir(D, taps, x[: n0 * D]), "dec8 f64 window 0")
+    monkeypatch.setenv("GRB200_FIR_TC", "0")
+    ref = grb.filter.fir_filter_ccf(D, taps).process(xin, nout)
+    assert_parity(got, ref, "dec8 tc vs cuda-core")
+
+
 def test_fir_tensor_core_linearity_and_impulse(grb, monkeypatch):
     """Size-independent properties at a BASELINE-sized call (2^24): impulse -> taps, linearity, shift invariance."""
     monkeypatch.setenv("GRB200_FIR_TC", "1")
