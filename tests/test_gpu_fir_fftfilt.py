@@ -150,6 +150,22 @@ def test_fir_tensor_core_decimate_by_8(grb, orc, monkeypatch, ntaps, nout):
     assert_parity(got, ref, "dec8 tc vs cuda-core")
 
 
+@pytest.mark.parametrize("mode", ["ccf", "ccc", "dec8"])
+def test_fir_tensor_core_run_to_run_identical(grb, monkeypatch, mode):
+    """The warp-specialised pipeline (TMA ring, converter / MMA / epilogue hand-offs over mbarriers, TMEM accumulator ring)
+    must be race free: the same call repeated gives bit-identical output, at a size where every CTA walks many tiles."""
+    monkeypatch.setenv("GRB200_FIR_TC", "1")
+    rng = np.random.default_rng(5)
+    D, ntaps = (8, 1024) if mode == "dec8" else (1, 64)
+    nout = (1 << 22) // D + 777
+    taps = crand(rng, ntaps) if mode == "ccc" else rng.uniform(-1, 1, ntaps).astype(np.float32)
+    blk = (grb.filter.fir_filter_ccc if mode == "ccc" else grb.filter.fir_filter_ccf)(D, taps)
+    xin = crand(rng, nout * D + ntaps - 1)
+    first = blk.process(xin, nout)
+    for _ in range(8):
+        np.testing.assert_array_equal(blk.process(xin, nout), first)
+
+
 def test_fir_tensor_core_linearity_and_impulse(grb, monkeypatch):
     """Size-independent properties at a BASELINE-sized call (2^24): impulse -> taps, linearity, shift invariance."""
     monkeypatch.setenv("GRB200_FIR_TC", "1")
