@@ -38,6 +38,8 @@ SIGNATURES = {
     "grb200_fir_destroy": (None, [vp]),
     "grb200_fftfilt_ccc_create": (i32, [i32, vp, i32, i32, pvp]),
     "grb200_fftfilt_set_taps": (i32, [vp, vp, i32]),
+    "grb200_fftfilt_ccf_create": (i32, [i32, vp, i32, i32, pvp]),
+    "grb200_fftfilt_set_taps_real": (i32, [vp, vp, i32]),
     "grb200_fftfilt_nsamples": (i32, [vp]),
     "grb200_fftfilt_ntaps": (i32, [vp]),
     "grb200_fftfilt_work": (i32, [vp, vp, vp, i64]),

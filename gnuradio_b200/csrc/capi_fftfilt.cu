@@ -101,6 +101,33 @@ int grb200_fftfilt_set_taps(grb200_fftfilt* h, const float* taps_re_im, int ntap
     return fftfilt_prepare(h, taps_re_im, ntaps);
 }
 
+static std::vector<float> real_taps_as_complex(const float* taps, int ntaps)
+{
+    std::vector<float> t((size_t)2 * (ntaps > 0 ? ntaps : 0), 0.f);
+    for (int i = 0; i < ntaps; i++)
+        t[2 * (size_t)i] = taps[i]; // (t, 0): fft_filter.cc:317-320
+    return t;
+}
+
+int grb200_fftfilt_ccf_create(int decim, const float* taps, int ntaps, int device, grb200_fftfilt** out)
+{
+    if (ntaps < 1 || !taps) {
+        if (out)
+            *out = nullptr;
+        return fail(GRB200_EINVAL, "fft_filter_ccf: at least one tap is required");
+    }
+    const std::vector<float> t = real_taps_as_complex(taps, ntaps);
+    return grb200_fftfilt_ccc_create(decim, t.data(), ntaps, device, out);
+}
+
+int grb200_fftfilt_set_taps_real(grb200_fftfilt* h, const float* taps, int ntaps)
+{
+    if (!h || !taps || ntaps < 1)
+        return fail(GRB200_EINVAL, "fft_filter_ccf::set_taps: bad arguments");
+    const std::vector<float> t = real_taps_as_complex(taps, ntaps);
+    return grb200_fftfilt_set_taps(h, t.data(), ntaps);
+}
+
 int grb200_fftfilt_nsamples(const grb200_fftfilt* h) { return h ? h->nsamples : 0; }
 int grb200_fftfilt_ntaps(const grb200_fftfilt* h) { return h ? h->ntaps : 0; }
 

@@ -112,15 +112,20 @@ class fir_filter_ccc(_fir_filter_blk):
 
 
 class fft_filter_ccc(sync_decimator):
+    _name = "fft_filter_ccc"
+    _create = "grb200_fftfilt_ccc_create"
+    _set_taps = "grb200_fftfilt_set_taps"
+    _tap_dtype = np.complex64
+
     def __init__(self, decimation, taps, nthreads=1, device=0):
         L = _lib.lib()
         if int(decimation) < 1:
-            raise ValueError("fft_filter_ccc: decimation must be >= 1")
-        sync_decimator.__init__(self, "fft_filter_ccc", io_signature.make(1, 1, 8), io_signature.make(1, 1, 8),
+            raise ValueError("%s: decimation must be >= 1" % self._name)
+        sync_decimator.__init__(self, self._name, io_signature.make(1, 1, 8), io_signature.make(1, 1, 8),
                                 decimation)
         self._h = C.c_void_p()
         t = self._conv_taps(taps)
-        _lib.check(L.grb200_fftfilt_ccc_create(int(decimation), _ptr(t), len(t), int(device), C.byref(self._h)))
+        _lib.check(getattr(L, self._create)(int(decimation), _ptr(t), len(t), int(device), C.byref(self._h)))
         self._taps = t.copy()
         self._new_taps = t.copy()
         self._nthreads = int(nthreads)
@@ -133,11 +138,11 @@ class fft_filter_ccc(sync_decimator):
     def make(cls, decimation, taps, nthreads=1, device=0):
         return cls(decimation, taps, nthreads, device)
 
-    @staticmethod
-    def _conv_taps(taps):
-        t = np.ascontiguousarray(taps, np.complex64)
+    @classmethod
+    def _conv_taps(cls, taps):
+        t = np.ascontiguousarray(taps, cls._tap_dtype)
         if t.ndim != 1 or t.size < 1:
-            raise ValueError("fft_filter_ccc: at least one tap is required")
+            raise ValueError("%s: at least one tap is required" % cls._name)
         return t
 
     def set_taps(self, taps):  # fft_filter_ccc_impl.cc:49-53: deferred to the next work()
@@ -160,7 +165,7 @@ class fft_filter_ccc(sync_decimator):
         L = _lib.lib()
         if self.d_updated:  # fft_filter_ccc_impl.cc:68-73
             t = self._new_taps
-            _lib.check(L.grb200_fftfilt_set_taps(self._h, _ptr(t), len(t)))
+            _lib.check(getattr(L, self._set_taps)(self._h, _ptr(t), len(t)))
             self._taps = t.copy()
             self.d_nsamples = L.grb200_fftfilt_nsamples(self._h)
             self.d_updated = False
@@ -193,6 +198,15 @@ class fft_filter_ccc(sync_decimator):
                 _lib.lib().grb200_fftfilt_destroy(h)
             except Exception:
                 pass
+
+
+class fft_filter_ccf(fft_filter_ccc):
+    """gr::filter::fft_filter_ccf (gr-filter/lib/fft_filter_ccf_impl.cc:32-78 over kernel::fft_filter_ccf,
+    fft_filter.cc:291-419): real taps on a complex stream; same geometry, state and work() contract as ccc."""
+    _name = "fft_filter_ccf"
+    _create = "grb200_fftfilt_ccf_create"
+    _set_taps = "grb200_fftfilt_set_taps_real"
+    _tap_dtype = np.float32
 
 
 class pfb_channelizer_ccf(block):

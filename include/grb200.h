@@ -84,6 +84,12 @@ void grb200_fir_destroy(grb200_fir* h);
 typedef struct grb200_fftfilt grb200_fftfilt;
 int grb200_fftfilt_ccc_create(int decim, const float* taps_re_im, int ntaps, int device, grb200_fftfilt** out);
 int grb200_fftfilt_set_taps(grb200_fftfilt* h, const float* taps_re_im, int ntaps);
+/* fft_filter_ccf: kernel::fft_filter_ccf (gr-filter/lib/fft_filter.cc:291-419) and the block shell
+ * gr-filter/lib/fft_filter_ccf_impl.cc -- real taps, complex stream.  The reference transforms the taps as (t, 0) complex
+ * numbers (fft_filter.cc:317-320) and is otherwise the ccc kernel, so both constructors give the same handle type; every
+ * other grb200_fftfilt_* call applies unchanged. */
+int grb200_fftfilt_ccf_create(int decim, const float* taps, int ntaps, int device, grb200_fftfilt** out);
+int grb200_fftfilt_set_taps_real(grb200_fftfilt* h, const float* taps, int ntaps);
 int grb200_fftfilt_nsamples(const grb200_fftfilt* h);
 int grb200_fftfilt_ntaps(const grb200_fftfilt* h);
 int grb200_fftfilt_work(grb200_fftfilt* h, const void* in_host, void* out_host, long long noutput);

@@ -269,6 +269,57 @@ private:
     bool d_updated = false;
 };
 
+// fft_filter_ccf (gr-filter/include/gnuradio/filter/fft_filter_ccf.h, lib/fft_filter_ccf_impl.cc:32-78): real taps
+class fft_filter_ccf : public grb200::rt::sync_decimator
+{
+public:
+    typedef std::shared_ptr<fft_filter_ccf> sptr;
+    static sptr make(int decimation, const std::vector<float>& taps, int nthreads = 1)
+    {
+        return sptr(new fft_filter_ccf(decimation, taps, nthreads));
+    }
+    ~fft_filter_ccf() override { grb200_fftfilt_destroy(d_h); }
+
+    void set_taps(const std::vector<float>& taps) // fft_filter_ccf_impl.cc:49-53
+    {
+        d_new_taps = taps;
+        d_updated = true;
+    }
+    std::vector<float> taps() const { return d_new_taps; }
+    void set_nthreads(int n) { d_nthreads = n; }
+    int nthreads() const { return d_nthreads; }
+
+    int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
+    {
+        if (d_updated) { // fft_filter_ccf_impl.cc:68-73
+            grb200::check(grb200_fftfilt_set_taps_real(d_h, d_new_taps.data(), (int)d_new_taps.size()));
+            d_nsamples = grb200_fftfilt_nsamples(d_h);
+            d_updated = false;
+            set_output_multiple(d_nsamples);
+            return 0;
+        }
+        grb200::check(grb200_fftfilt_work(d_h, input_items[0], output_items[0], noutput_items));
+        return noutput_items;
+    }
+    grb200_fftfilt* handle() { return d_h; }
+
+private:
+    fft_filter_ccf(int decimation, const std::vector<float>& taps, int nthreads)
+        : sync_decimator("fft_filter_ccf", grb200::rt::io_signature::make(1, 1, sizeof(gr_complex)),
+                         grb200::rt::io_signature::make(1, 1, sizeof(gr_complex)), decimation),
+          d_new_taps(taps), d_nthreads(nthreads)
+    {
+        set_history(1);
+        grb200::check(grb200_fftfilt_ccf_create(decimation, taps.data(), (int)taps.size(), grb200::default_device(), &d_h));
+        d_nsamples = grb200_fftfilt_nsamples(d_h);
+        set_output_multiple(d_nsamples);
+    }
+    grb200_fftfilt* d_h = nullptr;
+    std::vector<float> d_new_taps;
+    int d_nsamples = 0, d_nthreads = 1;
+    bool d_updated = false;
+};
+
 // ---------------------------------------------------------------------------------------------------
 // pfb_channelizer_ccf
 // ---------------------------------------------------------------------------------------------------

@@ -245,6 +245,22 @@ int grbo_fft_filter_ccc(int decim, const cf32* taps, int ntaps, const cf32* in, 
     return nsamples;
 }
 
+/* fft_filter_ccf (gr-filter/lib/fft_filter.cc:291-419): the taps enter the transform as (t, 0) (:317-320); everything
+ * else is the ccc kernel line for line. */
+int grbo_fft_filter_ccf(int decim, const float* taps, int ntaps, const cf32* in, cf32* out, long nitems, long chunk_out)
+{
+    cf32* t = (cf32*)malloc(sizeof(cf32) * (size_t)(ntaps > 0 ? ntaps : 1));
+    if (!t)
+        return -2;
+    for (int i = 0; i < ntaps; i++) {
+        t[i].re = taps[i];
+        t[i].im = 0.0f;
+    }
+    int rc = grbo_fft_filter_ccc(decim, t, ntaps, in, out, nitems, chunk_out);
+    free(t);
+    return rc;
+}
+
 /* ------------------------------------------------------------------------------------------------
  * pfb_channelizer_ccf: polyphase_filterbank::set_taps (gr-filter/lib/polyphase_filterbank.cc:53-81),
  * ctor LUT / output multiple (gr-filter/lib/pfb_channelizer_ccf_impl.cc:49-84), general_work

@@ -108,6 +108,20 @@ class _CLib:
         assert rc == ns, rc
         return out
 
+    def fft_filter_ccf(self, decim, taps, x, chunk_out=0):
+        """kernel::fft_filter_ccf (gr-filter/lib/fft_filter.cc:291-419) driven like fft_filter_ccf_impl::work."""
+        t = np.ascontiguousarray(taps, np.float32)
+        x = _c64(x)
+        ns = self.fft_filter_nsamples(len(t))
+        nitems = (len(x) // decim // ns) * ns
+        out = np.empty(nitems, np.complex64)
+        if nitems == 0:
+            return out
+        rc = self._f("fft_filter_ccf")(decim, _p(t), len(t), _p(x), _p(out), C.c_long(nitems),
+                                       C.c_long(chunk_out))
+        assert rc == ns, rc
+        return out
+
     # -- pfb_channelizer_ccf: one general_work() call ---------------------------------------------
     def pfb_taps_per_filter(self, nfilts, ntaps):
         return int(self._f("pfb_taps_per_filter")(C.c_uint(nfilts), int(ntaps)))

@@ -159,6 +159,29 @@ int grref_fft_filter_ccc(int decim,
     return nsamples;
 }
 
+/* same driver for kernel::fft_filter_ccf (gr-filter/lib/fft_filter.cc:291-419; shell fft_filter_ccf_impl.cc:61-78) */
+int grref_fft_filter_ccf(int decim, const float* taps, int ntaps, const void* in, void* out, long nitems, long chunk_out)
+{
+    std::vector<float> t(taps, taps + ntaps);
+    gr::filter::kernel::fft_filter_ccf filt(decim, t, 1);
+    const int nsamples = filt.set_taps(t);
+    if (nitems % nsamples != 0)
+        return -1;
+    long chunk = (chunk_out / nsamples) * nsamples;
+    if (chunk <= 0)
+        chunk = nsamples;
+    const gr_complex* ip = (const gr_complex*)in;
+    gr_complex* op = (gr_complex*)out;
+    for (long done = 0; done < nitems;) {
+        long n = std::min(chunk, nitems - done);
+        filt.filter((int)n, ip, op);
+        ip += n * decim;
+        op += n;
+        done += n;
+    }
+    return nsamples;
+}
+
 int grref_fft_filter_nsamples(int ntaps)
 {
     std::vector<gr_complex> t(ntaps, gr_complex(1.0f, 0.0f));

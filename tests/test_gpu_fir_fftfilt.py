@@ -272,6 +272,39 @@ def test_fft_filter_qa_random_trials(grb, orc):
         assert_parity(got, ref, "dec %d" % dec)
 
 
+def test_fft_filter_ccf(grb, orc):
+    """fft_filter_ccf (qa_fft_filter.py:214-283): real taps through grb200_fftfilt_ccf_create /
+    set_taps_real, against kernel::fft_filter_ccf (oracle), fir_filter_ccf and float64; decimation and set_taps too."""
+    src = np.arange(8).astype(np.complex64)
+    for g in (1.0, 2.0):
+        blk = grb.filter.fft_filter_ccf(1, [g], 2)
+        assert blk.nthreads() == 2 and blk.nsamples() == 2
+        assert_tuples_almost_equal2((g * src).tolist(), sched_mock.run_sync(blk, src).tolist(), abs_eps=1e-5, rel_eps=1e-5)
+    random.seed(0)
+    for i in range(6):
+        src = np.array(make_random_complex_tuple(4096), np.complex64)
+        ntaps = int(random.uniform(2, 1000))
+        taps = np.array([2 * random.random() - 1 for _ in range(ntaps)], np.float32)
+        dec = 1 + i % 3
+        blk = grb.filter.fft_filter_ccf(dec, taps)
+        got = sched_mock.run_sync(blk, src)
+        ref = orc.fft_filter_ccf(dec, taps, src)
+        assert len(got) == len(ref) > 0
+        assert_parity(got, ref, "ccf trial %d vs oracle" % i)
+        assert_parity(got, orc.fir_stream(dec, taps, src)[: len(got)], "ccf trial %d vs fir" % i)
+        assert_parity(got, po.f64_fft_filter(dec, taps, src, blk.nsamples()), "ccf trial %d f64" % i)
+    blk = grb.filter.fft_filter_ccf(1, np.ones(5, np.float32))
+    x = crand(np.random.default_rng(9), 12 * 40)
+    a = sched_mock.run_sync(blk, x)
+    t2 = np.linspace(-1, 1, 37).astype(np.float32)
+    blk.set_taps(t2)  # deferred to the next work(): output multiple changes from 12 to 92
+    assert blk.taps() == t2.tolist()
+    b = sched_mock.run_sync(blk, x)
+    assert blk.nsamples() == 128 - 37 + 1
+    assert_parity(a, orc.fft_filter_ccf(1, np.ones(5, np.float32), x), "before set_taps")
+    assert_parity(b, orc.fft_filter_ccf(1, t2, x)[: len(b)], "after set_taps")
+
+
 @pytest.mark.parametrize("ntaps", [1, 2, 31, 1024, 4096, 6000])
 def test_fft_filter_sizes(grb, orc, ntaps):
     rng = np.random.default_rng(ntaps)

@@ -79,6 +79,25 @@ def test_fft_filter_qa_random_trials(lay):
         assert_parity(got, exp[: len(got)], "dec %d" % dec, 2e-6, 4e-5)
 
 
+def test_fft_filter_ccf_qa(lay):
+    """fft_filter_ccf: qa_fft_filter.py:214-283 -- identity / gain taps (test_ccf_001..003) and the
+    seeded random trials against fir_filter_ccf (test_ccf_004, rel_eps 4e-4); both oracle layers, real taps."""
+    src = np.arange(8).astype(np.complex64)
+    assert_tuples_almost_equal2(src.tolist(), lay.fft_filter_ccf(1, [1.0], src).tolist(), abs_eps=1e-5, rel_eps=1e-5)
+    assert_tuples_almost_equal2((2 * src).tolist(), lay.fft_filter_ccf(1, [2.0], src).tolist(), abs_eps=1e-5, rel_eps=1e-5)
+    random.seed(0)
+    for i in range(6):
+        src = np.array(make_random_complex_tuple(4096), np.complex64)
+        ntaps = int(random.uniform(2, 1000))
+        taps = np.array([2 * random.random() - 1 for _ in range(ntaps)], np.float32)
+        exp = lay.fir_stream(1, taps, src)
+        got = lay.fft_filter_ccf(1, taps, src)
+        assert len(got) == (4096 // lay.fft_filter_nsamples(ntaps)) * lay.fft_filter_nsamples(ntaps)
+        assert_parity(got, exp[: len(got)], "ccf trial %d" % i, 2e-6, 4e-5)
+        assert_parity(got, lay.fft_filter_ccc(1, taps.astype(np.complex64), src), "ccf == ccc with (t, 0) taps", 1e-7, 1e-6)
+        assert_parity(got, po.f64_fft_filter(1, taps, src, lay.fft_filter_nsamples(ntaps)), "ccf f64", 2e-6, 2e-5)
+
+
 def test_fft_filter_chunked_state(lay):
     # the OLA tail (d_tail) carries between filter() calls: one call == many calls
     rng = np.random.default_rng(5)
