@@ -17,7 +17,7 @@
 //
 // Complex taps (fir_filter_ccc, fir_filter.cc:153-162): two such products per tile, Dr = A(Re h) B and Di = A(Im h) B on
 // the same B operand; the (re, im) columns of an input row are adjacent registers of the epilogue thread, which forms
-// out = (Dr.re - Di.im, Dr.im + Di.re).  A then takes 256 TMEM columns, so a tile is 32 rows (Cfg<true>).
+// out = (Dr.re - Di.im, Dr.im + Di.re).  A then takes 256 TMEM columns and Dr | Di the other 256 (one accumulator stage).
 //
 // Precision: kind::tf32 truncates the low 13 mantissa bits of an fp32 operand (measured: tools/tc_probe.cu), so
 // x_hi is the raw value and x_lo = x - trunc(x) is exact; D = A_hi B_hi + A_lo B_hi + A_hi B_lo leaves an error of
@@ -46,8 +46,9 @@ constexpr int NTHREADS = (NCONV + 2 + NEPI) * 32;
 // Tile geometry per MODE.
 // M_CCF: 64 input rows (N = 128), one accumulator of 128 columns per stage, A = [hi | lo] (128 TMEM columns).
 // M_CCC: taps hr + j hi need TWO products per tile, Dr = A(hr) B and Di = A(hi) B (out = (Dr.re - Di.im, Dr.im + Di.re)), and
-//        A = [hr_hi | hr_lo | hi_hi | hi_lo] takes 256 of the 512 TMEM columns, so a tile is 32 rows (N = 64): Dr | Di = 128
-//        columns per stage, two stages.
+//        A = [hr_hi | hr_lo | hi_hi | hi_lo] takes 256 of the 512 TMEM columns; Dr | Di take the other 256, so there is ONE
+//        accumulator stage (an N = 64 tile with two stages was tried: a tcgen05.mma of N = 64 takes as long as one of N = 128,
+//        56 vs 71 clocks here, so halving N halves the throughput).
 // M_DEC8: fir_filter_ccf with decimation 8 and up to 1024 taps (BASELINE configs[3]).  A row of 64 inputs yields 8 outputs
 //        j; out[8r + j] = sum_{d=0..16} sum_k h[64 d + k - 8 j] X_{r+d}[k].  The 16 blocks d = 0..15 are STACKED in the 128
 //        lanes of one A operand (lane group (d, j)), so the MMA work per input sample equals the 64-tap case; block 16
@@ -61,18 +62,18 @@ enum { M_CCF = 0, M_CCC = 1, M_DEC8 = 2 };
 template <int MODE>
 struct Cfg {
     static constexpr bool CT = MODE == M_CCC;
-    static constexpr int ROWS = CT ? 32 : 64;                  // input rows per tile
+    static constexpr int ROWS = 64;                            // input rows per tile
     static constexpr int OROWS = MODE == M_DEC8 ? 48 : ROWS - 1; // rows of the tile that produce output
     static constexpr int OUT_PER_ROW = MODE == M_DEC8 ? 8 : 64;
     static constexpr int NCOL = 2 * ROWS;                      // MMA N: (row, re|im)
-    static constexpr int RSTAGES = CT ? 4 : (MODE == M_DEC8 ? 2 : 3); // raw input ring
-    static constexpr int BSTAGES = CT ? 3 : 2;                 // converted operand ring
-    static constexpr int DSTAGES = CT ? 2 : 3;                 // TMEM accumulator ring
+    static constexpr int RSTAGES = MODE == M_DEC8 ? 2 : 3;     // raw input ring
+    static constexpr int BSTAGES = 2;                          // converted operand ring
+    static constexpr int DSTAGES = CT ? 1 : 3;                 // TMEM accumulator ring
     static constexpr int RAW_BYTES = ROWS * 64 * 8;
     static constexpr int KBLK_BYTES = NCOL * 128;        // one 32-float K block of the B tile, 128-byte swizzle
     static constexpr int OPER_BYTES = 2 * KBLK_BYTES;    // K = 64 floats
     static constexpr int BSTAGE_BYTES = 2 * OPER_BYTES;  // hi + lo
-    static constexpr int DSTRIDE = 128;                  // TMEM columns per accumulator stage
+    static constexpr int DSTRIDE = CT ? 256 : 128;       // TMEM columns per accumulator stage (ccc: Dr | Di)
     static constexpr unsigned TMEM_A = DSTAGES * DSTRIDE; // ccf 384, ccc/dec8 256; 64-column blocks follow
     static constexpr int CHUNKS = ROWS * 16 / (NCONV * 32); // 32-byte chunks per converter thread and tile
     static constexpr int TSTAGES = 4;                    // M_DEC8: ring of 17th-block results (tail warps -> epilogue)
@@ -567,11 +568,14 @@ static int fir_tc_launch_t(int ntaps, const void* rev, const void* in, void* out
                            cudaStream_t st)
 {
     using C = tc::Cfg<MODE>;
-    static std::atomic<int> configured{0};
-    if (!configured.load(std::memory_order_acquire)) {
+    static std::atomic<int> configured[64]; // the attribute is per device
+    int dev = 0;
+    GRB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !configured[dev].load(std::memory_order_acquire)) {
         GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
         GRB_CUDA(cudaFuncSetAttribute(fir_tc_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-        configured.store(1, std::memory_order_release);
+        if (dev >= 0 && dev < 64)
+            configured[dev].store(1, std::memory_order_release);
     }
     const long long orows = (nout + C::OUT_PER_ROW - 1) / C::OUT_PER_ROW;
     const long long ntiles = (orows + C::OROWS - 1) / C::OROWS;

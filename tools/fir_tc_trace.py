@@ -8,7 +8,9 @@ D = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 n = 1 << 23
 rng = np.random.default_rng(1)
 x = (rng.uniform(-1, 1, n + ntaps - 1) + 1j * rng.uniform(-1, 1, n + ntaps - 1)).astype(np.complex64)
-blk = grb.filter.fir_filter_ccf(D, rng.uniform(-1, 1, ntaps).astype(np.float32))
+cplx = len(sys.argv) > 3 and sys.argv[3] == "ccc"
+taps = (rng.uniform(-1, 1, ntaps) + 1j * rng.uniform(-1, 1, ntaps)).astype(np.complex64) if cplx else rng.uniform(-1, 1, ntaps).astype(np.float32)
+blk = (grb.filter.fir_filter_ccc if cplx else grb.filter.fir_filter_ccf)(D, taps)
 blk.process(x, n // D)
 os.environ["GRB200_FIR_TC_TRACE"] = "gpurun_out/fir_tc_trace.txt"
 blk.process(x, n // D)
