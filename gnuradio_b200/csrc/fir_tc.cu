@@ -53,8 +53,9 @@ constexpr int NTHREADS = (NCONV + 2 + NEPI) * 32;
 //        j; out[8r + j] = sum_{d=0..16} sum_k h[64 d + k - 8 j] X_{r+d}[k].  The 16 blocks d = 0..15 are STACKED in the 128
 //        lanes of one A operand (lane group (d, j)), so the MMA work per input sample equals the 64-tap case; block 16
 //        (only k < 8 j, taps 968..1023: 28 multiply-adds per output) does not fit the 128 lanes and is evaluated on the CUDA
-//        cores by the converter warps straight from the raw tile, after they have handed the B tile to the MMA warp (a second
-//        MMA for it cost 44 %, two dedicated warps were too slow).  The epilogue sums the 16 lane groups with their row shifts: four per thread in registers
+//        cores by the converter warps from the samples they still hold in registers, after they have handed the B tile to
+//        the MMA warp: 28 taps per thread live in registers, the 16 lanes of a row reduce-scatter the 8 phase sums with 16
+//        shuffles (a second MMA for it cost 44 %; reading the samples back from shared memory was load bound).  The epilogue sums the 16 lane groups with their row shifts: four per thread in registers
 //        (tcgen05.ld column offsets are free), the last four across the epilogue warps through shared memory.
 //        A tile = 64 input rows -> 48 output rows x 8 (tiles overlap by 16 rows).
 enum { M_CCF = 0, M_CCC = 1, M_DEC8 = 2 };
@@ -80,7 +81,7 @@ struct Cfg {
     static constexpr int NBARS = 2 * RSTAGES + 2 * BSTAGES + 2 * DSTAGES + 1 + (MODE == M_DEC8 ? 2 * TSTAGES : 0);
     static constexpr int RED_BYTES = MODE == M_DEC8 ? 4 * 384 * 8 : 0;            // 4 partial sums x 384 outputs
     static constexpr int TAIL_BYTES = MODE == M_DEC8 ? TSTAGES * 384 * 8 : 0;     // 17th-block sums per tile
-    static constexpr int COEF_BYTES = MODE == M_DEC8 ? 8 * 56 * 4 : 0;            // 17th-block taps [j][k]
+    static constexpr int COEF_BYTES = 0;
     static constexpr int SMEM_BYTES =
         BSTAGES * BSTAGE_BYTES + RSTAGES * RAW_BYTES + RED_BYTES + TAIL_BYTES + COEF_BYTES + 256 + 1024;
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
@@ -233,14 +234,16 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
         const int p = tid;
         const unsigned sB_u32 = smem_u32(sB), sR_u32 = smem_u32(sR);
         const int hsel = (lane >> 2) & 1; // which 16-byte half of its 32-byte chunk a lane reads first (bank-conflict free)
-        if (have_tail) { // taps of the partial 17th block: coef[j][k] = h[1024 + k - 8 j] for k < 8 j
-            float* coef = (float*)sCoef;
-            for (int idx = p; idx < 8 * 56; idx += NCONV * 32) {
-                const int j = idx / 56, k = idx % 56, t = 1024 + k - 8 * j;
-                coef[idx] = (k < 8 * j && t < ntaps) ? __ldg((const float*)rev_ + t) : 0.f;
+        // M_DEC8, partial 17th tap block: this thread's chunk is always samples k = 4 q .. 4 q + 3 of a row (q = p & 15), so its
+        // 7 x 4 taps c[j][u] = h[1024 + 4 q + u - 8 j] (zero unless 4 q + u < 8 j) stay in registers for the whole kernel
+        float ct[8][4];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int k = 4 * (p & 15) + u, t = 1024 + k - 8 * j;
+                ct[j][u] = (have_tail && k < 8 * j && t < ntaps) ? __ldg((const float*)rev_ + t) : 0.f;
             }
-            asm volatile("bar.sync 2, 256;" ::: "memory");
-        }
         int it = 0;
 #pragma unroll 1
         for (long long tile = blockIdx.x; tile < ntiles; tile += G, ++it) {
@@ -301,40 +304,51 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                 mbar_arrive(&raw_empty[rs]); // the stores above depend on every raw read of this warp
             }
             if (have_tail) {
-                // 17th tap block on the CUDA cores: out[8 r + j] += sum_{k < 8 j} h[1024 + k - 8 j] X_{r+16}[k], X read back from
-                // the B_hi tile just written (rows 2 (r + 16) and + 1: re and im, zero-filled past the end of the input).
-                // thread = (output row r = p / 4, phase pair (jq + 1, 7 - jq)): 64 / 64 / 64 / 32 multiply-adds, balanced
-                asm volatile("bar.sync 2, 256;" ::: "memory"); // every converter warp has written its part of the tile
+                // 17th tap block on the CUDA cores: out[8 r + j] += sum_{k < 8 j} h[1024 + k - 8 j] X_{r+16}[k].  The samples are
+                // still in this thread's registers (chunk i = rows (p >> 4) + 16 i: i = 1..3 are rows 16..63 = output rows 0..47);
+                // the 16 lanes that hold a row reduce-scatter their 8 phase sums (xor 8, 4, 2: halve the phases kept; xor 1: add).
                 const int ts = it % C::TSTAGES, tuse = it / C::TSTAGES;
-                const int r = p >> 2, jq = p & 3, jA = jq + 1, jB = 7 - jq;
-                float2 accA = make_float2(0.f, 0.f), accB = accA;
-                if (r < OROWS) {
-                    const int n = 2 * (r + 16);
-                    const unsigned rowre = bh + (n >> 3) * 1024 + (n & 7) * 128, rowim = rowre + 128;
-                    const unsigned cA = smem_u32(sCoef) + jA * 56 * 4, cB = smem_u32(sCoef) + jB * 56 * 4;
+                float2 tot[3];
 #pragma unroll
-                    for (int ch = 0; ch < 14; ++ch) { // k = 4 ch .. 4 ch + 3 < 56
-                        const unsigned ko = (ch >> 3) * KBLK_BYTES;
-                        const float4 xr = lds128(rowre + ko + (((ch & 7) ^ (n & 7)) << 4));
-                        const float4 xi = lds128(rowim + ko + (((ch & 7) ^ ((n & 7) + 1)) << 4));
-                        const float4 a = lds128(cA + 16 * ch), b = lds128(cB + 16 * ch);
-                        accA.x = fmaf(a.x, xr.x, accA.x), accA.y = fmaf(a.x, xi.x, accA.y);
-                        accA.x = fmaf(a.y, xr.y, accA.x), accA.y = fmaf(a.y, xi.y, accA.y);
-                        accA.x = fmaf(a.z, xr.z, accA.x), accA.y = fmaf(a.z, xi.z, accA.y);
-                        accA.x = fmaf(a.w, xr.w, accA.x), accA.y = fmaf(a.w, xi.w, accA.y);
-                        accB.x = fmaf(b.x, xr.x, accB.x), accB.y = fmaf(b.x, xi.x, accB.y);
-                        accB.x = fmaf(b.y, xr.y, accB.x), accB.y = fmaf(b.y, xi.y, accB.y);
-                        accB.x = fmaf(b.z, xr.z, accB.x), accB.y = fmaf(b.z, xi.z, accB.y);
-                        accB.x = fmaf(b.w, xr.w, accB.x), accB.y = fmaf(b.w, xi.w, accB.y);
+                for (int i = 1; i < 4; ++i) {
+                    const float4 a = v[i][0], b = v[i][1];
+                    float2 val[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        val[j].x = fmaf(ct[j][3], b.z, fmaf(ct[j][2], b.x, fmaf(ct[j][1], a.z, ct[j][0] * a.x)));
+                        val[j].y = fmaf(ct[j][3], b.w, fmaf(ct[j][2], b.y, fmaf(ct[j][1], a.w, ct[j][0] * a.y)));
                     }
+                    float2 k4[4], k2[2], k1;
+                    const bool b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float2 keep = b3 ? val[j + 4] : val[j], send = b3 ? val[j] : val[j + 4];
+                        k4[j].x = keep.x + __shfl_xor_sync(0xffffffffu, send.x, 8);
+                        k4[j].y = keep.y + __shfl_xor_sync(0xffffffffu, send.y, 8);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        const float2 keep = b2 ? k4[j + 2] : k4[j], send = b2 ? k4[j] : k4[j + 2];
+                        k2[j].x = keep.x + __shfl_xor_sync(0xffffffffu, send.x, 4);
+                        k2[j].y = keep.y + __shfl_xor_sync(0xffffffffu, send.y, 4);
+                    }
+                    {
+                        const float2 keep = b1 ? k2[1] : k2[0], send = b1 ? k2[0] : k2[1];
+                        k1.x = keep.x + __shfl_xor_sync(0xffffffffu, send.x, 2);
+                        k1.y = keep.y + __shfl_xor_sync(0xffffffffu, send.y, 2);
+                    }
+                    tot[i - 1].x = k1.x + __shfl_xor_sync(0xffffffffu, k1.x, 1);
+                    tot[i - 1].y = k1.y + __shfl_xor_sync(0xffffffffu, k1.y, 1);
                 }
                 if (tuse > 0)
                     mbar_wait(&t_empty[ts], (tuse - 1) & 1);
-                if (r < OROWS) {
-                    sTail[ts * 384 + r * 8 + jA] = accA;
-                    sTail[ts * 384 + r * 8 + jB] = accB;
+                if ((lane & 1) == 0) { // lane bits (3, 2, 1) = the phase j this lane ended up with
+                    const int j = ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+#pragma unroll
+                    for (int i = 1; i < 4; ++i)
+                        sTail[ts * 384 + ((p >> 4) + 16 * (i - 1)) * 8 + j] = tot[i - 1];
                 }
-                asm volatile("bar.sync 2, 256;" ::: "memory"); // all tail reads of this B stage are done before anyone refills it
+                __syncwarp();
                 if (lane == 0)
                     mbar_arrive(&t_full[ts]);
             }
