@@ -275,35 +275,8 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                     v[i][1] = make_float4(z[2].x, z[2].y, z[3].x, z[3].y);
                 }
             }
-            if (buse > 0)
-                mbar_wait(&b_empty[stage], (buse - 1) & 1);
-            if (tr) trace[it * 16 + 2] = clock64();
-            const unsigned bh = sB_u32 + stage * BSTAGE_BYTES;
-#pragma unroll
-            for (int i = 0; i < C::CHUNKS; ++i) {
-                const int c = p + 256 * i;
-                const int n0 = 2 * (c >> 4), q = c & 15;
-                const unsigned base = (unsigned)((q >> 3) * KBLK_BYTES + (n0 >> 3) * 1024 + (n0 & 7) * 128);
-                const unsigned off_re = base + (((q & 7) ^ (n0 & 7)) << 4);
-                const unsigned off_im = base + 128 + (((q & 7) ^ ((n0 & 7) + 1)) << 4);
-                const float4 a = v[i][0], b = v[i][1];
-                const float4 re = make_float4(a.x, a.z, b.x, b.z), im = make_float4(a.y, a.w, b.y, b.w);
-                const float4 rl = make_float4(re.x - trunc_tf32(re.x), re.y - trunc_tf32(re.y), re.z - trunc_tf32(re.z),
-                                              re.w - trunc_tf32(re.w));
-                const float4 il = make_float4(im.x - trunc_tf32(im.x), im.y - trunc_tf32(im.y), im.z - trunc_tf32(im.z),
-                                              im.w - trunc_tf32(im.w));
-                sts128(bh + off_re, re); // the tensor core ignores the low 13 bits: raw value = hi part
-                sts128(bh + off_im, im);
-                sts128(bh + OPER_BYTES + off_re, rl);
-                sts128(bh + OPER_BYTES + off_im, il);
-            }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(&b_full[stage]);
-                mbar_arrive(&raw_empty[rs]); // the stores above depend on every raw read of this warp
-            }
             if (have_tail) {
+                // (done here, before waiting for a free B stage: in the MMA-bound regime that wait hides it)
                 // 17th tap block on the CUDA cores: out[8 r + j] += sum_{k < 8 j} h[1024 + k - 8 j] X_{r+16}[k].  The samples are
                 // still in this thread's registers (chunk i = rows (p >> 4) + 16 i: i = 1..3 are rows 16..63 = output rows 0..47);
                 // the 16 lanes that hold a row reduce-scatter their 8 phase sums (xor 8, 4, 2: halve the phases kept; xor 1: add).
@@ -351,6 +324,34 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                 __syncwarp();
                 if (lane == 0)
                     mbar_arrive(&t_full[ts]);
+            }
+            if (buse > 0)
+                mbar_wait(&b_empty[stage], (buse - 1) & 1);
+            if (tr) trace[it * 16 + 2] = clock64();
+            const unsigned bh = sB_u32 + stage * BSTAGE_BYTES;
+#pragma unroll
+            for (int i = 0; i < C::CHUNKS; ++i) {
+                const int c = p + 256 * i;
+                const int n0 = 2 * (c >> 4), q = c & 15;
+                const unsigned base = (unsigned)((q >> 3) * KBLK_BYTES + (n0 >> 3) * 1024 + (n0 & 7) * 128);
+                const unsigned off_re = base + (((q & 7) ^ (n0 & 7)) << 4);
+                const unsigned off_im = base + 128 + (((q & 7) ^ ((n0 & 7) + 1)) << 4);
+                const float4 a = v[i][0], b = v[i][1];
+                const float4 re = make_float4(a.x, a.z, b.x, b.z), im = make_float4(a.y, a.w, b.y, b.w);
+                const float4 rl = make_float4(re.x - trunc_tf32(re.x), re.y - trunc_tf32(re.y), re.z - trunc_tf32(re.z),
+                                              re.w - trunc_tf32(re.w));
+                const float4 il = make_float4(im.x - trunc_tf32(im.x), im.y - trunc_tf32(im.y), im.z - trunc_tf32(im.z),
+                                              im.w - trunc_tf32(im.w));
+                sts128(bh + off_re, re); // the tensor core ignores the low 13 bits: raw value = hi part
+                sts128(bh + off_im, im);
+                sts128(bh + OPER_BYTES + off_re, rl);
+                sts128(bh + OPER_BYTES + off_im, il);
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&b_full[stage]);
+                mbar_arrive(&raw_empty[rs]); // the stores above depend on every raw read of this warp
             }
             if (tr) trace[it * 16 + 3] = clock64();
         }
