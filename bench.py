@@ -108,6 +108,9 @@ class PfbChannelizer(Workload):
     alg_bytes, flops, log2n, seed = 16.0, 94.0, 30, 3
     kernel = "pfb_stream_kernel"
     M, T = 64, 16
+    # profiles/r1_pfb_stream_kernel_ncu.txt: 2.157 GB read + 2.103 GB written for a 2^28-sample launch
+    ncu_dram_bytes_per_sample = (2.157e9 + 2.103e9) / (1 << 28)
+    ncu_source = "profiles/r1_pfb_stream_kernel_ncu.txt (2^28-sample launch, scaled)"
 
     def setup(self):
         M, T = self.M, self.T
@@ -169,6 +172,9 @@ class FirCcf(Workload):
     alg_bytes, flops, log2n, seed = 16.0, 256.0, 24, 1
     kernel = "fir_tc_kernel"
     ntaps, decim, nsets = 64, 1, 4
+    # profiles/r1_fir_tc_ncu.txt: 134.2 MB read + 84.3 MB written per 2^24-sample launch (part of the output is still in L2)
+    ncu_dram_bytes_per_sample = (134.2e6 + 84.3e6) / (1 << 24)
+    ncu_source = "profiles/r1_fir_tc_ncu.txt"
 
     def setup(self):
         self.taps = lowpass(self.ntaps, 0.1, hamming(self.ntaps))
@@ -209,6 +215,9 @@ class FirLongDecim(FirCcf):
     alg_bytes, flops, log2n, seed = 9.0, 512.0, 27, 4
     kernel = "fir_tc_kernel<M_DEC8>"
     ntaps, decim, nsets = 1024, 8, 1
+    # profiles/r1_firdec_tc_ncu.txt: 1.074 GB read + 128 MB written per 2^27-input-sample launch
+    ncu_dram_bytes_per_sample = (1.0738e9 + 128.07e6) / (1 << 27)
+    ncu_source = "profiles/r1_firdec_tc_ncu.txt"
 
     def setup(self):
         self.taps = lowpass(self.ntaps, 1.0 / 32, blackman_harris(self.ntaps))
@@ -511,8 +520,13 @@ def main():
     kernel_ms = float(np.mean(per)) / wl.launches_per_step  # one dominant kernel per launch, no other work in a step
     alg_bytes_launch = wl.alg_bytes * samples_per_step / wl.launches_per_step
     achieved = alg_bytes_launch / (kernel_ms * 1e-3) / 1e9
+    # DRAM bytes of the dominant kernel per launch: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full`
+    # capture (committed under profiles/), scaled from the captured launch size to this launch's sample count
+    traffic = getattr(wl, "ncu_dram_bytes_per_sample", None)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": wl.kernel, "peak_source": peak_src,
+                "traffic": traffic * samples_per_step / wl.launches_per_step if traffic else None,
+                "traffic_source": getattr(wl, "ncu_source", None),
+                "kernel": wl.kernel, "peak_source": peak_src,
                 "alg_bytes_per_sample": wl.alg_bytes, "alg_flops_per_sample": wl.flops,
                 "fp32_tflops": wl.flops * samples_per_step / wl.launches_per_step / (kernel_ms * 1e-3) / 1e12}
 
