@@ -12,7 +12,7 @@ OK, EINVAL, ERANGE, ECUDA, ENOMEM, EWINDOW = 0, -1, -2, -3, -4, -5
 
 _lib = None
 
-vp, i32, i64, u64, f32 = C.c_void_p, C.c_int, C.c_longlong, C.c_ulonglong, C.c_float
+vp, i32, i64, u64, f32, f64 = C.c_void_p, C.c_int, C.c_longlong, C.c_ulonglong, C.c_float, C.c_double
 pvp = C.POINTER(C.c_void_p)
 
 # name -> (restype, argtypes); every symbol include/grb200.h declares
@@ -36,6 +36,17 @@ SIGNATURES = {
     "grb200_fir_work": (i32, [vp, vp, vp, i64]),
     "grb200_fir_work_dev": (i32, [vp, vp, vp, i64, vp]),
     "grb200_fir_destroy": (None, [vp]),
+    "grb200_freq_xlating_fir_ccf_create": (i32, [i32, vp, i32, f64, f64, i32, pvp]),
+    "grb200_freq_xlating_fir_ccc_create": (i32, [i32, vp, i32, f64, f64, i32, pvp]),
+    "grb200_freq_xlating_fir_set_taps": (i32, [vp, vp, i32]),
+    "grb200_freq_xlating_fir_set_center_freq": (i32, [vp, f64]),
+    "grb200_freq_xlating_fir_center_freq": (f64, [vp]),
+    "grb200_freq_xlating_fir_ntaps": (i32, [vp]),
+    "grb200_freq_xlating_fir_decimation": (i32, [vp]),
+    "grb200_freq_xlating_fir_composite_taps": (i32, [vp, vp, i32]),
+    "grb200_freq_xlating_fir_work": (i32, [vp, vp, vp, i64]),
+    "grb200_freq_xlating_fir_work_dev": (i32, [vp, vp, vp, i64, vp]),
+    "grb200_freq_xlating_fir_destroy": (None, [vp]),
     "grb200_fftfilt_ccc_create": (i32, [i32, vp, i32, i32, pvp]),
     "grb200_fftfilt_set_taps": (i32, [vp, vp, i32]),
     "grb200_fftfilt_ccf_create": (i32, [i32, vp, i32, i32, pvp]),

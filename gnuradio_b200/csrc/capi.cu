@@ -1,6 +1,8 @@
 // capi.cu -- the C-ABI of libgrb200 (include/grb200.h): handles, tap/window preparation, host-staged and
 // device-resident work() entry points.  No compute happens on the host beyond O(ntaps) tap re-layout.
 #include "capi_common.cuh"
+#include <complex>
+#include <cstring>
 
 using namespace grb;
 
@@ -88,6 +90,9 @@ struct grb200_fir {
     int decim = 1;
     int ntaps = 0;
     DevBuf gtaps, rev;
+    // freq_xlating_fir_filter (capi_xlat.cu) drives this handle with a rotator behind the filter: out[n] *= e^{j (theta + n delta)}
+    bool rot = false;
+    double theta = 0.0, delta = 0.0;
     Stager sg;
     std::mutex mu;
 };
@@ -173,8 +178,13 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
     int rc = use_device(h->device);
     if (rc)
         return rc;
-    return fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput,
-                      pick_stream(stream, h->sg));
+    cudaStream_t st = pick_stream(stream, h->sg);
+    rc = fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput, st);
+    if (!rc && h->rot) {
+        rc = rotate_launch(out_dev, noutput, h->theta, h->delta, st);
+        h->theta = rotate_advance(h->theta, h->delta, noutput);
+    }
+    return rc;
 }
 
 int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long long noutput)
@@ -199,7 +209,7 @@ int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long lon
     const char* in = (const char*)in_host;
     char* out = (char*)out_host;
     Stager& sg = h->sg;
-    return sg.run(
+    rc = sg.run(
         nchunks,
         [&](long long c, int slot, Stager::Chunk& ch) {
             const long long o0 = c * chunk, n = std::min(chunk, noutput - o0);
@@ -209,8 +219,14 @@ int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long lon
         },
         [&](long long c, int slot, cudaStream_t st) {
             const long long o0 = c * chunk, n = std::min(chunk, noutput - o0);
-            return fir_launch(h->ct, D, nt, h->gtaps.p, h->rev.p, sg.dev[slot][0], sg.dev[slot][1], n, st);
+            int r2 = fir_launch(h->ct, D, nt, h->gtaps.p, h->rev.p, sg.dev[slot][0], sg.dev[slot][1], n, st);
+            if (!r2 && h->rot)
+                r2 = rotate_launch(sg.dev[slot][1], n, rotate_advance(h->theta, h->delta, o0), h->delta, st);
+            return r2;
         });
+    if (!rc && h->rot)
+        h->theta = rotate_advance(h->theta, h->delta, noutput);
+    return rc;
 }
 
 void grb200_fir_destroy(grb200_fir* h)
@@ -222,6 +238,150 @@ void grb200_fir_destroy(grb200_fir* h)
     h->gtaps.release();
     h->rev.release();
     delete h;
+}
+
+} // extern "C"
+
+// =====================================================================================================
+// freq_xlating_fir_filter_ccf / ccc  (gr-filter/lib/freq_xlating_fir_filter_impl.cc)
+// =====================================================================================================
+// The reference is fir_filter<gr_complex,gr_complex,gr_complex> over composite taps followed by blocks::rotator.
+// Here it is the same FIR handle (so the tcgen05 complex-tap kernel serves it) with the rotator hook switched on.
+struct grb200_xlat {
+    grb200_fir* fir = nullptr;
+    bool cplx_taps = false;
+    std::vector<std::complex<float>> proto;
+    double center_freq = 0.0, sampling_freq = 1.0;
+};
+
+// build_composite_fir(), freq_xlating_fir_filter_impl.cc:74-93, float arithmetic as written there
+static void xlat_composite(const grb200_xlat* x, int decim, std::vector<std::complex<float>>& ctaps, double* delta)
+{
+    const float fwT0 = 2 * M_PI * x->center_freq / x->sampling_freq;
+    ctaps.resize(x->proto.size());
+    for (unsigned int i = 0; i < x->proto.size(); i++) {
+        const std::complex<float> e = std::exp(std::complex<float>(0, i * fwT0));
+        ctaps[i] = x->cplx_taps ? x->proto[i] * e : x->proto[i].real() * e;
+    }
+    // rotator::set_phase_incr (rotator.h:31) normalises the float phasor; the device rotates by its angle
+    std::complex<float> incr = std::exp(std::complex<float>(0, -fwT0 * decim));
+    incr = incr / std::abs(incr);
+    *delta = std::atan2((double)incr.imag(), (double)incr.real());
+}
+
+static void xlat_store_proto(grb200_xlat* x, const float* taps, int ntaps)
+{
+    x->proto.resize(ntaps);
+    for (int i = 0; i < ntaps; i++)
+        x->proto[i] = x->cplx_taps ? std::complex<float>(taps[2 * i], taps[2 * i + 1]) : std::complex<float>(taps[i], 0.f);
+}
+
+static int xlat_create(bool cplx_taps, int decim, const float* taps, int ntaps, double center_freq, double sampling_freq,
+                       int device, grb200_xlat** out)
+{
+    if (!out)
+        return fail(GRB200_EINVAL, "freq_xlating_fir_filter: null output handle");
+    *out = nullptr;
+    if (decim < 1)
+        return fail(GRB200_EINVAL, "freq_xlating_fir_filter: decimation must be >= 1 (got %d)", decim);
+    if (ntaps < 1 || !taps)
+        return fail(GRB200_EINVAL, "freq_xlating_fir_filter: at least one tap is required");
+    if (sampling_freq == 0.0)
+        return fail(GRB200_EINVAL, "freq_xlating_fir_filter: sampling_freq must not be 0");
+    std::unique_ptr<grb200_xlat> x(new grb200_xlat);
+    x->cplx_taps = cplx_taps;
+    x->center_freq = center_freq;
+    x->sampling_freq = sampling_freq;
+    xlat_store_proto(x.get(), taps, ntaps);
+    std::vector<std::complex<float>> ctaps;
+    double delta = 0.0;
+    xlat_composite(x.get(), decim, ctaps, &delta);
+    int rc = fir_create(true, decim, reinterpret_cast<const float*>(ctaps.data()), ntaps, device, &x->fir);
+    if (rc)
+        return rc;
+    x->fir->rot = true;
+    x->fir->delta = delta;
+    *out = x.release();
+    return 0;
+}
+
+static int xlat_rebuild(grb200_xlat* x)
+{
+    std::vector<std::complex<float>> ctaps;
+    double delta = 0.0;
+    xlat_composite(x, x->fir->decim, ctaps, &delta);
+    int rc = grb200_fir_set_taps(x->fir, reinterpret_cast<const float*>(ctaps.data()), (int)ctaps.size());
+    if (rc)
+        return rc;
+    std::lock_guard<std::mutex> lk(x->fir->mu);
+    x->fir->delta = delta; // the phase itself carries on (rotator::set_phase_incr leaves d_phase alone)
+    return 0;
+}
+
+extern "C" {
+
+int grb200_freq_xlating_fir_ccf_create(int decim, const float* taps, int ntaps, double center_freq, double sampling_freq,
+                                       int device, grb200_xlat** out)
+{
+    return xlat_create(false, decim, taps, ntaps, center_freq, sampling_freq, device, out);
+}
+int grb200_freq_xlating_fir_ccc_create(int decim, const float* taps_re_im, int ntaps, double center_freq,
+                                       double sampling_freq, int device, grb200_xlat** out)
+{
+    return xlat_create(true, decim, taps_re_im, ntaps, center_freq, sampling_freq, device, out);
+}
+
+int grb200_freq_xlating_fir_set_taps(grb200_xlat* x, const float* taps, int ntaps)
+{
+    if (!x || !taps || ntaps < 1)
+        return fail(GRB200_EINVAL, "freq_xlating_fir_filter::set_taps: bad arguments");
+    xlat_store_proto(x, taps, ntaps);
+    return xlat_rebuild(x);
+}
+
+int grb200_freq_xlating_fir_set_center_freq(grb200_xlat* x, double center_freq)
+{
+    if (!x)
+        return fail(GRB200_EINVAL, "freq_xlating_fir_filter::set_center_freq: null handle");
+    x->center_freq = center_freq;
+    return xlat_rebuild(x);
+}
+
+double grb200_freq_xlating_fir_center_freq(const grb200_xlat* x) { return x ? x->center_freq : 0.0; }
+int grb200_freq_xlating_fir_ntaps(const grb200_xlat* x) { return x ? grb200_fir_ntaps(x->fir) : 0; }
+int grb200_freq_xlating_fir_decimation(const grb200_xlat* x) { return x ? grb200_fir_decimation(x->fir) : 0; }
+
+int grb200_freq_xlating_fir_composite_taps(const grb200_xlat* x, float* taps_re_im_out, int capacity)
+{
+    if (!x || !taps_re_im_out || capacity < (int)x->proto.size())
+        return fail(GRB200_EINVAL, "freq_xlating_fir_filter::composite_taps: bad arguments");
+    std::vector<std::complex<float>> ctaps;
+    double delta;
+    xlat_composite(x, x->fir->decim, ctaps, &delta);
+    std::memcpy(taps_re_im_out, ctaps.data(), ctaps.size() * sizeof(ctaps[0]));
+    return 0;
+}
+
+int grb200_freq_xlating_fir_work(grb200_xlat* x, const void* in_host, void* out_host, long long noutput)
+{
+    if (!x)
+        return fail(GRB200_EINVAL, "freq_xlating_fir_filter::work: null handle");
+    return grb200_fir_work(x->fir, in_host, out_host, noutput);
+}
+
+int grb200_freq_xlating_fir_work_dev(grb200_xlat* x, const void* in_dev, void* out_dev, long long noutput, void* stream)
+{
+    if (!x)
+        return fail(GRB200_EINVAL, "freq_xlating_fir_filter::work_dev: null handle");
+    return grb200_fir_work_dev(x->fir, in_dev, out_dev, noutput, stream);
+}
+
+void grb200_freq_xlating_fir_destroy(grb200_xlat* x)
+{
+    if (!x)
+        return;
+    grb200_fir_destroy(x->fir);
+    delete x;
 }
 
 } // extern "C"

@@ -11,6 +11,9 @@ namespace grb {
 int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, const void* in, void* out,
                long long nout, cudaStream_t st);
 int fir_upad(int D, int ntaps);
+// rotator behind freq_xlating_fir_filter: y[n] *= e^{j (theta + n delta)} in place (fir.cu); angle bookkeeping on the host
+int rotate_launch(void* y, long long n, double theta, double delta, cudaStream_t st);
+double rotate_advance(double theta, double delta, long long n);
 bool fft_size_is_fast(int N);
 int fft_direct_max();
 int fft_vcc_launch(int N, bool fwd, const void* in, void* out, long long nvec, const float* window, int shift,

@@ -18,6 +18,7 @@
 // per-warp shared staging area (no CTA barrier) so the global stores are coalesced.
 #include <cstdint>
 #include <cstdlib>
+#include <cmath>
 #include "common.cuh"
 
 namespace grb {
@@ -733,6 +734,43 @@ int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, co
                                                                (const float*)rev);
     GRB_LAUNCH_CHECK();
     return 0;
+}
+
+// ---- rotator (gr-blocks/include/gnuradio/blocks/rotator.h:33-53 behind freq_xlating_fir_filter_impl::work :168-178) ----
+// The reference multiplies by a float phasor that it advances by complex multiplication (renormalised every 512 items):
+// phase_n = incr^n up to a rounding random walk.  The device evaluates the closed form: angle in float64, reduced to
+// [-pi, pi], then sincosf -- no state in the kernel, any chunking gives the same output.
+__global__ void __launch_bounds__(256) rotate_kernel(float2* __restrict__ y, long long n, double theta, double delta)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    const double two_pi = 6.283185307179586476925286766559;
+    double a = fma((double)i, delta, theta);
+    a -= two_pi * rint(a / two_pi);
+    float sn, cs;
+    sincosf((float)a, &sn, &cs);
+    const float2 v = y[i];
+    y[i] = make_float2(v.x * cs - v.y * sn, v.x * sn + v.y * cs);
+}
+
+int rotate_launch(void* y, long long n, double theta, double delta, cudaStream_t st)
+{
+    if (n <= 0)
+        return 0;
+    const long long nblk = (n + 255) / 256;
+    if (nblk > 0x7fffffffLL)
+        return fail(GRB200_ERANGE, "rotator: too many items");
+    rotate_kernel<<<(unsigned)nblk, 256, 0, st>>>((float2*)y, n, theta, delta);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+double rotate_advance(double theta, double delta, long long n)
+{
+    const double two_pi = 6.283185307179586476925286766559;
+    double a = theta + (double)n * delta;
+    return a - two_pi * std::rint(a / two_pi);
 }
 
 int fir_upad(int D, int ntaps)

@@ -83,6 +83,35 @@ long long grbx_fir_run(int complex_taps, int decim, const float* taps, int ntaps
     });
 }
 
+// freq_xlating_fir_filter_ccf/ccc: starts at center_freq 0 and retunes through set_center_freq() before the first item,
+// so the deferred rebuild (work() returns 0 once) is on the tested path
+long long grbx_freq_xlating_run(int complex_taps, int decim, const float* taps, int ntaps, double center_freq,
+                                double sampling_freq, const void* in, void* out, long long nout, int chunk)
+{
+    return guarded([&]() -> long long {
+        gr_vector_const_void_star ii(1, in);
+        gr_vector_void_star oo(1, out);
+        if (complex_taps) {
+            std::vector<gr_complex> t((const gr_complex*)taps, (const gr_complex*)taps + ntaps);
+            auto b = gr::filter::freq_xlating_fir_filter_ccc::make(decim, t, 0.0, sampling_freq);
+            b->set_center_freq(center_freq);
+            if (b->history() != (unsigned)ntaps || b->taps() != t || b->center_freq() != center_freq)
+                throw std::logic_error("freq_xlating_fir_filter_ccc: accessor mismatch");
+            if (b->work(1, ii, oo) != 0)
+                throw std::logic_error("freq_xlating_fir_filter_ccc: work() after set_center_freq() must return 0 once");
+            return run_sync(*b, (const char*)in, (char*)out, nout, chunk, 8, 8);
+        }
+        std::vector<float> t(taps, taps + ntaps);
+        auto b = gr::filter::freq_xlating_fir_filter_ccf::make(decim, t, 0.0, sampling_freq);
+        b->set_center_freq(center_freq);
+        if (b->history() != (unsigned)ntaps || b->taps() != t || b->center_freq() != center_freq)
+            throw std::logic_error("freq_xlating_fir_filter_ccf: accessor mismatch");
+        if (b->work(1, ii, oo) != 0)
+            throw std::logic_error("freq_xlating_fir_filter_ccf: work() after set_center_freq() must return 0 once");
+        return run_sync(*b, (const char*)in, (char*)out, nout, chunk, 8, 8);
+    });
+}
+
 long long grbx_fft_filter_run(int decim, const float* taps_re_im, int ntaps, const void* in, void* out, long long nout,
                               int chunk, int* nsamples)
 {

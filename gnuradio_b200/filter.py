@@ -2,6 +2,8 @@
 
   fir_filter_ccf / fir_filter_ccc   gr-filter/include/gnuradio/filter/fir_filter_blk.h:46-68,
                                     gr-filter/lib/fir_filter_blk_impl.cc:22-90
+  freq_xlating_fir_filter_ccf/ccc   gr-filter/include/gnuradio/filter/freq_xlating_fir_filter.h:56-90,
+                                    gr-filter/lib/freq_xlating_fir_filter_impl.cc:26-180
   fft_filter_ccc                    gr-filter/include/gnuradio/filter/fft_filter_ccc.h:43-70,
                                     gr-filter/lib/fft_filter_ccc_impl.cc:22-78
   pfb_channelizer_ccf               gr-filter/include/gnuradio/filter/pfb_channelizer_ccf.h:100-192,
@@ -109,6 +111,132 @@ class fir_filter_ccf(_fir_filter_blk):
 class fir_filter_ccc(_fir_filter_blk):
     _complex_taps = True
     _name = "fir_filter_ccc"
+
+
+class _freq_xlating_fir_filter(sync_decimator):
+    """freq_xlating_fir_filter: band-pass FIR (prototype taps moved up to center_freq), decimate, derotate.
+
+    set_taps()/set_center_freq() only mark the block (freq_xlating_fir_filter_impl.cc:96-113); the next work()
+    rebuilds the composite taps and returns 0 (:155-160).  The rotator phase runs on across work() calls."""
+    _complex_taps = False
+    _name = "freq_xlating_fir_filter"
+
+    def __init__(self, decimation, taps, center_freq, sampling_freq, device=0):
+        L = _lib.lib()
+        if int(decimation) < 1:
+            raise ValueError("freq_xlating_fir_filter: decimation must be >= 1")
+        sync_decimator.__init__(self, self._name, io_signature.make(1, 1, 8), io_signature.make(1, 1, 8), decimation)
+        self._device = int(device)
+        self._h = C.c_void_p()
+        t = self._conv_taps(taps)
+        create = L.grb200_freq_xlating_fir_ccc_create if self._complex_taps else L.grb200_freq_xlating_fir_ccf_create
+        _lib.check(create(int(decimation), _ptr(t), len(t), float(center_freq), float(sampling_freq), self._device,
+                          C.byref(self._h)))
+        self._proto_taps = t.copy()
+        self._center_freq = float(center_freq)
+        self._sampling_freq = float(sampling_freq)
+        self.d_updated = False
+        self.set_history(len(t))  # freq_xlating_fir_filter_impl.cc:53
+
+    @classmethod
+    def make(cls, decimation, taps, center_freq, sampling_freq, device=0):
+        return cls(decimation, taps, center_freq, sampling_freq, device)
+
+    def _conv_taps(self, taps):
+        t = np.ascontiguousarray(taps, np.complex64 if self._complex_taps else np.float32)
+        if t.ndim != 1 or t.size < 1:
+            raise ValueError("freq_xlating_fir_filter: at least one tap is required")
+        return t
+
+    def set_center_freq(self, center_freq):
+        self._center_freq = float(center_freq)
+        self.d_updated = True
+
+    def center_freq(self):
+        return self._center_freq
+
+    def set_taps(self, taps):
+        self._proto_taps = self._conv_taps(taps).copy()
+        self.d_updated = True
+
+    def taps(self):
+        return self._proto_taps.tolist()
+
+    def handle_set_center_freq(self, msg):
+        """The "freq" message port (freq_xlating_fir_filter_impl.cc:121-141): a dict with key "freq" or a
+        (key, value) pair; anything else is ignored."""
+        if isinstance(msg, dict):
+            v = msg.get("freq")
+        elif isinstance(msg, tuple) and len(msg) == 2:
+            v = msg[1]
+        else:
+            return
+        if isinstance(v, (int, float)) and not isinstance(v, bool):
+            self.set_center_freq(float(v))
+
+    def composite_taps(self):
+        t = np.empty(len(self._proto_taps), np.complex64)
+        _lib.check(_lib.lib().grb200_freq_xlating_fir_composite_taps(self._h, _ptr(t), len(t)))
+        return t
+
+    def _rebuild(self):
+        L = _lib.lib()
+        # the library rebuilds on each call; push the frequency first so one rebuild sees both new values
+        if len(self._proto_taps) == L.grb200_freq_xlating_fir_ntaps(self._h):
+            _lib.check(L.grb200_freq_xlating_fir_set_center_freq(self._h, self._center_freq))
+            _lib.check(L.grb200_freq_xlating_fir_set_taps(self._h, _ptr(self._proto_taps), len(self._proto_taps)))
+        else:
+            _lib.check(L.grb200_freq_xlating_fir_set_taps(self._h, _ptr(self._proto_taps), len(self._proto_taps)))
+            _lib.check(L.grb200_freq_xlating_fir_set_center_freq(self._h, self._center_freq))
+
+    def work(self, noutput_items, input_items, output_items):
+        if self.d_updated:  # freq_xlating_fir_filter_impl.cc:155-160
+            self.set_history(len(self._proto_taps))
+            self._rebuild()
+            self.d_updated = False
+            return 0
+        n = int(noutput_items)
+        need = n * self.decimation() + len(self._proto_taps) - 1
+        xin = as_items(input_items[0], _c64, need if n else 0, "input_items[0]")
+        out = as_items(output_items[0], _c64, n, "output_items[0]")
+        _lib.check(_lib.lib().grb200_freq_xlating_fir_work(self._h, _ptr(xin), _ptr(out), n))
+        return n
+
+    def work_dev(self, in_dev, out_dev, noutput_items, stream=0):
+        """Device-resident mode: in_dev/out_dev are device addresses; asynchronous on `stream`."""
+        if self.d_updated:
+            self._rebuild()
+            self.d_updated = False
+        _lib.check(_lib.lib().grb200_freq_xlating_fir_work_dev(self._h, C.c_void_p(in_dev), C.c_void_p(out_dev),
+                                                               int(noutput_items), C.c_void_p(stream)))
+        return int(noutput_items)
+
+    def process(self, xin, noutput_items):
+        """Convenience: one work() call on `xin` (history items first); returns the output array."""
+        xin = np.ascontiguousarray(xin, np.complex64)
+        out = np.empty(int(noutput_items), np.complex64)
+        if self.d_updated:
+            self.work(0, [xin], [out])
+        r = self.work(noutput_items, [xin], [out])
+        return out[:r]
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().grb200_freq_xlating_fir_destroy(h)
+            except Exception:
+                pass
+
+
+class freq_xlating_fir_filter_ccf(_freq_xlating_fir_filter):
+    _complex_taps = False
+    _name = "freq_xlating_fir_filter_ccf"
+
+
+class freq_xlating_fir_filter_ccc(_freq_xlating_fir_filter):
+    _complex_taps = True
+    _name = "freq_xlating_fir_filter_ccc"
 
 
 class fft_filter_ccc(sync_decimator):

@@ -71,6 +71,32 @@ int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long lon
 int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long long noutput, void* stream);
 void grb200_fir_destroy(grb200_fir* h);
 
+/* ---- freq_xlating_fir_filter_ccf / freq_xlating_fir_filter_ccc ----------------------------------
+ * Replaces gr::filter::freq_xlating_fir_filter_impl<gr_complex,gr_complex,float|gr_complex>
+ *   build_composite_fir  gr-filter/lib/freq_xlating_fir_filter_impl.cc:74-93
+ *       ctaps[i] = taps[i] * exp(j i fwT0), float fwT0 = 2 pi center_freq / sampling_freq;
+ *       rotator increment exp(-j fwT0 decimation)
+ *   work                 gr-filter/lib/freq_xlating_fir_filter_impl.cc:143-180
+ *       out[i] = composite_fir.filter(&in[i*decimation]);  rotator.rotateN(out, out, noutput)
+ *   rotator              gr-blocks/include/gnuradio/blocks/rotator.h:33-53
+ * Same buffer convention as fir_filter (history = ntaps).  set_taps / set_center_freq rebuild the composite taps at
+ * once; the rotator phase carries on across calls and across rebuilds as in the reference.  The block mirrors above
+ * this ABI keep the reference's "return 0 from the work() that sees d_updated" behaviour. */
+typedef struct grb200_xlat grb200_xlat;
+int grb200_freq_xlating_fir_ccf_create(int decim, const float* taps, int ntaps, double center_freq, double sampling_freq,
+                                       int device, grb200_xlat** out);
+int grb200_freq_xlating_fir_ccc_create(int decim, const float* taps_re_im, int ntaps, double center_freq,
+                                       double sampling_freq, int device, grb200_xlat** out);
+int grb200_freq_xlating_fir_set_taps(grb200_xlat* h, const float* taps, int ntaps); /* re/im pairs for ccc */
+int grb200_freq_xlating_fir_set_center_freq(grb200_xlat* h, double center_freq);
+double grb200_freq_xlating_fir_center_freq(const grb200_xlat* h);
+int grb200_freq_xlating_fir_ntaps(const grb200_xlat* h);
+int grb200_freq_xlating_fir_decimation(const grb200_xlat* h);
+int grb200_freq_xlating_fir_composite_taps(const grb200_xlat* h, float* taps_re_im_out, int capacity);
+int grb200_freq_xlating_fir_work(grb200_xlat* h, const void* in_host, void* out_host, long long noutput);
+int grb200_freq_xlating_fir_work_dev(grb200_xlat* h, const void* in_dev, void* out_dev, long long noutput, void* stream);
+void grb200_freq_xlating_fir_destroy(grb200_xlat* h);
+
 /* ---- fft_filter_ccc ----------------------------------------------------------------------------
  * Replaces gr::filter::kernel::fft_filter_ccc
  *   compute_sizes  gr-filter/lib/fft_filter.cc:204-224   (fftsize = 2*2^ceil(log2 ntaps), nsamples = fftsize-ntaps+1)

@@ -215,6 +215,81 @@ typedef fir_filter_blk<gr_complex, gr_complex, float> fir_filter_ccf;
 typedef fir_filter_blk<gr_complex, gr_complex, gr_complex> fir_filter_ccc;
 
 // ---------------------------------------------------------------------------------------------------
+// freq_xlating_fir_filter<gr_complex, gr_complex, float|gr_complex>  (freq_xlating_fir_filter_ccf / _ccc)
+// gr-filter/include/gnuradio/filter/freq_xlating_fir_filter.h:56-90, lib/freq_xlating_fir_filter_impl.cc
+// ---------------------------------------------------------------------------------------------------
+template <class IN_T, class OUT_T, class TAP_T>
+class freq_xlating_fir_filter : public grb200::rt::sync_decimator
+{
+    static_assert(std::is_same<IN_T, gr_complex>::value && std::is_same<OUT_T, gr_complex>::value &&
+                      (std::is_same<TAP_T, float>::value || std::is_same<TAP_T, gr_complex>::value),
+                  "libgrb200 re-hosts the ccf and ccc instantiations (SURVEY.md section 8)");
+
+public:
+    typedef std::shared_ptr<freq_xlating_fir_filter<IN_T, OUT_T, TAP_T>> sptr;
+
+    static sptr make(int decimation, const std::vector<TAP_T>& taps, double center_freq, double sampling_freq)
+    {
+        return sptr(new freq_xlating_fir_filter<IN_T, OUT_T, TAP_T>(decimation, taps, center_freq, sampling_freq));
+    }
+
+    ~freq_xlating_fir_filter() override { grb200_freq_xlating_fir_destroy(d_h); }
+
+    void set_center_freq(double center_freq) // freq_xlating_fir_filter_impl.cc:96-100: picked up by the next work()
+    {
+        d_center_freq = center_freq;
+        d_updated = true;
+    }
+    double center_freq() const { return d_center_freq; }
+
+    void set_taps(const std::vector<TAP_T>& taps) // :109-113
+    {
+        d_proto_taps = taps;
+        d_updated = true;
+    }
+    std::vector<TAP_T> taps() const { return d_proto_taps; }
+
+    int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
+    {
+        if (d_updated) { // :155-160: rebuild composite FIR, history requirements may have changed
+            set_history(d_proto_taps.size());
+            grb200::check(grb200_freq_xlating_fir_set_center_freq(d_h, d_center_freq));
+            grb200::check(grb200_freq_xlating_fir_set_taps(
+                d_h, reinterpret_cast<const float*>(d_proto_taps.data()), (int)d_proto_taps.size()));
+            d_updated = false;
+            return 0;
+        }
+        grb200::check(grb200_freq_xlating_fir_work(d_h, input_items[0], output_items[0], noutput_items));
+        return noutput_items;
+    }
+
+    grb200_xlat* handle() { return d_h; } // device-resident chaining (grb200_freq_xlating_fir_work_dev)
+
+private:
+    freq_xlating_fir_filter(int decimation, const std::vector<TAP_T>& taps, double center_freq, double sampling_freq)
+        : sync_decimator(std::is_same<TAP_T, float>::value ? "freq_xlating_fir_filter_ccf" : "freq_xlating_fir_filter_ccc",
+                         grb200::rt::io_signature::make(1, 1, sizeof(IN_T)),
+                         grb200::rt::io_signature::make(1, 1, sizeof(OUT_T)), decimation),
+          d_proto_taps(taps), d_center_freq(center_freq)
+    {
+        const float* t = reinterpret_cast<const float*>(taps.data());
+        if (std::is_same<TAP_T, float>::value)
+            grb200::check(grb200_freq_xlating_fir_ccf_create(decimation, t, (int)taps.size(), center_freq, sampling_freq,
+                                                             grb200::default_device(), &d_h));
+        else
+            grb200::check(grb200_freq_xlating_fir_ccc_create(decimation, t, (int)taps.size(), center_freq, sampling_freq,
+                                                             grb200::default_device(), &d_h));
+        set_history(taps.size()); // freq_xlating_fir_filter_impl.cc:53
+    }
+    grb200_xlat* d_h = nullptr;
+    std::vector<TAP_T> d_proto_taps;
+    double d_center_freq;
+    bool d_updated = false;
+};
+typedef freq_xlating_fir_filter<gr_complex, gr_complex, float> freq_xlating_fir_filter_ccf;
+typedef freq_xlating_fir_filter<gr_complex, gr_complex, gr_complex> freq_xlating_fir_filter_ccc;
+
+// ---------------------------------------------------------------------------------------------------
 // fft_filter_ccc
 // ---------------------------------------------------------------------------------------------------
 class fft_filter_ccc : public grb200::rt::sync_decimator

@@ -72,6 +72,80 @@ int grbo_fir_ccc(int decim, const cf32* taps, int ntaps, const cf32* in, cf32* o
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * freq_xlating_fir_filter_impl<gr_complex,gr_complex,float|gr_complex>
+ * (gr-filter/lib/freq_xlating_fir_filter_impl.cc): build_composite_fir :74-93 -- float fwT0, composite taps
+ * taps[i] * e^{j i fwT0}, rotator increment e^{-j fwT0 decim} normalised (rotator.h:31); work :143-180 -- composite
+ * FIR then rotator.rotateN, i.e. VOLK's generic rotator: z = in * phase; phase *= incr; phase /= |phase| after every
+ * 512 items and at the end of each call.  work() is driven `chunk_out` outputs at a time like the scheduler does.
+ * phase_io = rotator phase in/out ({1,0} for a fresh block).
+ * ---------------------------------------------------------------------------------------------- */
+static void rot_norm(cf32* p)
+{
+    const float m = hypotf(p->re, p->im);
+    p->re /= m;
+    p->im /= m;
+}
+
+int grbo_freq_xlating_fir(int cplx_taps, int decim, const float* taps, int ntaps, double center_freq,
+                          double sampling_freq, const cf32* in, cf32* out, long nout, long chunk_out, float* phase_io)
+{
+    cf32* ct = (cf32*)malloc(sizeof(cf32) * (size_t)ntaps);
+    if (!ct)
+        return -1;
+    const float fwT0 = (float)(2 * PI_D * center_freq / sampling_freq);
+    for (unsigned int i = 0; i < (unsigned int)ntaps; i++) {
+        const float a = (float)i * fwT0, c = cosf(a), sn = sinf(a);
+        if (cplx_taps) {
+            const float tr = taps[2 * i], ti = taps[2 * i + 1];
+            ct[i].re = tr * c - ti * sn;
+            ct[i].im = tr * sn + ti * c;
+        } else {
+            ct[i].re = taps[i] * c;
+            ct[i].im = taps[i] * sn;
+        }
+    }
+    cf32 incr, ph = { 1.0f, 0.0f };
+    {
+        const float a = -fwT0 * (float)decim;
+        incr.re = cosf(a);
+        incr.im = sinf(a);
+        const float m = hypotf(incr.re, incr.im); /* std::abs(complex<float>) */
+        incr.re /= m;
+        incr.im /= m;
+    }
+    if (phase_io) {
+        ph.re = phase_io[0];
+        ph.im = phase_io[1];
+        rot_norm(&ph); /* rotator::set_phase */
+    }
+    if (chunk_out < 1)
+        chunk_out = nout > 0 ? nout : 1;
+    for (long o0 = 0; o0 < nout; o0 += chunk_out) {
+        const long n = (nout - o0 < chunk_out) ? nout - o0 : chunk_out;
+        grbo_fir_ccc(decim, ct, ntaps, in + o0 * decim, out + o0, n);
+        long i = 0;
+        for (; i < n; i++) {
+            const cf32 z = out[o0 + i];
+            out[o0 + i].re = z.re * ph.re - z.im * ph.im;
+            out[o0 + i].im = z.re * ph.im + z.im * ph.re;
+            const cf32 q = ph;
+            ph.re = q.re * incr.re - q.im * incr.im;
+            ph.im = q.re * incr.im + q.im * incr.re;
+            if (((i + 1) & 511) == 0)
+                rot_norm(&ph);
+        }
+        if (n & 511)
+            rot_norm(&ph);
+    }
+    if (phase_io) {
+        phase_io[0] = ph.re;
+        phase_io[1] = ph.im;
+    }
+    free(ct);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
  * FFT: gr::fft::fft_complex (gr-fft/lib/fft.cc:151-203): unnormalised, forward = e^{-j...},
  * backward = e^{+j...}.  Power-of-two sizes: Stockham radix-2 in float; otherwise a direct DFT
  * accumulated in double.

@@ -91,6 +91,24 @@ class _CLib:
         xin = np.concatenate([np.zeros(ntaps - 1, np.complex64), _c64(x)])
         return self.fir(decim, taps, xin, len(x) // decim)
 
+    # -- freq_xlating_fir_filter_ccf / ccc -----------------------------------------------------------
+    def freq_xlating_fir(self, decim, taps, center_freq, sampling_freq, xin, nout, chunk_out=0, phase=None):
+        """work() over xin (ntaps-1 history items in front), `chunk_out` outputs per call (0 = one call).
+        Returns (out, phase) with phase the rotator state after the run (complex64)."""
+        taps = np.ascontiguousarray(taps)
+        xin = _headroom(xin)
+        ntaps = len(taps)
+        assert len(xin) >= nout * decim + ntaps - 1
+        cplx = bool(np.iscomplexobj(taps))
+        t = _c64(taps) if cplx else np.ascontiguousarray(taps, np.float32)
+        out = np.empty(nout, np.complex64)
+        ph = np.array([1.0, 0.0] if phase is None else [np.real(phase), np.imag(phase)], np.float32)
+        rc = self._f("freq_xlating_fir")(int(cplx), int(decim), _p(t), ntaps, C.c_double(center_freq),
+                                          C.c_double(sampling_freq), _p(xin), _p(out), C.c_long(nout),
+                                          C.c_long(chunk_out), _p(ph))
+        assert rc == 0
+        return out, np.complex64(complex(ph[0], ph[1]))
+
     # -- fft_filter_ccc ---------------------------------------------------------------------------
     def fft_filter_nsamples(self, ntaps):
         return int(self._f("fft_filter_nsamples")(int(ntaps)))
@@ -230,6 +248,35 @@ def f64_fir(decim, taps, x):
     t = np.asarray(taps, np.complex128 if np.iscomplexobj(taps) else np.float64)
     n = (len(x) // decim)
     return np.convolve(x, t)[: n * decim: decim][:n]
+
+
+_libm = None
+
+
+def xlat_increment_angle(fwT0, decim):
+    """Angle of the float phasor exp(gr_complex(0, -fwT0*decim)) the rotator steps by (:92, rotator.h:31).  One ulp of
+    its cosf/sinf moves the angle by ~6e-8 rad per item -- 2e-4 rad over 4000 items -- so the C library's own
+    cosf/sinf are called here rather than numpy's float32 kernels, which may round differently."""
+    global _libm
+    if _libm is None:
+        _libm = C.CDLL("libm.so.6")
+        for f in (_libm.cosf, _libm.sinf):
+            f.restype, f.argtypes = C.c_float, [C.c_float]
+    a = np.float32(-np.float32(fwT0) * np.float32(decim))
+    return float(np.arctan2(float(_libm.sinf(C.c_float(a))), float(_libm.cosf(C.c_float(a)))))
+
+
+def f64_freq_xlating_fir(decim, taps, center_freq, sampling_freq, x, n0=0):
+    """Closed form in float64 over the float32 quantities the block derives (freq_xlating_fir_filter_impl.cc:85-92):
+    y[n] = e^{j delta (n0+n)} sum_k taps[k] e^{j k fwT0} x[nD-k], with float fwT0 and delta the angle of the float
+    rotator increment exp(-j fwT0 D) the block really steps by (xlat_increment_angle).  Same quantity as the expected_result of
+    gr-filter/python/filter/qa_freq_xlating_fir_filter.py:96-127 (mix down, filter, decimate)."""
+    fwT0 = np.float32(2 * np.pi * center_freq / sampling_freq)
+    arg = np.arange(len(taps), dtype=np.float32) * fwT0  # float product as in :87; it defines the composite taps
+    t = np.asarray(taps, np.complex128) * np.exp(1j * arg.astype(np.float64))
+    y = f64_fir(decim, t, x)
+    delta = xlat_increment_angle(fwT0, decim)
+    return y * np.exp(1j * delta * (n0 + np.arange(len(y))))
 
 
 def f64_fft_filter(decim, taps, x, nsamples):

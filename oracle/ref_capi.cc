@@ -8,13 +8,16 @@
  * restated below next to the reference file:line each loop follows.  Third-party arithmetic comes
  * from oracle/shim (generic-C VOLK stand-ins, own FFT engine in place of FFTW3f).
  */
+#include <gnuradio/blocks/rotator.h>
 #include <gnuradio/fft/fft.h>
 #include <gnuradio/fft/window.h>
 #include <gnuradio/filter/fft_filter.h>
 #include <gnuradio/filter/fir_filter.h>
 #include <gnuradio/filter/firdes.h>
 #include <gnuradio/filter/polyphase_filterbank.h>
+#include <gnuradio/math.h>
 #include <volk/volk.h>
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <stdexcept>
@@ -123,6 +126,50 @@ int grref_fir_ccc(int decim, const void* taps, int ntaps, const void* in, void* 
         fir.filterN((gr_complex*)out, (const gr_complex*)in, (unsigned long)nout);
     else
         fir.filterNdec((gr_complex*)out, (const gr_complex*)in, (unsigned long)nout, decim);
+    return 0;
+}
+
+/* freq_xlating_fir_filter_impl<gr_complex,gr_complex,float|gr_complex> (gr-filter/lib/freq_xlating_fir_filter_impl.cc):
+ * the block class needs the runtime, so build_composite_fir() (:74-93) and work() (:143-180) are restated here over
+ * the reference's OWN fir_filter_ccc kernel and its OWN blocks::rotator (header-only, rotator.h).  work() is driven
+ * like the scheduler does, `chunk_out` output items per call (the rotator renormalises at the end of each call).
+ * phase_io (re, im) carries the rotator phase in and out; pass {1, 0} for a fresh block. */
+int grref_freq_xlating_fir(int cplx_taps, int decim, const float* taps, int ntaps, double center_freq,
+                           double sampling_freq, const void* in, void* out, long nout, long chunk_out, float* phase_io)
+{
+    std::vector<gr_complex> ctaps(ntaps);
+    float fwT0 = 2 * GR_M_PI * center_freq / sampling_freq;
+    for (unsigned int i = 0; i < (unsigned int)ntaps; i++) {
+        if (cplx_taps)
+            ctaps[i] = gr_complex(taps[2 * i], taps[2 * i + 1]) * exp(gr_complex(0, i * fwT0));
+        else
+            ctaps[i] = taps[i] * exp(gr_complex(0, i * fwT0));
+    }
+    fir_filter_ccc fir(decim, ctaps);
+    gr::blocks::rotator r;
+    if (phase_io)
+        r.set_phase(gr_complex(phase_io[0], phase_io[1]));
+    r.set_phase_incr(exp(gr_complex(0, -fwT0 * decim)));
+    const gr_complex* x = (const gr_complex*)in;
+    gr_complex* y = (gr_complex*)out;
+    if (chunk_out < 1)
+        chunk_out = nout > 0 ? nout : 1;
+    for (long o0 = 0; o0 < nout; o0 += chunk_out) {
+        const long n = std::min(chunk_out, nout - o0);
+        if (decim == 1)
+            fir.filterN(y + o0, x + o0, (unsigned long)n);
+        else
+            fir.filterNdec(y + o0, x + o0 * decim, (unsigned long)n, decim);
+        r.rotateN(y + o0, y + o0, (int)n);
+    }
+    if (phase_io) {
+        /* rotator keeps d_phase private; one zero-free probe item reads it back without advancing past it */
+        gr_complex one(1.f, 0.f), ph;
+        gr::blocks::rotator probe = r;
+        ph = probe.rotate(one);
+        phase_io[0] = ph.real();
+        phase_io[1] = ph.imag();
+    }
     return 0;
 }
 

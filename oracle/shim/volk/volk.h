@@ -6,7 +6,8 @@
  * this is what the reference's QA pins, because its tests run with VOLK_GENERIC=1
  * (/root/reference/cmake/Modules/GrTest.cmake:64).  GCC auto-vectorises the loops at -O3.
  * Only the entry points the hot path calls are provided (call sites:
- * gr-filter/lib/fir_filter.cc:129-182, gr-filter/lib/fft_filter.cc:128,259,393).
+ * gr-filter/lib/fir_filter.cc:129-182, gr-filter/lib/fft_filter.cc:128,259,393,
+ * gr-blocks/include/gnuradio/blocks/rotator.h:52).
  */
 #ifndef GRB200_ORACLE_SHIM_VOLK_H
 #define GRB200_ORACLE_SHIM_VOLK_H
@@ -135,6 +136,31 @@ volk_32fc_magnitude_squared_32f(float* out, const lv_32fc_t* in, unsigned int n)
     const float* x = reinterpret_cast<const float*>(in);
     for (unsigned int i = 0; i < n; i++)
         out[i] = x[2 * i] * x[2 * i] + x[2 * i + 1] * x[2 * i + 1];
+}
+
+/* out[i] = in[i] * phase; phase *= phase_inc; renormalised every 512 items and at the end of every call
+ * (VOLK's published generic kernel volk_32fc_s32fc_x2_rotator_32fc, ROTATOR_RELOAD = 512; call site
+ * gr-blocks/include/gnuradio/blocks/rotator.h:50-53) */
+static inline void volk_32fc_s32fc_x2_rotator_32fc(lv_32fc_t* out,
+                                                   const lv_32fc_t* in,
+                                                   const lv_32fc_t phase_inc,
+                                                   lv_32fc_t* phase,
+                                                   unsigned int n)
+{
+    unsigned int i = 0;
+    for (unsigned int b = 0; b < n / 512; b++) {
+        for (int j = 0; j < 512; j++) {
+            *out++ = *in++ * (*phase);
+            (*phase) *= phase_inc;
+        }
+        (*phase) /= hypotf(phase->real(), phase->imag());
+    }
+    for (i = 0; i < n % 512; i++) {
+        *out++ = *in++ * (*phase);
+        (*phase) *= phase_inc;
+    }
+    if (i)
+        (*phase) /= hypotf(phase->real(), phase->imag());
 }
 
 #endif

@@ -118,11 +118,30 @@ def ref_fixtures():
     for fwd in (0, 1):
         fx["vcc15_f%d_s1" % fwd] = R.fft_vcc(15, fwd, None, 1, fx["vcc_x15"])
     fx["magsq"] = R.mag_squared(fx["vcc_x"])
+    # ---- freq_xlating_fir_filter_ccf / ccc (own generator: the arrays above stay bit-identical) ----
+    rng2 = np.random.default_rng(20261105)
+    fx["xlat_x"] = crand(rng2, 4000)
+    fx["xlat_taps_f"] = rng2.uniform(-1, 1, 48).astype(np.float32)
+    fx["xlat_taps_c"] = crand(rng2, 33)
+    fx["xlat_meta"] = np.array([0.3, 1.0, 1100], np.float64)  # center_freq, sampling_freq, scheduler-like chunk
+    for D in (1, 4):
+        for tag in ("f", "c"):
+            t = fx["xlat_taps_" + tag]
+            xin = np.concatenate([np.zeros(len(t) - 1, np.complex64), fx["xlat_x"]])
+            y, ph = R.freq_xlating_fir(D, t, 0.3, 1.0, xin, len(fx["xlat_x"]) // D, chunk_out=1100 // D)
+            fx["xlat_cc%s_d%d" % (tag, D)] = y
+            fx["xlat_cc%s_d%d_phase" % (tag, D)] = np.complex64(ph)
     return fx
 
 
 if __name__ == "__main__":
     json.dump(lift_qa_vectors(), open(os.path.join(HERE, "qa_vectors.json"), "w"), indent=0)
     fx = ref_fixtures()
+    path = os.path.join(HERE, "ref_fixtures.npz")
+    if os.path.exists(path) and "--all" not in sys.argv:
+        # arrays already committed are kept as they are (the reference's auto-vectorised float loops may differ in
+        # the last bit between builds); only new keys are added.  --all regenerates everything.
+        old = dict(np.load(path))
+        fx = {k: old.get(k, v) for k, v in fx.items()}
     np.savez_compressed(os.path.join(HERE, "ref_fixtures.npz"), **fx)
     print("wrote", len(fx), "arrays,", os.path.getsize(os.path.join(HERE, "ref_fixtures.npz")), "bytes")

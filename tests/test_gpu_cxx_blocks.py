@@ -16,7 +16,7 @@ LL = C.c_longlong
 @pytest.fixture(scope="module")
 def drv():
     lib = C.CDLL(os.path.join(ROOT, "gnuradio_b200", "cxx", "libgrb200_blocks.so"))
-    for f in ("grbx_fir_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run"):
+    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run"):
         getattr(lib, f).restype = LL
     lib.grbx_what.restype = C.c_char_p
     return lib
@@ -38,6 +38,24 @@ def test_cxx_fir(drv, orc):
         assert rc == nout, drv.grbx_what()
         assert_parity(out, orc.fir(D, taps, xin, nout), "c++ fir ct=%d %d/%d" % (ct, nt, D))
     rc = drv.grbx_fir_run(0, 0, p(taps), 4, p(xin), p(out), LL(10), 4096, 0)
+    assert rc == -1  # std::invalid_argument
+
+
+def test_cxx_freq_xlating(drv, orc):
+    rng = np.random.default_rng(6)
+    for ct, nt, D in ((0, 64, 1), (1, 33, 4)):
+        nout = 4000
+        x = crand(rng, nout * D)
+        taps = crand(rng, nt) if ct else rng.uniform(-1, 1, nt).astype(np.float32)
+        xin = np.concatenate([np.zeros(nt - 1, np.complex64), x])
+        out = np.zeros(nout, np.complex64)
+        rc = drv.grbx_freq_xlating_run(ct, D, p(taps), nt, C.c_double(-3e3), C.c_double(48e3), p(xin), p(out), LL(nout), 1024)
+        assert rc == nout, drv.grbx_what()
+        ref, _ = orc.freq_xlating_fir(D, taps, -3e3, 48e3, xin, nout, chunk_out=1024)
+        from test_gpu_freq_xlating import assert_vs_reference  # tolerance explained there
+
+        assert_vs_reference(out, ref, "c++ freq_xlating ct=%d" % ct)
+    rc = drv.grbx_freq_xlating_run(0, 0, p(taps), 4, C.c_double(0), C.c_double(1), p(xin), p(out), LL(10), 1024)
     assert rc == -1  # std::invalid_argument
 
 
