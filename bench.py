@@ -238,8 +238,11 @@ class FftFilter(Workload):
     """configs[1]: fft_filter_ccc 4096-tap low-pass, 2^28 samples on 1 B200."""
     name = "fft_filter_ccc 4096 taps, 2^%d samples (BASELINE configs[1])"
     block = "fft_filter_ccc"
-    alg_bytes, flops, log2n, seed = 16.0, 195.0, 28, 2  # device transform length 16384
-    kernel = "fftfilt_ols_kernel"
+    # two tap partitions on the 4096-point kernel: (2 x 5 N log2 N + 16 N) / (N/2) flops per output sample, N = 4096
+    alg_bytes, flops, log2n, seed = 16.0, 272.0, 28, 2
+    kernel = "fftfilt_upols_kernel"
+    ncu_dram_bytes_per_sample = (2.158e9 + 2.104e9) / (1 << 28)
+    ncu_source = "profiles/r1_fftfilt_upols_ncu.txt"
     ntaps = 4096
 
     def setup(self):

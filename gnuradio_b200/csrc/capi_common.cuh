@@ -19,8 +19,8 @@ int fft_direct_max();
 int fft_vcc_launch(int N, bool fwd, const void* in, void* out, long long nvec, const float* window, int shift,
                    int magsq, const float2* tw, int nsm, cudaStream_t st);
 int magsq_launch(const void* in, float* out, long long n, int nsm, cudaStream_t st);
-int fftfilt_device_fftsize(int ntaps);
-int fftfilt_launch(int L, const void* in, void* out, long long nout, int ntaps, int D, const float2* H,
+int fftfilt_device_plan(int ntaps, int* parts);
+int fftfilt_launch(int L, int parts, const void* in, void* out, long long nout, int ntaps, int D, const float2* H,
                    const float2* tw, int nsm, cudaStream_t st);
 int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stride, int nouts, const int* cmap,
                int identity, long long noutput, const float* h, const float2* wM, int nsm, bool allow_fast,

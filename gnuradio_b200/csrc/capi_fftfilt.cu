@@ -10,6 +10,7 @@ struct grb200_fftfilt {
     int ntaps = 0;
     int nsamples = 0; // the reference's block length = the block's output_multiple (fft_filter.cc:208-209)
     int L = 0;        // device FFT length
+    int parts = 1;    // tap partitions (fftfilt_device_plan)
     DevBuf H, tw;
     std::vector<float2> hist; // last ntaps-1 input items of the previous work() call (the d_tail equivalent)
     Stager sg;
@@ -25,7 +26,8 @@ static int ref_nsamples(int ntaps)
 
 static int fftfilt_prepare(grb200_fftfilt* h, const float* taps_re_im, int ntaps)
 {
-    const int L = fftfilt_device_fftsize(ntaps);
+    int K = 1;
+    const int L = fftfilt_device_plan(ntaps, &K);
     if (L < 0)
         return fail(GRB200_ERANGE, "fft_filter_ccc: %d taps exceed the single-CTA transform (max %d)", ntaps,
                     16384 * 3 / 4 + 1);
@@ -35,11 +37,13 @@ static int fftfilt_prepare(grb200_fftfilt* h, const float* taps_re_im, int ntaps
         if ((rc = h->tw.upload(roots.data(), roots.size() * sizeof(float2))))
             return rc;
     }
-    // H = FFT_L(taps / L): scale on the host like fft_filter.cc:184-189, transform on the device
-    std::vector<float2> padded((size_t)L, make_float2(0.f, 0.f));
+    // H_p = FFT_L(taps of partition p / L): scale on the host like fft_filter.cc:184-189, transform on the device.
+    // One partition holds all taps; two hold taps [0, L/2) and [L/2, ntaps).
+    const int P = K == 1 ? ntaps : L / 2;
+    std::vector<float2> padded((size_t)L * K, make_float2(0.f, 0.f));
     const float scale = 1.0f / (float)L;
     for (int i = 0; i < ntaps; i++)
-        padded[i] = make_float2(taps_re_im[2 * i] * scale, taps_re_im[2 * i + 1] * scale);
+        padded[(size_t)(i / P) * L + i % P] = make_float2(taps_re_im[2 * i] * scale, taps_re_im[2 * i + 1] * scale);
     DevBuf tmp;
     if ((rc = tmp.upload(padded.data(), padded.size() * sizeof(float2))))
         return rc;
@@ -47,7 +51,7 @@ static int fftfilt_prepare(grb200_fftfilt* h, const float* taps_re_im, int ntaps
         tmp.release();
         return rc;
     }
-    rc = fft_vcc_launch(L, true, tmp.p, h->H.p, 1, nullptr, 0, 0, (const float2*)h->tw.p, sm_count(h->device),
+    rc = fft_vcc_launch(L, true, tmp.p, h->H.p, K, nullptr, 0, 0, (const float2*)h->tw.p, sm_count(h->device),
                         h->sg.s_exec);
     if (!rc) {
         cudaError_t e = cudaStreamSynchronize(h->sg.s_exec);
@@ -58,6 +62,7 @@ static int fftfilt_prepare(grb200_fftfilt* h, const float* taps_re_im, int ntaps
     if (rc)
         return rc;
     h->L = L;
+    h->parts = K;
     h->ntaps = ntaps;
     h->nsamples = ref_nsamples(ntaps);
     h->hist.assign((size_t)(ntaps - 1), make_float2(0.f, 0.f)); // set_taps zeroes the overlap state (:177-179)
@@ -139,7 +144,7 @@ int grb200_fftfilt_work_dev(grb200_fftfilt* h, const void* in_dev, void* out_dev
     int rc = use_device(h->device);
     if (rc)
         return rc;
-    return fftfilt_launch(h->L, in_dev, out_dev, noutput, h->ntaps, h->decim, (const float2*)h->H.p,
+    return fftfilt_launch(h->L, h->parts, in_dev, out_dev, noutput, h->ntaps, h->decim, (const float2*)h->H.p,
                           (const float2*)h->tw.p, sm_count(h->device), pick_stream(stream, h->sg));
 }
 
@@ -189,7 +194,7 @@ int grb200_fftfilt_work(grb200_fftfilt* h, const void* in_host, void* out_host, 
         },
         [&](long long c, int slot, cudaStream_t st) {
             const long long o0 = c * chunk, n = std::min(chunk, noutput - o0);
-            return fftfilt_launch(h->L, sg.dev[slot][0], sg.dev[slot][1], n, h->ntaps, D, (const float2*)h->H.p,
+            return fftfilt_launch(h->L, h->parts, sg.dev[slot][0], sg.dev[slot][1], n, h->ntaps, D, (const float2*)h->H.p,
                                   (const float2*)h->tw.p, sm_count(h->device), st);
         });
     if (rc)

@@ -229,30 +229,285 @@ static int launch_ols_stream(const void* in, void* out, long long nout, long lon
     return 0;
 }
 
-// Device FFT length for a tap count: at least the reference's 2*2^ceil(log2 ntaps), never below 4096.
-int fftfilt_device_fftsize(int ntaps)
+// ---- two-partition variant (long filters; L = 4096 or 8192, hop V = L/2, ntaps <= L) -------------------------------
+// Plain overlap-save wastes ntaps-1 of every L transformed items; at 4096 taps that forces a 16384-point transform
+// (1024 threads, 64-register cap, spills, no room for a prefetch buffer: 78 Gsps, profiles/r1_fftfilt_ncu.txt).
+// Uniformly partitioned overlap-save keeps the efficient 4096-point machinery instead: the taps are split into
+// h0 = h[0, V) and h1 = h[V, ntaps), H0/H1 are their L-point spectra, and
+//     y_b = IFFT( X_b . H0 + X_{b-1} . H1 ),   X_b = FFT of the L items that end at block b's last output,
+// whose last V items are alias-free.  One forward and one inverse transform per V outputs, like plain overlap-save at
+// 50 % overlap -- but X_{b-1} has to survive from one block to the next.  Registers (128/thread at 2 CTAs/SM) and shared
+// memory (100 KB/CTA) are both full, so the previous spectrum lives in TENSOR MEMORY: each thread parks its 16 complex
+// values in 32 columns of its own TMEM lane (tcgen05.st.32x32b) and reads them back one block later (tcgen05.ld) -- 64
+// columns per 256-thread CTA of an SM-local memory this kernel otherwise leaves idle.  Every CTA owns a contiguous run of
+// blocks (one extra forward transform warms the delay line up), so consecutive blocks also share their overlap in
+// shared memory: only the V NEW items of a block come from HBM (one TMA bulk copy per block into a two-slice ring).
+template <int L>
+struct UpolsGeom {
+    static constexpr int TPV = L / 16, V = L / 2;
+    static constexpr int SLICE = V + 2; // items per ring slice: the copy starts at an even item (16-byte TMA rule)
+    static constexpr int XIN_BYTES = 2 * SLICE * 8;
+    static constexpr int S_BYTES = ((fft_smem_elems(L) * 8 + 15) / 16) * 16;
+    static constexpr int TWF_BYTES = fft_tws_slots(L, false) * TPV * 8;
+    static constexpr int TWR_BYTES = fft_tws_slots(L, true) * TPV * 8;
+    static constexpr int SMEM = XIN_BYTES + S_BYTES + TWF_BYTES + TWR_BYTES + 32;
+    static constexpr int TMEM_COLS = (TPV / 128) * 32; // 32 columns per thread, 128 lanes
+};
+
+template <int L>
+__global__ void __launch_bounds__(L / 16)
+fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin,
+                     int ntaps, int D, const float2* __restrict__ H, const float2* __restrict__ tw, long long run, int gs)
 {
-    int L = 4096;
+    // `in` is 16-byte aligned; the stream's first item is in[gs] (gs = 1 when the caller's pointer was only 8-byte aligned;
+    // nin counts from in[0]); items in front of it read as zero like the ones in front of the stream
+    using G = UpolsGeom<L>;
+    constexpr int E = 16, TPV = G::TPV, V = G::V, SLICE = G::SLICE;
+    constexpr int R0 = fft_first_radix(L, false);
+    constexpr int RM = fft_last_radix(L, false); // == first radix of the reversed schedule
+    constexpr int RL = fft_last_radix(L, true);
+    static_assert(R0 >= 2 && (L / R0) % V == 0 || V % (L / R0) == 0, "first-pass stride must not straddle the slices");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float2* XIN = reinterpret_cast<float2*>(smem_raw);
+    float2* S = reinterpret_cast<float2*>(smem_raw + G::XIN_BYTES);
+    float2* TWF = reinterpret_cast<float2*>(smem_raw + G::XIN_BYTES + G::S_BYTES);
+    float2* TWR = reinterpret_cast<float2*>(smem_raw + G::XIN_BYTES + G::S_BYTES + G::TWF_BYTES);
+    unsigned long long* bar =
+        reinterpret_cast<unsigned long long*>(smem_raw + G::XIN_BYTES + G::S_BYTES + G::TWF_BYTES + G::TWR_BYTES);
+    unsigned* tmem_slot = reinterpret_cast<unsigned*>(bar + 2);
+    const int t = threadIdx.x, warp = t >> 5;
+    const long long ny = nout * D;
+    const long long nblocks = (ny + V - 1) / V;
+    const long long nin_even = nin & ~1LL; // items the bulk copies may touch (the odd last one is read directly)
+    const int c0 = ntaps - 1 + gs, off = c0 & 1;
+    const long long b0 = blockIdx.x * run, b1 = (b0 + run < nblocks) ? b0 + run : nblocks;
+
+    // slice j = buffer items [(j-1)V + c0, jV + c0); block b transforms slices b (old half) and b+1 (new half)
+    auto issue = [&](long long j) {
+        const int h = (int)(j & 1);
+        const long long lo = (j - 1) * V + c0 - off; // even; negative in front of the stream (zeros)
+        const long long lo_c = lo < 0 ? 0 : lo;
+        long long hi_c = lo + SLICE;
+        hi_c = hi_c > nin_even ? nin_even : hi_c;
+        const long long n = hi_c > lo_c ? hi_c - lo_c : 0;
+        mbar_expect_tx(&bar[h], (unsigned)(n * 8));
+        if (n)
+            bulk_g2s(XIN + h * SLICE + (lo_c - lo), in + lo_c, (unsigned)(n * 8), &bar[h]);
+    };
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(G::TMEM_COLS < 32 ? 32 : G::TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (t == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+    }
+    cta_fft_tws_init<L, true, false>(TWF, t, tw);
+    cta_fft_tws_init<L, false, true>(TWR, t, tw);
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const unsigned tmem = *tmem_slot;
+    // this thread's parking space: its own lane (sub-partition = warp % 4), 32 columns per group of four warps
+    const unsigned taddr = tmem + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)((warp >> 2) * 32);
+
+    if (b0 < b1) {
+        if (t == 0) {
+            issue(b0 - 1);
+            issue(b0);
+        }
+        unsigned ph = 0; // bit h = parity the next wait on bar[h] expects
+        for (long long blk = b0 - 1; blk < b1; blk++) {
+            const int hnew = (int)((blk + 1) & 1);
+            if (blk == b0 - 1) {
+                mbar_wait(&bar[hnew ^ 1], (ph >> (hnew ^ 1)) & 1);
+                ph ^= 1u << (hnew ^ 1);
+            }
+            mbar_wait(&bar[hnew], (ph >> hnew) & 1);
+            ph ^= 1u << hnew;
+            const long long s = (blk - 1) * V + c0; // buffer index of the block's first item
+            float2 v[E];
+#pragma unroll
+            for (int b = 0; b < E / R0; b++)
+#pragma unroll
+                for (int q = 0; q < R0; q++) {
+                    const int m = (t + b * TPV) + q * (L / R0);
+                    const long long g = s + m;
+                    const int half = m / V, idx = m % V;
+                    float2 x = make_float2(0.f, 0.f);
+                    if (g >= gs && g < nin_even)
+                        x = XIN[((int)((blk + half) & 1)) * SLICE + idx + off];
+                    else if (g >= gs && g < nin)
+                        x = in[g];
+                    v[b * R0 + q] = x;
+                }
+            cta_fft_tws<L, true, false>(v, S, t, TWF, tw, [&]() {
+                if (t == 0 && blk + 1 < b1)
+                    issue(blk + 2); // into the half that held slice blk: every thread has read it by now
+            });
+            if (blk == b0 - 1) { // warm-up: only park the spectrum
+#pragma unroll
+                for (int c = 0; c < 4; c++)
+                    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(
+                                     taddr + c * 8),
+                                 "f"(v[4 * c].x), "f"(v[4 * c].y), "f"(v[4 * c + 1].x), "f"(v[4 * c + 1].y),
+                                 "f"(v[4 * c + 2].x), "f"(v[4 * c + 2].y), "f"(v[4 * c + 3].x), "f"(v[4 * c + 3].y)
+                                 : "memory");
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                __syncthreads(); // the transform's last gather is done before the next block reuses S
+                continue;
+            }
+            // v = X_b . H0 + X_{b-1} . H1; X_b takes X_{b-1}'s place in tensor memory.  Four chunks of four values,
+            // software-pipelined: chunk c+1's TMEM read and its eight H values (L2) are in flight while chunk c is
+            // multiplied.  (The tcgen05 statements are volatile asm, so they keep their order among themselves; the
+            // wait lists the loaded registers as in/out operands so that no use of them can move above it.)
+            float2 xp[2][4], hh[2][8];
+            auto fetch = [&](int c) {
+                float2* x = xp[c & 1];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                             : "=f"(x[0].x), "=f"(x[0].y), "=f"(x[1].x), "=f"(x[1].y), "=f"(x[2].x), "=f"(x[2].y),
+                               "=f"(x[3].x), "=f"(x[3].y)
+                             : "r"(taddr + c * 8));
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const int i = 4 * c + e;
+                    const int k = (t + (i / RM) * TPV) + (i % RM) * (L / RM);
+                    hh[c & 1][2 * e] = __ldg(H + k);
+                    hh[c & 1][2 * e + 1] = __ldg(H + L + k);
+                }
+            };
+            fetch(0);
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                if (c < 3)
+                    fetch(c + 1);
+                float2* x = xp[c & 1];
+                float2* y = xp[(c + 1) & 1]; // listed too: the wait also completes the read just issued
+                asm volatile("tcgen05.wait::ld.sync.aligned;"
+                             : "+f"(x[0].x), "+f"(x[0].y), "+f"(x[1].x), "+f"(x[1].y), "+f"(x[2].x), "+f"(x[2].y),
+                               "+f"(x[3].x), "+f"(x[3].y), "+f"(y[0].x), "+f"(y[0].y), "+f"(y[1].x), "+f"(y[1].y),
+                               "+f"(y[2].x), "+f"(y[2].y), "+f"(y[3].x), "+f"(y[3].y));
+                asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(
+                                 taddr + c * 8),
+                             "f"(v[4 * c].x), "f"(v[4 * c].y), "f"(v[4 * c + 1].x), "f"(v[4 * c + 1].y),
+                             "f"(v[4 * c + 2].x), "f"(v[4 * c + 2].y), "f"(v[4 * c + 3].x), "f"(v[4 * c + 3].y));
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const int i = 4 * c + e;
+                    const float2 h0 = hh[c & 1][2 * e], h1 = hh[c & 1][2 * e + 1];
+                    const float2 a = v[i], p = x[e];
+                    v[i] = make_float2(fmaf(a.x, h0.x, fmaf(-a.y, h0.y, fmaf(p.x, h1.x, -p.y * h1.y))),
+                                       fmaf(a.x, h0.y, fmaf(a.y, h0.x, fmaf(p.x, h1.y, p.y * h1.x))));
+                }
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            __syncthreads(); // forward transform's last gather is done before the inverse reuses S
+            cta_fft_tws<L, false, true>(v, S, t, TWR, tw, []() {});
+#pragma unroll
+            for (int b = 0; b < E / RL; b++)
+#pragma unroll
+                for (int q = 0; q < RL; q++) {
+                    const int m = (t + b * TPV) + q * (L / RL);
+                    if (m >= V) {
+                        const long long n = blk * V + (m - V);
+                        if (n < ny) {
+                            if (D == 1)
+                                out[n] = v[b * RL + q];
+                            else if (n % D == 0)
+                                out[n / D] = v[b * RL + q];
+                        }
+                    }
+                }
+            __syncthreads();
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem),
+                     "r"(G::TMEM_COLS < 32 ? 32 : G::TMEM_COLS));
+}
+
+template <int L>
+static int launch_upols(const void* in, void* out, long long nout, long long nin, int ntaps, int D, const float2* H,
+                        const float2* tw, int nsm, cudaStream_t st)
+{
+    using G = UpolsGeom<L>;
+    auto kern = fftfilt_upols_kernel<L>;
+    GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, L / 16, G::SMEM));
+    if (occ < 1)
+        occ = 1;
+    // The occupancy query answers 1 for a kernel that allocates tensor memory, whatever it asks for; the hardware
+    // co-schedules as many CTAs as registers, shared memory and the 512 TMEM columns allow (checked with ncu).
+    cudaFuncAttributes fa;
+    GRB_CUDA(cudaFuncGetAttributes(&fa, kern));
+    int by_regs = 65536 / (fa.numRegs * (L / 16)), by_smem = (227 * 1024) / (G::SMEM + 1024), by_tmem = 512 / G::TMEM_COLS;
+    int fit = by_regs < by_smem ? by_regs : by_smem;
+    fit = fit < by_tmem ? fit : by_tmem;
+    if (const char* e = getenv("GRB200_FFTFILT_UPOLS_OCC"))
+        fit = atoi(e);
+    if (fit > occ)
+        occ = fit;
+    const long long nblocks = (nout * D + G::V - 1) / G::V;
+    long long grid = (long long)nsm * occ;
+    if (grid > nblocks)
+        grid = nblocks;
+    const long long run = (nblocks + grid - 1) / grid;
+    grid = (nblocks + run - 1) / run;
+    const int gs = (int)((((uintptr_t)in) >> 3) & 1); // 8-byte aligned only: start the stream one item into an aligned one
+    kern<<<(unsigned)grid, L / 16, G::SMEM, st>>>((const float2*)in - gs, (float2*)out, nout, nin + gs, ntaps, D, H, tw,
+                                                  run, gs);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+// Device plan for a tap count: FFT length L (at least the reference's 2*2^ceil(log2 ntaps), never below 4096) and
+// the number of tap partitions K (1 = plain overlap-save with hop L-ntaps+1, 2 = partitioned with hop L/2).
+int fftfilt_device_plan(int ntaps, int* parts)
+{
+    int L = 4096, K = 1;
     while (L < 2 * ntaps && L < 16384)
         L *= 2;
     if (L == 8192 && ntaps - 1 > L / 4)
         L = 16384; // > 25 % of every block would be overlap: the longer transform wins (cfg2: 70 -> 78 Gsps)
+    const char* ue = getenv("GRB200_FFTFILT_UPOLS"); // 0 = never, 1 = whenever the geometry allows, unset = auto
+    const int upols = ue ? atoi(ue) : -1;
+    if (upols != 0 && L == 16384 && ntaps <= 4096) {
+        L = 4096; // the 16384-point transform is the slow one: two partitions on the 4096-point kernel instead
+        K = 2;
+    } else if (upols == 1 && ntaps > 1025 && ntaps <= 4096) {
+        L = 4096;
+        K = 2;
+    }
     if (const char* e = getenv("GRB200_FFTFILT_L")) { // tuning knob: a longer transform wastes less on the overlap
         const int v = atoi(e);
-        if ((v == 4096 || v == 8192 || v == 16384) && v >= L)
+        if (K == 1 && (v == 4096 || v == 8192 || v == 16384) && v >= L)
             L = v;
     }
-    if (L - (ntaps - 1) < L / 4)
+    if (K == 1 && L - (ntaps - 1) < L / 4)
         return -1; // too many taps for a single-CTA transform
+    if (parts)
+        *parts = K;
     return L;
 }
 
-int fftfilt_launch(int L, const void* in, void* out, long long nout, int ntaps, int D, const float2* H,
+int fftfilt_launch(int L, int parts, const void* in, void* out, long long nout, int ntaps, int D, const float2* H,
                    const float2* tw, int nsm, cudaStream_t st)
 {
     if (nout <= 0)
         return 0;
     const long long nin = nout * D + ntaps - 1;
+    if (parts == 2) {
+        if ((((uintptr_t)in) & 7) != 0)
+            return fail(GRB200_EINVAL, "fft_filter: input stream is not aligned to its item size");
+        if (L == 4096)
+            return launch_upols<4096>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+        return fail(GRB200_ERANGE, "fft_filter: no partitioned kernel for fft length %d", L);
+    }
     static const bool use_stream = [] {
         const char* e = getenv("GRB200_FFTFILT_STREAM");
         return !(e && e[0] == '0');

@@ -336,6 +336,61 @@ def test_fft_filter_many_blocks_per_cta(grb, orc, ntaps, decim):
     assert_parity(got[:n_c], orc.fft_filter_ccc(decim, taps, x[: n_c * decim]), "oracle prefix")
 
 
+@pytest.mark.parametrize("ntaps,decim", [(4096, 1), (4095, 1), (3001, 2), (2050, 1), (1026, 5), (2049, 1)])
+def test_fft_filter_partitioned_kernel(grb, orc, monkeypatch, ntaps, decim):
+    """Two tap partitions on the 4096-point kernel, previous spectrum parked in tensor memory (the default plan for
+    2050..4096 taps; forced here for shorter filters too).  2^21 samples = many blocks per CTA run plus a ragged tail;
+    odd and even tap counts give odd and even slice bases for the TMA ring."""
+    import scipy.signal
+
+    monkeypatch.setenv("GRB200_FFTFILT_UPOLS", "1")
+    rng = np.random.default_rng(99 + ntaps)
+    x, taps = crand(rng, (1 << 21) + 777), crand(rng, ntaps) * np.float32(4.0 / ntaps)
+    blk = grb.filter.fft_filter_ccc(decim, taps)
+    ns = blk.nsamples()
+    assert ns == orc.fft_filter_nsamples(ntaps)
+    got = sched_mock.run_sync(blk, x, max_noutput=1 << 23)
+    nitems = (len(x) // decim // ns) * ns
+    assert len(got) == nitems
+    ref64 = scipy.signal.fftconvolve(x.astype(np.complex128), taps.astype(np.complex128))[: nitems * decim: decim]
+    assert_parity(got, ref64, "f64 ntaps %d decim %d" % (ntaps, decim))
+    n_c = max((100000 // decim // ns), 1) * ns  # the C oracle on a prefix
+    assert_parity(got[:n_c], orc.fft_filter_ccc(decim, taps, x[: n_c * decim]), "oracle prefix")
+    # scheduler-sized calls (one reference block each): the overlap state carries across work() calls
+    small = sched_mock.run_sync(grb.filter.fft_filter_ccc(decim, taps), x[: 40 * ns * decim], max_noutput=ns)
+    assert_parity(small, got[: len(small)], "one block per call")
+    monkeypatch.setenv("GRB200_FFTFILT_UPOLS", "0")
+    plain = sched_mock.run_sync(grb.filter.fft_filter_ccc(decim, taps), x, max_noutput=1 << 23)
+    assert_parity(got, plain, "vs plain overlap-save", 2e-6, 2e-5)
+
+
+def test_fft_filter_partitioned_device_resident_unaligned(grb):
+    """work_dev with an input pointer that is only 8-byte aligned: the partitioned kernel starts one item into the
+    aligned stream; same result as the aligned call."""
+    import torch
+
+    rng = np.random.default_rng(101)
+    nt, n = 4096, 1 << 20
+    taps = crand(rng, nt) * np.float32(4.0 / nt)
+    x = crand(rng, n + nt - 1 + 1)
+    xd = torch.from_numpy(x.view(np.float32)).cuda()
+    y0 = torch.zeros(2 * n, dtype=torch.float32, device="cuda")
+    y1 = torch.zeros(2 * n, dtype=torch.float32, device="cuda")
+    blk = grb.filter.fft_filter_ccc(1, taps)
+    st = torch.cuda.current_stream().cuda_stream
+    blk.work_dev(xd.data_ptr() + 8, y1.data_ptr(), n, st)   # stream starts at item 1: 8-byte aligned
+    torch.cuda.synchronize()
+    xs = torch.from_numpy(x[1:].copy().view(np.float32)).cuda()  # the same stream, 16-byte aligned
+    blk.work_dev(xs.data_ptr(), y0.data_ptr(), n, st)
+    torch.cuda.synchronize()
+    a, b = y0.cpu().numpy().view(np.complex64), y1.cpu().numpy().view(np.complex64)
+    assert np.array_equal(a, b)
+    import scipy.signal
+
+    ref = scipy.signal.fftconvolve(x[1:].astype(np.complex128), taps.astype(np.complex128))[nt - 1: nt - 1 + n]
+    assert_parity(a, ref, "f64")
+
+
 def test_fft_filter_state_across_calls_and_set_taps(grb, orc):
     rng = np.random.default_rng(8)
     x, taps = crand(rng, 20000), crand(rng, 100)
