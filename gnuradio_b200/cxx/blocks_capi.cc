@@ -183,4 +183,36 @@ long long grbx_pfb_run(unsigned nfilts, const float* taps, int ntaps, float osr,
     });
 }
 
+// pfb_decimator_ccf over in_streams[s] (no history in front: a fresh stream), scheduler-sized calls
+long long grbx_pfb_dec_run(unsigned decim, const float* taps, int ntaps, unsigned channel, int use_fft_rotator,
+                           int use_fft_filters, const void* const* in_streams, void* out, long long nitems, int chunk)
+{
+    return guarded([&]() -> long long {
+        std::vector<float> t(taps, taps + ntaps);
+        auto b = gr::filter::pfb_decimator_ccf::make(decim, t, channel, use_fft_rotator != 0, use_fft_filters != 0);
+        const long long hist = b->history();
+        std::vector<std::vector<gr_complex>> buf(decim);
+        for (unsigned s = 0; s < decim; s++) {
+            buf[s].assign((size_t)(hist - 1), gr_complex(0, 0));
+            buf[s].insert(buf[s].end(), (const gr_complex*)in_streams[s], (const gr_complex*)in_streams[s] + nitems);
+        }
+        long long produced = 0;
+        while (produced < nitems) {
+            long long n = std::min<long long>(chunk, nitems - produced);
+            n = n / b->output_multiple() * b->output_multiple();
+            if (n == 0)
+                break;
+            gr_vector_const_void_star ii(decim);
+            gr_vector_void_star oo(1, (gr_complex*)out + produced);
+            for (unsigned s = 0; s < decim; s++)
+                ii[s] = buf[s].data() + produced;
+            const int r = b->work((int)n, ii, oo);
+            if (r <= 0)
+                break;
+            produced += r;
+        }
+        return produced;
+    });
+}
+
 } // extern "C"

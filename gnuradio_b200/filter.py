@@ -9,6 +9,8 @@
   pfb_channelizer_ccf               gr-filter/include/gnuradio/filter/pfb_channelizer_ccf.h:100-192,
                                     gr-filter/lib/pfb_channelizer_ccf_impl.cc:34-193
   pfb.channelizer_ccf               gr-filter/python/filter/pfb.py:23-50 (hier block; stream_to_streams absorbed)
+  pfb_decimator_ccf                 gr-filter/include/gnuradio/filter/pfb_decimator_ccf.h:94-138,
+                                    gr-filter/lib/pfb_decimator_ccf_impl.cc:24-257
 
 work()/general_work() take borrowed HOST numpy buffers like the scheduler's; *_dev variants take raw
 device pointers (ints, e.g. torch.Tensor.data_ptr()) for chained GPU blocks.  All arithmetic runs in the
@@ -19,7 +21,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from .runtime import as_items, block, io_signature, sync_decimator
+from .runtime import as_items, block, io_signature, sync_block, sync_decimator
 
 _c64 = np.dtype(np.complex64)
 
@@ -463,6 +465,101 @@ class pfb_channelizer_ccf(block):
         if h:
             try:
                 _lib.lib().grb200_pfb_chan_destroy(h)
+            except Exception:
+                pass
+
+
+class pfb_decimator_ccf(sync_block):
+    """Polyphase filterbank decimator: `decim` input streams (a stream_to_streams in front), one output = channel
+    `channel` of the bank, at 1/decim of the total input rate.
+
+    use_fft_rotator / use_fft_filters pick among the reference's four work() variants (pfb_decimator_ccf_impl.cc:
+    120-131), which differ only in rounding; here they only decide what the scheduler is told: with use_fft_filters
+    the block declares history 1 and an output multiple (:57-59) and the overlap is carried in the handle, otherwise
+    history = taps_per_filter (:61)."""
+
+    def __init__(self, decim, taps, channel, use_fft_rotator=True, use_fft_filters=True, device=0):
+        L = _lib.lib()
+        decim = int(decim)
+        if decim < 1:
+            raise ValueError("pfb_decimator_ccf: decimation must be >= 1")
+        sync_block.__init__(self, "pfb_decimator_ccf", io_signature.make(decim, decim, 8), io_signature.make(1, 1, 8))
+        self._h = C.c_void_p()
+        self._M = decim
+        t = pfb_channelizer_ccf._conv_taps(taps)
+        _lib.check(L.grb200_pfb_dec_ccf_create(decim, _ptr(t), len(t), int(channel), int(device), C.byref(self._h)))
+        self._proto = t.copy()
+        self.d_chan = int(channel)
+        self.d_use_fft_rotator = bool(use_fft_rotator)
+        self.d_use_fft_filters = bool(use_fft_filters)
+        self.d_taps_per_filter = L.grb200_pfb_dec_taps_per_filter(self._h)
+        self.d_updated = False
+        if self.d_use_fft_filters:
+            # fft_filter_ccf geometry for taps_per_filter taps (fft_filter.cc:336-341): filtersize - ntaps + 1
+            T = self.d_taps_per_filter
+            fftsize = int(2 * 2 ** np.ceil(np.log(float(T)) / np.log(2.0)))
+            self.set_history(1)
+            self.set_output_multiple(fftsize - T + 1)
+        else:
+            self.set_history(self.d_taps_per_filter)
+
+    @classmethod
+    def make(cls, decim, taps, channel, use_fft_rotator=True, use_fft_filters=True, device=0):
+        return cls(decim, taps, channel, use_fft_rotator, use_fft_filters, device)
+
+    def set_taps(self, taps):
+        t = pfb_channelizer_ccf._conv_taps(taps)
+        with self.d_setlock:  # pfb_decimator_ccf_impl.cc:88-95
+            L = _lib.lib()
+            _lib.check(L.grb200_pfb_dec_set_taps(self._h, _ptr(t), len(t)))
+            self._proto = t.copy()
+            self.d_taps_per_filter = L.grb200_pfb_dec_taps_per_filter(self._h)
+            self.set_history(self.d_taps_per_filter)
+            self.d_updated = True
+
+    def taps(self):
+        M, T = self._M, self.d_taps_per_filter
+        padded = np.zeros(M * T, np.float32)
+        padded[: len(self._proto)] = self._proto
+        return padded.reshape(T, M).T.tolist()  # d_taps[i][j] = padded[i + j*M], polyphase_filterbank.cc:69-73
+
+    def print_taps(self):
+        for i, row in enumerate(self.taps()):
+            print("filter[%d]: [%s]" % (i, " ".join("%.4e" % v for v in row)))
+
+    def set_channel(self, chan):
+        with self.d_setlock:  # :106-110
+            _lib.check(_lib.lib().grb200_pfb_dec_set_channel(self._h, int(chan)))
+            self.d_chan = int(chan)
+
+    def work(self, noutput_items, input_items, output_items):
+        with self.d_setlock:
+            if self.d_updated:  # :114-117
+                self.d_updated = False
+                return 0
+            n = int(noutput_items)
+            M = self._M
+            if len(input_items) != M:
+                raise ValueError("pfb_decimator_ccf: %d input streams, %d needed" % (len(input_items), M))
+            need = n + self.history() - 1
+            ins = [as_items(a, _c64, need if n else 0, "input_items[%d]" % j) for j, a in enumerate(input_items)]
+            out = as_items(output_items[0], _c64, n, "output_items[0]")
+            inp = (C.c_void_p * M)(*[a.ctypes.data for a in ins])
+            carry = 1 if self.history() == 1 and self.d_taps_per_filter > 1 else 0
+            _lib.check(_lib.lib().grb200_pfb_dec_work(self._h, inp, _ptr(out), n, carry))
+            return n
+
+    def work_dev(self, x_dev, stride, out_dev, noutput_items, stream=0):
+        """Device-resident, stateless: stream s at x_dev + 8*s*stride bytes, taps_per_filter-1 history items first."""
+        _lib.check(_lib.lib().grb200_pfb_dec_work_dev(self._h, C.c_void_p(x_dev), int(stride), C.c_void_p(out_dev),
+                                                      int(noutput_items), C.c_void_p(stream)))
+        return int(noutput_items)
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().grb200_pfb_dec_destroy(h)
             except Exception:
                 pass
 

@@ -157,6 +157,29 @@ int grb200_pfb_chan_work_interleaved_dev(grb200_pfb* h, const void* in_dev, void
                                          void* stream);
 void grb200_pfb_chan_destroy(grb200_pfb* h);
 
+/* ---- pfb_decimator_ccf ---------------------------------------------------------------------------
+ * Replaces gr::filter::pfb_decimator_ccf_impl::work and its four variants work_fir_exp / work_fir_fft /
+ * work_fft_exp / work_fft_fft (gr-filter/lib/pfb_decimator_ccf_impl.cc:107-257) over
+ * kernel::polyphase_filterbank (gr-filter/lib/polyphase_filterbank.cc:22-81):
+ *     out[i] = sum_j rot[j] * (branch filter j over input stream M-1-j)[i],  rot[j] = e^{+j 2 pi j channel / M}.
+ * The variants differ only in rounding (table vs M-point FFT, FIR vs FFT branch filters); one device kernel serves all.
+ * in_streams[s] (s < decim): the block's input stream s.  carry_state = 0: noutput + taps_per_filter-1 items each,
+ * history first (set_history(taps_per_filter), :61).  carry_state = 1: noutput items each, the overlap is kept in the
+ * handle like the fft_filter kernels keep theirs (set_history(1), :57-59).
+ * work_dev: x_dev holds the streams stream-major, stream s at x_dev + s*stride items, history first. */
+typedef struct grb200_pfbdec grb200_pfbdec;
+int grb200_pfb_dec_ccf_create(unsigned int decim, const float* taps, int ntaps, unsigned int channel, int device,
+                              grb200_pfbdec** out);
+int grb200_pfb_dec_set_taps(grb200_pfbdec* h, const float* taps, int ntaps);
+int grb200_pfb_dec_set_channel(grb200_pfbdec* h, unsigned int channel);
+int grb200_pfb_dec_taps_per_filter(const grb200_pfbdec* h);
+int grb200_pfb_dec_decimation(const grb200_pfbdec* h);
+int grb200_pfb_dec_work(grb200_pfbdec* h, const void* const* in_streams, void* out_host, long long noutput,
+                        int carry_state);
+int grb200_pfb_dec_work_dev(grb200_pfbdec* h, const void* x_dev, long long stride, void* out_dev, long long noutput,
+                            void* stream);
+void grb200_pfb_dec_destroy(grb200_pfbdec* h);
+
 /* ---- fft_vcc (+ complex_to_mag_squared) --------------------------------------------------------
  * Replaces gr::fft::fft_complex (gr-fft/lib/fft.cc:151-203) and fft_vcc_fftw: ctor/set_window
  * gr-fft/lib/fft_vcc_fftw.cc:33-61, work :63-122; and complex_to_mag_squared_impl::work

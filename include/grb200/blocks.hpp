@@ -483,6 +483,94 @@ private:
     bool d_updated = false;
 };
 
+// ---------------------------------------------------------------------------------------------------
+// pfb_decimator_ccf  (gr-filter/include/gnuradio/filter/pfb_decimator_ccf.h:94-138, lib/pfb_decimator_ccf_impl.cc)
+// ---------------------------------------------------------------------------------------------------
+class pfb_decimator_ccf : public grb200::rt::sync_block
+{
+public:
+    typedef std::shared_ptr<pfb_decimator_ccf> sptr;
+    static sptr make(unsigned int decim, const std::vector<float>& taps, unsigned int channel,
+                     bool use_fft_rotator = true, bool use_fft_filters = true)
+    {
+        return sptr(new pfb_decimator_ccf(decim, taps, channel, use_fft_rotator, use_fft_filters));
+    }
+    ~pfb_decimator_ccf() override { grb200_pfb_dec_destroy(d_h); }
+
+    void set_taps(const std::vector<float>& taps) // pfb_decimator_ccf_impl.cc:88-95
+    {
+        std::lock_guard<std::mutex> l(d_setlock);
+        grb200::check(grb200_pfb_dec_set_taps(d_h, taps.data(), (int)taps.size()));
+        d_proto = taps;
+        set_history(grb200_pfb_dec_taps_per_filter(d_h));
+        d_updated = true;
+    }
+    std::vector<std::vector<float>> taps() const // d_taps[i][j] = padded[i + j*M], polyphase_filterbank.cc:69-73
+    {
+        const int T = grb200_pfb_dec_taps_per_filter(d_h);
+        std::vector<std::vector<float>> out(d_rate, std::vector<float>((size_t)T, 0.f));
+        for (size_t k = 0; k < d_proto.size(); k++)
+            out[k % d_rate][k / d_rate] = d_proto[k];
+        return out;
+    }
+    void print_taps()
+    {
+        auto t = taps();
+        for (unsigned i = 0; i < d_rate; i++) {
+            printf("filter[%u]: [", i);
+            for (float v : t[i])
+                printf(" %.4e", v);
+            printf("]\n\n");
+        }
+    }
+    void set_channel(const unsigned int channel) // :106-110
+    {
+        std::lock_guard<std::mutex> l(d_setlock);
+        grb200::check(grb200_pfb_dec_set_channel(d_h, channel));
+    }
+
+    int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
+    {
+        std::lock_guard<std::mutex> l(d_setlock);
+        if (d_updated) { // :114-117
+            d_updated = false;
+            return 0; // history requirements may have changed.
+        }
+        if (input_items.size() != d_rate)
+            throw std::invalid_argument("pfb_decimator_ccf: one input stream per branch is required");
+        // history 1 (the FFT-filter variants, :57-59): the handle carries the overlap between calls
+        const int carry = history() == 1 && grb200_pfb_dec_taps_per_filter(d_h) > 1;
+        grb200::check(grb200_pfb_dec_work(d_h, input_items.data(), output_items[0], noutput_items, carry));
+        return noutput_items;
+    }
+
+    grb200_pfbdec* handle() { return d_h; } // device-resident chaining (grb200_pfb_dec_work_dev)
+
+private:
+    pfb_decimator_ccf(unsigned int decim, const std::vector<float>& taps, unsigned int channel, bool use_fft_rotator,
+                      bool use_fft_filters)
+        : sync_block("pfb_decimator_ccf", grb200::rt::io_signature::make(decim, decim, sizeof(gr_complex)),
+                     grb200::rt::io_signature::make(1, 1, sizeof(gr_complex))),
+          d_rate(decim), d_proto(taps), d_use_fft_rotator(use_fft_rotator), d_use_fft_filters(use_fft_filters)
+    {
+        grb200::check(grb200_pfb_dec_ccf_create(decim, taps.data(), (int)taps.size(), channel, grb200::default_device(),
+                                                &d_h));
+        const int T = grb200_pfb_dec_taps_per_filter(d_h);
+        if (d_use_fft_filters) { // :56-59, fft_filter_ccf geometry for T taps (fft_filter.cc:336-341)
+            const int fftsize = (int)(2 * pow(2.0, ceil(log((double)T) / log(2.0))));
+            set_history(1);
+            set_output_multiple(fftsize - T + 1);
+        } else {
+            set_history(T); // :61
+        }
+    }
+    grb200_pfbdec* d_h = nullptr;
+    unsigned int d_rate;
+    std::vector<float> d_proto;
+    bool d_use_fft_rotator, d_use_fft_filters; // the reference's four variants differ in rounding only
+    bool d_updated = false;
+};
+
 } // namespace filter
 
 namespace fft {

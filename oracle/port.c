@@ -443,6 +443,55 @@ int grbo_pfb_channelizer_ccf(unsigned int nfilts, const float* taps, int ntaps, 
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * pfb_decimator_ccf_impl::work_fir_exp (gr-filter/lib/pfb_decimator_ccf_impl.cc:135-154) over
+ * polyphase_filterbank::set_taps (gr-filter/lib/polyphase_filterbank.cc:53-81):
+ *   out[i] = sum_{j=M-1..0} fir_j(&in_{M-1-j}[i]) * rot[j],  taps_j[t] = padded[j + t*M],
+ *   rot[j] = gr_expj(j*chan*2*pi/M) (:49-51, float phase).
+ * The other three variants (:156-257) compute the same sum with an M-point backward FFT in place of the
+ * rotator table and/or FFT branch filters; they differ in rounding only.
+ * in_streams[s]: noutput + T-1 items, history first (set_history(T), :61).
+ * ---------------------------------------------------------------------------------------------- */
+int grbo_pfb_decimator_ccf(unsigned int decim, const float* taps, int ntaps, unsigned int channel,
+                           const cf32* const* in_streams, cf32* out, long noutput)
+{
+    const int M = (int)decim, T = (ntaps + M - 1) / M;
+    float* br = (float*)calloc((size_t)M * T, sizeof(float)); /* br[j*T + t] = reversed taps of branch j */
+    cf32* rot = (cf32*)malloc(sizeof(cf32) * (size_t)M);
+    if (!br || !rot) {
+        free(br);
+        free(rot);
+        return -1;
+    }
+    for (int j = 0; j < M; j++) {
+        for (int t = 0; t < T; t++) {
+            const int k = j + (T - 1 - t) * M;
+            br[j * T + t] = k < ntaps ? taps[k] : 0.0f;
+        }
+        const float ph = (float)((unsigned int)j * channel * 2 * PI_D / decim);
+        rot[j].re = cosf(ph);
+        rot[j].im = sinf(ph);
+    }
+    for (long i = 0; i < noutput; i++) {
+        float ore = 0.0f, oim = 0.0f;
+        for (int j = M - 1; j >= 0; j--) {
+            const cf32* x = in_streams[M - 1 - j] + i;
+            float re = 0.0f, im = 0.0f;
+            for (int t = 0; t < T; t++) {
+                re += x[t].re * br[j * T + t];
+                im += x[t].im * br[j * T + t];
+            }
+            ore += re * rot[j].re - im * rot[j].im;
+            oim += re * rot[j].im + im * rot[j].re;
+        }
+        out[i].re = ore;
+        out[i].im = oim;
+    }
+    free(br);
+    free(rot);
+    return (int)noutput;
+}
+
+/* ------------------------------------------------------------------------------------------------
  * fft_vcc_fftw::work (gr-fft/lib/fft_vcc_fftw.cc:63-122) and set_window (:54-61).
  * ---------------------------------------------------------------------------------------------- */
 int grbo_fft_vcc(int fft_size, int forward, const float* window, int nwindow, int shift,

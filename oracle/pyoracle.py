@@ -165,6 +165,33 @@ class _CLib:
             raise ValueError("pfb_channelizer_ccf oracle error %d" % rc)
         return outs, rc
 
+    # -- pfb_decimator_ccf ------------------------------------------------------------------------
+    def pfb_decimator(self, decim, taps, channel, streams, mode=0):
+        """streams: [decim][n] fresh input streams (zero history).  mode bit 0 = use_fft_rotator, bit 1 =
+        use_fft_filters (reference layer only; the port restates work_fir_exp, which the others equal up to rounding).
+        FFT-filter modes emit whole multiples of the block's output multiple only."""
+        taps = np.ascontiguousarray(taps, np.float32)
+        streams = np.ascontiguousarray(streams, np.complex64)
+        M, n = streams.shape
+        assert M == decim
+        T = -(-len(taps) // M)
+        if self.kind == "reference" and (mode & 2):
+            ns = self._f("pfb_decimator_nsamples")(C.c_uint(decim), _p(taps), len(taps))
+            n = (n // ns) * ns
+            xs = [_headroom(np.ascontiguousarray(streams[s, :n])) for s in range(M)]
+        else:
+            xs = [_headroom(np.concatenate([np.zeros(T - 1, np.complex64), streams[s]])) for s in range(M)]
+        out = np.empty(n, np.complex64)
+        inp = (C.c_void_p * M)(*[x.ctypes.data for x in xs])
+        if self.kind == "reference":
+            rc = self._f("pfb_decimator_ccf")(C.c_uint(decim), _p(taps), len(taps), C.c_uint(channel), int(mode), inp,
+                                              _p(out), int(n), None)
+        else:
+            rc = self._f("pfb_decimator_ccf")(C.c_uint(decim), _p(taps), len(taps), C.c_uint(channel), inp, _p(out),
+                                              C.c_long(n))
+        assert rc == n, rc
+        return out
+
     # -- fft_vcc -----------------------------------------------------------------------------------
     def fft_vcc(self, fft_size, forward, window, shift, x):
         x = _c64(x)
@@ -306,6 +333,22 @@ def f64_channelizer(nfilts, taps, x, nout, osr=1.0):
         y = np.convolve(x, g)[: len(x)]
         out[c] = y[P] * np.exp(-2j * np.pi * c * ((o + 2) * R % M) / M)
     return out
+
+
+def f64_pfb_decimator(decim, taps, channel, streams):
+    """out[i] = sum_k h[k] e^{j 2 pi k chan / M} x[iM + M-1 - k] with x the stream_to_streams-interleaved input
+    (stream s holds x[s], x[s+M], ...): the closed form of every pfb_decimator_ccf work() variant."""
+    M = decim
+    streams = np.asarray(streams, np.complex128)
+    n = streams.shape[1]
+    x = streams.T.reshape(-1)  # x[i*M + s] = streams[s][i]
+    k = np.arange(len(taps))
+    # rot[j] = gr_expj(float(j * chan * 2 pi / M)) (pfb_decimator_ccf_impl.cc:49-51): the float rounding of the phase
+    # (up to 4e-5 rad at j*chan ~ 10^4) belongs to the block's definition, like a tap value
+    ph = ((k % M) * channel * 2 * np.pi / M).astype(np.float32).astype(np.float64)
+    g = np.asarray(taps, np.float64) * np.exp(1j * ph)
+    y = np.convolve(x, g)
+    return y[M - 1: M - 1 + n * M: M][:n]
 
 
 def f64_fft_vcc(fft_size, forward, window, shift, x):

@@ -15,6 +15,7 @@
 #include <gnuradio/filter/fir_filter.h>
 #include <gnuradio/filter/firdes.h>
 #include <gnuradio/filter/polyphase_filterbank.h>
+#include <gnuradio/expj.h>
 #include <gnuradio/math.h>
 #include <volk/volk.h>
 #include <algorithm>
@@ -100,9 +101,90 @@ public:
     }
 };
 
+/* pfb_decimator_ccf_impl (gr-filter/lib/pfb_decimator_ccf_impl.cc) without the runtime: the block derives from
+ * sync_block AND polyphase_filterbank; this shell keeps the second base (the reference's own class, compiled from its
+ * source) and restates the four work() bodies (:135-257) over its members. */
+struct decimator_shell : public gr::filter::kernel::polyphase_filterbank {
+    unsigned int d_rate, d_chan;
+    std::vector<gr_complex> d_rotator;
+    decimator_shell(unsigned int decim, const std::vector<float>& taps, unsigned int channel)
+        : polyphase_filterbank(decim, taps), d_rate(decim), d_chan(channel), d_rotator(decim)
+    {
+        for (unsigned int i = 0; i < d_rate; i++) /* :49-51 */
+            d_rotator[i] = gr_expj(i * d_chan * 2 * GR_M_PI / d_rate);
+    }
+    int taps_per_filter() const { return (int)d_taps_per_filter; }
+    int fft_nsamples() const { return d_fft_filters[0]->filtersize() - d_fft_filters[0]->ntaps() + 1; } /* :58 */
+
+    /* mode bit 0 = use_fft_rotator, bit 1 = use_fft_filters.  FIR modes: in[s] has n + T-1 items, history first.
+     * FFT-filter modes: in[s] has n items (history 1, :57), n a multiple of fft_nsamples(). */
+    int work(int mode, int n, const gr_complex* const* input_items, gr_complex* out)
+    {
+        const bool rot_fft = mode & 1, filt_fft = mode & 2;
+        std::vector<gr_complex> tmp;
+        if (filt_fft) { /* :187-192 / :217-220 */
+            tmp.resize((size_t)n * d_rate);
+            for (unsigned int j = 0; j < d_rate; j++)
+                d_fft_filters[j]->filter(n, input_items[d_rate - j - 1], &tmp[(size_t)j * n]);
+        }
+        for (int i = 0; i < n; i++) {
+            if (!rot_fft) { /* work_fir_exp :143-151 / work_fft_exp :197-202 */
+                out[i] = 0;
+                if (filt_fft) {
+                    for (unsigned int j = 0; j < d_rate; j++)
+                        out[i] += tmp[(size_t)j * n + i] * d_rotator[j];
+                } else {
+                    for (int j = (int)d_rate - 1; j >= 0; j--)
+                        out[i] += d_fir_filters[j]->filter(&input_items[d_rate - 1 - j][i]) * d_rotator[j];
+                }
+            } else { /* work_fir_fft :164-176 / work_fft_fft :224-235 */
+                for (unsigned int j = 0; j < d_rate; j++)
+                    d_fft->get_inbuf()[j] =
+                        filt_fft ? tmp[(size_t)j * n + i] : d_fir_filters[j]->filter(&input_items[d_rate - 1 - j][i]);
+                d_fft->execute();
+                out[i] = d_fft->get_outbuf()[d_chan];
+            }
+        }
+        return n;
+    }
+};
+
 } // namespace
 
 extern "C" {
+
+/* pfb_decimator_ccf.  state: pass a pointer to a null void* for the first call and the same pointer afterwards to keep
+ * the FFT filters' overlap across calls (mode bit 1); free it with grref_pfb_decimator_free.  Returns n, <0 on error. */
+int grref_pfb_decimator_ccf(unsigned int decim, const float* taps, int ntaps, unsigned int channel, int mode,
+                            const void* const* in_streams, void* out, int noutput, void** state)
+{
+    try {
+        decimator_shell* d = state && *state ? (decimator_shell*)*state : nullptr;
+        if (!d) {
+            std::vector<float> t(taps, taps + ntaps);
+            d = new decimator_shell(decim, t, channel);
+        }
+        int r = noutput;
+        if ((mode & 2) && noutput % d->fft_nsamples() != 0)
+            r = -3;
+        else
+            d->work(mode, noutput, (const gr_complex* const*)in_streams, (gr_complex*)out);
+        if (state)
+            *state = d;
+        else
+            delete d;
+        return r;
+    } catch (const std::invalid_argument&) {
+        return -1;
+    }
+}
+void grref_pfb_decimator_free(void* state) { delete (decimator_shell*)state; }
+int grref_pfb_decimator_nsamples(unsigned int decim, const float* taps, int ntaps)
+{
+    std::vector<float> t(taps, taps + ntaps);
+    decimator_shell d(decim, t, 0);
+    return d.fft_nsamples();
+}
 
 /* fir_filter_blk_impl<gr_complex,gr_complex,float>::work (gr-filter/lib/fir_filter_blk_impl.cc:67-90):
  * in[] holds nout*decim + ntaps-1 items, in[0] = oldest history item. */

@@ -131,6 +131,15 @@ def ref_fixtures():
             y, ph = R.freq_xlating_fir(D, t, 0.3, 1.0, xin, len(fx["xlat_x"]) // D, chunk_out=1100 // D)
             fx["xlat_cc%s_d%d" % (tag, D)] = y
             fx["xlat_cc%s_d%d_phase" % (tag, D)] = np.complex64(ph)
+    # ---- pfb_decimator_ccf: the four work() variants of the reference on one input ----
+    rng3 = np.random.default_rng(20261106)
+    fx["pfbdec_x"] = crand(rng3, 5 * 920).reshape(5, 920)  # 920 = 4 output multiples of the FFT-filter variants
+    for ch in (0, 3):
+        for mode in range(4):
+            fx["pfbdec_c%d_m%d" % (ch, mode)] = R.pfb_decimator(5, fx["lp2_qa_taps"], ch, fx["pfbdec_x"], mode)
+    fx["pfbdec_b_x"] = crand(rng3, 8 * 500).reshape(8, 500)
+    fx["pfbdec_b_taps"] = rng3.uniform(-1, 1, 50).astype(np.float32)  # 50 taps over 8 branches: ragged last column
+    fx["pfbdec_b_c5"] = R.pfb_decimator(8, fx["pfbdec_b_taps"], 5, fx["pfbdec_b_x"], 0)
     return fx
 
 

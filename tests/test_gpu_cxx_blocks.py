@@ -16,7 +16,7 @@ LL = C.c_longlong
 @pytest.fixture(scope="module")
 def drv():
     lib = C.CDLL(os.path.join(ROOT, "gnuradio_b200", "cxx", "libgrb200_blocks.so"))
-    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run"):
+    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_pfb_dec_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run"):
         getattr(lib, f).restype = LL
     lib.grbx_what.restype = C.c_char_p
     return lib
@@ -104,3 +104,19 @@ def test_cxx_pfb(drv, orc):
         ref, _ = orc.pfb_channelizer(M, taps, osr, ins, nout, channel_map=cmap, nouts=nouts)
         assert_parity(outs, ref, "c++ pfb M=%d" % M)
     assert drv.grbx_pfb_run(36, p(taps), nt, C.c_float(10.1334), None, 0, inp, outp, 1, LL(0), 10, None) == -1
+
+
+def test_cxx_pfb_decimator(drv, orc):
+    rng = np.random.default_rng(7)
+    M, nt, n = 6, 100, 17 * 16 * 5
+    x = crand(rng, M * n).reshape(M, n)
+    taps = rng.uniform(-1, 1, nt).astype(np.float32)
+    ins = (C.c_void_p * M)(*[x[s].ctypes.data for s in range(M)])
+    ref = orc.pfb_decimator(M, taps, 4, x)
+    for rot, filt in ((0, 0), (1, 1)):  # history 17 / history 1 with the FFT filters' output multiple 64 - 17 + 1 = 48
+        out = np.zeros(n, np.complex64)
+        rc = drv.grbx_pfb_dec_run(M, p(taps), nt, 4, rot, filt, ins, p(out), LL(n), 480)
+        assert rc == (n if not filt else n // 48 * 48), drv.grbx_what()
+        assert_parity(out[:rc], ref[:rc], "c++ pfb_decimator rot=%d filt=%d" % (rot, filt), 2e-6, 2e-5)
+    rc = drv.grbx_pfb_dec_run(M, p(taps), nt, 6, 0, 0, ins, p(out), LL(n), 480)
+    assert rc == -1  # channel out of range -> std::invalid_argument

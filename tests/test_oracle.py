@@ -237,6 +237,59 @@ def test_channelizer_qa_tones(lay):
         np.testing.assert_allclose(rec / rec[0], exp / exp[0], atol=0.5e-3 * 2)
 
 
+def test_pfb_decimator_fixtures_and_closed_form(lay):
+    fx = fixtures()
+    taps, x = fx["lp2_qa_taps"], fx["pfbdec_x"]
+    for ch in (0, 3):
+        f64 = po.f64_pfb_decimator(5, taps, ch, x)
+        for mode in range(4 if lay.kind == "reference" else 1):
+            got = lay.pfb_decimator(5, taps, ch, x, mode)
+            assert_parity(got, fx["pfbdec_c%d_m%d" % (ch, mode)], "fixture ch %d mode %d" % (ch, mode), 1e-6, 1e-5)
+            assert_parity(got, f64[: len(got)], "f64 ch %d mode %d" % (ch, mode), 1e-6, 1e-5)
+        # the four variants of the reference agree with each other: one device kernel may stand for all of them
+        for mode in range(1, 4):
+            a, b = fx["pfbdec_c%d_m0" % ch], fx["pfbdec_c%d_m%d" % (ch, mode)]
+            assert_parity(b, a[: len(b)], "variant %d vs work_fir_exp" % mode, 1e-6, 1e-5)
+    got = lay.pfb_decimator(8, fx["pfbdec_b_taps"], 5, fx["pfbdec_b_x"])
+    assert_parity(got, fx["pfbdec_b_c5"], "ragged taps fixture", 1e-6, 1e-5)
+    assert_parity(got, po.f64_pfb_decimator(8, fx["pfbdec_b_taps"], 5, fx["pfbdec_b_x"]), "ragged taps f64", 1e-6, 1e-5)
+
+
+def pfb_decimator_qa_case(channel):
+    """gr-filter/python/filter/qa_pfb_decimator.py:22-76 (run_test): five tones, one per channel, summed at
+    ifs = M*fs and dealt round-robin onto M streams; returns (streams, taps_args, expected tone of the channel)."""
+    N, M, fs = 1000, 5, 5000.0
+    ifs = M * fs
+    freqs = [-230., 121., 110., -513., 203.]
+    Mch = ((len(freqs) - 1) // 2 + channel) % len(freqs)
+    x = np.zeros(N, np.complex128)
+    for i in range(M):
+        f = freqs[i] + (M // 2 - M + i + 1) * fs
+        x += np.array(sig_source_c(ifs, f, 1, N))
+    streams = x.astype(np.complex64).reshape(N // M, M).T.copy()  # stream_to_streams
+    phase = [0.11058476216852586, 4.5108246571401693, 3.9739891674564594, 2.2820531095511924,
+             1.3782797467397869][channel]
+    return streams, freqs[Mch], phase, fs
+
+
+def pfb_decimator_qa_expected(ntaps, L, f, phase, fs, M=5):
+    tpf = int(np.ceil(ntaps / float(M)))
+    delay = int(-(tpf - 1.0) / 2.0)
+    t = np.arange(delay, L + delay) / fs
+    return np.cos(2. * np.pi * f * t + phase) + 1j * np.sin(2. * np.pi * f * t + phase)
+
+
+@pytest.mark.parametrize("channel", [0, 1, 2, 3, 4])
+def test_pfb_decimator_qa_tones(lay, channel):
+    # qa_pfb_decimator.py:78-141 (test_000..004): last 50 outputs against the channel's tone, 4 places, all variants
+    taps = fixtures()["lp2_qa_taps"]  # low_pass_2(1, 25000, 2500, 500, 80, BLACKMAN_hARRIS), qa_pfb_decimator.py:29-31
+    streams, f, phase, fs = pfb_decimator_qa_case(channel)
+    for mode in range(4 if lay.kind == "reference" else 1):
+        got = lay.pfb_decimator(5, taps, channel, streams, mode)
+        exp = pfb_decimator_qa_expected(len(taps), len(got), f, phase, fs)
+        np.testing.assert_allclose(got[-50:], exp[-50:], atol=0.5e-4, rtol=0)
+
+
 def test_port_matches_reference_layer_on_fresh_data():
     if not po.have_ref():
         pytest.skip("oracle/_ref not built here")
