@@ -6,7 +6,9 @@
 // and differ only in rounding.  The device evaluates that sum directly: one pass over the M input streams, real-tap
 // branch dot products, one complex multiply per branch: 4T + 8 flops per INPUT item against its 8 bytes.
 #include <cstdint>
+#include <cstdlib>
 #include "capi_common.cuh"
+#include "tma.cuh"
 
 using namespace grb;
 
@@ -119,6 +121,113 @@ __global__ void __launch_bounds__(256) pfbdec_pair_kernel(const float2* __restri
     }
 }
 
+// Tiled kernel (T = 8, 16, 32, 64; aligned rows): a CTA walks the M streams of one tile of 256*R outputs.  Each stream's
+// NT+T-1 item row segment arrives by ONE TMA bulk copy into a two-deep shared-memory ring (the copy of stream s+2 is in
+// flight while s is multiplied); a thread owns R = 9 CONSECUTIVE outputs, so every item it loads (one 8-byte LDS) feeds
+// up to min(R, T) packed FMAs (fma.rn.f32x2: re and im together) -- (T+R-1)/R = 2.7 shared loads per output and stream
+// instead of T.  R is odd on purpose: lanes sit 2R = 18 words apart, which spreads a half-warp's 8-byte loads over all
+// 32 banks without padding, so the linear layout a bulk copy produces is already conflict-free.
+__device__ __forceinline__ void ffma2(float2& d, float2 a, float h)
+{
+    unsigned long long dd = *reinterpret_cast<unsigned long long*>(&d);
+    const unsigned long long aa = *reinterpret_cast<const unsigned long long*>(&a);
+    const float2 hh2 = make_float2(h, h);
+    const unsigned long long hh = *reinterpret_cast<const unsigned long long*>(&hh2);
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(dd) : "l"(aa), "l"(hh));
+    d = *reinterpret_cast<float2*>(&dd);
+}
+
+template <int TT>
+struct PfbDecTile {
+    static constexpr int R = 9, NTHR = 256, NT = R * NTHR;
+    static constexpr int SEG = (NT + TT + 1) & ~1; // items per ring slot (even: slots stay 16-byte aligned)
+    static constexpr int RING_BYTES = 2 * SEG * 8;
+};
+
+template <int TT>
+__global__ void __launch_bounds__(256) pfbdec_tile_kernel(const float2* __restrict__ X, long long stride,
+                                                          float2* __restrict__ out, long long nout, int M,
+                                                          const float* __restrict__ crev, const float2* __restrict__ rot)
+{
+    using G = PfbDecTile<TT>;
+    constexpr int R = G::R, NT = G::NT, SEG = G::SEG;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float2* ring = reinterpret_cast<float2*>(smem_raw);
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem_raw + G::RING_BYTES);
+    float2* srot = reinterpret_cast<float2*>(smem_raw + G::RING_BYTES + 16);
+    float* srev = reinterpret_cast<float*>(smem_raw + G::RING_BYTES + 16 + (size_t)M * 8);
+    const int t = threadIdx.x;
+    for (int k = t; k < M; k += blockDim.x)
+        srot[k] = rot[k];
+    for (int k = t; k < M * TT; k += blockDim.x)
+        srev[k] = crev[k];
+    if (t == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+    }
+    __syncthreads();
+    const long long ntiles = (nout + NT - 1) / NT;
+    unsigned ph = 0; // bit b = parity the next wait on bar[b] expects
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long i0 = tile * NT;
+        long long nit = stride - i0; // items of the row segment the copy may touch
+        nit = nit > SEG ? SEG : nit;
+        const unsigned bytes = (unsigned)(nit * 8);
+        auto issue = [&](int s) {
+            mbar_expect_tx(&bar[s & 1], bytes);
+            bulk_g2s(ring + (s & 1) * SEG, X + (long long)s * stride + i0, bytes, &bar[s & 1]);
+        };
+        if (t == 0) {
+            issue(0);
+            if (M > 1)
+                issue(1);
+        }
+        float2 acc[R];
+#pragma unroll
+        for (int r = 0; r < R; r++)
+            acc[r] = make_float2(0.f, 0.f);
+        for (int s = 0; s < M; s++) {
+            const int b = s & 1;
+            float h[TT];
+#pragma unroll
+            for (int q = 0; q < TT; q++)
+                h[q] = srev[s * TT + q];
+            mbar_wait(&bar[b], (ph >> b) & 1);
+            ph ^= 1u << b;
+            const float2* w = ring + b * SEG + t * R;
+            float2 a[R];
+#pragma unroll
+            for (int r = 0; r < R; r++)
+                a[r] = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < TT + R - 1; j++) {
+                const float2 v = w[j]; // item i0 + t*R + j: output r = j - q takes it with tap q
+#pragma unroll
+                for (int r = 0; r < R; r++) {
+                    const int q = j - r;
+                    if (q >= 0 && q < TT)
+                        ffma2(a[r], v, h[q]);
+                }
+            }
+            const float2 rr = srot[s];
+#pragma unroll
+            for (int r = 0; r < R; r++) {
+                acc[r].x = fmaf(a[r].x, rr.x, fmaf(-a[r].y, rr.y, acc[r].x));
+                acc[r].y = fmaf(a[r].x, rr.y, fmaf(a[r].y, rr.x, acc[r].y));
+            }
+            __syncthreads(); // every thread has read slot b
+            if (t == 0 && s + 2 < M)
+                issue(s + 2);
+        }
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const long long i = i0 + (long long)t * R + r;
+            if (i < nout)
+                out[i] = acc[r];
+        }
+    }
+}
+
 static int pfbdec_launch(const void* X, long long stride, void* out, long long nout, int M, int T, const float* crev,
                          const float2* rot, int nsm, cudaStream_t st)
 {
@@ -150,6 +259,35 @@ static int pfbdec_launch(const void* X, long long stride, void* out, long long n
         return 0;
     };
     const bool aligned = ((((uintptr_t)X) & 15) == 0) && (stride % 2 == 0);
+    static const bool use_tile = [] {
+        const char* e = getenv("GRB200_PFBDEC_TILE");
+        return !(e && e[0] == '0');
+    }();
+    auto launch_tile = [&](auto kern, int ring_bytes, int NT) -> int {
+        const size_t sm = (size_t)ring_bytes + 16 + smem;
+        GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        int occ = 1;
+        GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, sm));
+        long long nblk = (nout + NT - 1) / NT;
+        const long long fit = (long long)nsm * (occ < 1 ? 1 : occ);
+        if (nblk > fit)
+            nblk = fit;
+        kern<<<(unsigned)nblk, 256, sm, st>>>((const float2*)X, stride, (float2*)out, nout, M, crev, rot);
+        GRB_LAUNCH_CHECK();
+        return 0;
+    };
+    if (aligned && use_tile && nout >= 4 * PfbDecTile<16>::NT && smem <= 64 * 1024) {
+        switch (T) {
+        case 8:
+            return launch_tile(pfbdec_tile_kernel<8>, PfbDecTile<8>::RING_BYTES, PfbDecTile<8>::NT);
+        case 16:
+            return launch_tile(pfbdec_tile_kernel<16>, PfbDecTile<16>::RING_BYTES, PfbDecTile<16>::NT);
+        case 32:
+            return launch_tile(pfbdec_tile_kernel<32>, PfbDecTile<32>::RING_BYTES, PfbDecTile<32>::NT);
+        case 64:
+            return launch_tile(pfbdec_tile_kernel<64>, PfbDecTile<64>::RING_BYTES, PfbDecTile<64>::NT);
+        }
+    }
     if (aligned) {
         switch (T) {
         case 4:

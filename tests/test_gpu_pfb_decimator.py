@@ -147,3 +147,17 @@ def test_pfb_decimator_large_device_resident(grb):
         got = yd.cpu().numpy().view(np.complex64)
         assert_parity(got[:nn], ref[:nn], "2^22 device-resident, stride %d" % stride, 2e-6, 2e-5)
         assert np.all(got[nn:] == 0)
+
+
+@pytest.mark.parametrize("M,T,n", [(4, 8, 50001), (16, 32, 30000), (5, 64, 12345), (1, 16, 20000), (3, 16, 9216), (64, 16, 9217)])
+def test_pfb_decimator_tiled_kernel(grb, orc, M, T, n):
+    """Sizes that take the tiled kernel (TMA ring + register window, even T, >= 4 tiles): ragged last tile, a single
+    stream, odd stream counts (the two-slot ring ends on either slot), and the exact 4-tile threshold."""
+    rng = np.random.default_rng(M * 100 + T)
+    taps = rng.uniform(-1, 1, M * T).astype(np.float32) / np.float32(np.sqrt(M * T))
+    x = crand(rng, M * n).reshape(M, n)
+    chan = M // 2
+    got = run_block(grb.filter.pfb_decimator_ccf(M, taps, chan, False, False), x, max_noutput=1 << 20)
+    assert_parity(got, po.f64_pfb_decimator(M, taps, chan, x), "f64 %dx%d" % (M, T), 2e-6, 2e-5)
+    m = min(n, 20000)
+    assert_parity(got[:m], orc.pfb_decimator(M, taps, chan, x[:, :m]), "oracle %dx%d" % (M, T), 2e-6, 2e-5)
