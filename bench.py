@@ -305,7 +305,67 @@ class FftVccMagSq(Workload):
         self.cpu_lay.mag_squared(self.cpu_lay.fft_vcc(self.N, True, self.cpu_win, True, self.cpu_x))
 
 
-WORKLOADS = {"pfb": PfbChannelizer, "fir": FirCcf, "fftfilt": FftFilter, "firdec": FirLongDecim, "fftvcc": FftVccMagSq}
+class FreqXlating(FirCcf):
+    """freq_xlating_fir_filter_ccf, 128-tap channel filter, decimate by 8 (not a BASELINE config)."""
+    name = "freq_xlating_fir_filter_ccf 128 taps decim 8, 2^%d input samples per GPU x %d set(s) (section 8(f) row)"
+    block = "freq_xlating_fir_filter_ccf"
+    alg_bytes, flops, log2n, seed = 8.0 + 8.0 / 8, 128.0, 28, 6  # one read per input item, one write per output item
+    kernel = "fir_tiled_kernel + rotate_kernel"
+    ntaps, decim, nsets = 128, 8, 1
+
+    def setup(self):
+        self.taps = lowpass(self.ntaps, 0.05, hamming(self.ntaps))
+        self.blk = self.grb.filter.freq_xlating_fir_filter_ccf(self.decim, self.taps, 0.21, 1.0, device=self.device)
+        self.nout = self.n // self.decim
+        self.d_in = [self.rand_c64(self.n + self.ntaps - 1, self.seed)]
+        self.d_out = [self.torch.empty(2 * self.nout, dtype=self.torch.float32, device="cuda")]
+        self.launches_per_step = 2
+        self.samples_per_step = self.n
+
+    def cpu_call(self):
+        self.cpu_lay.freq_xlating_fir(self.decim, self.cpu_taps, 0.21, 1.0, self.cpu_x, self.cpu_nout)
+
+
+class PfbDecimator(Workload):
+    """pfb_decimator_ccf 64 branches x 16 taps (not a BASELINE config)."""
+    name = "pfb_decimator_ccf 64 branches x 16 taps, 2^%d input samples per GPU (section 8(f) row)"
+    block = "pfb_decimator_ccf"
+    alg_bytes, flops, log2n, seed = 8.0 * (1 + 1.0 / 64), 72.0, 28, 7
+    kernel = "pfbdec_tile_kernel"
+    M, T = 64, 16
+    ncu_dram_bytes_per_sample = (2.148e9 + 34.1e6) / (1 << 28)
+    ncu_source = "profiles/r1_pfbdec_tile_ncu.txt"
+
+    def setup(self):
+        M, T = self.M, self.T
+        self.taps = lowpass(M * T, 0.5 / M, blackman_harris(M * T))
+        self.blk = self.grb.filter.pfb_decimator_ccf(M, self.taps, 5, False, False, device=self.device)
+        self.nout = self.n // M
+        self.stride = (self.nout + T - 1 + 1) & ~1
+        self.d_in = self.rand_c64(M * self.stride, self.seed)
+        self.d_out = self.torch.empty(2 * self.nout, dtype=self.torch.float32, device="cuda")
+        self.samples_per_step = self.n
+
+    def step(self):
+        self.blk.work_dev(self.d_in.data_ptr(), self.stride, self.d_out.data_ptr(), self.nout, self.stream)
+
+    def describe(self):
+        return self.name % self.log2n
+
+    def cpu_setup(self, lay, log2n):
+        rng = np.random.default_rng(self.seed)
+        n = 1 << log2n
+        self.cpu_lay = lay
+        self.cpu_x = (rng.uniform(-1, 1, (self.M, n // self.M)) + 1j * rng.uniform(-1, 1, (self.M, n // self.M))).astype(np.complex64)
+        self.cpu_taps = lowpass(self.M * self.T, 0.5 / self.M, blackman_harris(self.M * self.T))
+        return n
+
+    def cpu_call(self):
+        self.cpu_lay.pfb_decimator(self.M, self.cpu_taps, 5, self.cpu_x)
+
+
+WORKLOADS = {"pfb": PfbChannelizer, "fir": FirCcf, "fftfilt": FftFilter, "firdec": FirLongDecim, "fftvcc": FftVccMagSq,
+             "xlat": FreqXlating, "pfbdec": PfbDecimator}
 
 
 # ---------------------------------------------------------------------------------------------------------

@@ -48,6 +48,7 @@ SIGNATURES = {
     "grb200_freq_xlating_fir_ccc_create": (i32, [i32, vp, i32, f64, f64, i32, pvp]),
     "grb200_freq_xlating_fir_set_taps": (i32, [vp, vp, i32]),
     "grb200_freq_xlating_fir_set_center_freq": (i32, [vp, f64]),
+    "grb200_freq_xlating_fir_advance": (i32, [vp, i64]),
     "grb200_freq_xlating_fir_center_freq": (f64, [vp]),
     "grb200_freq_xlating_fir_ntaps": (i32, [vp]),
     "grb200_freq_xlating_fir_decimation": (i32, [vp]),

@@ -347,6 +347,15 @@ int grb200_freq_xlating_fir_set_center_freq(grb200_xlat* x, double center_freq)
     return xlat_rebuild(x);
 }
 
+int grb200_freq_xlating_fir_advance(grb200_xlat* x, long long noutput)
+{
+    if (!x)
+        return fail(GRB200_EINVAL, "freq_xlating_fir_filter::advance: null handle");
+    std::lock_guard<std::mutex> lk(x->fir->mu);
+    x->fir->theta = rotate_advance(x->fir->theta, x->fir->delta, noutput);
+    return 0;
+}
+
 double grb200_freq_xlating_fir_center_freq(const grb200_xlat* x) { return x ? x->center_freq : 0.0; }
 int grb200_freq_xlating_fir_ntaps(const grb200_xlat* x) { return x ? grb200_fir_ntaps(x->fir) : 0; }
 int grb200_freq_xlating_fir_decimation(const grb200_xlat* x) { return x ? grb200_fir_decimation(x->fir) : 0; }

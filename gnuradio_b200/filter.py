@@ -176,6 +176,11 @@ class _freq_xlating_fir_filter(sync_decimator):
         if isinstance(v, (int, float)) and not isinstance(v, bool):
             self.set_center_freq(float(v))
 
+    def advance(self, noutput_items):
+        """Move the rotator on by noutput_items outputs without data: a shard that starts at output item n0 of the
+        stream (sharding.py) calls advance(n0) once so that its phase continues the global stream's."""
+        _lib.check(_lib.lib().grb200_freq_xlating_fir_advance(self._h, int(noutput_items)))
+
     def composite_taps(self):
         t = np.empty(len(self._proto_taps), np.complex64)
         _lib.check(_lib.lib().grb200_freq_xlating_fir_composite_taps(self._h, _ptr(t), len(t)))

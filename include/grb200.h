@@ -89,6 +89,9 @@ int grb200_freq_xlating_fir_ccc_create(int decim, const float* taps_re_im, int n
                                        double sampling_freq, int device, grb200_xlat** out);
 int grb200_freq_xlating_fir_set_taps(grb200_xlat* h, const float* taps, int ntaps); /* re/im pairs for ccc */
 int grb200_freq_xlating_fir_set_center_freq(grb200_xlat* h, double center_freq);
+/* Moves the rotator on as if `noutput` items had been produced (no data touched): a worker that takes over a stream at
+ * output item n0 -- time-segment sharding across GPUs, DESIGN.md section 6 -- calls this once with n0 (negative: back). */
+int grb200_freq_xlating_fir_advance(grb200_xlat* h, long long noutput);
 double grb200_freq_xlating_fir_center_freq(const grb200_xlat* h);
 int grb200_freq_xlating_fir_ntaps(const grb200_xlat* h);
 int grb200_freq_xlating_fir_decimation(const grb200_xlat* h);
