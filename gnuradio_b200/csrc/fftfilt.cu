@@ -251,11 +251,18 @@ struct UpolsGeom {
     static constexpr int TWF_BYTES = fft_tws_slots(L, false) * TPV * 8;
     static constexpr int TWR_BYTES = fft_tws_slots(L, true) * TPV * 8;
     static constexpr int SMEM = XIN_BYTES + S_BYTES + TWF_BYTES + TWR_BYTES + 32;
-    static constexpr int TMEM_COLS = (TPV / 128) * 32; // 32 columns per thread, 128 lanes
+    static constexpr int SLOT_COLS = (TPV / 128) * 32; // one parked spectrum: 32 columns per thread, 128 lanes
+    static __host__ __device__ constexpr int tmem_cols(int K) // power of two >= 32 (tcgen05.alloc)
+    {
+        int c = 32;
+        while (c < SLOT_COLS * (K - 1))
+            c *= 2;
+        return c;
+    }
 };
 
-template <int L>
-__global__ void __launch_bounds__(L / 16)
+template <int L, int K>
+__global__ void __launch_bounds__(L / 16, K == 2 ? 0 : 8192 / L) // K > 2: hold ptxas to 128 registers (two CTAs per SM)
 fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin,
                      int ntaps, int D, const float2* __restrict__ H, const float2* __restrict__ tw, long long run, int gs)
 {
@@ -297,7 +304,7 @@ fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, lo
 
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"(G::TMEM_COLS < 32 ? 32 : G::TMEM_COLS));
+                     "r"(G::tmem_cols(K)));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     if (t == 0) {
@@ -310,18 +317,23 @@ fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, lo
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;");
     const unsigned tmem = *tmem_slot;
-    // this thread's parking space: its own lane (sub-partition = warp % 4), 32 columns per group of four warps
-    const unsigned taddr = tmem + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)((warp >> 2) * 32);
+    // this thread's parking space: its own lane (sub-partition = warp % 4); per group of four warps K-1 slots of 32
+    // columns, slot (it mod K-1) holding the spectrum of the block of iteration `it`
+    constexpr int nslot = K - 1;
+    const unsigned taddr0 = tmem + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)((warp >> 2) * nslot * 32);
 
     if (b0 < b1) {
+        const long long bw = b0 - nslot; // first warm-up block: K-1 forward transforms fill the delay line
         if (t == 0) {
-            issue(b0 - 1);
-            issue(b0);
+            issue(bw);
+            issue(bw + 1);
         }
         unsigned ph = 0; // bit h = parity the next wait on bar[h] expects
-        for (long long blk = b0 - 1; blk < b1; blk++) {
+        int it = 0;
+        for (long long blk = bw; blk < b1; blk++, it++) {
             const int hnew = (int)((blk + 1) & 1);
-            if (blk == b0 - 1) {
+            const unsigned tnew = taddr0 + (unsigned)((it % nslot) * 32);
+            if (blk == bw) {
                 mbar_wait(&bar[hnew ^ 1], (ph >> (hnew ^ 1)) & 1);
                 ph ^= 1u << (hnew ^ 1);
             }
@@ -347,11 +359,11 @@ fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, lo
                 if (t == 0 && blk + 1 < b1)
                     issue(blk + 2); // into the half that held slice blk: every thread has read it by now
             });
-            if (blk == b0 - 1) { // warm-up: only park the spectrum
+            if (blk < b0) { // warm-up: only park the spectrum
 #pragma unroll
                 for (int c = 0; c < 4; c++)
                     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(
-                                     taddr + c * 8),
+                                     tnew + c * 8),
                                  "f"(v[4 * c].x), "f"(v[4 * c].y), "f"(v[4 * c + 1].x), "f"(v[4 * c + 1].y),
                                  "f"(v[4 * c + 2].x), "f"(v[4 * c + 2].y), "f"(v[4 * c + 3].x), "f"(v[4 * c + 3].y)
                                  : "memory");
@@ -359,47 +371,106 @@ fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, lo
                 __syncthreads(); // the transform's last gather is done before the next block reuses S
                 continue;
             }
-            // v = X_b . H0 + X_{b-1} . H1; X_b takes X_{b-1}'s place in tensor memory.  Four chunks of four values,
-            // software-pipelined: chunk c+1's TMEM read and its eight H values (L2) are in flight while chunk c is
-            // multiplied.  (The tcgen05 statements are volatile asm, so they keep their order among themselves; the
-            // wait lists the loaded registers as in/out operands so that no use of them can move above it.)
-            float2 xp[2][4], hh[2][8];
-            auto fetch = [&](int c) {
-                float2* x = xp[c & 1];
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-                             : "=f"(x[0].x), "=f"(x[0].y), "=f"(x[1].x), "=f"(x[1].y), "=f"(x[2].x), "=f"(x[2].y),
-                               "=f"(x[3].x), "=f"(x[3].y)
-                             : "r"(taddr + c * 8));
-#pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    const int i = 4 * c + e;
-                    const int k = (t + (i / RM) * TPV) + (i % RM) * (L / RM);
-                    hh[c & 1][2 * e] = __ldg(H + k);
-                    hh[c & 1][2 * e + 1] = __ldg(H + L + k);
+            if constexpr (K == 2) {
+                // v = X_b . H0 + X_{b-1} . H1; X_b takes X_{b-1}'s place in tensor memory.  Four chunks of four values,
+                // software-pipelined: chunk c+1's TMEM read and its eight H values (L2) are in flight while chunk c is
+                // multiplied.  (The tcgen05 statements are volatile asm, so they keep their order among themselves; the
+                // wait lists the loaded registers as in/out operands so that no use of them can move above it.)
+                float2 xp[2][4], hh[2][8];
+                auto fetch = [&](int c) {
+                    float2* x = xp[c & 1];
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                                 : "=f"(x[0].x), "=f"(x[0].y), "=f"(x[1].x), "=f"(x[1].y), "=f"(x[2].x), "=f"(x[2].y),
+                                   "=f"(x[3].x), "=f"(x[3].y)
+                                 : "r"(tnew + c * 8));
+    #pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        const int i = 4 * c + e;
+                        const int k = (t + (i / RM) * TPV) + (i % RM) * (L / RM);
+                        hh[c & 1][2 * e] = __ldg(H + k);
+                        hh[c & 1][2 * e + 1] = __ldg(H + L + k);
+                    }
+                };
+                fetch(0);
+    #pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    if (c < 3)
+                        fetch(c + 1);
+                    float2* x = xp[c & 1];
+                    float2* y = xp[(c + 1) & 1]; // listed too: the wait also completes the read just issued
+                    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                                 : "+f"(x[0].x), "+f"(x[0].y), "+f"(x[1].x), "+f"(x[1].y), "+f"(x[2].x), "+f"(x[2].y),
+                                   "+f"(x[3].x), "+f"(x[3].y), "+f"(y[0].x), "+f"(y[0].y), "+f"(y[1].x), "+f"(y[1].y),
+                                   "+f"(y[2].x), "+f"(y[2].y), "+f"(y[3].x), "+f"(y[3].y));
+                    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(
+                                     tnew + c * 8),
+                                 "f"(v[4 * c].x), "f"(v[4 * c].y), "f"(v[4 * c + 1].x), "f"(v[4 * c + 1].y),
+                                 "f"(v[4 * c + 2].x), "f"(v[4 * c + 2].y), "f"(v[4 * c + 3].x), "f"(v[4 * c + 3].y));
+    #pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        const int i = 4 * c + e;
+                        const float2 h0 = hh[c & 1][2 * e], h1 = hh[c & 1][2 * e + 1];
+                        const float2 a = v[i], p = x[e];
+                        v[i] = make_float2(fmaf(a.x, h0.x, fmaf(-a.y, h0.y, fmaf(p.x, h1.x, -p.y * h1.y))),
+                                           fmaf(a.x, h0.y, fmaf(a.y, h0.x, fmaf(p.x, h1.y, p.y * h1.x))));
+                    }
                 }
-            };
-            fetch(0);
-#pragma unroll
-            for (int c = 0; c < 4; c++) {
-                if (c < 3)
-                    fetch(c + 1);
-                float2* x = xp[c & 1];
-                float2* y = xp[(c + 1) & 1]; // listed too: the wait also completes the read just issued
-                asm volatile("tcgen05.wait::ld.sync.aligned;"
-                             : "+f"(x[0].x), "+f"(x[0].y), "+f"(x[1].x), "+f"(x[1].y), "+f"(x[2].x), "+f"(x[2].y),
-                               "+f"(x[3].x), "+f"(x[3].y), "+f"(y[0].x), "+f"(y[0].y), "+f"(y[1].x), "+f"(y[1].y),
-                               "+f"(y[2].x), "+f"(y[2].y), "+f"(y[3].x), "+f"(y[3].y));
-                asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(
-                                 taddr + c * 8),
-                             "f"(v[4 * c].x), "f"(v[4 * c].y), "f"(v[4 * c + 1].x), "f"(v[4 * c + 1].y),
-                             "f"(v[4 * c + 2].x), "f"(v[4 * c + 2].y), "f"(v[4 * c + 3].x), "f"(v[4 * c + 3].y));
-#pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    const int i = 4 * c + e;
-                    const float2 h0 = hh[c & 1][2 * e], h1 = hh[c & 1][2 * e + 1];
-                    const float2 a = v[i], p = x[e];
-                    v[i] = make_float2(fmaf(a.x, h0.x, fmaf(-a.y, h0.y, fmaf(p.x, h1.x, -p.y * h1.y))),
-                                       fmaf(a.x, h0.y, fmaf(a.y, h0.x, fmaf(p.x, h1.y, p.y * h1.x))));
+            } else {
+                // v = X_b . H_0 + sum_p X_{b-p} . H_p, p = 1..K-1; X_b then takes the oldest spectrum's slot.  Four chunks
+                // of four values x (K-1) parked spectra = 4(K-1) steps, software-pipelined: step q+1's TMEM read and its H
+                // values (L2) are in flight while step q is multiplied.  (The tcgen05 statements are volatile asm and keep
+                // their order among themselves; the wait lists the loaded registers as in/out operands so that no use of
+                // them can move above it.)
+                constexpr int NQ = 4 * nslot;
+                const int sbase = it % nslot;
+                float2 xp[2][4], hp[2][4], h0[2][4];
+                auto fetch = [&](int q) {
+                    const int c = q / nslot, p = q % nslot + 1, bf = q & 1;
+                    const int sl = (sbase + nslot - (p % nslot)) % nslot; // slot of iteration it - p
+                    float2* x = xp[bf];
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                                 : "=f"(x[0].x), "=f"(x[0].y), "=f"(x[1].x), "=f"(x[1].y), "=f"(x[2].x), "=f"(x[2].y),
+                                   "=f"(x[3].x), "=f"(x[3].y)
+                                 : "r"(taddr0 + (unsigned)(sl * 32 + c * 8)));
+    #pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        const int i = 4 * c + e;
+                        const int k = (t + (i / RM) * TPV) + (i % RM) * (L / RM);
+                        hp[bf][e] = __ldg(H + (long long)p * L + k);
+                        if (p == 1)
+                            h0[bf][e] = __ldg(H + k);
+                    }
+                };
+                fetch(0);
+                float2 acc[4];
+    #pragma unroll
+                for (int q = 0; q < NQ; q++) {
+                    const int c = q / nslot, p = q % nslot + 1, bf = q & 1;
+                    if (q + 1 < NQ)
+                        fetch(q + 1);
+                    float2* x = xp[bf];
+                    float2* y = xp[bf ^ 1]; // listed too: the wait also completes the read just issued
+                    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                                 : "+f"(x[0].x), "+f"(x[0].y), "+f"(x[1].x), "+f"(x[1].y), "+f"(x[2].x), "+f"(x[2].y),
+                                   "+f"(x[3].x), "+f"(x[3].y), "+f"(y[0].x), "+f"(y[0].y), "+f"(y[1].x), "+f"(y[1].y),
+                                   "+f"(y[2].x), "+f"(y[2].y), "+f"(y[3].x), "+f"(y[3].y));
+    #pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        if (p == 1)
+                            acc[e] = cmul(v[4 * c + e], h0[bf][e]);
+                        acc[e].x = fmaf(x[e].x, hp[bf][e].x, fmaf(-x[e].y, hp[bf][e].y, acc[e].x));
+                        acc[e].y = fmaf(x[e].x, hp[bf][e].y, fmaf(x[e].y, hp[bf][e].x, acc[e].y));
+                    }
+                    if (p == nslot) {
+                        // slot it mod K-1 held X_{b-(K-1)}, read just above
+                        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(
+                                         tnew + c * 8),
+                                     "f"(v[4 * c].x), "f"(v[4 * c].y), "f"(v[4 * c + 1].x), "f"(v[4 * c + 1].y),
+                                     "f"(v[4 * c + 2].x), "f"(v[4 * c + 2].y), "f"(v[4 * c + 3].x), "f"(v[4 * c + 3].y));
+    #pragma unroll
+                        for (int e = 0; e < 4; e++)
+                            v[4 * c + e] = acc[e];
+                    }
                 }
             }
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
@@ -426,16 +497,15 @@ fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, lo
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
     if (warp == 0)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem),
-                     "r"(G::TMEM_COLS < 32 ? 32 : G::TMEM_COLS));
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(G::tmem_cols(K)));
 }
 
-template <int L>
-static int launch_upols(const void* in, void* out, long long nout, long long nin, int ntaps, int D, const float2* H,
-                        const float2* tw, int nsm, cudaStream_t st)
+template <int L, int K>
+static int launch_upols(const void* in, void* out, long long nout, long long nin, int ntaps, int D,
+                        const float2* H, const float2* tw, int nsm, cudaStream_t st)
 {
     using G = UpolsGeom<L>;
-    auto kern = fftfilt_upols_kernel<L>;
+    auto kern = fftfilt_upols_kernel<L, K>;
     GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
     int occ = 1;
     GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, L / 16, G::SMEM));
@@ -445,7 +515,7 @@ static int launch_upols(const void* in, void* out, long long nout, long long nin
     // co-schedules as many CTAs as registers, shared memory and the 512 TMEM columns allow (checked with ncu).
     cudaFuncAttributes fa;
     GRB_CUDA(cudaFuncGetAttributes(&fa, kern));
-    int by_regs = 65536 / (fa.numRegs * (L / 16)), by_smem = (227 * 1024) / (G::SMEM + 1024), by_tmem = 512 / G::TMEM_COLS;
+    int by_regs = 65536 / (fa.numRegs * (L / 16)), by_smem = (227 * 1024) / (G::SMEM + 1024), by_tmem = 512 / G::tmem_cols(K);
     int fit = by_regs < by_smem ? by_regs : by_smem;
     fit = fit < by_tmem ? fit : by_tmem;
     if (const char* e = getenv("GRB200_FFTFILT_UPOLS_OCC"))
@@ -476,12 +546,15 @@ int fftfilt_device_plan(int ntaps, int* parts)
         L = 16384; // > 25 % of every block would be overlap: the longer transform wins (cfg2: 70 -> 78 Gsps)
     const char* ue = getenv("GRB200_FFTFILT_UPOLS"); // 0 = never, 1 = whenever the geometry allows, unset = auto
     const int upols = ue ? atoi(ue) : -1;
-    if (upols != 0 && L == 16384 && ntaps <= 4096) {
-        L = 4096; // the 16384-point transform is the slow one: two partitions on the 4096-point kernel instead
-        K = 2;
-    } else if (upols == 1 && ntaps > 1025 && ntaps <= 4096) {
+    // 2050..10240 taps: K = ceil(ntaps / 2048) partitions on the 4096-point kernel (K-1 <= 4 parked spectra fit in the
+    // 512 TMEM columns of an SM at two CTAs) beat the 16384-point transform; below 2050 plain overlap-save is faster.
+    const int kneed = (ntaps + 2047) / 2048;
+    if (upols != 0 && L == 16384 && kneed <= 5) {
         L = 4096;
-        K = 2;
+        K = kneed < 2 ? 2 : kneed;
+    } else if (upols == 1 && ntaps > 1025 && kneed <= 5) {
+        L = 4096;
+        K = kneed < 2 ? 2 : kneed;
     }
     if (const char* e = getenv("GRB200_FFTFILT_L")) { // tuning knob: a longer transform wastes less on the overlap
         const int v = atoi(e);
@@ -501,11 +574,21 @@ int fftfilt_launch(int L, int parts, const void* in, void* out, long long nout, 
     if (nout <= 0)
         return 0;
     const long long nin = nout * D + ntaps - 1;
-    if (parts == 2) {
+    if (parts >= 2) {
         if ((((uintptr_t)in) & 7) != 0)
             return fail(GRB200_EINVAL, "fft_filter: input stream is not aligned to its item size");
-        if (L == 4096)
-            return launch_upols<4096>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+        if (L == 4096) {
+            switch (parts) {
+            case 2:
+                return launch_upols<4096, 2>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+            case 3:
+                return launch_upols<4096, 3>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+            case 4:
+                return launch_upols<4096, 4>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+            case 5:
+                return launch_upols<4096, 5>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+            }
+        }
         return fail(GRB200_ERANGE, "fft_filter: no partitioned kernel for fft length %d", L);
     }
     static const bool use_stream = [] {

@@ -336,10 +336,11 @@ def test_fft_filter_many_blocks_per_cta(grb, orc, ntaps, decim):
     assert_parity(got[:n_c], orc.fft_filter_ccc(decim, taps, x[: n_c * decim]), "oracle prefix")
 
 
-@pytest.mark.parametrize("ntaps,decim", [(4096, 1), (4095, 1), (3001, 2), (2050, 1), (1026, 5), (2049, 1)])
+@pytest.mark.parametrize("ntaps,decim", [(4096, 1), (4095, 1), (3001, 2), (2050, 1), (1026, 5), (2049, 1), (4097, 1), (6000, 3),
+                                         (8192, 1), (10240, 1)])
 def test_fft_filter_partitioned_kernel(grb, orc, monkeypatch, ntaps, decim):
-    """Two tap partitions on the 4096-point kernel, previous spectrum parked in tensor memory (the default plan for
-    2050..4096 taps; forced here for shorter filters too).  2^21 samples = many blocks per CTA run plus a ragged tail;
+    """K = ceil(ntaps/2048) tap partitions on the 4096-point kernel, the K-1 previous spectra parked in tensor memory (the
+    default plan for 2050..10240 taps; forced here for shorter filters too).  2^21 samples = many blocks per CTA run plus a ragged tail;
     odd and even tap counts give odd and even slice bases for the TMA ring."""
     import scipy.signal
 

@@ -10,7 +10,7 @@ rng = np.random.default_rng(0)
 xd = torch.randn(2 * (n + 16384), dtype=torch.float32, device="cuda")
 yd = torch.empty(2 * n, dtype=torch.float32, device="cuda")
 ts = torch.cuda.Stream()
-for nt in [int(a) for a in sys.argv[1:]] or [1026, 1500, 2049, 2050, 3000, 4096]:
+for nt in [int(a) for a in sys.argv[1:]] or [1026, 1500, 2049, 2050, 3000, 4096, 6000, 8192, 10240]:
     for mode in ("0", "1"):
         os.environ["GRB200_FFTFILT_UPOLS"] = mode
         taps = ((rng.uniform(-1, 1, nt) + 1j * rng.uniform(-1, 1, nt)) / nt).astype(np.complex64)
