@@ -36,6 +36,14 @@ SIGNATURES = {
     "grb200_fir_work": (i32, [vp, vp, vp, i64]),
     "grb200_fir_work_dev": (i32, [vp, vp, vp, i64, vp]),
     "grb200_fir_destroy": (None, [vp]),
+    "grb200_interp_fir_ccf_create": (i32, [C.c_uint, vp, i32, i32, pvp]),
+    "grb200_interp_fir_ccc_create": (i32, [C.c_uint, vp, i32, i32, pvp]),
+    "grb200_interp_fir_set_taps": (i32, [vp, vp, i32]),
+    "grb200_interp_fir_taps_per_filter": (i32, [vp]),
+    "grb200_interp_fir_interpolation": (i32, [vp]),
+    "grb200_interp_fir_work": (i32, [vp, vp, vp, i64]),
+    "grb200_interp_fir_work_dev": (i32, [vp, vp, vp, i64, vp]),
+    "grb200_interp_fir_destroy": (None, [vp]),
     "grb200_pfb_dec_ccf_create": (i32, [C.c_uint, vp, i32, C.c_uint, i32, pvp]),
     "grb200_pfb_dec_set_taps": (i32, [vp, vp, i32]),
     "grb200_pfb_dec_set_channel": (i32, [vp, C.c_uint]),

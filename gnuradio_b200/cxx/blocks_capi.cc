@@ -183,6 +183,41 @@ long long grbx_pfb_run(unsigned nfilts, const float* taps, int ntaps, float osr,
     });
 }
 
+// interp_fir_filter_ccf/ccc over a fresh stream of nin items (no history in front): returns items produced
+long long grbx_interp_fir_run(int complex_taps, unsigned interpolation, const float* taps, int ntaps, const void* in,
+                              void* out, long long nin, int chunk_in)
+{
+    return guarded([&]() -> long long {
+        auto drive = [&](auto& b) -> long long {
+            const long long hist = b->history();
+            std::vector<gr_complex> buf((size_t)(hist - 1), gr_complex(0, 0));
+            buf.insert(buf.end(), (const gr_complex*)in, (const gr_complex*)in + nin);
+            long long done = 0;
+            while (done < nin) {
+                const long long n = std::min<long long>(chunk_in, nin - done);
+                gr_vector_const_void_star ii(1, buf.data() + done);
+                gr_vector_void_star oo(1, (gr_complex*)out + done * interpolation);
+                gr_vector_int ni(1, 0);
+                const int r = b->general_work((int)(n * interpolation), ni, ii, oo);
+                if (r <= 0)
+                    break;
+                done += b->nitems_consumed_last();
+            }
+            return done * interpolation;
+        };
+        if (complex_taps) {
+            std::vector<gr_complex> t((const gr_complex*)taps, (const gr_complex*)taps + ntaps);
+            auto b = gr::filter::interp_fir_filter_ccc::make(interpolation, t);
+            return drive(b);
+        }
+        std::vector<float> t(taps, taps + ntaps);
+        auto b = gr::filter::interp_fir_filter_ccf::make(interpolation, t);
+        if ((int)b->taps().size() != (ntaps + (int)interpolation - 1) / (int)interpolation * (int)interpolation)
+            throw std::logic_error("interp_fir_filter_ccf: taps() must return the padded taps");
+        return drive(b);
+    });
+}
+
 // pfb_decimator_ccf over in_streams[s] (no history in front: a fresh stream), scheduler-sized calls
 long long grbx_pfb_dec_run(unsigned decim, const float* taps, int ntaps, unsigned channel, int use_fft_rotator,
                            int use_fft_filters, const void* const* in_streams, void* out, long long nitems, int chunk)

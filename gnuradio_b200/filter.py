@@ -9,6 +9,8 @@
   pfb_channelizer_ccf               gr-filter/include/gnuradio/filter/pfb_channelizer_ccf.h:100-192,
                                     gr-filter/lib/pfb_channelizer_ccf_impl.cc:34-193
   pfb.channelizer_ccf               gr-filter/python/filter/pfb.py:23-50 (hier block; stream_to_streams absorbed)
+  interp_fir_filter_ccf/ccc         gr-filter/include/gnuradio/filter/interp_fir_filter.h:43-72,
+                                    gr-filter/lib/interp_fir_filter_impl.cc:24-152
   pfb_decimator_ccf                 gr-filter/include/gnuradio/filter/pfb_decimator_ccf.h:94-138,
                                     gr-filter/lib/pfb_decimator_ccf_impl.cc:24-257
 
@@ -21,7 +23,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from .runtime import as_items, block, io_signature, sync_block, sync_decimator
+from .runtime import as_items, block, io_signature, sync_block, sync_decimator, sync_interpolator
 
 _c64 = np.dtype(np.complex64)
 
@@ -244,6 +246,88 @@ class freq_xlating_fir_filter_ccf(_freq_xlating_fir_filter):
 class freq_xlating_fir_filter_ccc(_freq_xlating_fir_filter):
     _complex_taps = True
     _name = "freq_xlating_fir_filter_ccc"
+
+
+class _interp_fir_filter(sync_interpolator):
+    """interp_fir_filter: `interpolation` polyphase FIRs over one input stream, outputs interleaved.  set_taps() is
+    picked up by the next work(), which installs the taps, re-declares the history and returns 0
+    (interp_fir_filter_impl.cc:72-90, 136-139)."""
+    _complex_taps = False
+    _name = "interp_fir_filter"
+
+    def __init__(self, interpolation, taps, device=0):
+        L = _lib.lib()
+        if int(interpolation) <= 0:
+            raise IndexError("interp_fir_filter_impl: interpolation must be > 0")  # std::out_of_range, :46-48
+        t = self._conv_taps(taps)
+        sync_interpolator.__init__(self, self._name, io_signature.make(1, 1, 8), io_signature.make(1, 1, 8),
+                                   interpolation)
+        self._h = C.c_void_p()
+        create = L.grb200_interp_fir_ccc_create if self._complex_taps else L.grb200_interp_fir_ccf_create
+        _lib.check(create(int(interpolation), _ptr(t), len(t), int(device), C.byref(self._h)))
+        self._new_taps = self._padded(t)
+        self.d_updated = False
+        self.set_history(L.grb200_interp_fir_taps_per_filter(self._h))  # install_taps, :115
+
+    @classmethod
+    def make(cls, interpolation, taps, device=0):
+        return cls(interpolation, taps, device)
+
+    def _conv_taps(self, taps):
+        t = np.ascontiguousarray(taps, np.complex64 if self._complex_taps else np.float32)
+        if t.ndim != 1 or t.size < 1:
+            raise RuntimeError("interp_fir_filter_impl: no filter taps provided.")  # std::runtime_error, :50-52
+        return t
+
+    def _padded(self, t):  # :78-84: rounded up to a multiple of the interpolation with zeros
+        n = (-len(t)) % self.interpolation()
+        return np.concatenate([t, np.zeros(n, t.dtype)])
+
+    def set_taps(self, taps):
+        self._new_taps = self._padded(self._conv_taps(taps))
+        self.d_updated = True
+
+    def taps(self):
+        return self._new_taps.tolist()  # d_new_taps, padding included (:120-124)
+
+    def work(self, noutput_items, input_items, output_items):
+        L = _lib.lib()
+        if self.d_updated:  # :136-139
+            _lib.check(L.grb200_interp_fir_set_taps(self._h, _ptr(self._new_taps), len(self._new_taps)))
+            self.set_history(L.grb200_interp_fir_taps_per_filter(self._h))
+            self.d_updated = False
+            return 0
+        n = int(noutput_items)
+        ni = n // self.interpolation()
+        n = ni * self.interpolation()
+        xin = as_items(input_items[0], _c64, ni + self.history() - 1 if n else 0, "input_items[0]")
+        out = as_items(output_items[0], _c64, n, "output_items[0]")
+        _lib.check(L.grb200_interp_fir_work(self._h, _ptr(xin), _ptr(out), n))
+        return n
+
+    def work_dev(self, in_dev, out_dev, noutput_items, stream=0):
+        """Device-resident mode: in_dev/out_dev are device addresses; asynchronous on `stream`."""
+        _lib.check(_lib.lib().grb200_interp_fir_work_dev(self._h, C.c_void_p(in_dev), C.c_void_p(out_dev),
+                                                         int(noutput_items), C.c_void_p(stream)))
+        return int(noutput_items)
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().grb200_interp_fir_destroy(h)
+            except Exception:
+                pass
+
+
+class interp_fir_filter_ccf(_interp_fir_filter):
+    _complex_taps = False
+    _name = "interp_fir_filter_ccf"
+
+
+class interp_fir_filter_ccc(_interp_fir_filter):
+    _complex_taps = True
+    _name = "interp_fir_filter_ccc"
 
 
 class fft_filter_ccc(sync_decimator):

@@ -120,6 +120,33 @@ class sync_decimator(sync_block):
         return self._decimation
 
 
+class sync_interpolator(sync_block):
+    """gr::sync_interpolator: noutput is a multiple of the interpolation, ninput = noutput / interpolation."""
+
+    def __init__(self, name, in_sig, out_sig, interpolation):
+        super().__init__(name, in_sig, out_sig)
+        self._interpolation = int(interpolation)
+        self.set_relative_rate(float(interpolation))
+        self.set_output_multiple(self._interpolation)
+
+    def interpolation(self):
+        return self._interpolation
+
+    def forecast(self, noutput_items, ninputs):
+        return [self.fixed_rate_noutput_to_ninput(noutput_items)] * ninputs
+
+    def fixed_rate_noutput_to_ninput(self, noutput_items):
+        return noutput_items // self._interpolation + self.history() - 1
+
+    def fixed_rate_ninput_to_noutput(self, ninput_items):
+        return max(0, ninput_items - self.history() + 1) * self._interpolation
+
+    def general_work(self, noutput_items, ninput_items, input_items, output_items):
+        r = self.work(noutput_items, input_items, output_items)
+        self.consume_each(r // self._interpolation if r > 0 else 0)
+        return r
+
+
 def as_items(a, dtype, min_items, what):
     """Borrowed host buffer check: contiguous, right dtype, at least min_items items."""
     if not isinstance(a, np.ndarray) or a.dtype != dtype or not a.flags["C_CONTIGUOUS"]:

@@ -183,6 +183,25 @@ int grb200_pfb_dec_work_dev(grb200_pfbdec* h, const void* x_dev, long long strid
                             void* stream);
 void grb200_pfb_dec_destroy(grb200_pfbdec* h);
 
+/* ---- interp_fir_filter_ccf / interp_fir_filter_ccc -------------------------------------------------
+ * Replaces gr::filter::interp_fir_filter_impl<gr_complex,gr_complex,float|gr_complex>
+ *   set_taps / install_taps  gr-filter/lib/interp_fir_filter_impl.cc:72-117 (zero-pad to a multiple of the
+ *                            interpolation, xtaps[n][k] = taps[n + k*interpolation], history = taps per phase)
+ *   work                     gr-filter/lib/interp_fir_filter_impl.cc:128-152
+ *       out[i*interpolation + n] = firs[n].filter(&in[i])
+ * in: noutput/interpolation + taps_per_filter-1 items, history first; noutput must be a multiple of the interpolation
+ * (sync_interpolator).  A zero interpolation returns GRB200_ERANGE (std::out_of_range in the reference, :46-48). */
+typedef struct grb200_interp grb200_interp;
+int grb200_interp_fir_ccf_create(unsigned int interpolation, const float* taps, int ntaps, int device, grb200_interp** out);
+int grb200_interp_fir_ccc_create(unsigned int interpolation, const float* taps_re_im, int ntaps, int device,
+                                 grb200_interp** out);
+int grb200_interp_fir_set_taps(grb200_interp* h, const float* taps, int ntaps); /* re/im pairs for ccc */
+int grb200_interp_fir_taps_per_filter(const grb200_interp* h);
+int grb200_interp_fir_interpolation(const grb200_interp* h);
+int grb200_interp_fir_work(grb200_interp* h, const void* in_host, void* out_host, long long noutput);
+int grb200_interp_fir_work_dev(grb200_interp* h, const void* in_dev, void* out_dev, long long noutput, void* stream);
+void grb200_interp_fir_destroy(grb200_interp* h);
+
 /* ---- fft_vcc (+ complex_to_mag_squared) --------------------------------------------------------
  * Replaces gr::fft::fft_complex (gr-fft/lib/fft.cc:151-203) and fft_vcc_fftw: ctor/set_window
  * gr-fft/lib/fft_vcc_fftw.cc:33-61, work :63-122; and complex_to_mag_squared_impl::work

@@ -124,6 +124,27 @@ public:
 private:
     unsigned d_decimation;
 };
+class sync_interpolator : public sync_block
+{
+public:
+    sync_interpolator(const std::string& name, io_signature in, io_signature out, unsigned interpolation)
+        : sync_block(name, in, out), d_interpolation(interpolation)
+    {
+        set_relative_rate((double)interpolation);
+        set_output_multiple((int)interpolation); // sync_interpolator.cc:27-33
+    }
+    unsigned interpolation() const { return d_interpolation; }
+    int general_work(int noutput_items, gr_vector_int&, gr_vector_const_void_star& input_items,
+                     gr_vector_void_star& output_items) override
+    {
+        int r = work(noutput_items, input_items, output_items); // sync_interpolator.cc:57-66
+        consume_each(r > 0 ? r / (int)d_interpolation : 0);
+        return r;
+    }
+
+private:
+    unsigned d_interpolation;
+};
 } // namespace rt
 } // namespace grb200
 #endif
@@ -288,6 +309,81 @@ private:
 };
 typedef freq_xlating_fir_filter<gr_complex, gr_complex, float> freq_xlating_fir_filter_ccf;
 typedef freq_xlating_fir_filter<gr_complex, gr_complex, gr_complex> freq_xlating_fir_filter_ccc;
+
+// ---------------------------------------------------------------------------------------------------
+// interp_fir_filter<gr_complex, gr_complex, float|gr_complex>  (interp_fir_filter_ccf / _ccc)
+// gr-filter/include/gnuradio/filter/interp_fir_filter.h:43-72, lib/interp_fir_filter_impl.cc
+// ---------------------------------------------------------------------------------------------------
+template <class IN_T, class OUT_T, class TAP_T>
+class interp_fir_filter : public grb200::rt::sync_interpolator
+{
+    static_assert(std::is_same<IN_T, gr_complex>::value && std::is_same<OUT_T, gr_complex>::value &&
+                      (std::is_same<TAP_T, float>::value || std::is_same<TAP_T, gr_complex>::value),
+                  "libgrb200 re-hosts the ccf and ccc instantiations (SURVEY.md section 8)");
+
+public:
+    typedef std::shared_ptr<interp_fir_filter<IN_T, OUT_T, TAP_T>> sptr;
+
+    static sptr make(unsigned interpolation, const std::vector<TAP_T>& taps)
+    {
+        if (interpolation == 0) // :46-48
+            throw std::out_of_range("interp_fir_filter_impl: interpolation must be > 0");
+        if (taps.empty()) // :50-52
+            throw std::runtime_error("interp_fir_filter_impl: no filter taps provided.");
+        return sptr(new interp_fir_filter<IN_T, OUT_T, TAP_T>(interpolation, taps));
+    }
+
+    ~interp_fir_filter() override { grb200_interp_fir_destroy(d_h); }
+
+    void set_taps(const std::vector<TAP_T>& taps) // :72-90: padded to a multiple of the interpolation
+    {
+        d_new_taps = taps;
+        d_updated = true;
+        int n = taps.size() % this->interpolation();
+        if (n > 0) {
+            n = this->interpolation() - n;
+            while (n-- > 0)
+                d_new_taps.insert(d_new_taps.end(), 0);
+        }
+    }
+    std::vector<TAP_T> taps() const { return d_new_taps; }
+
+    int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
+    {
+        if (d_updated) { // :136-139: install_taps, history requirements may have changed
+            grb200::check(grb200_interp_fir_set_taps(d_h, reinterpret_cast<const float*>(d_new_taps.data()),
+                                                     (int)d_new_taps.size()));
+            set_history(grb200_interp_fir_taps_per_filter(d_h));
+            d_updated = false;
+            return 0;
+        }
+        grb200::check(grb200_interp_fir_work(d_h, input_items[0], output_items[0], noutput_items));
+        return noutput_items;
+    }
+
+    grb200_interp* handle() { return d_h; } // device-resident chaining (grb200_interp_fir_work_dev)
+
+private:
+    interp_fir_filter(unsigned interpolation, const std::vector<TAP_T>& taps)
+        : sync_interpolator(std::is_same<TAP_T, float>::value ? "interp_fir_filter_ccf" : "interp_fir_filter_ccc",
+                            grb200::rt::io_signature::make(1, 1, sizeof(IN_T)),
+                            grb200::rt::io_signature::make(1, 1, sizeof(OUT_T)), interpolation)
+    {
+        set_taps(taps);
+        const float* t = reinterpret_cast<const float*>(d_new_taps.data());
+        if (std::is_same<TAP_T, float>::value)
+            grb200::check(grb200_interp_fir_ccf_create(interpolation, t, (int)d_new_taps.size(), grb200::default_device(), &d_h));
+        else
+            grb200::check(grb200_interp_fir_ccc_create(interpolation, t, (int)d_new_taps.size(), grb200::default_device(), &d_h));
+        set_history(grb200_interp_fir_taps_per_filter(d_h)); // install_taps, :115
+        d_updated = false;
+    }
+    grb200_interp* d_h = nullptr;
+    std::vector<TAP_T> d_new_taps;
+    bool d_updated = false;
+};
+typedef interp_fir_filter<gr_complex, gr_complex, float> interp_fir_filter_ccf;
+typedef interp_fir_filter<gr_complex, gr_complex, gr_complex> interp_fir_filter_ccc;
 
 // ---------------------------------------------------------------------------------------------------
 // fft_filter_ccc

@@ -443,6 +443,45 @@ int grbo_pfb_channelizer_ccf(unsigned int nfilts, const float* taps, int ntaps, 
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * interp_fir_filter_impl<gr_complex,gr_complex,float|gr_complex> (gr-filter/lib/interp_fir_filter_impl.cc):
+ * set_taps :72-90 pads the taps with zeros to a multiple of the interpolation L; install_taps :97-117 deals them
+ * round-robin, xtaps[n][k] = taps[n + k*L], history = taps per phase T; work :128-152 writes
+ * out[i*L + n] = firs[n].filter(&in[i]) = sum_t rev_n[t] * in[i + t] with rev_n[t] = xtaps[n][T-1-t].
+ * in: ni + T-1 items, history first.  Returns T.
+ * ---------------------------------------------------------------------------------------------- */
+int grbo_interp_fir(int cplx_taps, unsigned int interpolation, const float* taps, int ntaps, const cf32* in, cf32* out,
+                    long ni)
+{
+    if (interpolation == 0)
+        return -1;
+    if (ntaps < 1)
+        return -2;
+    const int L = (int)interpolation, T = (ntaps + L - 1) / L;
+    for (long i = 0; i < ni; i++) {
+        for (int n = 0; n < L; n++) {
+            float re = 0.0f, im = 0.0f;
+            for (int t = 0; t < T; t++) {
+                const int k = n + (T - 1 - t) * L; /* index into the padded prototype */
+                if (k >= ntaps)
+                    continue;
+                const cf32 x = in[i + t];
+                if (cplx_taps) {
+                    const float hr = taps[2 * k], hi = taps[2 * k + 1];
+                    re += x.re * hr - x.im * hi;
+                    im += x.re * hi + x.im * hr;
+                } else {
+                    re += x.re * taps[k];
+                    im += x.im * taps[k];
+                }
+            }
+            out[i * L + n].re = re;
+            out[i * L + n].im = im;
+        }
+    }
+    return T;
+}
+
+/* ------------------------------------------------------------------------------------------------
  * pfb_decimator_ccf_impl::work_fir_exp (gr-filter/lib/pfb_decimator_ccf_impl.cc:135-154) over
  * polyphase_filterbank::set_taps (gr-filter/lib/polyphase_filterbank.cc:53-81):
  *   out[i] = sum_{j=M-1..0} fir_j(&in_{M-1-j}[i]) * rot[j],  taps_j[t] = padded[j + t*M],

@@ -165,6 +165,19 @@ class _CLib:
             raise ValueError("pfb_channelizer_ccf oracle error %d" % rc)
         return outs, rc
 
+    # -- interp_fir_filter_ccf / ccc ----------------------------------------------------------------
+    def interp_fir(self, interpolation, taps, x):
+        """Fresh stream x (zero history): returns len(x)*interpolation output items."""
+        taps = np.ascontiguousarray(taps)
+        cplx = bool(np.iscomplexobj(taps))
+        t = _c64(taps) if cplx else np.ascontiguousarray(taps, np.float32)
+        T = -(-len(t) // interpolation)
+        xin = _headroom(np.concatenate([np.zeros(T - 1, np.complex64), _c64(x)]))
+        out = np.empty(len(x) * interpolation, np.complex64)
+        rc = self._f("interp_fir")(int(cplx), C.c_uint(interpolation), _p(t), len(t), _p(xin), _p(out), C.c_long(len(x)))
+        assert rc == T, rc
+        return out
+
     # -- pfb_decimator_ccf ------------------------------------------------------------------------
     def pfb_decimator(self, decim, taps, channel, streams, mode=0):
         """streams: [decim][n] fresh input streams (zero history).  mode bit 0 = use_fft_rotator, bit 1 =
@@ -333,6 +346,17 @@ def f64_channelizer(nfilts, taps, x, nout, osr=1.0):
         y = np.convolve(x, g)[: len(x)]
         out[c] = y[P] * np.exp(-2j * np.pi * c * ((o + 2) * R % M) / M)
     return out
+
+
+def f64_interp_fir(interpolation, taps, x):
+    """y = taps (*) zero-stuffed x: y[m] = sum_k taps[k] u[m-k], u[i*L] = x[i] (what qa_interp_fir_filter.py:24-45 spells
+    out digit by digit)."""
+    L = interpolation
+    x = np.asarray(x, np.complex128)
+    u = np.zeros(len(x) * L, np.complex128)
+    u[::L] = x
+    t = np.asarray(taps, np.complex128 if np.iscomplexobj(taps) else np.float64)
+    return np.convolve(u, t)[: len(u)]
 
 
 def f64_pfb_decimator(decim, taps, channel, streams):

@@ -255,6 +255,48 @@ int grref_freq_xlating_fir(int cplx_taps, int decim, const float* taps, int ntap
     return 0;
 }
 
+/* interp_fir_filter_impl<gr_complex,gr_complex,float|gr_complex> (gr-filter/lib/interp_fir_filter_impl.cc): the block
+ * class needs the runtime (sync_interpolator), so set_taps (:72-90), install_taps (:97-117) and work (:128-152) are
+ * restated over the reference's OWN kernel::fir_filter objects.  in: ni + taps_per_filter-1 items, history first;
+ * out: ni*interpolation items.  Returns taps per filter, <0 on the reference's exceptions. */
+int grref_interp_fir(int cplx_taps, unsigned interpolation, const float* taps, int ntaps, const void* in, void* out, long ni)
+{
+    if (interpolation == 0)
+        return -1; /* std::out_of_range, :46-48 */
+    if (ntaps < 1)
+        return -2; /* std::runtime_error, :50-52 */
+    const int padded = (int)((ntaps + interpolation - 1) / interpolation * interpolation);
+    const int nt = padded / (int)interpolation;
+    const gr_complex* x = (const gr_complex*)in;
+    gr_complex* y = (gr_complex*)out;
+    if (cplx_taps) {
+        std::vector<std::vector<gr_complex>> xt(interpolation, std::vector<gr_complex>(nt, gr_complex(0, 0)));
+        for (int i = 0; i < ntaps; i++)
+            xt[i % interpolation][i / interpolation] = gr_complex(taps[2 * i], taps[2 * i + 1]);
+        std::vector<fir_filter_ccc*> firs(interpolation);
+        for (unsigned n = 0; n < interpolation; n++)
+            firs[n] = new fir_filter_ccc(1, xt[n]);
+        for (long i = 0; i < ni; i++)
+            for (unsigned nf = 0; nf < interpolation; nf++)
+                y[i * interpolation + nf] = firs[nf]->filter(&x[i]);
+        for (auto f : firs)
+            delete f;
+    } else {
+        std::vector<std::vector<float>> xt(interpolation, std::vector<float>(nt, 0.f));
+        for (int i = 0; i < ntaps; i++)
+            xt[i % interpolation][i / interpolation] = taps[i];
+        std::vector<fir_filter_ccf*> firs(interpolation);
+        for (unsigned n = 0; n < interpolation; n++)
+            firs[n] = new fir_filter_ccf(1, xt[n]);
+        for (long i = 0; i < ni; i++)
+            for (unsigned nf = 0; nf < interpolation; nf++)
+                y[i * interpolation + nf] = firs[nf]->filter(&x[i]);
+        for (auto f : firs)
+            delete f;
+    }
+    return nt;
+}
+
 /* fft_filter_ccc_impl::work driven like the scheduler does (gr-filter/lib/fft_filter_ccc_impl.cc:61-78):
  * one filter() call per chunk of `chunk_out` output items (rounded down to a multiple of nsamples,
  * at least one block).  nitems must be a multiple of nsamples; consumes nitems*decim inputs.

@@ -140,6 +140,13 @@ def ref_fixtures():
     fx["pfbdec_b_x"] = crand(rng3, 8 * 500).reshape(8, 500)
     fx["pfbdec_b_taps"] = rng3.uniform(-1, 1, 50).astype(np.float32)  # 50 taps over 8 branches: ragged last column
     fx["pfbdec_b_c5"] = R.pfb_decimator(8, fx["pfbdec_b_taps"], 5, fx["pfbdec_b_x"], 0)
+    # ---- interp_fir_filter_ccf / ccc ----
+    rng4 = np.random.default_rng(20261107)
+    fx["interp_x"] = crand(rng4, 1500)
+    fx["interp_taps_f"] = rng4.uniform(-1, 1, 50).astype(np.float32)  # 50 taps over 4 phases: zero-padded to 52
+    fx["interp_taps_c"] = crand(rng4, 33)
+    fx["interp_ccf_l4"] = R.interp_fir(4, fx["interp_taps_f"], fx["interp_x"])
+    fx["interp_ccc_l3"] = R.interp_fir(3, fx["interp_taps_c"], fx["interp_x"])
     return fx
 
 

@@ -16,7 +16,7 @@ LL = C.c_longlong
 @pytest.fixture(scope="module")
 def drv():
     lib = C.CDLL(os.path.join(ROOT, "gnuradio_b200", "cxx", "libgrb200_blocks.so"))
-    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_pfb_dec_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run"):
+    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_pfb_dec_run", "grbx_interp_fir_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run"):
         getattr(lib, f).restype = LL
     lib.grbx_what.restype = C.c_char_p
     return lib
@@ -120,3 +120,16 @@ def test_cxx_pfb_decimator(drv, orc):
         assert_parity(out[:rc], ref[:rc], "c++ pfb_decimator rot=%d filt=%d" % (rot, filt), 2e-6, 2e-5)
     rc = drv.grbx_pfb_dec_run(M, p(taps), nt, 6, 0, 0, ins, p(out), LL(n), 480)
     assert rc == -1  # channel out of range -> std::invalid_argument
+
+
+def test_cxx_interp_fir(drv, orc):
+    rng = np.random.default_rng(8)
+    x = crand(rng, 5000)
+    for ct, L, nt in ((0, 4, 50), (1, 3, 33)):
+        taps = crand(rng, nt) if ct else rng.uniform(-1, 1, nt).astype(np.float32)
+        out = np.zeros(L * len(x), np.complex64)
+        rc = drv.grbx_interp_fir_run(ct, L, p(taps), nt, p(x), p(out), LL(len(x)), 1024)
+        assert rc == L * len(x), drv.grbx_what()
+        assert_parity(out, orc.interp_fir(L, taps, x), "c++ interp_fir ct=%d" % ct, 2e-6, 2e-5)
+    rc = drv.grbx_interp_fir_run(0, 0, p(taps), 4, p(x), p(out), LL(10), 1024)
+    assert rc == -2  # std::out_of_range

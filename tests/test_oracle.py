@@ -290,6 +290,27 @@ def test_pfb_decimator_qa_tones(lay, channel):
         np.testing.assert_allclose(got[-50:], exp[-50:], atol=0.5e-4, rtol=0)
 
 
+INTERP_QA_TAPS = [1, 10, 100, 1000, 10000]  # gr-filter/python/filter/qa_interp_fir_filter.py:25-35 (test_fff)
+INTERP_QA_SRC = (0, 2, 3, 5, 7, 11, 13, 17)
+INTERP_QA_EXPECTED = (0, 0, 0, 2, 20, 200, 2003, 20030, 300, 3005, 30050, 500, 5007, 50070, 700, 7011, 70110,
+                      1100, 11013, 110130, 1300, 13017, 130170)
+
+
+def test_interp_fir_qa_golden_and_fixtures(lay):
+    # the QA's only case is the fff instantiation; the same integers through the complex-stream blocks must come out
+    # exactly (every partial sum is an integer below 2^24), on the real and on the imaginary rail
+    src = np.array(INTERP_QA_SRC, np.float32)
+    exp = np.array(INTERP_QA_EXPECTED, np.float32)
+    for taps in (np.array(INTERP_QA_TAPS, np.float32), np.array(INTERP_QA_TAPS, np.complex64)):
+        got = lay.interp_fir(3, taps, (src + 1j * 2 * src).astype(np.complex64))
+        assert np.array_equal(got[: len(exp)].real, exp) and np.array_equal(got[: len(exp)].imag, 2 * exp)
+    fx = fixtures()
+    for key, L, tk in (("interp_ccf_l4", 4, "interp_taps_f"), ("interp_ccc_l3", 3, "interp_taps_c")):
+        got = lay.interp_fir(L, fx[tk], fx["interp_x"])
+        assert_parity(got, fx[key], key, 1e-6, 1e-5)
+        assert_parity(got, po.f64_interp_fir(L, fx[tk], fx["interp_x"]), key + " f64", 1e-6, 1e-5)
+
+
 def test_port_matches_reference_layer_on_fresh_data():
     if not po.have_ref():
         pytest.skip("oracle/_ref not built here")
