@@ -252,6 +252,7 @@ struct grb200_xlat {
     bool cplx_taps = false;
     std::vector<std::complex<float>> proto;
     double center_freq = 0.0, sampling_freq = 1.0;
+    std::mutex mu; // serialises the setters (the FIR handle's own mutex orders them against work())
 };
 
 // build_composite_fir(), freq_xlating_fir_filter_impl.cc:74-93, float arithmetic as written there
@@ -335,6 +336,7 @@ int grb200_freq_xlating_fir_set_taps(grb200_xlat* x, const float* taps, int ntap
 {
     if (!x || !taps || ntaps < 1)
         return fail(GRB200_EINVAL, "freq_xlating_fir_filter::set_taps: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
     xlat_store_proto(x, taps, ntaps);
     return xlat_rebuild(x);
 }
@@ -343,6 +345,7 @@ int grb200_freq_xlating_fir_set_center_freq(grb200_xlat* x, double center_freq)
 {
     if (!x)
         return fail(GRB200_EINVAL, "freq_xlating_fir_filter::set_center_freq: null handle");
+    std::lock_guard<std::mutex> lk(x->mu);
     x->center_freq = center_freq;
     return xlat_rebuild(x);
 }
