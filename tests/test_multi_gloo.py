@@ -71,6 +71,61 @@ def _worker(rank, world, port, case, outdir):
             full = full[:, seg.out_begin:seg.out_end]
             np.save(os.path.join(outdir, "ok_%d.npy" % rank), np.array([np.array_equal(y, full)]))
             return
+        elif case == "xlat":
+            # freq_xlating_fir_filter: FIR halo as above + the rotator taken over at the segment's first output
+            # (grb200_freq_xlating_fir_advance on the device; the phase handed to the oracle here)
+            ntaps, D, nout_total, fc, fs = 29, 4, 3000, 1.5e3, 48e3
+            taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
+            x = (rng.uniform(-1, 1, nout_total * D) + 1j * rng.uniform(-1, 1, nout_total * D)).astype(np.complex64)
+            seg = sharding.segment(rank, world, nout_total, decimation=D, history=ntaps)
+            buf = np.zeros(seg.halo + seg.ninput, np.complex64)
+            buf[seg.halo:] = x[seg.in_begin:seg.in_end]
+            tbuf = _c64_to_t(buf)
+            head, tail = tbuf[: 2 * seg.halo], tbuf[-2 * seg.halo:].clone()
+            sharding.exchange_halo(dist, head, tail, rank, world)
+            delta = po.xlat_increment_angle(np.float32(2 * np.pi * fc / fs), D)
+            y, _ = orc.freq_xlating_fir(D, taps, fc, fs, tbuf.numpy().view(np.complex64), seg.noutput,
+                                        phase=np.exp(1j * delta * seg.out_begin))
+            xin = np.concatenate([np.zeros(ntaps - 1, np.complex64), x])
+            full, _ = orc.freq_xlating_fir(D, taps, fc, fs, xin, nout_total)
+            # the float phasor recurrence restarted mid-stream rounds differently: equal to a few ulp, not bit for bit
+            ok = np.allclose(y, full[seg.out_begin:seg.out_end], atol=2e-5, rtol=0)
+            np.save(os.path.join(outdir, "ok_%d.npy" % rank), np.array([ok]))
+            return
+        elif case == "pfbdec":
+            # pfb_decimator_ccf: M input streams, each sharded in time with its own T-1 item halo
+            M, T, nout_total = 6, 7, 1200
+            taps = rng.uniform(-1, 1, M * T - 3).astype(np.float32)
+            xs = (rng.uniform(-1, 1, (M, nout_total)) + 1j * rng.uniform(-1, 1, (M, nout_total))).astype(np.complex64)
+            seg = sharding.segment(rank, world, nout_total, history=T)
+            bufs = []
+            for m in range(M):
+                b = np.zeros(seg.halo + seg.ninput, np.complex64)
+                b[seg.halo:] = xs[m, seg.in_begin:seg.in_end]
+                bufs.append(_c64_to_t(b))
+            pairs = [(t[: 2 * seg.halo], t[-2 * seg.halo:].clone()) for t in bufs]
+            sharding.exchange_halos(dist, pairs, rank, world)
+            streams = np.stack([t.numpy().view(np.complex64) for t in bufs])
+            # the oracle wrapper prepends T-1 zeros itself: drop the outputs those produce, keep the segment's
+            y = orc.pfb_decimator(M, taps, 2, streams)[seg.halo:]
+            full = orc.pfb_decimator(M, taps, 2, xs)
+        elif case == "interp":
+            # interp_fir_filter: sharded on INPUT positions (T-1 item halo); rank r owns outputs [in_begin*L, in_end*L)
+            L, ntaps, nin_total = 4, 30, 2000
+            taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
+            T = -(-ntaps // L)
+            x = (rng.uniform(-1, 1, nin_total) + 1j * rng.uniform(-1, 1, nin_total)).astype(np.complex64)
+            seg = sharding.segment(rank, world, nin_total, history=T)
+            buf = np.zeros(seg.halo + seg.ninput, np.complex64)
+            buf[seg.halo:] = x[seg.in_begin:seg.in_end]
+            tbuf = _c64_to_t(buf)
+            head, tail = tbuf[: 2 * seg.halo], tbuf[-2 * seg.halo:].clone()
+            sharding.exchange_halo(dist, head, tail, rank, world)
+            y = orc.interp_fir(L, taps, tbuf.numpy().view(np.complex64))[seg.halo * L:]
+            full = orc.interp_fir(L, taps, x)
+            np.save(os.path.join(outdir, "ok_%d.npy" % rank),
+                    np.array([np.array_equal(y, full[seg.out_begin * L:seg.out_end * L])]))
+            return
         else:
             raise AssertionError(case)
         np.save(os.path.join(outdir, "ok_%d.npy" % rank),
@@ -80,7 +135,7 @@ def _worker(rank, world, port, case, outdir):
 
 
 @pytest.mark.parametrize("world", [2, 3])
-@pytest.mark.parametrize("case", ["fir", "pfb"])
+@pytest.mark.parametrize("case", ["fir", "pfb", "xlat", "pfbdec", "interp"])
 def test_segments_plus_halo_equal_single_stream(tmp_path, world, case):
     mp.spawn(_worker, args=(world, _free_port(), case, str(tmp_path)), nprocs=world, join=True)
     for r in range(world):
