@@ -44,6 +44,17 @@ SIGNATURES = {
     "grb200_interp_fir_work": (i32, [vp, vp, vp, i64]),
     "grb200_interp_fir_work_dev": (i32, [vp, vp, vp, i64, vp]),
     "grb200_interp_fir_destroy": (None, [vp]),
+    "grb200_rational_resampler_ccf_create": (i32, [C.c_uint, C.c_uint, vp, i32, i32, pvp]),
+    "grb200_rational_resampler_ccc_create": (i32, [C.c_uint, C.c_uint, vp, i32, i32, pvp]),
+    "grb200_rational_resampler_set_taps": (i32, [vp, vp, i32]),
+    "grb200_rational_resampler_taps_per_filter": (i32, [vp]),
+    "grb200_rational_resampler_interpolation": (C.c_uint, [vp]),
+    "grb200_rational_resampler_decimation": (C.c_uint, [vp]),
+    "grb200_rational_resampler_ctr": (C.c_uint, [vp]),
+    "grb200_rational_resampler_set_ctr": (i32, [vp, C.c_uint]),
+    "grb200_rational_resampler_work": (i32, [vp, vp, i64, vp, i64, vp, vp]),
+    "grb200_rational_resampler_work_dev": (i32, [vp, vp, i64, vp, i64, vp, vp, vp]),
+    "grb200_rational_resampler_destroy": (None, [vp]),
     "grb200_pfb_dec_ccf_create": (i32, [C.c_uint, vp, i32, C.c_uint, i32, pvp]),
     "grb200_pfb_dec_set_taps": (i32, [vp, vp, i32]),
     "grb200_pfb_dec_set_channel": (i32, [vp, C.c_uint]),

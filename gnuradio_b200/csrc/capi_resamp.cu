@@ -1,0 +1,292 @@
+// capi_resamp.cu -- rational_resampler_base_ccf / _ccc (gr-filter/lib/rational_resampler_base_impl.cc): kernel + C-ABI.
+//
+// The reference keeps `interpolation` polyphase FIRs, xtaps[n][k] = taps[n + k*interpolation] (install_taps :97-117), and
+// walks a phase counter: out[i] = firs[ctr].filter(in); ctr += decimation; every time ctr wraps past the interpolation
+// the input pointer advances (general_work :151-173).  In closed form, with s_i = ctr0 + i*decimation:
+//     out[i] = sum_t rev[s_i % L][t] * in[s_i / L + t],   consumed = s_n / L,   ctr' = s_n % L
+// so every output is independent.  A thread owns one output item: phase and window start from one 64-bit divide, phase
+// taps from shared memory, window through the read-only path (neighbouring outputs share all but D/L of their window, so
+// L1 serves the re-reads).  8*D/L + 8 algorithmic bytes per output item.
+#include <cstdint>
+#include "capi_common.cuh"
+
+using namespace grb;
+
+namespace grb {
+
+// rev[(p*T + t) * ES + e]: reversed taps of phase p (fir_filter.cc:62-64), ES = 1 (real) or 2 (complex)
+template <bool CT>
+__global__ void __launch_bounds__(256) resamp_kernel(const float2* __restrict__ in, float2* __restrict__ out,
+                                                     long long nout, unsigned ctr0, unsigned L, unsigned D, int T,
+                                                     const float* __restrict__ rev)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* sh = reinterpret_cast<float*>(smem_raw);
+    constexpr int ES = CT ? 2 : 1;
+    for (int k = threadIdx.x; k < (int)L * T * ES; k += blockDim.x)
+        sh[k] = rev[k];
+    __syncthreads();
+    const long long step = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nout; i += step) {
+        const unsigned long long s = (unsigned long long)ctr0 + (unsigned long long)i * D;
+        const unsigned long long q = s / L;
+        const unsigned p = (unsigned)(s - q * L);
+        const float2* x = in + q;
+        const float* h = sh + (size_t)p * T * ES;
+        float2 a = make_float2(0.f, 0.f);
+#pragma unroll 4
+        for (int t = 0; t < T; t++) {
+            const float2 v = __ldg(x + t);
+            if (CT) {
+                const float hr = h[2 * t], hi = h[2 * t + 1];
+                a.x = fmaf(v.x, hr, fmaf(-v.y, hi, a.x));
+                a.y = fmaf(v.x, hi, fmaf(v.y, hr, a.y));
+            } else {
+                a.x = fmaf(v.x, h[t], a.x);
+                a.y = fmaf(v.y, h[t], a.y);
+            }
+        }
+        out[i] = a;
+    }
+}
+
+static int resamp_launch(bool ct, const void* in, void* out, long long nout, unsigned ctr0, unsigned L, unsigned D, int T,
+                         const float* rev, int nsm, cudaStream_t st)
+{
+    if (nout <= 0)
+        return 0;
+    const size_t smem = (size_t)L * T * (ct ? 8 : 4);
+    if (smem > 200 * 1024)
+        return fail(GRB200_ERANGE, "rational_resampler_base: %u x %d taps do not fit in shared memory", L, T);
+    long long nblk = (nout + 255) / 256;
+    const long long cap = (long long)nsm * 8;
+    if (nblk > cap)
+        nblk = cap;
+    auto launch = [&](auto kern) -> int {
+        if (smem > 48 * 1024)
+            GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<(unsigned)nblk, 256, smem, st>>>((const float2*)in, (float2*)out, nout, ctr0, L, D, T, rev);
+        GRB_LAUNCH_CHECK();
+        return 0;
+    };
+    return ct ? launch(resamp_kernel<true>) : launch(resamp_kernel<false>);
+}
+
+} // namespace grb
+
+struct grb200_resamp {
+    int device = 0;
+    bool ct = false;
+    unsigned L = 1, D = 1, ctr = 0; // interpolation, decimation, d_ctr
+    int T = 0, ntaps = 0;           // taps per phase, taps as given
+    DevBuf rev;
+    Stager sg;
+    std::mutex mu;
+};
+
+static int resamp_upload(grb200_resamp* h, const float* taps, int ntaps)
+{
+    // set_taps (:77-93): pad with zeros to a multiple of the interpolation; install_taps (:97-117): deal round-robin
+    const int L = (int)h->L, es = h->ct ? 2 : 1;
+    const int T = (ntaps + L - 1) / L;
+    std::vector<float> rev((size_t)L * T * es, 0.f);
+    for (int i = 0; i < ntaps; i++) {
+        const int p = i % L, k = i / L; // xtaps[p][k]
+        for (int e = 0; e < es; e++)
+            rev[((size_t)p * T + (T - 1 - k)) * es + e] = taps[(size_t)i * es + e];
+    }
+    int rc = h->rev.upload(rev.data(), rev.size() * sizeof(float));
+    if (rc)
+        return rc;
+    h->T = T;
+    h->ntaps = ntaps;
+    return 0;
+}
+
+static int resamp_create(bool ct, unsigned interpolation, unsigned decimation, const float* taps, int ntaps, int device,
+                         grb200_resamp** out)
+{
+    if (!out)
+        return fail(GRB200_EINVAL, "rational_resampler_base: null output handle");
+    *out = nullptr;
+    if (interpolation == 0) // std::out_of_range in the reference (:46-48)
+        return fail(GRB200_ERANGE, "rational_resampler_base_impl: interpolation must be > 0");
+    if (decimation == 0) // std::out_of_range in the reference (:49-51)
+        return fail(GRB200_ERANGE, "rational_resampler_base_impl: decimation must be > 0");
+    if (ntaps < 1 || !taps)
+        return fail(GRB200_EINVAL, "rational_resampler_base_impl: no filter taps provided.");
+    std::unique_ptr<grb200_resamp> h(new grb200_resamp);
+    h->device = device;
+    h->ct = ct;
+    h->L = interpolation;
+    h->D = decimation;
+    int rc = h->sg.init(device);
+    if (rc)
+        return rc;
+    if ((rc = resamp_upload(h.get(), taps, ntaps)))
+        return rc;
+    *out = h.release();
+    return 0;
+}
+
+// the loop of general_work (:160-169) in closed form: outputs i = 0.. while i < noutput and s_i / L < nin
+static void resamp_counts(const grb200_resamp* h, long long nin, long long noutput, long long* produced,
+                          long long* consumed, unsigned* ctr_after)
+{
+    const unsigned long long L = h->L, D = h->D, c0 = h->ctr;
+    long long n = 0;
+    if (nin > 0 && noutput > 0) {
+        const unsigned long long room = (unsigned long long)nin * L - c0; // c0 < L <= nin*L
+        const unsigned long long fit = (room + D - 1) / D;
+        n = (long long)std::min<unsigned long long>(fit, (unsigned long long)noutput);
+    }
+    const unsigned long long s = c0 + (unsigned long long)n * D;
+    *produced = n;
+    *consumed = (long long)(s / L);
+    *ctr_after = (unsigned)(s % L);
+}
+
+extern "C" {
+
+int grb200_rational_resampler_ccf_create(unsigned int interpolation, unsigned int decimation, const float* taps, int ntaps,
+                                         int device, grb200_resamp** out)
+{
+    return resamp_create(false, interpolation, decimation, taps, ntaps, device, out);
+}
+int grb200_rational_resampler_ccc_create(unsigned int interpolation, unsigned int decimation, const float* taps_re_im,
+                                         int ntaps, int device, grb200_resamp** out)
+{
+    return resamp_create(true, interpolation, decimation, taps_re_im, ntaps, device, out);
+}
+
+int grb200_rational_resampler_set_taps(grb200_resamp* h, const float* taps, int ntaps)
+{
+    if (!h || !taps || ntaps < 1)
+        return fail(GRB200_EINVAL, "rational_resampler_base::set_taps: bad arguments");
+    std::lock_guard<std::mutex> lk(h->mu);
+    int rc = use_device(h->device);
+    if (rc)
+        return rc;
+    GRB_CUDA(cudaDeviceSynchronize()); // kernels in flight still read the old taps
+    return resamp_upload(h, taps, ntaps);
+}
+
+int grb200_rational_resampler_taps_per_filter(const grb200_resamp* h) { return h ? h->T : 0; }
+unsigned int grb200_rational_resampler_interpolation(const grb200_resamp* h) { return h ? h->L : 0; }
+unsigned int grb200_rational_resampler_decimation(const grb200_resamp* h) { return h ? h->D : 0; }
+unsigned int grb200_rational_resampler_ctr(const grb200_resamp* h) { return h ? h->ctr : 0; }
+
+int grb200_rational_resampler_set_ctr(grb200_resamp* h, unsigned int ctr)
+{
+    if (!h || ctr >= h->L)
+        return fail(GRB200_EINVAL, "rational_resampler_base::set_ctr: the phase counter must be below the interpolation");
+    std::lock_guard<std::mutex> lk(h->mu);
+    h->ctr = ctr;
+    return 0;
+}
+
+// in: nin + taps_per_filter-1 readable items; out: room for noutput items
+int grb200_rational_resampler_work_dev(grb200_resamp* h, const void* in_dev, long long nin, void* out_dev,
+                                       long long noutput, long long* consumed, long long* produced, void* stream)
+{
+    if (!h || nin < 0 || noutput < 0 || !consumed || !produced)
+        return fail(GRB200_EINVAL, "rational_resampler_base::work_dev: bad arguments");
+    std::lock_guard<std::mutex> lk(h->mu);
+    unsigned ctr_after;
+    long long n, used;
+    resamp_counts(h, nin, noutput, &n, &used, &ctr_after);
+    if (n > 0 && (!in_dev || !out_dev))
+        return fail(GRB200_EINVAL, "rational_resampler_base::work_dev: null buffer");
+    int rc = use_device(h->device);
+    if (rc)
+        return rc;
+    rc = resamp_launch(h->ct, in_dev, out_dev, n, h->ctr, h->L, h->D, h->T, (const float*)h->rev.p, sm_count(h->device),
+                       pick_stream(stream, h->sg));
+    if (rc)
+        return rc;
+    h->ctr = ctr_after;
+    *consumed = used;
+    *produced = n;
+    return 0;
+}
+
+int grb200_rational_resampler_work(grb200_resamp* h, const void* in_host, long long nin, void* out_host, long long noutput,
+                                   long long* consumed, long long* produced)
+{
+    if (!h || nin < 0 || noutput < 0 || !consumed || !produced)
+        return fail(GRB200_EINVAL, "rational_resampler_base::work: bad arguments");
+    std::lock_guard<std::mutex> lk(h->mu);
+    unsigned ctr_after;
+    long long n, used;
+    resamp_counts(h, nin, noutput, &n, &used, &ctr_after);
+    *consumed = 0;
+    *produced = 0;
+    if (n > 0) {
+        if (!in_host || !out_host)
+            return fail(GRB200_EINVAL, "rational_resampler_base::work: null buffer");
+        int rc = use_device(h->device);
+        if (rc)
+            return rc;
+        const unsigned long long L = h->L, D = h->D, c0 = h->ctr;
+        const int T = h->T;
+        // outputs per chunk: bound both the output bytes and the input span (n*D/L items) of a chunk
+        long long chunk = (long long)(kChunkBytes / 8);
+        if (D > L)
+            chunk = std::max<long long>(1, (long long)((unsigned long long)chunk * L / D));
+        if (chunk > n)
+            chunk = n;
+        const long long nchunks = (n + chunk - 1) / chunk;
+        const long long span = (long long)(((unsigned long long)chunk * D + L - 1) / L) + 1 + T; // input items per chunk
+        Stager& sg = h->sg;
+        if ((rc = sg.reserve_dev(0, (size_t)span * 8)) || (rc = sg.reserve_dev(1, (size_t)chunk * 8)))
+            return rc;
+        const float2* in = (const float2*)in_host;
+        float2* out = (float2*)out_host;
+        auto geom = [&](long long c, long long* o0, long long* no, unsigned long long* q0, unsigned* cc, long long* nitems) {
+            *o0 = c * chunk;
+            *no = std::min(chunk, n - *o0);
+            const unsigned long long s0 = c0 + (unsigned long long)*o0 * D;
+            const unsigned long long sl = c0 + (unsigned long long)(*o0 + *no - 1) * D;
+            *q0 = s0 / L;
+            *cc = (unsigned)(s0 % L);
+            *nitems = (long long)(sl / L - *q0) + T; // first window start .. last window end
+        };
+        rc = sg.run(
+            nchunks,
+            [&](long long c, int slot, Stager::Chunk& ch) {
+                long long o0, no, nitems;
+                unsigned long long q0;
+                unsigned cc;
+                geom(c, &o0, &no, &q0, &cc, &nitems);
+                ch.h2d.push_back({ in + q0, sg.dev[slot][0], (size_t)nitems * 8 });
+                ch.d2h.push_back({ sg.dev[slot][1], out + o0, (size_t)no * 8 });
+                return 0;
+            },
+            [&](long long c, int slot, cudaStream_t st) {
+                long long o0, no, nitems;
+                unsigned long long q0;
+                unsigned cc;
+                geom(c, &o0, &no, &q0, &cc, &nitems);
+                return resamp_launch(h->ct, sg.dev[slot][0], sg.dev[slot][1], no, cc, h->L, h->D, T, (const float*)h->rev.p,
+                                     sm_count(h->device), st);
+            });
+        if (rc)
+            return rc;
+    }
+    h->ctr = ctr_after;
+    *consumed = used;
+    *produced = n;
+    return 0;
+}
+
+void grb200_rational_resampler_destroy(grb200_resamp* h)
+{
+    if (!h)
+        return;
+    cudaSetDevice(h->device);
+    h->sg.destroy();
+    h->rev.release();
+    delete h;
+}
+
+} // extern "C"

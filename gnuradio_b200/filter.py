@@ -11,6 +11,8 @@
   pfb.channelizer_ccf               gr-filter/python/filter/pfb.py:23-50 (hier block; stream_to_streams absorbed)
   interp_fir_filter_ccf/ccc         gr-filter/include/gnuradio/filter/interp_fir_filter.h:43-72,
                                     gr-filter/lib/interp_fir_filter_impl.cc:24-152
+  rational_resampler_base_ccf/ccc   gr-filter/include/gnuradio/filter/rational_resampler_base.h,
+                                    gr-filter/lib/rational_resampler_base_impl.cc:24-176
   pfb_decimator_ccf                 gr-filter/include/gnuradio/filter/pfb_decimator_ccf.h:94-138,
                                     gr-filter/lib/pfb_decimator_ccf_impl.cc:24-257
 
@@ -328,6 +330,123 @@ class interp_fir_filter_ccf(_interp_fir_filter):
 class interp_fir_filter_ccc(_interp_fir_filter):
     _complex_taps = True
     _name = "interp_fir_filter_ccc"
+
+
+class _rational_resampler_base(block):
+    """rational_resampler_base: `interpolation` polyphase FIRs walked by a phase counter that advances `decimation` per
+    output (rational_resampler_base_impl.cc:141-173).  The reference class shadows history() (…_impl.h:48-49): the
+    scheduler sees history 1 and puts no zeros in front of the stream; history() here returns the taps per phase like the
+    shadowing accessor does.  set_taps() is picked up by the next general_work(), which installs the taps and returns 0
+    (:151-154)."""
+    _complex_taps = False
+    _name = "rational_resampler_base"
+
+    def __init__(self, interpolation, decimation, taps, device=0):
+        L = _lib.lib()
+        if int(interpolation) <= 0:  # std::out_of_range, :46-48
+            raise IndexError("rational_resampler_base_impl<IN_T,OUT_T,TAP_T>: interpolation must be > 0")
+        if int(decimation) <= 0:  # std::out_of_range, :49-51
+            raise IndexError("rational_resampler_base_impl<IN_T,OUT_T,TAP_T>: decimation must be > 0")
+        block.__init__(self, self._name, io_signature.make(1, 1, 8), io_signature.make(1, 1, 8))
+        self._interpolation, self._decimation = int(interpolation), int(decimation)
+        self.set_relative_rate(self._interpolation / self._decimation)  # :53
+        self.set_output_multiple(1)
+        t = self._conv_taps(taps)
+        self._h = C.c_void_p()
+        create = L.grb200_rational_resampler_ccc_create if self._complex_taps else L.grb200_rational_resampler_ccf_create
+        _lib.check(create(self._interpolation, self._decimation, _ptr(t), len(t), int(device), C.byref(self._h)))
+        self._new_taps = self._padded(t)
+        self.d_updated = False
+        self._nt = L.grb200_rational_resampler_taps_per_filter(self._h)  # install_taps, :115
+
+    @classmethod
+    def make(cls, interpolation, decimation, taps, device=0):
+        return cls(interpolation, decimation, taps, device)
+
+    def _conv_taps(self, taps):
+        t = np.ascontiguousarray(taps, np.complex64 if self._complex_taps else np.float32)
+        if t.ndim != 1 or t.size < 1:
+            raise RuntimeError("rational_resampler_base_impl: no filter taps provided.")
+        return t
+
+    def _padded(self, t):  # :83-90: rounded up to a multiple of the interpolation with zeros
+        n = (-len(t)) % self._interpolation
+        return np.concatenate([t, np.zeros(n, t.dtype)])
+
+    def interpolation(self):
+        return self._interpolation
+
+    def decimation(self):
+        return self._decimation
+
+    def history(self):  # the shadowing accessor of rational_resampler_base_impl.h:48
+        return self._nt
+
+    def set_history(self, h):
+        self._nt = int(h)
+
+    def set_taps(self, taps):
+        self._new_taps = self._padded(self._conv_taps(taps))
+        self.d_updated = True
+
+    def taps(self):
+        return self._new_taps.tolist()  # d_new_taps, padding included (:120-124)
+
+    def forecast(self, noutput_items, ninputs):  # :128-138
+        nreqd = max(1, int((noutput_items + 1) * self._decimation / self._interpolation) + self.history() - 1)
+        return [nreqd] * ninputs
+
+    def general_work(self, noutput_items, ninput_items, input_items, output_items):
+        L = _lib.lib()
+        if self.d_updated:  # :151-154
+            _lib.check(L.grb200_rational_resampler_set_taps(self._h, _ptr(self._new_taps), len(self._new_taps)))
+            self.set_history(L.grb200_rational_resampler_taps_per_filter(self._h))
+            self.d_updated = False
+            return 0
+        xin = as_items(input_items[0], _c64, 0, "input_items[0]")
+        # the reference's loop runs while count < ninput_items[0] and filter() reads history() items from there -- past
+        # ninput_items[0] into the circular buffer; a borrowed array ends, so the walk stops where the array does
+        nin = max(0, min(int(ninput_items[0]), xin.size - (self.history() - 1)))
+        out = as_items(output_items[0], _c64, int(noutput_items), "output_items[0]")
+        consumed, produced = C.c_longlong(0), C.c_longlong(0)
+        _lib.check(L.grb200_rational_resampler_work(self._h, _ptr(xin), nin, _ptr(out), int(noutput_items),
+                                                    C.byref(consumed), C.byref(produced)))
+        self.consume_each(consumed.value)
+        return produced.value
+
+    def work_dev(self, in_dev, ninput_items, out_dev, noutput_items, stream=0):
+        """Device-resident mode: in_dev (ninput_items + history()-1 readable items) / out_dev are device addresses;
+        asynchronous on `stream`.  Returns (consumed, produced)."""
+        consumed, produced = C.c_longlong(0), C.c_longlong(0)
+        _lib.check(_lib.lib().grb200_rational_resampler_work_dev(
+            self._h, C.c_void_p(in_dev), int(ninput_items), C.c_void_p(out_dev), int(noutput_items), C.byref(consumed),
+            C.byref(produced), C.c_void_p(stream)))
+        return consumed.value, produced.value
+
+    def ctr(self):
+        return int(_lib.lib().grb200_rational_resampler_ctr(self._h))
+
+    def set_ctr(self, ctr):
+        """Phase counter hand-over for a time-sharded stream (d_ctr, :156,171)."""
+        _lib.check(_lib.lib().grb200_rational_resampler_set_ctr(self._h, int(ctr)))
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().grb200_rational_resampler_destroy(h)
+            except Exception:
+                pass
+
+
+class rational_resampler_base_ccf(_rational_resampler_base):
+    _complex_taps = False
+    _name = "rational_resampler_base_ccf"
+
+
+class rational_resampler_base_ccc(_rational_resampler_base):
+    _complex_taps = True
+    _name = "rational_resampler_base_ccc"
 
 
 class fft_filter_ccc(sync_decimator):

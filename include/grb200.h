@@ -202,6 +202,36 @@ int grb200_interp_fir_work(grb200_interp* h, const void* in_host, void* out_host
 int grb200_interp_fir_work_dev(grb200_interp* h, const void* in_dev, void* out_dev, long long noutput, void* stream);
 void grb200_interp_fir_destroy(grb200_interp* h);
 
+/* ---- rational_resampler_base_ccf / rational_resampler_base_ccc ------------------------------------
+ * Replaces gr::filter::rational_resampler_base_impl<gr_complex,gr_complex,float|gr_complex>
+ *   set_taps / install_taps  gr-filter/lib/rational_resampler_base_impl.cc:77-117 (zero-pad to a multiple of the
+ *                            interpolation, xtaps[n][k] = taps[n + k*interpolation])
+ *   general_work             gr-filter/lib/rational_resampler_base_impl.cc:141-173
+ *       while (i < noutput && count < ninput) { out[i++] = firs[ctr].filter(in); ctr += decimation;
+ *                                               while (ctr >= interpolation) { ctr -= interpolation; in++; count++; } }
+ * The reference class shadows history() (rational_resampler_base_impl.h:48-49), so the scheduler puts NO zero history in
+ * front of the stream: the first output is the first full window.  The loop tests count < ninput only and filter() reads
+ * taps_per_filter items from there, so `in` must hold nin + taps_per_filter-1 readable items (forecast :128-138 asks the
+ * scheduler for that much).  *consumed is what general_work passes to consume_each(), *produced what it returns; the
+ * phase counter d_ctr is carried in the handle (ctr / set_ctr expose it so a time-sharded stream can hand it over).
+ * Zero interpolation or decimation returns GRB200_ERANGE (std::out_of_range in the reference, :46-51). */
+typedef struct grb200_resamp grb200_resamp;
+int grb200_rational_resampler_ccf_create(unsigned int interpolation, unsigned int decimation, const float* taps, int ntaps,
+                                         int device, grb200_resamp** out);
+int grb200_rational_resampler_ccc_create(unsigned int interpolation, unsigned int decimation, const float* taps_re_im,
+                                         int ntaps, int device, grb200_resamp** out);
+int grb200_rational_resampler_set_taps(grb200_resamp* h, const float* taps, int ntaps); /* re/im pairs for ccc */
+int grb200_rational_resampler_taps_per_filter(const grb200_resamp* h);
+unsigned int grb200_rational_resampler_interpolation(const grb200_resamp* h);
+unsigned int grb200_rational_resampler_decimation(const grb200_resamp* h);
+unsigned int grb200_rational_resampler_ctr(const grb200_resamp* h);
+int grb200_rational_resampler_set_ctr(grb200_resamp* h, unsigned int ctr);
+int grb200_rational_resampler_work(grb200_resamp* h, const void* in_host, long long nin, void* out_host, long long noutput,
+                                   long long* consumed, long long* produced);
+int grb200_rational_resampler_work_dev(grb200_resamp* h, const void* in_dev, long long nin, void* out_dev,
+                                       long long noutput, long long* consumed, long long* produced, void* stream);
+void grb200_rational_resampler_destroy(grb200_resamp* h);
+
 /* ---- fft_vcc (+ complex_to_mag_squared) --------------------------------------------------------
  * Replaces gr::fft::fft_complex (gr-fft/lib/fft.cc:151-203) and fft_vcc_fftw: ctor/set_window
  * gr-fft/lib/fft_vcc_fftw.cc:33-61, work :63-122; and complex_to_mag_squared_impl::work

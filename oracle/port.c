@@ -482,6 +482,55 @@ int grbo_interp_fir(int cplx_taps, unsigned int interpolation, const float* taps
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * rational_resampler_base_impl<gr_complex,gr_complex,float|gr_complex>
+ * (gr-filter/lib/rational_resampler_base_impl.cc): set_taps :77-93 pads the taps with zeros to a multiple of the
+ * interpolation L; install_taps :97-117 deals them round-robin, xtaps[n][k] = taps[n + k*L], T taps per phase;
+ * general_work :141-173 walks the phase counter: out[i] = firs[ctr].filter(in), ctr += D, the input advances once per
+ * wrap of ctr past L.  The loop tests count < ninput only and filter() reads T items from there: in holds
+ * nin + T-1 readable items.  *ctr is d_ctr (in/out), *consumed what consume_each() gets.  Returns items produced.
+ * ---------------------------------------------------------------------------------------------- */
+long grbo_rational_resampler(int cplx_taps, unsigned int interpolation, unsigned int decimation, const float* taps,
+                             int ntaps, const cf32* in, long nin, cf32* out, long noutput, unsigned int* ctr_io,
+                             long* consumed)
+{
+    if (interpolation == 0 || decimation == 0)
+        return -1;
+    if (ntaps < 1)
+        return -2;
+    const int L = (int)interpolation, T = (ntaps + L - 1) / L;
+    unsigned int ctr = *ctr_io;
+    long count = 0, i = 0;
+    while (i < noutput && count < nin) {
+        float re = 0.0f, im = 0.0f;
+        for (int t = 0; t < T; t++) {
+            const int k = (int)ctr + (T - 1 - t) * L; /* index into the padded prototype */
+            if (k >= ntaps)
+                continue;
+            const cf32 x = in[count + t];
+            if (cplx_taps) {
+                const float hr = taps[2 * k], hi = taps[2 * k + 1];
+                re += x.re * hr - x.im * hi;
+                im += x.re * hi + x.im * hr;
+            } else {
+                re += x.re * taps[k];
+                im += x.im * taps[k];
+            }
+        }
+        out[i].re = re;
+        out[i].im = im;
+        i++;
+        ctr += decimation;
+        while (ctr >= interpolation) {
+            ctr -= interpolation;
+            count++;
+        }
+    }
+    *ctr_io = ctr;
+    *consumed = count;
+    return i;
+}
+
+/* ------------------------------------------------------------------------------------------------
  * pfb_decimator_ccf_impl::work_fir_exp (gr-filter/lib/pfb_decimator_ccf_impl.cc:135-154) over
  * polyphase_filterbank::set_taps (gr-filter/lib/polyphase_filterbank.cc:53-81):
  *   out[i] = sum_{j=M-1..0} fir_j(&in_{M-1-j}[i]) * rot[j],  taps_j[t] = padded[j + t*M],

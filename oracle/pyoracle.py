@@ -178,6 +178,31 @@ class _CLib:
         assert rc == T, rc
         return out
 
+    # -- rational_resampler_base_ccf / ccc ----------------------------------------------------------
+    def rational_resampler(self, interpolation, decimation, taps, x, noutput=None, ctr=0, nin=None):
+        """One general_work() call over x (no history in front; the reference class shadows history()).  `nin` is
+        ninput_items[0] (default: everything whose window fits in x); returns (out[:produced], consumed, ctr_after)."""
+        taps = np.ascontiguousarray(taps)
+        cplx = bool(np.iscomplexobj(taps))
+        t = _c64(taps) if cplx else np.ascontiguousarray(taps, np.float32)
+        T = -(-len(t) // interpolation)
+        x = _c64(x)
+        if nin is None:
+            nin = max(0, len(x) - (T - 1))
+        assert nin + T - 1 <= len(x) or nin == 0
+        if noutput is None:
+            noutput = (nin * interpolation) // decimation + 2
+        xin = _headroom(x)
+        out = np.empty(max(noutput, 1), np.complex64)
+        c, used = C.c_uint(ctr), C.c_long(0)
+        fn = self._f("rational_resampler")
+        fn.restype = C.c_long
+        n = fn(int(cplx), C.c_uint(interpolation), C.c_uint(decimation), _p(t), len(t), _p(xin), C.c_long(nin), _p(out),
+               C.c_long(noutput), C.byref(c), C.byref(used))
+        if n < 0:
+            raise ValueError("rational_resampler_base oracle error %d" % n)
+        return out[:n].copy(), used.value, c.value
+
     # -- pfb_decimator_ccf ------------------------------------------------------------------------
     def pfb_decimator(self, decim, taps, channel, streams, mode=0):
         """streams: [decim][n] fresh input streams (zero history).  mode bit 0 = use_fft_rotator, bit 1 =
@@ -357,6 +382,20 @@ def f64_interp_fir(interpolation, taps, x):
     u[::L] = x
     t = np.asarray(taps, np.complex128 if np.iscomplexobj(taps) else np.float64)
     return np.convolve(u, t)[: len(u)]
+
+
+def f64_rational_resampler(interpolation, decimation, taps, x, nout, ctr=0):
+    """out[i] = y[(T-1)*L + ctr + i*D], y = taps (*) zero-stuffed x (u[j*L] = x[j]): the polyphase walk of
+    rational_resampler_base_impl.cc:156-172 with no history in front of the stream."""
+    L, D = interpolation, decimation
+    x = np.asarray(x, np.complex128)
+    u = np.zeros(len(x) * L, np.complex128)
+    u[::L] = x
+    t = np.asarray(taps, np.complex128 if np.iscomplexobj(taps) else np.float64)
+    T = -(-len(t) // L)
+    y = np.convolve(u, t)
+    idx = (T - 1) * L + ctr + np.arange(nout) * D
+    return y[idx]
 
 
 def f64_pfb_decimator(decim, taps, channel, streams):

@@ -297,6 +297,68 @@ int grref_interp_fir(int cplx_taps, unsigned interpolation, const float* taps, i
     return nt;
 }
 
+/* rational_resampler_base_impl<gr_complex,gr_complex,float|gr_complex> (gr-filter/lib/rational_resampler_base_impl.cc):
+ * the block class needs the runtime (gr::block), so set_taps (:77-93), install_taps (:97-117) and the general_work loop
+ * (:156-172) are restated over the reference's OWN kernel::fir_filter objects.  in: nin + taps_per_filter-1 readable
+ * items; *ctr_io is d_ctr, *consumed the consume_each() argument.  Returns items produced, <0 on the reference's
+ * exceptions. */
+} /* extern "C": the helper below is a template */
+template <class FIR, class TAP>
+static long resamp_run(unsigned interpolation, unsigned decimation, const std::vector<TAP>& taps, const gr_complex* in,
+                       long nin, gr_complex* out, long noutput, unsigned* ctr_io, long* consumed)
+{
+    std::vector<TAP> padded(taps);
+    int n = padded.size() % interpolation;
+    if (n > 0) {
+        n = interpolation - n;
+        while (n-- > 0)
+            padded.insert(padded.end(), TAP(0));
+    }
+    const int nt = (int)(padded.size() / interpolation);
+    std::vector<std::vector<TAP>> xt(interpolation, std::vector<TAP>(nt));
+    for (int i = 0; i < (int)padded.size(); i++)
+        xt[i % interpolation][i / interpolation] = padded[i];
+    std::vector<FIR*> firs(interpolation);
+    for (unsigned k = 0; k < interpolation; k++)
+        firs[k] = new FIR(1, xt[k]);
+    unsigned ctr = *ctr_io;
+    long count = 0, i = 0;
+    while (i < noutput && count < nin) {
+        out[i++] = firs[ctr]->filter(in);
+        ctr += decimation;
+        while (ctr >= interpolation) {
+            ctr -= interpolation;
+            in++;
+            count++;
+        }
+    }
+    for (auto f : firs)
+        delete f;
+    *ctr_io = ctr;
+    *consumed = count;
+    return i;
+}
+extern "C" {
+
+long grref_rational_resampler(int cplx_taps, unsigned interpolation, unsigned decimation, const float* taps, int ntaps,
+                              const void* in, long nin, void* out, long noutput, unsigned* ctr_io, long* consumed)
+{
+    if (interpolation == 0 || decimation == 0)
+        return -1; /* std::out_of_range, :46-51 */
+    if (ntaps < 1)
+        return -2;
+    if (cplx_taps) {
+        std::vector<gr_complex> t(ntaps);
+        for (int i = 0; i < ntaps; i++)
+            t[i] = gr_complex(taps[2 * i], taps[2 * i + 1]);
+        return resamp_run<fir_filter_ccc, gr_complex>(interpolation, decimation, t, (const gr_complex*)in, nin,
+                                                      (gr_complex*)out, noutput, ctr_io, consumed);
+    }
+    std::vector<float> t(taps, taps + ntaps);
+    return resamp_run<fir_filter_ccf, float>(interpolation, decimation, t, (const gr_complex*)in, nin, (gr_complex*)out,
+                                             noutput, ctr_io, consumed);
+}
+
 /* fft_filter_ccc_impl::work driven like the scheduler does (gr-filter/lib/fft_filter_ccc_impl.cc:61-78):
  * one filter() call per chunk of `chunk_out` output items (rounded down to a multiple of nsamples,
  * at least one block).  nitems must be a multiple of nsamples; consumes nitems*decim inputs.

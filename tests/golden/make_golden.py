@@ -147,6 +147,13 @@ def ref_fixtures():
     fx["interp_taps_c"] = crand(rng4, 33)
     fx["interp_ccf_l4"] = R.interp_fir(4, fx["interp_taps_f"], fx["interp_x"])
     fx["interp_ccc_l3"] = R.interp_fir(3, fx["interp_taps_c"], fx["interp_x"])
+    # ---- rational_resampler_base_ccf / ccc (one general_work() over the whole stream, no history in front) ----
+    rng5 = np.random.default_rng(20261108)
+    fx["resamp_x"] = crand(rng5, 3000)
+    fx["resamp_taps_f"] = rng5.uniform(-1, 1, 50).astype(np.float32)  # 50 taps over 4 phases: zero-padded to 52
+    fx["resamp_taps_c"] = crand(rng5, 33)
+    fx["resamp_ccf_4_7"] = R.rational_resampler(4, 7, fx["resamp_taps_f"], fx["resamp_x"])[0]
+    fx["resamp_ccc_3_2"] = R.rational_resampler(3, 2, fx["resamp_taps_c"], fx["resamp_x"])[0]
     return fx
 
 

@@ -311,6 +311,54 @@ def test_interp_fir_qa_golden_and_fixtures(lay):
         assert_parity(got, po.f64_interp_fir(L, fx[tk], fx["interp_x"]), key + " f64", 1e-6, 1e-5)
 
 
+# gr-filter/python/filter/qa_rational_resampler.py:71-85 (test_000_1_to_1) and :87-109 (test_001_interp), fff
+# instantiation; the block shadows history(), so the first output is the first full window (no zeros in front)
+RESAMP_QA0_TAPS, RESAMP_QA0_SRC = (-4, 5), (234, -4, 23, -56, 45, 98, -23, -7)
+RESAMP_QA0_EXPECTED = (1186, -112, 339, -460, -167, 582)
+RESAMP_QA1_EXPECTED = (2, 20, 200, 2003, 20030, 300, 3005, 30050, 500, 5007, 50070, 700, 7011, 70110, 1100, 11013, 110130,
+                       1300, 13017, 130170, 1700.0, 17000.0, 170000.0, 0.0)
+
+
+def test_rational_resampler_qa_golden_and_fixtures(lay):
+    # the same integers through the complex-stream blocks come out exactly (partial sums are integers below 2^24)
+    for cplx in (False, True):
+        dt = np.complex64 if cplx else np.float32
+        src = np.array(RESAMP_QA0_SRC, np.float32)
+        got, used, ctr = lay.rational_resampler(1, 1, np.array(RESAMP_QA0_TAPS, dt), (src + 2j * src).astype(np.complex64),
+                                                noutput=6)
+        exp = np.array(RESAMP_QA0_EXPECTED, np.float32)
+        assert np.array_equal(got.real, exp) and np.array_equal(got.imag, 2 * exp) and (used, ctr) == (6, 0)
+        # test_001: 24 outputs from 8 inputs -- the last three windows read one item past the stream, which the QA's
+        # freshly zeroed buffer supplies (general_work tests count < ninput only, :160)
+        src = np.array(INTERP_QA_SRC + (0,), np.float32)
+        got, used, ctr = lay.rational_resampler(3, 1, np.array(INTERP_QA_TAPS, dt), (src + 2j * src).astype(np.complex64),
+                                                noutput=24, nin=8)
+        exp = np.array(RESAMP_QA1_EXPECTED, np.float32)
+        assert np.array_equal(got.real, exp) and np.array_equal(got.imag, 2 * exp) and (used, ctr) == (8, 0)
+    fx = fixtures()
+    for key, L, D, tk in (("resamp_ccf_4_7", 4, 7, "resamp_taps_f"), ("resamp_ccc_3_2", 3, 2, "resamp_taps_c")):
+        got, used, ctr = lay.rational_resampler(L, D, fx[tk], fx["resamp_x"])
+        assert_parity(got, fx[key], key, 1e-6, 1e-5)
+        assert_parity(got, po.f64_rational_resampler(L, D, fx[tk], fx["resamp_x"], len(got)), key + " f64", 1e-6, 1e-5)
+        T = -(-len(fx[tk]) // L)
+        nin = len(fx["resamp_x"]) - (T - 1)
+        assert len(got) == -(-nin * L // D) and used == len(got) * D // L and ctr == len(got) * D % L
+
+
+def test_rational_resampler_split_calls_carry_ctr(lay):
+    # d_ctr and the consumed count carry a stream across general_work() calls (:156,171-172)
+    rng = np.random.default_rng(11)
+    x = crand(rng, 1200)
+    taps = rng.uniform(-1, 1, 23).astype(np.float32)
+    whole, _, _ = lay.rational_resampler(5, 3, taps, x)
+    parts, pos, ctr = [], 0, 0
+    for nout in (1, 7, 64, 333, 10 ** 6):
+        got, used, ctr = lay.rational_resampler(5, 3, taps, x[pos:], noutput=nout, ctr=ctr)
+        parts.append(got)
+        pos += used
+    assert_parity(np.concatenate(parts), whole, "split", 1e-6, 1e-5)
+
+
 def test_port_matches_reference_layer_on_fresh_data():
     if not po.have_ref():
         pytest.skip("oracle/_ref not built here")
