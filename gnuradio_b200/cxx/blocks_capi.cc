@@ -218,6 +218,49 @@ long long grbx_interp_fir_run(int complex_taps, unsigned interpolation, const fl
     });
 }
 
+// rational_resampler_base_ccf/ccc over a stream of nin items (the scheduler sees history 1: no zeros in front), driven in
+// calls of at most max_noutput outputs stepped down until forecast() fits what is left: returns items produced
+long long grbx_rational_resampler_run(int complex_taps, unsigned interpolation, unsigned decimation, const float* taps,
+                                      int ntaps, const void* in, void* out, long long nin, int max_noutput)
+{
+    return guarded([&]() -> long long {
+        auto drive = [&](auto& b) -> long long {
+            long long consumed = 0, produced = 0;
+            while (true) {
+                const long long avail = nin - consumed;
+                gr_vector_int need(1, 0);
+                int nout = max_noutput;
+                for (; nout > 0; nout--) {
+                    b->forecast(nout, need);
+                    if (need[0] <= avail)
+                        break;
+                }
+                if (nout <= 0 || avail < (long long)b->history())
+                    break;
+                gr_vector_const_void_star ii(1, (const gr_complex*)in + consumed);
+                gr_vector_void_star oo(1, (gr_complex*)out + produced);
+                gr_vector_int ni(1, (int)(avail - (b->history() - 1))); // the array ends: no reads past it
+                const int r = b->general_work(nout, ni, ii, oo);
+                if (r <= 0)
+                    break;
+                produced += r;
+                consumed += b->nitems_consumed_last();
+            }
+            return produced;
+        };
+        if (complex_taps) {
+            std::vector<gr_complex> t((const gr_complex*)taps, (const gr_complex*)taps + ntaps);
+            auto b = gr::filter::rational_resampler_base_ccc::make(interpolation, decimation, t);
+            return drive(b);
+        }
+        std::vector<float> t(taps, taps + ntaps);
+        auto b = gr::filter::rational_resampler_base_ccf::make(interpolation, decimation, t);
+        if ((int)b->taps().size() != (ntaps + (int)interpolation - 1) / (int)interpolation * (int)interpolation)
+            throw std::logic_error("rational_resampler_base_ccf: taps() must return the padded taps");
+        return drive(b);
+    });
+}
+
 // pfb_decimator_ccf over in_streams[s] (no history in front: a fresh stream), scheduler-sized calls
 long long grbx_pfb_dec_run(unsigned decim, const float* taps, int ntaps, unsigned channel, int use_fft_rotator,
                            int use_fft_filters, const void* const* in_streams, void* out, long long nitems, int chunk)

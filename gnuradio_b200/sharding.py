@@ -93,3 +93,34 @@ def exchange_halo(dist, head, tail, rank, world, ring=False):
     if ops:
         for r in dist.batch_isend_irecv(ops):
             r.wait()
+
+
+@dataclass(frozen=True)
+class ResamplerSegment:
+    rank: int
+    world: int
+    out_begin: int   # first output item owned
+    out_end: int
+    in_begin: int    # input item the first owned output's window starts at
+    in_end: int      # one past the last input item any owned window reads (taps_per_filter-1 items of look-ahead included)
+    ctr: int         # d_ctr at out_begin: the rank sets it with set_ctr() before its first call
+    ninput: int      # ninput_items[0] for the rank's call: in_end - in_begin - (taps_per_filter-1)
+
+    @property
+    def noutput(self):
+        return self.out_end - self.out_begin
+
+
+def resampler_segment(rank, world, noutput_total, interpolation, decimation, taps_per_filter, ctr0=0):
+    """Segment of rational_resampler_base (gr-filter/lib/rational_resampler_base_impl.cc:156-172): output i filters the
+    window that starts at input (ctr0 + i*decimation) / interpolation with phase (ctr0 + i*decimation) % interpolation,
+    so a rank needs no neighbour data -- it reads its own span of the source, look-ahead included, and takes the phase
+    counter over in closed form.  No exchange step."""
+    b = split_outputs(noutput_total, world)
+    o0, o1 = b[rank], b[rank + 1]
+    s0 = ctr0 + o0 * decimation
+    q0 = s0 // interpolation
+    if o1 == o0:
+        return ResamplerSegment(rank, world, o0, o1, q0, q0, s0 % interpolation, 0)
+    q_last = (ctr0 + (o1 - 1) * decimation) // interpolation
+    return ResamplerSegment(rank, world, o0, o1, q0, q_last + taps_per_filter, s0 % interpolation, q_last + 1 - q0)

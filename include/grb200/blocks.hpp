@@ -386,6 +386,106 @@ typedef interp_fir_filter<gr_complex, gr_complex, float> interp_fir_filter_ccf;
 typedef interp_fir_filter<gr_complex, gr_complex, gr_complex> interp_fir_filter_ccc;
 
 // ---------------------------------------------------------------------------------------------------
+// rational_resampler_base<gr_complex, gr_complex, float|gr_complex>  (rational_resampler_base_ccf / _ccc)
+// gr-filter/include/gnuradio/filter/rational_resampler_base.h, lib/rational_resampler_base_impl.{h,cc}
+// ---------------------------------------------------------------------------------------------------
+template <class IN_T, class OUT_T, class TAP_T>
+class rational_resampler_base : public grb200::rt::block
+{
+    static_assert(std::is_same<IN_T, gr_complex>::value && std::is_same<OUT_T, gr_complex>::value,
+                  "only the ccf and ccc instantiations are built");
+
+public:
+    typedef std::shared_ptr<rational_resampler_base<IN_T, OUT_T, TAP_T>> sptr;
+
+    static sptr make(unsigned interpolation, unsigned decimation, const std::vector<TAP_T>& taps)
+    {
+        if (interpolation == 0) // :46-48
+            throw std::out_of_range("rational_resampler_base_impl<IN_T,OUT_T,TAP_T>: interpolation must be > 0");
+        if (decimation == 0) // :49-51
+            throw std::out_of_range("rational_resampler_base_impl<IN_T,OUT_T,TAP_T>: decimation must be > 0");
+        if (taps.empty())
+            throw std::runtime_error("rational_resampler_base_impl: no filter taps provided.");
+        return sptr(new rational_resampler_base<IN_T, OUT_T, TAP_T>(interpolation, decimation, taps));
+    }
+
+    ~rational_resampler_base() override { grb200_rational_resampler_destroy(d_h); }
+
+    // shadow the block's accessors like rational_resampler_base_impl.h:48-49: the scheduler keeps seeing history 1
+    unsigned history() const { return d_history; }
+    void set_history(unsigned history) { d_history = history; }
+
+    unsigned interpolation() const { return d_interpolation; }
+    unsigned decimation() const { return d_decimation; }
+
+    void set_taps(const std::vector<TAP_T>& taps) // :77-93: padded to a multiple of the interpolation
+    {
+        d_new_taps = taps;
+        d_updated = true;
+        int n = taps.size() % d_interpolation;
+        if (n > 0) {
+            n = d_interpolation - n;
+            while (n-- > 0)
+                d_new_taps.insert(d_new_taps.end(), TAP_T(0));
+        }
+    }
+    std::vector<TAP_T> taps() const { return d_new_taps; }
+
+    void forecast(int noutput_items, gr_vector_int& ninput_items_required) // :128-138
+    {
+        int nreqd = std::max((unsigned)1, (int)((double)(noutput_items + 1) * d_decimation / d_interpolation) + history() - 1);
+        for (auto& r : ninput_items_required)
+            r = nreqd;
+    }
+
+    // input_items[0] must hold ninput_items[0] + history()-1 readable items (what forecast() asked for covers it)
+    int general_work(int noutput_items, gr_vector_int& ninput_items, gr_vector_const_void_star& input_items,
+                     gr_vector_void_star& output_items) override
+    {
+        if (d_updated) { // :151-154
+            grb200::check(grb200_rational_resampler_set_taps(d_h, reinterpret_cast<const float*>(d_new_taps.data()),
+                                                             (int)d_new_taps.size()));
+            set_history(grb200_rational_resampler_taps_per_filter(d_h));
+            d_updated = false;
+            return 0;
+        }
+        long long consumed = 0, produced = 0;
+        grb200::check(grb200_rational_resampler_work(d_h, input_items[0], ninput_items[0], output_items[0], noutput_items,
+                                                     &consumed, &produced));
+        consume_each((int)consumed);
+        return (int)produced;
+    }
+
+    grb200_resamp* handle() { return d_h; } // device-resident chaining (grb200_rational_resampler_work_dev)
+
+private:
+    rational_resampler_base(unsigned interpolation, unsigned decimation, const std::vector<TAP_T>& taps)
+        : block(std::is_same<TAP_T, float>::value ? "rational_resampler_base_ccf" : "rational_resampler_base_ccc",
+                grb200::rt::io_signature::make(1, 1, sizeof(IN_T)), grb200::rt::io_signature::make(1, 1, sizeof(OUT_T))),
+          d_interpolation(interpolation), d_decimation(decimation)
+    {
+        set_relative_rate((double)interpolation / (double)decimation); // :53
+        set_output_multiple(1);
+        set_taps(taps);
+        const float* t = reinterpret_cast<const float*>(d_new_taps.data());
+        if (std::is_same<TAP_T, float>::value)
+            grb200::check(grb200_rational_resampler_ccf_create(interpolation, decimation, t, (int)d_new_taps.size(),
+                                                               grb200::default_device(), &d_h));
+        else
+            grb200::check(grb200_rational_resampler_ccc_create(interpolation, decimation, t, (int)d_new_taps.size(),
+                                                               grb200::default_device(), &d_h));
+        set_history(grb200_rational_resampler_taps_per_filter(d_h)); // install_taps, :115
+        d_updated = false;
+    }
+    unsigned d_history = 1, d_interpolation, d_decimation;
+    grb200_resamp* d_h = nullptr;
+    std::vector<TAP_T> d_new_taps;
+    bool d_updated = false;
+};
+typedef rational_resampler_base<gr_complex, gr_complex, float> rational_resampler_base_ccf;
+typedef rational_resampler_base<gr_complex, gr_complex, gr_complex> rational_resampler_base_ccc;
+
+// ---------------------------------------------------------------------------------------------------
 // fft_filter_ccc
 // ---------------------------------------------------------------------------------------------------
 class fft_filter_ccc : public grb200::rt::sync_decimator

@@ -16,7 +16,7 @@ LL = C.c_longlong
 @pytest.fixture(scope="module")
 def drv():
     lib = C.CDLL(os.path.join(ROOT, "gnuradio_b200", "cxx", "libgrb200_blocks.so"))
-    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_pfb_dec_run", "grbx_interp_fir_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run"):
+    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_pfb_dec_run", "grbx_interp_fir_run", "grbx_rational_resampler_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run"):
         getattr(lib, f).restype = LL
     lib.grbx_what.restype = C.c_char_p
     return lib
@@ -133,3 +133,19 @@ def test_cxx_interp_fir(drv, orc):
         assert_parity(out, orc.interp_fir(L, taps, x), "c++ interp_fir ct=%d" % ct, 2e-6, 2e-5)
     rc = drv.grbx_interp_fir_run(0, 0, p(taps), 4, p(x), p(out), LL(10), 1024)
     assert rc == -2  # std::out_of_range
+
+
+def test_cxx_rational_resampler(drv, orc):
+    rng = np.random.default_rng(9)
+    x = crand(rng, 6000)
+    for ct, L, D, nt in ((0, 4, 7, 50), (1, 3, 2, 33), (0, 1, 1, 2)):
+        taps = crand(rng, nt) if ct else rng.uniform(-1, 1, nt).astype(np.float32)
+        exp, _, _ = orc.rational_resampler(L, D, taps, x)
+        out = np.zeros(len(exp) + 8, np.complex64)
+        rc = drv.grbx_rational_resampler_run(ct, L, D, p(taps), nt, p(x), p(out), LL(len(x)), 1000)
+        assert len(exp) - 2 * (L // D + 2) <= rc <= len(exp), drv.grbx_what()
+        assert_parity(out[:rc], exp[:rc], "c++ rational_resampler ct=%d" % ct, 2e-6, 2e-5)
+    rc = drv.grbx_rational_resampler_run(0, 0, 1, p(taps), 2, p(x), p(out), LL(10), 1000)
+    assert rc == -2  # std::out_of_range
+    rc = drv.grbx_rational_resampler_run(0, 1, 0, p(taps), 2, p(x), p(out), LL(10), 1000)
+    assert rc == -2

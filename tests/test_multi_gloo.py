@@ -151,3 +151,25 @@ def test_split_outputs_respects_multiples():
     assert (s.out_begin, s.out_end, s.in_begin, s.in_end, s.halo) == (500, 1000, 4000, 8000, 1023)
     s = sharding.segment(0, 8, 1 << 24, history=17, items_per_output=64)
     assert s.halo == 16 * 64 and s.ninput == (1 << 27)
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+@pytest.mark.parametrize("L,D", [(3, 2), (2, 3), (160, 147), (1, 5), (7, 1)])
+def test_resampler_segments_equal_single_stream(orc, world, L, D):
+    # rational_resampler_base shards on outputs with no exchange: window start and d_ctr of a rank's first output are
+    # closed-form (sharding.resampler_segment); the ranks' outputs concatenate to the single-stream result bit for bit
+    rng = np.random.default_rng(world * 1000 + L * 10 + D)
+    taps = rng.uniform(-1, 1, 61).astype(np.float32)
+    T = -(-61 // L)
+    x = (rng.uniform(-1, 1, 3000) + 1j * rng.uniform(-1, 1, 3000)).astype(np.complex64)
+    port = __import__("oracle.pyoracle", fromlist=["Port"]).Port()  # the C port sums in one order whatever the alignment
+    full, _, _ = port.rational_resampler(L, D, taps, x)
+    parts = []
+    for r in range(world):
+        seg = sharding.resampler_segment(r, world, len(full), L, D, T)
+        assert seg.in_end <= len(x) and 0 <= seg.ctr < L
+        y, used, _ = port.rational_resampler(L, D, taps, x[seg.in_begin:seg.in_end], noutput=seg.noutput, ctr=seg.ctr,
+                                             nin=seg.ninput)
+        assert len(y) == seg.noutput
+        parts.append(y)
+    assert np.array_equal(np.concatenate(parts), full)
