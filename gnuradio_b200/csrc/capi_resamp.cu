@@ -4,8 +4,9 @@
 // walks a phase counter: out[i] = firs[ctr].filter(in); ctr += decimation; every time ctr wraps past the interpolation
 // the input pointer advances (general_work :151-173).  In closed form, with s_i = ctr0 + i*decimation:
 //     out[i] = sum_t rev[s_i % L][t] * in[s_i / L + t],   consumed = s_n / L,   ctr' = s_n % L
-// so every output is independent.  A thread owns one output item: phase and window start from one 64-bit divide, phase
-// taps from shared memory, window through the read-only path (neighbouring outputs share all but D/L of their window, so
+// so every output is independent.  A thread owns one output item: phase and window start from one divide (32-bit when
+// the launch's largest s_i fits), phase taps from shared memory (tap-major: the phases a warp holds at one tap index sit
+// in different banks), window through the read-only path (neighbouring outputs share all but D/L of their window, so
 // L1 serves the re-reads).  8*D/L + 8 algorithmic bytes per output item.
 #include <cstdint>
 #include "capi_common.cuh"
@@ -14,8 +15,9 @@ using namespace grb;
 
 namespace grb {
 
-// rev[(p*T + t) * ES + e]: reversed taps of phase p (fir_filter.cc:62-64), ES = 1 (real) or 2 (complex)
-template <bool CT>
+// rev[(t*L + p) * ES + e]: reversed taps of phase p (fir_filter.cc:62-64), tap-major so the phases a warp holds at one
+// tap index sit in different banks; ES = 1 (real) or 2 (complex).  W32: every s_i fits 32 bits (one 32-bit divide).
+template <bool CT, bool W32>
 __global__ void __launch_bounds__(256) resamp_kernel(const float2* __restrict__ in, float2* __restrict__ out,
                                                      long long nout, unsigned ctr0, unsigned L, unsigned D, int T,
                                                      const float* __restrict__ rev)
@@ -28,22 +30,37 @@ __global__ void __launch_bounds__(256) resamp_kernel(const float2* __restrict__ 
     __syncthreads();
     const long long step = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nout; i += step) {
-        const unsigned long long s = (unsigned long long)ctr0 + (unsigned long long)i * D;
-        const unsigned long long q = s / L;
-        const unsigned p = (unsigned)(s - q * L);
+        unsigned long long q;
+        unsigned p;
+        if (W32) {
+            const unsigned s = ctr0 + (unsigned)i * D;
+            const unsigned q32 = s / L;
+            p = s - q32 * L;
+            q = q32;
+        } else {
+            const unsigned long long s = (unsigned long long)ctr0 + (unsigned long long)i * D;
+            q = s / L;
+            p = (unsigned)(s - q * L);
+        }
         const float2* x = in + q;
-        const float* h = sh + (size_t)p * T * ES;
         float2 a = make_float2(0.f, 0.f);
-#pragma unroll 4
-        for (int t = 0; t < T; t++) {
-            const float2 v = __ldg(x + t);
-            if (CT) {
-                const float hr = h[2 * t], hi = h[2 * t + 1];
-                a.x = fmaf(v.x, hr, fmaf(-v.y, hi, a.x));
-                a.y = fmaf(v.x, hi, fmaf(v.y, hr, a.y));
-            } else {
-                a.x = fmaf(v.x, h[t], a.x);
-                a.y = fmaf(v.y, h[t], a.y);
+        if (CT) {
+            const float2* h = reinterpret_cast<const float2*>(sh) + p;
+#pragma unroll 8
+            for (int t = 0; t < T; t++) {
+                const float2 v = __ldg(x + t);
+                const float2 c = h[(size_t)t * L];
+                a.x = fmaf(v.x, c.x, fmaf(-v.y, c.y, a.x));
+                a.y = fmaf(v.x, c.y, fmaf(v.y, c.x, a.y));
+            }
+        } else {
+            const float* h = sh + p;
+#pragma unroll 8
+            for (int t = 0; t < T; t++) {
+                const float2 v = __ldg(x + t);
+                const float c = h[(size_t)t * L];
+                a.x = fmaf(v.x, c, a.x);
+                a.y = fmaf(v.y, c, a.y);
             }
         }
         out[i] = a;
@@ -69,7 +86,10 @@ static int resamp_launch(bool ct, const void* in, void* out, long long nout, uns
         GRB_LAUNCH_CHECK();
         return 0;
     };
-    return ct ? launch(resamp_kernel<true>) : launch(resamp_kernel<false>);
+    const bool w32 = (unsigned long long)ctr0 + (unsigned long long)nout * D < (1ull << 32);
+    if (w32)
+        return ct ? launch(resamp_kernel<true, true>) : launch(resamp_kernel<false, true>);
+    return ct ? launch(resamp_kernel<true, false>) : launch(resamp_kernel<false, false>);
 }
 
 } // namespace grb
@@ -93,7 +113,7 @@ static int resamp_upload(grb200_resamp* h, const float* taps, int ntaps)
     for (int i = 0; i < ntaps; i++) {
         const int p = i % L, k = i / L; // xtaps[p][k]
         for (int e = 0; e < es; e++)
-            rev[((size_t)p * T + (T - 1 - k)) * es + e] = taps[(size_t)i * es + e];
+            rev[((size_t)(T - 1 - k) * L + p) * es + e] = taps[(size_t)i * es + e];
     }
     int rc = h->rev.upload(rev.data(), rev.size() * sizeof(float));
     if (rc)

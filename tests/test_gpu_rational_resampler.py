@@ -118,6 +118,21 @@ def test_rational_resampler_counts_match_oracle_loop(grb, orc):
         assert T == -(-37 // L)
 
 
+def test_rational_resampler_wide_index_path(grb, orc):
+    # one launch whose s_i = ctr + i*D passes 2^32 (the kernel's 64-bit divide): 40000 one-tap phases, D = 39999
+    rng = np.random.default_rng(12)
+    L, D, nout = 40000, 39999, 120000
+    taps = rng.uniform(-1, 1, L).astype(np.float32)
+    x = crand(rng, nout + 8)
+    blk = grb.filter.rational_resampler_base_ccf(L, D, taps)
+    blk.set_ctr(17)
+    ob = np.empty(nout, np.complex64)
+    assert blk.general_work(nout, [len(x)], [x], [ob]) == nout and (17 + nout * D) >= 1 << 32
+    exp, used, ctr = orc.rational_resampler(L, D, taps, x, noutput=nout, ctr=17)
+    assert (blk._consumed, blk.ctr()) == (used, ctr)
+    assert_parity(ob, exp, "wide index", 2e-6, 2e-5)
+
+
 def test_rational_resampler_set_taps_midstream_and_errors(grb, orc):
     rng = np.random.default_rng(6)
     x = crand(rng, 4000)
