@@ -67,6 +67,85 @@ __global__ void __launch_bounds__(256) resamp_kernel(const float2* __restrict__ 
     }
 }
 
+// Phase-fixed variant: with G = (a multiple of L) active threads and a grid stride of G outputs, thread g keeps the phase
+// (ctr0 + g*D) mod L for all of its outputs and its window start advances by the integer G*D/L per step -- the TT phase
+// taps live in registers (no shared-memory reads, no divide in the loop) and the loop is TT read-only loads + FMAs.
+template <bool CT, int TT>
+__global__ void __launch_bounds__(256) resamp_phase_kernel(const float2* __restrict__ in, float2* __restrict__ out,
+                                                           long long nout, unsigned ctr0, unsigned L, unsigned D,
+                                                           long long G, long long qstep, const float* __restrict__ rev)
+{
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G)
+        return;
+    const unsigned long long s = (unsigned long long)ctr0 + (unsigned long long)g * D;
+    unsigned long long q = s / L;
+    const unsigned p = (unsigned)(s - q * L);
+    float hr[TT], hi[CT ? TT : 1];
+#pragma unroll
+    for (int t = 0; t < TT; t++) {
+        if (CT) {
+            const float2 c = __ldg(reinterpret_cast<const float2*>(rev) + (size_t)t * L + p);
+            hr[t] = c.x;
+            hi[t] = c.y;
+        } else {
+            hr[t] = __ldg(rev + (size_t)t * L + p);
+        }
+    }
+    for (long long i = g; i < nout; i += G, q += qstep) {
+        const float2* x = in + q;
+        float2 a = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int t = 0; t < TT; t++) {
+            const float2 v = __ldg(x + t);
+            if (CT) {
+                a.x = fmaf(v.x, hr[t], fmaf(-v.y, hi[t], a.x));
+                a.y = fmaf(v.x, hi[t], fmaf(v.y, hr[t], a.y));
+            } else {
+                a.x = fmaf(v.x, hr[t], a.x);
+                a.y = fmaf(v.y, hr[t], a.y);
+            }
+        }
+        out[i] = a;
+    }
+}
+
+template <bool CT>
+static int resamp_phase_launch(const void* in, void* out, long long nout, unsigned ctr0, unsigned L, unsigned D, int T,
+                               const float* rev, long long nblk, cudaStream_t st, bool* done)
+{
+    *done = false;
+    const long long G = nblk * 256 / L * L;
+    if (G == 0)
+        return 0;
+    const long long qstep = G / L * D;
+    auto launch = [&](auto kern) -> int {
+        kern<<<(unsigned)nblk, 256, 0, st>>>((const float2*)in, (float2*)out, nout, ctr0, L, D, G, qstep, rev);
+        GRB_LAUNCH_CHECK();
+        *done = true;
+        return 0;
+    };
+    switch (T) {
+    case 4:
+        return launch(resamp_phase_kernel<CT, 4>);
+    case 8:
+        return launch(resamp_phase_kernel<CT, 8>);
+    case 10:
+        return launch(resamp_phase_kernel<CT, 10>);
+    case 12:
+        return launch(resamp_phase_kernel<CT, 12>);
+    case 16:
+        return launch(resamp_phase_kernel<CT, 16>);
+    case 24:
+        return launch(resamp_phase_kernel<CT, 24>);
+    case 32:
+        return launch(resamp_phase_kernel<CT, 32>);
+    case 64:
+        return launch(resamp_phase_kernel<CT, 64>);
+    }
+    return 0;
+}
+
 static int resamp_launch(bool ct, const void* in, void* out, long long nout, unsigned ctr0, unsigned L, unsigned D, int T,
                          const float* rev, int nsm, cudaStream_t st)
 {
@@ -86,6 +165,11 @@ static int resamp_launch(bool ct, const void* in, void* out, long long nout, uns
         GRB_LAUNCH_CHECK();
         return 0;
     };
+    bool done = false;
+    int rc = ct ? resamp_phase_launch<true>(in, out, nout, ctr0, L, D, T, rev, nblk, st, &done)
+                : resamp_phase_launch<false>(in, out, nout, ctr0, L, D, T, rev, nblk, st, &done);
+    if (rc || done)
+        return rc;
     const bool w32 = (unsigned long long)ctr0 + (unsigned long long)nout * D < (1ull << 32);
     if (w32)
         return ct ? launch(resamp_kernel<true, true>) : launch(resamp_kernel<false, true>);
