@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(256) resamp_kernel(const float2* __restrict__ 
 
 // Phase-fixed variant: with G = (a multiple of L) active threads and a grid stride of G outputs, thread g keeps the phase
 // (ctr0 + g*D) mod L for all of its outputs and its window start advances by the integer G*D/L per step -- the TT phase
-// taps live in registers (no shared-memory reads, no divide in the loop) and the loop is TT read-only loads + FMAs.
+// taps live in registers (no shared-memory reads, no divide in the loop) and the loop is TT/2 16-byte read-only loads + FMAs.
 template <bool CT, int TT>
 __global__ void __launch_bounds__(256) resamp_phase_kernel(const float2* __restrict__ in, float2* __restrict__ out,
                                                            long long nout, unsigned ctr0, unsigned L, unsigned D,
@@ -81,31 +81,43 @@ __global__ void __launch_bounds__(256) resamp_phase_kernel(const float2* __restr
     const unsigned long long s = (unsigned long long)ctr0 + (unsigned long long)g * D;
     unsigned long long q = s / L;
     const unsigned p = (unsigned)(s - q * L);
-    float hr[TT], hi[CT ? TT : 1];
+    // 16-byte window loads: the window is read from the even item at or below q; an odd q shifts the taps up by one
+    // (zero in front) and needs one more item at the end.  G/L * D is even, so a thread keeps its parity.
+    const unsigned odd = (unsigned)(q & 1);
+    q -= odd;
+    float hr[TT + 1], hi[CT ? TT + 1 : 1];
 #pragma unroll
-    for (int t = 0; t < TT; t++) {
+    for (int j = 0; j <= TT; j++) {
+        const int t = j - (int)odd;
+        const bool ok = t >= 0 && t < TT;
         if (CT) {
-            const float2 c = __ldg(reinterpret_cast<const float2*>(rev) + (size_t)t * L + p);
-            hr[t] = c.x;
-            hi[t] = c.y;
+            const float2 c = ok ? __ldg(reinterpret_cast<const float2*>(rev) + (size_t)t * L + p) : make_float2(0.f, 0.f);
+            hr[j] = c.x;
+            hi[j] = c.y;
         } else {
-            hr[t] = __ldg(rev + (size_t)t * L + p);
+            hr[j] = ok ? __ldg(rev + (size_t)t * L + p) : 0.f;
         }
     }
+    auto mac = [&](float2& a, const float2 v, const int j) {
+        if (CT) {
+            a.x = fmaf(v.x, hr[j], fmaf(-v.y, hi[j], a.x));
+            a.y = fmaf(v.x, hi[j], fmaf(v.y, hr[j], a.y));
+        } else {
+            a.x = fmaf(v.x, hr[j], a.x);
+            a.y = fmaf(v.y, hr[j], a.y);
+        }
+    };
     for (long long i = g; i < nout; i += G, q += qstep) {
-        const float2* x = in + q;
+        const float4* x = reinterpret_cast<const float4*>(in + q);
         float2 a = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int t = 0; t < TT; t++) {
-            const float2 v = __ldg(x + t);
-            if (CT) {
-                a.x = fmaf(v.x, hr[t], fmaf(-v.y, hi[t], a.x));
-                a.y = fmaf(v.x, hi[t], fmaf(v.y, hr[t], a.y));
-            } else {
-                a.x = fmaf(v.x, hr[t], a.x);
-                a.y = fmaf(v.y, hr[t], a.y);
-            }
+        for (int j = 0; j < TT / 2; j++) {
+            const float4 v = __ldg(x + j);
+            mac(a, make_float2(v.x, v.y), 2 * j);
+            mac(a, make_float2(v.z, v.w), 2 * j + 1);
         }
+        if (odd)
+            mac(a, __ldg(in + q + TT), TT);
         out[i] = a;
     }
 }
@@ -115,7 +127,10 @@ static int resamp_phase_launch(const void* in, void* out, long long nout, unsign
                                const float* rev, long long nblk, cudaStream_t st, bool* done)
 {
     *done = false;
-    const long long G = nblk * 256 / L * L;
+    if (reinterpret_cast<uintptr_t>(in) & 15) // the kernel reads the window in 16-byte pairs
+        return 0;
+    const long long unit = (D & 1) ? 2ll * L : (long long)L; // G/L * D even: the window start keeps its parity
+    const long long G = nblk * 256 / unit * unit;
     if (G == 0)
         return 0;
     const long long qstep = G / L * D;
