@@ -9,6 +9,7 @@
 // in different banks), window through the read-only path (neighbouring outputs share all but D/L of their window, so
 // L1 serves the re-reads).  8*D/L + 8 algorithmic bytes per output item.
 #include <cstdint>
+#include <type_traits>
 #include "capi_common.cuh"
 
 using namespace grb;
@@ -70,7 +71,9 @@ __global__ void __launch_bounds__(256) resamp_kernel(const float2* __restrict__ 
 // Phase-fixed variant: with G = (a multiple of L) active threads and a grid stride of G outputs, thread g keeps the phase
 // (ctr0 + g*D) mod L for all of its outputs and its window start advances by the integer G*D/L per step -- the TT phase
 // taps live in registers (no shared-memory reads, no divide in the loop) and the loop is TT/2 16-byte read-only loads + FMAs.
-template <bool CT, int TT>
+// PAIR: the window is read in 16-byte pairs (pays when windows of neighbouring threads overlap little, D/L >= 0.8);
+// otherwise item by item (neighbouring threads hit the same L1 lines).  Same FMA order either way.
+template <bool CT, int TT, bool PAIR>
 __global__ void __launch_bounds__(256) resamp_phase_kernel(const float2* __restrict__ in, float2* __restrict__ out,
                                                            long long nout, unsigned ctr0, unsigned L, unsigned D,
                                                            long long G, long long qstep, const float* __restrict__ rev)
@@ -83,7 +86,7 @@ __global__ void __launch_bounds__(256) resamp_phase_kernel(const float2* __restr
     const unsigned p = (unsigned)(s - q * L);
     // 16-byte window loads: the window is read from the even item at or below q; an odd q shifts the taps up by one
     // (zero in front) and needs one more item at the end.  G/L * D is even, so a thread keeps its parity.
-    const unsigned odd = (unsigned)(q & 1);
+    const unsigned odd = PAIR ? (unsigned)(q & 1) : 0u;
     q -= odd;
     float hr[TT + 1], hi[CT ? TT + 1 : 1];
 #pragma unroll
@@ -108,16 +111,22 @@ __global__ void __launch_bounds__(256) resamp_phase_kernel(const float2* __restr
         }
     };
     for (long long i = g; i < nout; i += G, q += qstep) {
-        const float4* x = reinterpret_cast<const float4*>(in + q);
         float2 a = make_float2(0.f, 0.f);
+        if (PAIR) {
+            const float4* x = reinterpret_cast<const float4*>(in + q);
 #pragma unroll
-        for (int j = 0; j < TT / 2; j++) {
-            const float4 v = __ldg(x + j);
-            mac(a, make_float2(v.x, v.y), 2 * j);
-            mac(a, make_float2(v.z, v.w), 2 * j + 1);
+            for (int j = 0; j < TT / 2; j++) {
+                const float4 v = __ldg(x + j);
+                mac(a, make_float2(v.x, v.y), 2 * j);
+                mac(a, make_float2(v.z, v.w), 2 * j + 1);
+            }
+            if (odd)
+                mac(a, __ldg(in + q + TT), TT);
+        } else {
+#pragma unroll
+            for (int t = 0; t < TT; t++)
+                mac(a, __ldg(in + q + t), t);
         }
-        if (odd)
-            mac(a, __ldg(in + q + TT), TT);
         out[i] = a;
     }
 }
@@ -127,9 +136,9 @@ static int resamp_phase_launch(const void* in, void* out, long long nout, unsign
                                const float* rev, long long nblk, cudaStream_t st, bool* done)
 {
     *done = false;
-    if (reinterpret_cast<uintptr_t>(in) & 15) // the kernel reads the window in 16-byte pairs
-        return 0;
-    const long long unit = (D & 1) ? 2ll * L : (long long)L; // G/L * D even: the window start keeps its parity
+    // 16-byte pairs when neighbouring windows overlap little and the stream is 16-byte aligned
+    const bool pair = 5ull * D >= 4ull * L && (reinterpret_cast<uintptr_t>(in) & 15) == 0;
+    const long long unit = (pair && (D & 1)) ? 2ll * L : (long long)L; // pairs: G/L * D even keeps a thread's parity
     const long long G = nblk * 256 / unit * unit;
     if (G == 0)
         return 0;
@@ -140,23 +149,27 @@ static int resamp_phase_launch(const void* in, void* out, long long nout, unsign
         *done = true;
         return 0;
     };
+    auto pick = [&](auto tt) -> int {
+        constexpr int TTv = decltype(tt)::value;
+        return pair ? launch(resamp_phase_kernel<CT, TTv, true>) : launch(resamp_phase_kernel<CT, TTv, false>);
+    };
     switch (T) {
     case 4:
-        return launch(resamp_phase_kernel<CT, 4>);
+        return pick(std::integral_constant<int, 4>{});
     case 8:
-        return launch(resamp_phase_kernel<CT, 8>);
+        return pick(std::integral_constant<int, 8>{});
     case 10:
-        return launch(resamp_phase_kernel<CT, 10>);
+        return pick(std::integral_constant<int, 10>{});
     case 12:
-        return launch(resamp_phase_kernel<CT, 12>);
+        return pick(std::integral_constant<int, 12>{});
     case 16:
-        return launch(resamp_phase_kernel<CT, 16>);
+        return pick(std::integral_constant<int, 16>{});
     case 24:
-        return launch(resamp_phase_kernel<CT, 24>);
+        return pick(std::integral_constant<int, 24>{});
     case 32:
-        return launch(resamp_phase_kernel<CT, 32>);
+        return pick(std::integral_constant<int, 32>{});
     case 64:
-        return launch(resamp_phase_kernel<CT, 64>);
+        return pick(std::integral_constant<int, 64>{});
     }
     return 0;
 }
