@@ -38,7 +38,8 @@ int grb200_host_free(void* ptr)
 }
 int grb200_dev_alloc(int device, void** ptr, unsigned long long bytes)
 {
-    int rc = use_device(device);
+    grb::DeviceScope _ds(device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     cudaError_t e = cudaMalloc(ptr, (size_t)bytes);
@@ -48,7 +49,8 @@ int grb200_dev_alloc(int device, void** ptr, unsigned long long bytes)
 }
 int grb200_dev_free(int device, void* ptr)
 {
-    int rc = use_device(device);
+    grb::DeviceScope _ds(device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     GRB_CUDA(cudaFree(ptr));
@@ -56,7 +58,8 @@ int grb200_dev_free(int device, void* ptr)
 }
 int grb200_memcpy_h2d(int device, void* dst, const void* src, unsigned long long bytes)
 {
-    int rc = use_device(device);
+    grb::DeviceScope _ds(device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     GRB_CUDA(cudaMemcpy(dst, src, (size_t)bytes, cudaMemcpyHostToDevice));
@@ -64,7 +67,8 @@ int grb200_memcpy_h2d(int device, void* dst, const void* src, unsigned long long
 }
 int grb200_memcpy_d2h(int device, void* dst, const void* src, unsigned long long bytes)
 {
-    int rc = use_device(device);
+    grb::DeviceScope _ds(device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     GRB_CUDA(cudaMemcpy(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost));
@@ -72,7 +76,8 @@ int grb200_memcpy_d2h(int device, void* dst, const void* src, unsigned long long
 }
 int grb200_dev_sync(int device)
 {
-    int rc = use_device(device);
+    grb::DeviceScope _ds(device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     GRB_CUDA(cudaDeviceSynchronize());
@@ -160,10 +165,12 @@ int grb200_fir_set_taps(grb200_fir* h, const float* taps, int ntaps)
     if (!h || !taps || ntaps < 1)
         return fail(GRB200_EINVAL, "fir_filter::set_taps: bad arguments");
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    GRB_CUDA(cudaDeviceSynchronize()); // kernels in flight still read the old taps
+    if ((rc = h->sg.quiesce())) // launches through this handle may still read the old state
+        return rc;
     return fir_upload_taps(h, taps, ntaps);
 }
 
@@ -175,7 +182,8 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
     if (!h || noutput < 0 || (noutput > 0 && (!in_dev || !out_dev)))
         return fail(GRB200_EINVAL, "fir_filter::work_dev: bad arguments");
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     cudaStream_t st = pick_stream(stream, h->sg);
@@ -184,7 +192,7 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
         rc = rotate_launch(out_dev, noutput, h->theta, h->delta, st);
         h->theta = rotate_advance(h->theta, h->delta, noutput);
     }
-    return rc;
+    return dev_done(rc, h->sg, st);
 }
 
 int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long long noutput)
@@ -194,7 +202,8 @@ int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long lon
     if (noutput == 0)
         return 0;
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     const int D = h->decim, nt = h->ntaps;
@@ -233,7 +242,7 @@ void grb200_fir_destroy(grb200_fir* h)
 {
     if (!h)
         return;
-    cudaSetDevice(h->device);
+    grb::DeviceScope _ds(h->device);
     h->sg.destroy();
     h->gtaps.release();
     h->rev.release();

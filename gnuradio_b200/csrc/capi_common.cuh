@@ -86,7 +86,16 @@ inline std::vector<float2> make_roots(int N, int sign)
     return w;
 }
 
-inline cudaStream_t pick_stream(void* user, Stager& sg) { return user ? (cudaStream_t)user : sg.s_exec; }
+// `stream` argument of every *_work_dev: a cudaStream_t as void*.  NULL is what it is everywhere else in CUDA -- the legacy
+// default stream (torch's current stream unless the caller switched) -- so producer -> work_dev -> consumer on one stream
+// are ordered.  GRB200_STREAM_OWN selects the handle's private non-blocking stream.
+inline cudaStream_t pick_stream(void* user, Stager& sg)
+{
+    return user == GRB200_STREAM_OWN ? sg.s_exec : (cudaStream_t)user;
+}
+
+// epilogue of a device-resident launch: remember the caller's stream position so that set_* can wait for it
+inline int dev_done(int rc, Stager& sg, cudaStream_t st) { return rc ? rc : sg.note_user_launch(st); }
 
 } // namespace grb
 

@@ -99,10 +99,12 @@ int grb200_fftfilt_set_taps(grb200_fftfilt* h, const float* taps_re_im, int ntap
     if (!h || !taps_re_im || ntaps < 1)
         return fail(GRB200_EINVAL, "fft_filter_ccc::set_taps: bad arguments");
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    GRB_CUDA(cudaDeviceSynchronize());
+    if ((rc = h->sg.quiesce())) // launches through this handle may still read the old state
+        return rc;
     return fftfilt_prepare(h, taps_re_im, ntaps);
 }
 
@@ -141,11 +143,13 @@ int grb200_fftfilt_work_dev(grb200_fftfilt* h, const void* in_dev, void* out_dev
     if (!h || noutput < 0 || (noutput > 0 && (!in_dev || !out_dev)))
         return fail(GRB200_EINVAL, "fft_filter_ccc::work_dev: bad arguments");
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    return fftfilt_launch(h->L, h->parts, in_dev, out_dev, noutput, h->ntaps, h->decim, (const float2*)h->H.p,
-                          (const float2*)h->tw.p, sm_count(h->device), pick_stream(stream, h->sg));
+    cudaStream_t st_ = pick_stream(stream, h->sg);
+    return dev_done(fftfilt_launch(h->L, h->parts, in_dev, out_dev, noutput, h->ntaps, h->decim, (const float2*)h->H.p,
+                          (const float2*)h->tw.p, sm_count(h->device), st_), h->sg, st_);
 }
 
 int grb200_fftfilt_work(grb200_fftfilt* h, const void* in_host, void* out_host, long long noutput)
@@ -158,7 +162,8 @@ int grb200_fftfilt_work(grb200_fftfilt* h, const void* in_host, void* out_host, 
     if (noutput % h->nsamples != 0)
         return fail(GRB200_EINVAL, "fft_filter_ccc::work: noutput (%lld) must be a multiple of nsamples (%d)", noutput,
                     h->nsamples);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     const int D = h->decim, nh = h->ntaps - 1;
@@ -216,7 +221,7 @@ void grb200_fftfilt_destroy(grb200_fftfilt* h)
 {
     if (!h)
         return;
-    cudaSetDevice(h->device);
+    grb::DeviceScope _ds(h->device);
     h->sg.destroy();
     h->H.release();
     h->tw.release();

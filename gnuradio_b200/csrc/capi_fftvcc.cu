@@ -43,7 +43,8 @@ static int vcc_work_host(grb200_fftvcc* h, const void* in_host, void* out_host, 
     if (nvectors == 0)
         return 0;
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     const size_t vin = (size_t)h->N * 8, vout = (size_t)h->N * (magsq ? 4 : 8);
@@ -107,12 +108,14 @@ int grb200_fft_vcc_set_window(grb200_fftvcc* h, const float* window, int nwindow
     if (!h || nwindow < 0)
         return fail(GRB200_EINVAL, "fft_vcc::set_window: bad arguments");
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     if (nwindow != 0 && nwindow != h->N)
         return fail(GRB200_EWINDOW, "fft_vcc: window not the same length as fft_size");
-    GRB_CUDA(cudaDeviceSynchronize());
+    if ((rc = h->sg.quiesce())) // launches through this handle may still read the old state
+        return rc;
     return vcc_set_window(h, window, nwindow);
 }
 
@@ -132,10 +135,12 @@ int grb200_fft_vcc_work_dev(grb200_fftvcc* h, const void* in_dev, void* out_dev,
     if (!h || nvectors < 0 || (nvectors > 0 && (!in_dev || !out_dev)))
         return fail(GRB200_EINVAL, "fft_vcc::work_dev: bad arguments");
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    return vcc_run_dev(h, in_dev, out_dev, nvectors, 0, pick_stream(stream, h->sg));
+    cudaStream_t st_ = pick_stream(stream, h->sg);
+    return dev_done(vcc_run_dev(h, in_dev, out_dev, nvectors, 0, st_), h->sg, st_);
 }
 int grb200_fft_vcc_work_magsq_dev(grb200_fftvcc* h, const void* in_dev, float* out_dev, long long nvectors,
                                   void* stream)
@@ -143,17 +148,19 @@ int grb200_fft_vcc_work_magsq_dev(grb200_fftvcc* h, const void* in_dev, float* o
     if (!h || nvectors < 0 || (nvectors > 0 && (!in_dev || !out_dev)))
         return fail(GRB200_EINVAL, "fft_vcc::work_magsq_dev: bad arguments");
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    return vcc_run_dev(h, in_dev, out_dev, nvectors, 1, pick_stream(stream, h->sg));
+    cudaStream_t st_ = pick_stream(stream, h->sg);
+    return dev_done(vcc_run_dev(h, in_dev, out_dev, nvectors, 1, st_), h->sg, st_);
 }
 
 void grb200_fft_vcc_destroy(grb200_fftvcc* h)
 {
     if (!h)
         return;
-    cudaSetDevice(h->device);
+    grb::DeviceScope _ds(h->device);
     h->sg.destroy();
     h->window.release();
     h->tw.release();
@@ -166,7 +173,8 @@ static Stager* g_magsq_sg[64];
 
 static int magsq_stager(int device, Stager** out)
 {
-    int rc = use_device(device);
+    grb::DeviceScope _ds(device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     std::lock_guard<std::mutex> lk(g_magsq_mu);
@@ -190,7 +198,8 @@ int grb200_magsq_work_dev(int device, const void* in_dev, float* out_dev, long l
     int rc = magsq_stager(device, &sg);
     if (rc)
         return rc;
-    return magsq_launch(in_dev, out_dev, nitems, sm_count(device), pick_stream(stream, *sg));
+    cudaStream_t st_ = pick_stream(stream, *sg);
+    return dev_done(magsq_launch(in_dev, out_dev, nitems, sm_count(device), st_), *sg, st_);
 }
 
 int grb200_magsq_work(int device, const void* in_host, float* out_host, long long nitems)

@@ -194,10 +194,12 @@ int grb200_interp_fir_set_taps(grb200_interp* h, const float* taps, int ntaps)
     if (!h || !taps || ntaps < 1)
         return fail(GRB200_EINVAL, "interp_fir_filter::set_taps: bad arguments");
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    GRB_CUDA(cudaDeviceSynchronize()); // kernels in flight still read the old taps
+    if ((rc = h->sg.quiesce())) // launches through this handle may still read the old state
+        return rc;
     return interp_upload(h, taps, ntaps);
 }
 
@@ -213,11 +215,13 @@ int grb200_interp_fir_work_dev(grb200_interp* h, const void* in_dev, void* out_d
         return fail(GRB200_EINVAL, "interp_fir_filter: noutput (%lld) must be a multiple of the interpolation %d", noutput,
                     h->L);
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    return interp_launch(h->ct, in_dev, out_dev, noutput / h->L, h->L, h->T, (const float*)h->rev.p, sm_count(h->device),
-                         pick_stream(stream, h->sg));
+    cudaStream_t st_ = pick_stream(stream, h->sg);
+    return dev_done(interp_launch(h->ct, in_dev, out_dev, noutput / h->L, h->L, h->T, (const float*)h->rev.p, sm_count(h->device),
+                         st_), h->sg, st_);
 }
 
 int grb200_interp_fir_work(grb200_interp* h, const void* in_host, void* out_host, long long noutput)
@@ -230,7 +234,8 @@ int grb200_interp_fir_work(grb200_interp* h, const void* in_host, void* out_host
         return fail(GRB200_EINVAL, "interp_fir_filter: noutput (%lld) must be a multiple of the interpolation %d", noutput,
                     h->L);
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     const int L = h->L, T = h->T;
@@ -263,7 +268,7 @@ void grb200_interp_fir_destroy(grb200_interp* h)
 {
     if (!h)
         return;
-    cudaSetDevice(h->device);
+    grb::DeviceScope _ds(h->device);
     h->sg.destroy();
     h->rev.release();
     delete h;

@@ -107,10 +107,12 @@ int grb200_pfb_chan_set_taps(grb200_pfb* p, const float* taps, int ntaps)
     if (!p || !taps || ntaps < 1)
         return fail(GRB200_EINVAL, "pfb_channelizer_ccf::set_taps: bad arguments");
     std::lock_guard<std::mutex> lk(p->mu);
-    int rc = use_device(p->device);
+    grb::DeviceScope _ds(p->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    GRB_CUDA(cudaDeviceSynchronize());
+    if ((rc = p->sg.quiesce())) // launches through this handle may still read the old state
+        return rc;
     return pfb_upload_taps(p, taps, ntaps);
 }
 
@@ -124,10 +126,12 @@ int grb200_pfb_chan_set_channel_map(grb200_pfb* p, const int* map, int n)
         if (map[i] < 0 || map[i] >= p->M)
             return fail(GRB200_EINVAL, "pfb_channelizer_ccf_impl::set_channel_map: map range out of bounds.");
     std::lock_guard<std::mutex> lk(p->mu);
-    int rc = use_device(p->device);
+    grb::DeviceScope _ds(p->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    GRB_CUDA(cudaDeviceSynchronize());
+    if ((rc = p->sg.quiesce())) // launches through this handle may still read the old state
+        return rc;
     p->cmap.assign(map, map + n);
     return pfb_upload_map(p);
 }
@@ -166,11 +170,13 @@ int grb200_pfb_chan_work_interleaved_dev(grb200_pfb* p, const void* in_dev, void
         return rc;
     if (noutput % p->om != 0)
         return fail(GRB200_EINVAL, "pfb_channelizer_ccf: noutput (%lld) must be a multiple of %d", noutput, p->om);
-    if ((rc = use_device(p->device)))
+    grb::DeviceScope _ds(p->device);
+    if ((rc = _ds.rc))
         return rc;
-    return pfb_launch(p->M, p->T, p->R, in_dev, out_dev, out_stride, nout_streams, (const int*)p->dmap.p,
+    cudaStream_t st_ = pick_stream(stream, p->sg);
+    return dev_done(pfb_launch(p->M, p->T, p->R, in_dev, out_dev, out_stride, nout_streams, (const int*)p->dmap.p,
                       p->identity ? 1 : 0, noutput, (const float*)p->h.p, (const float2*)p->wM.p,
-                      sm_count(p->device), true, pick_stream(stream, p->sg));
+                      sm_count(p->device), true, st_), p->sg, st_);
 }
 
 // Shared host-staged driver.  `interleaved` selects the input form:
@@ -193,7 +199,8 @@ static int pfb_work_host(grb200_pfb* p, int interleaved, const void* const* in_s
         *consumed = rows_total;
     if (noutput == 0)
         return 0;
-    if ((rc = use_device(p->device)))
+    grb::DeviceScope _ds(p->device);
+    if ((rc = _ds.rc))
         return rc;
     // chunk: outputs per chunk, a multiple of the output multiple so every chunk starts on a whole input row
     long long chunk = (long long)(kChunkBytes / 8) / R;
@@ -253,7 +260,7 @@ void grb200_pfb_chan_destroy(grb200_pfb* p)
 {
     if (!p)
         return;
-    cudaSetDevice(p->device);
+    grb::DeviceScope _ds(p->device);
     p->sg.destroy();
     p->h.release();
     p->wM.release();

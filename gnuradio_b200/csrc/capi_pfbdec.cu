@@ -390,10 +390,12 @@ int grb200_pfb_dec_set_taps(grb200_pfbdec* p, const float* taps, int ntaps)
     if (!p || !taps || ntaps < 1)
         return fail(GRB200_EINVAL, "pfb_decimator_ccf::set_taps: bad arguments");
     std::lock_guard<std::mutex> lk(p->mu);
-    int rc = use_device(p->device);
+    grb::DeviceScope _ds(p->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    GRB_CUDA(cudaDeviceSynchronize()); // kernels in flight still read the old taps
+    if ((rc = p->sg.quiesce())) // launches through this handle may still read the old state
+        return rc;
     p->proto.assign(taps, taps + ntaps);
     return pfbdec_upload(p);
 }
@@ -405,10 +407,12 @@ int grb200_pfb_dec_set_channel(grb200_pfbdec* p, unsigned int channel)
     if ((int)channel >= p->M)
         return fail(GRB200_EINVAL, "pfb_decimator_ccf: channel %u out of range (decimation %d)", channel, p->M);
     std::lock_guard<std::mutex> lk(p->mu);
-    int rc = use_device(p->device);
+    grb::DeviceScope _ds(p->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    GRB_CUDA(cudaDeviceSynchronize());
+    if ((rc = p->sg.quiesce())) // launches through this handle may still read the old state
+        return rc;
     p->chan = (int)channel;
     return pfbdec_upload(p);
 }
@@ -422,11 +426,13 @@ int grb200_pfb_dec_work_dev(grb200_pfbdec* p, const void* x_dev, long long strid
     if (!p || noutput < 0 || (noutput > 0 && (!x_dev || !out_dev)) || stride < noutput + p->T - 1)
         return fail(GRB200_EINVAL, "pfb_decimator_ccf::work_dev: bad arguments");
     std::lock_guard<std::mutex> lk(p->mu);
-    int rc = use_device(p->device);
+    grb::DeviceScope _ds(p->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    return pfbdec_launch(x_dev, stride, out_dev, noutput, p->M, p->T, (const float*)p->crev.p, (const float2*)p->rot.p,
-                         sm_count(p->device), pick_stream(stream, p->sg));
+    cudaStream_t st_ = pick_stream(stream, p->sg);
+    return dev_done(pfbdec_launch(x_dev, stride, out_dev, noutput, p->M, p->T, (const float*)p->crev.p, (const float2*)p->rot.p,
+                         sm_count(p->device), st_), p->sg, st_);
 }
 
 // carry_state = 0: in_streams[s] holds noutput + T-1 items, history first (the block's set_history(T) mode, :61).
@@ -441,7 +447,8 @@ int grb200_pfb_dec_work(grb200_pfbdec* p, const void* const* in_streams, void* o
     if (noutput == 0)
         return 0;
     std::lock_guard<std::mutex> lk(p->mu);
-    int rc = use_device(p->device);
+    grb::DeviceScope _ds(p->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
     const int M = p->M, T = p->T, Hn = T - 1;
@@ -502,7 +509,7 @@ void grb200_pfb_dec_destroy(grb200_pfbdec* p)
 {
     if (!p)
         return;
-    cudaSetDevice(p->device);
+    grb::DeviceScope _ds(p->device);
     p->sg.destroy();
     p->crev.release();
     p->rot.release();

@@ -117,7 +117,10 @@ __global__ void __launch_bounds__(256) resamp_phase_kernel(const float2* __restr
 #pragma unroll
             for (int j = 0; j < TT / 2; j++) {
                 const float4 v = __ldg(x + j);
-                mac(a, make_float2(v.x, v.y), 2 * j);
+                // an odd window starts one item late: in[q] lies OUTSIDE the reference's window, so it must not enter the
+                // sum at all (0 * Inf/NaN would poison an output the reference keeps finite)
+                if (!(j == 0 && odd))
+                    mac(a, make_float2(v.x, v.y), 2 * j);
                 mac(a, make_float2(v.z, v.w), 2 * j + 1);
             }
             if (odd)
@@ -296,10 +299,12 @@ int grb200_rational_resampler_set_taps(grb200_resamp* h, const float* taps, int 
     if (!h || !taps || ntaps < 1)
         return fail(GRB200_EINVAL, "rational_resampler_base::set_taps: bad arguments");
     std::lock_guard<std::mutex> lk(h->mu);
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    GRB_CUDA(cudaDeviceSynchronize()); // kernels in flight still read the old taps
+    if ((rc = h->sg.quiesce())) // launches through this handle may still read the old state
+        return rc;
     return resamp_upload(h, taps, ntaps);
 }
 
@@ -329,11 +334,14 @@ int grb200_rational_resampler_work_dev(grb200_resamp* h, const void* in_dev, lon
     resamp_counts(h, nin, noutput, &n, &used, &ctr_after);
     if (n > 0 && (!in_dev || !out_dev))
         return fail(GRB200_EINVAL, "rational_resampler_base::work_dev: null buffer");
-    int rc = use_device(h->device);
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
     if (rc)
         return rc;
-    rc = resamp_launch(h->ct, in_dev, out_dev, n, h->ctr, h->L, h->D, h->T, (const float*)h->rev.p, sm_count(h->device),
-                       pick_stream(stream, h->sg));
+    cudaStream_t st_ = pick_stream(stream, h->sg);
+    rc = dev_done(resamp_launch(h->ct, in_dev, out_dev, n, h->ctr, h->L, h->D, h->T, (const float*)h->rev.p,
+                                sm_count(h->device), st_),
+                  h->sg, st_);
     if (rc)
         return rc;
     h->ctr = ctr_after;
@@ -356,7 +364,8 @@ int grb200_rational_resampler_work(grb200_resamp* h, const void* in_host, long l
     if (n > 0) {
         if (!in_host || !out_host)
             return fail(GRB200_EINVAL, "rational_resampler_base::work: null buffer");
-        int rc = use_device(h->device);
+        grb::DeviceScope _ds(h->device);
+        int rc = _ds.rc;
         if (rc)
             return rc;
         const unsigned long long L = h->L, D = h->D, c0 = h->ctr;
@@ -415,7 +424,7 @@ void grb200_rational_resampler_destroy(grb200_resamp* h)
 {
     if (!h)
         return;
-    cudaSetDevice(h->device);
+    grb::DeviceScope _ds(h->device);
     h->sg.destroy();
     h->rev.release();
     delete h;

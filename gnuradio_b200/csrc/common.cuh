@@ -4,6 +4,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -43,9 +44,32 @@ inline int fail(int code, const char* fmt, ...)
                              cudaGetErrorString(_e), __FILE__, __LINE__);                   \
     } while (0)
 
+// tuning / developer knobs are read from the environment ONCE per process, never per work() call
+#define GRB_GETENV_ONCE(name) ([]() -> const char* { static const char* const v_ = getenv(name); return v_; }())
+
 // Select a device and check that it is a Blackwell (sm_100) part: there is no other code path.
 int use_device(int device);
 int sm_count(int device);
+// Every C-ABI entry point runs inside one of these: selects the handle's device for the call and puts the CALLER's
+// current device back on return (a torch / NCCL process keeps its own current device).
+struct DeviceScope {
+    int prev = -1, dev = -1, rc = 0;
+    explicit DeviceScope(int device) : dev(device)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) {
+            cudaGetLastError();
+            prev = -1;
+        }
+        rc = use_device(device);
+    }
+    ~DeviceScope()
+    {
+        if (prev >= 0 && prev != dev)
+            cudaSetDevice(prev);
+    }
+    DeviceScope(const DeviceScope&) = delete;
+    DeviceScope& operator=(const DeviceScope&) = delete;
+};
 
 // ---- device-side complex helpers --------------------------------------------------------------
 // Packed FP32 (sm_100 FADD2/FMUL2/FFMA2): a complex add is ONE instruction, a complex multiply TWO; the

@@ -518,7 +518,7 @@ static int launch_upols(const void* in, void* out, long long nout, long long nin
     int by_regs = 65536 / (fa.numRegs * (L / 16)), by_smem = (227 * 1024) / (G::SMEM + 1024), by_tmem = 512 / G::tmem_cols(K);
     int fit = by_regs < by_smem ? by_regs : by_smem;
     fit = fit < by_tmem ? fit : by_tmem;
-    if (const char* e = getenv("GRB200_FFTFILT_UPOLS_OCC"))
+    if (const char* e = GRB_GETENV_ONCE("GRB200_FFTFILT_UPOLS_OCC"))
         fit = atoi(e);
     if (fit > occ)
         occ = fit;
@@ -544,7 +544,7 @@ int fftfilt_device_plan(int ntaps, int* parts)
         L *= 2;
     if (L == 8192 && ntaps - 1 > L / 4)
         L = 16384; // > 25 % of every block would be overlap: the longer transform wins (cfg2: 70 -> 78 Gsps)
-    const char* ue = getenv("GRB200_FFTFILT_UPOLS"); // 0 = never, 1 = whenever the geometry allows, unset = auto
+    const char* ue = GRB_GETENV_ONCE("GRB200_FFTFILT_UPOLS"); // 0 = never, 1 = whenever the geometry allows, unset = auto
     const int upols = ue ? atoi(ue) : -1;
     // 2050..10240 taps: K = ceil(ntaps / 2048) partitions on the 4096-point kernel (K-1 <= 4 parked spectra fit in the
     // 512 TMEM columns of an SM at two CTAs) beat the 16384-point transform; below 2050 plain overlap-save is faster.
@@ -556,7 +556,7 @@ int fftfilt_device_plan(int ntaps, int* parts)
         L = 4096;
         K = kneed < 2 ? 2 : kneed;
     }
-    if (const char* e = getenv("GRB200_FFTFILT_L")) { // tuning knob: a longer transform wastes less on the overlap
+    if (const char* e = GRB_GETENV_ONCE("GRB200_FFTFILT_L")) { // tuning knob: a longer transform wastes less on the overlap
         const int v = atoi(e);
         if (K == 1 && (v == 4096 || v == 8192 || v == 16384) && v >= L)
             L = v;
@@ -592,7 +592,7 @@ int fftfilt_launch(int L, int parts, const void* in, void* out, long long nout, 
         return fail(GRB200_ERANGE, "fft_filter: no partitioned kernel for fft length %d", L);
     }
     static const bool use_stream = [] {
-        const char* e = getenv("GRB200_FFTFILT_STREAM");
+        const char* e = GRB_GETENV_ONCE("GRB200_FFTFILT_STREAM");
         return !(e && e[0] == '0');
     }();
     if (use_stream && (((uintptr_t)in) & 15) == 0) { // TMA bulk copies need a 16-byte aligned stream

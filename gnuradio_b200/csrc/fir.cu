@@ -552,7 +552,7 @@ static FirPlan plan_fir(int D, int ntaps, bool ct)
             best.smem = per_warp * (NT / 32) + (size_t)D * best.Upad * (ct ? 8 : 4);
         }
     };
-    if (const char* e = getenv("GRB200_FIR_PLAN")) { // tuning knob: "R,NT,NBUF" (NBUF 3 = warp-private pipelines)
+    if (const char* e = GRB_GETENV_ONCE("GRB200_FIR_PLAN")) { // tuning knob: "R,NT,NBUF" (NBUF 3 = warp-private pipelines)
         int R = 0, NT = 0, NB = 0;
         if (sscanf(e, "%d,%d,%d", &R, &NT, &NB) == 3 && (R == 8 || R == 16) && NT >= 32 && NT <= 256 && NT % 32 == 0) {
             if (NB == 1 || NB == 2)
@@ -582,7 +582,7 @@ static FirPlan plan_fir(int D, int ntaps, bool ct)
         }
     };
     static const bool allow_splitk = [] {
-        const char* e = getenv("GRB200_FIR_SPLITK");
+        const char* e = GRB_GETENV_ONCE("GRB200_FIR_SPLITK");
         return !(e && e[0] == '0');
     }();
     if (allow_splitk) {

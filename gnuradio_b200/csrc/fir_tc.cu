@@ -569,8 +569,12 @@ int fir_tc_mode(bool ct, int D, int ntaps, const void* in, long long nout)
         mode = tc::M_DEC8;
     if (mode < 0 || ((uintptr_t)in & 15) != 0)
         return -1;
-    if (const char* e = getenv("GRB200_FIR_TC"))
-        return atoi(e) != 0 ? mode : -1;
+    static const int forced = [] { // read once, not per work()
+        const char* e = getenv("GRB200_FIR_TC");
+        return e ? (atoi(e) != 0 ? 1 : 0) : -1;
+    }();
+    if (forced >= 0)
+        return forced ? mode : -1;
     if (mode == tc::M_CCC && ntaps < 20) // measured: the CUDA-core ccc kernel is as fast below ~20 taps (137 vs 154 Gsps at 21)
         return -1;
     if (mode == tc::M_DEC8 && ntaps < 256) // short decimators are already HBM-bound on the CUDA cores
@@ -595,7 +599,8 @@ static int fir_tc_launch_t(int ntaps, const void* rev, const void* in, void* out
     const long long orows = (nout + C::OUT_PER_ROW - 1) / C::OUT_PER_ROW;
     const long long ntiles = (orows + C::OROWS - 1) / C::OROWS;
     const unsigned grid = (unsigned)(ntiles < nsm ? ntiles : nsm);
-    if (const char* path = getenv("GRB200_FIR_TC_TRACE")) { // developer aid: per-tile clock64() stamps of CTA 0
+    static const char* const trace_path = getenv("GRB200_FIR_TC_TRACE"); // read once, not per work()
+    if (const char* path = trace_path) { // developer aid: per-tile clock64() stamps of CTA 0
         long long* dtrace = nullptr;
         GRB_CUDA(cudaMalloc(&dtrace, 64 * 16 * sizeof(long long)));
         GRB_CUDA(cudaMemsetAsync(dtrace, 0, 64 * 16 * sizeof(long long), st));

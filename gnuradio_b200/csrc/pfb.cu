@@ -300,7 +300,7 @@ int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stri
     if (noutput <= 0)
         return 0;
     const long long nrows = T + (noutput * R) / M; // history rows + consumed rows
-    if (allow_fast && identity && pfb_stream_supported(M, T, R, x) && !getenv("GRB200_PFB_V1"))
+    if (allow_fast && identity && pfb_stream_supported(M, T, R, x) && !GRB_GETENV_ONCE("GRB200_PFB_V1"))
         return pfb_stream_launch(M, T, x, out, out_stride, nouts, noutput, h, wM, nsm, st);
     if (allow_fast && R == M && T <= 32 && (M == 16 || M == 64 || M == 256)) {
         if (M == 16)

@@ -49,7 +49,31 @@ int Stager::init(int dev_id)
         GRB_CUDA(cudaEventCreateWithFlags(&ev_exec[i], cudaEventDisableTiming));
         GRB_CUDA(cudaEventCreateWithFlags(&ev_d2h[i], cudaEventDisableTiming));
     }
+    GRB_CUDA(cudaEventCreateWithFlags(&ev_user, cudaEventDisableTiming));
     ready = true;
+    return 0;
+}
+
+int Stager::note_user_launch(cudaStream_t st)
+{
+    if (st == s_exec)
+        return 0;
+    GRB_CUDA(cudaEventRecord(ev_user, st));
+    user_pending = true;
+    return 0;
+}
+
+int Stager::quiesce()
+{
+    if (!ready)
+        return 0;
+    GRB_CUDA(cudaStreamSynchronize(s_h2d));
+    GRB_CUDA(cudaStreamSynchronize(s_exec));
+    GRB_CUDA(cudaStreamSynchronize(s_d2h));
+    if (user_pending) {
+        GRB_CUDA(cudaEventSynchronize(ev_user));
+        user_pending = false;
+    }
     return 0;
 }
 
@@ -57,7 +81,7 @@ void Stager::destroy()
 {
     if (!ready)
         return;
-    cudaSetDevice(device);
+    DeviceScope ds(device);
     cudaStreamSynchronize(s_h2d);
     cudaStreamSynchronize(s_exec);
     cudaStreamSynchronize(s_d2h);
@@ -73,9 +97,19 @@ void Stager::destroy()
             if (dev[i][k])
                 cudaFree(dev[i][k]);
     }
+    if (user_pending)
+        cudaEventSynchronize(ev_user);
+    cudaEventDestroy(ev_user);
     cudaStreamDestroy(s_h2d);
     cudaStreamDestroy(s_exec);
     cudaStreamDestroy(s_d2h);
+    for (int i = 0; i < NSLOT; i++) {
+        pin_in[i] = pin_out[i] = nullptr;
+        for (int k = 0; k < 3; k++)
+            dev[i][k] = nullptr;
+    }
+    pin_in_cap = pin_out_cap = 0;
+    dev_cap[0] = dev_cap[1] = dev_cap[2] = 0;
     ready = false;
 }
 

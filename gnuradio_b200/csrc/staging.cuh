@@ -28,9 +28,16 @@ struct Stager {
     void* dev[NSLOT][3] = {}; // [slot][in, out, scratch]
     size_t dev_cap[3] = { 0, 0, 0 };
     bool ready = false;
+    // last *_work_dev launch on a CALLER's stream: setters wait for it (and for the handle's own streams) instead of
+    // stalling the whole device with cudaDeviceSynchronize
+    cudaEvent_t ev_user = nullptr;
+    bool user_pending = false;
 
     int init(int dev_id);
     void destroy();
+    ~Stager() { destroy(); } // create-failure paths delete the handle without calling destroy()
+    int note_user_launch(cudaStream_t st); // record ev_user behind a device-resident launch
+    int quiesce();                         // block until nothing launched through this handle is still running
     int reserve_dev(int which, size_t bytes);  // both slots
     int reserve_pin(bool in, size_t bytes);    // both slots
     static bool is_pinned(const void* p);

@@ -15,7 +15,9 @@
  *                   over, gnuradio-runtime/include/gnuradio/block.h:176-179); blocks until the outputs are valid.
  *                   Inputs are staged through pinned double-buffered async copies on the handle's streams.
  *  - `*_work_dev` : DEVICE buffers (device-resident chaining mode); asynchronous on `stream`
- *                   (a cudaStream_t passed as void*, NULL = the handle's own stream).
+ *                   (a cudaStream_t passed as void*; NULL = CUDA's legacy default stream, as everywhere else in
+ *                   CUDA -- so a producer, work_dev and a consumer on one stream are ordered; GRB200_STREAM_OWN =
+ *                   the handle's private non-blocking stream).  set_* waits for the handle's own work only.
  *  - One handle <-> one calling thread for work(); set_* may come from any thread (internally serialised,
  *    mirroring d_setlock / d_mutex in the reference blocks).
  *  - There is no CPU fallback: every call fails with GRB200_ECUDA when no sm_100 device is usable.
@@ -26,6 +28,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+
+/* `stream` sentinel: run on the handle's private stream (never a valid cudaStream_t) */
+#define GRB200_STREAM_OWN ((void*)(~(unsigned long long)0))
 
 typedef enum {
     GRB200_OK = 0,
