@@ -93,6 +93,14 @@ class Workload:
     def describe(self):
         return self.name
 
+    # -- parity OUTSIDE the timed region: first/last segment + 64 seeded interior windows of the last step's output against
+    #    the CPU oracle and float64 (oracle/spotcheck.py -- the checker, never the thing measured) -------------------------
+    def fetch_c64(self, t):
+        return lambda a, b: t[2 * a: 2 * b].cpu().numpy().view(np.complex64)
+
+    def parity(self, sc):
+        return None
+
     def free(self):
         for k in list(self.__dict__):
             if k.startswith("d_"):
@@ -126,6 +134,13 @@ class PfbChannelizer(Workload):
 
     def describe(self):
         return self.name % self.log2n
+
+    def parity(self, sc):
+        M, nout = self.M, self.nout
+        xv, yv = self.d_in.view(-1, 2 * M), self.d_out.view(M, 2 * nout)
+        return sc.pfb_channelizer(lambda a, b: xv[a:b].cpu().numpy().view(np.complex64),
+                                  lambda a, b: np.ascontiguousarray(yv[:, 2 * a: 2 * b].cpu().numpy()).view(np.complex64),
+                                  M, self.taps, nout, width=64, count=64, seed=self.seed)
 
     # -- multi-GPU: the segment's history comes from the left neighbour's tail ---------------------------
     def halo_views(self):
@@ -187,6 +202,11 @@ class FirCcf(Workload):
     def step(self):
         for i in range(self.nsets):
             self.blk.work_dev(self.d_in[i].data_ptr(), self.d_out[i].data_ptr(), self.nout, self.stream)
+
+    def parity(self, sc):
+        k = len(self.d_in) - 1  # the last buffer set the step wrote
+        return sc.fir(self.fetch_c64(self.d_in[k]), self.fetch_c64(self.d_out[k]), self.decim, self.taps, self.nout,
+                      width=512, count=64, seed=self.seed)
 
     def halo_views(self):  # ntaps-1 history items in front of every segment
         h = 2 * (self.ntaps - 1)
@@ -259,6 +279,10 @@ class FftFilter(Workload):
     def describe(self):
         return self.name % self.log2n
 
+    def parity(self, sc):
+        return sc.fft_filter(self.fetch_c64(self.d_in), self.fetch_c64(self.d_out), self.taps, self.nout, count=64,
+                             seed=self.seed)
+
     def cpu_setup(self, lay, log2n):
         rng = np.random.default_rng(self.seed)
         n = 1 << log2n
@@ -277,7 +301,7 @@ class FftVccMagSq(Workload):
     name = "fft_vcc 4096 Blackman-Harris fwd shift + complex_to_mag_squared fused, 2^%d samples (BASELINE configs[4])"
     block = "fft_vcc+complex_to_mag_squared"
     alg_bytes, flops, log2n, seed = 12.0, 65.0, 30, 5
-    kernel = "fft_vcc_kernel"
+    kernel = "fft_vcc_stream_kernel"
     N = 4096
 
     def setup(self):
@@ -292,6 +316,12 @@ class FftVccMagSq(Workload):
 
     def describe(self):
         return self.name % self.log2n
+
+    def parity(self, sc):
+        N = self.N
+        xv, yv = self.d_in.view(self.nvec, 2 * N), self.d_out.view(self.nvec, N)
+        return sc.fft_vcc(lambda a, b: xv[a:b].cpu().numpy().view(np.complex64), lambda a, b: yv[a:b].cpu().numpy(), N, True,
+                          self.win, True, self.nvec, magsq=True, count=64, seed=self.seed)
 
     def cpu_setup(self, lay, log2n):
         rng = np.random.default_rng(self.seed)
@@ -320,6 +350,18 @@ class FreqXlating(FirCcf):
         self.d_out = [self.torch.empty(2 * self.nout, dtype=self.torch.float32, device="cuda")]
         self.launches_per_step = 2
         self.samples_per_step = self.n
+
+    def parity(self, sc):
+        from oracle import pyoracle as po
+
+        # a fresh block: the rotator phase of the timed block has run on over every step
+        blk = self.grb.filter.freq_xlating_fir_filter_ccf(self.decim, self.taps, 0.21, 1.0, device=self.device)
+        blk.work_dev(self.d_in[0].data_ptr(), self.d_out[0].data_ptr(), self.nout, self.stream)
+        self.torch.cuda.synchronize()
+        ctaps = blk.composite_taps()
+        delta = po.xlat_increment_angle(np.float32(2 * np.pi * 0.21 / 1.0), self.decim)
+        return sc.fir(self.fetch_c64(self.d_in[0]), self.fetch_c64(self.d_out[0]), self.decim, ctaps, self.nout, width=512,
+                      count=64, seed=self.seed, rotator=(0.0, delta))
 
     def cpu_call(self):
         self.cpu_lay.freq_xlating_fir(self.decim, self.cpu_taps, 0.21, 1.0, self.cpu_x, self.cpu_nout)
@@ -350,6 +392,11 @@ class PfbDecimator(Workload):
 
     def describe(self):
         return self.name % self.log2n
+
+    def parity(self, sc):
+        xv = self.d_in.view(self.M, 2 * self.stride)
+        return sc.pfb_decimator(lambda s_, a, b: xv[s_, 2 * a: 2 * b].cpu().numpy().view(np.complex64),
+                                self.fetch_c64(self.d_out), self.M, self.taps, 5, self.nout, width=128, count=64, seed=self.seed)
 
     def cpu_setup(self, lay, log2n):
         rng = np.random.default_rng(self.seed)
@@ -509,6 +556,23 @@ def timed_steps(torch, dist, wl, steps, warmup, halo=None):
     return total, per
 
 
+def run_parity(torch, wl):
+    """Spot-window parity of the workload's LAST step at its full size (outside any timed region): first + last segment and 64
+    seeded interior windows against the CPU oracle and float64.  north_star tolerance: NRMS <= 1e-5, max-abs <= 1e-4 x RMS."""
+    try:
+        from oracle import spotcheck as sc  # the checker (test infrastructure), used as such
+
+        torch.cuda.synchronize()
+        res = wl.parity(sc)
+        if res is None:
+            return None
+        res["ok"] = bool(sc.ok(res))
+        res["tolerance"] = {"nrms": sc.NRMS_TOL, "max_over_rms": sc.MAXABS_TOL}
+        return res
+    except Exception as e:  # a checker failure must be visible in the line, not hide the measurement
+        return {"error": repr(e)[:300], "ok": False}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -591,6 +655,8 @@ def main():
                 "alg_bytes_per_sample": wl.alg_bytes, "alg_flops_per_sample": wl.flops,
                 "fp32_tflops": wl.flops * samples_per_step / wl.launches_per_step / (kernel_ms * 1e-3) / 1e12}
 
+    parity = run_parity(torch, wl)
+
     line = {
         "metric": "complex Msps (%s)" % wl.block, "value": value, "unit": "Msps", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -599,7 +665,7 @@ def main():
                    "l2": "inputs larger than L2 (%.1f GiB read per step)" % (8.0 * samples_per_step / 2 ** 30),
                    "parallelism": "time-sharded x%d, weak scaling, %d-sample history halo over NCCL send/recv" % (
                        world, getattr(wl, "halo_items", 0)) if world > 1 else "single GPU"},
-        "roofline": roofline, "gpu_launches": launches_timed, "gpu_launches_total_process": launches,
+        "roofline": roofline, "parity": parity, "gpu_launches": launches_timed, "gpu_launches_total_process": launches,
     }
 
     if not args.no_e2e and hasattr(wl, "e2e_setup"):
@@ -645,7 +711,8 @@ def main():
                 ach = o.alg_bytes * sps / o.launches_per_step / (kms * 1e-3) / 1e9
                 others[key] = {"workload": o.describe(), "msps": sps * len(pr) / (tot * 1e-3) / 1e6,
                                "hbm_gbs": ach, "hbm_frac": ach / peak, "kernel_ms": kms,
-                               "fp32_tflops": o.flops * sps / o.launches_per_step / (kms * 1e-3) / 1e12}
+                               "fp32_tflops": o.flops * sps / o.launches_per_step / (kms * 1e-3) / 1e12,
+                               "kernel": o.kernel, "parity": run_parity(torch, o)}
                 o.free()
                 del o
             except Exception as e:  # a failing side config must not hide the headline

@@ -65,3 +65,18 @@ def lowpass_taps(ntaps, cutoff, window):
     n = np.arange(ntaps) - M / 2.0
     h = np.sinc(2 * cutoff * n) * 2 * cutoff * np.asarray(window, np.float64)
     return (h / h.sum()).astype(np.float32)
+
+
+def coswindow(n, c0, c1, c2, c3=0.0):
+    """gr-fft/lib/window.cc:94-104 in float64."""
+    M = n - 1
+    k = np.arange(n)
+    return c0 - c1 * np.cos(2 * np.pi * k / M) + c2 * np.cos(4 * np.pi * k / M) - c3 * np.cos(6 * np.pi * k / M)
+
+
+def blackman_harris(n):
+    return coswindow(n, 0.35875, 0.48829, 0.14128, 0.01168).astype(np.float32)  # window.cc:170-185, atten 92
+
+
+def hamming(n):
+    return coswindow(n, 0.54, 0.46, 0.0).astype(np.float32)
