@@ -302,6 +302,9 @@ class FftVccMagSq(Workload):
     block = "fft_vcc+complex_to_mag_squared"
     alg_bytes, flops, log2n, seed = 12.0, 65.0, 30, 5
     kernel = "fft_vcc_stream_kernel"
+    # profiles/r2_fftvcc_stream_ncu.txt: 8.590 GB read + 4.267 GB written per 2^30-sample launch (algorithmic 8.59 + 4.29)
+    ncu_dram_bytes_per_sample = (8.590198e9 + 4.267297e9) / (1 << 30)
+    ncu_source = "profiles/r2_fftvcc_stream_ncu.txt"
     N = 4096
 
     def setup(self):

@@ -98,6 +98,7 @@ struct grb200_fir {
     // freq_xlating_fir_filter (capi_xlat.cu) drives this handle with a rotator behind the filter: out[n] *= e^{j (theta + n delta)}
     bool rot = false;
     double theta = 0.0, delta = 0.0;
+    int tc_pref = -1; // GRB200_FIR_TC as it stood when the handle was made
     Stager sg;
     std::mutex mu;
 };
@@ -139,6 +140,7 @@ static int fir_create(bool ct, int decim, const float* taps, int ntaps, int devi
     h->device = device;
     h->ct = ct;
     h->decim = decim;
+    h->tc_pref = fir_tc_env();
     int rc = h->sg.init(device);
     if (rc)
         return rc;
@@ -187,7 +189,7 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
     if (rc)
         return rc;
     cudaStream_t st = pick_stream(stream, h->sg);
-    rc = fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput, st);
+    rc = fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput, h->tc_pref, st);
     if (!rc && h->rot) {
         rc = rotate_launch(out_dev, noutput, h->theta, h->delta, st);
         h->theta = rotate_advance(h->theta, h->delta, noutput);
@@ -228,7 +230,7 @@ int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long lon
         },
         [&](long long c, int slot, cudaStream_t st) {
             const long long o0 = c * chunk, n = std::min(chunk, noutput - o0);
-            int r2 = fir_launch(h->ct, D, nt, h->gtaps.p, h->rev.p, sg.dev[slot][0], sg.dev[slot][1], n, st);
+            int r2 = fir_launch(h->ct, D, nt, h->gtaps.p, h->rev.p, sg.dev[slot][0], sg.dev[slot][1], n, h->tc_pref, st);
             if (!r2 && h->rot)
                 r2 = rotate_launch(sg.dev[slot][1], n, rotate_advance(h->theta, h->delta, o0), h->delta, st);
             return r2;

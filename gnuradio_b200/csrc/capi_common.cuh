@@ -8,8 +8,10 @@
 
 namespace grb {
 // kernels' host launchers (fir.cu, fftvcc.cu, fftfilt.cu, pfb.cu)
+// tc_pref: the handle's GRB200_FIR_TC setting, read when the handle is made (fir_tc_env): -1 auto, 0 never, 1 whenever possible
 int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, const void* in, void* out,
-               long long nout, cudaStream_t st);
+               long long nout, int tc_pref, cudaStream_t st);
+int fir_tc_env();
 int fir_upad(int D, int ntaps);
 // rotator behind freq_xlating_fir_filter: y[n] *= e^{j (theta + n delta)} in place (fir.cu); angle bookkeeping on the host
 int rotate_launch(void* y, long long n, double theta, double delta, cudaStream_t st);

@@ -536,7 +536,8 @@ static int launch_upols(const void* in, void* out, long long nout, long long nin
 }
 
 // Device plan for a tap count: FFT length L (at least the reference's 2*2^ceil(log2 ntaps), never below 4096) and
-// the number of tap partitions K (1 = plain overlap-save with hop L-ntaps+1, 2 = partitioned with hop L/2).
+// the number of tap partitions K (1 = plain overlap-save with hop L-ntaps+1, 2 = partitioned with hop L/2).  Runs at
+// create / set_taps time only (the developer knobs below are never read per work()).
 int fftfilt_device_plan(int ntaps, int* parts)
 {
     int L = 4096, K = 1;
@@ -544,7 +545,7 @@ int fftfilt_device_plan(int ntaps, int* parts)
         L *= 2;
     if (L == 8192 && ntaps - 1 > L / 4)
         L = 16384; // > 25 % of every block would be overlap: the longer transform wins (cfg2: 70 -> 78 Gsps)
-    const char* ue = GRB_GETENV_ONCE("GRB200_FFTFILT_UPOLS"); // 0 = never, 1 = whenever the geometry allows, unset = auto
+    const char* ue = getenv("GRB200_FFTFILT_UPOLS");           // 0 = never, 1 = whenever the geometry allows, unset = auto
     const int upols = ue ? atoi(ue) : -1;
     // 2050..10240 taps: K = ceil(ntaps / 2048) partitions on the 4096-point kernel (K-1 <= 4 parked spectra fit in the
     // 512 TMEM columns of an SM at two CTAs) beat the 16384-point transform; below 2050 plain overlap-save is faster.
@@ -556,7 +557,7 @@ int fftfilt_device_plan(int ntaps, int* parts)
         L = 4096;
         K = kneed < 2 ? 2 : kneed;
     }
-    if (const char* e = GRB_GETENV_ONCE("GRB200_FFTFILT_L")) { // tuning knob: a longer transform wastes less on the overlap
+    if (const char* e = getenv("GRB200_FFTFILT_L")) { // tuning knob: a longer transform wastes less on the overlap
         const int v = atoi(e);
         if (K == 1 && (v == 4096 || v == 8192 || v == 16384) && v >= L)
             L = v;

@@ -698,13 +698,13 @@ static int launch_tiled_nb(const FirPlan& pl, const void* in, void* out, long lo
                         : launch_tiled<R, CT, 1>(pl, in, out, nout, nin, D, gtaps, nsm, st);
 }
 
-int fir_tc_mode(bool ct, int D, int ntaps, const void* in, long long nout);
+int fir_tc_mode(bool ct, int D, int ntaps, const void* in, long long nout, int tc_pref);
 int fir_tc_launch(int mode, int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
                   cudaStream_t st);
 
 // gtaps: phase-major padded taps [D][Upad]; rev: reversed taps [ntaps] (both on the device).
 int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, const void* in, void* out,
-               long long nout, cudaStream_t st)
+               long long nout, int tc_pref, cudaStream_t st)
 {
     if (nout <= 0)
         return 0;
@@ -713,7 +713,7 @@ int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, co
     int dev = 0;
     cudaGetDevice(&dev);
     const int nsm = sm_count(dev);
-    const int tc_mode = fir_tc_mode(ct, D, ntaps, in, nout); // tcgen05 block-Toeplitz paths (fir_tc.cu)
+    const int tc_mode = fir_tc_mode(ct, D, ntaps, in, nout, tc_pref); // tcgen05 block-Toeplitz paths (fir_tc.cu)
     if (tc_mode >= 0)
         return fir_tc_launch(tc_mode, ntaps, rev, in, out, nout, nin, nsm, st);
     if (pl.tiled) {

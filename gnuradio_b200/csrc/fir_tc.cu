@@ -560,7 +560,15 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
 
 // Which tensor-core mode serves this call, or -1 (CUDA-core kernels).  `in` must be 16-byte aligned (TMA bulk copies).
 //   M_CCF / M_CCC: decimation 1, ntaps <= 64.   M_DEC8: real taps, decimation 8, ntaps <= 1024.
-int fir_tc_mode(bool ct, int D, int ntaps, const void* in, long long nout)
+// GRB200_FIR_TC (developer knob: 0 = CUDA-core kernels only, 1 = tensor-core path whenever the geometry allows), read when a
+// handle is created -- never per work()
+int fir_tc_env()
+{
+    const char* e = getenv("GRB200_FIR_TC");
+    return e ? (atoi(e) != 0 ? 1 : 0) : -1;
+}
+
+int fir_tc_mode(bool ct, int D, int ntaps, const void* in, long long nout, int tc_pref)
 {
     int mode = -1;
     if (D == 1 && ntaps <= 64)
@@ -569,12 +577,8 @@ int fir_tc_mode(bool ct, int D, int ntaps, const void* in, long long nout)
         mode = tc::M_DEC8;
     if (mode < 0 || ((uintptr_t)in & 15) != 0)
         return -1;
-    static const int forced = [] { // read once, not per work()
-        const char* e = getenv("GRB200_FIR_TC");
-        return e ? (atoi(e) != 0 ? 1 : 0) : -1;
-    }();
-    if (forced >= 0)
-        return forced ? mode : -1;
+    if (tc_pref >= 0)
+        return tc_pref ? mode : -1;
     if (mode == tc::M_CCC && ntaps < 20) // measured: the CUDA-core ccc kernel is as fast below ~20 taps (137 vs 154 Gsps at 21)
         return -1;
     if (mode == tc::M_DEC8 && ntaps < 256) // short decimators are already HBM-bound on the CUDA cores
