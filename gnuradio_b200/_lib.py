@@ -8,7 +8,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libgrb200.so")
 
-OK, EINVAL, ERANGE, ECUDA, ENOMEM, EWINDOW = 0, -1, -2, -3, -4, -5
+OK, EINVAL, ERANGE, ECUDA, ENOMEM, EWINDOW, ERUNTIME = 0, -1, -2, -3, -4, -5, -6
 
 _lib = None
 
@@ -30,12 +30,31 @@ SIGNATURES = {
     "grb200_dev_sync": (i32, [i32]),
     "grb200_fir_ccf_create": (i32, [i32, vp, i32, i32, pvp]),
     "grb200_fir_ccc_create": (i32, [i32, vp, i32, i32, pvp]),
+    "grb200_fir_fff_create": (i32, [i32, vp, i32, i32, pvp]),
     "grb200_fir_set_taps": (i32, [vp, vp, i32]),
     "grb200_fir_ntaps": (i32, [vp]),
     "grb200_fir_decimation": (i32, [vp]),
     "grb200_fir_work": (i32, [vp, vp, vp, i64]),
     "grb200_fir_work_dev": (i32, [vp, vp, vp, i64, vp]),
     "grb200_fir_destroy": (None, [vp]),
+    "grb200_pfb_synth_ccf_create": (i32, [C.c_uint, vp, i32, i32, i32, pvp]),
+    "grb200_pfb_synth_set_taps": (i32, [vp, vp, i32]),
+    "grb200_pfb_synth_set_channel_map": (i32, [vp, vp, i32]),
+    "grb200_pfb_synth_get_channel_map": (i32, [vp, vp, i32]),
+    "grb200_pfb_synth_taps_per_filter": (i32, [vp]),
+    "grb200_pfb_synth_numchans": (i32, [vp]),
+    "grb200_pfb_synth_twox": (i32, [vp]),
+    "grb200_pfb_synth_branch_taps": (i32, [vp, vp]),
+    "grb200_pfb_synth_work": (i32, [vp, pvp, i32, vp, i64]),
+    "grb200_pfb_synth_work_dev": (i32, [vp, vp, i64, i32, vp, i64, i32, vp]),
+    "grb200_pfb_synth_destroy": (None, [vp]),
+    "grb200_filterbank_vcvcf_create": (i32, [i32, i32, vp, i32, pvp]),
+    "grb200_filterbank_vcvcf_set_taps": (i32, [vp, i32, i32, vp]),
+    "grb200_filterbank_vcvcf_nfilts": (i32, [vp]),
+    "grb200_filterbank_vcvcf_ntaps": (i32, [vp]),
+    "grb200_filterbank_vcvcf_work": (i32, [vp, vp, vp, i64]),
+    "grb200_filterbank_vcvcf_work_dev": (i32, [vp, vp, vp, i64, vp]),
+    "grb200_filterbank_vcvcf_destroy": (None, [vp]),
     "grb200_interp_fir_ccf_create": (i32, [C.c_uint, vp, i32, i32, pvp]),
     "grb200_interp_fir_ccc_create": (i32, [C.c_uint, vp, i32, i32, pvp]),
     "grb200_interp_fir_set_taps": (i32, [vp, vp, i32]),
@@ -103,6 +122,25 @@ SIGNATURES = {
     "grb200_fft_vcc_work_magsq": (i32, [vp, vp, vp, i64]),
     "grb200_fft_vcc_work_magsq_dev": (i32, [vp, vp, vp, i64, vp]),
     "grb200_fft_vcc_destroy": (None, [vp]),
+    "grb200_fft_vfc_create": (i32, [i32, i32, vp, i32, i32, pvp]),
+    "grb200_logpwrfft_create": (i32, [i32, f64, i32, f64, f64, f64, i32, vp, i32, i32, pvp]),
+    "grb200_logpwrfft_set_decimation": (i32, [vp, f64]),
+    "grb200_logpwrfft_set_vec_rate": (i32, [vp, f64]),
+    "grb200_logpwrfft_set_sample_rate": (i32, [vp, f64]),
+    "grb200_logpwrfft_set_average": (i32, [vp, i32]),
+    "grb200_logpwrfft_set_avg_alpha": (i32, [vp, f64]),
+    "grb200_logpwrfft_decimation": (i32, [vp]),
+    "grb200_logpwrfft_sample_rate": (f64, [vp]),
+    "grb200_logpwrfft_frame_rate": (f64, [vp]),
+    "grb200_logpwrfft_average": (i32, [vp]),
+    "grb200_logpwrfft_avg_alpha": (f64, [vp]),
+    "grb200_logpwrfft_fft_size": (i32, [vp]),
+    "grb200_logpwrfft_work": (i32, [vp, vp, i64, vp, i64, C.POINTER(i64), C.POINTER(i64)]),
+    "grb200_logpwrfft_work_dev": (i32, [vp, vp, i64, vp, i64, C.POINTER(i64), C.POINTER(i64), vp]),
+    "grb200_logpwrfft_destroy": (None, [vp]),
+    "grb200_vector_to_streams_work": (i32, [i32, i32, i32, vp, pvp, i64]),
+    "grb200_vector_to_streams_work_dev": (i32, [i32, i32, i32, vp, vp, i64, i64, vp]),
+    "grb200_streams_to_vector_work_dev": (i32, [i32, i32, i32, vp, i64, vp, i64, vp]),
     "grb200_magsq_work": (i32, [i32, vp, vp, i64]),
     "grb200_magsq_work_dev": (i32, [i32, vp, vp, i64, vp]),
 }

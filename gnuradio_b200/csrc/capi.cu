@@ -99,12 +99,24 @@ struct grb200_fir {
     bool rot = false;
     double theta = 0.0, delta = 0.0;
     int tc_pref = -1; // GRB200_FIR_TC as it stood when the handle was made
+    bool real = false; // fir_filter_fff: float stream, float taps (fir_fff.cu)
+    int isz() const { return real ? 4 : 8; }
     Stager sg;
     std::mutex mu;
 };
 
 static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
 {
+    if (h->real) { // reversed taps zero padded to what fir_fff_kernel unrolls by
+        std::vector<float> rev((size_t)fir_fff_pad(ntaps), 0.f);
+        for (int t = 0; t < ntaps; t++)
+            rev[t] = taps[ntaps - 1 - t];
+        int rc = h->rev.upload(rev.data(), rev.size() * sizeof(float));
+        if (rc)
+            return rc;
+        h->ntaps = ntaps;
+        return 0;
+    }
     // reversed copy (fir_filter.cc:62-64) and its phase-major re-layout g_p[u] = rev[D*u + p]
     const int D = h->decim, es = h->ct ? 2 : 1;
     const int Upad = fir_upad(D, ntaps);
@@ -127,7 +139,7 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
     return 0;
 }
 
-static int fir_create(bool ct, int decim, const float* taps, int ntaps, int device, grb200_fir** out)
+static int fir_create(bool ct, int decim, const float* taps, int ntaps, int device, grb200_fir** out, bool real = false)
 {
     if (!out)
         return fail(GRB200_EINVAL, "fir: null output handle");
@@ -141,6 +153,7 @@ static int fir_create(bool ct, int decim, const float* taps, int ntaps, int devi
     h->ct = ct;
     h->decim = decim;
     h->tc_pref = fir_tc_env();
+    h->real = real;
     int rc = h->sg.init(device);
     if (rc)
         return rc;
@@ -160,6 +173,10 @@ int grb200_fir_ccf_create(int decim, const float* taps, int ntaps, int device, g
 int grb200_fir_ccc_create(int decim, const float* taps, int ntaps, int device, grb200_fir** out)
 {
     return fir_create(true, decim, taps, ntaps, device, out);
+}
+int grb200_fir_fff_create(int decim, const float* taps, int ntaps, int device, grb200_fir** out)
+{
+    return fir_create(false, decim, taps, ntaps, device, out, true);
 }
 
 int grb200_fir_set_taps(grb200_fir* h, const float* taps, int ntaps)
@@ -189,7 +206,8 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
     if (rc)
         return rc;
     cudaStream_t st = pick_stream(stream, h->sg);
-    rc = fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput, h->tc_pref, st);
+    rc = h->real ? fir_fff_launch(h->decim, h->ntaps, (const float*)h->rev.p, in_dev, out_dev, noutput, sm_count(h->device), st)
+                 : fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput, h->tc_pref, st);
     if (!rc && h->rot) {
         rc = rotate_launch(out_dev, noutput, h->theta, h->delta, st);
         h->theta = rotate_advance(h->theta, h->delta, noutput);
@@ -209,13 +227,14 @@ int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long lon
     if (rc)
         return rc;
     const int D = h->decim, nt = h->ntaps;
-    long long chunk = (long long)(kChunkBytes / 8) / D; // outputs per chunk
+    const size_t isz = (size_t)h->isz();
+    long long chunk = (long long)(kChunkBytes / isz) / D; // outputs per chunk
     if (chunk < 1)
         chunk = 1;
     if (chunk > noutput)
         chunk = noutput;
     const long long nchunks = (noutput + chunk - 1) / chunk;
-    if ((rc = h->sg.reserve_dev(0, (size_t)(chunk * D + nt - 1) * 8)) || (rc = h->sg.reserve_dev(1, (size_t)chunk * 8)))
+    if ((rc = h->sg.reserve_dev(0, (size_t)(chunk * D + nt - 1) * isz)) || (rc = h->sg.reserve_dev(1, (size_t)chunk * isz)))
         return rc;
     const char* in = (const char*)in_host;
     char* out = (char*)out_host;
@@ -224,13 +243,15 @@ int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long lon
         nchunks,
         [&](long long c, int slot, Stager::Chunk& ch) {
             const long long o0 = c * chunk, n = std::min(chunk, noutput - o0);
-            ch.h2d.push_back({ in + (size_t)o0 * D * 8, sg.dev[slot][0], (size_t)(n * D + nt - 1) * 8 });
-            ch.d2h.push_back({ sg.dev[slot][1], out + (size_t)o0 * 8, (size_t)n * 8 });
+            ch.h2d.push_back({ in + (size_t)o0 * D * isz, sg.dev[slot][0], (size_t)(n * D + nt - 1) * isz });
+            ch.d2h.push_back({ sg.dev[slot][1], out + (size_t)o0 * isz, (size_t)n * isz });
             return 0;
         },
         [&](long long c, int slot, cudaStream_t st) {
             const long long o0 = c * chunk, n = std::min(chunk, noutput - o0);
-            int r2 = fir_launch(h->ct, D, nt, h->gtaps.p, h->rev.p, sg.dev[slot][0], sg.dev[slot][1], n, h->tc_pref, st);
+            int r2 = h->real ? fir_fff_launch(D, nt, (const float*)h->rev.p, sg.dev[slot][0], sg.dev[slot][1], n,
+                                              sm_count(h->device), st)
+                             : fir_launch(h->ct, D, nt, h->gtaps.p, h->rev.p, sg.dev[slot][0], sg.dev[slot][1], n, h->tc_pref, st);
             if (!r2 && h->rot)
                 r2 = rotate_launch(sg.dev[slot][1], n, rotate_advance(h->theta, h->delta, o0), h->delta, st);
             return r2;

@@ -12,6 +12,9 @@ namespace grb {
 int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, const void* in, void* out,
                long long nout, int tc_pref, cudaStream_t st);
 int fir_tc_env();
+// fir_filter_fff (fir_fff.cu): revp = reversed taps zero padded to fir_fff_pad(ntaps) floats
+int fir_fff_pad(int ntaps);
+int fir_fff_launch(int D, int ntaps, const float* revp, const void* in, void* out, long long nout, int nsm, cudaStream_t st);
 int fir_upad(int D, int ntaps);
 // rotator behind freq_xlating_fir_filter: y[n] *= e^{j (theta + n delta)} in place (fir.cu); angle bookkeeping on the host
 int rotate_launch(void* y, long long n, double theta, double delta, cudaStream_t st);
@@ -21,6 +24,23 @@ int fft_direct_max();
 int fft_vcc_launch(int N, bool fwd, const void* in, void* out, long long nvec, const float* window, int shift,
                    int magsq, const float2* tw, int nsm, cudaStream_t st);
 int magsq_launch(const void* in, float* out, long long n, int nsm, cudaStream_t st);
+// generalised vector FFT launch (fftvcc.cu): real input (fft_vfc), strided input vectors and the log epilogue (logpwrfft)
+struct VccArgs {
+    const void* in;
+    void* out;
+    long long nvec;
+    const float* window;
+    const float2* tw;
+    int shift, mode; // mode 0 complex out, 1 |X|^2, 2 log_mul * log2(max(|X|^2, FLT_MIN) * log_scale)
+    long long vstride, voff;
+    float log_mul, log_scale;
+    float* ystate;
+};
+int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st);
+// logpwr.cu: single_pole_iir along the frames + nlog10, in place on p [nframes][N]
+long long logpwr_scratch_floats(long long nframes, int N, int nsm);
+int logpwr_iir_log_launch(float* p, long long nframes, int N, double alpha, float* ystate, float* scratch, float log_mul,
+                          float log_scale, int nsm, cudaStream_t st);
 int fftfilt_device_plan(int ntaps, int* parts);
 int fftfilt_launch(int L, int parts, const void* in, void* out, long long nout, int ntaps, int D, const float2* H,
                    const float2* tw, int nsm, cudaStream_t st);
@@ -30,6 +50,16 @@ int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stri
 bool pfb_stream_supported(int M, int T, int R, const void* x);
 int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
                       const float* h, const float2* wM, int nsm, cudaStream_t st);
+// pfb_synthesizer_ccf (pfb_synth.cu)
+bool pfb_synth_fast_supported(int M, int T, int twox, const void* x, long long stride, int nin);
+int pfb_synth_fast_launch(int M, int T, const void* x, long long stride, int nin, void* out, long long ntimes, const float* h,
+                          const float2* wM, const int* inv, int nsm, cudaStream_t st);
+long long pfb_synth_slab(int NF, int T);
+int pfb_synth_general_launch(int M, int twox, int T, const void* x, long long stride, void* out, long long ntimes,
+                             const float* h, const float2* twNF, const int* inv, int par0, void* scratch, long long slab_rows,
+                             int nsm, cudaStream_t st);
+int filterbank_launch(const void* x, void* out, long long nout, int nf, int T, const float* hrev, const unsigned char* active,
+                      int nsm, cudaStream_t st);
 int streams_to_interleaved_launch(const void* in, long long in_stride, void* out, int M, long long nrows,
                                   cudaStream_t st);
 
@@ -46,6 +76,20 @@ inline size_t chunk_bytes()
     return v;
 }
 #define kChunkBytes (grb::chunk_bytes())
+
+// Chunk size for a host-staged call that moves `total` input bytes.  Big calls use the configured chunk.  A call that
+// would fit in ONE chunk but is larger than 1 MiB is still cut in four, so that its H2D copy, kernel and D2H copy overlap
+// (three streams, three slots) instead of running back to back -- scheduler-sized work() calls (32 KiB .. 32 MiB) are the
+// normal case inside a flowgraph.  Below 1 MiB the per-chunk launch and copy set-up costs more than the overlap gains.
+inline size_t chunk_bytes_for(size_t total)
+{
+    const size_t cb = chunk_bytes();
+    if (total <= ((size_t)1 << 20) || total >= 4 * cb)
+        return cb;
+    size_t c = (total + 3) / 4;
+    c = (c + 4095) & ~(size_t)4095;
+    return c < cb ? c : cb;
+}
 
 struct DevBuf {
     void* p = nullptr;

@@ -12,8 +12,31 @@
 #include <cstdlib>
 #include "fft.cuh"
 #include "tma.cuh"
+#include "capi_common.cuh"
 
 namespace grb {
+
+// What one launch does besides the transform.  in: vectors of N complex64, or N float32 when REAL (fft_vfc_fftw.cc:70-80);
+// output vector j transforms input vector j*vstride + voff (keep_one_in_n in front of the FFT, logpwrfft.py:49-52);
+// mode 0: complex out; 1: |X|^2 (complex_to_mag_squared fused); 2: log_mul * log2(max(|X|^2, FLT_MIN) * log_scale) -- the
+// nlog10_ff at the end of logpwrfft without averaging (nlog10_ff_impl.cc:47-58) -- and the last vector's |X|^2 goes to ystate
+// (the single_pole_iir memory a later set_average(true) continues from).
+
+__device__ __forceinline__ void vcc_store(const VccArgs& a, long long vec, int N, int k, float2 X)
+{
+    if (a.mode == 0) {
+        reinterpret_cast<float2*>(a.out)[vec * N + k] = X;
+    } else {
+        const float p = fmaf(X.x, X.x, X.y * X.y);
+        if (a.mode == 1) {
+            reinterpret_cast<float*>(a.out)[vec * N + k] = p;
+        } else {
+            reinterpret_cast<float*>(a.out)[vec * N + k] = log2f(fmaxf(p, 1.17549435e-38f) * a.log_scale) * a.log_mul;
+            if (vec == a.nvec - 1)
+                a.ystate[k] = p;
+        }
+    }
+}
 
 template <int N>
 struct VccGeom {
@@ -24,12 +47,15 @@ struct VccGeom {
     static constexpr int SMEM = VPC * fft_smem_elems(N) * 8;
 };
 
-template <int N, bool FWD>
+template <int N, bool FWD, bool REAL>
 __global__ void __launch_bounds__(VccGeom<N>::NT)
-fft_vcc_kernel(const float2* __restrict__ in, void* __restrict__ out, long long nvec,
-               const float* __restrict__ window, int shift, int magsq, const float2* __restrict__ tw)
+fft_vcc_kernel(const VccArgs a)
 {
     using G = VccGeom<N>;
+    const long long nvec = a.nvec;
+    const float* __restrict__ window = a.window;
+    const float2* __restrict__ tw = a.tw;
+    const int shift = a.shift;
     constexpr int E = G::E, TPV = G::TPV, VPC = G::VPC;
     constexpr int R0 = fft_first_radix(N, false);
     constexpr int RL = fft_last_radix(N, false);
@@ -44,7 +70,7 @@ fft_vcc_kernel(const float2* __restrict__ in, void* __restrict__ out, long long 
         const long long vec = vbase + vl;
         const bool valid = vec < nvec;
         float2 v[E];
-        const float2* src = in + vec * N;
+        const long long sv = (vec * a.vstride + a.voff) * N;
 #pragma unroll
         for (int b = 0; b < E / R0; b++) {
 #pragma unroll
@@ -54,7 +80,8 @@ fft_vcc_kernel(const float2* __restrict__ in, void* __restrict__ out, long long 
                     d = (d + N / 2) & (N - 1);
                 float2 x = make_float2(0.f, 0.f);
                 if (valid) {
-                    x = src[d];
+                    x = REAL ? make_float2(reinterpret_cast<const float*>(a.in)[sv + d], 0.f)
+                             : reinterpret_cast<const float2*>(a.in)[sv + d];
                     if (window != nullptr) {
                         const float w = __ldg(window + d);
                         x.x *= w;
@@ -73,11 +100,7 @@ fft_vcc_kernel(const float2* __restrict__ in, void* __restrict__ out, long long 
                     int k = (t + b * TPV) + q * (N / RL);
                     if (out_rot)
                         k = (k + N / 2) & (N - 1);
-                    const float2 X = v[b * RL + q];
-                    if (magsq)
-                        reinterpret_cast<float*>(out)[vec * N + k] = fmaf(X.x, X.x, X.y * X.y);
-                    else
-                        reinterpret_cast<float2*>(out)[vec * N + k] = X;
+                    vcc_store(a, vec, N, k, v[b * RL + q]);
                 }
             }
         }
@@ -103,13 +126,17 @@ struct VccStreamGeom {
     static constexpr int SMEM = XIN_BYTES + S_BYTES + TW_BYTES + WIN_BYTES + 16;
 };
 
-template <int N, bool FWD>
+template <int N, bool FWD, bool REAL>
 __global__ void __launch_bounds__(VccGeom<N>::NT)
-fft_vcc_stream_kernel(const float2* __restrict__ in, void* __restrict__ out, long long nvec,
-                      const float* __restrict__ window, int shift, int magsq, const float2* __restrict__ tw)
+fft_vcc_stream_kernel(const VccArgs a)
 {
     using G = VccGeom<N>;
     using SG = VccStreamGeom<N>;
+    constexpr int ISZ = REAL ? 4 : 8; // bytes per input item
+    const long long nvec = a.nvec;
+    const float* __restrict__ window = a.window;
+    const float2* __restrict__ tw = a.tw;
+    const int shift = a.shift;
     constexpr int E = G::E, TPV = G::TPV, VPC = G::VPC;
     constexpr int R0 = fft_first_radix(N, false);
     constexpr int RL = fft_last_radix(N, false);
@@ -124,6 +151,7 @@ fft_vcc_stream_kernel(const float2* __restrict__ in, void* __restrict__ out, lon
     const int t = threadIdx.x % TPV;
     float2* S = Sall + vl * fft_smem_elems(N);
     const float2* X = XIN + vl * N;
+    const float* XR = reinterpret_cast<const float*>(XIN) + vl * N;
     const bool in_swap = (!FWD) && shift;
     const bool out_rot = FWD && shift;
     const bool has_win = window != nullptr;
@@ -132,9 +160,14 @@ fft_vcc_stream_kernel(const float2* __restrict__ in, void* __restrict__ out, lon
     auto issue = [&](long long vbase) {
         long long nv = nvec - vbase;
         nv = nv > VPC ? VPC : nv;
-        const unsigned bytes = (unsigned)(nv * N * 8);
-        mbar_expect_tx(bar, bytes);
-        bulk_g2s(XIN, in + vbase * N, bytes, bar);
+        mbar_expect_tx(bar, (unsigned)(nv * N * ISZ));
+        if (a.vstride == 1) { // the CTA's vectors are contiguous in the stream: one copy
+            bulk_g2s(XIN, reinterpret_cast<const char*>(a.in) + (vbase + a.voff) * N * ISZ, (unsigned)(nv * N * ISZ), bar);
+        } else {
+            for (int s = 0; s < (int)nv; s++)
+                bulk_g2s(reinterpret_cast<char*>(XIN) + (size_t)s * N * ISZ,
+                         reinterpret_cast<const char*>(a.in) + ((vbase + s) * a.vstride + a.voff) * N * ISZ, N * ISZ, bar);
+        }
     };
 
     if (threadIdx.x == 0)
@@ -162,7 +195,9 @@ fft_vcc_stream_kernel(const float2* __restrict__ in, void* __restrict__ out, lon
                 int d = (t + b * TPV) + q * (N / R0);
                 if (in_swap)
                     d = (d + N / 2) & (N - 1);
-                float2 x = valid ? X[d] : make_float2(0.f, 0.f);
+                float2 x = make_float2(0.f, 0.f);
+                if (valid)
+                    x = REAL ? make_float2(XR[d], 0.f) : X[d];
                 if (has_win) {
                     const float w = WIN[d];
                     x = __fmul2_rn(x, make_float2(w, w));
@@ -183,11 +218,7 @@ fft_vcc_stream_kernel(const float2* __restrict__ in, void* __restrict__ out, lon
                     int k = (t + b * TPV) + q * (N / RL);
                     if (out_rot)
                         k = (k + N / 2) & (N - 1);
-                    const float2 Xk = v[b * RL + q];
-                    if (magsq)
-                        reinterpret_cast<float*>(out)[vec * N + k] = fmaf(Xk.x, Xk.x, Xk.y * Xk.y);
-                    else
-                        reinterpret_cast<float2*>(out)[vec * N + k] = Xk;
+                    vcc_store(a, vec, N, k, v[b * RL + q]);
                 }
             }
         }
@@ -198,9 +229,12 @@ fft_vcc_stream_kernel(const float2* __restrict__ in, void* __restrict__ out, lon
 // Any other size: direct DFT from shared memory, one CTA per vector (O(N^2), correctness path for the
 // sizes FFTW would also accept; the hot configurations are powers of two).
 __global__ void __launch_bounds__(256)
-dft_direct_kernel(const float2* __restrict__ in, void* __restrict__ out, long long nvec, int N, int forward,
-                  const float* __restrict__ window, int shift, int magsq, const float2* __restrict__ tw)
+dft_direct_kernel(const VccArgs a, int N, int forward, int real_in)
 {
+    const long long nvec = a.nvec;
+    const float* __restrict__ window = a.window;
+    const float2* __restrict__ tw = a.tw;
+    const int shift = a.shift;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2* x = reinterpret_cast<float2*>(smem_raw);
     float2* w = x + N;
@@ -216,7 +250,9 @@ dft_direct_kernel(const float2* __restrict__ in, void* __restrict__ out, long lo
         __syncthreads();
         for (int d = threadIdx.x; d < N; d += blockDim.x) {
             int s = in_swap ? (d + len_in) % N : d;
-            float2 c = in[vec * N + s];
+            const long long sv = (vec * a.vstride + a.voff) * N;
+            float2 c = real_in ? make_float2(reinterpret_cast<const float*>(a.in)[sv + s], 0.f)
+                               : reinterpret_cast<const float2*>(a.in)[sv + s];
             if (window != nullptr) {
                 const float ww = window[s];
                 c.x *= ww;
@@ -239,10 +275,7 @@ dft_direct_kernel(const float2* __restrict__ in, void* __restrict__ out, long lo
                     idx -= N;
             }
             const int o = out_rot ? (k + N - len_out) % N : k;
-            if (magsq)
-                reinterpret_cast<float*>(out)[vec * N + o] = fmaf(acc.x, acc.x, acc.y * acc.y);
-            else
-                reinterpret_cast<float2*>(out)[vec * N + o] = acc;
+            vcc_store(a, vec, N, o, acc);
         }
     }
 }
@@ -259,77 +292,72 @@ magsq_kernel(const float2* __restrict__ in, float* __restrict__ out, long long n
 }
 
 // ---- host dispatch --------------------------------------------------------------------------------
-template <int N, bool FWD>
-static int launch_vcc(const void* in, void* out, long long nvec, const float* window, int shift, int magsq,
-                      const float2* tw, int nsm, cudaStream_t st)
+template <int N, bool FWD, bool REAL>
+static int launch_vcc(const VccArgs& a, int nsm, cudaStream_t st)
 {
     using G = VccGeom<N>;
-    auto kern = fft_vcc_kernel<N, FWD>;
+    auto kern = fft_vcc_kernel<N, FWD, REAL>;
     if (G::SMEM > 48 * 1024)
         GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
     int occ = 1;
     GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, G::NT, G::SMEM));
     if (occ < 1)
         occ = 1;
-    long long need = (nvec + G::VPC - 1) / G::VPC;
+    long long need = (a.nvec + G::VPC - 1) / G::VPC;
     long long grid = (long long)nsm * occ;
     if (grid > need)
         grid = need;
-    kern<<<(unsigned)grid, G::NT, G::SMEM, st>>>((const float2*)in, out, nvec, window, shift, magsq, tw);
+    kern<<<(unsigned)grid, G::NT, G::SMEM, st>>>(a);
     GRB_LAUNCH_CHECK();
     return 0;
 }
 
-template <int N, bool FWD>
-static int launch_vcc_stream(const void* in, void* out, long long nvec, const float* window, int shift, int magsq,
-                             const float2* tw, int nsm, cudaStream_t st)
+template <int N, bool FWD, bool REAL>
+static int launch_vcc_stream(const VccArgs& a, int nsm, cudaStream_t st)
 {
     using G = VccGeom<N>;
     using SG = VccStreamGeom<N>;
-    auto kern = fft_vcc_stream_kernel<N, FWD>;
+    auto kern = fft_vcc_stream_kernel<N, FWD, REAL>;
     GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::SMEM));
     int occ = 1;
     GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, G::NT, SG::SMEM));
     if (occ < 1)
         occ = 1;
-    long long need = (nvec + G::VPC - 1) / G::VPC;
+    long long need = (a.nvec + G::VPC - 1) / G::VPC;
     long long grid = (long long)nsm * occ;
     if (grid > need)
         grid = need;
-    kern<<<(unsigned)grid, G::NT, SG::SMEM, st>>>((const float2*)in, out, nvec, window, shift, magsq, tw);
+    kern<<<(unsigned)grid, G::NT, SG::SMEM, st>>>(a);
     GRB_LAUNCH_CHECK();
     return 0;
 }
 
-template <int N>
-static int launch_vcc_dir(bool fwd, const void* in, void* out, long long nvec, const float* window, int shift,
-                          int magsq, const float2* tw, int nsm, cudaStream_t st)
+template <int N, bool REAL>
+static int launch_vcc_dir(bool fwd, const VccArgs& a, int nsm, cudaStream_t st)
 {
     if constexpr (N >= 1024 && N <= 8192) {
         static const bool use_stream = [] {
             const char* e = getenv("GRB200_FFT_STREAM");
             return !(e && e[0] == '0');
         }();
-        // TMA source must be 16-byte aligned; a few vectors are not worth a persistent pipeline
-        if (use_stream && (((uintptr_t)in) & 15) == 0 && nvec >= 64)
-            return fwd ? launch_vcc_stream<N, true>(in, out, nvec, window, shift, magsq, tw, nsm, st)
-                       : launch_vcc_stream<N, false>(in, out, nvec, window, shift, magsq, tw, nsm, st);
+        // TMA sources must be 16-byte aligned (every vector start is, once the base is); a few vectors are not worth a
+        // persistent pipeline
+        if (use_stream && (((uintptr_t)a.in) & 15) == 0 && a.nvec >= 64)
+            return fwd ? launch_vcc_stream<N, true, REAL>(a, nsm, st) : launch_vcc_stream<N, false, REAL>(a, nsm, st);
     }
-    return fwd ? launch_vcc<N, true>(in, out, nvec, window, shift, magsq, tw, nsm, st)
-               : launch_vcc<N, false>(in, out, nvec, window, shift, magsq, tw, nsm, st);
+    return fwd ? launch_vcc<N, true, REAL>(a, nsm, st) : launch_vcc<N, false, REAL>(a, nsm, st);
 }
 
 bool fft_size_is_fast(int N) { return N >= 2 && N <= 16384 && (N & (N - 1)) == 0; }
 int fft_direct_max() { return 8192; }
 
-int fft_vcc_launch(int N, bool fwd, const void* in, void* out, long long nvec, const float* window, int shift,
-                   int magsq, const float2* tw, int nsm, cudaStream_t st)
+int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st)
 {
-    if (nvec <= 0)
+    if (a.nvec <= 0)
         return 0;
-#define GRB_VCC_CASE(n) \
-    case n:             \
-        return launch_vcc_dir<n>(fwd, in, out, nvec, window, shift, magsq, tw, nsm, st);
+#define GRB_VCC_CASE(n)                                                                   \
+    case n:                                                                               \
+        return real_in ? launch_vcc_dir<n, true>(fwd, a, nsm, st) : launch_vcc_dir<n, false>(fwd, a, nsm, st);
     if (fft_size_is_fast(N)) {
         switch (N) {
             GRB_VCC_CASE(2)
@@ -355,11 +383,17 @@ int fft_vcc_launch(int N, bool fwd, const void* in, void* out, long long nvec, c
     const size_t smem = (size_t)N * 16;
     if (smem > 48 * 1024)
         GRB_CUDA(cudaFuncSetAttribute(dft_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    long long grid = nvec < (long long)nsm * 4 ? nvec : (long long)nsm * 4;
-    dft_direct_kernel<<<(unsigned)grid, 256, smem, st>>>((const float2*)in, out, nvec, N, fwd ? 1 : 0, window, shift,
-                                                          magsq, tw);
+    long long grid = a.nvec < (long long)nsm * 4 ? a.nvec : (long long)nsm * 4;
+    dft_direct_kernel<<<(unsigned)grid, 256, smem, st>>>(a, N, fwd ? 1 : 0, real_in ? 1 : 0);
     GRB_LAUNCH_CHECK();
     return 0;
+}
+
+int fft_vcc_launch(int N, bool fwd, const void* in, void* out, long long nvec, const float* window, int shift,
+                   int magsq, const float2* tw, int nsm, cudaStream_t st)
+{
+    VccArgs a{ in, out, nvec, window, tw, shift, magsq ? 1 : 0, 1, 0, 0.f, 0.f, nullptr };
+    return fft_vcc_launch_ex(N, fwd, false, a, nsm, st);
 }
 
 int magsq_launch(const void* in, float* out, long long n, int nsm, cudaStream_t st)

@@ -1,0 +1,159 @@
+// logpwr.cu -- the averaging tail of logpwrfft: single_pole_iir_filter_ff(alpha, vlen) -> nlog10_ff(10, vlen, k).
+//
+// Replaces single_pole_iir_filter_ff_impl::work (reference gr-filter/lib/single_pole_iir_filter_ff_impl.cc:47-67 over
+// gr-filter/include/gnuradio/filter/single_pole_iir.h:78-86:  y = alpha*x + (1-alpha)*y_prev, double arithmetic, float state)
+// and nlog10_ff_impl::work (gr-blocks/lib/nlog10_ff_impl.cc:38-60:  out = n/log2(10) * log2(max(y, FLT_MIN) * 10^(k/n)))
+// behind the fused window -> FFT -> |.|^2 kernel (fftvcc.cu, mode 1), in place on the [frames][N] float array.
+//
+// The recurrence runs along the frame axis, one independent filter per bin.  The frames are cut into runs; three small
+// kernels make it parallel in both axes (a linear recurrence: y_j = z_j + beta^(j-j0+1) * carry, z = the run filtered from a
+// zero state):
+//   logpwr_local_kernel  thread (run, bin): filters its run from zero in place, leaves the run's last value in agg[run][bin]
+//   logpwr_carry_kernel  thread (bin): carry[r+1] = agg[r] + beta^len_r * carry[r], carry[0] = the block's filter memory;
+//                        stores the new filter memory
+//   logpwr_fixup_kernel  thread (run, bin): adds beta^(j-j0+1) * carry[run], takes the logarithm
+// A short call (one run) is a single kernel that starts from the filter memory and writes the logarithm directly.
+// Without averaging (alpha = 1) none of this runs: the FFT kernel's mode 2 writes the logarithm itself.
+// Extra HBM traffic: 16 B per output bin on top of the FFT kernel's 4 B write -- per KEPT frame; logpwrfft normally keeps one
+// frame in tens (frame_rate << sample_rate / fft_size), so the block's traffic is the frames it reads.
+#include "common.cuh"
+
+namespace grb {
+
+__device__ __forceinline__ float logpwr_log(float y, float log_mul, float log_scale)
+{
+    return log2f(fmaxf(y, 1.17549435e-38f) * log_scale) * log_mul;
+}
+
+// p: [nframes][N] in place.  Thread (run, bin) -- bins across lanes, so every access is a coalesced row segment.
+// direct != 0: a single run that starts from ystate, writes the logarithm and the new ystate.
+__global__ void __launch_bounds__(256)
+logpwr_local_kernel(float* __restrict__ p, long long nframes, int N, int run_len, double alpha, double beta,
+                    float* __restrict__ agg, float* __restrict__ ystate, int direct, float log_mul, float log_scale)
+{
+    const int bin = blockIdx.x * blockDim.x + threadIdx.x;
+    const long long run = blockIdx.y;
+    if (bin >= N)
+        return;
+    const long long j0 = run * run_len;
+    long long j1 = j0 + run_len;
+    j1 = j1 > nframes ? nframes : j1;
+    float y = direct ? ystate[bin] : 0.f;
+    for (long long j = j0; j < j1; j += 8) { // eight independent loads in flight per thread, then the dependent chain
+        float x[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+            x[u] = j + u < j1 ? p[(j + u) * N + bin] : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            if (j + u < j1) {
+                y = (float)(alpha * (double)x[u] + beta * (double)y); // single_pole_iir.h:82: double arithmetic, float state
+                p[(j + u) * N + bin] = direct ? logpwr_log(y, log_mul, log_scale) : y;
+            }
+        }
+    }
+    if (direct)
+        ystate[bin] = y;
+    else
+        agg[run * N + bin] = y;
+}
+
+// carry[r][bin] = filter memory at the start of run r.  agg is overwritten by carry in place (carry[r] replaces agg[r]).
+__global__ void __launch_bounds__(256)
+logpwr_carry_kernel(float* __restrict__ agg, long long nruns, long long nframes, int N, int run_len, double beta,
+                    float* __restrict__ ystate)
+{
+    const int bin = blockIdx.x * blockDim.x + threadIdx.x;
+    if (bin >= N)
+        return;
+    const double bfull = pow(beta, (double)run_len);
+    double c = (double)ystate[bin];
+    for (long long r = 0; r < nruns; r++) {
+        const float a = agg[r * N + bin];
+        agg[r * N + bin] = (float)c;
+        const long long len = (r + 1) * run_len <= nframes ? run_len : nframes - r * run_len;
+        const double b = len == run_len ? bfull : pow(beta, (double)len);
+        c = (double)a + b * c;
+    }
+    ystate[bin] = (float)c;
+}
+
+__global__ void __launch_bounds__(256)
+logpwr_fixup_kernel(float* __restrict__ p, long long nframes, int N, int run_len, double beta,
+                    const float* __restrict__ carry, float log_mul, float log_scale)
+{
+    const int bin = blockIdx.x * blockDim.x + threadIdx.x;
+    const long long run = blockIdx.y;
+    if (bin >= N)
+        return;
+    const long long j0 = run * run_len;
+    long long j1 = j0 + run_len;
+    j1 = j1 > nframes ? nframes : j1;
+    const double c = (double)carry[run * N + bin];
+    double m = beta;
+    for (long long j = j0; j < j1; j += 8) {
+        float z[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+            z[u] = j + u < j1 ? p[(j + u) * N + bin] : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            if (j + u < j1) {
+                p[(j + u) * N + bin] = logpwr_log(z[u] + (float)(m * c), log_mul, log_scale);
+                m *= beta;
+            }
+        }
+    }
+}
+
+// In place on p [nframes][N]: y = alpha*x + (1-alpha)*y_prev along the frames, then the logarithm.  ystate: [N] filter
+// memory, read and updated.  scratch: at least logpwr_scratch_floats(nframes, N) floats (run aggregates / carries).
+static long long logpwr_run_len(long long nframes, int N, int nsm)
+{
+    // enough (run, bin) threads to fill the machine, runs no shorter than 8 frames
+    const long long want_threads = (long long)nsm * 2048 * 2;
+    long long nruns = (want_threads + N - 1) / N;
+    if (nruns < 1)
+        nruns = 1;
+    if (nruns > 65535) // grid.y
+        nruns = 65535;
+    long long len = (nframes + nruns - 1) / nruns;
+    return len < 8 ? 8 : len;
+}
+
+long long logpwr_scratch_floats(long long nframes, int N, int nsm)
+{
+    if (nframes <= 16)
+        return 0;
+    const long long len = logpwr_run_len(nframes, N, nsm);
+    return ((nframes + len - 1) / len) * N;
+}
+
+int logpwr_iir_log_launch(float* p, long long nframes, int N, double alpha, float* ystate, float* scratch, float log_mul,
+                          float log_scale, int nsm, cudaStream_t st)
+{
+    if (nframes <= 0)
+        return 0;
+    const double beta = 1.0 - alpha;
+    const unsigned gx = (unsigned)((N + 255) / 256);
+    if (nframes <= 16 || !scratch) {
+        logpwr_local_kernel<<<dim3(gx, 1), 256, 0, st>>>(p, nframes, N, (int)nframes, alpha, beta, nullptr, ystate, 1, log_mul,
+                                                         log_scale);
+        GRB_LAUNCH_CHECK();
+        return 0;
+    }
+    const long long len = logpwr_run_len(nframes, N, nsm);
+    const long long nruns = (nframes + len - 1) / len;
+    if (nruns > 65535 || len > 0x7fffffffLL)
+        return fail(GRB200_ERANGE, "logpwrfft: too many frames in one call");
+    logpwr_local_kernel<<<dim3(gx, (unsigned)nruns), 256, 0, st>>>(p, nframes, N, (int)len, alpha, beta, scratch, ystate, 0,
+                                                                   log_mul, log_scale);
+    GRB_LAUNCH_CHECK();
+    logpwr_carry_kernel<<<gx, 256, 0, st>>>(scratch, nruns, nframes, N, (int)len, beta, ystate);
+    GRB_LAUNCH_CHECK();
+    logpwr_fixup_kernel<<<dim3(gx, (unsigned)nruns), 256, 0, st>>>(p, nframes, N, (int)len, beta, scratch, log_mul, log_scale);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+} // namespace grb

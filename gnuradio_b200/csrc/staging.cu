@@ -167,6 +167,31 @@ bool Stager::is_pinned(const void* p)
     return attr.type == cudaMemoryTypeHost;
 }
 
+static std::mutex g_shared_mu;
+static std::mutex g_shared_work_mu[64];
+static Stager* g_shared_sg[64];
+
+int shared_stager(int device, Stager** out)
+{
+    DeviceScope ds(device);
+    if (ds.rc)
+        return ds.rc;
+    std::lock_guard<std::mutex> lk(g_shared_mu);
+    if (!g_shared_sg[device]) {
+        Stager* s = new Stager;
+        int rc = s->init(device);
+        if (rc) {
+            delete s;
+            return rc;
+        }
+        g_shared_sg[device] = s;
+    }
+    *out = g_shared_sg[device];
+    return 0;
+}
+
+std::mutex& shared_stager_mutex(int device) { return g_shared_work_mu[device >= 0 && device < 64 ? device : 0]; }
+
 // Pieces that form an arithmetic progression on both sides (equal sizes, constant positive pitches) -- e.g. the M output
 // streams of the channelizer when the caller's buffers are rows of one array -- go out as ONE cudaMemcpy2DAsync: the copy
 // engine then streams the whole chunk instead of paying the per-copy setup cost M times (measured on B200: 64 x 1 MiB

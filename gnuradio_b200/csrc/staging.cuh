@@ -54,4 +54,9 @@ struct Stager {
     int run(long long nchunks, const PlanFn& plan, const LaunchFn& launch);
 };
 
+// One Stager per device for the handle-less entry points (complex_to_mag_squared, vector_to_streams): created on first use,
+// lives for the process.  Host-staged calls through it hold shared_stager_mutex(device) for their duration.
+int shared_stager(int device, Stager** out);
+std::mutex& shared_stager_mutex(int device);
+
 } // namespace grb

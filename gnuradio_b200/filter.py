@@ -1,6 +1,6 @@
 """gr-filter hot-path blocks re-hosted on libgrb200 (same names, arguments and error behaviour as the reference).
 
-  fir_filter_ccf / fir_filter_ccc   gr-filter/include/gnuradio/filter/fir_filter_blk.h:46-68,
+  fir_filter_ccf / ccc / fff        gr-filter/include/gnuradio/filter/fir_filter_blk.h:46-68,
                                     gr-filter/lib/fir_filter_blk_impl.cc:22-90
   freq_xlating_fir_filter_ccf/ccc   gr-filter/include/gnuradio/filter/freq_xlating_fir_filter.h:56-90,
                                     gr-filter/lib/freq_xlating_fir_filter_impl.cc:26-180
@@ -36,17 +36,20 @@ def _ptr(a):
 
 class _fir_filter_blk(sync_decimator):
     _complex_taps = False
+    _item = _c64  # stream item type (fir_filter_fff: float32)
     _name = "fir_filter"
 
     def __init__(self, decimation, taps, device=0):
         L = _lib.lib()
         if int(decimation) < 1:
             raise ValueError("fir_filter: decimation must be >= 1")
-        sync_decimator.__init__(self, self._name, io_signature.make(1, 1, 8), io_signature.make(1, 1, 8), decimation)
+        isz = self._item.itemsize
+        sync_decimator.__init__(self, self._name, io_signature.make(1, 1, isz), io_signature.make(1, 1, isz), decimation)
         self._device = int(device)
         self._h = C.c_void_p()
         t = self._conv_taps(taps)
-        create = L.grb200_fir_ccc_create if self._complex_taps else L.grb200_fir_ccf_create
+        create = (L.grb200_fir_fff_create if self._item is not _c64 else
+                  L.grb200_fir_ccc_create if self._complex_taps else L.grb200_fir_ccf_create)
         _lib.check(create(int(decimation), _ptr(t), len(t), self._device, C.byref(self._h)))
         self._taps = t.copy()
         self.d_updated = False
@@ -80,8 +83,8 @@ class _fir_filter_blk(sync_decimator):
                 return 0
             n = int(noutput_items)
             need = n * self.decimation() + len(self._taps) - 1
-            xin = as_items(input_items[0], _c64, need if n else 0, "input_items[0]")
-            out = as_items(output_items[0], _c64, n, "output_items[0]")
+            xin = as_items(input_items[0], self._item, need if n else 0, "input_items[0]")
+            out = as_items(output_items[0], self._item, n, "output_items[0]")
             _lib.check(_lib.lib().grb200_fir_work(self._h, _ptr(xin), _ptr(out), n))
             return n
 
@@ -93,8 +96,8 @@ class _fir_filter_blk(sync_decimator):
 
     def process(self, xin, noutput_items):
         """Convenience: one work() call on `xin` (history items first); returns the output array."""
-        xin = np.ascontiguousarray(xin, np.complex64)
-        out = np.empty(int(noutput_items), np.complex64)
+        xin = np.ascontiguousarray(xin, self._item)
+        out = np.empty(int(noutput_items), self._item)
         if self.d_updated:
             self.work(0, [xin], [out])
         r = self.work(noutput_items, [xin], [out])
@@ -117,6 +120,13 @@ class fir_filter_ccf(_fir_filter_blk):
 class fir_filter_ccc(_fir_filter_blk):
     _complex_taps = True
     _name = "fir_filter_ccc"
+
+
+class fir_filter_fff(_fir_filter_blk):
+    """fir_filter_blk<float,float,float> (gr-filter/include/gnuradio/filter/fir_filter_blk.h:66): float stream, float taps."""
+    _complex_taps = False
+    _item = np.dtype(np.float32)
+    _name = "fir_filter_fff"
 
 
 class _freq_xlating_fir_filter(sync_decimator):
@@ -772,6 +782,192 @@ class pfb_decimator_ccf(sync_block):
                 pass
 
 
+class pfb_synthesizer_ccf(sync_interpolator):
+    """pfb_synthesizer_ccf (gr-filter/include/gnuradio/filter/pfb_synthesizer_ccf.h, lib/pfb_synthesizer_ccf_impl.cc:23-284):
+    up to twox*numchans input streams -> one stream at numchans times the rate.  work() takes the NEW items only
+    (history 1); the filters' delay lines live in the library handle."""
+
+    def __init__(self, numchans, taps, twox=False, device=0):
+        L = _lib.lib()
+        numchans = int(numchans)
+        if numchans < 1:
+            raise ValueError("pfb_synthesizer_ccf: bad channel count")
+        sync_interpolator.__init__(self, "pfb_synthesizer_ccf", io_signature.make(1, numchans, 8), io_signature.make(1, 1, 8),
+                                   numchans)
+        self._h = C.c_void_p()
+        self._M = numchans
+        self.d_twox = 2 if twox else 1
+        t = pfb_channelizer_ccf._conv_taps(taps)
+        _lib.check(L.grb200_pfb_synth_ccf_create(numchans, _ptr(t), len(t), int(bool(twox)), int(device), C.byref(self._h)))
+        self.d_taps_per_filter = L.grb200_pfb_synth_taps_per_filter(self._h)
+        self.set_history(1)  # :92
+        self.set_output_multiple(numchans)  # :68
+        self.d_updated = True  # the constructor goes through set_taps (:63, :93)
+
+    @classmethod
+    def make(cls, numchans, taps, twox=False, device=0):
+        return cls(numchans, taps, twox, device)
+
+    def set_taps(self, taps):
+        t = pfb_channelizer_ccf._conv_taps(taps)
+        with self.d_setlock:  # :79-94
+            L = _lib.lib()
+            _lib.check(L.grb200_pfb_synth_set_taps(self._h, _ptr(t), len(t)))
+            self.d_taps_per_filter = L.grb200_pfb_synth_taps_per_filter(self._h)
+            self.set_history(1)
+            self.d_updated = True
+
+    def taps(self):
+        out = np.zeros((self.d_twox * self._M, self.d_taps_per_filter), np.float32)
+        _lib.check(_lib.lib().grb200_pfb_synth_branch_taps(self._h, _ptr(out)))
+        return out.tolist()
+
+    def print_taps(self):
+        for i, row in enumerate(self.taps()):
+            print("filter[%d]: [%s]" % (i, " ".join("%.4e" % v for v in row)))
+
+    def set_channel_map(self, chan_map):
+        m = np.ascontiguousarray(chan_map, np.int32)
+        with self.d_setlock:
+            _lib.check(_lib.lib().grb200_pfb_synth_set_channel_map(self._h, _ptr(m), len(m)))
+
+    def channel_map(self):
+        m = np.empty(4 * self._M + 16, np.int32)
+        n = _lib.lib().grb200_pfb_synth_get_channel_map(self._h, _ptr(m), len(m))
+        if n < 0:
+            _lib.check(n)
+        return m[:n].tolist()
+
+    def taps_per_filter(self):
+        return self.d_taps_per_filter
+
+    def work(self, noutput_items, input_items, output_items):
+        with self.d_setlock:
+            if self.d_updated:  # :229-232
+                self.d_updated = False
+                return 0
+            n = int(noutput_items)
+            nin = len(input_items)
+            ins = [as_items(a, _c64, n // self._M, "input_items[%d]" % j) for j, a in enumerate(input_items)]
+            out = as_items(output_items[0], _c64, n, "output_items[0]")
+            inp = (C.c_void_p * nin)(*[a.ctypes.data for a in ins])
+            _lib.check(_lib.lib().grb200_pfb_synth_work(self._h, inp, nin, _ptr(out), n))
+            return n
+
+    def work_dev(self, x_dev, stride, nin, out_dev, noutput_items, parity=0, stream=0):
+        """Device-resident, stateless: stream i at x_dev + 8*i*stride bytes, taps_per_filter-1 history items first."""
+        _lib.check(_lib.lib().grb200_pfb_synth_work_dev(self._h, C.c_void_p(x_dev), int(stride), int(nin), C.c_void_p(out_dev),
+                                                        int(noutput_items), int(parity), C.c_void_p(stream)))
+        return int(noutput_items)
+
+    def process(self, in_streams):
+        """Convenience: all of in_streams ([nin][n]) through work(); returns n*numchans items."""
+        ins = [np.ascontiguousarray(a, np.complex64) for a in in_streams]
+        n = min(len(a) for a in ins) * self._M
+        out = np.empty(n, np.complex64)
+        if self.d_updated:
+            self.work(0, ins, [out])
+        r = self.work(n, ins, [out])
+        return out[:r]
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().grb200_pfb_synth_destroy(h)
+            except Exception:
+                pass
+
+
+class filterbank_vcvcf(block):
+    """filterbank_vcvcf (gr-filter/include/gnuradio/filter/filterbank_vcvcf.h, lib/filterbank_vcvcf_impl.cc:23-96 over
+    lib/filterbank.cc): items are vectors of len(taps) complex; one FIR per vector element; history ntaps+1."""
+
+    def __init__(self, taps, device=0):
+        L = _lib.lib()
+        t = self._conv_taps(taps)
+        nf, nt = t.shape
+        block.__init__(self, "filterbank_vcvcf", io_signature.make(1, 1, 8 * nf), io_signature.make(1, 1, 8 * nf))
+        self._h = C.c_void_p()
+        _lib.check(L.grb200_filterbank_vcvcf_create(nf, nt, _ptr(t), int(device), C.byref(self._h)))
+        self.d_nfilts, self.d_ntaps = nf, nt
+        self._taps = t.copy()
+        self.d_updated = False
+        self.set_history(nt + 1)  # :34
+
+    @classmethod
+    def make(cls, taps, device=0):
+        return cls(taps, device)
+
+    @staticmethod
+    def _conv_taps(taps):
+        rows = [np.asarray(r, np.float32).reshape(-1) for r in taps]
+        if len(rows) == 0:
+            raise ValueError("The taps vector may not be empty.")  # filterbank.cc:30-32 (std::invalid_argument)
+        if any(len(r) != len(rows[0]) for r in rows):
+            raise RuntimeError("All sets of taps must be of the same length.")  # :60-64 (std::runtime_error)
+        if len(rows[0]) == 0:
+            raise ValueError("filterbank_vcvcf: at least one tap per filter is required")
+        return np.ascontiguousarray(np.stack(rows), np.float32)
+
+    def set_taps(self, taps):
+        rows = list(taps)
+        if len(rows) != self.d_nfilts:
+            raise RuntimeError("The number of filters is incorrect.")  # filterbank.cc:54-56
+        t = self._conv_taps(rows)
+        with self.d_setlock:  # filterbank_vcvcf_impl.cc:39-45
+            _lib.check(_lib.lib().grb200_filterbank_vcvcf_set_taps(self._h, t.shape[0], t.shape[1], _ptr(t)))
+            self.d_ntaps = t.shape[1]
+            self._taps = t.copy()
+            self.set_history(self.d_ntaps + 1)
+            self.d_updated = True
+
+    def taps(self):
+        return self._taps.tolist()
+
+    def print_taps(self):
+        for i, row in enumerate(self.taps()):
+            print("filter[%d]: [%s]" % (i, " ".join("%.4e" % v for v in row)))
+
+    def forecast(self, noutput_items, ninputs):
+        return [int(noutput_items) + self.history() - 1] * ninputs
+
+    def general_work(self, noutput_items, ninput_items, input_items, output_items):
+        with self.d_setlock:
+            if self.d_updated:  # :67-70
+                self.d_updated = False
+                return 0
+            n, nf = int(noutput_items), self.d_nfilts
+            xin = as_items(input_items[0], _c64, (n + self.d_ntaps) * nf if n else 0, "input_items[0]")
+            out = as_items(output_items[0], _c64, n * nf, "output_items[0]")
+            _lib.check(_lib.lib().grb200_filterbank_vcvcf_work(self._h, _ptr(xin), _ptr(out), n))
+            self.consume_each(n)  # :94
+            return n
+
+    def work_dev(self, in_dev, out_dev, noutput_items, stream=0):
+        """Device-resident: in_dev holds (noutput + ntaps) vectors, history first."""
+        _lib.check(_lib.lib().grb200_filterbank_vcvcf_work_dev(self._h, C.c_void_p(in_dev), C.c_void_p(out_dev),
+                                                               int(noutput_items), C.c_void_p(stream)))
+        return int(noutput_items)
+
+    def process(self, xin, noutput_items):
+        """One general_work() on xin ((noutput + ntaps) vectors, history first)."""
+        xin = np.ascontiguousarray(xin, np.complex64).reshape(-1)
+        out = np.empty(int(noutput_items) * self.d_nfilts, np.complex64)
+        if self.d_updated:
+            self.general_work(0, [0], [xin], [out])
+        r = self.general_work(noutput_items, [len(xin) // self.d_nfilts], [xin], [out])
+        return out[: r * self.d_nfilts].reshape(r, self.d_nfilts)
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().grb200_filterbank_vcvcf_destroy(h)
+            except Exception:
+                pass
+
+
 class _pfb_namespace:
     """gnuradio.filter.pfb: the Python hier blocks of gr-filter/python/filter/pfb.py."""
 
@@ -813,6 +1009,70 @@ class _pfb_namespace:
             outs = np.zeros((nouts, noutput), np.complex64)
             self.pfb.work_interleaved(xin, [outs[j] for j in range(nouts)], noutput)
             return outs
+
+    class channelizer_hier_ccf:
+        """pfb.channelizer_hier_ccf(n_chans, n_filterbanks, taps, outchans) (gr-filter/python/filter/pfb.py:406-480):
+        stream_to_vector -> vector_map split -> n_filterbanks x filterbank_vcvcf (branch taps reversed(taps[i::n_chans]))
+        -> vector_map combine -> fft_vcc(n_chans, forward, window of ones) -> selector -> vector_to_streams.
+
+        On the CPU the split into n_filterbanks blocks buys threads; it does not change a single output value, so here ONE
+        filterbank_vcvcf handle carries all n_chans branch filters, stream_to_vector is the pointer reinterpretation it is
+        on a device, and the three stages are chained device-resident (no host round trip between them)."""
+
+        def __init__(self, n_chans, n_filterbanks=1, taps=None, outchans=None, atten=100, bw=1.0, tb=0.2, ripple=0.1,
+                     device=0):
+            from . import blocks as _blocks
+            from . import fft as _fft
+
+            if taps is None or len(taps) == 0:
+                # pfb.py:434-435 designs taps with optfir; tap design is out of scope here (SURVEY.md section 2)
+                raise ValueError("pfb.channelizer_hier_ccf: taps must be supplied")
+            n_chans = int(n_chans)
+            self.n_chans = n_chans
+            self.n_filterbanks = min(int(n_filterbanks), n_chans)  # :423-424
+            self.outchans = list(range(n_chans)) if outchans is None else [int(c) for c in outchans]
+            if any(c < 0 or c >= n_chans for c in self.outchans):
+                raise ValueError("pfb.channelizer_hier_ccf: outchans out of range")
+            taps = [float(v) for v in taps]
+            extra = int(np.ceil(1.0 * len(taps) / n_chans) * n_chans - len(taps))  # :437-438
+            taps = taps + [0.0] * extra
+            chantaps = [list(reversed(taps[i: len(taps): n_chans])) for i in range(n_chans)]  # :440
+            self._device = int(device)
+            self.fb = filterbank_vcvcf(chantaps, device)
+            self.fft = _fft.fft_vcc(n_chans, True, [1.0] * n_chans, False, 1, device)  # :466
+            self.v2ss = _blocks.vector_to_streams(8, n_chans, device)
+            self.ntaps = self.fb.d_ntaps
+
+        def run(self, x):
+            """Whole finite stream x, zeros before t=0 (what tb.run() delivers): returns [len(outchans)][n] complex64."""
+            M, nt = self.n_chans, self.ntaps
+            x = np.ascontiguousarray(x, np.complex64)
+            n = len(x) // M
+            xin = np.concatenate([np.zeros(nt * M, np.complex64), x[: n * M]])  # history ntaps+1 -> ntaps zero vectors
+            L = _lib.lib()
+            dev = self._device
+            bufs = []
+
+            def dalloc(nbytes):
+                p = C.c_void_p()
+                _lib.check(L.grb200_dev_alloc(dev, C.byref(p), max(int(nbytes), 16)))
+                bufs.append(p)
+                return p
+
+            try:
+                d_in, d_fb, d_fft, d_out = dalloc(xin.nbytes), dalloc(n * M * 8), dalloc(n * M * 8), dalloc(n * M * 8)
+                _lib.check(L.grb200_memcpy_h2d(dev, d_in, _ptr(xin), xin.nbytes))
+                # one stream (0 = the legacy default stream) orders the three launches; no host round trip in between
+                self.fb.work_dev(d_in.value, d_fb.value, n, 0)
+                self.fft.work_dev(d_fb.value, d_fft.value, n, 0)  # stream_to_vector / the vector stream: same bytes
+                self.v2ss.work_dev(d_fft.value, d_out.value, n, n, 0)
+                outs = np.empty((M, n), np.complex64)
+                _lib.check(L.grb200_dev_sync(dev))
+                _lib.check(L.grb200_memcpy_d2h(dev, _ptr(outs), d_out, outs.nbytes))
+            finally:
+                for p in bufs:
+                    L.grb200_dev_free(dev, p)
+            return outs[self.outchans]
 
 
 pfb = _pfb_namespace()

@@ -38,7 +38,8 @@ typedef enum {
     GRB200_ERANGE = -2, /* size out of range       -> std::out_of_range     */
     GRB200_ECUDA = -3,  /* CUDA runtime failure    -> std::runtime_error    */
     GRB200_ENOMEM = -4, /* allocation failure      -> std::runtime_error    */
-    GRB200_EWINDOW = -5 /* window length mismatch  -> std::runtime_error ("fft_vcc: window not the same length as fft_size") */
+    GRB200_EWINDOW = -5, /* window length mismatch -> std::runtime_error ("fft_vcc: window not the same length as fft_size") */
+    GRB200_ERUNTIME = -6 /* any other std::runtime_error site of the reference blocks */
 } grb200_status;
 
 /* ---- library / device ------------------------------------------------------------------------- */
@@ -69,6 +70,10 @@ int grb200_dev_sync(int device);
 typedef struct grb200_fir grb200_fir;
 int grb200_fir_ccf_create(int decim, const float* taps, int ntaps, int device, grb200_fir** out);
 int grb200_fir_ccc_create(int decim, const float* taps_re_im, int ntaps, int device, grb200_fir** out);
+/* fir_filter_fff: fir_filter_blk<float,float,float> (gr-filter/include/gnuradio/filter/fir_filter_blk.h:66)
+ * over kernel::fir_filter<float,float,float>::filter (gr-filter/lib/fir_filter.cc:122-130).  Same handle type and calls;
+ * items are float32 (in: noutput*decim + ntaps-1 floats, out: noutput floats). */
+int grb200_fir_fff_create(int decim, const float* taps, int ntaps, int device, grb200_fir** out);
 int grb200_fir_set_taps(grb200_fir* h, const float* taps, int ntaps); /* re/im pairs for ccc */
 int grb200_fir_ntaps(const grb200_fir* h);
 int grb200_fir_decimation(const grb200_fir* h);
@@ -188,6 +193,50 @@ int grb200_pfb_dec_work_dev(grb200_pfbdec* h, const void* x_dev, long long strid
                             void* stream);
 void grb200_pfb_dec_destroy(grb200_pfbdec* h);
 
+/* ---- pfb_synthesizer_ccf ---------------------------------------------
+ * Replaces pfb_synthesizer_ccf_impl: ctor gr-filter/lib/pfb_synthesizer_ccf_impl.cc:31-69, set_taps/set_taps1/set_taps2
+ * :77-184, set_channel_map :202-217, work :221-284 (over kernel::fir_filter_with_buffer_ccf delay lines and a
+ * twox*numchans-point backward fft_complex).  sync_interpolator by numchans: every input item of the (up to twox*numchans)
+ * input streams makes numchans output items;  out[n*numchans + i] = sum_j taps[i + j*numchans] V_q[n-j],
+ * V = IFFT over the channel-mapped inputs, q = i (1x) or the half of the 2*numchans-point IFFT that alternates with n (2x).
+ * work(): in_streams[i] holds noutput/numchans NEW items (history 1, :92); the filters' delay lines are kept in the handle
+ * (as the last taps_per_filter-1 items of every stream) and zeroed by set_taps like the reference's.  noutput must be a
+ * multiple of numchans (set_output_multiple, :68).  work_dev() is stateless: stream i at x_dev + i*stride items with
+ * taps_per_filter-1 history items in front; `parity` = d_state at the first output (2x only).
+ * The block mirrors keep the reference's "return 0 from the work() that sees d_updated". */
+typedef struct grb200_pfbsynth grb200_pfbsynth;
+int grb200_pfb_synth_ccf_create(unsigned int numchans, const float* taps, int ntaps, int twox, int device,
+                                grb200_pfbsynth** out);
+int grb200_pfb_synth_set_taps(grb200_pfbsynth* h, const float* taps, int ntaps);
+int grb200_pfb_synth_set_channel_map(grb200_pfbsynth* h, const int* map, int n);
+int grb200_pfb_synth_get_channel_map(const grb200_pfbsynth* h, int* map, int n); /* returns the map length */
+int grb200_pfb_synth_taps_per_filter(const grb200_pfbsynth* h);
+int grb200_pfb_synth_numchans(const grb200_pfbsynth* h);
+int grb200_pfb_synth_twox(const grb200_pfbsynth* h);
+/* d_taps as taps() returns them: twox*numchans rows of taps_per_filter floats */
+int grb200_pfb_synth_branch_taps(const grb200_pfbsynth* h, float* out);
+int grb200_pfb_synth_work(grb200_pfbsynth* h, const void* const* in_streams, int nin, void* out_host, long long noutput);
+int grb200_pfb_synth_work_dev(grb200_pfbsynth* h, const void* x_dev, long long stride, int nin, void* out_dev,
+                              long long noutput, int parity, void* stream);
+void grb200_pfb_synth_destroy(grb200_pfbsynth* h);
+
+/* ---- filterbank_vcvcf ------------------------------------------------
+ * Replaces gr::filter::kernel::filterbank (ctor/set_taps, gr-filter/lib/filterbank.cc:26-79) and
+ * filterbank_vcvcf_impl::general_work (gr-filter/lib/filterbank_vcvcf_impl.cc:54-96): items are vectors of nfilts complex64,
+ *     out[j][i] = sum_k taps[i][k] * in[j + ntaps-1-k][i];
+ * `in` holds noutput + ntaps vectors, the first ntaps being history (set_history(ntaps + 1), :34 -- the newest vector of a
+ * window is never read: the block delays by one item); a filter whose taps are all zero writes zeros (:83-88).
+ * taps: [nfilts][ntaps] row-major.  set_taps with a different nfilts returns GRB200_ERUNTIME (std::runtime_error,
+ * filterbank.cc:54-56); rows of unequal length are refused by the block mirrors above this ABI (:60-64). */
+typedef struct grb200_fbank grb200_fbank;
+int grb200_filterbank_vcvcf_create(int nfilts, int ntaps, const float* taps, int device, grb200_fbank** out);
+int grb200_filterbank_vcvcf_set_taps(grb200_fbank* h, int nfilts, int ntaps, const float* taps);
+int grb200_filterbank_vcvcf_nfilts(const grb200_fbank* h);
+int grb200_filterbank_vcvcf_ntaps(const grb200_fbank* h);
+int grb200_filterbank_vcvcf_work(grb200_fbank* h, const void* in_host, void* out_host, long long noutput);
+int grb200_filterbank_vcvcf_work_dev(grb200_fbank* h, const void* in_dev, void* out_dev, long long noutput, void* stream);
+void grb200_filterbank_vcvcf_destroy(grb200_fbank* h);
+
 /* ---- interp_fir_filter_ccf / interp_fir_filter_ccc -------------------------------------------------
  * Replaces gr::filter::interp_fir_filter_impl<gr_complex,gr_complex,float|gr_complex>
  *   set_taps / install_taps  gr-filter/lib/interp_fir_filter_impl.cc:72-117 (zero-pad to a multiple of the
@@ -253,6 +302,58 @@ int grb200_fft_vcc_work_dev(grb200_fftvcc* h, const void* in_dev, void* out_dev,
 int grb200_fft_vcc_work_magsq(grb200_fftvcc* h, const void* in_host, float* out_host, long long nvectors);
 int grb200_fft_vcc_work_magsq_dev(grb200_fftvcc* h, const void* in_dev, float* out_dev, long long nvectors, void* stream);
 void grb200_fft_vcc_destroy(grb200_fftvcc* h);
+
+/* ---- fft_vfc -------------------------------------------------------
+ * Replaces fft_vfc_fftw: ctor/set_window gr-fft/lib/fft_vfc_fftw.cc:30-55, work :57-92 -- float32 vectors in, the full
+ * fft_size-point complex transform out (no shift option).  Same handle type as fft_vcc: set_window, fft_size, work,
+ * work_dev and destroy are the grb200_fft_vcc_* calls; `in` holds fft_size floats per vector. */
+int grb200_fft_vfc_create(int fft_size, int forward, const float* window, int nwindow, int device, grb200_fftvcc** out);
+
+/* ---- logpwrfft_c / logpwrfft_f -------------------------------------
+ * Replaces the hier block gr-fft/python/fft/logpwrfft.py:29-64 as one handle:
+ *   stream_to_vector_decimator (gr-blocks/python/blocks/stream_to_vector_decimator.py:15-96: stream_to_vector + keep_one_in_n,
+ *   gr-blocks/lib/keep_one_in_n_impl.cc:56-77 -- the LAST vector of every group of `decimation` is kept)
+ *   -> fft_vcc | fft_vfc (forward, window, no shift) -> complex_to_mag_squared
+ *   -> single_pole_iir_filter_ff (gr-filter/lib/single_pole_iir_filter_ff_impl.cc:47-67; alpha = avg_alpha when averaging, else 1)
+ *   -> nlog10_ff(10, fft_size, -20log10(fft_size) - 10log10(sum(w^2)/fft_size) - 20log10(ref_scale/2)) (gr-blocks/lib/nlog10_ff_impl.cc).
+ * `window` must hold fft_size floats (the Python block always passes one; default window.blackmanharris).
+ * work: `in` holds nitems stream items (complex64 or float32); whole vectors only are consumed; at most max_out frames of
+ * fft_size floats are written.  *consumed = stream items used, *produced = frames written.  The decimator's counter and the
+ * filter memory live in the handle like in the reference blocks.  Setters mirror the Python methods :66-113. */
+typedef struct grb200_logpwr grb200_logpwr;
+int grb200_logpwrfft_create(int complex_input, double sample_rate, int fft_size, double ref_scale, double frame_rate,
+                            double avg_alpha, int average, const float* window, int nwindow, int device, grb200_logpwr** out);
+int grb200_logpwrfft_set_decimation(grb200_logpwr* h, double decim);
+int grb200_logpwrfft_set_vec_rate(grb200_logpwr* h, double vec_rate);
+int grb200_logpwrfft_set_sample_rate(grb200_logpwr* h, double sample_rate);
+int grb200_logpwrfft_set_average(grb200_logpwr* h, int average);
+int grb200_logpwrfft_set_avg_alpha(grb200_logpwr* h, double avg_alpha);
+int grb200_logpwrfft_decimation(const grb200_logpwr* h);
+double grb200_logpwrfft_sample_rate(const grb200_logpwr* h);
+double grb200_logpwrfft_frame_rate(const grb200_logpwr* h);
+int grb200_logpwrfft_average(const grb200_logpwr* h);
+double grb200_logpwrfft_avg_alpha(const grb200_logpwr* h);
+int grb200_logpwrfft_fft_size(const grb200_logpwr* h);
+int grb200_logpwrfft_work(grb200_logpwr* h, const void* in_host, long long nitems, float* out_host, long long max_out,
+                          long long* consumed, long long* produced);
+int grb200_logpwrfft_work_dev(grb200_logpwr* h, const void* in_dev, long long nitems, float* out_dev, long long max_out,
+                              long long* consumed, long long* produced, void* stream);
+void grb200_logpwrfft_destroy(grb200_logpwr* h);
+
+/* ---- stream_to_vector / vector_to_stream / vector_to_streams --------
+ * stream_to_vector_impl::work (gr-blocks/lib/stream_to_vector_impl.cc:46-58) is memcpy(out, in, noutput*block_size): a stream
+ * of items and the stream of vectors over it are THE SAME BYTES.  In the device-resident mode the block therefore is a pointer
+ * reinterpretation: hand the upstream block's device buffer to grb200_fft_vcc_work_dev (etc.) as it is -- no entry point, no
+ * kernel, no copy.  vector_to_stream (vector_to_stream_impl.cc) is the same statement read backwards.
+ * vector_to_streams_impl::work (gr-blocks/lib/vector_to_streams_impl.cc:34-55): out_j[n] = in[n*nstreams + j] -- a transpose;
+ * streams_to_vector is its mirror image (and, with itemsize 8, the stream_to_streams step the channelizer absorbs).
+ * itemsize: 4 (float) or 8 (gr_complex).  Device forms: stream j at base + j*stride items. */
+int grb200_vector_to_streams_work(int device, int itemsize, int nstreams, const void* in_host, void* const* out_streams,
+                                  long long noutput);
+int grb200_vector_to_streams_work_dev(int device, int itemsize, int nstreams, const void* in_dev, void* out_dev,
+                                      long long out_stride, long long noutput, void* stream);
+int grb200_streams_to_vector_work_dev(int device, int itemsize, int nstreams, const void* in_dev, long long in_stride,
+                                      void* out_dev, long long noutput, void* stream);
 
 int grb200_magsq_work(int device, const void* in_host, float* out_host, long long nitems);
 int grb200_magsq_work_dev(int device, const void* in_dev, float* out_dev, long long nitems, void* stream);

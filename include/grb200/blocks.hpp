@@ -25,6 +25,7 @@
 
 #include <cmath>
 #include <complex>
+#include <cstdlib>
 #include <memory>
 #include <mutex>
 #include <stdexcept>
@@ -37,6 +38,7 @@
 #ifdef GRB200_WITH_GNURADIO
 #include <gnuradio/block.h>
 #include <gnuradio/io_signature.h>
+#include <gnuradio/sptr_magic.h>
 #include <gnuradio/sync_block.h>
 #include <gnuradio/sync_decimator.h>
 namespace grb200 {
@@ -164,7 +166,34 @@ inline void check(int rc)
     throw std::runtime_error(msg);
 }
 
-inline int default_device() { return 0; }
+// Device the next make() puts its block on: GRB200_DEVICE in the environment (read once), or whatever the application set
+// with set_default_device() -- e.g. one flowgraph per GPU, or the upper and lower half of a channel plan on two GPUs.
+inline int& default_device_ref()
+{
+    static int dev = [] {
+        const char* e = std::getenv("GRB200_DEVICE");
+        return e ? std::atoi(e) : 0;
+    }();
+    return dev;
+}
+inline int default_device() { return default_device_ref(); }
+inline void set_default_device(int device) { default_device_ref() = device; }
+
+// make() hands the new block to the runtime exactly like the reference: gnuradio::get_initial_sptr (gnuradio-runtime/include/
+// gnuradio/sptr_magic.h) registers it for hier-block self-connection; the stand-in build has no such registry.
+#ifdef GRB200_WITH_GNURADIO
+template <class T>
+inline std::shared_ptr<T> make_sptr(T* p)
+{
+    return gnuradio::get_initial_sptr(p);
+}
+#else
+template <class T>
+inline std::shared_ptr<T> make_sptr(T* p)
+{
+    return std::shared_ptr<T>(p);
+}
+#endif
 
 } // namespace grb200
 
@@ -172,21 +201,23 @@ namespace gr {
 namespace filter {
 
 // ---------------------------------------------------------------------------------------------------
-// fir_filter_blk<gr_complex, gr_complex, float|gr_complex>  (fir_filter_ccf / fir_filter_ccc)
+// fir_filter_blk<gr_complex, gr_complex, float|gr_complex> and <float, float, float>  (fir_filter_ccf / _ccc / _fff)
 // ---------------------------------------------------------------------------------------------------
 template <class IN_T, class OUT_T, class TAP_T>
 class fir_filter_blk : public grb200::rt::sync_decimator
 {
-    static_assert(std::is_same<IN_T, gr_complex>::value && std::is_same<OUT_T, gr_complex>::value &&
-                      (std::is_same<TAP_T, float>::value || std::is_same<TAP_T, gr_complex>::value),
-                  "libgrb200 re-hosts the ccf and ccc instantiations (SURVEY.md section 8)");
+    static constexpr bool is_fff =
+        std::is_same<IN_T, float>::value && std::is_same<OUT_T, float>::value && std::is_same<TAP_T, float>::value;
+    static_assert(is_fff || (std::is_same<IN_T, gr_complex>::value && std::is_same<OUT_T, gr_complex>::value &&
+                             (std::is_same<TAP_T, float>::value || std::is_same<TAP_T, gr_complex>::value)),
+                  "libgrb200 re-hosts the ccf, ccc and fff instantiations (SURVEY.md section 8)");
 
 public:
     typedef std::shared_ptr<fir_filter_blk<IN_T, OUT_T, TAP_T>> sptr;
 
     static sptr make(int decimation, const std::vector<TAP_T>& taps)
     {
-        return sptr(new fir_filter_blk<IN_T, OUT_T, TAP_T>(decimation, taps));
+        return grb200::make_sptr(new fir_filter_blk<IN_T, OUT_T, TAP_T>(decimation, taps));
     }
 
     ~fir_filter_blk() override { grb200_fir_destroy(d_h); }
@@ -216,13 +247,15 @@ public:
 
 private:
     fir_filter_blk(int decimation, const std::vector<TAP_T>& taps)
-        : sync_decimator(std::is_same<TAP_T, float>::value ? "fir_filter_ccf" : "fir_filter_ccc",
+        : sync_decimator(is_fff ? "fir_filter_fff" : std::is_same<TAP_T, float>::value ? "fir_filter_ccf" : "fir_filter_ccc",
                          grb200::rt::io_signature::make(1, 1, sizeof(IN_T)),
                          grb200::rt::io_signature::make(1, 1, sizeof(OUT_T)), decimation),
           d_taps(taps)
     {
         const float* t = reinterpret_cast<const float*>(taps.data());
-        if (std::is_same<TAP_T, float>::value)
+        if (is_fff)
+            grb200::check(grb200_fir_fff_create(decimation, t, (int)taps.size(), grb200::default_device(), &d_h));
+        else if (std::is_same<TAP_T, float>::value)
             grb200::check(grb200_fir_ccf_create(decimation, t, (int)taps.size(), grb200::default_device(), &d_h));
         else
             grb200::check(grb200_fir_ccc_create(decimation, t, (int)taps.size(), grb200::default_device(), &d_h));
@@ -234,6 +267,7 @@ private:
 };
 typedef fir_filter_blk<gr_complex, gr_complex, float> fir_filter_ccf;
 typedef fir_filter_blk<gr_complex, gr_complex, gr_complex> fir_filter_ccc;
+typedef fir_filter_blk<float, float, float> fir_filter_fff;
 
 // ---------------------------------------------------------------------------------------------------
 // freq_xlating_fir_filter<gr_complex, gr_complex, float|gr_complex>  (freq_xlating_fir_filter_ccf / _ccc)
@@ -242,16 +276,18 @@ typedef fir_filter_blk<gr_complex, gr_complex, gr_complex> fir_filter_ccc;
 template <class IN_T, class OUT_T, class TAP_T>
 class freq_xlating_fir_filter : public grb200::rt::sync_decimator
 {
-    static_assert(std::is_same<IN_T, gr_complex>::value && std::is_same<OUT_T, gr_complex>::value &&
-                      (std::is_same<TAP_T, float>::value || std::is_same<TAP_T, gr_complex>::value),
-                  "libgrb200 re-hosts the ccf and ccc instantiations (SURVEY.md section 8)");
+    static constexpr bool is_fff =
+        std::is_same<IN_T, float>::value && std::is_same<OUT_T, float>::value && std::is_same<TAP_T, float>::value;
+    static_assert(is_fff || (std::is_same<IN_T, gr_complex>::value && std::is_same<OUT_T, gr_complex>::value &&
+                             (std::is_same<TAP_T, float>::value || std::is_same<TAP_T, gr_complex>::value)),
+                  "libgrb200 re-hosts the ccf, ccc and fff instantiations (SURVEY.md section 8)");
 
 public:
     typedef std::shared_ptr<freq_xlating_fir_filter<IN_T, OUT_T, TAP_T>> sptr;
 
     static sptr make(int decimation, const std::vector<TAP_T>& taps, double center_freq, double sampling_freq)
     {
-        return sptr(new freq_xlating_fir_filter<IN_T, OUT_T, TAP_T>(decimation, taps, center_freq, sampling_freq));
+        return grb200::make_sptr(new freq_xlating_fir_filter<IN_T, OUT_T, TAP_T>(decimation, taps, center_freq, sampling_freq));
     }
 
     ~freq_xlating_fir_filter() override { grb200_freq_xlating_fir_destroy(d_h); }
@@ -317,9 +353,11 @@ typedef freq_xlating_fir_filter<gr_complex, gr_complex, gr_complex> freq_xlating
 template <class IN_T, class OUT_T, class TAP_T>
 class interp_fir_filter : public grb200::rt::sync_interpolator
 {
-    static_assert(std::is_same<IN_T, gr_complex>::value && std::is_same<OUT_T, gr_complex>::value &&
-                      (std::is_same<TAP_T, float>::value || std::is_same<TAP_T, gr_complex>::value),
-                  "libgrb200 re-hosts the ccf and ccc instantiations (SURVEY.md section 8)");
+    static constexpr bool is_fff =
+        std::is_same<IN_T, float>::value && std::is_same<OUT_T, float>::value && std::is_same<TAP_T, float>::value;
+    static_assert(is_fff || (std::is_same<IN_T, gr_complex>::value && std::is_same<OUT_T, gr_complex>::value &&
+                             (std::is_same<TAP_T, float>::value || std::is_same<TAP_T, gr_complex>::value)),
+                  "libgrb200 re-hosts the ccf, ccc and fff instantiations (SURVEY.md section 8)");
 
 public:
     typedef std::shared_ptr<interp_fir_filter<IN_T, OUT_T, TAP_T>> sptr;
@@ -330,7 +368,7 @@ public:
             throw std::out_of_range("interp_fir_filter_impl: interpolation must be > 0");
         if (taps.empty()) // :50-52
             throw std::runtime_error("interp_fir_filter_impl: no filter taps provided.");
-        return sptr(new interp_fir_filter<IN_T, OUT_T, TAP_T>(interpolation, taps));
+        return grb200::make_sptr(new interp_fir_filter<IN_T, OUT_T, TAP_T>(interpolation, taps));
     }
 
     ~interp_fir_filter() override { grb200_interp_fir_destroy(d_h); }
@@ -406,7 +444,7 @@ public:
             throw std::out_of_range("rational_resampler_base_impl<IN_T,OUT_T,TAP_T>: decimation must be > 0");
         if (taps.empty())
             throw std::runtime_error("rational_resampler_base_impl: no filter taps provided.");
-        return sptr(new rational_resampler_base<IN_T, OUT_T, TAP_T>(interpolation, decimation, taps));
+        return grb200::make_sptr(new rational_resampler_base<IN_T, OUT_T, TAP_T>(interpolation, decimation, taps));
     }
 
     ~rational_resampler_base() override { grb200_rational_resampler_destroy(d_h); }
@@ -494,7 +532,7 @@ public:
     typedef std::shared_ptr<fft_filter_ccc> sptr;
     static sptr make(int decimation, const std::vector<gr_complex>& taps, int nthreads = 1)
     {
-        return sptr(new fft_filter_ccc(decimation, taps, nthreads));
+        return grb200::make_sptr(new fft_filter_ccc(decimation, taps, nthreads));
     }
     ~fft_filter_ccc() override { grb200_fftfilt_destroy(d_h); }
 
@@ -547,7 +585,7 @@ public:
     typedef std::shared_ptr<fft_filter_ccf> sptr;
     static sptr make(int decimation, const std::vector<float>& taps, int nthreads = 1)
     {
-        return sptr(new fft_filter_ccf(decimation, taps, nthreads));
+        return grb200::make_sptr(new fft_filter_ccf(decimation, taps, nthreads));
     }
     ~fft_filter_ccf() override { grb200_fftfilt_destroy(d_h); }
 
@@ -600,7 +638,7 @@ public:
     typedef std::shared_ptr<pfb_channelizer_ccf> sptr;
     static sptr make(unsigned int numchans, const std::vector<float>& taps, float oversample_rate)
     {
-        return sptr(new pfb_channelizer_ccf(numchans, taps, oversample_rate));
+        return grb200::make_sptr(new pfb_channelizer_ccf(numchans, taps, oversample_rate));
     }
     ~pfb_channelizer_ccf() override { grb200_pfb_chan_destroy(d_h); }
 
@@ -689,7 +727,7 @@ public:
     static sptr make(unsigned int decim, const std::vector<float>& taps, unsigned int channel,
                      bool use_fft_rotator = true, bool use_fft_filters = true)
     {
-        return sptr(new pfb_decimator_ccf(decim, taps, channel, use_fft_rotator, use_fft_filters));
+        return grb200::make_sptr(new pfb_decimator_ccf(decim, taps, channel, use_fft_rotator, use_fft_filters));
     }
     ~pfb_decimator_ccf() override { grb200_pfb_dec_destroy(d_h); }
 
@@ -781,7 +819,7 @@ public:
     static sptr make(int fft_size, bool forward, const std::vector<float>& window, bool shift = false,
                      int nthreads = 1)
     {
-        return sptr(new fft_vcc(fft_size, forward, window, shift, nthreads));
+        return grb200::make_sptr(new fft_vcc(fft_size, forward, window, shift, nthreads));
     }
     ~fft_vcc() override { grb200_fft_vcc_destroy(d_h); }
     void set_nthreads(int n) { d_nthreads = n; }
@@ -824,7 +862,7 @@ class complex_to_mag_squared : public grb200::rt::sync_block
 {
 public:
     typedef std::shared_ptr<complex_to_mag_squared> sptr;
-    static sptr make(size_t vlen = 1) { return sptr(new complex_to_mag_squared(vlen)); }
+    static sptr make(size_t vlen = 1) { return grb200::make_sptr(new complex_to_mag_squared(vlen)); }
     int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
     {
         grb200::check(grb200_magsq_work(grb200::default_device(), input_items[0], (float*)output_items[0],

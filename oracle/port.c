@@ -724,3 +724,237 @@ int grbo_firdes_low_pass_2(double gain, double fs, double cutoff, double tw, dou
     free(taps);
     return ntaps;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * fir_filter_fff: kernel::fir_filter<float,float,float>::filter (gr-filter/lib/fir_filter.cc:122-130) under
+ * fir_filter_blk_impl<float,float,float>::work (gr-filter/lib/fir_filter_blk_impl.cc:67-90).
+ * ---------------------------------------------------------------------------------------------- */
+int grbo_fir_fff(int decim, const float* taps, int ntaps, const float* in, float* out, long nout)
+{
+    float* rev = (float*)malloc(sizeof(float) * (size_t)ntaps);
+    if (!rev)
+        return -1;
+    for (int t = 0; t < ntaps; t++)
+        rev[t] = taps[ntaps - 1 - t];
+    for (long i = 0; i < nout; i++) {
+        const float* x = in + i * decim;
+        float acc = 0.0f;
+        for (int t = 0; t < ntaps; t++)
+            acc += x[t] * rev[t];
+        out[i] = acc;
+    }
+    free(rev);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * fft_vfc_fftw::work (gr-fft/lib/fft_vfc_fftw.cc:57-92): float vector -> (window) -> complex FFT, all N bins.
+ * ---------------------------------------------------------------------------------------------- */
+int grbo_fft_vfc(int fft_size, int forward, const float* window, int nwindow, const float* in, cf32* out, long nvec)
+{
+    if (!(nwindow == 0 || nwindow == fft_size))
+        return -1;
+    fftplan plan;
+    if (plan_init(&plan, fft_size, forward))
+        return -2;
+    const int N = fft_size;
+    cf32* dst = (cf32*)malloc(sizeof(cf32) * (size_t)N);
+    for (long v = 0; v < nvec; v++, in += N, out += N) {
+        for (int i = 0; i < N; i++) {
+            dst[i].re = nwindow ? in[i] * window[i] : in[i];
+            dst[i].im = 0.0f;
+        }
+        plan_exec(&plan, dst, out);
+    }
+    free(dst);
+    plan_free(&plan);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * logpwrfft_c / logpwrfft_f (gr-fft/python/fft/logpwrfft.py:29-64), the whole hier block as one loop:
+ * stream_to_vector + keep_one_in_n (gr-blocks/lib/keep_one_in_n_impl.cc:56-77: d_count counts down from n, the LAST vector
+ * of every group of n is kept) -> window, forward FFT, no shift -> |.|^2 -> single_pole_iir<float,float,double>
+ * (gr-filter/include/gnuradio/filter/single_pole_iir.h:78-86: y = alpha*x + (1-alpha)*y_prev in double, stored as float)
+ * -> nlog10_ff (gr-blocks/lib/nlog10_ff_impl.cc:28-60: n/log2f(10) * log2f(max(x, FLT_MIN) * 10^(k/n))).
+ * count_state / iir_state carry keep_one_in_n's counter and the filter memory across calls.
+ * ---------------------------------------------------------------------------------------------- */
+long grbo_logpwrfft(int complex_input, int fft_size, double ref_scale, int decim, double avg_alpha, int average,
+                    const float* window, const void* in_, long nitems, float* out, long max_out, int* count_state,
+                    float* iir_state)
+{
+    if (decim < 1 || fft_size < 1)
+        return -1;
+    const int N = fft_size;
+    fftplan plan;
+    if (plan_init(&plan, N, 1))
+        return -2;
+    double window_power = 0.0;
+    for (int i = 0; i < N; i++)
+        window_power += (double)window[i] * (double)window[i];
+    const double kd = -20 * log10((double)N) - 10 * log10(window_power / N) - 20 * log10(ref_scale / 2);
+    const float n = 10.0f, k = (float)kd;
+    const float n_log2_10 = n / log2f(10.0f);
+    const float ten_k_n = powf(10.0f, k / n);
+    const double alpha = average ? avg_alpha : 1.0, one_minus_alpha = 1.0 - alpha;
+    cf32* dst = (cf32*)malloc(sizeof(cf32) * (size_t)N);
+    cf32* res = (cf32*)malloc(sizeof(cf32) * (size_t)N);
+    const long nvec_in = nitems / N;
+    long no = 0;
+    for (long ni = 0; ni < nvec_in && no < max_out; ni++) {
+        (*count_state)--;
+        if (*count_state > 0)
+            continue;
+        *count_state = decim;
+        if (complex_input) {
+            const cf32* x = (const cf32*)in_ + ni * N;
+            for (int i = 0; i < N; i++) {
+                dst[i].re = x[i].re * window[i];
+                dst[i].im = x[i].im * window[i];
+            }
+        } else {
+            const float* x = (const float*)in_ + ni * N;
+            for (int i = 0; i < N; i++) {
+                dst[i].re = x[i] * window[i];
+                dst[i].im = 0.0f;
+            }
+        }
+        plan_exec(&plan, dst, res);
+        float* o = out + no * N;
+        for (int i = 0; i < N; i++) {
+            const float p = res[i].re * res[i].re + res[i].im * res[i].im;
+            const float y = (float)(alpha * (double)p + one_minus_alpha * (double)iir_state[i]);
+            iir_state[i] = y;
+            float v = y > 1.17549435e-38f ? y : 1.17549435e-38f;
+            if (ten_k_n != 1.0f)
+                v = v * ten_k_n;
+            o[i] = log2f(v) * n_log2_10;
+        }
+        no++;
+    }
+    free(dst);
+    free(res);
+    plan_free(&plan);
+    return no;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * pfb_synthesizer_ccf (gr-filter/lib/pfb_synthesizer_ccf_impl.cc): set_taps1 :95-129, set_taps2 :131-184, work :221-284
+ * over fir_filter_with_buffer_ccf::filter (gr-filter/lib/fir_filter_with_buffer.cc: a delay line, y = sum_j taps[j] x[n-j]).
+ * A fresh block; the delay lines carry on over `chunk`-sized work() calls (chunking cannot change the result).
+ * in_streams[i] holds noutput/numchans items.  Returns noutput, <0 on error.
+ * ---------------------------------------------------------------------------------------------- */
+int grbo_pfb_synthesizer_ccf(unsigned int numchans, const float* taps, int ntaps, int twox, const int* channel_map, int nmap,
+                             const cf32* const* in_streams, int nin, cf32* out, int noutput, int chunk)
+{
+    (void)chunk;
+    const int M = (int)numchans, tw = twox ? 2 : 1, NF = tw * M;
+    if (M % tw != 0)
+        return -1;
+    if (noutput % M != 0)
+        return -3;
+    const int T = (ntaps + M - 1) / M;
+    /* d_taps[f][j], f < NF */
+    float* ft = (float*)calloc((size_t)NF * T, sizeof(float));
+    for (int i = 0; i < M; i++) {
+        int state = 0;
+        for (int j = 0; j < T; j++) {
+            const int idx = i + j * M;
+            const float v = idx < ntaps ? taps[idx] : 0.0f;
+            if (tw == 1) {
+                ft[i * T + j] = v;
+            } else if (state == 0) {
+                ft[(M + i) * T + j] = v;
+                state = 1;
+            } else {
+                ft[i * T + j] = v;
+                state = 0;
+            }
+        }
+    }
+    int* map = (int*)malloc(sizeof(int) * (size_t)NF);
+    for (int i = 0; i < NF; i++)
+        map[i] = i;
+    if (nmap > 0) {
+        for (int i = 0; i < nmap; i++)
+            if (channel_map[i] < 0 || channel_map[i] >= NF) {
+                free(ft);
+                free(map);
+                return -2;
+            }
+        for (int i = 0; i < nmap && i < NF; i++)
+            map[i] = channel_map[i];
+    }
+    fftplan plan;
+    plan_init(&plan, NF, 0);
+    cf32* fin = (cf32*)calloc((size_t)NF, sizeof(cf32));
+    cf32* fout = (cf32*)malloc(sizeof(cf32) * (size_t)NF);
+    cf32* dl = (cf32*)calloc((size_t)NF * T, sizeof(cf32)); /* delay lines, dl[f][0] = newest */
+    int state = 0;
+    for (int n = 0; n < noutput / M; n++) {
+        for (int i = 0; i < nin; i++)
+            fin[map[i]] = in_streams[i][n];
+        plan_exec(&plan, fin, fout);
+        for (int f = 0; f < NF; f++) {
+            const int src = tw == 1 ? f : (f < M ? state * M + f : (state ^ 1) * M + (f - M));
+            memmove(dl + (size_t)f * T + 1, dl + (size_t)f * T, sizeof(cf32) * (size_t)(T - 1));
+            dl[(size_t)f * T] = fout[src];
+        }
+        for (int i = 0; i < M; i++) {
+            float re = 0.0f, im = 0.0f;
+            for (int j = T - 1; j >= 0; j--) { /* oldest first, like the reversed-tap dot product */
+                re += dl[(size_t)i * T + j].re * ft[i * T + j];
+                im += dl[(size_t)i * T + j].im * ft[i * T + j];
+            }
+            if (tw == 2) {
+                float re2 = 0.0f, im2 = 0.0f;
+                for (int j = T - 1; j >= 0; j--) {
+                    re2 += dl[(size_t)(M + i) * T + j].re * ft[(M + i) * T + j];
+                    im2 += dl[(size_t)(M + i) * T + j].im * ft[(M + i) * T + j];
+                }
+                re += re2;
+                im += im2;
+            }
+            out[(size_t)n * M + i].re = re;
+            out[(size_t)n * M + i].im = im;
+        }
+        state ^= 1;
+    }
+    free(ft);
+    free(map);
+    free(fin);
+    free(fout);
+    free(dl);
+    plan_free(&plan);
+    return noutput;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * filterbank_vcvcf_impl::general_work (gr-filter/lib/filterbank_vcvcf_impl.cc:54-96) over kernel::filterbank
+ * (gr-filter/lib/filterbank.cc:50-79): item = vector of nfilts complex; history ntaps+1;
+ * out[j][i] = sum_t rev_i[t] in[j+t][i]; a filter whose taps are all zero writes zeros without looking at its input.
+ * ---------------------------------------------------------------------------------------------- */
+int grbo_filterbank_vcvcf(int nfilts, int ntaps, const float* taps, const cf32* in, cf32* out, int nout)
+{
+    if (nfilts < 1 || ntaps < 1)
+        return -1;
+    for (int i = 0; i < nfilts; i++) {
+        const float* h = taps + (size_t)i * ntaps;
+        int active = 0;
+        for (int t = 0; t < ntaps; t++)
+            if (h[t] != 0)
+                active = 1;
+        for (int j = 0; j < nout; j++) {
+            float re = 0.0f, im = 0.0f;
+            if (active)
+                for (int t = 0; t < ntaps; t++) {
+                    const cf32 x = in[(size_t)(j + t) * nfilts + i];
+                    re += x.re * h[ntaps - 1 - t];
+                    im += x.im * h[ntaps - 1 - t];
+                }
+            out[(size_t)j * nfilts + i].re = re;
+            out[(size_t)j * nfilts + i].im = im;
+        }
+    }
+    return nout;
+}

@@ -252,6 +252,87 @@ class _CLib:
         self._f("mag_squared")(_p(x), _p(out), C.c_long(len(x)))
         return out
 
+    # -- fir_filter_fff ------------------------------------------------------------------------------
+    def fir_fff(self, decim, taps, xin, nout):
+        """fir_filter_fff work(): xin carries ntaps-1 history floats in front."""
+        t = np.ascontiguousarray(taps, np.float32)
+        buf = np.zeros(len(xin) + 16, np.float32)  # headroom in front: filter() rounds its pointer down
+        buf[16:] = np.asarray(xin, np.float32)
+        x = buf[16:]
+        assert len(x) >= nout * decim + len(t) - 1
+        out = np.empty(nout, np.float32)
+        rc = self._f("fir_fff")(int(decim), _p(t), len(t), _p(x), _p(out), C.c_long(nout))
+        assert rc == 0
+        return out
+
+    # -- fft_vfc -------------------------------------------------------------------------------------
+    def fft_vfc(self, fft_size, forward, window, x):
+        x = np.ascontiguousarray(x, np.float32)
+        nvec = len(x) // fft_size
+        out = np.empty(nvec * fft_size, np.complex64)
+        if window is None or len(window) == 0:
+            w, nw = None, 0
+        else:
+            wa = np.ascontiguousarray(window, np.float32)
+            w, nw = _p(wa), len(wa)
+        rc = self._f("fft_vfc")(int(fft_size), int(bool(forward)), w, nw, _p(x), _p(out), C.c_long(nvec))
+        if rc != 0:
+            raise RuntimeError("fft_vfc: window not the same length as fft_size")
+        return out
+
+    # -- logpwrfft_c / logpwrfft_f ---------------------------------------------------------------------
+    def logpwrfft(self, complex_input, fft_size, ref_scale, decim, avg_alpha, average, window, x, count=None, iir=None):
+        """The whole hier block over the stream x.  count / iir: keep_one_in_n counter and filter memory to continue from
+        (None = a fresh block).  Returns (frames [nout, fft_size] float32, count, iir)."""
+        x = np.ascontiguousarray(x, np.complex64 if complex_input else np.float32)
+        w = np.ascontiguousarray(window, np.float32)
+        assert len(w) == fft_size
+        nvec = len(x) // fft_size
+        out = np.empty((max(nvec, 1), fft_size), np.float32)
+        cnt = C.c_int(int(decim) if count is None else int(count))
+        st = np.zeros(fft_size, np.float32) if iir is None else np.array(iir, np.float32)
+        fn = self._f("logpwrfft")
+        fn.restype = C.c_long
+        n = fn(int(bool(complex_input)), int(fft_size), C.c_double(ref_scale), int(decim), C.c_double(avg_alpha),
+               int(bool(average)), _p(w), _p(x), C.c_long(len(x)), _p(out), C.c_long(nvec), C.byref(cnt), _p(st))
+        if n < 0:
+            raise ValueError("logpwrfft oracle error %d" % n)
+        return out[:n].copy(), cnt.value, st
+
+    # -- pfb_synthesizer_ccf -------------------------------------------------------------------------
+    def pfb_synthesizer(self, numchans, taps, twox, in_streams, channel_map=None, chunk=0):
+        """A fresh block fed in_streams [nin][n]: returns n*numchans output items (ValueError on ctor/map errors)."""
+        t = np.ascontiguousarray(taps, np.float32)
+        ins = np.ascontiguousarray(in_streams, np.complex64)
+        nin, n = ins.shape
+        out = np.zeros(n * numchans, np.complex64)
+        inp = (C.c_void_p * nin)(*[ins[j].ctypes.data for j in range(nin)])
+        if channel_map is None:
+            cm, ncm = None, 0
+        else:
+            cma = np.ascontiguousarray(channel_map, np.int32)
+            cm, ncm = _p(cma), len(cma)
+        rc = self._f("pfb_synthesizer_ccf")(C.c_uint(numchans), _p(t), len(t), int(bool(twox)), cm, ncm, inp, nin, _p(out),
+                                            int(n * numchans), int(chunk))
+        if rc < 0:
+            raise ValueError("pfb_synthesizer_ccf oracle error %d" % rc)
+        return out
+
+    # -- filterbank_vcvcf ----------------------------------------------------------------------------
+    def filterbank(self, taps, xin, nout):
+        """taps [nfilts][ntaps]; xin: (nout + ntaps) vectors of nfilts items, history (ntaps vectors) first."""
+        t = np.ascontiguousarray(taps, np.float32)
+        nfilts, ntaps = t.shape
+        pad = np.zeros(len(np.asarray(xin).reshape(-1)) + 8 * nfilts, np.complex64)
+        pad[8 * nfilts:] = np.asarray(xin, np.complex64).reshape(-1)
+        x = pad[8 * nfilts:]
+        assert len(x) >= (nout + ntaps) * nfilts
+        out = np.empty(nout * nfilts, np.complex64)
+        rc = self._f("filterbank_vcvcf")(int(nfilts), int(ntaps), _p(t), _p(x), _p(out), int(nout))
+        if rc < 0:
+            raise ValueError("filterbank_vcvcf oracle error %d" % rc)
+        return out.reshape(nout, nfilts)
+
     # -- window / firdes ---------------------------------------------------------------------------
     def window(self, wtype, ntaps, beta=6.76):
         out = np.empty(ntaps, np.float32)
@@ -428,6 +509,77 @@ def f64_fft_vcc(fft_size, forward, window, shift, x):
             v = np.fft.ifftshift(v, axes=1)
         y = np.fft.ifft(v, axis=1) * N
     return y.reshape(-1)
+
+
+def f64_fft_vfc(fft_size, forward, window, x):
+    return f64_fft_vcc(fft_size, forward, window, False, np.asarray(x, np.float64).astype(np.complex128))
+
+
+def f64_logpwrfft(complex_input, fft_size, ref_scale, decim, avg_alpha, average, window, x, count=None, iir=None):
+    """logpwrfft in float64 (gr-fft/python/fft/logpwrfft.py:29-64): every decim-th vector (the LAST of each group,
+    keep_one_in_n_impl.cc:66-74) -> window -> FFT -> |.|^2 -> y = a x + (1-a) y -> 10 log10(y) + k."""
+    N = fft_size
+    w = np.asarray(window, np.float64)
+    v = np.asarray(x, np.complex128 if complex_input else np.float64)
+    v = v[: (len(v) // N) * N].reshape(-1, N)
+    cnt = decim if count is None else count
+    keep = []
+    for i in range(len(v)):
+        cnt -= 1
+        if cnt <= 0:
+            keep.append(i)
+            cnt = decim
+    p = np.abs(np.fft.fft(v[keep] * w[None, :], axis=1)) ** 2
+    a = avg_alpha if average else 1.0
+    y = np.zeros(N) if iir is None else np.asarray(iir, np.float64).copy()
+    out = np.empty_like(p)
+    for j in range(len(p)):
+        y = a * p[j] + (1 - a) * y
+        out[j] = y
+    k = -20 * np.log10(N) - 10 * np.log10(np.sum(w * w) / N) - 20 * np.log10(ref_scale / 2)
+    return 10 * np.log10(np.maximum(out, np.finfo(np.float32).tiny)) + k
+
+
+def f64_pfb_synthesizer(numchans, taps, twox, in_streams, channel_map=None):
+    """Closed form of pfb_synthesizer_ccf_impl::work (:221-284) from a zero state:
+    V_q[m] = sum_i X_i[m] e^{+j 2 pi map[i] q / (tw M)};  out[n M + i] = sum_j h[i + j M] V_{q(n,i)}[n - j],
+    q = i (1x);  q = (((n+1) mod 2) M + i) (2x: the filter pair of branch i reads the IFFT half that alternates with n)."""
+    M = numchans
+    tw = 2 if twox else 1
+    X = np.asarray(in_streams, np.complex128)
+    nin, n = X.shape
+    cmap = np.arange(tw * M) if channel_map is None else np.asarray(channel_map)
+    NF = tw * M
+    F = np.zeros((n, NF), np.complex128)
+    for i in range(nin):
+        F[:, cmap[i]] = X[i]  # a later stream overwrites an earlier one mapped to the same bin (:236-239)
+    V = np.fft.ifft(F, axis=1) * NF  # [time][q]
+    T = -(-len(taps) // M)
+    h = np.zeros(M * T)
+    h[: len(taps)] = np.asarray(taps, np.float64)
+    out = np.zeros((n, M), np.complex128)
+    for j in range(T):
+        hj = h[j * M: (j + 1) * M]
+        if tw == 1:
+            out[j:] += hj[None, :] * V[: n - j, :M]
+        else:
+            for par in (0, 1):
+                rows = np.arange(j, n)
+                rows = rows[(rows % 2) == par]
+                half = ((par + 1) % 2) * M
+                out[rows] += hj[None, :] * V[rows - j, half: half + M]
+    return out.reshape(-1)
+
+
+def f64_filterbank(taps, xin, nout):
+    """out[j][i] = sum_k taps[i][k] xin[j + ntaps-1-k][i] (filterbank_vcvcf_impl.cc:73-82)."""
+    t = np.asarray(taps, np.float64)
+    nfilts, ntaps = t.shape
+    x = np.asarray(xin, np.complex128).reshape(-1, nfilts)
+    out = np.zeros((nout, nfilts), np.complex128)
+    for k in range(ntaps):
+        out += t[None, :, k] * x[ntaps - 1 - k: ntaps - 1 - k + nout]
+    return out
 
 
 def nrms(a, ref):

@@ -3,7 +3,8 @@
  * C entry points around the REAL reference kernel classes, which oracle/Makefile compiles
  * unmodified from /root/reference into oracle/_ref/libgrref.so:
  *   gr-filter/lib/fir_filter.cc, gr-filter/lib/fft_filter.cc, gr-filter/lib/polyphase_filterbank.cc,
- *   gr-filter/lib/firdes.cc, gr-fft/lib/window.cc.
+ *   gr-filter/lib/firdes.cc, gr-fft/lib/window.cc, gr-filter/lib/fir_filter_with_buffer.cc, gr-filter/lib/filterbank.cc
+ *   (+ the header-only gr-filter/include/gnuradio/filter/single_pole_iir.h).
  * The block shells (work()/general_work()) depend on gr::block (Boost/PMT/GMP, absent here) and are
  * restated below next to the reference file:line each loop follows.  Third-party arithmetic comes
  * from oracle/shim (generic-C VOLK stand-ins, own FFT engine in place of FFTW3f).
@@ -12,7 +13,10 @@
 #include <gnuradio/fft/fft.h>
 #include <gnuradio/fft/window.h>
 #include <gnuradio/filter/fft_filter.h>
+#include <gnuradio/filter/filterbank.h>
 #include <gnuradio/filter/fir_filter.h>
+#include <gnuradio/filter/fir_filter_with_buffer.h>
+#include <gnuradio/filter/single_pole_iir.h>
 #include <gnuradio/filter/firdes.h>
 #include <gnuradio/filter/polyphase_filterbank.h>
 #include <gnuradio/expj.h>
@@ -21,6 +25,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <limits>
 #include <stdexcept>
 #include <vector>
 
@@ -149,9 +154,316 @@ struct decimator_shell : public gr::filter::kernel::polyphase_filterbank {
     }
 };
 
+/* pfb_synthesizer_ccf_impl (gr-filter/lib/pfb_synthesizer_ccf_impl.cc) without the runtime: the members and the three
+ * methods set_taps1 (:95-129), set_taps2 (:131-184) and work (:221-284) restated over the reference's own
+ * kernel::fir_filter_with_buffer_ccf (compiled from its source) and the shim fft_complex. */
+struct synthesizer_shell {
+    unsigned int d_numchans, d_twox, d_taps_per_filter;
+    int d_state;
+    std::vector<gr::filter::kernel::fir_filter_with_buffer_ccf*> d_filters;
+    std::vector<std::vector<float>> d_taps;
+    std::vector<int> d_channel_map;
+    gr::fft::fft_complex* d_fft;
+
+    synthesizer_shell(unsigned int numchans, const std::vector<float>& taps, bool twox) : d_numchans(numchans), d_state(0)
+    {
+        d_twox = twox ? 2 : 1; /* :42-47 */
+        if (d_numchans % d_twox != 0)
+            throw std::invalid_argument("pfb_synthesizer_ccf_impl: number of channels must be even for 2x oversampling.");
+        d_filters.resize(d_twox * d_numchans);
+        d_channel_map.resize(d_twox * d_numchans);
+        std::vector<float> vtaps(0, d_twox * d_numchans); /* :55 (sic: an empty vector) */
+        for (unsigned int i = 0; i < d_twox * d_numchans; i++) {
+            d_filters[i] = new gr::filter::kernel::fir_filter_with_buffer_ccf(vtaps);
+            d_channel_map[i] = i;
+        }
+        if (d_twox == 1)
+            set_taps1(taps);
+        else
+            set_taps2(taps);
+        d_fft = new gr::fft::fft_complex(d_twox * d_numchans, false); /* :65-66 */
+        std::fill_n(d_fft->get_inbuf(), d_twox * d_numchans, 0);
+    }
+    ~synthesizer_shell()
+    {
+        delete d_fft;
+        for (auto f : d_filters)
+            delete f;
+    }
+    void set_taps1(const std::vector<float>& taps)
+    {
+        unsigned int ntaps = taps.size();
+        d_taps_per_filter = (unsigned int)ceil((double)ntaps / (double)d_numchans);
+        d_taps.resize(d_numchans);
+        std::vector<float> tmp_taps = taps;
+        while ((float)(tmp_taps.size()) < d_numchans * d_taps_per_filter)
+            tmp_taps.push_back(0.0);
+        for (unsigned int i = 0; i < d_numchans; i++) {
+            d_taps[i] = std::vector<float>(d_taps_per_filter, 0);
+            for (unsigned int j = 0; j < d_taps_per_filter; j++)
+                d_taps[i][j] = tmp_taps[i + j * d_numchans];
+            d_filters[i]->set_taps(d_taps[i]);
+        }
+    }
+    void set_taps2(const std::vector<float>& taps)
+    {
+        unsigned int ntaps = taps.size();
+        d_taps_per_filter = (unsigned int)ceil((double)ntaps / (double)d_numchans);
+        d_taps.resize(d_twox * d_numchans);
+        std::vector<float> tmp_taps = taps;
+        while ((float)(tmp_taps.size()) < d_numchans * d_taps_per_filter)
+            tmp_taps.push_back(0.0);
+        for (unsigned int i = 0; i < d_numchans; i++) {
+            d_taps[i] = std::vector<float>(d_taps_per_filter, 0);
+            d_taps[d_numchans + i] = std::vector<float>(d_taps_per_filter, 0);
+            int state = 0;
+            for (unsigned int j = 0; j < d_taps_per_filter; j++) {
+                if (state == 0) {
+                    d_taps[i][j] = 0;
+                    d_taps[d_numchans + i][j] = tmp_taps[i + j * d_numchans];
+                    state = 1;
+                } else {
+                    d_taps[i][j] = tmp_taps[i + j * d_numchans];
+                    d_taps[d_numchans + i][j] = 0;
+                    state = 0;
+                }
+            }
+            d_filters[i]->set_taps(d_taps[i]);
+            d_filters[d_numchans + i]->set_taps(d_taps[d_numchans + i]);
+        }
+    }
+    int set_channel_map(const std::vector<int>& map)
+    { /* :202-217 */
+        if (!map.empty()) {
+            int mx = *std::max_element(map.begin(), map.end());
+            int mn = *std::min_element(map.begin(), map.end());
+            if ((mx >= static_cast<int>(d_twox * d_numchans)) || (mn < 0))
+                return -2;
+            d_channel_map = map;
+            std::fill_n(d_fft->get_inbuf(), d_twox * d_numchans, 0);
+        }
+        return 0;
+    }
+    int work(int noutput_items, const gr_complex* const* input_items, size_t ninputs, size_t in_off, gr_complex* out)
+    { /* :221-284 */
+        unsigned int n, i;
+        if (d_twox == 1) {
+            for (n = 0; n < noutput_items / d_numchans; n++) {
+                for (i = 0; i < ninputs; i++)
+                    d_fft->get_inbuf()[d_channel_map[i]] = input_items[i][in_off + n];
+                d_fft->execute();
+                for (i = 0; i < d_numchans; i++)
+                    out[i] = d_filters[i]->filter(d_fft->get_outbuf()[i]);
+                out += d_numchans;
+            }
+        } else {
+            for (n = 0; n < noutput_items / d_numchans; n++) {
+                for (i = 0; i < ninputs; i++)
+                    d_fft->get_inbuf()[d_channel_map[i]] = input_items[i][in_off + n];
+                d_fft->execute();
+                for (i = 0; i < d_numchans; i++) {
+                    out[i] = d_filters[i]->filter(d_fft->get_outbuf()[d_state * d_numchans + i]);
+                    out[i] += d_filters[d_numchans + i]->filter(d_fft->get_outbuf()[(d_state ^ 1) * d_numchans + i]);
+                }
+                d_state ^= 1;
+                out += d_numchans;
+            }
+        }
+        return noutput_items;
+    }
+};
+
+/* filterbank_vcvcf_impl::general_work (gr-filter/lib/filterbank_vcvcf_impl.cc:54-96) over the reference's own
+ * kernel::filterbank (gr-filter/lib/filterbank.cc, compiled from its source). */
+struct filterbank_shell : public gr::filter::kernel::filterbank {
+    explicit filterbank_shell(const std::vector<std::vector<float>>& taps) : filterbank(taps) {}
+    unsigned int ntaps() const { return d_ntaps; }
+    int work(int noutput_items, const gr_complex* in, gr_complex* out)
+    {
+        std::vector<gr_complex> working_v(noutput_items + d_ntaps + 16);
+        gr_complex* working = working_v.data() + 8; /* headroom: filter() rounds its pointer down (fir_filter.cc:133-141) */
+        for (unsigned int i = 0; i < d_nfilts; i++) {
+            if (d_active[i]) {
+                for (unsigned int j = 0; j < noutput_items + d_ntaps - 1; j++)
+                    working[j] = in[i + j * d_nfilts];
+                for (unsigned int j = 0; j < (unsigned int)(noutput_items); j++)
+                    out[i + j * d_nfilts] = d_fir_filters[i]->filter(working + j);
+            } else {
+                for (unsigned int j = 0; j < (unsigned int)(noutput_items); j++)
+                    out[i + j * d_nfilts] = 0;
+            }
+        }
+        return noutput_items;
+    }
+};
+
 } // namespace
 
 extern "C" {
+
+/* fir_filter_blk_impl<float,float,float>::work over kernel::fir_filter<float,float,float> (gr-filter/lib/fir_filter.cc:122-130,
+ * volk_32f_x2_dot_prod_32f_a): fir_filter_fff.  in[] holds nout*decim + ntaps-1 floats. */
+int grref_fir_fff(int decim, const float* taps, int ntaps, const float* in, float* out, long nout)
+{
+    std::vector<float> t(taps, taps + ntaps);
+    gr::filter::kernel::fir_filter_fff fir(decim, t);
+    if (decim == 1)
+        fir.filterN(out, in, (unsigned long)nout);
+    else
+        fir.filterNdec(out, in, (unsigned long)nout, decim);
+    return 0;
+}
+
+/* fft_vfc_fftw::work (gr-fft/lib/fft_vfc_fftw.cc:57-92) restated over the shim fft_complex. */
+int grref_fft_vfc(int fft_size, int forward, const float* window, int nwindow, const float* in, void* out_, long nvec)
+{
+    if (!(nwindow == 0 || nwindow == fft_size))
+        return -1; /* ctor throws: fft_vfc_fftw.cc:40-41 */
+    gr::fft::fft_complex fft(fft_size, forward != 0, 1);
+    gr_complex* out = (gr_complex*)out_;
+    const unsigned int N = (unsigned int)fft_size;
+    for (long count = 0; count < nvec; count++) {
+        gr_complex* dst = fft.get_inbuf();
+        if (nwindow) {
+            for (unsigned int i = 0; i < N; i++)
+                dst[i] = in[i] * window[i];
+        } else {
+            for (unsigned int i = 0; i < N; i++)
+                dst[i] = in[i];
+        }
+        fft.execute();
+        memcpy(out, fft.get_outbuf(), sizeof(gr_complex) * N);
+        in += N;
+        out += N;
+    }
+    return 0;
+}
+
+/* The logpwrfft_c / logpwrfft_f hier block (gr-fft/python/fft/logpwrfft.py:29-64) as one function: the chain
+ *   stream_to_vector (gr-blocks/lib/stream_to_vector_impl.cc:46-58) -> keep_one_in_n (gr-blocks/lib/keep_one_in_n_impl.cc:56-77)
+ *   -> fft_vcc / fft_vfc (forward, window, no shift) -> complex_to_mag_squared -> single_pole_iir_filter_ff
+ *   (gr-filter/lib/single_pole_iir_filter_ff_impl.cc:47-67 over the reference's own single_pole_iir.h) -> nlog10_ff
+ *   (gr-blocks/lib/nlog10_ff_impl.cc:28-60).
+ * in: nitems stream items (float or gr_complex); whole vectors only are consumed.  count_state: keep_one_in_n's d_count
+ * (in/out; a fresh block starts at n).  iir_state: fft_size floats, d_prev_output of every bin (in/out; zeros at start).
+ * Returns the number of output vectors written (at most max_out), <0 on error. */
+long grref_logpwrfft(int complex_input, int fft_size, double ref_scale, int decim, double avg_alpha, int average,
+                     const float* window, const void* in_, long nitems, float* out, long max_out, int* count_state,
+                     float* iir_state)
+{
+    if (decim < 1 || fft_size < 1)
+        return -1;
+    const unsigned int N = (unsigned int)fft_size;
+    gr::fft::fft_complex fft(fft_size, true, 1);
+    /* logpwrfft.py:47-60 (Python float arithmetic = double) */
+    double window_power = 0;
+    for (unsigned int i = 0; i < N; i++)
+        window_power += (double)window[i] * (double)window[i];
+    const double kd = -20 * log10((double)fft_size) - 10 * log10(window_power / fft_size) - 20 * log10(ref_scale / 2);
+    /* nlog10_ff_impl ctor, :28-36: float n, float k */
+    const float n = 10.0f, k = (float)kd;
+    const float d_n_log2_10 = n / log2f(10.0f);
+    const float d_10_k_n = std::pow(10.0f, k / n);
+    /* single_pole_iir<float,float,double> (single_pole_iir.h): d_prev_output is private with no setter, so to carry the state
+     * across calls every bin's filter is primed by one filter() call with alpha = 1 (which stores its input, :82-83) and
+     * then switched to the working alpha (set_average, logpwrfft.py:101-113). */
+    std::vector<gr::filter::single_pole_iir<float, float, double>> iir(N);
+    for (unsigned int i = 0; i < N; i++) {
+        iir[i].set_taps(1.0);
+        iir[i].filter(iir_state[i]);
+        iir[i].set_taps(average ? avg_alpha : 1.0);
+    }
+    const long nvec_in = nitems / N;
+    long no = 0;
+    std::vector<float> p(N);
+    constexpr float float_min = std::numeric_limits<float>::min();
+    for (long ni = 0; ni < nvec_in && no < max_out; ni++) {
+        (*count_state)--;
+        if (*count_state > 0)
+            continue;
+        *count_state = decim;
+        gr_complex* dst = fft.get_inbuf();
+        if (complex_input) { /* fft_vcc_fftw.cc:78-100, forward, no shift */
+            const gr_complex* x = (const gr_complex*)in_ + ni * N;
+            volk_32fc_32f_multiply_32fc(dst, x, window, N);
+        } else { /* fft_vfc_fftw.cc:70-74 */
+            const float* x = (const float*)in_ + ni * N;
+            for (unsigned int i = 0; i < N; i++)
+                dst[i] = x[i] * window[i];
+        }
+        fft.execute();
+        volk_32fc_magnitude_squared_32f(p.data(), fft.get_outbuf(), N);
+        float* o = out + no * N;
+        for (unsigned int i = 0; i < N; i++) {
+            float y = iir[i].filter(p[i]); /* the reference's own class: double arithmetic, float state (single_pole_iir.h:78-86) */
+            /* nlog10_ff_impl::work :47-58 (volk_32f_log2_32f generic = log2f) */
+            float v = std::max(y, float_min);
+            if (d_10_k_n != 1.0f)
+                v = v * d_10_k_n;
+            o[i] = log2f(v) * d_n_log2_10;
+        }
+        no++;
+    }
+    for (unsigned int i = 0; i < N; i++)
+        iir_state[i] = iir[i].prev_output();
+    return no;
+}
+
+/* pfb_synthesizer_ccf: a fresh block, optional channel map, work() over `chunk` output items per call (0 = one call; the
+ * filters' internal buffers carry the state between calls).  in_streams[i]: noutput/numchans items each. */
+int grref_pfb_synthesizer_ccf(unsigned int numchans, const float* taps, int ntaps, int twox, const int* channel_map, int nmap,
+                              const void* const* in_streams, int nin, void* out_, int noutput, int chunk)
+{
+    try {
+        std::vector<float> t(taps, taps + ntaps);
+        synthesizer_shell sh(numchans, t, twox != 0);
+        if (nmap > 0) {
+            int rc = sh.set_channel_map(std::vector<int>(channel_map, channel_map + nmap));
+            if (rc)
+                return rc;
+        }
+        if (noutput % (int)numchans != 0)
+            return -3; /* set_output_multiple(d_numchans), :68 */
+        if (chunk <= 0)
+            chunk = noutput;
+        chunk = std::max<int>(numchans, (chunk / (int)numchans) * (int)numchans);
+        gr_complex* out = (gr_complex*)out_;
+        for (int o = 0; o < noutput; o += chunk) {
+            const int n = std::min(chunk, noutput - o);
+            sh.work(n, (const gr_complex* const*)in_streams, (size_t)nin, (size_t)(o / numchans), out + o);
+        }
+        return noutput;
+    } catch (const std::invalid_argument&) {
+        return -1;
+    }
+}
+int grref_pfb_synthesizer_taps(unsigned int numchans, const float* taps, int ntaps, int twox, float* out /*[twox*numchans][T]*/)
+{
+    try {
+        std::vector<float> t(taps, taps + ntaps);
+        synthesizer_shell sh(numchans, t, twox != 0);
+        for (size_t i = 0; i < sh.d_taps.size(); i++)
+            memcpy(out + i * sh.d_taps_per_filter, sh.d_taps[i].data(), sizeof(float) * sh.d_taps_per_filter);
+        return (int)sh.d_taps_per_filter;
+    } catch (const std::invalid_argument&) {
+        return -1;
+    }
+}
+
+/* filterbank_vcvcf: one general_work() call.  taps: [nfilts][ntaps] row-major; in: (nout + ntaps) vectors of nfilts items
+ * (history = ntaps + 1, filterbank_vcvcf_impl.cc:34); out: nout vectors. */
+int grref_filterbank_vcvcf(int nfilts, int ntaps, const float* taps, const void* in, void* out, int nout)
+{
+    try {
+        std::vector<std::vector<float>> t((size_t)nfilts);
+        for (int i = 0; i < nfilts; i++)
+            t[i].assign(taps + (size_t)i * ntaps, taps + (size_t)(i + 1) * ntaps);
+        filterbank_shell fb(t);
+        return fb.work(nout, (const gr_complex*)in, (gr_complex*)out);
+    } catch (const std::exception&) {
+        return -1;
+    }
+}
 
 /* pfb_decimator_ccf.  state: pass a pointer to a null void* for the first call and the same pointer afterwards to keep
  * the FFT filters' overlap across calls (mode bit 1); free it with grref_pfb_decimator_free.  Returns n, <0 on error. */

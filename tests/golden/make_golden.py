@@ -5,7 +5,8 @@
                      gr-fft/python/fft/qa_fft.py (32-point primes FFT, Hamming-windowed, reverse+window+shift),
                      gr-blocks/python/blocks/qa_type_conversions.py:129-137 (complex_to_mag_squared).
   ref_fixtures.npz   outputs of oracle/_ref/libgrref.so -- the reference's OWN fir_filter.cc, fft_filter.cc,
-                     polyphase_filterbank.cc, firdes.cc, window.cc compiled unmodified -- on seeded inputs.
+                     polyphase_filterbank.cc, firdes.cc, window.cc, fir_filter_with_buffer.cc, filterbank.cc (and the
+                     header-only single_pole_iir.h) compiled unmodified -- on seeded inputs.
                      Inputs are stored next to the outputs so the fixtures stand alone on the GPU box.
 
     python tests/golden/make_golden.py
@@ -154,6 +155,34 @@ def ref_fixtures():
     fx["resamp_taps_c"] = crand(rng5, 33)
     fx["resamp_ccf_4_7"] = R.rational_resampler(4, 7, fx["resamp_taps_f"], fx["resamp_x"])[0]
     fx["resamp_ccc_3_2"] = R.rational_resampler(3, 2, fx["resamp_taps_c"], fx["resamp_x"])[0]
+    # ---- round 2: fir_filter_fff, fft_vfc, logpwrfft, pfb_synthesizer_ccf, filterbank_vcvcf (own generator again) ----
+    rng6 = np.random.default_rng(20261109)
+    fx["fff_x"] = rng6.uniform(-1, 1, 4000).astype(np.float32)
+    fx["fff_taps"] = rng6.uniform(-1, 1, 101).astype(np.float32)
+    for D in (1, 3):
+        xin = np.concatenate([np.zeros(100, np.float32), fx["fff_x"]])
+        fx["fff_d%d" % D] = R.fir_fff(D, fx["fff_taps"], xin, len(fx["fff_x"]) // D)
+    fx["vfc_x"] = rng6.uniform(-1, 1, 64 * 5).astype(np.float32)
+    fx["vfc64_f1_w"] = R.fft_vfc(64, True, fx["win_bh_64"], fx["vfc_x"])
+    fx["vfc64_f0"] = R.fft_vfc(64, False, None, fx["vfc_x"])
+    fx["logpwr_xc"] = crand(rng6, 64 * 37)
+    fx["logpwr_xf"] = rng6.uniform(-1, 1, 64 * 37).astype(np.float32)
+    fx["logpwr_c_d3_avg"] = R.logpwrfft(True, 64, 2.0, 3, 0.25, True, fx["win_bh_64"], fx["logpwr_xc"])[0]
+    fx["logpwr_c_d1"] = R.logpwrfft(True, 64, 2.0, 1, 1.0, False, fx["win_bh_64"], fx["logpwr_xc"])[0]
+    fx["logpwr_f_d2_avg"] = R.logpwrfft(False, 64, 1.0, 2, 0.1, True, fx["win_bh_64"], fx["logpwr_xf"])[0]
+    fx["synth_taps"] = R.low_pass_2(5, 5000, 500, 100, 80, 5)  # qa_pfb_synthesizer.py:39-41
+    fx["synth_in5"] = crand(rng6, 5 * 400).reshape(5, 400)
+    fx["synth_5_1x"] = R.pfb_synthesizer(5, fx["synth_taps"], False, fx["synth_in5"])
+    fx["synth_map"] = np.array([3, 0, 4], np.int32)
+    fx["synth_5_1x_map3"] = R.pfb_synthesizer(5, fx["synth_taps"], False, fx["synth_in5"][:3], channel_map=fx["synth_map"])
+    fx["synth_in8"] = crand(rng6, 8 * 300).reshape(8, 300)
+    fx["synth_taps8"] = rng6.uniform(-1, 1, 8 * 7 - 3).astype(np.float32)
+    fx["synth_8_2x"] = R.pfb_synthesizer(8, fx["synth_taps8"], True, fx["synth_in8"])
+    fx["fbank_taps"] = rng6.uniform(-1, 1, (10, 5)).astype(np.float32)
+    fx["fbank_taps"][3] = 0
+    fx["fbank_taps"][7] = 0
+    fx["fbank_x"] = crand(rng6, 10 * (200 + 5))
+    fx["fbank_out"] = R.filterbank(fx["fbank_taps"], fx["fbank_x"], 200)
     return fx
 
 
