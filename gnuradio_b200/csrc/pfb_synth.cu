@@ -213,7 +213,10 @@ static int launch_synth(const CUtensorMap& tmap, void* out, long long ntimes, in
     if (nruns * min_region > ntimes)
         nruns = (ntimes + min_region - 1) / min_region;
     nruns = ((nruns + Geo::NG - 1) / Geo::NG) * Geo::NG;
-    const long long region = (ntimes + nruns - 1) / nruns;
+    // whole KT-column boxes per run: every TMA box then starts on a 128-byte boundary of its stream (the tensor copy wants
+    // the box start 16-byte aligned; an odd item index is not)
+    long long region = (ntimes + nruns - 1) / nruns;
+    region = ((region + Geo::KT - 1) / Geo::KT) * Geo::KT;
     grid = ((ntimes + region - 1) / region + Geo::NG - 1) / Geo::NG; // drop CTAs the rounding left without work
     long long iters = (region + T - 1 + Geo::KT - 1) / Geo::KT;
     if (iters > 0x7fffffffLL / Geo::KT)

@@ -64,6 +64,9 @@ def test_fir_fff_tiles_ragged_ends_and_unaligned(grb, orc):
         x = rng.uniform(-1, 1, nout + nt - 1).astype(np.float32)
         got = blk.process(x, nout)
         k = min(nout, 30000)
+        if nout < 64:  # a handful of outputs: no RMS to speak of, compare against the size of the terms instead
+            np.testing.assert_allclose(got, orc.fir_fff(1, taps, x, nout), atol=1e-5 * np.sqrt(nt))
+            continue
         assert_parity(got[:k], orc.fir_fff(1, taps, x[: k + nt - 1], k), "head %d" % nout)
         assert_parity(got[-k:], orc.fir_fff(1, taps, x[nout - k:], k), "tail %d" % nout)
     n = 100000
@@ -159,12 +162,16 @@ def test_logpwrfft_against_oracle(grb, orc, cin, N, dec, avg, alpha, nvec):
     got = blk.process(x)
     ref, cnt, st = orc.logpwrfft(cin, N, 2.0, dec, alpha, avg, w, x)
     assert got.shape == ref.shape
-    # dB values: compare on the dB scale (absolute) -- 1e-3 dB -- and as powers at north_star's relative tolerance
-    assert np.abs(got - ref).max() < 2e-3, np.abs(got - ref).max()
+    # the block's output is a power in dB: north_star's tolerance applies to the power; on the dB scale every bin within
+    # 60 dB of the strongest must agree to 2e-3 dB (a bin in a deep null carries the transform's rounding floor, fp32 like the
+    # reference's -- there the two differ by what two fp32 FFTs differ)
     f64 = po.f64_logpwrfft(cin, N, 2.0, dec, alpha, avg, w, x)
-    assert np.abs(got - f64).max() < 2e-3
     pw = lambda d: 10.0 ** (np.asarray(d, np.float64) / 10.0)
-    assert_parity(pw(got), pw(f64), "power", 1e-5, 2e-4)
+    assert_parity(pw(got), pw(f64), "power vs f64", 1e-5, 2e-4)
+    assert_parity(pw(got), pw(ref), "power vs oracle", 1e-5, 2e-4)
+    strong = f64 > f64.max() - 60.0
+    assert np.abs(got - ref)[strong].max() < 2e-3, np.abs(got - ref)[strong].max()
+    assert np.abs(got - f64)[strong].max() < 2e-3
     # the stream handed over in scheduler-sized pieces: counter and filter memory carry on
     blk2 = cls(float(N * dec), N, 2.0, 1.0, alpha, avg, lambda n: w)
     parts, pos = [], 0
@@ -176,7 +183,8 @@ def test_logpwrfft_against_oracle(grb, orc, cin, N, dec, avg, alpha, nvec):
             break
     got2 = np.concatenate([p for p in parts if len(p)])
     assert got2.shape == got.shape
-    assert np.abs(got2 - ref).max() < 2e-3
+    assert_parity(pw(got2), pw(f64), "pieces: power vs f64", 1e-5, 2e-4)
+    assert np.abs(got2 - got)[strong].max() < 2e-3
 
 
 def test_logpwrfft_setters_and_limits(grb, orc):
