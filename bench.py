@@ -31,6 +31,29 @@ sys.path.insert(0, ROOT)
 HBM_FALLBACK_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md fallback
 
 
+def fp32_peak():
+    """FP32 (CUDA-core, packed FFMA2) peak in TFLOP/s measured on this pool by tools/ubench.cu (profiles/r1_ubench.json)."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r1_ubench.json")))
+        return 2.0 * float(d["ffma2_tfma_s"]), "measured (tools/ubench.cu packed-FFMA2 loop, profiles/r1_ubench.json)"
+    except Exception:
+        return 66.6, "measured in round 1 (tools/ubench.cu): 66.6 TFLOP/s"
+
+
+def roofline_entry(wl, kernel_ms, samples_per_launch, hbm_peak, hbm_src):
+    """The roofline object of one kernel launch: achieved = algorithmic bytes (or flops) per launch / mean launch time."""
+    gbs = wl.alg_bytes * samples_per_launch / (kernel_ms * 1e-3) / 1e9
+    tfl = wl.flops * samples_per_launch / (kernel_ms * 1e-3) / 1e12
+    fpk, fsrc = fp32_peak()
+    r = {"kernel": wl.kernel, "alg_bytes_per_sample": wl.alg_bytes, "alg_flops_per_sample": wl.flops,
+         "hbm_gbs": gbs, "hbm_frac": gbs / hbm_peak, "fp32_tflops": tfl, "fp32_frac": tfl / fpk}
+    if getattr(wl, "bound", "hbm") == "fp32":
+        r.update({"bound": "fp32", "achieved": tfl, "peak": fpk, "unit": "TFLOP/s", "frac": tfl / fpk, "peak_source": fsrc})
+    else:
+        r.update({"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak, "peak_source": hbm_src})
+    return r
+
+
 def measured_peaks():
     try:
         d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -260,6 +283,7 @@ class FftFilter(Workload):
     # two tap partitions on the 4096-point kernel: (2 x 5 N log2 N + 16 N) / (N/2) flops per output sample, N = 4096
     alg_bytes, flops, log2n, seed = 16.0, 272.0, 28, 2
     kernel = "fftfilt_upols_kernel"
+    bound = "fp32"  # ncu: DRAM 18 % busy, FMA pipe and issue slots ~50 % -- the butterflies bound it, not HBM
     ncu_dram_bytes_per_sample = (2.158e9 + 2.104e9) / (1 << 28)
     ncu_source = "profiles/r1_fftfilt_upols_ncu.txt"
     ntaps = 4096
@@ -343,6 +367,7 @@ class FreqXlating(FirCcf):
     block = "freq_xlating_fir_filter_ccf"
     alg_bytes, flops, log2n, seed = 8.0 + 8.0 / 8, 128.0, 28, 6  # one read per input item, one write per output item
     kernel = "fir_tiled_kernel + rotate_kernel"
+    bound = "fp32"  # complex composite taps with decimation run on the CUDA cores
     ntaps, decim, nsets = 128, 8, 1
 
     def setup(self):
@@ -413,8 +438,157 @@ class PfbDecimator(Workload):
         self.cpu_lay.pfb_decimator(self.M, self.cpu_taps, 5, self.cpu_x)
 
 
+class FirFff(Workload):
+    """fir_filter_fff, 256 taps -- the one block the reference holds published numbers for
+    (gnuradio-runtime/examples/mp-sched/perf-data/*.dat:2, BASELINE.md section 1: 14.2 - 18.4 Msps on 2007-8 CPUs)."""
+    name = "fir_filter_fff 256 taps decim 1, 2^%d float samples per GPU (section 8(f) row; mp-sched perf-data shape)"
+    block = "fir_filter_fff"
+    alg_bytes, flops, log2n, seed = 8.0, 512.0, 28, 8
+    kernel = "fir_fff_kernel"
+    bound = "fp32"
+    ntaps = 256
+
+    def setup(self):
+        self.taps = lowpass(self.ntaps, 0.1, blackman_harris(self.ntaps))
+        self.blk = self.grb.filter.fir_filter_fff(1, self.taps, device=self.device)
+        g = self.torch.Generator(device="cuda")
+        g.manual_seed(self.seed)
+        self.d_in = self.torch.empty(self.n + self.ntaps - 1, dtype=self.torch.float32, device="cuda")
+        self.d_in.uniform_(-1.0, 1.0, generator=g)
+        self.d_out = self.torch.empty(self.n, dtype=self.torch.float32, device="cuda")
+
+    def step(self):
+        self.blk.work_dev(self.d_in.data_ptr(), self.d_out.data_ptr(), self.n, self.stream)
+
+    def describe(self):
+        return self.name % self.log2n
+
+    def parity(self, sc):
+        f = lambda t: (lambda a, b: t[a:b].cpu().numpy())
+        return sc.fir_fff(f(self.d_in), f(self.d_out), 1, self.taps, self.n, width=1024, count=64, seed=self.seed)
+
+    def cpu_setup(self, lay, log2n):
+        rng = np.random.default_rng(self.seed)
+        n = 1 << log2n
+        self.cpu_x = rng.uniform(-1, 1, n + self.ntaps - 1).astype(np.float32)
+        self.cpu_lay, self.cpu_taps = lay, lowpass(self.ntaps, 0.1, blackman_harris(self.ntaps))
+        self.cpu_nout = n
+        return n
+
+    def cpu_call(self):
+        self.cpu_lay.fir_fff(1, self.cpu_taps, self.cpu_x, self.cpu_nout)
+
+
+class PfbSynthesizer(Workload):
+    """pfb_synthesizer_ccf 64 channels x 16 taps/branch (the channelizer transposed)."""
+    name = "pfb_synthesizer_ccf 64ch x 16 taps/branch, 2^%d output samples per GPU (section 8(f) row)"
+    block = "pfb_synthesizer_ccf"
+    alg_bytes, flops, log2n, seed = 16.0, 94.0, 28, 9
+    kernel = "pfb_synth_kernel"
+    M, T = 64, 16
+
+    def setup(self):
+        M, T = self.M, self.T
+        self.taps = lowpass(M * T, 0.5 / M, blackman_harris(M * T)) * np.float32(M)
+        self.blk = self.grb.filter.pfb_synthesizer_ccf(M, self.taps, False, device=self.device)
+        self.ntimes = self.n // M
+        self.stride = (self.ntimes + T - 1 + 1) & ~1
+        self.d_in = self.rand_c64(M * self.stride, self.seed)
+        self.d_out = self.torch.empty(2 * self.n, dtype=self.torch.float32, device="cuda")
+
+    def step(self):
+        self.blk.work_dev(self.d_in.data_ptr(), self.stride, self.M, self.d_out.data_ptr(), self.n, 0, self.stream)
+
+    def describe(self):
+        return self.name % self.log2n
+
+    def parity(self, sc):
+        xv, M = self.d_in.view(self.M, 2 * self.stride), self.M
+        return sc.pfb_synthesizer(lambda a, b: np.ascontiguousarray(xv[:, 2 * a: 2 * b].cpu().numpy()).view(np.complex64),
+                                  lambda a, b: self.d_out[2 * a * M: 2 * b * M].cpu().numpy().view(np.complex64),
+                                  M, self.taps, self.ntimes, width=64, count=64, seed=self.seed)
+
+    def cpu_setup(self, lay, log2n):
+        rng = np.random.default_rng(self.seed)
+        n = 1 << log2n
+        self.cpu_lay = lay
+        self.cpu_ins = (rng.uniform(-1, 1, (self.M, n // self.M)) + 1j * rng.uniform(-1, 1, (self.M, n // self.M))).astype(np.complex64)
+        self.cpu_taps = lowpass(self.M * self.T, 0.5 / self.M, blackman_harris(self.M * self.T)) * np.float32(self.M)
+        return n
+
+    def cpu_call(self):
+        self.cpu_lay.pfb_synthesizer(self.M, self.cpu_taps, False, self.cpu_ins)
+
+
+class Filterbank(Workload):
+    """filterbank_vcvcf 64 filters x 16 taps (the branch-FIR half of channelizer_hier_ccf)."""
+    name = "filterbank_vcvcf 64 filters x 16 taps, 2^%d samples per GPU (section 8(f) row)"
+    block = "filterbank_vcvcf"
+    alg_bytes, flops, log2n, seed = 16.0, 64.0, 28, 10
+    kernel = "filterbank_kernel"
+    M, T = 64, 16
+
+    def setup(self):
+        M, T = self.M, self.T
+        rng = np.random.default_rng(self.seed)
+        self.taps = rng.uniform(-1, 1, (M, T)).astype(np.float32)
+        self.blk = self.grb.filter.filterbank_vcvcf(self.taps, device=self.device)
+        self.nvec = self.n // M
+        self.d_in = self.rand_c64(M * (self.nvec + T), self.seed)
+        self.d_out = self.torch.empty(2 * self.n, dtype=self.torch.float32, device="cuda")
+
+    def step(self):
+        self.blk.work_dev(self.d_in.data_ptr(), self.d_out.data_ptr(), self.nvec, self.stream)
+
+    def describe(self):
+        return self.name % self.log2n
+
+    def parity(self, sc):
+        M = self.M
+        fi = lambda a, b: self.d_in[2 * a * M: 2 * b * M].cpu().numpy().view(np.complex64)
+        fo = lambda a, b: self.d_out[2 * a * M: 2 * b * M].cpu().numpy().view(np.complex64).reshape(-1, M)
+        return sc.filterbank(fi, fo, self.taps, self.nvec, width=64, count=64, seed=self.seed)
+
+    def cpu_setup(self, lay, log2n):
+        rng = np.random.default_rng(self.seed)
+        n = 1 << log2n
+        self.cpu_lay = lay
+        self.cpu_taps = rng.uniform(-1, 1, (self.M, self.T)).astype(np.float32)
+        self.cpu_nvec = n // self.M
+        self.cpu_x = (rng.uniform(-1, 1, n + self.M * self.T) + 1j * rng.uniform(-1, 1, n + self.M * self.T)).astype(np.complex64)
+        return n
+
+    def cpu_call(self):
+        self.cpu_lay.filterbank(self.cpu_taps, self.cpu_x, self.cpu_nvec)
+
+
+class LogPwrFft(Workload):
+    """logpwrfft_c 4096 bins, every frame kept (decimation 1), averaging on -- the worst case
+    for the averaging tail (normally one frame in tens is kept and the block's cost is the frames it reads)."""
+    name = "logpwrfft_c 4096 Blackman-Harris, decimation 1, avg_alpha 0.1, 2^%d samples per GPU (section 8(f) row)"
+    block = "logpwrfft_c"
+    alg_bytes, flops, log2n, seed = 12.0, 70.0, 28, 11
+    kernel = "fft_vcc_stream_kernel + logpwr_local/carry/fixup"
+    launches_per_step = 4
+    N = 4096
+
+    def setup(self):
+        N = self.N
+        self.blk = self.grb.fft.logpwrfft_c(float(N), N, 2.0, 1.0, 0.1, True, device=self.device)
+        self.nvec = self.n // N
+        self.d_in = self.rand_c64(self.n, self.seed)
+        self.d_out = self.torch.empty(self.n, dtype=self.torch.float32, device="cuda")
+
+    def step(self):
+        self.blk.work_dev(self.d_in.data_ptr(), self.n, self.d_out.data_ptr(), self.nvec, self.stream)
+
+    def describe(self):
+        return self.name % self.log2n
+
+
 WORKLOADS = {"pfb": PfbChannelizer, "fir": FirCcf, "fftfilt": FftFilter, "firdec": FirLongDecim, "fftvcc": FftVccMagSq,
-             "xlat": FreqXlating, "pfbdec": PfbDecimator}
+             "xlat": FreqXlating, "pfbdec": PfbDecimator, "firfff": FirFff, "pfbsynth": PfbSynthesizer, "fbank": Filterbank,
+             "logpwr": LogPwrFft}
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -715,7 +889,8 @@ def main():
                 others[key] = {"workload": o.describe(), "msps": sps * len(pr) / (tot * 1e-3) / 1e6,
                                "hbm_gbs": ach, "hbm_frac": ach / peak, "kernel_ms": kms,
                                "fp32_tflops": o.flops * sps / o.launches_per_step / (kms * 1e-3) / 1e12,
-                               "kernel": o.kernel, "parity": run_parity(torch, o)}
+                               "kernel": o.kernel, "roofline": roofline_entry(o, kms, sps / o.launches_per_step, peak, peak_src),
+                               "parity": run_parity(torch, o)}
                 o.free()
                 del o
             except Exception as e:  # a failing side config must not hide the headline

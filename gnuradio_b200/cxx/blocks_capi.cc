@@ -293,4 +293,106 @@ long long grbx_pfb_dec_run(unsigned decim, const float* taps, int ntaps, unsigne
     });
 }
 
+
+// fir_filter_fff: float stream
+long long grbx_fir_fff_run(int decim, const float* taps, int ntaps, const float* in, float* out, long long nout, int chunk)
+{
+    return guarded([&]() -> long long {
+        std::vector<float> t(taps, taps + ntaps);
+        auto b = gr::filter::fir_filter_fff::make(decim, t);
+        if (b->history() != (unsigned)ntaps || b->taps() != t || b->input_signature().item_size != 4)
+            throw std::logic_error("fir_filter_fff: history/taps/io_signature mismatch");
+        return run_sync(*b, (const char*)in, (char*)out, nout, chunk, 4, 4);
+    });
+}
+
+long long grbx_fft_vfc_run(int fft_size, int forward, const float* window, int nwindow, const float* in, void* out,
+                           long long nvec, int chunk)
+{
+    return guarded([&]() -> long long {
+        std::vector<float> w(window, window + nwindow);
+        auto b = gr::fft::fft_vfc::make(fft_size, forward != 0, w, 1);
+        return run_sync(*b, (const char*)in, (char*)out, nvec, chunk, (size_t)fft_size * 4, (size_t)fft_size * 8);
+    });
+}
+
+// pfb_synthesizer_ccf: in_streams[i] holds nout/numchans items; work() in chunks of `chunk` output items
+long long grbx_pfb_synth_run(unsigned numchans, const float* taps, int ntaps, int twox, const int* cmap, int ncmap,
+                             const void* const* in_streams, int nin, void* out, long long nout, int chunk)
+{
+    return guarded([&]() -> long long {
+        std::vector<float> t(taps, taps + ntaps);
+        auto b = gr::filter::pfb_synthesizer_ccf::make(numchans, t, twox != 0);
+        if (ncmap > 0) {
+            b->set_channel_map(std::vector<int>(cmap, cmap + ncmap));
+            if (b->channel_map() != std::vector<int>(cmap, cmap + ncmap))
+                throw std::logic_error("pfb_synthesizer_ccf: channel_map accessor mismatch");
+        }
+        if (b->output_multiple() != (int)numchans || b->history() != 1 || b->interpolation() != numchans)
+            throw std::logic_error("pfb_synthesizer_ccf: rate contract mismatch");
+        long long produced = 0;
+        int zero_calls = 0;
+        while (produced < nout) {
+            long long n = std::min<long long>(chunk, nout - produced);
+            n = n / numchans * numchans;
+            if (n == 0)
+                break;
+            gr_vector_const_void_star ii((size_t)nin);
+            for (int i = 0; i < nin; i++)
+                ii[i] = (const char*)in_streams[i] + (size_t)(produced / numchans) * 8;
+            gr_vector_void_star oo(1, (char*)out + (size_t)produced * 8);
+            gr_vector_int ni((size_t)nin, (int)(n / numchans));
+            int r = b->general_work((int)n, ni, ii, oo);
+            if (r < 0)
+                break;
+            if (r == 0 && ++zero_calls > 4)
+                break;
+            if (r > 0 && b->nitems_consumed_last() != r / (int)numchans)
+                throw std::logic_error("pfb_synthesizer_ccf: consume_each mismatch");
+            produced += r;
+        }
+        return produced;
+    });
+}
+
+// filterbank_vcvcf: in holds ntaps history vectors + nout vectors; set_taps(taps2) after `retap_at` outputs when taps2 != NULL
+long long grbx_filterbank_run(int nfilts, int ntaps, const float* taps, const float* taps2, long long retap_at, const void* in,
+                              void* out, long long nout, int chunk)
+{
+    return guarded([&]() -> long long {
+        auto rows = [&](const float* p) {
+            std::vector<std::vector<float>> t((size_t)nfilts);
+            for (int i = 0; i < nfilts; i++)
+                t[i].assign(p + (size_t)i * ntaps, p + (size_t)(i + 1) * ntaps);
+            return t;
+        };
+        auto b = gr::filter::filterbank_vcvcf::make(rows(taps));
+        if (b->history() != (unsigned)ntaps + 1 || b->taps() != rows(taps))
+            throw std::logic_error("filterbank_vcvcf: history/taps accessor mismatch");
+        const size_t vsz = (size_t)nfilts * 8;
+        long long produced = 0;
+        int zero_calls = 0;
+        bool retapped = false;
+        while (produced < nout) {
+            if (taps2 && !retapped && produced >= retap_at) {
+                b->set_taps(rows(taps2));
+                retapped = true;
+            }
+            long long n = std::min<long long>(chunk, nout - produced);
+            if (taps2 && !retapped)
+                n = std::min<long long>(n, retap_at - produced);
+            gr_vector_const_void_star ii(1, (const char*)in + (size_t)produced * vsz);
+            gr_vector_void_star oo(1, (char*)out + (size_t)produced * vsz);
+            gr_vector_int ni(1, (int)(n + ntaps));
+            int r = b->general_work((int)n, ni, ii, oo);
+            if (r < 0)
+                break;
+            if (r == 0 && ++zero_calls > 4)
+                break;
+            produced += r;
+        }
+        return produced;
+    });
+}
+
 } // extern "C"

@@ -12,6 +12,9 @@
 //   gr::filter::pfb_channelizer_ccf         gr-filter/include/gnuradio/filter/pfb_channelizer_ccf.h:100-192
 //                                           gr-filter/lib/pfb_channelizer_ccf_impl.{h,cc}
 //   gr::fft::fft_vcc                        gr-fft/include/gnuradio/fft/fft_vcc.h:47-70, gr-fft/lib/fft_vcc_fftw.{h,cc}
+//   gr::fft::fft_vfc                        gr-fft/include/gnuradio/fft/fft_vfc.h, gr-fft/lib/fft_vfc_fftw.{h,cc}
+//   gr::filter::pfb_synthesizer_ccf         gr-filter/include/gnuradio/filter/pfb_synthesizer_ccf.h, lib/pfb_synthesizer_ccf_impl.{h,cc}
+//   gr::filter::filterbank_vcvcf            gr-filter/include/gnuradio/filter/filterbank_vcvcf.h, lib/filterbank_vcvcf_impl.{h,cc}
 //   gr::blocks::complex_to_mag_squared      gr-blocks/lib/complex_to_mag_squared_impl.{h,cc}
 //
 // Build modes
@@ -25,6 +28,7 @@
 
 #include <cmath>
 #include <complex>
+#include <cstdio>
 #include <cstdlib>
 #include <memory>
 #include <mutex>
@@ -805,6 +809,164 @@ private:
     bool d_updated = false;
 };
 
+// ---------------------------------------------------------------------------------------------------
+// pfb_synthesizer_ccf  (gr-filter/include/gnuradio/filter/pfb_synthesizer_ccf.h, lib/pfb_synthesizer_ccf_impl.{h,cc})
+// ---------------------------------------------------------------------------------------------------
+class pfb_synthesizer_ccf : public grb200::rt::sync_interpolator
+{
+public:
+    typedef std::shared_ptr<pfb_synthesizer_ccf> sptr;
+    static sptr make(unsigned int numchans, const std::vector<float>& taps, bool twox = false)
+    {
+        return grb200::make_sptr(new pfb_synthesizer_ccf(numchans, taps, twox));
+    }
+    ~pfb_synthesizer_ccf() override { grb200_pfb_synth_destroy(d_h); }
+
+    void set_taps(const std::vector<float>& taps) // pfb_synthesizer_ccf_impl.cc:77-93
+    {
+        std::lock_guard<std::mutex> l(d_setlock);
+        grb200::check(grb200_pfb_synth_set_taps(d_h, taps.data(), (int)taps.size()));
+        set_history(1);
+        d_updated = true;
+    }
+    std::vector<std::vector<float>> taps() const // d_taps, :95-184
+    {
+        const int rows = grb200_pfb_synth_twox(d_h) * grb200_pfb_synth_numchans(d_h), T = grb200_pfb_synth_taps_per_filter(d_h);
+        std::vector<float> flat((size_t)rows * T);
+        grb200::check(grb200_pfb_synth_branch_taps(d_h, flat.data()));
+        std::vector<std::vector<float>> out((size_t)rows);
+        for (int i = 0; i < rows; i++)
+            out[i].assign(flat.begin() + (size_t)i * T, flat.begin() + (size_t)(i + 1) * T);
+        return out;
+    }
+    void print_taps()
+    {
+        const std::vector<std::vector<float>> t = taps();
+        for (size_t i = 0; i < t.size(); i++) {
+            printf("filter[%d]: [", (int)i);
+            for (float v : t[i])
+                printf(" %.4e", v);
+            printf("]\n\n");
+        }
+    }
+    void set_channel_map(const std::vector<int>& map) // :202-217
+    {
+        std::lock_guard<std::mutex> l(d_setlock);
+        grb200::check(grb200_pfb_synth_set_channel_map(d_h, map.data(), (int)map.size()));
+    }
+    std::vector<int> channel_map() const
+    {
+        std::vector<int> m((size_t)grb200_pfb_synth_twox(d_h) * grb200_pfb_synth_numchans(d_h) * 2 + 16);
+        const int n = grb200_pfb_synth_get_channel_map(d_h, m.data(), (int)m.size());
+        grb200::check(n < 0 ? n : 0);
+        m.resize((size_t)n);
+        return m;
+    }
+
+    int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
+    {
+        std::lock_guard<std::mutex> l(d_setlock); // :225
+        if (d_updated) {                           // :229-232
+            d_updated = false;
+            return 0; // history requirements may have changed
+        }
+        grb200::check(grb200_pfb_synth_work(d_h, input_items.data(), (int)input_items.size(), output_items[0], noutput_items));
+        return noutput_items;
+    }
+    grb200_pfbsynth* handle() { return d_h; } // device-resident chaining (grb200_pfb_synth_work_dev)
+
+private:
+    pfb_synthesizer_ccf(unsigned int numchans, const std::vector<float>& taps, bool twox)
+        : sync_interpolator("pfb_synthesizer_ccf", grb200::rt::io_signature::make(1, numchans, sizeof(gr_complex)),
+                            grb200::rt::io_signature::make(1, 1, sizeof(gr_complex)), numchans)
+    {
+        // an odd channel count with twox throws std::invalid_argument (:44-47)
+        grb200::check(grb200_pfb_synth_ccf_create(numchans, taps.data(), (int)taps.size(), twox ? 1 : 0,
+                                                  grb200::default_device(), &d_h));
+        set_history(1);                 // :92
+        set_output_multiple(numchans);  // :68
+        d_updated = true;               // the constructor goes through set_taps (:63)
+    }
+    grb200_pfbsynth* d_h = nullptr;
+    bool d_updated = false;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// filterbank_vcvcf  (gr-filter/include/gnuradio/filter/filterbank_vcvcf.h, lib/filterbank_vcvcf_impl.{h,cc}, lib/filterbank.cc)
+// ---------------------------------------------------------------------------------------------------
+class filterbank_vcvcf : public grb200::rt::block
+{
+public:
+    typedef std::shared_ptr<filterbank_vcvcf> sptr;
+    static sptr make(const std::vector<std::vector<float>>& taps) { return grb200::make_sptr(new filterbank_vcvcf(taps)); }
+    ~filterbank_vcvcf() override { grb200_filterbank_vcvcf_destroy(d_h); }
+
+    void set_taps(const std::vector<std::vector<float>>& taps) // filterbank_vcvcf_impl.cc:39-45 over filterbank.cc:50-79
+    {
+        std::lock_guard<std::mutex> l(d_setlock);
+        if (taps.size() != d_taps.size())
+            throw std::runtime_error("The number of filters is incorrect.");
+        const std::vector<float> flat = flatten(taps);
+        grb200::check(grb200_filterbank_vcvcf_set_taps(d_h, (int)taps.size(), (int)taps[0].size(), flat.data()));
+        d_taps = taps;
+        set_history(taps[0].size() + 1);
+        d_updated = true;
+    }
+    void print_taps()
+    {
+        for (size_t i = 0; i < d_taps.size(); i++) {
+            printf("filter[%d]: [", (int)i);
+            for (float v : d_taps[i])
+                printf(" %.4e", v);
+            printf("]\n\n");
+        }
+    }
+    std::vector<std::vector<float>> taps() const { return d_taps; }
+
+    int general_work(int noutput_items, gr_vector_int&, gr_vector_const_void_star& input_items,
+                     gr_vector_void_star& output_items) override
+    {
+        std::lock_guard<std::mutex> l(d_setlock); // :59
+        if (d_updated) {                           // :64-67
+            d_updated = false;
+            return 0; // history requirements may have changed
+        }
+        grb200::check(grb200_filterbank_vcvcf_work(d_h, input_items[0], output_items[0], noutput_items));
+        consume_each(noutput_items); // :94
+        return noutput_items;
+    }
+    grb200_fbank* handle() { return d_h; }
+
+private:
+    static std::vector<float> flatten(const std::vector<std::vector<float>>& taps)
+    {
+        if (taps.empty())
+            throw std::invalid_argument("The taps vector may not be empty."); // filterbank.cc:30-32
+        const size_t nt = taps[0].size();
+        std::vector<float> flat;
+        flat.reserve(taps.size() * nt);
+        for (const std::vector<float>& row : taps) {
+            if (row.size() != nt)
+                throw std::runtime_error("All sets of taps must be of the same length."); // :60-64
+            flat.insert(flat.end(), row.begin(), row.end());
+        }
+        return flat;
+    }
+    explicit filterbank_vcvcf(const std::vector<std::vector<float>>& taps)
+        : block("filterbank_vcvcf", grb200::rt::io_signature::make(1, 1, sizeof(gr_complex) * taps.size()),
+                grb200::rt::io_signature::make(1, 1, sizeof(gr_complex) * taps.size())),
+          d_taps(taps)
+    {
+        const std::vector<float> flat = flatten(taps);
+        grb200::check(grb200_filterbank_vcvcf_create((int)taps.size(), (int)taps[0].size(), flat.data(),
+                                                     grb200::default_device(), &d_h));
+        set_history(taps[0].size() + 1); // filterbank_vcvcf_impl.cc:34
+    }
+    grb200_fbank* d_h = nullptr;
+    std::vector<std::vector<float>> d_taps;
+    bool d_updated = false;
+};
+
 } // namespace filter
 
 namespace fft {
@@ -847,6 +1009,50 @@ private:
     {
         // wrong window length -> std::runtime_error("fft_vcc: window not the same length as fft_size"), :46-47
         grb200::check(grb200_fft_vcc_create(fft_size, forward ? 1 : 0, window.data(), (int)window.size(), shift ? 1 : 0,
+                                            grb200::default_device(), &d_h));
+    }
+    grb200_fftvcc* d_h = nullptr;
+    size_t d_fft_size;
+    int d_nthreads;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// fft_vfc  (gr-fft/include/gnuradio/fft/fft_vfc.h, gr-fft/lib/fft_vfc_fftw.{h,cc})
+// ---------------------------------------------------------------------------------------------------
+class fft_vfc : public grb200::rt::sync_block
+{
+public:
+    typedef std::shared_ptr<fft_vfc> sptr;
+    static sptr make(int fft_size, bool forward, const std::vector<float>& window, int nthreads = 1)
+    {
+        return grb200::make_sptr(new fft_vfc(fft_size, forward, window, nthreads));
+    }
+    ~fft_vfc() override { grb200_fft_vcc_destroy(d_h); }
+    void set_nthreads(int n) { d_nthreads = n; }
+    int nthreads() const { return d_nthreads; }
+    bool set_window(const std::vector<float>& window) // fft_vfc_fftw.cc:48-55
+    {
+        if (window.empty() || window.size() == d_fft_size) {
+            grb200::check(grb200_fft_vcc_set_window(d_h, window.data(), (int)window.size()));
+            return true;
+        }
+        return false;
+    }
+    int work(int noutput_items, gr_vector_const_void_star& input_items, gr_vector_void_star& output_items) override
+    {
+        grb200::check(grb200_fft_vcc_work(d_h, input_items[0], output_items[0], noutput_items)); // :57-92
+        return noutput_items;
+    }
+    grb200_fftvcc* handle() { return d_h; }
+
+private:
+    fft_vfc(int fft_size, bool forward, const std::vector<float>& window, int nthreads)
+        : sync_block("fft_vfc_fftw", grb200::rt::io_signature::make(1, 1, fft_size * sizeof(float)),
+                     grb200::rt::io_signature::make(1, 1, fft_size * sizeof(gr_complex))),
+          d_fft_size(fft_size > 0 ? fft_size : 0), d_nthreads(nthreads)
+    {
+        // wrong window length -> std::runtime_error("fft_vfc: window not the same length as fft_size"), :40-41
+        grb200::check(grb200_fft_vfc_create(fft_size, forward ? 1 : 0, window.data(), (int)window.size(),
                                             grb200::default_device(), &d_h));
     }
     grb200_fftvcc* d_h = nullptr;

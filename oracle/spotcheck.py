@@ -176,3 +176,58 @@ def pfb_decimator(fetch_in, fetch_out, decim, taps, channel, nout, width=256, co
         f64 = po.f64_pfb_decimator(M, taps, channel, streams)[T - 1:]
         acc.add(got, ref, f64)
     return acc.result()
+
+
+def fir_fff(fetch_in, fetch_out, decim, taps, nout, width=1024, count=64, seed=0, orc=None):
+    """fir_filter_fff: float stream with ntaps-1 history floats in front."""
+    orc = orc or po.best()
+    acc = _Acc(orc.kind)
+    nt = len(taps)
+    t64 = np.asarray(taps, np.float64)
+    for o0 in window_starts(nout, width, count, seed):
+        w = min(width, nout - o0)
+        xin = fetch_in(o0 * decim, (o0 + w) * decim + nt - 1)
+        got = fetch_out(o0, o0 + w)
+        ref = orc.fir_fff(decim, taps, xin, w)
+        f64 = np.convolve(xin.astype(np.float64), t64)[nt - 1: nt - 1 + w * decim: decim][:w]
+        assert np.isfinite(got).all()
+        a, b = po.nrms(got, ref)
+        c, d = po.nrms(got.astype(np.float64), f64)
+        r = acc.d
+        r["nrms_max"], r["max_over_rms"] = max(r["nrms_max"], a), max(r["max_over_rms"], b)
+        r["nrms_f64_max"], r["max_over_rms_f64"] = max(r["nrms_f64_max"], c), max(r["max_over_rms_f64"], d)
+        r["windows"] += 1
+        r["items"] += got.size
+    return acc.result()
+
+
+def pfb_synthesizer(fetch_in, fetch_out, numchans, taps, ntimes, width=128, count=64, seed=0, orc=None):
+    """pfb_synthesizer_ccf (1x), stateless device form: fetch_in(a, b) -> [nin][b-a] items of every input stream (T-1 history
+    items in front); fetch_out(a, b) -> output items [a*M, b*M).  A window is re-synthesised by the oracle from a zero state
+    T-1 items early; its first (T-1)*M outputs (the start-up transient) are dropped."""
+    orc = orc or po.best()
+    acc = _Acc(orc.kind)
+    M = numchans
+    T = -(-len(taps) // M)
+    for t0 in window_starts(ntimes, width, count, seed):
+        w = min(width, ntimes - t0)
+        ins = fetch_in(t0, t0 + w + T - 1)
+        got = fetch_out(t0, t0 + w)
+        ref = orc.pfb_synthesizer(M, taps, False, ins)[(T - 1) * M:]
+        f64 = po.f64_pfb_synthesizer(M, taps, False, ins)[(T - 1) * M:]
+        acc.add(got, ref, f64)
+    return acc.result()
+
+
+def filterbank(fetch_in, fetch_out, taps, nout, width=128, count=64, seed=0, orc=None):
+    """filterbank_vcvcf: fetch_in(a, b) -> vectors [a, b) of the input (ntaps history vectors in front), fetch_out likewise."""
+    orc = orc or po.best()
+    acc = _Acc(orc.kind)
+    t = np.asarray(taps, np.float32)
+    nt = t.shape[1]
+    for j0 in window_starts(nout, width, count, seed):
+        w = min(width, nout - j0)
+        xin = fetch_in(j0, j0 + w + nt)
+        got = fetch_out(j0, j0 + w)
+        acc.add(got, orc.filterbank(t, xin, w), po.f64_filterbank(t, xin, w))
+    return acc.result()

@@ -42,7 +42,8 @@ def test_library_is_sm100a_only():
 def test_cxx_block_wrappers_link():
     drv = os.path.join(ROOT, "gnuradio_b200", "cxx", "libgrb200_blocks.so")
     lib = C.CDLL(drv)
-    for s in ("grbx_fir_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run", "grbx_what"):
+    for s in ("grbx_fir_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run", "grbx_what",
+              "grbx_fir_fff_run", "grbx_fft_vfc_run", "grbx_pfb_synth_run", "grbx_filterbank_run"):
         assert hasattr(lib, s)
 
 

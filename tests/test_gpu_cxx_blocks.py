@@ -16,7 +16,7 @@ LL = C.c_longlong
 @pytest.fixture(scope="module")
 def drv():
     lib = C.CDLL(os.path.join(ROOT, "gnuradio_b200", "cxx", "libgrb200_blocks.so"))
-    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_pfb_dec_run", "grbx_interp_fir_run", "grbx_rational_resampler_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run"):
+    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_pfb_dec_run", "grbx_interp_fir_run", "grbx_rational_resampler_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run", "grbx_fir_fff_run", "grbx_fft_vfc_run", "grbx_pfb_synth_run", "grbx_filterbank_run"):
         getattr(lib, f).restype = LL
     lib.grbx_what.restype = C.c_char_p
     return lib
@@ -149,3 +149,62 @@ def test_cxx_rational_resampler(drv, orc):
     assert rc == -2  # std::out_of_range
     rc = drv.grbx_rational_resampler_run(0, 1, 0, p(taps), 2, p(x), p(out), LL(10), 1000)
     assert rc == -2
+
+
+def test_cxx_fir_fff(drv, orc):
+    rng = np.random.default_rng(21)
+    for nt, D in ((256, 1), (33, 4)):
+        nout = 20000
+        x = rng.uniform(-1, 1, nout * D).astype(np.float32)
+        taps = rng.uniform(-1, 1, nt).astype(np.float32)
+        xin = np.concatenate([np.zeros(nt - 1, np.float32), x])
+        out = np.zeros(nout, np.float32)
+        rc = drv.grbx_fir_fff_run(D, p(taps), nt, p(xin), p(out), LL(nout), 4096)
+        assert rc == nout, drv.grbx_what()
+        assert_parity(out, orc.fir_fff(D, taps, xin, nout), "c++ fir_filter_fff %d/%d" % (nt, D))
+
+
+def test_cxx_fft_vfc(drv, orc):
+    rng = np.random.default_rng(22)
+    N, nvec = 1024, 130
+    x = rng.uniform(-1, 1, N * nvec).astype(np.float32)
+    w = rng.uniform(0.1, 1, N).astype(np.float32)
+    out = np.zeros(N * nvec, np.complex64)
+    rc = drv.grbx_fft_vfc_run(N, 1, p(w), N, p(x), p(out), LL(nvec), 7)
+    assert rc == nvec, drv.grbx_what()
+    assert_parity(out, orc.fft_vfc(N, True, w, x), "c++ fft_vfc")
+    assert drv.grbx_fft_vfc_run(N, 1, p(w), N - 1, p(x), p(out), LL(1), 7) == -3  # std::runtime_error: window length
+
+
+def test_cxx_pfb_synthesizer(drv, orc):
+    rng = np.random.default_rng(23)
+    for M, T, twox, nin in ((64, 16, 0, 64), (8, 5, 1, 11), (5, 7, 0, 3)):
+        n = 3000
+        taps = rng.uniform(-1, 1, M * T - 1).astype(np.float32)
+        ins = crand(rng, nin * n).reshape(nin, n)
+        cmap = rng.permutation((2 if twox else 1) * M).astype(np.int32)
+        out = np.zeros(n * M, np.complex64)
+        inp = (C.c_void_p * nin)(*[ins[i].ctypes.data for i in range(nin)])
+        rc = drv.grbx_pfb_synth_run(M, p(taps), len(taps), twox, p(cmap), len(cmap), inp, nin, p(out), LL(n * M), 4096 // M * M)
+        assert rc == n * M, drv.grbx_what()
+        assert_parity(out, orc.pfb_synthesizer(M, taps, bool(twox), ins, channel_map=cmap), "c++ pfb_synthesizer %d" % M)
+    assert drv.grbx_pfb_synth_run(5, p(taps), 10, 1, None, 0, inp, 1, p(out), LL(5), 5) == -1  # odd channels with 2x
+
+
+def test_cxx_filterbank(drv, orc):
+    rng = np.random.default_rng(24)
+    nf, nt, n = 32, 9, 6000
+    t1 = rng.uniform(-1, 1, (nf, nt)).astype(np.float32)
+    t2 = rng.uniform(-1, 1, (nf, nt)).astype(np.float32)
+    t1[4] = 0
+    x = crand(rng, nf * (n + nt))
+    out = np.zeros(nf * n, np.complex64)
+    rc = drv.grbx_filterbank_run(nf, nt, p(t1), None, LL(0), p(x), p(out), LL(n), 512)
+    assert rc == n, drv.grbx_what()
+    assert_parity(out.reshape(n, nf), orc.filterbank(t1, x, n), "c++ filterbank")
+    # set_taps mid-stream: work() returns 0 once, then the new taps apply from that item on
+    rc = drv.grbx_filterbank_run(nf, nt, p(t1), p(t2), LL(2048), p(x), p(out), LL(n), 512)
+    assert rc == n, drv.grbx_what()
+    got = out.reshape(n, nf)
+    assert_parity(got[:2048], orc.filterbank(t1, x, 2048), "c++ filterbank before set_taps")
+    assert_parity(got[2048:], orc.filterbank(t2, x[2048 * nf:], n - 2048), "c++ filterbank after set_taps")
