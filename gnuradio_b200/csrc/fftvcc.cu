@@ -126,7 +126,9 @@ struct VccStreamGeom {
     static constexpr int SMEM = XIN_BYTES + S_BYTES + TW_BYTES + WIN_BYTES + 16;
 };
 
-template <int N, bool FWD, bool REAL>
+// MODE is a template parameter here (straight-line store code: the 16 stores of a thread issue back to back) -- the
+// per-element mode switch of vcc_store() cost the cfg5 kernel 17 % when it was first generalised.
+template <int N, bool FWD, bool REAL, int MODE>
 __global__ void __launch_bounds__(VccGeom<N>::NT)
 fft_vcc_stream_kernel(const VccArgs a)
 {
@@ -152,6 +154,9 @@ fft_vcc_stream_kernel(const VccArgs a)
     float2* S = Sall + vl * fft_smem_elems(N);
     const float2* X = XIN + vl * N;
     const float* XR = reinterpret_cast<const float*>(XIN) + vl * N;
+    float2* __restrict__ outc = reinterpret_cast<float2*>(a.out);
+    float* __restrict__ outf = reinterpret_cast<float*>(a.out);
+    const float log_mul = a.log_mul, log_scale = a.log_scale;
     const bool in_swap = (!FWD) && shift;
     const bool out_rot = FWD && shift;
     const bool has_win = window != nullptr;
@@ -218,7 +223,19 @@ fft_vcc_stream_kernel(const VccArgs a)
                     int k = (t + b * TPV) + q * (N / RL);
                     if (out_rot)
                         k = (k + N / 2) & (N - 1);
-                    vcc_store(a, vec, N, k, v[b * RL + q]);
+                    const float2 Xk = v[b * RL + q];
+                    if constexpr (MODE == 0) {
+                        outc[vec * N + k] = Xk;
+                    } else {
+                        const float pw = fmaf(Xk.x, Xk.x, Xk.y * Xk.y);
+                        if constexpr (MODE == 1) {
+                            outf[vec * N + k] = pw;
+                        } else {
+                            outf[vec * N + k] = log2f(fmaxf(pw, 1.17549435e-38f) * log_scale) * log_mul;
+                            if (vec == nvec - 1)
+                                a.ystate[k] = pw;
+                        }
+                    }
                 }
             }
         }
@@ -312,12 +329,12 @@ static int launch_vcc(const VccArgs& a, int nsm, cudaStream_t st)
     return 0;
 }
 
-template <int N, bool FWD, bool REAL>
-static int launch_vcc_stream(const VccArgs& a, int nsm, cudaStream_t st)
+template <int N, bool FWD, bool REAL, int MODE>
+static int launch_vcc_stream_m(const VccArgs& a, int nsm, cudaStream_t st)
 {
     using G = VccGeom<N>;
     using SG = VccStreamGeom<N>;
-    auto kern = fft_vcc_stream_kernel<N, FWD, REAL>;
+    auto kern = fft_vcc_stream_kernel<N, FWD, REAL, MODE>;
     GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::SMEM));
     int occ = 1;
     GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, G::NT, SG::SMEM));
@@ -330,6 +347,19 @@ static int launch_vcc_stream(const VccArgs& a, int nsm, cudaStream_t st)
     kern<<<(unsigned)grid, G::NT, SG::SMEM, st>>>(a);
     GRB_LAUNCH_CHECK();
     return 0;
+}
+
+template <int N, bool FWD, bool REAL>
+static int launch_vcc_stream(const VccArgs& a, int nsm, cudaStream_t st)
+{
+    if (a.mode == 0)
+        return launch_vcc_stream_m<N, FWD, REAL, 0>(a, nsm, st);
+    if (a.mode == 1)
+        return launch_vcc_stream_m<N, FWD, REAL, 1>(a, nsm, st);
+    if constexpr (FWD) // the log epilogue belongs to logpwrfft: forward transforms only
+        return launch_vcc_stream_m<N, FWD, REAL, 2>(a, nsm, st);
+    else
+        return fail(GRB200_EINVAL, "fft_vcc: the log epilogue needs a forward transform");
 }
 
 template <int N, bool REAL>

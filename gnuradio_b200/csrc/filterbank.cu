@@ -45,22 +45,35 @@ filterbank_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
         ring[v] = (v >= skip) ? x[r * nf + i] : make_float2(0.f, 0.f);
     }
     ring[TP - 1] = make_float2(0.f, 0.f);
+    // the TP new rows of a block are loaded together, one block ahead of the arithmetic: TP independent loads in flight per
+    // thread whatever the compiler's own scheduling would have done
+    float2 nx[TP];
+#pragma unroll
+    for (int k = 0; k < TP; k++)
+        nx[k] = j0 + k < j1 ? x[(j0 + k + T - 1) * nf + i] : make_float2(0.f, 0.f);
     for (long long j = j0; j < j1; j += TP) {
+        float2 cur[TP];
+#pragma unroll
+        for (int k = 0; k < TP; k++)
+            cur[k] = nx[k];
+        const long long jn = j + TP;
+#pragma unroll
+        for (int k = 0; k < TP; k++)
+            nx[k] = jn + k < j1 ? x[(jn + k + T - 1) * nf + i] : make_float2(0.f, 0.f);
 #pragma unroll
         for (int k = 0; k < TP; k++) {
             const long long jj = j + k;
-            if (jj < j1) {
-                ring[(k + TP - 1) % TP] = x[(jj + T - 1) * nf + i];
-                float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+            ring[(k + TP - 1) % TP] = cur[k];
+            float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
 #pragma unroll
-                for (int v = 0; v < TP; v += 2) {
-                    if (v >= skip)
-                        a0 = __ffma2_rn(make_float2(taps[v], taps[v]), ring[(k + v) % TP], a0);
-                    if (v + 1 >= skip)
-                        a1 = __ffma2_rn(make_float2(taps[v + 1], taps[v + 1]), ring[(k + v + 1) % TP], a1);
-                }
-                out[jj * nf + i] = __fadd2_rn(a0, a1);
+            for (int v = 0; v < TP; v += 2) {
+                if (v >= skip)
+                    a0 = __ffma2_rn(make_float2(taps[v], taps[v]), ring[(k + v) % TP], a0);
+                if (v + 1 >= skip)
+                    a1 = __ffma2_rn(make_float2(taps[v + 1], taps[v + 1]), ring[(k + v + 1) % TP], a1);
             }
+            if (jj < j1)
+                out[jj * nf + i] = __fadd2_rn(a0, a1);
         }
     }
 }
