@@ -16,6 +16,20 @@ def launch_count():
     return int(_lib.lib().grb200_launch_count())
 
 
+def host_register(array):
+    """Page-lock a numpy array the caller owns (what an integration does once for a gr::buffer) so that the staging path
+    copies from / to it directly instead of through the pinned bounce.  Undo with host_unregister() before freeing it."""
+    import ctypes as C
+
+    _lib.check(_lib.lib().grb200_host_register(C.c_void_p(array.ctypes.data), array.nbytes))
+
+
+def host_unregister(array):
+    import ctypes as C
+
+    _lib.check(_lib.lib().grb200_host_unregister(C.c_void_p(array.ctypes.data)))
+
+
 def version():
     return _lib.lib().grb200_version().decode()
 

@@ -23,6 +23,13 @@ SIGNATURES = {
     "grb200_launch_count": (u64, []),
     "grb200_host_alloc": (i32, [pvp, u64]),
     "grb200_host_free": (i32, [vp]),
+    "grb200_host_register": (i32, [vp, u64]),
+    "grb200_host_unregister": (i32, [vp]),
+    "grb200_fir_work_lag": (i32, [vp, vp, i64, vp, i64, C.POINTER(i64)]),
+    "grb200_fir_flush": (i32, [vp, vp, i64, C.POINTER(i64)]),
+    "grb200_pfb_chan_work_lag": (i32, [vp, pvp, i64, pvp, i32, i64, C.POINTER(i64), C.POINTER(i64)]),
+    "grb200_pfb_chan_work_interleaved_lag": (i32, [vp, vp, i64, pvp, i32, i64, C.POINTER(i64), C.POINTER(i64)]),
+    "grb200_pfb_chan_flush": (i32, [vp, pvp, i32, i64, C.POINTER(i64)]),
     "grb200_dev_alloc": (i32, [i32, pvp, u64]),
     "grb200_dev_free": (i32, [i32, vp]),
     "grb200_memcpy_h2d": (i32, [i32, vp, vp, u64]),

@@ -33,7 +33,30 @@ int grb200_host_alloc(void** ptr, unsigned long long bytes)
 }
 int grb200_host_free(void* ptr)
 {
+    pin_cache_invalidate();
     GRB_CUDA(cudaFreeHost(ptr));
+    return 0;
+}
+int grb200_host_register(void* ptr, unsigned long long bytes)
+{
+    if (!ptr || !bytes)
+        return fail(GRB200_EINVAL, "host_register: bad arguments");
+    cudaError_t e = cudaHostRegister(ptr, (size_t)bytes, cudaHostRegisterDefault);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) {
+        cudaGetLastError();
+        e = cudaSuccess;
+    }
+    if (e != cudaSuccess)
+        return fail(GRB200_ECUDA, "cudaHostRegister(%llu bytes) failed: %s", bytes, cudaGetErrorString(e));
+    pin_cache_invalidate();
+    return 0;
+}
+int grb200_host_unregister(void* ptr)
+{
+    cudaError_t e = cudaHostUnregister(ptr);
+    pin_cache_invalidate();
+    if (e != cudaSuccess)
+        return fail(GRB200_ECUDA, "cudaHostUnregister failed: %s", cudaGetErrorString(e));
     return 0;
 }
 int grb200_dev_alloc(int device, void** ptr, unsigned long long bytes)
@@ -215,11 +238,17 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
     return dev_done(rc, h->sg, st);
 }
 
-int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long long noutput)
+} // extern "C"
+
+// lag != 0: queue this call, hand the PREVIOUS call's results to out_host (at most out_cap items), count in *produced
+static int fir_work_host(grb200_fir* h, const void* in_host, void* out_host, long long noutput, int lag, long long out_cap,
+                         long long* produced)
 {
-    if (!h || noutput < 0 || (noutput > 0 && (!in_host || !out_host)))
+    if (!h || noutput < 0 || (noutput > 0 && (!in_host || (!lag && !out_host))))
         return fail(GRB200_EINVAL, "fir_filter::work: bad arguments");
-    if (noutput == 0)
+    if (produced)
+        *produced = lag ? 0 : noutput;
+    if (noutput == 0 && !lag)
         return 0;
     std::lock_guard<std::mutex> lk(h->mu);
     grb::DeviceScope _ds(h->device);
@@ -228,7 +257,14 @@ int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long lon
         return rc;
     const int D = h->decim, nt = h->ntaps;
     const size_t isz = (size_t)h->isz();
-    long long chunk = (long long)(kChunkBytes / isz) / D; // outputs per chunk
+    if (noutput == 0) { // lag mode, nothing to queue: hand out what is still parked (end of stream)
+        void* outs[1] = { out_host };
+        const Stager::LagResult& newest = h->sg.lag[h->sg.lag_cur ^ 1];
+        if (newest.pending && newest.nitems > out_cap)
+            return fail(GRB200_EINVAL, "fir_filter::flush: %lld items are waiting, room for %lld offered", newest.nitems, out_cap);
+        return h->sg.lag_flush(outs, 1, produced);
+    }
+    long long chunk = (long long)(chunk_bytes_for((size_t)noutput * D * isz) / isz) / D; // outputs per chunk
     if (chunk < 1)
         chunk = 1;
     if (chunk > noutput)
@@ -239,12 +275,20 @@ int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long lon
     const char* in = (const char*)in_host;
     char* out = (char*)out_host;
     Stager& sg = h->sg;
+    if (lag) {
+        // the previous call's result must fit what the caller offers now (the block mirrors submit equal-sized calls)
+        const Stager::LagResult& prev = sg.lag[sg.lag_cur ^ 1];
+        if (prev.pending && prev.nitems > out_cap)
+            return fail(GRB200_EINVAL, "fir_filter::work_lag: %lld items are waiting, room for %lld offered", prev.nitems, out_cap);
+        if ((rc = sg.lag_begin((size_t)noutput * isz, nchunks, noutput)))
+            return rc;
+    }
     rc = sg.run(
         nchunks,
         [&](long long c, int slot, Stager::Chunk& ch) {
             const long long o0 = c * chunk, n = std::min(chunk, noutput - o0);
             ch.h2d.push_back({ in + (size_t)o0 * D * isz, sg.dev[slot][0], (size_t)(n * D + nt - 1) * isz });
-            ch.d2h.push_back({ sg.dev[slot][1], out + (size_t)o0 * isz, (size_t)n * isz });
+            ch.d2h.push_back(Piece(sg.dev[slot][1], out + (size_t)o0 * isz, (size_t)n * isz, 0, (size_t)o0 * isz));
             return 0;
         },
         [&](long long c, int slot, cudaStream_t st) {
@@ -258,8 +302,38 @@ int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long lon
         });
     if (!rc && h->rot)
         h->theta = rotate_advance(h->theta, h->delta, noutput);
+    if (!rc && lag) {
+        void* outs[1] = { out_host };
+        long long got = 0;
+        rc = sg.lag_collect(outs, 1, &got);
+        if (produced)
+            *produced = got;
+    }
     return rc;
 }
+
+extern "C" {
+
+int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long long noutput)
+{
+    return fir_work_host(h, in_host, out_host, noutput, 0, noutput, nullptr);
+}
+
+int grb200_fir_work_lag(grb200_fir* h, const void* in_host, long long noutput, void* out_host, long long out_capacity,
+                        long long* produced)
+{
+    if (!produced || out_capacity < 0 || (out_capacity > 0 && !out_host))
+        return fail(GRB200_EINVAL, "fir_filter::work_lag: bad arguments");
+    return fir_work_host(h, in_host, out_host, noutput, 1, out_capacity, produced);
+}
+
+int grb200_fir_flush(grb200_fir* h, void* out_host, long long out_capacity, long long* produced)
+{
+    if (!produced || out_capacity < 0 || (out_capacity > 0 && !out_host))
+        return fail(GRB200_EINVAL, "fir_filter::flush: bad arguments");
+    return fir_work_host(h, nullptr, out_host, 0, 1, out_capacity, produced);
+}
+
 
 void grb200_fir_destroy(grb200_fir* h)
 {

@@ -169,7 +169,7 @@ int grb200_fftfilt_work(grb200_fftfilt* h, const void* in_host, void* out_host, 
     const int D = h->decim, nh = h->ntaps - 1;
     const long long V = h->parts > 1 ? h->L / 2 : h->L - nh; // the device kernel's hop
     // chunk = whole device blocks, and whole decimation periods so that every chunk starts on phase 0
-    long long per = (long long)(kChunkBytes / 8) / D; // outputs per chunk (target)
+    long long per = (long long)(chunk_bytes_for((size_t)noutput * D * 8) / 8) / D; // outputs per chunk (target)
     long long unit = V;                               // outputs*D per chunk must be a multiple of V for no waste
     long long chunk = std::max<long long>(1, per / unit) * unit; // outputs per chunk
     if (chunk > noutput)

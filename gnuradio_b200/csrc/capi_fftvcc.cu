@@ -51,7 +51,7 @@ static int vcc_work_host(grb200_fftvcc* h, const void* in_host, void* out_host, 
     if (rc)
         return rc;
     const size_t vin = (size_t)h->N * h->in_item(), vout = (size_t)h->N * (magsq ? 4 : 8);
-    long long chunk = std::max<long long>(1, (long long)(kChunkBytes / vin));
+    long long chunk = std::max<long long>(1, (long long)(chunk_bytes_for((size_t)nvectors * vin) / vin));
     if (chunk > nvectors)
         chunk = nvectors;
     const long long nchunks = (nvectors + chunk - 1) / chunk;
@@ -209,7 +209,7 @@ int grb200_magsq_work(int device, const void* in_host, float* out_host, long lon
     std::lock_guard<std::mutex> lk(shared_stager_mutex(device)); // the per-device stager is shared: one host-staged call at a time
     grb::DeviceScope _ds(device);
     Stager& sg = *sgp;
-    long long chunk = (long long)(kChunkBytes / 8);
+    long long chunk = std::max<long long>(1, (long long)(chunk_bytes_for((size_t)nitems * 8) / 8));
     if (chunk > nitems)
         chunk = nitems;
     const long long nchunks = (nitems + chunk - 1) / chunk;
@@ -470,7 +470,7 @@ int grb200_logpwrfft_work(grb200_logpwr* h, const void* in_host, long long nitem
         if (rc)
             return rc;
         const size_t vin = (size_t)h->N * h->in_item(), vout = (size_t)h->N * 4;
-        long long chunk = std::max<long long>(1, (long long)(kChunkBytes / vin));
+        long long chunk = std::max<long long>(1, (long long)(chunk_bytes_for((size_t)nkeep * vin) / vin));
         if (chunk > nkeep)
             chunk = nkeep;
         const long long nchunks = (nkeep + chunk - 1) / chunk;

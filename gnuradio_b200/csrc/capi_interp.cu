@@ -240,7 +240,7 @@ int grb200_interp_fir_work(grb200_interp* h, const void* in_host, void* out_host
         return rc;
     const int L = h->L, T = h->T;
     const long long ni = noutput / L;
-    long long chunk = std::max<long long>(1, (long long)(kChunkBytes / 8) / L); // input positions per chunk
+    long long chunk = std::max<long long>(1, (long long)(chunk_bytes_for((size_t)noutput * 8) / 8) / L); // input positions per chunk
     if (chunk > ni)
         chunk = ni;
     const long long nchunks = (ni + chunk - 1) / chunk;

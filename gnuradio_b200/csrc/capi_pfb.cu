@@ -182,10 +182,13 @@ int grb200_pfb_chan_work_interleaved_dev(grb200_pfb* p, const void* in_dev, void
 // Shared host-staged driver.  `interleaved` selects the input form:
 //   0: M separate streams (the block's io_signature), de-interleaved data is re-interleaved on the device
 //   1: one interleaved stream (what pfb.channelizer_ccf's stream_to_streams is fed with)
+// lag != 0: queue this call, hand the PREVIOUS call's results to out_streams (room for out_cap items each); the count goes
+// to *produced.  A zero-length lag call hands out what is still parked (end of stream).
 static int pfb_work_host(grb200_pfb* p, int interleaved, const void* const* in_streams, const void* in_il,
-                         void* const* out_streams, int nouts, long long noutput, long long* consumed)
+                         void* const* out_streams, int nouts, long long noutput, long long* consumed, int lag = 0,
+                         long long out_cap = 0, long long* produced = nullptr)
 {
-    if (!p || noutput < 0 || !out_streams || (interleaved ? !in_il : !in_streams))
+    if (!p || noutput < 0 || !out_streams || (noutput > 0 && (interleaved ? !in_il : !in_streams)))
         return fail(GRB200_EINVAL, "pfb_channelizer_ccf::work: bad arguments");
     std::lock_guard<std::mutex> lk(p->mu);
     int rc = pfb_check_nouts(p, nouts);
@@ -197,13 +200,23 @@ static int pfb_work_host(grb200_pfb* p, int interleaved, const void* const* in_s
     const long long rows_total = noutput * R / M; // toconsume, :158
     if (consumed)
         *consumed = rows_total;
-    if (noutput == 0)
+    if (produced)
+        *produced = lag ? 0 : noutput;
+    if (noutput == 0 && !lag)
         return 0;
     grb::DeviceScope _ds(p->device);
     if ((rc = _ds.rc))
         return rc;
+    if (lag) {
+        const Stager::LagResult& newest = p->sg.lag[p->sg.lag_cur ^ 1];
+        if (newest.pending && newest.nitems > out_cap)
+            return fail(GRB200_EINVAL, "pfb_channelizer_ccf::work_lag: %lld items are waiting, room for %lld offered",
+                        newest.nitems, out_cap);
+        if (noutput == 0)
+            return p->sg.lag_flush(out_streams, nouts, produced);
+    }
     // chunk: outputs per chunk, a multiple of the output multiple so every chunk starts on a whole input row
-    long long chunk = (long long)(kChunkBytes / 8) / R;
+    long long chunk = (long long)(chunk_bytes_for((size_t)noutput * R * 8) / 8) / R;
     chunk = std::max<long long>(1, chunk / om) * om;
     if (chunk > noutput)
         chunk = noutput;
@@ -213,7 +226,9 @@ static int pfb_work_host(grb200_pfb* p, int interleaved, const void* const* in_s
     if ((rc = sg.reserve_dev(0, (size_t)rows_chunk * M * 8)) || (rc = sg.reserve_dev(1, (size_t)chunk * nouts * 8)) ||
         (!interleaved && (rc = sg.reserve_dev(2, (size_t)rows_chunk * M * 8))))
         return rc;
-    return sg.run(
+    if (lag && (rc = sg.lag_begin((size_t)noutput * nouts * 8, nchunks * nouts, noutput)))
+        return rc;
+    rc = sg.run(
         nchunks,
         [&](long long c, int slot, Stager::Chunk& ch) {
             const long long o0 = c * chunk, n = std::min(chunk, noutput - o0);
@@ -226,8 +241,8 @@ static int pfb_work_host(grb200_pfb* p, int interleaved, const void* const* in_s
                                        (float2*)sg.dev[slot][2] + (size_t)j * rows_chunk, (size_t)rows * 8 });
             }
             for (int k = 0; k < nouts; k++)
-                ch.d2h.push_back({ (const float2*)sg.dev[slot][1] + (size_t)k * chunk, (float2*)out_streams[k] + o0,
-                                   (size_t)n * 8 });
+                ch.d2h.push_back(Piece((const float2*)sg.dev[slot][1] + (size_t)k * chunk, (float2*)out_streams[k] + o0,
+                                       (size_t)n * 8, k, (size_t)o0 * 8));
             return 0;
         },
         [&](long long c, int slot, cudaStream_t st) {
@@ -242,6 +257,33 @@ static int pfb_work_host(grb200_pfb* p, int interleaved, const void* const* in_s
                               p->identity ? 1 : 0, n, (const float*)p->h.p, (const float2*)p->wM.p,
                               sm_count(p->device), true, st);
         });
+    if (!rc && lag)
+        rc = sg.lag_collect(out_streams, nouts, produced);
+    return rc;
+}
+
+int grb200_pfb_chan_work_lag(grb200_pfb* p, const void* const* in_streams, long long noutput, void* const* out_streams,
+                             int nout_streams, long long out_capacity, long long* consumed, long long* produced)
+{
+    if (!produced || out_capacity < 0)
+        return fail(GRB200_EINVAL, "pfb_channelizer_ccf::work_lag: bad arguments");
+    return pfb_work_host(p, 0, in_streams, nullptr, out_streams, nout_streams, noutput, consumed, 1, out_capacity, produced);
+}
+
+int grb200_pfb_chan_work_interleaved_lag(grb200_pfb* p, const void* in_host, long long noutput, void* const* out_streams,
+                                         int nout_streams, long long out_capacity, long long* consumed, long long* produced)
+{
+    if (!produced || out_capacity < 0)
+        return fail(GRB200_EINVAL, "pfb_channelizer_ccf::work_lag: bad arguments");
+    return pfb_work_host(p, 1, nullptr, in_host, out_streams, nout_streams, noutput, consumed, 1, out_capacity, produced);
+}
+
+int grb200_pfb_chan_flush(grb200_pfb* p, void* const* out_streams, int nout_streams, long long out_capacity,
+                          long long* produced)
+{
+    if (!produced || out_capacity < 0)
+        return fail(GRB200_EINVAL, "pfb_channelizer_ccf::flush: bad arguments");
+    return pfb_work_host(p, 1, nullptr, nullptr, out_streams, nout_streams, 0, nullptr, 1, out_capacity, produced);
 }
 
 int grb200_pfb_chan_work(grb200_pfb* p, const void* const* in_streams, void* const* out_streams, int nout_streams,

@@ -455,7 +455,7 @@ int grb200_pfb_dec_work(grb200_pfbdec* p, const void* const* in_streams, void* o
     for (int s = 0; s < M; s++)
         if (!in_streams[s])
             return fail(GRB200_EINVAL, "pfb_decimator_ccf::work: input stream %d is null", s);
-    long long chunk = std::max<long long>(1, (long long)(kChunkBytes / 8) / M);
+    long long chunk = std::max<long long>(1, (long long)(chunk_bytes_for((size_t)noutput * M * 8) / 8) / M);
     if (chunk > noutput)
         chunk = noutput;
     const long long nchunks = (noutput + chunk - 1) / chunk;

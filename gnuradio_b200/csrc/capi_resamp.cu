@@ -371,7 +371,7 @@ int grb200_rational_resampler_work(grb200_resamp* h, const void* in_host, long l
         const unsigned long long L = h->L, D = h->D, c0 = h->ctr;
         const int T = h->T;
         // outputs per chunk: bound both the output bytes and the input span (n*D/L items) of a chunk
-        long long chunk = (long long)(kChunkBytes / 8);
+        long long chunk = (long long)(chunk_bytes_for((size_t)std::max<unsigned long long>(n, (unsigned long long)n * D / L) * 8) / 8);
         if (D > L)
             chunk = std::max<long long>(1, (long long)((unsigned long long)chunk * L / D));
         if (chunk > n)

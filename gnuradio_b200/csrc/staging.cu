@@ -1,5 +1,8 @@
 // staging.cu -- library globals, device selection and the pinned double-buffered staging pipeline (K8).
 #include <algorithm>
+#include <condition_variable>
+#include <cstdint>
+#include <thread>
 #include "staging.cuh"
 
 namespace grb {
@@ -100,6 +103,17 @@ void Stager::destroy()
     if (user_pending)
         cudaEventSynchronize(ev_user);
     cudaEventDestroy(ev_user);
+    for (auto& r : lag) {
+        if (r.pin)
+            cudaFreeHost(r.pin);
+        if (r.ev)
+            cudaEventDestroy(r.ev);
+        r = LagResult();
+    }
+    for (int i = 0; i < NSLOT; i++) {
+        pending[i] = false;
+        bounce[i].clear();
+    }
     cudaStreamDestroy(s_h2d);
     cudaStreamDestroy(s_exec);
     cudaStreamDestroy(s_d2h);
@@ -156,15 +170,131 @@ int Stager::reserve_pin(bool in, size_t bytes)
     return 0;
 }
 
+// Is this host address page-locked (cudaHostAlloc / cudaHostRegister / torch pinned)?  cudaPointerGetAttributes costs about a
+// microsecond; a scheduler-sized work() call asks 2..128 times, always about the same few buffers.  The answer is cached per
+// 64 KiB granule in a small direct-mapped table.  A stale entry is harmless: "pinned" for memory that no longer is just
+// makes cudaMemcpyAsync stage it itself, "pageable" for memory that now is pinned takes the bounce path.
+static std::atomic<unsigned long long> g_pin_cache[1024]; // (granule << 2) | valid << 1 | pinned
+static std::atomic<unsigned long long> g_pin_epoch{ 0 };
+
+void pin_cache_invalidate()
+{
+    for (auto& e : g_pin_cache)
+        e.store(0, std::memory_order_relaxed);
+    g_pin_epoch.fetch_add(1);
+}
+
 bool Stager::is_pinned(const void* p)
 {
+    const unsigned long long gran = (unsigned long long)(uintptr_t)p >> 16;
+    std::atomic<unsigned long long>& slot = g_pin_cache[(gran ^ (gran >> 10)) & 1023];
+    const unsigned long long v = slot.load(std::memory_order_relaxed);
+    if ((v >> 2) == gran && (v & 2))
+        return (v & 1) != 0;
     cudaPointerAttributes attr;
     cudaError_t e = cudaPointerGetAttributes(&attr, p);
-    if (e != cudaSuccess) {
+    bool pinned = false;
+    if (e != cudaSuccess)
         cudaGetLastError();
-        return false;
+    else
+        pinned = attr.type == cudaMemoryTypeHost;
+    slot.store((gran << 2) | 2 | (pinned ? 1 : 0), std::memory_order_relaxed);
+    return pinned;
+}
+
+// ---- parallel memcpy for the pageable bounce ---------------------------------------------------------------------
+// One thread copies 10-12 GB/s; PCIe 5 moves 50+.  Copies of a MiB or more are cut into slices for a small pool of helper
+// threads (GRB200_COPY_THREADS, default 4, 0 = inline), started on first use and shared by every handle of the process.
+namespace {
+struct CopyPool {
+    struct Job {
+        char* dst;
+        const char* src;
+        size_t bytes;
+    };
+    std::vector<std::thread> threads;
+    std::mutex mu;
+    std::condition_variable cv_work, cv_done;
+    std::vector<Job> jobs;
+    size_t next = 0, done = 0;
+    bool quit = false;
+    int n = 0;
+    CopyPool()
+    {
+        const char* e = getenv("GRB200_COPY_THREADS");
+        n = e ? atoi(e) : 4;
+        unsigned hw = std::thread::hardware_concurrency();
+        if (hw && (unsigned)n > hw / 2)
+            n = (int)(hw / 2);
+        if (n < 0)
+            n = 0;
+        for (int i = 0; i < n; i++)
+            threads.emplace_back([this] { loop(); });
     }
-    return attr.type == cudaMemoryTypeHost;
+    ~CopyPool()
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            quit = true;
+        }
+        cv_work.notify_all();
+        for (auto& t : threads)
+            t.join();
+    }
+    void loop()
+    {
+        std::unique_lock<std::mutex> lk(mu);
+        for (;;) {
+            cv_work.wait(lk, [this] { return quit || next < jobs.size(); });
+            if (quit)
+                return;
+            const Job j = jobs[next++];
+            lk.unlock();
+            memcpy(j.dst, j.src, j.bytes);
+            lk.lock();
+            if (++done == jobs.size())
+                cv_done.notify_all();
+        }
+    }
+    void copy(void* dst, const void* src, size_t bytes)
+    {
+        const size_t kMin = (size_t)1 << 20;
+        if (n == 0 || bytes < 2 * kMin) {
+            memcpy(dst, src, bytes);
+            return;
+        }
+        size_t parts = std::min<size_t>((size_t)n + 1, bytes / kMin);
+        size_t per = ((bytes + parts - 1) / parts + 63) & ~(size_t)63;
+        std::unique_lock<std::mutex> lk(mu);
+        jobs.clear();
+        next = done = 0;
+        for (size_t o = per; o < bytes; o += per) // slice 0 is the caller's own
+            jobs.push_back({ (char*)dst + o, (const char*)src + o, std::min(per, bytes - o) });
+        lk.unlock();
+        cv_work.notify_all();
+        memcpy(dst, src, std::min(per, bytes));
+        lk.lock();
+        cv_done.wait(lk, [this] { return done == jobs.size(); });
+        jobs.clear();
+        next = done = 0;
+    }
+};
+std::mutex g_pool_mu; // one big copy at a time through the pool
+CopyPool& copy_pool()
+{
+    static CopyPool p;
+    return p;
+}
+} // namespace
+
+void par_memcpy(void* dst, const void* src, size_t bytes)
+{
+    if (bytes < ((size_t)2 << 20)) {
+        memcpy(dst, src, bytes);
+        return;
+    }
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    copy_pool().copy(dst, src, bytes);
 }
 
 static std::mutex g_shared_mu;
@@ -216,28 +346,26 @@ static bool strided_group(const std::vector<Piece>& v, const std::vector<char>& 
     return true;
 }
 
+int Stager::retire(int slot)
+{
+    if (!pending[slot])
+        return 0;
+    GRB_CUDA(cudaEventSynchronize(ev_d2h[slot]));
+    for (auto& b : bounce[slot])
+        par_memcpy(b.host_dst, b.pin_src, b.bytes);
+    bounce[slot].clear();
+    pending[slot] = false;
+    return 0;
+}
+
 int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
 {
-    struct Bounce {
-        void* host_dst;
-        const void* pin_src;
-        size_t bytes;
-    };
-    std::vector<Bounce> bounce[NSLOT];
-    bool pending[NSLOT] = {};
     Chunk ch;
-    auto retire = [&](int slot) -> int {
-        if (!pending[slot])
-            return 0;
-        GRB_CUDA(cudaEventSynchronize(ev_d2h[slot]));
-        for (auto& b : bounce[slot])
-            memcpy(b.host_dst, b.pin_src, b.bytes);
-        bounce[slot].clear();
-        pending[slot] = false;
-        return 0;
-    };
-    for (long long c = 0; c < nchunks; c++) {
-        const int slot = (int)(c % NSLOT);
+    LagResult* lr = lag_active;
+    lag_active = nullptr; // whatever happens below, the next call starts clean
+    int last_slot = -1;
+    for (long long c = 0; c < nchunks; c++, next_chunk++) {
+        const int slot = (int)(next_chunk % NSLOT);
         int rc = retire(slot);
         if (rc)
             return rc;
@@ -254,15 +382,15 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
             if (!pinned_in[k])
                 need_in += (ch.h2d[k].bytes + 255) & ~(size_t)255;
         }
-        for (size_t k = 0; k < ch.d2h.size(); k++) {
+        for (size_t k = 0; k < ch.d2h.size() && !lr; k++) {
             pinned_out[k] = is_pinned(ch.d2h[k].dst);
             if (!pinned_out[k])
                 need_out += (ch.d2h[k].bytes + 255) & ~(size_t)255;
         }
         if (need_in > pin_in_cap || need_out > pin_out_cap) {
             // growing the bounce slots invalidates in-flight copies: drain first
-            for (long long k = c - NSLOT + 1; k < c; k++)
-                if (k >= 0 && (rc = retire((int)(k % NSLOT))))
+            for (int k = 0; k < NSLOT; k++)
+                if ((rc = retire(k)))
                     return rc;
             if ((rc = reserve_pin(true, need_in)) || (rc = reserve_pin(false, need_out)))
                 return rc;
@@ -280,7 +408,7 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
                 GRB_CUDA(cudaMemcpyAsync(p.dst, p.src, p.bytes, cudaMemcpyHostToDevice, s_h2d));
             } else {
                 char* b = (char*)pin_in[slot] + off;
-                memcpy(b, p.src, p.bytes);
+                par_memcpy(b, p.src, p.bytes);
                 GRB_CUDA(cudaMemcpyAsync(p.dst, b, p.bytes, cudaMemcpyHostToDevice, s_h2d));
                 off += (p.bytes + 255) & ~(size_t)255;
             }
@@ -293,33 +421,130 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
         GRB_CUDA(cudaEventRecord(ev_exec[slot], s_exec));
         GRB_CUDA(cudaStreamWaitEvent(s_d2h, ev_exec[slot], 0));
         off = 0;
-        const bool d2h_2d = strided_group(ch.d2h, pinned_out, &spitch, &dpitch);
-        if (d2h_2d)
-            GRB_CUDA(cudaMemcpy2DAsync(ch.d2h[0].dst, dpitch, ch.d2h[0].src, spitch, ch.d2h[0].bytes, ch.d2h.size(),
-                                       cudaMemcpyDeviceToHost, s_d2h));
-        for (size_t k = 0; k < ch.d2h.size() && !d2h_2d; k++) {
-            const Piece& p = ch.d2h[k];
-            if (p.bytes == 0)
-                continue;
-            if (pinned_out[k]) {
-                GRB_CUDA(cudaMemcpyAsync(p.dst, p.src, p.bytes, cudaMemcpyDeviceToHost, s_d2h));
-            } else {
-                char* b = (char*)pin_out[slot] + off;
-                GRB_CUDA(cudaMemcpyAsync(b, p.src, p.bytes, cudaMemcpyDeviceToHost, s_d2h));
-                bounce[slot].push_back({ p.dst, b, p.bytes });
-                off += (p.bytes + 255) & ~(size_t)255;
+        if (lr) { // lag-by-one: results are parked in the handle's pinned buffer, the caller's memory is not touched now
+            for (const Piece& p : ch.d2h) {
+                if (p.bytes == 0)
+                    continue;
+                if (lr->used + p.bytes > lr->cap)
+                    return fail(GRB200_ECUDA, "staging: lag buffer overflow (%zu + %zu > %zu)", lr->used, p.bytes, lr->cap);
+                GRB_CUDA(cudaMemcpyAsync((char*)lr->pin + lr->used, p.src, p.bytes, cudaMemcpyDeviceToHost, s_d2h));
+                lr->segs.push_back({ p.ostream, p.ooff, lr->used, p.bytes });
+                lr->used += (p.bytes + 63) & ~(size_t)63;
+            }
+        } else {
+            const bool d2h_2d = strided_group(ch.d2h, pinned_out, &spitch, &dpitch);
+            if (d2h_2d)
+                GRB_CUDA(cudaMemcpy2DAsync(ch.d2h[0].dst, dpitch, ch.d2h[0].src, spitch, ch.d2h[0].bytes, ch.d2h.size(),
+                                           cudaMemcpyDeviceToHost, s_d2h));
+            for (size_t k = 0; k < ch.d2h.size() && !d2h_2d; k++) {
+                const Piece& p = ch.d2h[k];
+                if (p.bytes == 0)
+                    continue;
+                if (pinned_out[k]) {
+                    GRB_CUDA(cudaMemcpyAsync(p.dst, p.src, p.bytes, cudaMemcpyDeviceToHost, s_d2h));
+                } else {
+                    char* b = (char*)pin_out[slot] + off;
+                    GRB_CUDA(cudaMemcpyAsync(b, p.src, p.bytes, cudaMemcpyDeviceToHost, s_d2h));
+                    bounce[slot].push_back({ p.dst, b, p.bytes });
+                    off += (p.bytes + 255) & ~(size_t)255;
+                }
             }
         }
         GRB_CUDA(cudaEventRecord(ev_d2h[slot], s_d2h));
         pending[slot] = true;
+        last_slot = slot;
     }
-    // drain in submission order
-    for (long long k = std::max<long long>(0, nchunks - NSLOT); k < nchunks; k++) {
-        int rc = retire((int)(k % NSLOT));
+    if (lr) {
+        // the caller's INPUT buffers are borrowed for this call only: every host->device copy that reads them directly
+        // (pinned memory; pageable went through the bounce already) must be over before we return.  Kernel and D2H run on.
+        if (last_slot >= 0)
+            GRB_CUDA(cudaEventSynchronize(ev_h2d[last_slot]));
+        GRB_CUDA(cudaEventRecord(lr->ev, s_d2h));
+        lr->pending = true;
+        return 0;
+    }
+    for (int k = 0; k < NSLOT; k++) { // drain: the caller's output buffers are valid when work() returns
+        int rc = retire(k);
         if (rc)
             return rc;
     }
     return 0;
+}
+
+// ---- lag-by-one mode -------------------------------------------------------------------------------------------------
+int Stager::lag_begin(size_t out_bytes, long long npieces, long long nitems)
+{
+    LagResult& r = lag[lag_cur];
+    if (r.pending) // two calls back: must have been collected; never overwrite a result nobody fetched
+        return fail(GRB200_EINVAL, "staging: lag result not collected before the buffer comes round again");
+    const size_t need = out_bytes + 64 * (size_t)npieces + 4096; // every piece starts on a 64-byte boundary
+    if (need > r.cap) {
+        if (r.pin)
+            GRB_CUDA(cudaFreeHost(r.pin));
+        r.pin = nullptr;
+        r.cap = 0;
+        cudaError_t e = cudaHostAlloc(&r.pin, need + need / 4, cudaHostAllocDefault);
+        if (e != cudaSuccess)
+            return fail(GRB200_ENOMEM, "cudaHostAlloc(%zu) failed: %s", need, cudaGetErrorString(e));
+        r.cap = need + need / 4;
+    }
+    if (!r.ev)
+        GRB_CUDA(cudaEventCreateWithFlags(&r.ev, cudaEventDisableTiming));
+    r.used = 0;
+    r.nitems = nitems;
+    r.segs.clear();
+    lag_active = &r;
+    lag_cur ^= 1;
+    return 0;
+}
+
+static int lag_deliver(Stager::LagResult& r, void* const* outs, int nouts, long long* nitems)
+{
+    *nitems = 0;
+    if (!r.pending)
+        return 0;
+    GRB_CUDA(cudaEventSynchronize(r.ev));
+    for (const Stager::LagSeg& s : r.segs) {
+        if (s.ostream < 0 || s.ostream >= nouts || !outs[s.ostream])
+            return fail(GRB200_EINVAL, "staging: lag result for output stream %d, %d offered", s.ostream, nouts);
+        par_memcpy((char*)outs[s.ostream] + s.ooff, (const char*)r.pin + s.boff, s.bytes);
+    }
+    r.pending = false;
+    *nitems = r.nitems;
+    return 0;
+}
+
+int Stager::lag_collect(void* const* outs, int nouts, long long* nitems)
+{
+    // the result that is NOT the one just begun: lag_cur was flipped by lag_begin, so the previous call's is lag[lag_cur]
+    return lag_deliver(lag[lag_cur], outs, nouts, nitems);
+}
+
+int Stager::lag_flush(void* const* outs, int nouts, long long* nitems)
+{
+    // in submission order: the older of the two first (normally already collected), then the newest
+    long long a = 0, b = 0;
+    int rc = lag_deliver(lag[lag_cur], outs, nouts, &a);
+    if (rc)
+        return rc;
+    if (a) { // a result two calls old was still parked: hand that one out; the newest stays for another flush
+        *nitems = a;
+        return 0;
+    }
+    rc = lag_deliver(lag[lag_cur ^ 1], outs, nouts, &b);
+    *nitems = b;
+    return rc;
+}
+
+void Stager::lag_drop()
+{
+    for (auto& r : lag) {
+        if (r.pending && r.ev)
+            cudaEventSynchronize(r.ev);
+        r.pending = false;
+        r.segs.clear();
+    }
+    lag_active = nullptr;
 }
 
 } // namespace grb

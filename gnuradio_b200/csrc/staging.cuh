@@ -15,6 +15,12 @@ struct Piece {
     const void* src; // H2D: host source / D2H: device source (offset within the slot is in dst/src below)
     void* dst;
     size_t bytes;
+    // D2H only, lag-by-one mode: which output stream of the call this piece belongs to and where in it (bytes).  The result
+    // is parked in the handle and handed to the NEXT call's output buffers, whose addresses differ from this call's.
+    int ostream = 0;
+    size_t ooff = 0;
+    Piece(const void* s, void* d, size_t b) : src(s), dst(d), bytes(b) {}
+    Piece(const void* s, void* d, size_t b, int os, size_t oo) : src(s), dst(d), bytes(b), ostream(os), ooff(oo) {}
 };
 
 struct Stager {
@@ -28,6 +34,42 @@ struct Stager {
     void* dev[NSLOT][3] = {}; // [slot][in, out, scratch]
     size_t dev_cap[3] = { 0, 0, 0 };
     bool ready = false;
+    // slot state survives a run(): in lag-by-one mode a call returns with its last chunks still in flight
+    struct Bounce {
+        void* host_dst;
+        const void* pin_src;
+        size_t bytes;
+    };
+    std::vector<Bounce> bounce[NSLOT];
+    bool pending[NSLOT] = {};
+    long long next_chunk = 0; // chunks issued through this stager so far (slot = next_chunk % NSLOT)
+
+    // ---- lag-by-one mode (SURVEY.md section 7 "hard parts"): work() queues this call's chunk and hands
+    // back the PREVIOUS call's results, so H2D, kernel and D2H of call k overlap the scheduler's bookkeeping and call k+1
+    // instead of being waited for inside call k.  Legal for a gr::block: general_work may produce fewer items than it was
+    // offered and consume independently (gnuradio-runtime/include/gnuradio/block.h:160-175).
+    struct LagSeg {
+        int ostream;
+        size_t ooff, boff, bytes;
+    };
+    struct LagResult {
+        void* pin = nullptr;
+        size_t cap = 0, used = 0;
+        cudaEvent_t ev = nullptr;
+        bool pending = false;
+        long long nitems = 0;
+        std::vector<LagSeg> segs;
+    };
+    LagResult lag[2];
+    int lag_cur = 0;
+    bool lag_mode = false;
+    LagResult* lag_active = nullptr; // set between lag_begin() and the end of run()
+    int lag_begin(size_t out_bytes, long long npieces, long long nitems); // reserve the parking buffer of this call
+    // hand the previous call's results to `outs` (base address of every output stream); returns its item count in *nitems
+    int lag_collect(void* const* outs, int nouts, long long* nitems);
+    int lag_flush(void* const* outs, int nouts, long long* nitems); // the call still in flight (end of stream)
+    void lag_drop();                                                // forget parked results (set_taps, stop)
+
     // last *_work_dev launch on a CALLER's stream: setters wait for it (and for the handle's own streams) instead of
     // stalling the whole device with cudaDeviceSynchronize
     cudaEvent_t ev_user = nullptr;
@@ -41,6 +83,7 @@ struct Stager {
     int reserve_dev(int which, size_t bytes);  // both slots
     int reserve_pin(bool in, size_t bytes);    // both slots
     static bool is_pinned(const void* p);
+    int retire(int slot);
 
     // One chunk's description, filled by the `plan` callback:
     //   h2d : pieces {host src, device dst (inside dev[slot][0]), bytes}
@@ -53,6 +96,9 @@ struct Stager {
     using LaunchFn = std::function<int(long long c, int slot, cudaStream_t st)>;
     int run(long long nchunks, const PlanFn& plan, const LaunchFn& launch);
 };
+
+void par_memcpy(void* dst, const void* src, size_t bytes); // big copies sliced over a small helper-thread pool
+void pin_cache_invalidate();                               // after cudaHostRegister / Unregister / free of pinned memory
 
 // One Stager per device for the handle-less entry points (complex_to_mag_squared, vector_to_streams): created on first use,
 // lives for the process.  Host-staged calls through it hold shared_stager_mutex(device) for their duration.

@@ -94,6 +94,32 @@ class _fir_filter_blk(sync_decimator):
                                                   int(noutput_items), C.c_void_p(stream)))
         return int(noutput_items)
 
+    def general_work_lag(self, noutput_items, input_items, output_items):
+        """Lag-by-one host mode (include/grb200.h "Host staging"): takes the input of `noutput_items` outputs now, writes the
+        PREVIOUS call's outputs into output_items[0] and returns how many -- 0 on the first call.  consume = this call's
+        noutput_items * decimation (self._consumed), like a gr::block that consumes and produces independently."""
+        with self.d_setlock:
+            if self.d_updated:
+                self.set_history(len(self._taps))
+                self.d_updated = False
+                self._consumed = 0
+                return 0
+            n = int(noutput_items)
+            need = n * self.decimation() + len(self._taps) - 1
+            xin = as_items(input_items[0], self._item, need if n else 0, "input_items[0]")
+            out = output_items[0]
+            got = C.c_longlong(0)
+            _lib.check(_lib.lib().grb200_fir_work_lag(self._h, _ptr(xin), n, _ptr(out), out.size, C.byref(got)))
+            self._consumed = n * self.decimation()
+            return got.value
+
+    def flush(self, output_items):
+        """End of stream in lag mode: the outputs of the call still in flight."""
+        out = output_items[0]
+        got = C.c_longlong(0)
+        _lib.check(_lib.lib().grb200_fir_flush(self._h, _ptr(out), out.size, C.byref(got)))
+        return got.value
+
     def process(self, xin, noutput_items):
         """Convenience: one work() call on `xin` (history items first); returns the output array."""
         xin = np.ascontiguousarray(xin, self._item)
@@ -660,6 +686,37 @@ class pfb_channelizer_ccf(block):
                                                                   C.byref(consumed)))
         self.consume_each(consumed.value)
         return n
+
+    def work_lag(self, input_items, output_items, noutput_items, interleaved=False):
+        """Lag-by-one host mode: queues this call (M streams, or ONE interleaved stream when `interleaved`), writes the
+        previous call's outputs to output_items and returns how many items per stream (0 on the first call)."""
+        n = int(noutput_items)
+        M, T = self._M, self.d_taps_per_filter
+        nouts = len(output_items)
+        outp = (C.c_void_p * nouts)(*[a.ctypes.data for a in output_items])
+        cap = min(a.size for a in output_items)
+        consumed, got = C.c_longlong(0), C.c_longlong(0)
+        with self.d_setlock:
+            self.d_updated = False
+            if interleaved:
+                xin = as_items(input_items, _c64, (self._toconsume(n) + T) * M if n else 0, "input")
+                _lib.check(_lib.lib().grb200_pfb_chan_work_interleaved_lag(self._h, _ptr(xin), n, outp, nouts, cap,
+                                                                          C.byref(consumed), C.byref(got)))
+            else:
+                ins = [as_items(a, _c64, self._toconsume(n) + T if n else 0, "input_items[%d]" % j)
+                       for j, a in enumerate(input_items)]
+                inp = (C.c_void_p * M)(*[a.ctypes.data for a in ins])
+                _lib.check(_lib.lib().grb200_pfb_chan_work_lag(self._h, inp, n, outp, nouts, cap, C.byref(consumed),
+                                                              C.byref(got)))
+        self.consume_each(consumed.value)
+        return got.value
+
+    def flush(self, output_items):
+        nouts = len(output_items)
+        outp = (C.c_void_p * nouts)(*[a.ctypes.data for a in output_items])
+        got = C.c_longlong(0)
+        _lib.check(_lib.lib().grb200_pfb_chan_flush(self._h, outp, nouts, min(a.size for a in output_items), C.byref(got)))
+        return got.value
 
     def work_interleaved_dev(self, in_dev, out_dev, out_stride, nout_streams, noutput_items, stream=0):
         _lib.check(_lib.lib().grb200_pfb_chan_work_interleaved_dev(

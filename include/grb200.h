@@ -18,6 +18,14 @@
  *                   (a cudaStream_t passed as void*; NULL = CUDA's legacy default stream, as everywhere else in
  *                   CUDA -- so a producer, work_dev and a consumer on one stream are ordered; GRB200_STREAM_OWN =
  *                   the handle's private non-blocking stream).  set_* waits for the handle's own work only.
+ *  - Host staging.  A `*_work` call larger than 1 MiB is cut into chunks (at least four; 64 MiB for big calls,
+ *    GRB200_CHUNK_MB) that run H2D | kernel | D2H concurrently on three streams.  Page-locked caller memory (grb200_host_alloc,
+ *    grb200_host_register, cudaHostRegister, torch pinned tensors) is copied directly; pageable memory -- what a gr::buffer is
+ *    -- goes through pinned bounce slots, filled by a small pool of copy threads (GRB200_COPY_THREADS, default 4).
+ *    `*_work_lag` (fir_filter, pfb_channelizer): the call returns as soon as its INPUT has been taken and delivers the
+ *    previous call's results, so nothing is waited for inside work() but the copy of its own input; results are one call
+ *    late.  A gr::block may do this (general_work produces fewer items than offered and consumes on its own,
+ *    gnuradio-runtime/include/gnuradio/block.h:160-175); INTEGRATION.md shows the block side.
  *  - One handle <-> one calling thread for work(); set_* may come from any thread (internally serialised,
  *    mirroring d_setlock / d_mutex in the reference blocks).
  *  - There is no CPU fallback: every call fails with GRB200_ECUDA when no sm_100 device is usable.
@@ -51,6 +59,9 @@ unsigned long long grb200_launch_count(void);
 /* Pinned host buffers for callers that want zero-bounce staging (optional). */
 int grb200_host_alloc(void** ptr, unsigned long long bytes);
 int grb200_host_free(void* ptr);
+/* Page-lock memory the caller owns (a gr::buffer's circular buffer, a numpy array) for direct DMA; unregister before freeing. */
+int grb200_host_register(void* ptr, unsigned long long bytes);
+int grb200_host_unregister(void* ptr);
 /* Device buffers for the device-resident mode (thin cudaMalloc/cudaFree/cudaMemcpy wrappers, so a C++
  * block can chain handles without linking the CUDA runtime itself). */
 int grb200_dev_alloc(int device, void** ptr, unsigned long long bytes);
@@ -79,6 +90,12 @@ int grb200_fir_ntaps(const grb200_fir* h);
 int grb200_fir_decimation(const grb200_fir* h);
 int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long long noutput);
 int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long long noutput, void* stream);
+/* Lag-by-one host mode (see "Host staging" below): queues this call's `noutput` items and writes the PREVIOUS call's results
+ * to out_host (room for out_capacity items; GRB200_EINVAL when more are waiting); *produced = how many.  The first call
+ * produces 0.  flush() hands out the call still in flight (end of stream; *produced = 0 when nothing is parked). */
+int grb200_fir_work_lag(grb200_fir* h, const void* in_host, long long noutput, void* out_host, long long out_capacity,
+                        long long* produced);
+int grb200_fir_flush(grb200_fir* h, void* out_host, long long out_capacity, long long* produced);
 void grb200_fir_destroy(grb200_fir* h);
 
 /* ---- freq_xlating_fir_filter_ccf / freq_xlating_fir_filter_ccc ----------------------------------
@@ -165,6 +182,14 @@ int grb200_pfb_chan_work(grb200_pfb* h, const void* const* in_streams, void* con
  * (taps_per_filter + consumed) * numchans interleaved items, history rows first. */
 int grb200_pfb_chan_work_interleaved(grb200_pfb* h, const void* in_host, void* const* out_streams,
                                      int nout_streams, long long noutput, long long* consumed);
+/* Lag-by-one host forms of the two calls above (see grb200_fir_work_lag): this call's inputs are queued, the previous call's
+ * outputs delivered; out_capacity = room per output stream. */
+int grb200_pfb_chan_work_lag(grb200_pfb* h, const void* const* in_streams, long long noutput, void* const* out_streams,
+                             int nout_streams, long long out_capacity, long long* consumed, long long* produced);
+int grb200_pfb_chan_work_interleaved_lag(grb200_pfb* h, const void* in_host, long long noutput, void* const* out_streams,
+                                         int nout_streams, long long out_capacity, long long* consumed, long long* produced);
+int grb200_pfb_chan_flush(grb200_pfb* h, void* const* out_streams, int nout_streams, long long out_capacity,
+                          long long* produced);
 int grb200_pfb_chan_work_interleaved_dev(grb200_pfb* h, const void* in_dev, void* out_dev,
                                          long long out_stride, int nout_streams, long long noutput,
                                          void* stream);
