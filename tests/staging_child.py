@@ -120,7 +120,7 @@ grb.blocks.complex_to_mag_squared().work(N, [xv], [y])
 res["magsq"] = y.copy()
 lp = grb.fft.logpwrfft_c(1024.0 * 2, 1024, 2.0, 1.0, 0.2, True)
 y = buf(N // 2, np.float32)
-k = lp.general_work(N // 1024, [N], [xv], [y])
+k = lp.general_work(N // 2048, [N], [xv], [y])
 res["logpwr"] = y[: k * 1024].copy()
 y = buf(2 * N, np.complex64)
 grb.fft.fft_vfc(1024, True, []).work(2 * N // 1024, [xf], [y])
