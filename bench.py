@@ -750,6 +750,195 @@ def run_parity(torch, wl):
         return {"error": repr(e)[:300], "ok": False}
 
 
+# ---------------------------------------------------------------------------------------------------------
+# End-to-end through the host-buffer C-ABI, shaped like a flowgraph: the stream is handed to the block in calls of
+# `call_items` items -- what block_executor does with a block whose buffers hold that much (gnuradio-runtime/lib/
+# block_executor.cc:61-84; 4096 items at the default 32 KiB buffers, 2^22 after INTEGRATION.md's set_min_output_buffer) --
+# history carried in front of every call like the scheduler's read pointer does, out of host memory that is either page-locked
+# (cudaHostAlloc), registered (plain memory + cudaHostRegister, what an integration can do once for its gr::buffers) or
+# pageable (a gr::buffer as it comes).  mode "blocking": work() returns when its outputs are valid; "lag": work() returns the
+# previous call's outputs (grb200_*_work_lag).  Calls go straight through ctypes with precomputed addresses.
+# ---------------------------------------------------------------------------------------------------------
+class HostMem:
+    def __init__(self, grb, kind):
+        self.grb, self.kind, self.keep = grb, kind, []
+
+    def alloc(self, shape, dtype=np.complex64):
+        import ctypes as C
+
+        from gnuradio_b200 import _lib
+
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape))
+        if self.kind == "pinned":
+            p = C.c_void_p()
+            _lib.check(_lib.lib().grb200_host_alloc(C.byref(p), max(n * dtype.itemsize, 64)))
+            a = np.frombuffer((C.c_char * (n * dtype.itemsize)).from_address(p.value), dtype=dtype).reshape(shape)
+            self.keep.append(("alloc", p))
+        else:
+            a = np.empty(shape, dtype)
+            if self.kind == "registered":
+                self.grb.host_register(a)
+                self.keep.append(("reg", a))
+        return a
+
+    def free(self):
+        from gnuradio_b200 import _lib
+
+        for what, obj in self.keep:
+            if what == "alloc":
+                _lib.lib().grb200_host_free(obj)
+            else:
+                self.grb.host_unregister(obj)
+        self.keep = []
+
+
+class E2E:
+    """One block + one kind of host memory, buffers allocated once for `max_items`; run() pushes a stream through it in calls
+    of `call_items` items."""
+
+    def __init__(self, grb, device, block, mem, max_items):
+        self.grb, self.block, self.mem = grb, block, mem
+        self.hm = HostMem(grb, mem)
+        if block == "fir":
+            self.nt = 64
+            self.blk = grb.filter.fir_filter_ccf(1, lowpass(self.nt, 0.1, hamming(self.nt)), device=device)
+            self.x = self.hm.alloc(max_items + self.nt - 1)
+            self.y = self.hm.alloc(max_items)
+            self.x.view(np.float32)[:] = 0.25
+            self.y.view(np.float32)[:] = 0
+        else:
+            self.M, self.T = 64, 16
+            M, T = self.M, self.T
+            self.blk = grb.filter.pfb_channelizer_ccf(M, lowpass(M * T, 0.5 / M, blackman_harris(M * T)) * np.float32(M), 1.0,
+                                                      device=device)
+            self.nout_max = max_items // M
+            self.outs = self.hm.alloc((M, self.nout_max))
+            self.outs.view(np.float32)[:] = 0
+            self.x = self.hm.alloc((self.nout_max + T) * M) if block == "pfb_interleaved" else self.hm.alloc((M, self.nout_max + T))
+            self.x.view(np.float32)[:] = 0.25
+
+    def close(self):
+        self.blk = None
+        self.hm.free()
+
+    def run(self, call_items, total_items, mode, reps=1, dist=None, torch=None):
+        """Returns (Msps, h2d_bytes_per_call, d2h_bytes_per_call, calls) or None when the call size does not apply."""
+        import ctypes as C
+
+        from gnuradio_b200 import _lib
+
+        L = _lib.lib()
+        got, used = C.c_longlong(0), C.c_longlong(0)
+        h = self.blk._h
+        if self.block == "fir":
+            ncalls = max(1, total_items // call_items)
+            total = ncalls * call_items
+            xp, yp = self.x.ctypes.data, self.y.ctypes.data
+            bi, bo = (call_items + self.nt - 1) * 8, call_items * 8
+
+            def run_once():
+                if mode == "lag":
+                    done = 0
+                    for c in range(ncalls):
+                        rc = L.grb200_fir_work_lag(h, C.c_void_p(xp + c * call_items * 8), call_items, C.c_void_p(yp + done * 8),
+                                                   call_items, C.byref(got))
+                        if rc:
+                            _lib.check(rc)
+                        done += got.value
+                    L.grb200_fir_flush(h, C.c_void_p(yp + done * 8), call_items, C.byref(got))
+                    return done + got.value
+                for c in range(ncalls):
+                    rc = L.grb200_fir_work(h, C.c_void_p(xp + c * call_items * 8), C.c_void_p(yp + c * call_items * 8), call_items)
+                    if rc:
+                        _lib.check(rc)
+                return total
+        else:
+            M, T = self.M, self.T
+            nout_call = call_items // M
+            if nout_call < 1:
+                return None
+            ncalls = max(1, (total_items // M) // nout_call)
+            total = ncalls * nout_call * M
+            inter = self.block == "pfb_interleaved"
+            xp = self.x.ctypes.data
+            rowp = None if inter else [self.x[j].ctypes.data for j in range(M)]
+            orow = [self.outs[j].ctypes.data for j in range(M)]
+            bi, bo = (nout_call + T) * M * 8, nout_call * M * 8
+            VP = C.c_void_p * M
+
+            def run_once():
+                done = 0
+                for c in range(ncalls):
+                    op = VP(*[o + (done if mode == "lag" else c * nout_call) * 8 for o in orow])
+                    if inter:
+                        src = C.c_void_p(xp + c * nout_call * M * 8)
+                        if mode == "lag":
+                            rc = L.grb200_pfb_chan_work_interleaved_lag(h, src, nout_call, op, M, nout_call, C.byref(used), C.byref(got))
+                        else:
+                            rc = L.grb200_pfb_chan_work_interleaved(h, src, op, M, nout_call, C.byref(used))
+                    else:
+                        ip = VP(*[r + c * nout_call * 8 for r in rowp])
+                        if mode == "lag":
+                            rc = L.grb200_pfb_chan_work_lag(h, ip, nout_call, op, M, nout_call, C.byref(used), C.byref(got))
+                        else:
+                            rc = L.grb200_pfb_chan_work(h, ip, op, M, nout_call, C.byref(used))
+                    if rc:
+                        _lib.check(rc)
+                    done += got.value if mode == "lag" else nout_call
+                if mode == "lag":
+                    op = VP(*[o + done * 8 for o in orow])
+                    L.grb200_pfb_chan_flush(h, op, M, nout_call, C.byref(got))
+                    done += got.value
+                return done * M
+
+        n = run_once()  # warm-up: page faults, staging buffers, the lag ring
+        assert n == total, (n, total)
+        if dist is not None:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            run_once()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        return total * reps / dt / 1e6, bi, bo, ncalls
+
+
+def pcie_probe(torch, dist, seconds=0.25):
+    """Page-locked H2D and D2H copies running at once on this rank's GPU, every rank at the same time: the per-rank rate each
+    way (GB/s) -- the ceiling of any host-staged path on this box at this rank count."""
+    n = 1 << 28
+    h_in = torch.empty(n, dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(n, dtype=torch.uint8).pin_memory()
+    d_in = torch.empty(n, dtype=torch.uint8, device="cuda")
+    d_out = torch.empty(n, dtype=torch.uint8, device="cuda")
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def go(reps):
+        for _ in range(reps):
+            with torch.cuda.stream(s1):
+                d_in.copy_(h_in, non_blocking=True)
+            with torch.cuda.stream(s2):
+                h_out.copy_(d_out, non_blocking=True)
+        torch.cuda.synchronize()
+
+    go(1)
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    reps = 4
+    go(reps)
+    dt = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    return reps * n / dt / 1e9
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -761,6 +950,7 @@ def main():
     ap.add_argument("--no-others", action="store_true", help="skip the other BASELINE configs at N=1")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the e2e call-size sweep (N=1 only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "grb200" else args.warmup
     wl_cls = WORKLOADS[args.workload]
@@ -845,29 +1035,55 @@ def main():
         "roofline": roofline, "parity": parity, "gpu_launches": launches_timed, "gpu_launches_total_process": launches,
     }
 
-    if not args.no_e2e and hasattr(wl, "e2e_setup"):
-        # every rank pushes its own host-resident segment through the host-buffer C-ABI call (its own PCIe link);
-        # barrier on both sides, max over ranks
-        bi, bo = wl.e2e_setup(28)
-        for _ in range(2):
-            wl.e2e_step()
-        ksteps = max(3, min(args.steps, 8))
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(ksteps):
-            wl.e2e_step()  # blocking: returns when the host output buffers are valid
-        torch.cuda.synchronize()
-        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-        if dist is not None:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        dt = float(te.item())
-        line["e2e"] = {"value": wl.e2e_n * world * ksteps / dt / 1e6, "unit": "Msps", "h2d_bytes_per_step": bi * world,
-                       "d2h_bytes_per_step": bo * world, "steps": ksteps,
-                       "call": "grb200_pfb_chan_work_interleaved (pinned host in/out, 2^28 samples per step per GPU)",
-                       "pcie_gbs_each_way": bi * world * ksteps / dt / 1e9}
+    if not args.no_e2e and args.workload == "pfb":
+        # Headline e2e: the call a GNU Radio user's flowgraph makes after INTEGRATION.md's edits -- pfb.channelizer_ccf (one
+        # interleaved stream in, 64 streams out) handed 2^22 items per work() out of PAGEABLE memory (a gr::buffer), lag-by-one.
+        # Every rank pushes its own stream through its own GPU; barrier on both sides, max over ranks.
+        wl.free()
+        probe = pcie_probe(torch, dist)
+        items_call, total = 1 << 22, 1 << 27
+        e = E2E(grb, local, "pfb_interleaved", "pageable", total)
+        msps, bi, bo, ncalls = e.run(items_call, total, "lag", reps=2, dist=dist, torch=torch)
+        e.close()
+        e = E2E(grb, local, "pfb_interleaved", "pinned", 1 << 28)
+        best, _, _, _ = e.run(1 << 28, 1 << 28, "blocking", reps=2, dist=dist, torch=torch)
+        e.close()
+        gbs = msps * 1e6 * 8 / 1e9
+        line["e2e"] = {"value": msps * world, "unit": "Msps", "h2d_bytes_per_step": bi * world, "d2h_bytes_per_step": bo * world,
+                       "steps": 2 * ncalls, "step": "one work() call of 2^22 items per GPU",
+                       "call": "grb200_pfb_chan_work_interleaved_lag: 2^22 items per call, pageable host buffers, lag-by-one",
+                       "gbs_each_way_per_gpu": gbs, "pcie_probe_gbs_each_way_per_gpu": probe,
+                       "frac_of_pcie_probe": gbs / probe,
+                       "best_case": {"value": best * world, "unit": "Msps", "frac_of_pcie_probe": best * 8e-3 / probe,
+                                     "call": "grb200_pfb_chan_work_interleaved: one 2^28-item call, page-locked buffers (the "
+                                             "round-1 e2e figure)"}}
         line["gpu_launches_e2e"] = grb.launch_count() - launches0 - launches
+        if rank == 0 and world == 1 and not args.no_sweep:
+            sweep = {}
+            for block in ("fir", "pfb_streams", "pfb_interleaved"):
+                sweep[block] = {}
+                for mem in ("pinned", "registered", "pageable"):
+                    try:
+                        e = E2E(grb, local, block, mem, 1 << 28)
+                    except Exception as ex:
+                        sweep[block][mem] = {"error": repr(ex)[:160]}
+                        continue
+                    for mode in ("blocking", "lag"):
+                        row = {}
+                        for lg in (12, 16, 20, 22, 28):
+                            items = 1 << lg
+                            tot = min(1 << 28, max(items, min(items * 256, 1 << 26)))
+                            try:
+                                r = e.run(items, tot, mode, reps=1)
+                                row["2^%d" % lg] = None if r is None else {"msps": round(r[0], 1), "frac_of_pcie_probe":
+                                                                           round(r[0] * 8e-3 / probe, 3), "calls": r[3]}
+                            except Exception as ex:
+                                row["2^%d" % lg] = {"error": repr(ex)[:120]}
+                        sweep[block]["%s/%s" % (mem, mode)] = row
+                    e.close()
+            line["e2e_sweep"] = {"unit": "Msps of input through the host-buffer C-ABI, H2D + kernel + D2H per call",
+                                 "items_per_call": "2^12 (default gr::buffer) .. 2^28", "pcie_probe_gbs_each_way": probe,
+                                 "blocks": sweep}
 
     with ClockSampler(local) as _:
         pass
