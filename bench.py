@@ -842,11 +842,11 @@ class E2E:
                     done = 0
                     for c in range(ncalls):
                         rc = L.grb200_fir_work_lag(h, C.c_void_p(xp + c * call_items * 8), call_items, C.c_void_p(yp + done * 8),
-                                                   call_items, C.byref(got))
+                                                   total - done, C.byref(got))
                         if rc:
                             _lib.check(rc)
                         done += got.value
-                    L.grb200_fir_flush(h, C.c_void_p(yp + done * 8), call_items, C.byref(got))
+                    L.grb200_fir_flush(h, C.c_void_p(yp + done * 8), total - done, C.byref(got))
                     return done + got.value
                 for c in range(ncalls):
                     rc = L.grb200_fir_work(h, C.c_void_p(xp + c * call_items * 8), C.c_void_p(yp + c * call_items * 8), call_items)
@@ -860,6 +860,7 @@ class E2E:
                 return None
             ncalls = max(1, (total_items // M) // nout_call)
             total = ncalls * nout_call * M
+            nout_all = ncalls * nout_call
             inter = self.block == "pfb_interleaved"
             xp = self.x.ctypes.data
             rowp = None if inter else [self.x[j].ctypes.data for j in range(M)]
@@ -874,13 +875,13 @@ class E2E:
                     if inter:
                         src = C.c_void_p(xp + c * nout_call * M * 8)
                         if mode == "lag":
-                            rc = L.grb200_pfb_chan_work_interleaved_lag(h, src, nout_call, op, M, nout_call, C.byref(used), C.byref(got))
+                            rc = L.grb200_pfb_chan_work_interleaved_lag(h, src, nout_call, op, M, nout_all - done, C.byref(used), C.byref(got))
                         else:
                             rc = L.grb200_pfb_chan_work_interleaved(h, src, op, M, nout_call, C.byref(used))
                     else:
                         ip = VP(*[r + c * nout_call * 8 for r in rowp])
                         if mode == "lag":
-                            rc = L.grb200_pfb_chan_work_lag(h, ip, nout_call, op, M, nout_call, C.byref(used), C.byref(got))
+                            rc = L.grb200_pfb_chan_work_lag(h, ip, nout_call, op, M, nout_all - done, C.byref(used), C.byref(got))
                         else:
                             rc = L.grb200_pfb_chan_work(h, ip, op, M, nout_call, C.byref(used))
                     if rc:
@@ -888,12 +889,14 @@ class E2E:
                     done += got.value if mode == "lag" else nout_call
                 if mode == "lag":
                     op = VP(*[o + done * 8 for o in orow])
-                    L.grb200_pfb_chan_flush(h, op, M, nout_call, C.byref(got))
+                    L.grb200_pfb_chan_flush(h, op, M, nout_all - done, C.byref(got))
                     done += got.value
                 return done * M
 
         n = run_once()  # warm-up: page faults, staging buffers, the lag ring
         assert n == total, (n, total)
+        if mode == "lag" and ncalls < 2:
+            run_once()  # the two parking buffers of the lag ring alternate per call: touch both before timing
         if dist is not None:
             dist.barrier()
         t0 = time.perf_counter()

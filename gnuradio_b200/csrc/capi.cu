@@ -275,6 +275,7 @@ static int fir_work_host(grb200_fir* h, const void* in_host, void* out_host, lon
     const char* in = (const char*)in_host;
     char* out = (char*)out_host;
     Stager& sg = h->sg;
+    void* lag_out1[1] = { nullptr };
     if (lag) {
         // the previous call's result must fit what the caller offers now (the block mirrors submit equal-sized calls)
         const Stager::LagResult& prev = sg.lag[sg.lag_cur ^ 1];
@@ -282,6 +283,11 @@ static int fir_work_host(grb200_fir* h, const void* in_host, void* out_host, lon
             return fail(GRB200_EINVAL, "fir_filter::work_lag: %lld items are waiting, room for %lld offered", prev.nitems, out_cap);
         if ((rc = sg.lag_begin((size_t)noutput * isz, nchunks, noutput)))
             return rc;
+        const long long nprev = prev.pending ? prev.nitems : 0;
+        if (out_host && nprev + noutput <= out_cap) { // room behind the previous call's items: deliver in place
+            lag_out1[0] = out_host;
+            sg.lag_direct(lag_out1, 1, (size_t)nprev * isz);
+        }
     }
     rc = sg.run(
         nchunks,

@@ -226,8 +226,14 @@ static int pfb_work_host(grb200_pfb* p, int interleaved, const void* const* in_s
     if ((rc = sg.reserve_dev(0, (size_t)rows_chunk * M * 8)) || (rc = sg.reserve_dev(1, (size_t)chunk * nouts * 8)) ||
         (!interleaved && (rc = sg.reserve_dev(2, (size_t)rows_chunk * M * 8))))
         return rc;
-    if (lag && (rc = sg.lag_begin((size_t)noutput * nouts * 8, nchunks * nouts, noutput)))
-        return rc;
+    if (lag) {
+        const Stager::LagResult& newest = sg.lag[sg.lag_cur ^ 1];
+        const long long nprev = newest.pending ? newest.nitems : 0;
+        if ((rc = sg.lag_begin((size_t)noutput * nouts * 8, nchunks * nouts, noutput)))
+            return rc;
+        if (nprev + noutput <= out_cap) // room behind the previous call's items in every output stream: deliver in place
+            sg.lag_direct(out_streams, nouts, (size_t)nprev * 8);
+    }
     rc = sg.run(
         nchunks,
         [&](long long c, int slot, Stager::Chunk& ch) {

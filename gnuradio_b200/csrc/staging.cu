@@ -204,7 +204,7 @@ bool Stager::is_pinned(const void* p)
 
 // ---- parallel memcpy for the pageable bounce ---------------------------------------------------------------------
 // One thread copies 10-12 GB/s; PCIe 5 moves 50+.  Copies of a MiB or more are cut into slices for a small pool of helper
-// threads (GRB200_COPY_THREADS, default 4, 0 = inline), started on first use and shared by every handle of the process.
+// threads (GRB200_COPY_THREADS, default 8, at most half the cores, 0 = inline), started on first use and shared by every handle of the process.
 namespace {
 struct CopyPool {
     struct Job {
@@ -222,7 +222,7 @@ struct CopyPool {
     CopyPool()
     {
         const char* e = getenv("GRB200_COPY_THREADS");
-        n = e ? atoi(e) : 4;
+        n = e ? atoi(e) : 8;
         unsigned hw = std::thread::hardware_concurrency();
         if (hw && (unsigned)n > hw / 2)
             n = (int)(hw / 2);
@@ -256,24 +256,37 @@ struct CopyPool {
                 cv_done.notify_all();
         }
     }
-    void copy(void* dst, const void* src, size_t bytes)
+    // run a list of copies: big ones are cut into slices; helpers and the caller all pull from the same list
+    void run(const std::vector<Job>& list)
     {
-        const size_t kMin = (size_t)1 << 20;
-        if (n == 0 || bytes < 2 * kMin) {
-            memcpy(dst, src, bytes);
-            return;
-        }
-        size_t parts = std::min<size_t>((size_t)n + 1, bytes / kMin);
-        size_t per = ((bytes + parts - 1) / parts + 63) & ~(size_t)63;
+        const size_t kSlice = (size_t)1 << 20;
         std::unique_lock<std::mutex> lk(mu);
         jobs.clear();
         next = done = 0;
-        for (size_t o = per; o < bytes; o += per) // slice 0 is the caller's own
-            jobs.push_back({ (char*)dst + o, (const char*)src + o, std::min(per, bytes - o) });
+        for (const Job& j : list) {
+            if (j.bytes == 0)
+                continue;
+            if (j.bytes <= 2 * kSlice) {
+                jobs.push_back(j);
+                continue;
+            }
+            const size_t parts = std::min<size_t>((size_t)(n + 1) * 2, j.bytes / kSlice);
+            const size_t per = ((j.bytes + parts - 1) / parts + 63) & ~(size_t)63;
+            for (size_t o = 0; o < j.bytes; o += per)
+                jobs.push_back({ j.dst + o, j.src + o, std::min(per, j.bytes - o) });
+        }
+        if (jobs.empty())
+            return;
         lk.unlock();
         cv_work.notify_all();
-        memcpy(dst, src, std::min(per, bytes));
         lk.lock();
+        while (next < jobs.size()) { // the caller works too
+            const Job j = jobs[next++];
+            lk.unlock();
+            memcpy(j.dst, j.src, j.bytes);
+            lk.lock();
+            ++done;
+        }
         cv_done.wait(lk, [this] { return done == jobs.size(); });
         jobs.clear();
         next = done = 0;
@@ -287,14 +300,32 @@ CopyPool& copy_pool()
 }
 } // namespace
 
-void par_memcpy(void* dst, const void* src, size_t bytes)
+// Copies below this total are done inline: waking the helpers costs more than it saves
+static const size_t kParMin = (size_t)512 << 10;
+
+void par_memcpy_many(const std::vector<CopyJob>& list)
 {
-    if (bytes < ((size_t)2 << 20)) {
-        memcpy(dst, src, bytes);
+    size_t total = 0;
+    for (const CopyJob& j : list)
+        total += j.bytes;
+    if (total < kParMin || copy_pool().n == 0) {
+        for (const CopyJob& j : list)
+            if (j.bytes)
+                memcpy(j.dst, j.src, j.bytes);
         return;
     }
+    std::vector<CopyPool::Job> jobs;
+    jobs.reserve(list.size());
+    for (const CopyJob& j : list)
+        jobs.push_back({ (char*)j.dst, (const char*)j.src, j.bytes });
     std::lock_guard<std::mutex> lk(g_pool_mu);
-    copy_pool().copy(dst, src, bytes);
+    copy_pool().run(jobs);
+}
+
+void par_memcpy(void* dst, const void* src, size_t bytes)
+{
+    std::vector<CopyJob> one(1, CopyJob{ dst, src, bytes });
+    par_memcpy_many(one);
 }
 
 static std::mutex g_shared_mu;
@@ -351,8 +382,13 @@ int Stager::retire(int slot)
     if (!pending[slot])
         return 0;
     GRB_CUDA(cudaEventSynchronize(ev_d2h[slot]));
-    for (auto& b : bounce[slot])
-        par_memcpy(b.host_dst, b.pin_src, b.bytes);
+    if (!bounce[slot].empty()) {
+        std::vector<CopyJob> jobs;
+        jobs.reserve(bounce[slot].size());
+        for (auto& b : bounce[slot])
+            jobs.push_back({ b.host_dst, b.pin_src, b.bytes });
+        par_memcpy_many(jobs);
+    }
     bounce[slot].clear();
     pending[slot] = false;
     return 0;
@@ -363,7 +399,12 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
     Chunk ch;
     LagResult* lr = lag_active;
     lag_active = nullptr; // whatever happens below, the next call starts clean
+    void* const* louts = lag_outs;
+    const int lnouts = lag_nouts;
+    const size_t lshift = lag_shift;
+    lag_outs = nullptr;
     int last_slot = -1;
+    bool direct_in = false; // some H2D copy reads the caller's memory itself (page-locked input)
     for (long long c = 0; c < nchunks; c++, next_chunk++) {
         const int slot = (int)(next_chunk % NSLOT);
         int rc = retire(slot);
@@ -397,18 +438,49 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
         }
         size_t off = 0, spitch = 0, dpitch = 0;
         const bool h2d_2d = strided_group(ch.h2d, pinned_in, &spitch, &dpitch);
-        if (h2d_2d)
+        if (h2d_2d) {
             GRB_CUDA(cudaMemcpy2DAsync(ch.h2d[0].dst, dpitch, ch.h2d[0].src, spitch, ch.h2d[0].bytes, ch.h2d.size(),
                                        cudaMemcpyHostToDevice, s_h2d));
-        for (size_t k = 0; k < ch.h2d.size() && !h2d_2d; k++) {
+            direct_in = true;
+        }
+        if (!h2d_2d && need_in) { // all pageable pieces of the chunk into the bounce slot at once, over the copy threads
+            std::vector<CopyJob> jobs;
+            size_t o2 = 0;
+            for (size_t k = 0; k < ch.h2d.size(); k++) {
+                if (pinned_in[k] || ch.h2d[k].bytes == 0)
+                    continue;
+                jobs.push_back({ (char*)pin_in[slot] + o2, ch.h2d[k].src, ch.h2d[k].bytes });
+                o2 += (ch.h2d[k].bytes + 255) & ~(size_t)255;
+            }
+            par_memcpy_many(jobs);
+        }
+        bool bounce_2d = false;
+        if (!h2d_2d && need_in && ch.h2d.size() >= 4) { // every piece bounced, equal sizes, constant device pitch: one copy
+            std::vector<Piece> bp = ch.h2d;
+            std::vector<char> allp(bp.size(), 1);
+            size_t o2 = 0;
+            bool all_pageable = true;
+            for (size_t k = 0; k < bp.size(); k++) {
+                if (pinned_in[k] || bp[k].bytes == 0)
+                    all_pageable = false;
+                bp[k].src = (char*)pin_in[slot] + o2;
+                o2 += (bp[k].bytes + 255) & ~(size_t)255;
+            }
+            if (all_pageable && strided_group(bp, allp, &spitch, &dpitch)) {
+                GRB_CUDA(cudaMemcpy2DAsync(bp[0].dst, dpitch, bp[0].src, spitch, bp[0].bytes, bp.size(), cudaMemcpyHostToDevice,
+                                           s_h2d));
+                bounce_2d = true;
+            }
+        }
+        for (size_t k = 0; k < ch.h2d.size() && !h2d_2d && !bounce_2d; k++) {
             const Piece& p = ch.h2d[k];
             if (p.bytes == 0)
                 continue;
             if (pinned_in[k]) {
                 GRB_CUDA(cudaMemcpyAsync(p.dst, p.src, p.bytes, cudaMemcpyHostToDevice, s_h2d));
+                direct_in = true;
             } else {
                 char* b = (char*)pin_in[slot] + off;
-                par_memcpy(b, p.src, p.bytes);
                 GRB_CUDA(cudaMemcpyAsync(p.dst, b, p.bytes, cudaMemcpyHostToDevice, s_h2d));
                 off += (p.bytes + 255) & ~(size_t)255;
             }
@@ -421,22 +493,82 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
         GRB_CUDA(cudaEventRecord(ev_exec[slot], s_exec));
         GRB_CUDA(cudaStreamWaitEvent(s_d2h, ev_exec[slot], 0));
         off = 0;
-        if (lr) { // lag-by-one: results are parked in the handle's pinned buffer, the caller's memory is not touched now
-            for (const Piece& p : ch.d2h) {
-                if (p.bytes == 0)
-                    continue;
-                if (lr->used + p.bytes > lr->cap)
-                    return fail(GRB200_ECUDA, "staging: lag buffer overflow (%zu + %zu > %zu)", lr->used, p.bytes, lr->cap);
-                GRB_CUDA(cudaMemcpyAsync((char*)lr->pin + lr->used, p.src, p.bytes, cudaMemcpyDeviceToHost, s_d2h));
-                lr->segs.push_back({ p.ostream, p.ooff, lr->used, p.bytes });
-                lr->used += (p.bytes + 63) & ~(size_t)63;
+        if (lr) { // lag-by-one: delivered in place where the caller's output is page-locked, else parked in the handle
+            // in place: the caller's buffers, shifted behind the previous call's items
+            std::vector<char> direct(ch.d2h.size(), 0);
+            std::vector<Piece> tgt = ch.d2h;
+            bool all_direct = louts != nullptr && !ch.d2h.empty();
+            for (size_t k = 0; k < ch.d2h.size(); k++) {
+                const Piece& p = ch.d2h[k];
+                if (louts && p.ostream >= 0 && p.ostream < lnouts && louts[p.ostream] && p.bytes) {
+                    char* target = (char*)louts[p.ostream] + lshift + p.ooff;
+                    if (is_pinned(target) && is_pinned(target + p.bytes - 1)) {
+                        direct[k] = 1;
+                        tgt[k].dst = target;
+                    }
+                }
+                if (!direct[k] && p.bytes)
+                    all_direct = false;
             }
+            if (!all_direct && !lr->pin_ok()) { // first piece that must be parked: make room for the whole call
+                if (lr->pin)
+                    GRB_CUDA(cudaFreeHost(lr->pin));
+                lr->pin = nullptr;
+                lr->cap = 0;
+                const size_t want = lr->need + lr->need / 4;
+                cudaError_t e = cudaHostAlloc(&lr->pin, want, cudaHostAllocDefault);
+                if (e != cudaSuccess)
+                    return fail(GRB200_ENOMEM, "cudaHostAlloc(%zu) failed: %s", want, cudaGetErrorString(e));
+                lr->cap = want;
+            }
+            if (!all_direct) // parked pieces sit back to back (64-byte aligned) in the handle's buffer
+                for (size_t k = 0; k < ch.d2h.size(); k++)
+                    if (!direct[k] && ch.d2h[k].bytes) {
+                        if (lr->used + ch.d2h[k].bytes > lr->cap)
+                            return fail(GRB200_ECUDA, "staging: lag buffer overflow (%zu + %zu > %zu)", lr->used,
+                                        ch.d2h[k].bytes, lr->cap);
+                        tgt[k].dst = (char*)lr->pin + lr->used;
+                        lr->used += (ch.d2h[k].bytes + 63) & ~(size_t)63;
+                    }
+            std::vector<char> allp(tgt.size(), 1);
+            if (strided_group(tgt, allp, &spitch, &dpitch)) { // e.g. the 64 streams of a channelizer chunk: ONE 2-D copy
+                GRB_CUDA(cudaMemcpy2DAsync(tgt[0].dst, dpitch, tgt[0].src, spitch, tgt[0].bytes, tgt.size(),
+                                           cudaMemcpyDeviceToHost, s_d2h));
+            } else {
+                for (const Piece& p : tgt)
+                    if (p.bytes)
+                        GRB_CUDA(cudaMemcpyAsync(p.dst, p.src, p.bytes, cudaMemcpyDeviceToHost, s_d2h));
+            }
+            for (size_t k = 0; k < tgt.size(); k++)
+                if (tgt[k].bytes)
+                    lr->segs.push_back({ tgt[k].ostream, tgt[k].ooff,
+                                         direct[k] ? 0 : (size_t)((char*)tgt[k].dst - (char*)lr->pin), tgt[k].bytes, direct[k] != 0 });
         } else {
             const bool d2h_2d = strided_group(ch.d2h, pinned_out, &spitch, &dpitch);
             if (d2h_2d)
                 GRB_CUDA(cudaMemcpy2DAsync(ch.d2h[0].dst, dpitch, ch.d2h[0].src, spitch, ch.d2h[0].bytes, ch.d2h.size(),
                                            cudaMemcpyDeviceToHost, s_d2h));
-            for (size_t k = 0; k < ch.d2h.size() && !d2h_2d; k++) {
+            bool bounce_out_2d = false;
+            if (!d2h_2d && need_out && ch.d2h.size() >= 4) {
+                std::vector<Piece> bp = ch.d2h;
+                std::vector<char> allp(bp.size(), 1);
+                size_t o2 = 0;
+                bool all_pageable = true;
+                for (size_t k = 0; k < bp.size(); k++) {
+                    if (pinned_out[k] || bp[k].bytes == 0)
+                        all_pageable = false;
+                    bp[k].dst = (char*)pin_out[slot] + o2;
+                    o2 += (bp[k].bytes + 255) & ~(size_t)255;
+                }
+                if (all_pageable && strided_group(bp, allp, &spitch, &dpitch)) {
+                    GRB_CUDA(cudaMemcpy2DAsync(bp[0].dst, dpitch, bp[0].src, spitch, bp[0].bytes, bp.size(),
+                                               cudaMemcpyDeviceToHost, s_d2h));
+                    for (size_t k = 0; k < bp.size(); k++)
+                        bounce[slot].push_back({ ch.d2h[k].dst, bp[k].dst, bp[k].bytes });
+                    bounce_out_2d = true;
+                }
+            }
+            for (size_t k = 0; k < ch.d2h.size() && !d2h_2d && !bounce_out_2d; k++) {
                 const Piece& p = ch.d2h[k];
                 if (p.bytes == 0)
                     continue;
@@ -457,7 +589,7 @@ int Stager::run(long long nchunks, const PlanFn& plan, const LaunchFn& launch)
     if (lr) {
         // the caller's INPUT buffers are borrowed for this call only: every host->device copy that reads them directly
         // (pinned memory; pageable went through the bounce already) must be over before we return.  Kernel and D2H run on.
-        if (last_slot >= 0)
+        if (last_slot >= 0 && direct_in)
             GRB_CUDA(cudaEventSynchronize(ev_h2d[last_slot]));
         GRB_CUDA(cudaEventRecord(lr->ev, s_d2h));
         lr->pending = true;
@@ -477,17 +609,7 @@ int Stager::lag_begin(size_t out_bytes, long long npieces, long long nitems)
     LagResult& r = lag[lag_cur];
     if (r.pending) // two calls back: must have been collected; never overwrite a result nobody fetched
         return fail(GRB200_EINVAL, "staging: lag result not collected before the buffer comes round again");
-    const size_t need = out_bytes + 64 * (size_t)npieces + 4096; // every piece starts on a 64-byte boundary
-    if (need > r.cap) {
-        if (r.pin)
-            GRB_CUDA(cudaFreeHost(r.pin));
-        r.pin = nullptr;
-        r.cap = 0;
-        cudaError_t e = cudaHostAlloc(&r.pin, need + need / 4, cudaHostAllocDefault);
-        if (e != cudaSuccess)
-            return fail(GRB200_ENOMEM, "cudaHostAlloc(%zu) failed: %s", need, cudaGetErrorString(e));
-        r.cap = need + need / 4;
-    }
+    r.need = out_bytes + 64 * (size_t)npieces + 4096; // every piece starts on a 64-byte boundary
     if (!r.ev)
         GRB_CUDA(cudaEventCreateWithFlags(&r.ev, cudaEventDisableTiming));
     r.used = 0;
@@ -504,11 +626,16 @@ static int lag_deliver(Stager::LagResult& r, void* const* outs, int nouts, long 
     if (!r.pending)
         return 0;
     GRB_CUDA(cudaEventSynchronize(r.ev));
+    std::vector<CopyJob> jobs;
+    jobs.reserve(r.segs.size());
     for (const Stager::LagSeg& s : r.segs) {
+        if (s.direct)
+            continue; // went straight to the caller's page-locked buffer
         if (s.ostream < 0 || s.ostream >= nouts || !outs[s.ostream])
             return fail(GRB200_EINVAL, "staging: lag result for output stream %d, %d offered", s.ostream, nouts);
-        par_memcpy((char*)outs[s.ostream] + s.ooff, (const char*)r.pin + s.boff, s.bytes);
+        jobs.push_back({ (char*)outs[s.ostream] + s.ooff, (const char*)r.pin + s.boff, s.bytes });
     }
+    par_memcpy_many(jobs);
     r.pending = false;
     *nitems = r.nitems;
     return 0;

@@ -51,19 +51,34 @@ struct Stager {
     struct LagSeg {
         int ostream;
         size_t ooff, boff, bytes;
+        bool direct; // copied straight into the caller's page-locked output, nothing to deliver later
     };
     struct LagResult {
         void* pin = nullptr;
-        size_t cap = 0, used = 0;
+        size_t cap = 0, used = 0, need = 0; // the parking buffer is allocated when the first piece has to be parked
         cudaEvent_t ev = nullptr;
         bool pending = false;
         long long nitems = 0;
         std::vector<LagSeg> segs;
+        bool pin_ok() const { return pin != nullptr && cap >= need; }
     };
     LagResult lag[2];
     int lag_cur = 0;
     bool lag_mode = false;
     LagResult* lag_active = nullptr; // set between lag_begin() and the end of run()
+    // Zero-copy delivery: when the caller's output memory is page-locked and has room BEHIND the previous call's items, this
+    // call's results are copied by the DMA engine straight to where the caller will look for them next time -- its output
+    // pointer then is this call's pointer advanced by what this call returns, which is how a gr::buffer write pointer moves
+    // (and how any caller that appends results to one array moves).  lag_direct() arms it for the coming run().
+    void* const* lag_outs = nullptr;
+    int lag_nouts = 0;
+    size_t lag_shift = 0; // bytes of the previous call's items in front of this call's
+    void lag_direct(void* const* outs, int nouts, size_t shift_bytes)
+    {
+        lag_outs = outs;
+        lag_nouts = nouts;
+        lag_shift = shift_bytes;
+    }
     int lag_begin(size_t out_bytes, long long npieces, long long nitems); // reserve the parking buffer of this call
     // hand the previous call's results to `outs` (base address of every output stream); returns its item count in *nitems
     int lag_collect(void* const* outs, int nouts, long long* nitems);
@@ -97,7 +112,13 @@ struct Stager {
     int run(long long nchunks, const PlanFn& plan, const LaunchFn& launch);
 };
 
+struct CopyJob {
+    void* dst;
+    const void* src;
+    size_t bytes;
+};
 void par_memcpy(void* dst, const void* src, size_t bytes); // big copies sliced over a small helper-thread pool
+void par_memcpy_many(const std::vector<CopyJob>& list);    // many copies (e.g. 64 stream pieces) spread over the pool
 void pin_cache_invalidate();                               // after cudaHostRegister / Unregister / free of pinned memory
 
 // One Stager per device for the handle-less entry points (complex_to_mag_squared, vector_to_streams): created on first use,

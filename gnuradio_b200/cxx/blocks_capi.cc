@@ -395,4 +395,38 @@ long long grbx_filterbank_run(int nfilts, int ntaps, const float* taps, const fl
     });
 }
 
+// fir_filter_ccf in lag-by-one mode, driven like the scheduler: the output pointer advances by what general_work returns,
+// the input pointer by what it consumes; `room` = output items offered per call.  Returns the items produced before stop().
+long long grbx_fir_lag_run(int decim, const float* taps, int ntaps, const void* in, void* out, long long nout, int lag_items,
+                           int room)
+{
+    return guarded([&]() -> long long {
+        std::vector<float> t(taps, taps + ntaps);
+        auto b = gr::filter::fir_filter_ccf::make(decim, t);
+        b->set_lag(lag_items);
+        if (b->lag() != lag_items || b->min_output_buffer() != 4L * lag_items)
+            throw std::logic_error("fir_filter_ccf: lag bookkeeping mismatch");
+        long long produced = 0, consumed = 0;
+        int idle = 0;
+        while (consumed < nout * decim) {
+            // block_executor: noutput = min(output space, what the available input covers) for a fixed-rate block
+            long long offer = std::min<long long>(room, (nout * decim - consumed) / decim);
+            if (offer <= 0)
+                break;
+            gr_vector_const_void_star ii(1, (const char*)in + (size_t)consumed * 8);
+            gr_vector_void_star oo(1, (char*)out + (size_t)produced * 8);
+            gr_vector_int ni(1, (int)(offer * decim + b->history() - 1));
+            int r = b->general_work((int)offer, ni, ii, oo);
+            if (r < 0)
+                break;
+            if (r == 0 && b->nitems_consumed_last() == 0 && ++idle > 2)
+                break;
+            produced += r;
+            consumed += b->nitems_consumed_last();
+        }
+        b->stop();
+        return produced;
+    });
+}
+
 } // extern "C"

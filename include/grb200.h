@@ -21,7 +21,7 @@
  *  - Host staging.  A `*_work` call larger than 1 MiB is cut into chunks (at least four; 64 MiB for big calls,
  *    GRB200_CHUNK_MB) that run H2D | kernel | D2H concurrently on three streams.  Page-locked caller memory (grb200_host_alloc,
  *    grb200_host_register, cudaHostRegister, torch pinned tensors) is copied directly; pageable memory -- what a gr::buffer is
- *    -- goes through pinned bounce slots, filled by a small pool of copy threads (GRB200_COPY_THREADS, default 4).
+ *    -- goes through pinned bounce slots, filled by a small pool of copy threads (GRB200_COPY_THREADS, default 8).
  *    `*_work_lag` (fir_filter, pfb_channelizer): the call returns as soon as its INPUT has been taken and delivers the
  *    previous call's results, so nothing is waited for inside work() but the copy of its own input; results are one call
  *    late.  A gr::block may do this (general_work produces fewer items than offered and consumes on its own,
@@ -90,9 +90,13 @@ int grb200_fir_ntaps(const grb200_fir* h);
 int grb200_fir_decimation(const grb200_fir* h);
 int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long long noutput);
 int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long long noutput, void* stream);
-/* Lag-by-one host mode (see "Host staging" below): queues this call's `noutput` items and writes the PREVIOUS call's results
- * to out_host (room for out_capacity items; GRB200_EINVAL when more are waiting); *produced = how many.  The first call
- * produces 0.  flush() hands out the call still in flight (end of stream; *produced = 0 when nothing is parked). */
+/* Lag-by-one host mode (see "Host staging" above): queues this call's `noutput` items and delivers the PREVIOUS call's results
+ * at out_host (room for out_capacity items; GRB200_EINVAL when more are waiting); *produced = how many.  The first call
+ * produces 0.  flush() hands out the call still in flight (end of stream; *produced = 0 when nothing is parked).
+ * Pointer contract: the out_host of call k+1 must be the out_host of call k advanced by what call k returned -- how a
+ * gr::buffer's write pointer moves.  When out_host is page-locked and out_capacity leaves room behind the items being
+ * returned, the NEW results are DMA'd straight to where the next call will look (zero CPU copies); otherwise they are parked
+ * in the handle and copied out by the next call. */
 int grb200_fir_work_lag(grb200_fir* h, const void* in_host, long long noutput, void* out_host, long long out_capacity,
                         long long* produced);
 int grb200_fir_flush(grb200_fir* h, void* out_host, long long out_capacity, long long* produced);

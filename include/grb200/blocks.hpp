@@ -88,6 +88,10 @@ public:
     void set_tag_propagation_policy(tag_propagation_policy_t p) { d_tpp = p; }
     void consume_each(int n) { d_consumed = n; }
     int nitems_consumed_last() const { return d_consumed; }
+    void set_min_output_buffer(long n) { d_min_output_buffer = n; } // block.h: grows the downstream buffer allocation
+    long min_output_buffer() const { return d_min_output_buffer; }
+    virtual bool start() { return true; }
+    virtual bool stop() { return true; }
     virtual int general_work(int noutput_items, gr_vector_int& ninput_items, gr_vector_const_void_star& input_items,
                              gr_vector_void_star& output_items) = 0;
 
@@ -102,6 +106,7 @@ private:
     double d_relative_rate = 1.0;
     tag_propagation_policy_t d_tpp = TPP_ALL_TO_ALL;
     int d_consumed = 0;
+    long d_min_output_buffer = -1;
 };
 class sync_block : public block
 {
@@ -183,6 +188,20 @@ inline int& default_device_ref()
 inline int default_device() { return default_device_ref(); }
 inline void set_default_device(int device) { default_device_ref() = device; }
 
+// Lag-by-one host mode for the blocks that have it (fir_filter_blk, pfb_channelizer_ccf): GRB200_LAG=<items per call> in the
+// environment switches it on for every block made afterwards, set_lag() per block.  work() then takes the input of the items
+// it was offered, returns the PREVIOUS call's outputs (grb200_*_work_lag) and asks the scheduler for buffers of at least four
+// calls (set_min_output_buffer) so that a call is worth a launch and the results can be delivered in place.  Trade: one
+// call of latency, and the outputs of the last call are dropped at stop() -- a streaming flowgraph ends mid-stream anyway.
+inline long lag_items_env()
+{
+    static const long v = [] {
+        const char* e = std::getenv("GRB200_LAG");
+        return e ? std::atol(e) : 0L;
+    }();
+    return v;
+}
+
 // make() hands the new block to the runtime exactly like the reference: gnuradio::get_initial_sptr (gnuradio-runtime/include/
 // gnuradio/sptr_magic.h) registers it for hier-block self-connection; the stand-in build has no such registry.
 #ifdef GRB200_WITH_GNURADIO
@@ -249,6 +268,47 @@ public:
 
     grb200_fir* handle() { return d_h; } // device-resident chaining (grb200_fir_work_dev)
 
+    // ---- lag-by-one host mode (grb200.h "Host staging") ----
+    void set_lag(long items_per_call)
+    {
+        std::lock_guard<std::mutex> l(d_setlock);
+        d_lag = items_per_call;
+        if (d_lag > 0)
+            set_min_output_buffer(4 * d_lag); // flat_flowgraph.cc:131-145 honours it when the buffers are allocated
+    }
+    long lag() const { return d_lag; }
+    int general_work(int noutput_items, gr_vector_int& ninput_items, gr_vector_const_void_star& input_items,
+                     gr_vector_void_star& output_items) override
+    {
+        if (d_lag <= 0)
+            return grb200::rt::sync_decimator::general_work(noutput_items, ninput_items, input_items, output_items);
+        std::lock_guard<std::mutex> l(d_setlock);
+        if (d_updated) {
+            set_history(d_taps.size());
+            d_updated = false;
+            consume_each(0);
+            return 0;
+        }
+        // take as much input as leaves room for its results behind the ones returned now (delivered in place when the
+        // buffer is page-locked), at most one lag unit
+        if (noutput_items < d_parked) { // no room yet for what is waiting (or the stream is ending): no progress this call
+            consume_each(0);
+            return 0;
+        }
+        long long n = (long long)noutput_items - d_parked;
+        n = n > d_lag ? d_lag : n;
+        long long produced = 0;
+        grb200::check(grb200_fir_work_lag(d_h, input_items[0], n, output_items[0], noutput_items, &produced));
+        consume_each((int)(n * (long long)decimation()));
+        d_parked = n;
+        return (int)produced; // gr::block: fewer items than offered is fine (block.h:160-175)
+    }
+    bool stop() override
+    {
+        d_parked = 0; // the call still in flight is dropped with the flowgraph
+        return true;
+    }
+
 private:
     fir_filter_blk(int decimation, const std::vector<TAP_T>& taps)
         : sync_decimator(is_fff ? "fir_filter_fff" : std::is_same<TAP_T, float>::value ? "fir_filter_ccf" : "fir_filter_ccc",
@@ -264,10 +324,14 @@ private:
         else
             grb200::check(grb200_fir_ccc_create(decimation, t, (int)taps.size(), grb200::default_device(), &d_h));
         set_history(taps.size()); // fir_filter_blk_impl.cc:41
+        if (grb200::lag_items_env() > 0)
+            set_lag(grb200::lag_items_env());
     }
     grb200_fir* d_h = nullptr;
     std::vector<TAP_T> d_taps;
     bool d_updated = false;
+    long d_lag = 0;
+    long long d_parked = 0; // items of the previous lag call not yet returned
 };
 typedef fir_filter_blk<gr_complex, gr_complex, float> fir_filter_ccf;
 typedef fir_filter_blk<gr_complex, gr_complex, gr_complex> fir_filter_ccc;
@@ -695,12 +759,41 @@ public:
             return 0; // history requirements may have changed
         }
         long long consumed = 0;
+        if (d_lag > 0) { // lag-by-one host mode: see fir_filter_blk::general_work
+            const int om = output_multiple();
+            if (noutput_items < d_parked) {
+                consume_each(0);
+                return 0;
+            }
+            long long n = (long long)noutput_items - d_parked;
+            n = n > d_lag ? d_lag : n;
+            n = n / om * om;
+            long long produced = 0;
+            grb200::check(grb200_pfb_chan_work_lag(d_h, input_items.data(), n, output_items.data(), (int)output_items.size(),
+                                                   noutput_items, &consumed, &produced));
+            consume_each((int)consumed);
+            d_parked = n;
+            return (int)produced;
+        }
         grb200::check(grb200_pfb_chan_work(d_h, input_items.data(), output_items.data(), (int)output_items.size(),
                                            noutput_items, &consumed));
         consume_each((int)consumed); // :191
         return noutput_items;
     }
     grb200_pfb* handle() { return d_h; }
+    void set_lag(long items_per_call)
+    {
+        std::lock_guard<std::mutex> l(d_setlock);
+        d_lag = items_per_call;
+        if (d_lag > 0)
+            set_min_output_buffer(4 * d_lag);
+    }
+    long lag() const { return d_lag; }
+    bool stop() override
+    {
+        d_parked = 0;
+        return true;
+    }
 
 private:
     pfb_channelizer_ccf(unsigned int nfilts, const std::vector<float>& taps, float oversample_rate)
@@ -715,7 +808,11 @@ private:
         set_history(grb200_pfb_chan_taps_per_filter(d_h) + 1);            // :101
         d_updated = true;                                                 // ctor goes through set_taps (:87)
         set_tag_propagation_policy(TPP_ONE_TO_ONE);                       // :91
+        if (grb200::lag_items_env() > 0)
+            set_lag(grb200::lag_items_env());
     }
+    long d_lag = 0;
+    long long d_parked = 0;
     grb200_pfb* d_h = nullptr;
     unsigned d_nfilts;
     bool d_updated = false;

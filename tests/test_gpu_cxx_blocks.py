@@ -16,7 +16,7 @@ LL = C.c_longlong
 @pytest.fixture(scope="module")
 def drv():
     lib = C.CDLL(os.path.join(ROOT, "gnuradio_b200", "cxx", "libgrb200_blocks.so"))
-    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_pfb_dec_run", "grbx_interp_fir_run", "grbx_rational_resampler_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run", "grbx_fir_fff_run", "grbx_fft_vfc_run", "grbx_pfb_synth_run", "grbx_filterbank_run"):
+    for f in ("grbx_fir_run", "grbx_freq_xlating_run", "grbx_pfb_dec_run", "grbx_interp_fir_run", "grbx_rational_resampler_run", "grbx_fft_filter_run", "grbx_fft_vcc_run", "grbx_magsq_run", "grbx_pfb_run", "grbx_fir_fff_run", "grbx_fft_vfc_run", "grbx_pfb_synth_run", "grbx_filterbank_run", "grbx_fir_lag_run"):
         getattr(lib, f).restype = LL
     lib.grbx_what.restype = C.c_char_p
     return lib
@@ -208,3 +208,18 @@ def test_cxx_filterbank(drv, orc):
     got = out.reshape(n, nf)
     assert_parity(got[:2048], orc.filterbank(t1, x, 2048), "c++ filterbank before set_taps")
     assert_parity(got[2048:], orc.filterbank(t2, x[2048 * nf:], n - 2048), "c++ filterbank after set_taps")
+
+
+def test_cxx_fir_lag_by_one(drv, orc):
+    """fir_filter_ccf with set_lag(): general_work consumes the call it was offered and returns the previous call's outputs;
+    everything but the last call (dropped at stop()) comes out, in order, equal to the blocking block's."""
+    rng = np.random.default_rng(31)
+    nt, D, nout, lag = 64, 2, 200000, 16384
+    taps = rng.uniform(-1, 1, nt).astype(np.float32)
+    x = crand(rng, nout * D)
+    xin = np.concatenate([np.zeros(nt - 1, np.complex64), x])
+    out = np.zeros(nout, np.complex64)
+    rc = drv.grbx_fir_lag_run(D, p(taps), nt, p(xin), p(out), LL(nout), lag, 4 * lag)
+    assert rc > 0, drv.grbx_what()
+    assert nout - 4 * lag <= rc < nout  # at most the calls still in flight are missing
+    assert_parity(out[:rc], orc.fir(D, taps, xin, rc), "c++ fir lag-by-one")

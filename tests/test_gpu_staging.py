@@ -112,6 +112,57 @@ def test_lag_by_one_fir_and_channelizer(orc):
         np.testing.assert_array_equal(np.concatenate(got, axis=1), ref)
 
 
+def test_lag_by_one_delivers_in_place_into_page_locked_output(orc):
+    """Page-locked output with room behind the items being returned: the new results are DMA'd straight to where the next call
+    looks for them (no CPU copy).  The caller moves its output pointer like a gr::buffer write pointer: by what was returned."""
+    import ctypes as C
+
+    import gnuradio_b200 as grb
+    from gnuradio_b200 import _lib
+
+    rng = np.random.default_rng(17)
+    nt, n, calls = 48, 1 << 17, 6
+    taps = rng.uniform(-1, 1, nt).astype(np.float32)
+    x = crand(rng, calls * n + nt - 1)
+    ref = grb.filter.fir_filter_ccf(1, taps).process(x, calls * n)
+    y = np.zeros(calls * n, np.complex64)
+    grb.host_register(y)
+    try:
+        blk = grb.filter.fir_filter_ccf(1, taps)
+        L, got, done = _lib.lib(), C.c_longlong(0), 0
+        for c in range(calls):
+            seg = x[c * n: (c + 1) * n + nt - 1]
+            _lib.check(L.grb200_fir_work_lag(blk._h, C.c_void_p(seg.ctypes.data), n, C.c_void_p(y.ctypes.data + 8 * done),
+                                             len(y) - done, C.byref(got)))
+            assert got.value == (0 if c == 0 else n)
+            done += got.value
+        _lib.check(L.grb200_fir_flush(blk._h, C.c_void_p(y.ctypes.data + 8 * done), len(y) - done, C.byref(got)))
+        done += got.value
+        assert done == calls * n
+        assert_parity(y, ref, "in-place lag delivery", 2e-6, 2e-5)
+    finally:
+        grb.host_unregister(y)
+    # channelizer, 64 page-locked output streams
+    M, T, nout, calls = 64, 16, 1 << 11, 5
+    ptaps = rng.uniform(-1, 1, M * T).astype(np.float32)
+    xin = crand(rng, (calls * nout + T) * M)
+    refo = np.zeros((M, calls * nout), np.complex64)
+    grb.filter.pfb_channelizer_ccf(M, ptaps, 1.0).work_interleaved(xin, [refo[j] for j in range(M)], calls * nout)
+    outs = np.zeros((M, calls * nout), np.complex64)
+    grb.host_register(outs)
+    try:
+        ch = grb.filter.pfb_channelizer_ccf(M, ptaps, 1.0)
+        done = 0
+        for c in range(calls):
+            seg = xin[c * nout * M: ((c + 1) * nout + T) * M]
+            done += ch.work_lag(seg, [outs[j][done:] for j in range(M)], nout, interleaved=True)
+        done += ch.flush([outs[j][done:] for j in range(M)])
+        assert done == calls * nout
+        np.testing.assert_array_equal(outs, refo)
+    finally:
+        grb.host_unregister(outs)
+
+
 def test_null_stream_is_the_legacy_default_stream(orc):
     """producer -> work_dev(stream 0) -> consumer, all on torch's default stream, with NO device-wide synchronisation: the
     result is right only if the library's launch is ordered on that stream (stream 0 used to mean a private
