@@ -733,6 +733,53 @@ def timed_steps(torch, dist, wl, steps, warmup, halo=None):
     return total, per
 
 
+def attach_peer_halo(torch, dist, wl, device, rank, world):
+    """Multi-GPU: the only exchange of a time-sharded stream is the history halo.  Each rank maps the left neighbour's tail
+    (CUDA IPC, once) and the block fetches it itself over NVLink inside work_dev -- no host-launched send/recv per step
+    (round 1: a batch_isend_irecv group per step, ~0.25 ms of host time).  Ring: every rank does the same work."""
+    if not hasattr(wl, "halo_views"):
+        return None
+    from gnuradio_b200 import sharding
+
+    views = wl.halo_views()
+    if len(views) != 1:
+        raise RuntimeError("one buffer set per step with a device-side halo")
+    # once, through NCCL: the buffer's own history region holds the same items the block will read from the neighbour, so
+    # the parity spot check (which reads this rank's buffers) sees exactly what the kernels saw
+    sharding.exchange_halos(dist, views, rank, world, ring=True)
+    torch.cuda.synchronize()
+    ph = sharding.PeerHalo(dist, device, [views[0][1].data_ptr()], rank, world, ring=True)
+    wl.blk.set_halo_source(ph.ptrs[0])
+    dist.barrier()
+    return ph
+
+
+def sharded_run(torch, dist, grb, cls, device, rank, world, steps, peak, log2n=None, **attrs):
+    """One workload time-sharded over all ranks with the device-side halo: aggregate Msps (max over ranks) + parity."""
+    o = cls(torch, grb, device, log2n)
+    for k, v in attrs.items():
+        setattr(o, k, v)
+    o.setup()
+    ph = attach_peer_halo(torch, dist, o, device, rank, world)
+    sps = getattr(o, "samples_per_step", o.n)
+    tot, pr = timed_steps(torch, dist, o, steps, 3)
+    tt = torch.tensor([tot], dtype=torch.float64, device="cuda")
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    tot = float(tt.item())
+    msps = sps * world * steps / (tot * 1e-3) / 1e6
+    res = {"workload": o.describe(), "msps": msps, "msps_per_gpu": msps / world, "samples_per_gpu_per_step": sps,
+           "hbm_frac_per_gpu": o.alg_bytes * msps / world * 1e6 / 1e9 / peak, "ms_per_step": tot / steps,
+           "halo_items": getattr(o, "halo_items", 0), "halo": "fetched by the block from the left neighbour's memory (NVLink peer access)",
+           "parity": run_parity(torch, o)}
+    torch.cuda.synchronize()
+    dist.barrier()
+    o.blk.set_halo_source(None)
+    if ph is not None:
+        ph.close()
+    o.free()
+    return res
+
+
 def run_parity(torch, wl):
     """Spot-window parity of the workload's LAST step at its full size (outside any timed region): first + last segment and 64
     seeded interior windows against the CPU oracle and float64.  north_star tolerance: NRMS <= 1e-5, max-abs <= 1e-4 x RMS."""
@@ -993,13 +1040,7 @@ def main():
     samples_per_step = getattr(wl, "samples_per_step", wl.n)
 
     halo = None
-    if dist is not None and hasattr(wl, "halo_views"):
-        from gnuradio_b200 import sharding
-
-        views = wl.halo_views()
-
-        def halo():  # the segment's history = the left neighbour's newest items (ring: every rank does equal work)
-            sharding.exchange_halos(dist, views, rank, world, ring=True)
+    peer = attach_peer_halo(torch, dist, wl, local, rank, world) if dist is not None else None
 
     with ClockSampler(local) as clk:
         total_ms, per = timed_steps(torch, dist, wl, args.steps, args.warmup, halo)
@@ -1033,7 +1074,7 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic (uniform complex64 in [-1,1)^2, seeded torch Philox on device)",
         "config": {"workload": wl.describe(), "samples_per_step_per_gpu": samples_per_step,
                    "l2": "inputs larger than L2 (%.1f GiB read per step)" % (8.0 * samples_per_step / 2 ** 30),
-                   "parallelism": "time-sharded x%d, weak scaling, %d-sample history halo over NCCL send/recv" % (
+                   "parallelism": "time-sharded x%d, weak scaling, %d-sample history halo read from the left neighbour's memory over NVLink (CUDA IPC peer access, inside the kernel)" % (
                        world, getattr(wl, "halo_items", 0)) if world > 1 else "single GPU"},
         "roofline": roofline, "parity": parity, "gpu_launches": launches_timed, "gpu_launches_total_process": launches,
     }
@@ -1117,33 +1158,25 @@ def main():
         line["other_configs"] = others
 
     if world > 1 and not args.no_others and args.workload == "pfb":
-        # the two FIR configs time-sharded the same way (configs[0] with 16 buffer sets so a step outlasts the host-side
-        # cost of the halo exchange; configs[3] as is): every rank takes part, max over ranks
+        # the FIR configs time-sharded the same way, ONE buffer set per step (weak: the BASELINE size per GPU), and the two
+        # configs BASELINE.json words as a fixed total -- configs[2] "2^30 samples, sharded 1/2/4/8" and configs[3]
+        # "time-sharded 8 x B200" -- as STRONG scaling: 2^30 input samples in total, 2^30 / N per GPU
         others = {}
+        wl.blk.set_halo_source(None)
+        if peer is not None:
+            peer.close()
         wl.free()
-        for key, cls, kw in (("fir", FirCcf, {"nsets": 16}), ("firdec", FirLongDecim, {})):
-            o = cls(torch, grb, local)
-            for k, v in kw.items():
-                setattr(o, k, v)
-            o.setup()
-            views = o.halo_views()
-
-            def halo_o(views=views):
-                sharding.exchange_halos(dist, views, rank, world, ring=True)
-
-            sps = getattr(o, "samples_per_step", o.n)
-            nst = max(5, args.steps // 2)
-            tot, pr = timed_steps(torch, dist, o, nst, 3, halo_o)
-            tt = torch.tensor([tot], dtype=torch.float64, device="cuda")
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            tot = float(tt.item())
-            msps = sps * world * nst / (tot * 1e-3) / 1e6
-            others[key] = {"workload": o.describe(), "msps": msps, "msps_per_gpu": msps / world,
-                           "hbm_frac_per_gpu": o.alg_bytes * msps / world * 1e6 / 1e9 / peak, "ms_per_step": tot / nst,
-                           "halo_items": o.halo_items}
-            o.free()
-            del o
+        nst = max(5, args.steps // 2)
+        lg = 30 - int(round(np.log2(world)))
+        others["fir"] = sharded_run(torch, dist, grb, FirCcf, local, rank, world, nst, peak, nsets=1)
+        others["firdec"] = sharded_run(torch, dist, grb, FirLongDecim, local, rank, world, nst, peak)
+        strong = {"pfb": sharded_run(torch, dist, grb, PfbChannelizer, local, rank, world, nst, peak, log2n=lg),
+                  "firdec": sharded_run(torch, dist, grb, FirLongDecim, local, rank, world, nst, peak, log2n=lg)}
+        for v in strong.values():
+            v["scaling"] = "strong"
+            v["total_samples"] = 1 << 30
         line["other_configs"] = others
+        line["strong_scaling"] = strong
 
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1

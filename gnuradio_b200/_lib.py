@@ -35,6 +35,12 @@ SIGNATURES = {
     "grb200_memcpy_h2d": (i32, [i32, vp, vp, u64]),
     "grb200_memcpy_d2h": (i32, [i32, vp, vp, u64]),
     "grb200_dev_sync": (i32, [i32]),
+    "grb200_ipc_export": (i32, [i32, vp, vp]),
+    "grb200_ipc_open": (i32, [i32, vp, pvp]),
+    "grb200_ipc_close": (i32, [i32, vp]),
+    "grb200_enable_peer": (i32, [i32, i32]),
+    "grb200_fir_set_halo_source": (i32, [vp, vp]),
+    "grb200_pfb_chan_set_halo_source": (i32, [vp, vp]),
     "grb200_fir_ccf_create": (i32, [i32, vp, i32, i32, pvp]),
     "grb200_fir_ccc_create": (i32, [i32, vp, i32, i32, pvp]),
     "grb200_fir_fff_create": (i32, [i32, vp, i32, i32, pvp]),

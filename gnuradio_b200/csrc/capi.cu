@@ -122,6 +122,7 @@ struct grb200_fir {
     bool rot = false;
     double theta = 0.0, delta = 0.0;
     int tc_pref = -1; // GRB200_FIR_TC as it stood when the handle was made
+    const void* halo_src = nullptr; // left neighbour's newest ntaps-1 items (peer memory), see grb200_fir_set_halo_source
     bool real = false; // fir_filter_fff: float stream, float taps (fir_fff.cu)
     int isz() const { return real ? 4 : 8; }
     Stager sg;
@@ -216,6 +217,15 @@ int grb200_fir_set_taps(grb200_fir* h, const float* taps, int ntaps)
     return fir_upload_taps(h, taps, ntaps);
 }
 
+int grb200_fir_set_halo_source(grb200_fir* h, const void* peer_tail)
+{
+    if (!h)
+        return fail(GRB200_EINVAL, "fir_filter::set_halo_source: null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    h->halo_src = peer_tail;
+    return 0;
+}
+
 int grb200_fir_ntaps(const grb200_fir* h) { return h ? h->ntaps : 0; }
 int grb200_fir_decimation(const grb200_fir* h) { return h ? h->decim : 0; }
 
@@ -229,6 +239,9 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
     if (rc)
         return rc;
     cudaStream_t st = pick_stream(stream, h->sg);
+    if (h->halo_src && h->ntaps > 1 && noutput > 0) // the segment's history = the left neighbour's tail, fetched over NVLink
+        GRB_CUDA(cudaMemcpyAsync(const_cast<void*>(in_dev), h->halo_src, (size_t)(h->ntaps - 1) * h->isz(),
+                                 cudaMemcpyDeviceToDevice, st));
     rc = h->real ? fir_fff_launch(h->decim, h->ntaps, (const float*)h->rev.p, in_dev, out_dev, noutput, sm_count(h->device), st)
                  : fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput, h->tc_pref, st);
     if (!rc && h->rot) {

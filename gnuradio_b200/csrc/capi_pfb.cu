@@ -14,6 +14,7 @@ struct grb200_pfb {
     std::vector<float> padded; // prototype zero-padded to T*M; d_taps[i][j] = padded[i + j*M]
     std::vector<int> cmap;     // d_channel_map
     bool identity = true;
+    const void* halo_src = nullptr; // left neighbour's newest T rows (peer memory), see grb200_pfb_chan_set_halo_source
     DevBuf h, wM, dmap;
     Stager sg;
     std::mutex mu;
@@ -146,6 +147,15 @@ int grb200_pfb_chan_get_channel_map(const grb200_pfb* p, int* map, int n)
     return have;
 }
 
+int grb200_pfb_chan_set_halo_source(grb200_pfb* p, const void* peer_tail)
+{
+    if (!p)
+        return fail(GRB200_EINVAL, "pfb_channelizer_ccf::set_halo_source: null handle");
+    std::lock_guard<std::mutex> lk(p->mu);
+    p->halo_src = peer_tail;
+    return 0;
+}
+
 int grb200_pfb_chan_taps_per_filter(const grb200_pfb* p) { return p ? p->T : 0; }
 int grb200_pfb_chan_output_multiple(const grb200_pfb* p) { return p ? p->om : 0; }
 
@@ -176,7 +186,7 @@ int grb200_pfb_chan_work_interleaved_dev(grb200_pfb* p, const void* in_dev, void
     cudaStream_t st_ = pick_stream(stream, p->sg);
     return dev_done(pfb_launch(p->M, p->T, p->R, in_dev, out_dev, out_stride, nout_streams, (const int*)p->dmap.p,
                       p->identity ? 1 : 0, noutput, (const float*)p->h.p, (const float2*)p->wM.p,
-                      sm_count(p->device), true, st_), p->sg, st_);
+                      sm_count(p->device), true, st_, p->halo_src), p->sg, st_);
 }
 
 // Shared host-staged driver.  `interleaved` selects the input form:

@@ -40,7 +40,7 @@ template <int M, int TP, int NT>
 __global__ void __launch_bounds__(NT)
 pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long long out_stride, int nouts,
                   long long noutput, int T, long long nrows, const float* __restrict__ h,
-                  const float2* __restrict__ wM, int iters)
+                  const float2* __restrict__ wM, int iters, const float2* __restrict__ halo)
 {
     using Geo = PfbStreamGeom<M, NT>;
     constexpr int NG = Geo::NG, KT = Geo::KT, OT = Geo::OT, LD = Geo::LD, RDX = Geo::RDX, NI = Geo::NI;
@@ -72,7 +72,10 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
 #pragma unroll
     for (int u = 1; u < TP; u++) {
         const long long r = gs + T - u;
-        ring[(TP - u) % TP] = (r >= 0 && r < nrows) ? x[r * M + col] : make_float2(0.f, 0.f);
+        // the T history rows of a time-sharded segment are the left neighbour's newest rows: with a halo source they are
+        // read where they are -- the neighbour GPU's memory, plain loads over NVLink -- instead of being copied in first
+        const float2* src = (halo != nullptr && r < T) ? halo : x;
+        ring[(TP - u) % TP] = (r >= 0 && r < nrows) ? src[r * M + col] : make_float2(0.f, 0.f);
     }
     ring[0] = make_float2(0.f, 0.f);
     __syncthreads(); // barrier initialised, twiddle table written
@@ -175,7 +178,7 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
 // ---- host launcher ------------------------------------------------------------------------------------
 template <int M, int TP, int NT>
 static int launch_stream(const void* x, void* out, long long out_stride, int nouts, long long noutput, int T,
-                         long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st)
+                         long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo)
 {
     using Geo = PfbStreamGeom<M, NT>;
     auto kern = pfb_stream_kernel<M, TP, NT>;
@@ -201,20 +204,20 @@ static int launch_stream(const void* x, void* out, long long out_stride, int nou
     if (iters > 0x7fffffffLL / Geo::KT)
         return fail(GRB200_ERANGE, "pfb_channelizer: work() call too long for one launch");
     kern<<<(unsigned)grid, NT, Geo::SMEM, st>>>((const float2*)x, (float2*)out, out_stride, nouts, noutput, T, nrows,
-                                                 h, wM, (int)iters);
+                                                 h, wM, (int)iters, (const float2*)halo);
     GRB_LAUNCH_CHECK();
     return 0;
 }
 
 template <int M, int NT>
 static int launch_stream_tp(int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
-                            long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st)
+                            long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo)
 {
     if (T <= 8)
-        return launch_stream<M, 8, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st);
+        return launch_stream<M, 8, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo);
     if (T <= 16)
-        return launch_stream<M, 16, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st);
-    return launch_stream<M, 32, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st);
+        return launch_stream<M, 16, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo);
+    return launch_stream<M, 32, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo);
 }
 
 bool pfb_stream_supported(int M, int T, int R, const void* x)
@@ -224,7 +227,7 @@ bool pfb_stream_supported(int M, int T, int R, const void* x)
 
 // x: interleaved input with T*M history items in front (16-byte aligned); identity channel map.
 int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
-                      const float* h, const float2* wM, int nsm, cudaStream_t st)
+                      const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo)
 {
     if (noutput <= 0)
         return 0;
@@ -234,12 +237,12 @@ int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stri
         return (e && atoi(e) == 128) ? 128 : 256;
     }();
     if (M == 16)
-        return nt_small == 128 ? launch_stream_tp<16, 128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st)
-                               : launch_stream_tp<16, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+        return nt_small == 128 ? launch_stream_tp<16, 128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo)
+                               : launch_stream_tp<16, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
     if (M == 64)
-        return nt_small == 128 ? launch_stream_tp<64, 128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st)
-                               : launch_stream_tp<64, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
-    return launch_stream_tp<256, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+        return nt_small == 128 ? launch_stream_tp<64, 128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo)
+                               : launch_stream_tp<64, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+    return launch_stream_tp<256, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
 }
 
 } // namespace grb

@@ -94,6 +94,11 @@ class _fir_filter_blk(sync_decimator):
                                                   int(noutput_items), C.c_void_p(stream)))
         return int(noutput_items)
 
+    def set_halo_source(self, peer_tail):
+        """Time-sharded stream: work_dev() fetches the ntaps-1 history items in front of its input from `peer_tail` (the left
+        neighbour's newest items, a device address valid in this process -- sharding.PeerHalo) itself.  None clears."""
+        _lib.check(_lib.lib().grb200_fir_set_halo_source(self._h, C.c_void_p(peer_tail or 0)))
+
     def general_work_lag(self, noutput_items, input_items, output_items):
         """Lag-by-one host mode (include/grb200.h "Host staging"): takes the input of `noutput_items` outputs now, writes the
         PREVIOUS call's outputs into output_items[0] and returns how many -- 0 on the first call.  consume = this call's
@@ -686,6 +691,11 @@ class pfb_channelizer_ccf(block):
                                                                   C.byref(consumed)))
         self.consume_each(consumed.value)
         return n
+
+    def set_halo_source(self, peer_tail):
+        """Time-sharded stream: work_interleaved_dev() reads its taps_per_filter history rows from `peer_tail` (the left
+        neighbour's newest rows, in ITS memory over NVLink -- sharding.PeerHalo) inside the kernel.  None clears."""
+        _lib.check(_lib.lib().grb200_pfb_chan_set_halo_source(self._h, C.c_void_p(peer_tail or 0)))
 
     def work_lag(self, input_items, output_items, noutput_items, interleaved=False):
         """Lag-by-one host mode: queues this call (M streams, or ONE interleaved stream when `interleaved`), writes the

@@ -124,3 +124,47 @@ def resampler_segment(rank, world, noutput_total, interpolation, decimation, tap
         return ResamplerSegment(rank, world, o0, o1, q0, q0, s0 % interpolation, 0)
     q_last = (ctr0 + (o1 - 1) * decimation) // interpolation
     return ResamplerSegment(rank, world, o0, o1, q0, q_last + taps_per_filter, s0 % interpolation, q_last + 1 - q0)
+
+
+class PeerHalo:
+    """The halo without a host round trip per step (include/grb200.h "peer memory"): every rank exports the address of its
+    segment's TAIL (its newest `halo` items) once, opens the left neighbour's, and hands that pointer to its block
+    (set_halo_source) -- from then on the block fetches its history over NVLink itself, on its own stream.
+
+    One process per GPU (torchrun): CUDA IPC handles travel through torch.distributed.all_gather_object (72 bytes each).
+    ring=True lets rank 0 read the last rank's tail (bench: every rank does the same work)."""
+
+    def __init__(self, dist, device, tail_ptrs, rank, world, ring=False):
+        import ctypes as C
+
+        from . import _lib
+
+        self._device, self._open = int(device), []
+        self.ptrs = [None] * len(tail_ptrs)
+        if world == 1:
+            return
+        L = _lib.lib()
+        mine = []
+        for p in tail_ptrs:
+            blob = (C.c_ubyte * 72)()
+            _lib.check(L.grb200_ipc_export(self._device, C.c_void_p(int(p)), blob))
+            mine.append(bytes(blob))
+        everyone = [None] * world
+        dist.all_gather_object(everyone, mine)
+        left = rank - 1
+        if ring:
+            left %= world
+        if left < 0:
+            return
+        for k, blob in enumerate(everyone[left]):
+            q = C.c_void_p()
+            _lib.check(L.grb200_ipc_open(self._device, (C.c_ubyte * 72).from_buffer_copy(blob), C.byref(q)))
+            self._open.append(q)
+            self.ptrs[k] = q.value
+
+    def close(self):
+        from . import _lib
+
+        for q in self._open:
+            _lib.lib().grb200_ipc_close(self._device, q)
+        self._open = []

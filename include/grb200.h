@@ -70,6 +70,20 @@ int grb200_memcpy_h2d(int device, void* dst_dev, const void* src_host, unsigned 
 int grb200_memcpy_d2h(int device, void* dst_host, const void* src_dev, unsigned long long bytes);
 int grb200_dev_sync(int device);
 
+/* ---- peer memory: the halo of a time-sharded stream without a host round trip ----------------
+ * A stream sharded by time over several GPUs needs ONE exchange: every segment's history (ntaps-1 items; taps_per_filter *
+ * numchans items for the channelizer) is the left neighbour's newest items.  grb200_*_set_halo_source(h, peer_tail) makes
+ * *_work_dev fetch it itself, on its own stream, from the neighbour GPU's memory over NVLink -- the channelizer's streaming
+ * kernel reads the rows in place with plain loads, the FIR family copies the (at most 8 KiB) region in front of in_dev first
+ * (which it therefore overwrites).  The caller orders the fetch behind the neighbour's producer (an event, a flag, a barrier).
+ * peer_tail: a device pointer valid in THIS process -- from grb200_ipc_open (one process per GPU: the exporter calls
+ * grb200_ipc_export on its tail pointer and ships the 72-byte handle, e.g. through torch.distributed) or, inside one process,
+ * the neighbour's own pointer after grb200_enable_peer. */
+int grb200_ipc_export(int device, const void* dev_ptr, void* handle72);
+int grb200_ipc_open(int device, const void* handle72, void** peer_ptr);
+int grb200_ipc_close(int device, void* peer_ptr);
+int grb200_enable_peer(int device, int peer_device);
+
 /* ---- fir_filter_ccf / fir_filter_ccc -----------------------------------------------------------
  * Replaces gr::filter::kernel::fir_filter<gr_complex,gr_complex,float|gr_complex>
  *   ctor/set_taps  gr-filter/lib/fir_filter.cc:21-75
@@ -86,6 +100,7 @@ int grb200_fir_ccc_create(int decim, const float* taps_re_im, int ntaps, int dev
  * items are float32 (in: noutput*decim + ntaps-1 floats, out: noutput floats). */
 int grb200_fir_fff_create(int decim, const float* taps, int ntaps, int device, grb200_fir** out);
 int grb200_fir_set_taps(grb200_fir* h, const float* taps, int ntaps); /* re/im pairs for ccc */
+int grb200_fir_set_halo_source(grb200_fir* h, const void* peer_tail); /* NULL clears; see "peer memory" above */
 int grb200_fir_ntaps(const grb200_fir* h);
 int grb200_fir_decimation(const grb200_fir* h);
 int grb200_fir_work(grb200_fir* h, const void* in_host, void* out_host, long long noutput);
@@ -175,6 +190,7 @@ int grb200_pfb_chan_ccf_create(unsigned int numchans, const float* taps, int nta
 int grb200_pfb_chan_set_taps(grb200_pfb* h, const float* taps, int ntaps);
 int grb200_pfb_chan_set_channel_map(grb200_pfb* h, const int* map, int n);
 int grb200_pfb_chan_get_channel_map(const grb200_pfb* h, int* map, int n);
+int grb200_pfb_chan_set_halo_source(grb200_pfb* h, const void* peer_tail); /* for work_interleaved_dev; NULL clears */
 int grb200_pfb_chan_taps_per_filter(const grb200_pfb* h);
 int grb200_pfb_chan_output_multiple(const grb200_pfb* h);
 /* branch taps d_taps[i][j] = padded[i + j*numchans]; `out` holds numchans*taps_per_filter floats */
