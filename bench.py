@@ -215,7 +215,9 @@ class FirCcf(Workload):
 
     def setup(self):
         self.taps = lowpass(self.ntaps, 0.1, hamming(self.ntaps))
-        self.blk = self.grb.filter.fir_filter_ccf(self.decim, self.taps, device=self.device)
+        # one block per buffer set: on several GPUs every set has its own halo source (the left neighbour's set)
+        self.blks = [self.grb.filter.fir_filter_ccf(self.decim, self.taps, device=self.device) for _ in range(self.nsets)]
+        self.blk = self.blks[0]
         self.nout = self.n // self.decim
         self.d_in = [self.rand_c64(self.n + self.ntaps - 1, self.seed + i) for i in range(self.nsets)]
         self.d_out = [self.torch.empty(2 * self.nout, dtype=self.torch.float32, device="cuda") for _ in range(self.nsets)]
@@ -223,8 +225,8 @@ class FirCcf(Workload):
         self.samples_per_step = self.n * self.nsets
 
     def step(self):
-        for i in range(self.nsets):
-            self.blk.work_dev(self.d_in[i].data_ptr(), self.d_out[i].data_ptr(), self.nout, self.stream)
+        for i in range(len(self.d_in)):
+            self.blks[i % len(self.blks)].work_dev(self.d_in[i].data_ptr(), self.d_out[i].data_ptr(), self.nout, self.stream)
 
     def parity(self, sc):
         k = len(self.d_in) - 1  # the last buffer set the step wrote
@@ -264,6 +266,7 @@ class FirLongDecim(FirCcf):
     def setup(self):
         self.taps = lowpass(self.ntaps, 1.0 / 32, blackman_harris(self.ntaps))
         self.blk = self.grb.filter.fir_filter_ccf(self.decim, self.taps, device=self.device)
+        self.blks = [self.blk]
         self.nout = self.n // self.decim
         self.d_in = [self.rand_c64(self.n + self.ntaps - 1, self.seed)]
         self.d_out = [self.torch.empty(2 * self.nout, dtype=self.torch.float32, device="cuda")]
@@ -373,6 +376,7 @@ class FreqXlating(FirCcf):
     def setup(self):
         self.taps = lowpass(self.ntaps, 0.05, hamming(self.ntaps))
         self.blk = self.grb.filter.freq_xlating_fir_filter_ccf(self.decim, self.taps, 0.21, 1.0, device=self.device)
+        self.blks = [self.blk]
         self.nout = self.n // self.decim
         self.d_in = [self.rand_c64(self.n + self.ntaps - 1, self.seed)]
         self.d_out = [self.torch.empty(2 * self.nout, dtype=self.torch.float32, device="cuda")]
@@ -742,14 +746,16 @@ def attach_peer_halo(torch, dist, wl, device, rank, world):
     from gnuradio_b200 import sharding
 
     views = wl.halo_views()
-    if len(views) != 1:
-        raise RuntimeError("one buffer set per step with a device-side halo")
+    blks = getattr(wl, "blks", [wl.blk])
+    if len(views) != len(blks):
+        raise RuntimeError("one block per buffer set with a device-side halo")
     # once, through NCCL: the buffer's own history region holds the same items the block will read from the neighbour, so
     # the parity spot check (which reads this rank's buffers) sees exactly what the kernels saw
     sharding.exchange_halos(dist, views, rank, world, ring=True)
     torch.cuda.synchronize()
-    ph = sharding.PeerHalo(dist, device, [views[0][1].data_ptr()], rank, world, ring=True)
-    wl.blk.set_halo_source(ph.ptrs[0])
+    ph = sharding.PeerHalo(dist, device, [v[1].data_ptr() for v in views], rank, world, ring=True)
+    for b, q in zip(blks, ph.ptrs):
+        b.set_halo_source(q)
     dist.barrier()
     return ph
 
@@ -773,7 +779,8 @@ def sharded_run(torch, dist, grb, cls, device, rank, world, steps, peak, log2n=N
            "parity": run_parity(torch, o)}
     torch.cuda.synchronize()
     dist.barrier()
-    o.blk.set_halo_source(None)
+    for b in getattr(o, "blks", [o.blk]):
+        b.set_halo_source(None)
     if ph is not None:
         ph.close()
     o.free()
@@ -1158,17 +1165,18 @@ def main():
         line["other_configs"] = others
 
     if world > 1 and not args.no_others and args.workload == "pfb":
-        # the FIR configs time-sharded the same way, ONE buffer set per step (weak: the BASELINE size per GPU), and the two
+        # the FIR configs time-sharded the same way, exactly as at N = 1 -- same buffer sets, same launches per step, plus the halo fetch (weak: the BASELINE size per GPU), and the two
         # configs BASELINE.json words as a fixed total -- configs[2] "2^30 samples, sharded 1/2/4/8" and configs[3]
         # "time-sharded 8 x B200" -- as STRONG scaling: 2^30 input samples in total, 2^30 / N per GPU
         others = {}
-        wl.blk.set_halo_source(None)
+        for b in getattr(wl, "blks", [wl.blk]):
+            b.set_halo_source(None)
         if peer is not None:
             peer.close()
         wl.free()
         nst = max(5, args.steps // 2)
         lg = 30 - int(round(np.log2(world)))
-        others["fir"] = sharded_run(torch, dist, grb, FirCcf, local, rank, world, nst, peak, nsets=1)
+        others["fir"] = sharded_run(torch, dist, grb, FirCcf, local, rank, world, nst, peak)
         others["firdec"] = sharded_run(torch, dist, grb, FirLongDecim, local, rank, world, nst, peak)
         strong = {"pfb": sharded_run(torch, dist, grb, PfbChannelizer, local, rank, world, nst, peak, log2n=lg),
                   "firdec": sharded_run(torch, dist, grb, FirLongDecim, local, rank, world, nst, peak, log2n=lg)}

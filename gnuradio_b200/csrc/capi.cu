@@ -178,6 +178,7 @@ static int fir_create(bool ct, int decim, const float* taps, int ntaps, int devi
     h->decim = decim;
     h->tc_pref = fir_tc_env();
     h->real = real;
+    grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = h->sg.init(device);
     if (rc)
         return rc;
@@ -239,11 +240,14 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
     if (rc)
         return rc;
     cudaStream_t st = pick_stream(stream, h->sg);
-    if (h->halo_src && h->ntaps > 1 && noutput > 0) // the segment's history = the left neighbour's tail, fetched over NVLink
-        GRB_CUDA(cudaMemcpyAsync(const_cast<void*>(in_dev), h->halo_src, (size_t)(h->ntaps - 1) * h->isz(),
-                                 cudaMemcpyDeviceToDevice, st));
+    const size_t isz = (size_t)h->isz();
+    const void* halo = (h->halo_src && h->ntaps > 1) ? h->halo_src : nullptr; // see grb200_fir_set_halo_source
+    if (halo && h->real) { // fir_filter_fff stages through cp.async: bring the halo over first (one-CTA kernel, plain loads)
+        if ((rc = halo_fetch_launch(const_cast<void*>(in_dev), halo, (size_t)(h->ntaps - 1) * isz, st)))
+            return rc;
+    }
     rc = h->real ? fir_fff_launch(h->decim, h->ntaps, (const float*)h->rev.p, in_dev, out_dev, noutput, sm_count(h->device), st)
-                 : fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput, h->tc_pref, st);
+                 : fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput, h->tc_pref, st, halo);
     if (!rc && h->rot) {
         rc = rotate_launch(out_dev, noutput, h->theta, h->delta, st);
         h->theta = rotate_advance(h->theta, h->delta, noutput);

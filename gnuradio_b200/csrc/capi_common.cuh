@@ -10,8 +10,9 @@ namespace grb {
 // kernels' host launchers (fir.cu, fftvcc.cu, fftfilt.cu, pfb.cu)
 // tc_pref: the handle's GRB200_FIR_TC setting, read when the handle is made (fir_tc_env): -1 auto, 0 never, 1 whenever possible
 int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, const void* in, void* out,
-               long long nout, int tc_pref, cudaStream_t st);
+               long long nout, int tc_pref, cudaStream_t st, const void* halo = nullptr);
 int fir_tc_env();
+int halo_fetch_launch(void* dst, const void* src, size_t bytes, cudaStream_t st); // peer -> local by plain loads (fir.cu)
 // fir_filter_fff (fir_fff.cu): revp = reversed taps zero padded to fir_fff_pad(ntaps) floats
 int fir_fff_pad(int ntaps);
 int fir_fff_launch(int D, int ntaps, const float* revp, const void* in, void* out, long long nout, int nsm, cudaStream_t st);

@@ -47,6 +47,7 @@ int grb200_filterbank_vcvcf_create(int nfilts, int ntaps, const float* taps, int
         return fail(GRB200_EINVAL, "filterbank_vcvcf: at least one tap per filter is required");
     std::unique_ptr<grb200_fbank> h(new grb200_fbank);
     h->device = device;
+    grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = h->sg.init(device);
     if (rc)
         return rc;

@@ -83,6 +83,7 @@ int grb200_fftfilt_ccc_create(int decim, const float* taps_re_im, int ntaps, int
     std::unique_ptr<grb200_fftfilt> h(new grb200_fftfilt);
     h->device = device;
     h->decim = decim;
+    grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = h->sg.init(device);
     if (rc)
         return rc;

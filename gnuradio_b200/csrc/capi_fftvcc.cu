@@ -94,6 +94,7 @@ static int vcc_create(int fft_size, int forward, const float* window, int nwindo
     h->forward = forward != 0;
     h->shift = shift != 0;
     h->real_in = real_in != 0;
+    grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = h->sg.init(device);
     if (rc)
         return rc;
@@ -300,6 +301,7 @@ int grb200_logpwrfft_create(int complex_input, double sample_rate, int fft_size,
     const float n = 10.0f, k = (float)kd;
     h->log_mul = n / log2f(10.0f);
     h->log_scale = std::pow(10.0f, k / n);
+    grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = h->sg.init(device);
     if (rc)
         return rc;

@@ -168,6 +168,7 @@ static int interp_create(bool ct, unsigned interpolation, const float* taps, int
     h->device = device;
     h->ct = ct;
     h->L = (int)interpolation;
+    grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = h->sg.init(device);
     if (rc)
         return rc;

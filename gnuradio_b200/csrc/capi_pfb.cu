@@ -90,6 +90,7 @@ int grb200_pfb_chan_ccf_create(unsigned int numchans, const float* taps, int nta
     p->cmap.resize(numchans); // :59-63
     for (unsigned int i = 0; i < numchans; i++)
         p->cmap[i] = (int)i;
+    grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = p->sg.init(device);
     if (rc)
         return rc;

@@ -376,6 +376,7 @@ int grb200_pfb_dec_ccf_create(unsigned int decim, const float* taps, int ntaps, 
     p->M = (int)decim;
     p->chan = (int)channel;
     p->proto.assign(taps, taps + ntaps);
+    grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = p->sg.init(device);
     if (rc)
         return rc;

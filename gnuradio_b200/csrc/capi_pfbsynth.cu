@@ -111,6 +111,7 @@ int grb200_pfb_synth_ccf_create(unsigned int numchans, const float* taps, int nt
     p->cmap.resize((size_t)tw * numchans); // :50,58
     for (size_t i = 0; i < p->cmap.size(); i++)
         p->cmap[i] = (int)i;
+    grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = p->sg.init(device);
     if (rc)
         return rc;

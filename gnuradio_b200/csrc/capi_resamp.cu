@@ -255,6 +255,7 @@ static int resamp_create(bool ct, unsigned interpolation, unsigned decimation, c
     h->ct = ct;
     h->L = interpolation;
     h->D = decimation;
+    grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = h->sg.init(device);
     if (rc)
         return rc;

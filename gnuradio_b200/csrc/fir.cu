@@ -700,11 +700,12 @@ static int launch_tiled_nb(const FirPlan& pl, const void* in, void* out, long lo
 
 int fir_tc_mode(bool ct, int D, int ntaps, const void* in, long long nout, int tc_pref);
 int fir_tc_launch(int mode, int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
-                  cudaStream_t st);
+                  cudaStream_t st, const void* halo);
+int halo_fetch_launch(void* dst, const void* src, size_t bytes, cudaStream_t st);
 
 // gtaps: phase-major padded taps [D][Upad]; rev: reversed taps [ntaps] (both on the device).
 int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, const void* in, void* out,
-               long long nout, int tc_pref, cudaStream_t st)
+               long long nout, int tc_pref, cudaStream_t st, const void* halo)
 {
     if (nout <= 0)
         return 0;
@@ -714,8 +715,13 @@ int fir_launch(bool ct, int D, int ntaps, const void* gtaps, const void* rev, co
     cudaGetDevice(&dev);
     const int nsm = sm_count(dev);
     const int tc_mode = fir_tc_mode(ct, D, ntaps, in, nout, tc_pref); // tcgen05 block-Toeplitz paths (fir_tc.cu)
-    if (tc_mode >= 0)
-        return fir_tc_launch(tc_mode, ntaps, rev, in, out, nout, nin, nsm, st);
+    if (tc_mode >= 0) // the tensor-core kernels read a history halo in place (peer memory)
+        return fir_tc_launch(tc_mode, ntaps, rev, in, out, nout, nin, nsm, st, halo);
+    if (halo && ntaps > 1) { // the CUDA-core kernels stage through cp.async: bring the halo over first (one-CTA kernel)
+        int rc = halo_fetch_launch(const_cast<void*>(in), halo, (size_t)(ntaps - 1) * 8, st);
+        if (rc)
+            return rc;
+    }
     if (pl.tiled) {
         if (ct)
             return launch_tiled_nb<8, true>(pl, in, out, nout, nin, D, gtaps, nsm, st);
@@ -752,6 +758,23 @@ __global__ void __launch_bounds__(256) rotate_kernel(float2* __restrict__ y, lon
     sincosf((float)a, &sn, &cs);
     const float2 v = y[i];
     y[i] = make_float2(v.x * cs - v.y * sn, v.x * sn + v.y * cs);
+}
+
+// The history halo of a time-sharded segment, brought over from the left neighbour's memory by plain loads (NVLink peer
+// access): a one-CTA kernel costs ~2 us on the stream where a peer cudaMemcpyAsync of the same 0.5 - 8 KiB costs ~13.
+__global__ void __launch_bounds__(256) halo_fetch_kernel(float* __restrict__ dst, const float* __restrict__ src, int nwords)
+{
+    for (int i = threadIdx.x; i < nwords; i += blockDim.x)
+        dst[i] = src[i];
+}
+
+int halo_fetch_launch(void* dst, const void* src, size_t bytes, cudaStream_t st)
+{
+    if (bytes == 0)
+        return 0;
+    halo_fetch_kernel<<<1, 256, 0, st>>>((float*)dst, (const float*)src, (int)(bytes / 4));
+    GRB_LAUNCH_CHECK();
+    return 0;
 }
 
 int rotate_launch(void* y, long long n, double theta, double delta, cudaStream_t st)

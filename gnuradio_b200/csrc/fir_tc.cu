@@ -150,7 +150,8 @@ __device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__
 template <int MODE, bool TRACE>
 __global__ void __launch_bounds__(tc::NTHREADS, 1)
     fir_tc_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int ntaps,
-                  const void* __restrict__ rev_, long long ntiles, long long* __restrict__ trace)
+                  const void* __restrict__ rev_, long long ntiles, long long* __restrict__ trace,
+                  const float2* __restrict__ halo)
 {
     using namespace tc;
     using C = Cfg<MODE>;
@@ -255,7 +256,10 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
             mbar_wait(&raw_full[rs], ruse & 1);
             if (tr) trace[it * 16 + 1] = clock64();
             float4 v[C::CHUNKS][2];
-            if (e0 + ROWS * 64 <= nin) {
+            // a tile that reaches into the history halo of a time-sharded segment takes the plain-load path below and reads
+            // those ntaps-1 items where they are: the left neighbour's memory (halo), over NVLink
+            const bool in_halo = halo != nullptr && e0 < (long long)(ntaps - 1);
+            if (e0 + ROWS * 64 <= nin && !in_halo) {
                 const unsigned rb = sR_u32 + rs * RAW_BYTES + 32 * p;
 #pragma unroll
                 for (int i = 0; i < C::CHUNKS; ++i) {
@@ -270,7 +274,9 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                     const long long e = e0 + 4 * (p + 256 * i);
                     float2 z[4];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) z[u] = (e + u < nin) ? in[e + u] : make_float2(0.f, 0.f);
+                    for (int u = 0; u < 4; ++u)
+                        z[u] = (e + u < nin) ? ((in_halo && e + u < (long long)(ntaps - 1)) ? halo[e + u] : in[e + u])
+                                             : make_float2(0.f, 0.f);
                     v[i][0] = make_float4(z[0].x, z[0].y, z[1].x, z[1].y);
                     v[i][1] = make_float4(z[2].x, z[2].y, z[3].x, z[3].y);
                 }
@@ -588,7 +594,7 @@ int fir_tc_mode(bool ct, int D, int ntaps, const void* in, long long nout, int t
 
 template <int MODE>
 static int fir_tc_launch_t(int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
-                           cudaStream_t st)
+                           cudaStream_t st, const void* halo)
 {
     using C = tc::Cfg<MODE>;
     static std::atomic<int> configured[64]; // the attribute is per device
@@ -609,7 +615,7 @@ static int fir_tc_launch_t(int ntaps, const void* rev, const void* in, void* out
         GRB_CUDA(cudaMalloc(&dtrace, 64 * 16 * sizeof(long long)));
         GRB_CUDA(cudaMemsetAsync(dtrace, 0, 64 * 16 * sizeof(long long), st));
         fir_tc_kernel<MODE, true><<<grid, tc::NTHREADS, C::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps,
-                                                                            rev, ntiles, dtrace);
+                                                                            rev, ntiles, dtrace, (const float2*)halo);
         GRB_LAUNCH_CHECK();
         std::vector<long long> h(64 * 16);
         GRB_CUDA(cudaMemcpyAsync(h.data(), dtrace, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
@@ -625,21 +631,21 @@ static int fir_tc_launch_t(int ntaps, const void* rev, const void* in, void* out
         return 0;
     }
     fir_tc_kernel<MODE, false><<<grid, tc::NTHREADS, C::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps,
-                                                                         rev, ntiles, nullptr);
+                                                                         rev, ntiles, nullptr, (const float2*)halo);
     GRB_LAUNCH_CHECK();
     return 0;
 }
 
 int fir_tc_launch(int mode, int ntaps, const void* rev, const void* in, void* out, long long nout, long long nin, int nsm,
-                  cudaStream_t st)
+                  cudaStream_t st, const void* halo)
 {
     switch (mode) {
     case tc::M_CCF:
-        return fir_tc_launch_t<tc::M_CCF>(ntaps, rev, in, out, nout, nin, nsm, st);
+        return fir_tc_launch_t<tc::M_CCF>(ntaps, rev, in, out, nout, nin, nsm, st, halo);
     case tc::M_CCC:
-        return fir_tc_launch_t<tc::M_CCC>(ntaps, rev, in, out, nout, nin, nsm, st);
+        return fir_tc_launch_t<tc::M_CCC>(ntaps, rev, in, out, nout, nin, nsm, st, halo);
     case tc::M_DEC8:
-        return fir_tc_launch_t<tc::M_DEC8>(ntaps, rev, in, out, nout, nin, nsm, st);
+        return fir_tc_launch_t<tc::M_DEC8>(ntaps, rev, in, out, nout, nin, nsm, st, halo);
     }
     return fail(GRB200_ERANGE, "fir: no tensor-core mode %d", mode);
 }

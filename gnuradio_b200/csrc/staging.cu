@@ -53,6 +53,8 @@ int Stager::init(int dev_id)
         GRB_CUDA(cudaEventCreateWithFlags(&ev_d2h[i], cudaEventDisableTiming));
     }
     GRB_CUDA(cudaEventCreateWithFlags(&ev_user, cudaEventDisableTiming));
+    GRB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+    GRB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
     ready = true;
     return 0;
 }
@@ -103,6 +105,8 @@ void Stager::destroy()
     if (user_pending)
         cudaEventSynchronize(ev_user);
     cudaEventDestroy(ev_user);
+    cudaEventDestroy(ev_fork);
+    cudaEventDestroy(ev_join);
     for (auto& r : lag) {
         if (r.pin)
             cudaFreeHost(r.pin);

@@ -89,6 +89,7 @@ struct Stager {
     // stalling the whole device with cudaDeviceSynchronize
     cudaEvent_t ev_user = nullptr;
     bool user_pending = false;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr; // work_dev side branch (halo fetch overlapped with the main kernel)
 
     int init(int dev_id);
     void destroy();
