@@ -79,6 +79,83 @@ __global__ void __launch_bounds__(256) interp_fir_kernel(const float2* __restric
     }
 }
 
+
+// Tile form (EXPERIMENT, off by default; taps per phase 4 / 8 / 16 / 32, interpolation <= 16): ncu on the kernel above (profiles/r2_interp_ncu.txt) shows
+// the load/store unit, not HBM, as the limit -- L1/TEX 78 % busy, long-scoreboard stalls 11 per issue: every FMA pair costs a
+// scalar shared-memory tap load, the window comes through L1 one item at a time, and a warp's output stores are 16-byte
+// pieces 8L bytes apart.  Here a CTA stages the 256 + T-1 input items of a tile ONCE (coalesced), a thread reads its window
+// from shared memory (consecutive lanes, consecutive items), the taps of a phase arrive four per 16-byte broadcast load, and
+// the 256 L results go through shared memory so that the tile's output leaves as one contiguous run of 16-byte stores.
+template <int TT, bool CT>
+__global__ void __launch_bounds__(256) interp_fir_tile_kernel(const float2* __restrict__ in, float2* __restrict__ out,
+                                                              long long nin_pos, int L, const float* __restrict__ rev)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int ES = CT ? 2 : 1, PT = 256;
+    float* sh = reinterpret_cast<float*>(smem_raw);                       // [L][TT][ES] taps
+    float2* xs = reinterpret_cast<float2*>(sh + ((L * TT * ES + 3) & ~3)); // [PT + TT - 1] inputs (+1 pad)
+    float2* ys = xs + ((PT + TT + 1) & ~1);                               // [PT * L] outputs, rows skewed by one pair per 8 positions
+    const int tid = threadIdx.x;
+    for (int k = tid; k < L * TT * ES; k += PT)
+        sh[k] = rev[k];
+    const long long ntiles = (nin_pos + PT - 1) / PT;
+    const bool out16 = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long i0 = tile * PT;
+        const int npos = (int)(nin_pos - i0 < PT ? nin_pos - i0 : PT);
+        __syncthreads(); // the previous tile's outputs have left ys, its windows have been read
+        for (int k = tid; k < npos + TT - 1; k += PT)
+            xs[k] = __ldg(in + i0 + k);
+        __syncthreads();
+        if (tid < npos) {
+            float2 w[TT];
+#pragma unroll
+            for (int t = 0; t < TT; t++)
+                w[t] = xs[tid + t];
+            float2* y = ys + (size_t)tid * L;
+            for (int p = 0; p < L; p++) {
+                const float4* h4 = reinterpret_cast<const float4*>(sh + (size_t)p * TT * ES);
+                float2 a = make_float2(0.f, 0.f);
+                if (CT) {
+#pragma unroll
+                    for (int t = 0; t < TT; t += 2) {
+                        const float4 h = h4[t / 2]; // (hr, hi) of taps t, t+1
+                        a.x = fmaf(w[t].x, h.x, fmaf(-w[t].y, h.y, a.x));
+                        a.y = fmaf(w[t].x, h.y, fmaf(w[t].y, h.x, a.y));
+                        a.x = fmaf(w[t + 1].x, h.z, fmaf(-w[t + 1].y, h.w, a.x));
+                        a.y = fmaf(w[t + 1].x, h.w, fmaf(w[t + 1].y, h.z, a.y));
+                    }
+                } else {
+#pragma unroll
+                    for (int t = 0; t < TT; t += 4) {
+                        const float4 h = h4[t / 4];
+                        a = __ffma2_rn(make_float2(h.x, h.x), w[t], a);
+                        a = __ffma2_rn(make_float2(h.y, h.y), w[t + 1], a);
+                        a = __ffma2_rn(make_float2(h.z, h.z), w[t + 2], a);
+                        a = __ffma2_rn(make_float2(h.w, h.w), w[t + 3], a);
+                    }
+                }
+                y[p] = a;
+            }
+        }
+        __syncthreads();
+        // the tile's npos * L outputs are contiguous in the stream
+        const long long o0 = i0 * L;
+        const int nout = npos * L;
+        if (out16 && (o0 & 1) == 0) {
+            const float4* y4 = reinterpret_cast<const float4*>(ys);
+            float4* o4 = reinterpret_cast<float4*>(out + o0);
+            for (int k = tid; k < nout / 2; k += PT)
+                o4[k] = y4[k];
+            if ((nout & 1) && tid == 0)
+                out[o0 + nout - 1] = ys[nout - 1];
+        } else {
+            for (int k = tid; k < nout; k += PT)
+                out[o0 + k] = ys[k];
+        }
+    }
+}
+
 template <bool CT>
 static int interp_launch_t(const void* in, void* out, long long nin_pos, int L, int T, const float* rev, int nsm,
                            cudaStream_t st)
@@ -86,6 +163,37 @@ static int interp_launch_t(const void* in, void* out, long long nin_pos, int L, 
     const size_t smem = (size_t)L * T * (CT ? 8 : 4);
     if (smem > 200 * 1024)
         return fail(GRB200_ERANGE, "interp_fir_filter: %d x %d taps do not fit in shared memory", L, T);
+    static const bool use_tile = [] {
+        // measured on B200 (gpurun_out/r2_interp_check_v2.txt): 217 / 313 G output items/s at 4 x 16 / 8 x 8 against 355 / 439
+        // for the one-position-per-thread kernel -- three barriers per 256-position tile cost more than the load/store
+        // unit saves.  Kept as an experiment behind GRB200_INTERP_TILE=1.
+        const char* e = getenv("GRB200_INTERP_TILE");
+        return e && e[0] == '1';
+    }();
+    if (use_tile && L <= 16 && (T == 4 || T == 8 || T == 16 || T == 32) && nin_pos >= 1024) {
+        const size_t tsm = (((size_t)L * T * (CT ? 2 : 1) + 3) & ~(size_t)3) * 4 + (size_t)((256 + T + 1) & ~1) * 8 +
+                           (size_t)256 * L * 8;
+        long long ntiles = (nin_pos + 255) / 256, grid = (long long)nsm * 6;
+        if (grid > ntiles)
+            grid = ntiles;
+        auto tl = [&](auto kern) -> int {
+            if (tsm > 48 * 1024)
+                GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
+            kern<<<(unsigned)grid, 256, tsm, st>>>((const float2*)in, (float2*)out, nin_pos, L, rev);
+            GRB_LAUNCH_CHECK();
+            return 0;
+        };
+        switch (T) {
+        case 4:
+            return tl(interp_fir_tile_kernel<4, CT>);
+        case 8:
+            return tl(interp_fir_tile_kernel<8, CT>);
+        case 16:
+            return tl(interp_fir_tile_kernel<16, CT>);
+        default:
+            return tl(interp_fir_tile_kernel<32, CT>);
+        }
+    }
     long long nblk = (nin_pos + 255) / 256;
     const long long cap = (long long)nsm * 8;
     if (nblk > cap)
