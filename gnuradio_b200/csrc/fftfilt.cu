@@ -252,10 +252,14 @@ struct UpolsGeom {
     static constexpr int TWR_BYTES = fft_tws_slots(L, true) * TPV * 8;
     static constexpr int SMEM = XIN_BYTES + S_BYTES + TWF_BYTES + TWR_BYTES + 32;
     static constexpr int SLOT_COLS = (TPV / 128) * 32; // one parked spectrum: 32 columns per thread, 128 lanes
+    // K == 2: the filter's two partition spectra live in tensor memory too (a thread meets the same 16 bins in every
+    // block: 2 x 16 complex = 64 more columns of its lane), so the block loop reads nothing from L2
+    static __host__ __device__ constexpr int h_cols(int K) { return K == 2 ? 64 : 0; }
+    static __host__ __device__ constexpr int group_cols(int K) { return 32 * (K - 1) + h_cols(K); } // per 4 warps
     static __host__ __device__ constexpr int tmem_cols(int K) // power of two >= 32 (tcgen05.alloc)
     {
         int c = 32;
-        while (c < SLOT_COLS * (K - 1))
+        while (c < (TPV / 128) * group_cols(K))
             c *= 2;
         return c;
     }
@@ -320,7 +324,28 @@ fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, lo
     // this thread's parking space: its own lane (sub-partition = warp % 4); per group of four warps K-1 slots of 32
     // columns, slot (it mod K-1) holding the spectrum of the block of iteration `it`
     constexpr int nslot = K - 1;
-    const unsigned taddr0 = tmem + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)((warp >> 2) * nslot * 32);
+    const unsigned taddr0 = tmem + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)((warp >> 2) * G::group_cols(K));
+    const unsigned thaddr = taddr0 + (unsigned)(nslot * 32); // K == 2: this thread's H0 | H1 values, chunk c at +16c
+    if constexpr (K == 2) {
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            float2 a[4], b[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const int i = 4 * c + e;
+                const int k = (t + (i / RM) * TPV) + (i % RM) * (L / RM);
+                a[e] = __ldg(H + k);
+                b[e] = __ldg(H + L + k);
+            }
+            asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, "
+                         "%13, %14, %15, %16};" ::"r"(thaddr + c * 16),
+                         "f"(a[0].x), "f"(a[0].y), "f"(b[0].x), "f"(b[0].y), "f"(a[1].x), "f"(a[1].y), "f"(b[1].x),
+                         "f"(b[1].y), "f"(a[2].x), "f"(a[2].y), "f"(b[2].x), "f"(b[2].y), "f"(a[3].x), "f"(a[3].y),
+                         "f"(b[3].x), "f"(b[3].y)
+                         : "memory");
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
 
     if (b0 < b1) {
         const long long bw = b0 - nslot; // first warm-up block: K-1 forward transforms fill the delay line
@@ -383,13 +408,13 @@ fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, lo
                                  : "=f"(x[0].x), "=f"(x[0].y), "=f"(x[1].x), "=f"(x[1].y), "=f"(x[2].x), "=f"(x[2].y),
                                    "=f"(x[3].x), "=f"(x[3].y)
                                  : "r"(tnew + c * 8));
-    #pragma unroll
-                    for (int e = 0; e < 4; e++) {
-                        const int i = 4 * c + e;
-                        const int k = (t + (i / RM) * TPV) + (i % RM) * (L / RM);
-                        hh[c & 1][2 * e] = __ldg(H + k);
-                        hh[c & 1][2 * e + 1] = __ldg(H + L + k);
-                    }
+                    float2* h = hh[c & 1];
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, "
+                                 "%12, %13, %14, %15}, [%16];"
+                                 : "=f"(h[0].x), "=f"(h[0].y), "=f"(h[1].x), "=f"(h[1].y), "=f"(h[2].x), "=f"(h[2].y),
+                                   "=f"(h[3].x), "=f"(h[3].y), "=f"(h[4].x), "=f"(h[4].y), "=f"(h[5].x), "=f"(h[5].y),
+                                   "=f"(h[6].x), "=f"(h[6].y), "=f"(h[7].x), "=f"(h[7].y)
+                                 : "r"(thaddr + c * 16));
                 };
                 fetch(0);
     #pragma unroll
@@ -402,6 +427,19 @@ fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, lo
                                  : "+f"(x[0].x), "+f"(x[0].y), "+f"(x[1].x), "+f"(x[1].y), "+f"(x[2].x), "+f"(x[2].y),
                                    "+f"(x[3].x), "+f"(x[3].y), "+f"(y[0].x), "+f"(y[0].y), "+f"(y[1].x), "+f"(y[1].y),
                                    "+f"(y[2].x), "+f"(y[2].y), "+f"(y[3].x), "+f"(y[3].y));
+                    {
+                        // same wait, restated for the H registers of both buffers (a compiler fence for their uses)
+                        float2* h = hh[c & 1];
+                        float2* g = hh[(c + 1) & 1];
+                        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                                     : "+f"(h[0].x), "+f"(h[0].y), "+f"(h[1].x), "+f"(h[1].y), "+f"(h[2].x), "+f"(h[2].y),
+                                       "+f"(h[3].x), "+f"(h[3].y), "+f"(h[4].x), "+f"(h[4].y), "+f"(h[5].x), "+f"(h[5].y),
+                                       "+f"(h[6].x), "+f"(h[6].y), "+f"(h[7].x), "+f"(h[7].y));
+                        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                                     : "+f"(g[0].x), "+f"(g[0].y), "+f"(g[1].x), "+f"(g[1].y), "+f"(g[2].x), "+f"(g[2].y),
+                                       "+f"(g[3].x), "+f"(g[3].y), "+f"(g[4].x), "+f"(g[4].y), "+f"(g[5].x), "+f"(g[5].y),
+                                       "+f"(g[6].x), "+f"(g[6].y), "+f"(g[7].x), "+f"(g[7].y));
+                    }
                     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(
                                      tnew + c * 8),
                                  "f"(v[4 * c].x), "f"(v[4 * c].y), "f"(v[4 * c + 1].x), "f"(v[4 * c + 1].y),
