@@ -573,6 +573,316 @@ static int launch_upols(const void* in, void* out, long long nout, long long nin
     return 0;
 }
 
+// ---- two partitions, three blocks in flight per SM (`fftfilt_upols2_kernel`, 2050..4096 taps: cfg2) -----------------
+// The generic kernel above sits at 2 CTAs x 8 warps per SM (128 registers, 100 KB of shared memory per CTA) and its FMA pipe
+// idles half of the time: four warps per scheduler do not cover the exchanges between the radix passes.  This variant is
+// the same algorithm cut down so that THREE blocks are in flight per SM, as three independent 256-thread groups of ONE
+// 768-thread CTA (named barriers 1..3 instead of __syncthreads): one CTA owns all 512 tensor-memory columns, so H0 and H1
+// (a thread meets the same 16 bins in every block, and so do its two namesakes in the other groups) are written to tensor
+// memory once and shared by the three groups -- the block loop reads nothing from L2 -- next to the three parked spectra
+// (128 + 3 x 64 = 320 columns).  4096 = 16 x 16 x 16 written out; the twiddles of the middle pass come from a 16 x 15
+// table (no products: 11 complex multiplies fewer per transform), those of the last pass from three values per thread
+// (w, w^2, w^4; w^8 = (w^4)^2); one table for both directions (the inverse conjugates in registers), shared by the groups:
+// 3 x 66 + 8 KB of shared memory, 80 registers.
+struct Upols2 {
+    static constexpr int L = 4096, TPV = 256, V = 2048, SLICE = V + 2, NG = 3;
+    static constexpr int XIN_BYTES = 2 * SLICE * 8;
+    static constexpr int S_BYTES = ((fft_smem_elems(L) * 8 + 15) / 16) * 16;
+    static constexpr int T1_STRIDE = 18; // float2 per table row (144 bytes: 16-byte loads of 8 rows hit 8 x 4 distinct banks)
+    static constexpr int T1_BYTES = 16 * T1_STRIDE * 8;
+    static constexpr int TW2_BYTES = 3 * TPV * 8;
+    static constexpr int SMEM = NG * (XIN_BYTES + S_BYTES) + T1_BYTES + TW2_BYTES + NG * 16 + 16;
+    static constexpr int TMEM_COLS = 512; // [0,64) H0, [64,128) H1, [128 + 64 g, +64) group g's parked spectrum
+};
+
+template <bool FWD>
+__device__ __forceinline__ float2 cmul_dir(float2 a, float2 w) // a * w forward, a * conj(w) inverse
+{
+    if constexpr (FWD)
+        return cmul(a, w);
+    else {
+        const float2 t = __fmul2_rn(make_float2(a.y, a.y), make_float2(w.y, w.x)); // (a.y w.y, a.y w.x)
+        return __ffma2_rn(make_float2(a.x, a.x), make_float2(w.x, -w.y), t);
+    }
+}
+
+__device__ __forceinline__ void group_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
+
+// Register convention as cta_fft: in v[q] = x[t + 256 q], out v[q] = X[t + 256 q]; `bid` = the group's barrier.
+template <bool FWD, class After>
+__device__ __forceinline__ void fft4096_3x16(float2 (&v)[16], float2* S, int t, int bid, const float2* T1,
+                                             const float2* TW2, After after_first)
+{
+    // one base address per access pattern, constant offsets (fft_pad(i) = i + i / 16 is linear along each of them; left to
+    // itself the compiler forms 16 addresses per gather, keeps them across the block loop and spills them)
+    float2* Sg = S + t + (t >> 4);                                     // gather:  fft_pad(t + 256 q) = Sg + 272 q
+    float2* Sa = S + 17 * t;                                           // scatter 0: fft_pad(16 t + q) = Sa + q
+    float2* Sb = S + fft_pad((t >> 4) * 256 + (t & 15));               // scatter 1: fft_pad(base + 16 q) = Sb + 17 q
+    dft16<FWD>(v);
+#pragma unroll
+    for (int q = 0; q < 16; q++)
+        Sa[q] = v[q];
+    group_sync(bid);
+    after_first();
+#pragma unroll
+    for (int q = 0; q < 16; q++)
+        v[q] = Sg[272 * q];
+    {
+        // W256^{q (t mod 16)}.  (volatile asm: loop invariant, and ptxas would otherwise keep all 38 twiddle registers of
+        // the two directions live across the block loop and spill them)
+        const unsigned row = smem_u32(T1 + (t & 15) * Upols2::T1_STRIDE);
+#pragma unroll
+        for (int p = 0; p < 8; p++) {
+            float4 w;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(w.x), "=f"(w.y), "=f"(w.z), "=f"(w.w)
+                         : "r"(row + 16 * p));
+            if (p > 0)
+                v[2 * p] = cmul_dir<FWD>(v[2 * p], make_float2(w.x, w.y));
+            v[2 * p + 1] = cmul_dir<FWD>(v[2 * p + 1], make_float2(w.z, w.w));
+        }
+    }
+    dft16<FWD>(v);
+    group_sync(bid);
+#pragma unroll
+    for (int q = 0; q < 16; q++)
+        Sb[17 * q] = v[q];
+    group_sync(bid);
+#pragma unroll
+    for (int q = 0; q < 16; q++)
+        v[q] = Sg[272 * q];
+    {
+        float2 w1, w2, w4; // W4096^{t, 2t, 4t}
+        const unsigned a = smem_u32(TW2 + t);
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(w1.x), "=f"(w1.y) : "r"(a));
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(w2.x), "=f"(w2.y) : "r"(a + Upols2::TPV * 8));
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(w4.x), "=f"(w4.y) : "r"(a + 2 * Upols2::TPV * 8));
+        if constexpr (!FWD) {
+            w1 = cconj(w1);
+            w2 = cconj(w2);
+            w4 = cconj(w4);
+        }
+        const float2 w8 = cmul(w4, w4);
+        apply_twiddles_l<16>(v, [&](int k) { return k == 0 ? w1 : (k == 1 ? w2 : (k == 2 ? w4 : w8)); });
+    }
+    dft16<FWD>(v);
+}
+
+__global__ void __launch_bounds__(768, 1)
+fftfilt_upols2_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int ntaps,
+                      int D, const float2* __restrict__ H, const float2* __restrict__ tw, long long run, int gs)
+{
+    using G = Upols2;
+    constexpr int L = G::L, TPV = G::TPV, V = G::V, SLICE = G::SLICE, NG = G::NG;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int grp = threadIdx.x >> 8, t = threadIdx.x & 255, warp = t >> 5, bid = grp + 1;
+    float2* XIN = reinterpret_cast<float2*>(smem_raw + grp * (G::XIN_BYTES + G::S_BYTES));
+    float2* S = reinterpret_cast<float2*>(smem_raw + grp * (G::XIN_BYTES + G::S_BYTES) + G::XIN_BYTES);
+    float2* T1 = reinterpret_cast<float2*>(smem_raw + NG * (G::XIN_BYTES + G::S_BYTES));
+    float2* TW2 = reinterpret_cast<float2*>(smem_raw + NG * (G::XIN_BYTES + G::S_BYTES) + G::T1_BYTES);
+    unsigned long long* bar0 =
+        reinterpret_cast<unsigned long long*>(smem_raw + NG * (G::XIN_BYTES + G::S_BYTES) + G::T1_BYTES + G::TW2_BYTES);
+    unsigned long long* bar = bar0 + 2 * grp;
+    unsigned* tmem_slot = reinterpret_cast<unsigned*>(bar0 + 2 * NG);
+    const long long ny = nout * D;
+    const long long nblocks = (ny + V - 1) / V;
+    const long long nin_even = nin & ~1LL;
+    const int c0 = ntaps - 1 + gs, off = c0 & 1;
+    const long long b0 = ((long long)blockIdx.x * NG + grp) * run;
+    const long long b1 = (b0 + run < nblocks) ? b0 + run : nblocks;
+
+    auto issue = [&](long long j) { // slice j = buffer items [(j-1)V + c0, jV + c0), as in the generic kernel
+        const int h = (int)(j & 1);
+        const long long lo = (j - 1) * V + c0 - off;
+        const long long lo_c = lo < 0 ? 0 : lo;
+        long long hi_c = lo + SLICE;
+        hi_c = hi_c > nin_even ? nin_even : hi_c;
+        const long long n = hi_c > lo_c ? hi_c - lo_c : 0;
+        mbar_expect_tx(&bar[h], (unsigned)(n * 8));
+        if (n)
+            bulk_g2s(XIN + h * SLICE + (lo_c - lo), in + lo_c, (unsigned)(n * 8), &bar[h]);
+    };
+
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(G::TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (t == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+    }
+    if (grp == 0) {
+        const int r = t >> 4, q = t & 15; // T1[r][q] = W256^{q r} = W4096^{16 q r}
+        T1[r * G::T1_STRIDE + q] = tw[(16 * q * r) & (L - 1)];
+        if (q < 2)
+            T1[r * G::T1_STRIDE + 16 + q] = make_float2(0.f, 0.f);
+        TW2[t] = tw[t];
+        TW2[TPV + t] = tw[2 * t];
+        TW2[2 * TPV + t] = tw[4 * t];
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const unsigned tmem = *tmem_slot;
+    const unsigned tlane = tmem + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)((warp >> 2) * 32);
+    const unsigned th0 = tlane, th1 = tlane + 64, tpark = tlane + 128 + (unsigned)(grp * 64);
+    if (grp == 0) { // bins k = t + 256 i, i = 0..15, of both partitions: column 2 i of this thread's lane
+#pragma unroll
+        for (int p = 0; p < 2; p++)
+#pragma unroll
+            for (int c = 0; c < 2; c++) {
+                float2 a[8];
+#pragma unroll
+                for (int e = 0; e < 8; e++)
+                    a[e] = __ldg(H + p * L + t + 256 * (8 * c + e));
+                asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, "
+                             "%12, %13, %14, %15, %16};" ::"r"((p ? th1 : th0) + c * 16),
+                             "f"(a[0].x), "f"(a[0].y), "f"(a[1].x), "f"(a[1].y), "f"(a[2].x), "f"(a[2].y), "f"(a[3].x),
+                             "f"(a[3].y), "f"(a[4].x), "f"(a[4].y), "f"(a[5].x), "f"(a[5].y), "f"(a[6].x), "f"(a[6].y),
+                             "f"(a[7].x), "f"(a[7].y)
+                             : "memory");
+            }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads(); // H0 | H1 are in place for the other groups
+    asm volatile("tcgen05.fence::after_thread_sync;");
+
+    if (b0 < b1) {
+        const long long bw = b0 - 1; // warm-up block: one forward transform fills the delay line
+        if (t == 0) {
+            issue(bw);
+            issue(bw + 1);
+        }
+        unsigned ph = 0;
+        for (long long blk = bw; blk < b1; blk++) {
+            const int hnew = (int)((blk + 1) & 1);
+            if (blk == bw) {
+                mbar_wait(&bar[hnew ^ 1], (ph >> (hnew ^ 1)) & 1);
+                ph ^= 1u << (hnew ^ 1);
+            }
+            mbar_wait(&bar[hnew], (ph >> hnew) & 1);
+            ph ^= 1u << hnew;
+            const long long s = (blk - 1) * V + c0; // buffer index of the block's first item
+            float2 v[16];
+            const float2* xo = XIN + (hnew ^ 1) * SLICE + off + t; // old half: m = t + 256 q, q < 8
+            const float2* xn = XIN + hnew * SLICE + off + t;       // new half: q >= 8
+            if (s >= gs && s + L <= nin_even) { // interior block: every item came with the bulk copies
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    v[q] = xo[256 * q];
+                    v[q + 8] = xn[256 * q];
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < 16; q++) {
+                    const long long g = s + t + 256 * q;
+                    float2 x = make_float2(0.f, 0.f);
+                    if (g >= gs && g < nin_even)
+                        x = (q < 8 ? xo : xn)[256 * (q & 7)];
+                    else if (g >= gs && g < nin)
+                        x = in[g];
+                    v[q] = x;
+                }
+            }
+            fft4096_3x16<true>(v, S, t, bid, T1, TW2, [&]() {
+                if (t == 0 && blk + 1 < b1)
+                    issue(blk + 2); // into the half that held slice blk: every thread of the group has read it by now
+            });
+            if (blk < b0) { // warm-up: only park the spectrum
+#pragma unroll
+                for (int c = 0; c < 4; c++)
+                    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(
+                                     tpark + c * 8),
+                                 "f"(v[4 * c].x), "f"(v[4 * c].y), "f"(v[4 * c + 1].x), "f"(v[4 * c + 1].y),
+                                 "f"(v[4 * c + 2].x), "f"(v[4 * c + 2].y), "f"(v[4 * c + 3].x), "f"(v[4 * c + 3].y)
+                                 : "memory");
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                group_sync(bid); // the transform's last gather is done before the next block reuses S
+                continue;
+            }
+            // v = X_b . H0 + X_{b-1} . H1; X_b takes X_{b-1}'s place.  Four chunks of four bins, everything out of tensor
+            // memory (three short reads, one wait; the other two groups of the CTA fill the gap -- a second register
+            // buffer to overlap the reads spills at 80 registers).
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                float2 x[4], h0[4], h1[4];
+                auto ld8 = [&](float2* a, unsigned addr) {
+                    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                                 : "=f"(a[0].x), "=f"(a[0].y), "=f"(a[1].x), "=f"(a[1].y), "=f"(a[2].x), "=f"(a[2].y),
+                                   "=f"(a[3].x), "=f"(a[3].y)
+                                 : "r"(addr));
+                };
+                ld8(x, tpark + c * 8);
+                ld8(h0, th0 + c * 8);
+                ld8(h1, th1 + c * 8);
+                // the wait lists every register the reads write, so no use of them can move above it
+                asm volatile("tcgen05.wait::ld.sync.aligned;"
+                             : "+f"(x[0].x), "+f"(x[0].y), "+f"(x[1].x), "+f"(x[1].y), "+f"(x[2].x), "+f"(x[2].y),
+                               "+f"(x[3].x), "+f"(x[3].y), "+f"(h0[0].x), "+f"(h0[0].y), "+f"(h0[1].x), "+f"(h0[1].y),
+                               "+f"(h0[2].x), "+f"(h0[2].y), "+f"(h0[3].x), "+f"(h0[3].y), "+f"(h1[0].x), "+f"(h1[0].y),
+                               "+f"(h1[1].x), "+f"(h1[1].y), "+f"(h1[2].x), "+f"(h1[2].y), "+f"(h1[3].x), "+f"(h1[3].y));
+                asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(
+                                 tpark + c * 8),
+                             "f"(v[4 * c].x), "f"(v[4 * c].y), "f"(v[4 * c + 1].x), "f"(v[4 * c + 1].y),
+                             "f"(v[4 * c + 2].x), "f"(v[4 * c + 2].y), "f"(v[4 * c + 3].x), "f"(v[4 * c + 3].y));
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float2 a = v[4 * c + e], p = x[e], g0 = h0[e], g1 = h1[e];
+                    v[4 * c + e] = make_float2(fmaf(a.x, g0.x, fmaf(-a.y, g0.y, fmaf(p.x, g1.x, -p.y * g1.y))),
+                                               fmaf(a.x, g0.y, fmaf(a.y, g0.x, fmaf(p.x, g1.y, p.y * g1.x))));
+                }
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            group_sync(bid); // forward transform's last gather is done before the inverse reuses S
+            fft4096_3x16<false>(v, S, t, bid, T1, TW2, []() {});
+            const long long n0 = blk * V + t; // outputs m = t + 256 q, q >= 8 (the alias-free half)
+            if (D == 1 && (blk + 1) * V <= ny) {
+#pragma unroll
+                for (int q = 8; q < 16; q++)
+                    out[n0 + 256 * (q - 8)] = v[q];
+            } else {
+#pragma unroll
+                for (int q = 8; q < 16; q++) {
+                    const long long n = n0 + 256 * (q - 8);
+                    if (n < ny) {
+                        if (D == 1)
+                            out[n] = v[q];
+                        else if (n % D == 0)
+                            out[n / D] = v[q];
+                    }
+                }
+            }
+            group_sync(bid);
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    if (threadIdx.x < 32)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(G::TMEM_COLS));
+}
+
+static int launch_upols2(const void* in, void* out, long long nout, long long nin, int ntaps, int D, const float2* H,
+                         const float2* tw, int nsm, cudaStream_t st)
+{
+    using G = Upols2;
+    auto kern = fftfilt_upols2_kernel;
+    GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
+    const long long nblocks = (nout * D + G::V - 1) / G::V;
+    long long groups = (long long)nsm * G::NG; // one CTA per SM, NG independent block runs each
+    if (groups > nblocks)
+        groups = nblocks;
+    const long long run = (nblocks + groups - 1) / groups;
+    groups = (nblocks + run - 1) / run;
+    const long long grid = (groups + G::NG - 1) / G::NG;
+    const int gs = (int)((((uintptr_t)in) >> 3) & 1);
+    kern<<<(unsigned)grid, G::NG * G::TPV, G::SMEM, st>>>((const float2*)in - gs, (float2*)out, nout, nin + gs, ntaps, D, H,
+                                                          tw, run, gs);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
 // Device plan for a tap count: FFT length L (at least the reference's 2*2^ceil(log2 ntaps), never below 4096) and
 // the number of tap partitions K (1 = plain overlap-save with hop L-ntaps+1, 2 = partitioned with hop L/2).  Runs at
 // create / set_taps time only (the developer knobs below are never read per work()).
@@ -618,8 +928,15 @@ int fftfilt_launch(int L, int parts, const void* in, void* out, long long nout, 
             return fail(GRB200_EINVAL, "fft_filter: input stream is not aligned to its item size");
         if (L == 4096) {
             switch (parts) {
-            case 2:
+            case 2: {
+                static const bool three = [] {
+                    const char* e = GRB_GETENV_ONCE("GRB200_FFTFILT_UPOLS2"); // 0 = the generic kernel (2 CTAs per SM)
+                    return !(e && e[0] == '0');
+                }();
+                if (three)
+                    return launch_upols2(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
                 return launch_upols<4096, 2>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+            }
             case 3:
                 return launch_upols<4096, 3>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
             case 4:
