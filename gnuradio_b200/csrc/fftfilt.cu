@@ -619,18 +619,12 @@ __device__ __forceinline__ void fft4096_3x16(float2 (&v)[16], float2* S, int t, 
     float2* Sa = S + 17 * t;                                           // scatter 0: fft_pad(16 t + q) = Sa + q
     float2* Sb = S + fft_pad((t >> 4) * 256 + (t & 15));               // scatter 1: fft_pad(base + 16 q) = Sb + 17 q
     dft16<FWD>(v);
-#pragma unroll
-    for (int q = 0; q < 16; q++)
-        Sa[q] = v[q];
-    group_sync(bid);
-    after_first();
-#pragma unroll
-    for (int q = 0; q < 16; q++)
-        v[q] = Sg[272 * q];
     {
-        // W256^{q (t mod 16)}.  (volatile asm: loop invariant, and ptxas would otherwise keep all 38 twiddle registers of
-        // the two directions live across the block loop and spill them)
-        const unsigned row = smem_u32(T1 + (t & 15) * Upols2::T1_STRIDE);
+        // The middle pass's twiddles, applied here: output q of this thread becomes input t >> 4 of thread (16 t + q) mod
+        // 256, whose twiddle W256^{(t >> 4) ((16 t + q) mod 16)} = W256^{q (t >> 4)} -- row t >> 4 of the table, two rows
+        // per warp (a 16-byte load is one wavefront; by the reading thread's t mod 16 it would be four).  (volatile asm:
+        // loop invariant, and ptxas would otherwise keep the twiddle registers live across the block loop and spill them)
+        const unsigned row = smem_u32(T1 + (t >> 4) * Upols2::T1_STRIDE);
 #pragma unroll
         for (int p = 0; p < 8; p++) {
             float4 w;
@@ -642,6 +636,14 @@ __device__ __forceinline__ void fft4096_3x16(float2 (&v)[16], float2* S, int t, 
             v[2 * p + 1] = cmul_dir<FWD>(v[2 * p + 1], make_float2(w.z, w.w));
         }
     }
+#pragma unroll
+    for (int q = 0; q < 16; q++)
+        Sa[q] = v[q];
+    group_sync(bid);
+    after_first();
+#pragma unroll
+    for (int q = 0; q < 16; q++)
+        v[q] = Sg[272 * q];
     dft16<FWD>(v);
     group_sync(bid);
 #pragma unroll
@@ -750,31 +752,41 @@ fftfilt_upols2_kernel(const float2* __restrict__ in, float2* __restrict__ out, l
     asm volatile("tcgen05.fence::after_thread_sync;");
 
     if (b0 < b1) {
-        const long long bw = b0 - 1; // warm-up block: one forward transform fills the delay line
+        // loop state in 32 bits, relative to the run's first block (64-bit stream positions only on the edge paths):
+        // iteration i = -1 (warm-up: one forward transform fills the delay line) .. nrun - 1 is block b0 + i
+        const int nrun = (int)(b1 - b0);
+        const long long s0 = (b0 - 1) * V + c0; // buffer index of block b0's first item; block b0 + i starts at s0 + i V
+        // interior iterations: every item of the block came with the bulk copies (s >= gs and s + L <= nin_even)
+        long long lo64 = s0 >= gs ? 0 : (gs - s0 + V - 1) / V, hi64 = (nin_even - L - s0) >= 0 ? (nin_even - L - s0) / V + 1 : 0;
+        const int i_lo = (int)(lo64 > nrun ? nrun : lo64), i_hi = (int)(hi64 > nrun ? nrun : hi64);
+        // iterations whose 2048 outputs all exist: (b0 + i + 1) V <= ny
+        long long full64 = ny / V - b0;
+        const int i_full = D == 1 ? (int)(full64 > nrun ? nrun : (full64 < 0 ? 0 : full64)) : 0;
+        float2* outp = out + b0 * V + t; // block b0 + i's outputs: outp[i V + 256 (q - 8)]
         if (t == 0) {
-            issue(bw);
-            issue(bw + 1);
+            issue(b0 - 1);
+            issue(b0);
         }
         unsigned ph = 0;
-        for (long long blk = bw; blk < b1; blk++) {
-            const int hnew = (int)((blk + 1) & 1);
-            if (blk == bw) {
+        for (int i = -1; i < nrun; i++) {
+            const int hnew = (int)((b0 + i + 1) & 1);
+            if (i == -1) {
                 mbar_wait(&bar[hnew ^ 1], (ph >> (hnew ^ 1)) & 1);
                 ph ^= 1u << (hnew ^ 1);
             }
             mbar_wait(&bar[hnew], (ph >> hnew) & 1);
             ph ^= 1u << hnew;
-            const long long s = (blk - 1) * V + c0; // buffer index of the block's first item
             float2 v[16];
             const float2* xo = XIN + (hnew ^ 1) * SLICE + off + t; // old half: m = t + 256 q, q < 8
             const float2* xn = XIN + hnew * SLICE + off + t;       // new half: q >= 8
-            if (s >= gs && s + L <= nin_even) { // interior block: every item came with the bulk copies
+            if (i >= i_lo && i < i_hi) {
 #pragma unroll
                 for (int q = 0; q < 8; q++) {
                     v[q] = xo[256 * q];
                     v[q + 8] = xn[256 * q];
                 }
             } else {
+                const long long s = s0 + (long long)i * V;
 #pragma unroll
                 for (int q = 0; q < 16; q++) {
                     const long long g = s + t + 256 * q;
@@ -787,10 +799,10 @@ fftfilt_upols2_kernel(const float2* __restrict__ in, float2* __restrict__ out, l
                 }
             }
             fft4096_3x16<true>(v, S, t, bid, T1, TW2, [&]() {
-                if (t == 0 && blk + 1 < b1)
-                    issue(blk + 2); // into the half that held slice blk: every thread of the group has read it by now
+                if (t == 0 && i + 1 < nrun)
+                    issue(b0 + i + 2); // into the half that held slice blk: every thread of the group has read it by now
             });
-            if (blk < b0) { // warm-up: only park the spectrum
+            if (i < 0) { // warm-up: only park the spectrum
 #pragma unroll
                 for (int c = 0; c < 4; c++)
                     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(
@@ -837,12 +849,13 @@ fftfilt_upols2_kernel(const float2* __restrict__ in, float2* __restrict__ out, l
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             group_sync(bid); // forward transform's last gather is done before the inverse reuses S
             fft4096_3x16<false>(v, S, t, bid, T1, TW2, []() {});
-            const long long n0 = blk * V + t; // outputs m = t + 256 q, q >= 8 (the alias-free half)
-            if (D == 1 && (blk + 1) * V <= ny) {
+            if (i < i_full) { // outputs m = t + 256 q, q >= 8 (the alias-free half)
+                float2* o = outp + (long long)i * V;
 #pragma unroll
                 for (int q = 8; q < 16; q++)
-                    out[n0 + 256 * (q - 8)] = v[q];
+                    o[256 * (q - 8)] = v[q];
             } else {
+                const long long n0 = (b0 + i) * V + t;
 #pragma unroll
                 for (int q = 8; q < 16; q++) {
                     const long long n = n0 + 256 * (q - 8);
