@@ -150,6 +150,7 @@ SIGNATURES = {
     "grb200_logpwrfft_fft_size": (i32, [vp]),
     "grb200_logpwrfft_work": (i32, [vp, vp, i64, vp, i64, C.POINTER(i64), C.POINTER(i64)]),
     "grb200_logpwrfft_work_dev": (i32, [vp, vp, i64, vp, i64, C.POINTER(i64), C.POINTER(i64), vp]),
+    "grb200_logpwrfft_work_dev_static": (i32, [vp, vp, i64, vp, i64, C.POINTER(i64), C.POINTER(i64), vp]),
     "grb200_logpwrfft_destroy": (None, [vp]),
     "grb200_vector_to_streams_work": (i32, [i32, i32, i32, vp, pvp, i64]),
     "grb200_vector_to_streams_work_dev": (i32, [i32, i32, i32, vp, vp, i64, i64, vp]),

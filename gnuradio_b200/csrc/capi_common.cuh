@@ -40,6 +40,10 @@ struct VccArgs {
 int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st);
 // logpwr.cu: single_pole_iir along the frames + nlog10, in place on p [nframes][N]
 long long logpwr_scratch_floats(long long nframes, int N, int nsm);
+long long logpwr_static_scratch_floats();
+int logpwr_static_check(long long nframes, int N, int nsm);
+int logpwr_iir_log_launch_static(float* p, long long nframes, int N, double alpha, float* ystate, float log_mul,
+                                 float log_scale, int nsm, int device, cudaStream_t st);
 int logpwr_iir_log_launch(float* p, long long nframes, int N, double alpha, float* ystate, float* scratch, float log_mul,
                           float log_scale, int nsm, cudaStream_t st);
 int fftfilt_device_plan(int ntaps, int* parts);

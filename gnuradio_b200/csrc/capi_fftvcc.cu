@@ -521,3 +521,45 @@ void grb200_logpwrfft_destroy(grb200_logpwr* h)
 }
 
 } // extern "C"
+
+// ---- grb200_logpwrfft_work_dev_static: grb200_logpwrfft_work_dev that allocates nothing -------------------------------
+// No counterpart in the reference: the averaging tail's scratch is the
+// library's file-scope device array (logpwr.cu) instead of the handle's lazily cudaMalloc'ed buffer, so the call is legal
+// where cudaMalloc is not.  A call that does not fit is refused BEFORE anything is launched: the handle's decimator counter
+// and filter memory stay as they were.  Same kernels, same run lengths, same bits as grb200_logpwrfft_work_dev.
+extern "C" int grb200_logpwrfft_work_dev_static(grb200_logpwr* h, const void* in_dev, long long nitems, float* out_dev,
+                                                long long max_out, long long* consumed, long long* produced, void* stream)
+{
+    if (!h || nitems < 0 || max_out < 0 || !consumed || !produced)
+        return fail(GRB200_EINVAL, "logpwrfft::work_dev_static: bad arguments");
+    std::lock_guard<std::mutex> lk(h->mu);
+    long long first, nkeep, used;
+    int cnt;
+    logpwr_plan(h, nitems / h->N, max_out, &first, &nkeep, &used, &cnt);
+    if (nkeep > 0 && (!in_dev || !out_dev))
+        return fail(GRB200_EINVAL, "logpwrfft::work_dev_static: null buffer");
+    grb::DeviceScope _ds(h->device);
+    int rc = _ds.rc;
+    if (rc)
+        return rc;
+    const int nsm = sm_count(h->device);
+    const bool avg = h->average && h->avg_alpha != 1.0;
+    if (avg && nkeep > 0 && (rc = logpwr_static_check(nkeep, h->N, nsm)))
+        return rc;
+    cudaStream_t st_ = pick_stream(stream, h->sg);
+    if (nkeep > 0) {
+        VccArgs a{ in_dev, out_dev, nkeep, (const float*)h->window.p, (const float2*)h->tw.p, 0, avg ? 1 : 2, h->decim, first,
+                   h->log_mul, h->log_scale, (float*)h->ystate.p };
+        rc = fft_vcc_launch_ex(h->N, true, !h->complex_input, a, nsm, st_);
+        if (!rc && avg)
+            rc = logpwr_iir_log_launch_static(out_dev, nkeep, h->N, h->avg_alpha, (float*)h->ystate.p, h->log_mul,
+                                              h->log_scale, nsm, h->device, st_);
+    }
+    rc = dev_done(rc, h->sg, st_);
+    if (rc)
+        return rc;
+    h->count = cnt;
+    *consumed = used * h->N;
+    *produced = nkeep;
+    return 0;
+}

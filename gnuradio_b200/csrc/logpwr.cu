@@ -156,4 +156,70 @@ int logpwr_iir_log_launch(float* p, long long nframes, int N, double alpha, floa
     return 0;
 }
 
+// ---- the same three launches over a scratch array that is part of the library image (no allocation, ever) -------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it):
+// the run aggregates / carries go to a file-scope device array instead of the handle's lazily grown buffer.  Every GPU that
+// loads the library holds these LOGPWR_STATIC_SCRATCH_FLOATS * 4 bytes until the process exits.  ONE array per device,
+// shared by every handle and every call: two calls that overlap on the GPU (different streams, or different handles on
+// different streams) race on it -- the caller serialises them.  The array keeps the last call's contents; nothing in it has
+// to start at zero (logpwr_local_kernel writes agg[run][bin] for every run and bin before logpwr_carry_kernel reads it), so it
+// is never cleared.
+constexpr long long LOGPWR_STATIC_SCRATCH_FLOATS = GRB200_LOGPWR_STATIC_SCRATCH_BYTES / 4; // 1 MiB (grb200.h)
+static __device__ __align__(256) float g_logpwr_static_scratch[LOGPWR_STATIC_SCRATCH_FLOATS];
+
+long long logpwr_static_scratch_floats() { return LOGPWR_STATIC_SCRATCH_FLOATS; }
+
+// In HOST code the array's name is a host-side stand-in, not a device address: the address the kernels are given comes from
+// cudaGetSymbolAddress, asked once per device with that device current (the caller holds a DeviceScope).
+static int logpwr_static_scratch_ptr(int device, float** out)
+{
+    constexpr int MAXDEV = 64;
+    static std::mutex mu;
+    static float* ptr[MAXDEV] = {};
+    if (device < 0 || device >= MAXDEV)
+        return fail(GRB200_EINVAL, "logpwrfft (static scratch): device %d out of range", device);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[device]) {
+        int cur = -1;
+        GRB_CUDA(cudaGetDevice(&cur));
+        if (cur != device)
+            return fail(GRB200_EINVAL, "logpwrfft (static scratch): device %d is not current (%d is)", device, cur);
+        float* q = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&q, g_logpwr_static_scratch);
+        if (e != cudaSuccess || !q)
+            return fail(GRB200_ECUDA, "cudaGetSymbolAddress(static scratch) failed on device %d: %s", device,
+                        cudaGetErrorString(e));
+        ptr[device] = q;
+    }
+    *out = ptr[device];
+    return 0;
+}
+
+// 0 when a call of `nframes` kept frames fits the static array; GRB200_ERANGE (nothing launched) otherwise.
+int logpwr_static_check(long long nframes, int N, int nsm)
+{
+    const long long need = logpwr_scratch_floats(nframes, N, nsm);
+    if (need > LOGPWR_STATIC_SCRATCH_FLOATS)
+        return fail(GRB200_ERANGE,
+                    "logpwrfft (static scratch): %lld frames of %d bins need %lld bytes of scratch, the static array holds %lld "
+                    "(at most %lld frames per call at this fft_size)",
+                    nframes, N, need * 4, LOGPWR_STATIC_SCRATCH_FLOATS * 4, 8 * (LOGPWR_STATIC_SCRATCH_FLOATS / N));
+    return 0;
+}
+
+// logpwr_iir_log_launch over the static array.  `device` must be current.
+int logpwr_iir_log_launch_static(float* p, long long nframes, int N, double alpha, float* ystate, float log_mul,
+                                 float log_scale, int nsm, int device, cudaStream_t st)
+{
+    if (nframes <= 0)
+        return 0;
+    int rc = logpwr_static_check(nframes, N, nsm);
+    if (rc)
+        return rc;
+    float* scratch = nullptr;
+    if (logpwr_scratch_floats(nframes, N, nsm) > 0 && (rc = logpwr_static_scratch_ptr(device, &scratch)))
+        return rc;
+    return logpwr_iir_log_launch(p, nframes, N, alpha, ystate, scratch, log_mul, log_scale, nsm, st);
+}
+
 } // namespace grb

@@ -236,6 +236,14 @@ class _logpwrfft_base:
                                                        int(max_out), C.byref(used), C.byref(made), C.c_void_p(stream)))
         return used.value, made.value
 
+    def work_dev_static(self, in_dev, nitems, out_dev, max_out, stream=0):
+        """work_dev over the library's static device scratch: allocates nothing (grb200.h: grb200_logpwrfft_work_dev_static;
+        at most 8 * (2^18 // fft_size) kept frames per averaging call, calls that overlap on the GPU race)."""
+        used, made = C.c_longlong(0), C.c_longlong(0)
+        _lib.check(_lib.lib().grb200_logpwrfft_work_dev_static(self._h, C.c_void_p(in_dev), int(nitems), C.c_void_p(out_dev),
+                                                              int(max_out), C.byref(used), C.byref(made), C.c_void_p(stream)))
+        return used.value, made.value
+
     def process(self, x):
         """All whole vectors of x through one general_work(): returns frames [nframes, fft_size]."""
         x = np.ascontiguousarray(x, self._item).reshape(-1)

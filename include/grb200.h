@@ -384,6 +384,23 @@ int grb200_logpwrfft_work(grb200_logpwr* h, const void* in_host, long long nitem
 int grb200_logpwrfft_work_dev(grb200_logpwr* h, const void* in_dev, long long nitems, float* out_dev, long long max_out,
                               long long* consumed, long long* produced, void* stream);
 void grb200_logpwrfft_destroy(grb200_logpwr* h);
+/* grb200_logpwrfft_work_dev that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  grb200_logpwrfft_work_dev grows a per-handle scratch buffer (the averaging filter's run carries) with
+ * cudaMalloc on demand; this variant keeps that scratch in a file-scope `static __device__` array of
+ * GRB200_LOGPWR_STATIC_SCRATCH_BYTES inside the library image -- every GPU that loads the library holds it until the process
+ * exits -- and calls no cudaMalloc / cudaFree / allocating routine.  Arguments, results, handle state (decimator counter,
+ * filter memory) and output bits are those of grb200_logpwrfft_work_dev; the two may be mixed on one handle.
+ * Limit: with averaging on, a call may keep at most 8 * (GRB200_LOGPWR_STATIC_SCRATCH_BYTES / 4 / fft_size) frames (2048
+ * frames of 1024 bins; 128 of 16384); beyond that the call returns GRB200_ERANGE before anything is launched and the handle is
+ * unchanged -- split the call.  Calls of <= 16 kept frames and handles without averaging use no scratch at all.
+ * The array is ONE per GPU, shared by every handle and every call: calls that overlap on the GPU (different streams) race
+ * on it -- serialise them.  It keeps the last call's contents and needs no clearing (every word is written before it is
+ * read).  Its device address is resolved (cudaGetSymbolAddress, once per device) by the first averaging call on that
+ * device: make one such call before starting a graph capture. */
+#define GRB200_LOGPWR_STATIC_SCRATCH_BYTES (1 << 20)
+int grb200_logpwrfft_work_dev_static(grb200_logpwr* h, const void* in_dev, long long nitems, float* out_dev,
+                                     long long max_out, long long* consumed, long long* produced, void* stream);
 
 /* ---- stream_to_vector / vector_to_stream / vector_to_streams --------
  * stream_to_vector_impl::work (gr-blocks/lib/stream_to_vector_impl.cc:46-58) is memcpy(out, in, noutput*block_size): a stream
