@@ -285,10 +285,10 @@ class FftFilter(Workload):
     block = "fft_filter_ccc"
     # two tap partitions on the 4096-point kernel: (2 x 5 N log2 N + 16 N) / (N/2) flops per output sample, N = 4096
     alg_bytes, flops, log2n, seed = 16.0, 272.0, 28, 2
-    kernel = "fftfilt_upols_kernel"
-    bound = "fp32"  # ncu: DRAM 18 % busy, FMA pipe and issue slots ~50 % -- the butterflies bound it, not HBM
-    ncu_dram_bytes_per_sample = (2.158e9 + 2.104e9) / (1 << 28)
-    ncu_source = "profiles/r1_fftfilt_upols_ncu.txt"
+    kernel = "fftfilt_upols2_kernel"
+    bound = "fp32"  # ncu: DRAM 23 % busy, FMA pipe 65 %, shared-memory pipe 64 % -- the butterflies bound it, not HBM
+    ncu_dram_bytes_per_sample = (2.164e9 + 2.105e9) / (1 << 28)
+    ncu_source = "profiles/r2_fftfilt_upols2_ncu.txt"
     ntaps = 4096
 
     def setup(self):
