@@ -529,7 +529,7 @@ class Filterbank(Workload):
     name = "filterbank_vcvcf 64 filters x 16 taps, 2^%d samples per GPU (section 8(f) row)"
     block = "filterbank_vcvcf"
     alg_bytes, flops, log2n, seed = 16.0, 64.0, 28, 10
-    kernel = "filterbank_kernel"
+    kernel = "filterbank_stream_kernel"
     M, T = 64, 16
 
     def setup(self):

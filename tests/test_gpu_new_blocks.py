@@ -368,7 +368,11 @@ def test_filterbank_fixtures_and_qa(grb):
 
 
 @pytest.mark.parametrize("nf,nt,n", [(64, 16, 30000), (10, 5, 1000), (1, 1, 77), (3, 8, 5000), (100, 17, 3000), (64, 32, 2000),
-                                     (7, 33, 900), (256, 4, 4001)])
+                                     (7, 33, 900), (256, 4, 4001),
+                                     # the TMA-staged streaming kernel (nf in 16/64/256, <= 32 taps, >= 4096 vectors): all three
+                                     # ring depths, one tap, ragged last block, a partial last CTA
+                                     (16, 8, 10001), (64, 32, 9000), (256, 4, 5000), (64, 1, 4096), (16, 17, 33333),
+                                     (256, 32, 6000), (64, 9, 4097), (256, 16, 20011)])
 def test_filterbank_sweep(grb, orc, nf, nt, n):
     rng = np.random.default_rng(nf * 100 + nt)
     taps = rng.uniform(-1, 1, (nf, nt)).astype(np.float32)
