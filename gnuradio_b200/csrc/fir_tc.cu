@@ -151,7 +151,7 @@ template <int MODE, bool TRACE>
 __global__ void __launch_bounds__(tc::NTHREADS, 1)
     fir_tc_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int ntaps,
                   const void* __restrict__ rev_, long long ntiles, long long* __restrict__ trace,
-                  const float2* __restrict__ halo)
+                  const float2* __restrict__ halo, int dbg_)
 {
     using namespace tc;
     using C = Cfg<MODE>;
@@ -177,7 +177,10 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
     unsigned long long* a_ready = d_empty + DSTAGES;
     unsigned long long* t_full = a_ready + 1;          // M_DEC8
     unsigned long long* t_empty = t_full + C::TSTAGES; // M_DEC8
-    const bool have_tail = MODE == M_DEC8 && ntaps > 968;
+    // trace build only (GRB200_FIR_TC_DBG; timing experiments, wrong output): 1 = converters skip their operand stores,
+    // 2 = skip the 17th-block sums, 4 = skip the raw-tile reads
+    const int dbg = TRACE ? dbg_ : 0;
+    const bool have_tail = MODE == M_DEC8 && ntaps > 968 && !(dbg & 2);
     unsigned* tmem_ptr = (unsigned*)(bars + C::NBARS);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const long long G = gridDim.x;
@@ -259,7 +262,11 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
             // a tile that reaches into the history halo of a time-sharded segment takes the plain-load path below and reads
             // those ntaps-1 items where they are: the left neighbour's memory (halo), over NVLink
             const bool in_halo = halo != nullptr && e0 < (long long)(ntaps - 1);
-            if (e0 + ROWS * 64 <= nin && !in_halo) {
+            if (TRACE && (dbg & 4)) {
+#pragma unroll
+                for (int i = 0; i < C::CHUNKS; ++i)
+                    v[i][0] = v[i][1] = make_float4(1.f, 2.f, 3.f, 4.f);
+            } else if (e0 + ROWS * 64 <= nin && !in_halo) {
                 const unsigned rb = sR_u32 + rs * RAW_BYTES + 32 * p;
 #pragma unroll
                 for (int i = 0; i < C::CHUNKS; ++i) {
@@ -293,10 +300,15 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                     const float4 a = v[i][0], b = v[i][1];
                     float2 val[8];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        val[j].x = fmaf(ct[j][3], b.z, fmaf(ct[j][2], b.x, fmaf(ct[j][1], a.z, ct[j][0] * a.x)));
-                        val[j].y = fmaf(ct[j][3], b.w, fmaf(ct[j][2], b.y, fmaf(ct[j][1], a.w, ct[j][0] * a.y)));
-                    }
+                    const float2 x0 = make_float2(a.x, a.y), x1 = make_float2(a.z, a.w), x2 = make_float2(b.x, b.y),
+                                 x3 = make_float2(b.z, b.w);
+                    val[0] = make_float2(0.f, 0.f); // phase 0 never reaches the 17th block (k < 8 j is empty)
+#pragma unroll
+                    for (int j = 1; j < 8; ++j) // (re, im) together: one packed FMA per tap
+                        val[j] = __ffma2_rn(make_float2(ct[j][3], ct[j][3]), x3,
+                                            __ffma2_rn(make_float2(ct[j][2], ct[j][2]), x2,
+                                                       __ffma2_rn(make_float2(ct[j][1], ct[j][1]), x1,
+                                                                  __fmul2_rn(make_float2(ct[j][0], ct[j][0]), x0))));
                     float2 k4[4], k2[2], k1;
                     const bool b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
 #pragma unroll
@@ -348,6 +360,8 @@ __global__ void __launch_bounds__(tc::NTHREADS, 1)
                                               re.w - trunc_tf32(re.w));
                 const float4 il = make_float4(im.x - trunc_tf32(im.x), im.y - trunc_tf32(im.y), im.z - trunc_tf32(im.z),
                                               im.w - trunc_tf32(im.w));
+                if (TRACE && (dbg & 1) && rl.x != 12345.f)
+                    continue;
                 sts128(bh + off_re, re); // the tensor core ignores the low 13 bits: raw value = hi part
                 sts128(bh + off_im, im);
                 sts128(bh + OPER_BYTES + off_re, rl);
@@ -615,7 +629,8 @@ static int fir_tc_launch_t(int ntaps, const void* rev, const void* in, void* out
         GRB_CUDA(cudaMalloc(&dtrace, 64 * 16 * sizeof(long long)));
         GRB_CUDA(cudaMemsetAsync(dtrace, 0, 64 * 16 * sizeof(long long), st));
         fir_tc_kernel<MODE, true><<<grid, tc::NTHREADS, C::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps,
-                                                                            rev, ntiles, dtrace, (const float2*)halo);
+                                                                            rev, ntiles, dtrace, (const float2*)halo,
+                                                                            getenv("GRB200_FIR_TC_DBG") ? atoi(getenv("GRB200_FIR_TC_DBG")) : 0);
         GRB_LAUNCH_CHECK();
         std::vector<long long> h(64 * 16);
         GRB_CUDA(cudaMemcpyAsync(h.data(), dtrace, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
@@ -631,7 +646,7 @@ static int fir_tc_launch_t(int ntaps, const void* rev, const void* in, void* out
         return 0;
     }
     fir_tc_kernel<MODE, false><<<grid, tc::NTHREADS, C::SMEM_BYTES, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps,
-                                                                         rev, ntiles, nullptr, (const float2*)halo);
+                                                                         rev, ntiles, nullptr, (const float2*)halo, 0);
     GRB_LAUNCH_CHECK();
     return 0;
 }
