@@ -7,6 +7,7 @@
 // are contiguous in the output.  8 + 8L algorithmic bytes per input item: the block is bound by its own output stream.
 #include <cstdint>
 #include "capi_common.cuh"
+#include "tma.cuh"
 
 using namespace grb;
 
@@ -156,6 +157,159 @@ __global__ void __launch_bounds__(256) interp_fir_tile_kernel(const float2* __re
     }
 }
 
+// ---- streaming form (round 2, third attempt; interpolation <= 32, <= 32 taps per phase): a register ring per (phase, run) --
+// What bounds the kernels above is the load/store unit: every multiply-add pair drags a shared-memory tap load along and the
+// window comes through L1 item by item.  Here nothing but the stream itself moves: thread (phase l, run g) keeps the taps of
+// its phase AND the last TP input items of its run in registers and walks down the run -- per output one 8-byte shared load
+// (the new item, broadcast to the L lanes of the run), TP packed FMAs and one store; the L lanes of a run store L consecutive
+// outputs (a whole 32-byte sector at L = 4).  A producer warp streams the runs' new items: per iteration and run ONE bulk
+// copy of KT + 2 items (the copy starts on an even item: 16-byte rule) into a ring of NS stages, rows KT + 2 items apart (which
+// also keeps the 32 / L runs of a warp in different banks).
+namespace istream {
+constexpr int KT = 32, ROW = KT + 2, NCW = 8, MAXNS = 4; // items per run and iteration, row stride, consumer warps, stages <=
+}
+
+template <int TP, bool CT>
+__global__ void __launch_bounds__(288)
+interp_stream_kernel(const float2* __restrict__ in /* 16-byte aligned; the stream starts at in[gs] */, float2* __restrict__ out,
+                     long long nin_pos, int L, int T, const float* __restrict__ rev, int iters, int gs, int NS)
+{
+    using namespace istream;
+    constexpr int ES = CT ? 2 : 1;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int RW = 32 / L, NG = NCW * RW; // runs per warp, per CTA
+    float2* xs = reinterpret_cast<float2*>(smem_raw); // [NS][NG][ROW]
+    unsigned long long* full = reinterpret_cast<unsigned long long*>(smem_raw + (size_t)NS * NG * ROW * 8);
+    unsigned long long* empty = full + MAXNS;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long region = (long long)iters * KT; // input positions per run
+    const long long cta0 = (long long)blockIdx.x * NG * region;
+    const long long nitems = nin_pos + T - 1 + gs; // items of `in` that may be read (counted from the aligned base)
+    const long long nitems_even = nitems & ~1LL;
+    if (tid == 0)
+        for (int s = 0; s < NS; s++) {
+            mbar_init(&full[s], 32);
+            mbar_init(&empty[s], NCW);
+        }
+    __syncthreads();
+    // position n reads items n + gs .. n + gs + T - 1; the newest one of a run's iteration `it`, step k, is item
+    // b + it KT + k with b = n0 + gs + T - 1; copies start at the even item at or below it
+    if (warp == NCW) {
+        // ---------------- producer warp: lane j streams runs j, j + 32, ... ----------------
+        for (int it = 0; it < iters; it++) {
+            const int s = it % NS, use = it / NS;
+            if (use > 0)
+                mbar_wait(&empty[s], (unsigned)((use - 1) & 1));
+            unsigned bytes = 0;
+            for (int g = lane; g < NG; g += 32) {
+                const long long b = cta0 + (long long)g * region + gs + T - 1 + (long long)it * KT;
+                const long long a0 = b & ~1LL;
+                long long n = nitems_even - a0;
+                n = n < 0 ? 0 : (n > ROW ? ROW : n);
+                bytes += (unsigned)(n * 8);
+            }
+            mbar_expect_tx(&full[s], bytes); // (arrives: 32 arrivals complete the phase once the bytes are in)
+            for (int g = lane; g < NG; g += 32) {
+                const long long b = cta0 + (long long)g * region + gs + T - 1 + (long long)it * KT;
+                const long long a0 = b & ~1LL;
+                long long n = nitems_even - a0;
+                n = n < 0 ? 0 : (n > ROW ? ROW : n);
+                if (n)
+                    bulk_g2s(xs + ((size_t)s * NG + g) * ROW, in + a0, (unsigned)(n * 8), &full[s]);
+            }
+        }
+        return;
+    }
+    // ---------------- consumers ----------------
+    const int l = lane % L, gw = lane / L;
+    const bool idle = gw >= RW; // lanes beyond the last whole run of the warp (L does not divide 32)
+    const int g = warp * RW + (idle ? 0 : gw);
+    const long long n0 = cta0 + (long long)g * region; // first input position of this run
+    const long long b0 = n0 + gs + T - 1;
+    const int off = (int)(b0 & 1); // region is even: the same for every iteration
+    // taps of phase l; tap u multiplies the item u behind the newest one of a window (rev index T - 1 - u)
+    float hr[TP], hi[CT ? TP : 1];
+#pragma unroll
+    for (int u = 0; u < TP; u++) {
+        const bool ok = u < T && !idle;
+        hr[u] = ok ? __ldg(rev + ((size_t)l * T + (T - 1 - u)) * ES) : 0.f;
+        if (CT)
+            hi[u] = ok ? __ldg(rev + ((size_t)l * T + (T - 1 - u)) * ES + 1) : 0.f;
+    }
+    float2 ring[TP]; // once the newest item of position n = n0 + m is in, ring[(m - u) mod TP] = item b0 + m - u
+#pragma unroll
+    for (int u = 1; u < TP; u++) {
+        const long long r = b0 - u;
+        ring[(TP - u) % TP] = (u < T && r >= gs && r < nitems) ? in[r] : make_float2(0.f, 0.f);
+    }
+    ring[0] = make_float2(0.f, 0.f);
+    const long long last_odd = (nitems & 1) ? nitems - 1 : -1; // the one item the 16-byte copies cannot bring
+    for (int it = 0; it < iters; it++) {
+        const int s = it % NS;
+        mbar_wait(&full[s], (unsigned)((it / NS) & 1));
+        const float2* src = xs + ((size_t)s * NG + g) * ROW + off;
+        const long long nb = n0 + (long long)it * KT; // first position of this block
+        float2* o = out + nb * L + l;
+        const long long left = nin_pos - nb;
+        static_assert(KT % TP == 0, "the ring position returns to 0 every iteration");
+#pragma unroll
+        for (int k = 0; k < KT; k++) {
+            float2 x = src[k];
+            if (b0 + (long long)it * KT + k == last_odd)
+                x = in[last_odd];
+            ring[k % TP] = x;
+            float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int u = 0; u < TP; u++) {
+                const float2 w = ring[(k - u + 2 * TP) % TP];
+                if (CT) { // a += w * (hr + j hi)
+                    a0 = __ffma2_rn(make_float2(hr[u], hr[u]), w, a0);
+                    a1 = __ffma2_rn(make_float2(-hi[u], hi[u]), make_float2(w.y, w.x), a1);
+                } else if (u & 1) {
+                    a1 = __ffma2_rn(make_float2(hr[u], hr[u]), w, a1);
+                } else {
+                    a0 = __ffma2_rn(make_float2(hr[u], hr[u]), w, a0);
+                }
+            }
+            if (k < left && !idle)
+                o[(long long)k * L] = __fadd2_rn(a0, a1);
+        }
+        __syncwarp();
+        if (lane == 0)
+            mbar_arrive_one(&empty[s]);
+    }
+}
+
+template <int TP, bool CT>
+static int interp_stream_launch(const void* in, void* out, long long nin_pos, int L, int T, const float* rev, int nsm,
+                                cudaStream_t st)
+{
+    using namespace istream;
+    const int NG = NCW * (32 / L);
+    const size_t stage = (size_t)NG * ROW * 8;
+    const int NS = 3 * stage <= 72 * 1024 ? 3 : 2;
+    const size_t smem = (size_t)NS * stage + 2 * MAXNS * 8 + 16;
+    auto kern = interp_stream_kernel<TP, CT>;
+    GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 288, smem));
+    if (occ < 1)
+        occ = 1;
+    const long long per_iter = (long long)NG * KT; // positions per CTA and iteration
+    long long grid = (long long)nsm * occ;
+    const long long need = (nin_pos + per_iter - 1) / per_iter;
+    if (grid > need)
+        grid = need;
+    long long iters = (nin_pos + grid * per_iter - 1) / (grid * per_iter);
+    grid = (nin_pos + iters * per_iter - 1) / (iters * per_iter);
+    if (iters > 0x7fffffffLL / KT)
+        return fail(GRB200_ERANGE, "interp_fir_filter: work() call too long for one launch");
+    const int gs = (int)((((uintptr_t)in) >> 3) & 1); // 8-byte aligned only: the stream starts one item into an aligned one
+    kern<<<(unsigned)grid, 288, smem, st>>>((const float2*)in - gs, (float2*)out, nin_pos, L, T, rev, (int)iters, gs, NS);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
 template <bool CT>
 static int interp_launch_t(const void* in, void* out, long long nin_pos, int L, int T, const float* rev, int nsm,
                            cudaStream_t st)
@@ -170,6 +324,19 @@ static int interp_launch_t(const void* in, void* out, long long nin_pos, int L, 
         const char* e = getenv("GRB200_INTERP_TILE");
         return e && e[0] == '1';
     }();
+    static const bool use_stream = [] {
+        const char* e = GRB_GETENV_ONCE("GRB200_INTERP_STREAM"); // 0 = the one-position-per-thread kernel only
+        return !(e && e[0] == '0');
+    }();
+    if (use_stream && L >= 2 && L <= 32 && T <= 32 && nin_pos >= 8192 && !(CT && T > 16) &&
+        (size_t)2 * istream::NCW * (32 / L) * istream::ROW * 8 <= 100 * 1024) {
+        if (T <= 8)
+            return interp_stream_launch<8, CT>(in, out, nin_pos, L, T, rev, nsm, st);
+        if (T <= 16)
+            return interp_stream_launch<16, CT>(in, out, nin_pos, L, T, rev, nsm, st);
+        if constexpr (!CT)
+            return interp_stream_launch<32, CT>(in, out, nin_pos, L, T, rev, nsm, st);
+    }
     if (use_tile && L <= 16 && (T == 4 || T == 8 || T == 16 || T == 32) && nin_pos >= 1024) {
         const size_t tsm = (((size_t)L * T * (CT ? 2 : 1) + 3) & ~(size_t)3) * 4 + (size_t)((256 + T + 1) & ~1) * 8 +
                            (size_t)256 * L * 8;

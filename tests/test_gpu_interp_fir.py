@@ -56,6 +56,32 @@ def test_interp_fir_sweep(grb, orc, L, ntaps, cplx):
     assert_parity(got, po.f64_interp_fir(L, taps, x), "f64 %d/%d" % (L, ntaps), 2e-6, 2e-5)
 
 
+@pytest.mark.parametrize("L,ntaps,cplx,shift", [(2, 64, False, 0), (3, 33, True, 1), (4, 64, False, 1), (4, 31, False, 0),
+                                                (8, 64, True, 0), (5, 55, False, 1), (16, 400, False, 0), (7, 100, True, 0),
+                                                (32, 64, False, 1), (4, 61, False, 0), (6, 96, True, 1)])
+def test_interp_fir_streaming_kernel(grb, orc, L, ntaps, cplx, shift):
+    """One device-resident call long enough for interp_stream_kernel (>= 8192 input positions): every ring depth, phase counts
+    that do not divide the warp, complex taps, an input pointer that is only 8-byte aligned, ragged last blocks and runs."""
+    import torch
+
+    rng = np.random.default_rng(L * 977 + ntaps)
+    ni = 30011 + 2 * L
+    T = -(-ntaps // L)
+    x = crand(rng, ni)
+    taps = crand(rng, ntaps) if cplx else rng.uniform(-1, 1, ntaps).astype(np.float32)
+    xin = np.concatenate([np.zeros(shift + T - 1, np.complex64), x])
+    xd = torch.from_numpy(xin.view(np.float32).copy()).cuda()
+    yd = torch.full((2 * ni * L + 2,), float("nan"), dtype=torch.float32, device="cuda")
+    blk = _cls(grb, taps)(L, taps)
+    blk.work_dev(xd.data_ptr() + 8 * shift, yd.data_ptr(), ni * L, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    y = yd.cpu().numpy()
+    assert np.isnan(y[-2:]).all()  # nothing written past the end
+    got = y[:-2].view(np.complex64)
+    assert_parity(got, orc.interp_fir(L, taps, x), "oracle %d/%d" % (L, ntaps), 2e-6, 2e-5)
+    assert_parity(got, po.f64_interp_fir(L, taps, x), "f64 %d/%d" % (L, ntaps), 2e-6, 2e-5)
+
+
 def test_interp_fir_set_taps_midstream_and_errors(grb, orc):
     rng = np.random.default_rng(6)
     x = crand(rng, 4000)
