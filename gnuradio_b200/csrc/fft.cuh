@@ -127,7 +127,9 @@ __device__ __forceinline__ void dft16(float2* v)
 template <int R, bool FWD>
 __device__ __forceinline__ void dft_r(float2* v)
 {
-    if constexpr (R == 2)
+    if constexpr (R == 1)
+        return;
+    else if constexpr (R == 2)
         dft2<FWD>(v[0], v[1]);
     else if constexpr (R == 4)
         dft4<FWD>(v[0], v[1], v[2], v[3]);

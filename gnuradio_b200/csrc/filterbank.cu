@@ -122,7 +122,7 @@ static int launch_fb(const void* x, void* out, long long nout, int nf, int T, co
     return 0;
 }
 
-// ---- streaming form (nf in {16, 64, 256}, <= 32 taps, 16-byte aligned input): pfb_stream_kernel without its DFT --------
+// ---- streaming form (nf a power of two 8 .. 256, <= 32 taps, 16-byte aligned input): pfb_stream_kernel without its DFT --------
 // The register-ring kernel above is capped by its own occupancy (164 registers with the block-ahead loads: 0.66 of HBM).  Here
 // the loads are not the threads' business at all: a persistent CTA owns NG contiguous runs of output rows; per iteration and
 // run the KT new rows are ONE contiguous block of the input -- one TMA bulk copy into a ring of NS shared-memory stages, issued
@@ -172,21 +172,22 @@ filterbank_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out,
     auto issue = [&](int it) { // iteration it's NG blocks of KT new rows into stage it mod NS
         unsigned long long* b = &bar[it % NS];
         float2* dst = xs + (size_t)(it % NS) * (NG * KT * M);
-        unsigned total = 0, bytes[NG];
-#pragma unroll
-        for (int g = 0; g < NG; g++) {
-            const long long r0 = cta0 + (long long)g * region + (long long)it * KT + T - 1;
-            long long nv = nrows - r0;
-            nv = nv < 0 ? 0 : (nv > KT ? KT : nv);
-            bytes[g] = (unsigned)(nv * M * 8);
-            total += bytes[g];
-        }
+        auto rows_of = [&](int g, long long& r0) {
+            r0 = cta0 + (long long)g * region + (long long)it * KT + T - 1;
+            const long long nv = nrows - r0;
+            return (unsigned)((nv < 0 ? 0 : (nv > KT ? KT : nv)) * M * 8);
+        };
+        unsigned total = 0;
+        long long r0;
+#pragma unroll 1
+        for (int g = 0; g < NG; g++)
+            total += rows_of(g, r0);
         mbar_expect_tx(b, total);
-#pragma unroll
+#pragma unroll 1
         for (int g = 0; g < NG; g++) {
-            const long long r0 = cta0 + (long long)g * region + (long long)it * KT + T - 1;
-            if (bytes[g])
-                bulk_g2s(dst + g * KT * M, x + r0 * M, bytes[g], b);
+            const unsigned bytes = rows_of(g, r0);
+            if (bytes)
+                bulk_g2s(dst + g * KT * M, x + r0 * M, bytes, b);
         }
     };
     if (tid == 0)
@@ -280,8 +281,14 @@ int filterbank_launch(const void* x, void* out, long long nout, int nf, int T, c
         return !(e && e[0] == '0');
     }();
     if (use_stream && T <= 32 && nout >= 4096 && (((uintptr_t)x) & 15) == 0) { // (TMA bulk copies: 16-byte aligned rows)
+        if (nf == 8)
+            return launch_fb_stream_tp<8>(x, out, nout, T, hrev, active, nsm, st);
         if (nf == 16)
             return launch_fb_stream_tp<16>(x, out, nout, T, hrev, active, nsm, st);
+        if (nf == 32)
+            return launch_fb_stream_tp<32>(x, out, nout, T, hrev, active, nsm, st);
+        if (nf == 128)
+            return launch_fb_stream_tp<128>(x, out, nout, T, hrev, active, nsm, st);
         if (nf == 64)
             return launch_fb_stream_tp<64>(x, out, nout, T, hrev, active, nsm, st);
         if (nf == 256)

@@ -24,16 +24,18 @@ namespace grb {
 
 template <int M, int NT>
 struct PfbStreamGeom {
-    static constexpr int RDX = M == 16 ? 4 : (M == 64 ? 8 : 16); // sqrt(M)
+    // M = R1 * R2: pass 1 runs radix-R1 transforms over the branches j + R2 q, pass 2 radix-R2 ones over j (R2 = 1: none)
+    static constexpr int R1 = M >= 128 ? 16 : (M >= 32 ? 8 : (M == 16 ? 4 : M));
+    static constexpr int R2 = M / R1;
     static constexpr int NG = NT / M;                            // group runs per CTA
     static constexpr int KT = 16;                                // output times per group per iteration
     static constexpr int OT = NG * KT;                           // output times per CTA per iteration
     static constexpr int LD = M + 1;                             // padded row of the [time][branch] buffer
-    static constexpr int NI = OT * RDX / NT;                     // DFT items per thread and pass
+    static constexpr int NI1 = OT * R2 / NT, NI2 = OT * R1 / NT; // DFT items per thread in pass 1 / pass 2
     static constexpr int XS_BYTES = NG * KT * M * 8;
     static constexpr int VB_BYTES = OT * LD * 8;
     static constexpr int SMEM = XS_BYTES + VB_BYTES + M * 8 + 16;
-    static_assert(NT % M == 0 && (OT * RDX) % NT == 0, "geometry");
+    static_assert(NT % M == 0 && (OT * R2) % NT == 0 && (OT * R1) % NT == 0 && R1 * R2 == M && R2 <= 16, "geometry");
 };
 
 template <int M, int TP, int NT>
@@ -43,7 +45,7 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
                   const float2* __restrict__ wM, int iters, const float2* __restrict__ halo)
 {
     using Geo = PfbStreamGeom<M, NT>;
-    constexpr int NG = Geo::NG, KT = Geo::KT, OT = Geo::OT, LD = Geo::LD, RDX = Geo::RDX, NI = Geo::NI;
+    constexpr int NG = Geo::NG, KT = Geo::KT, OT = Geo::OT, LD = Geo::LD, R1 = Geo::R1, R2 = Geo::R2;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float2* xs = reinterpret_cast<float2*>(smem_raw);                     // [NG][KT][M]
     float2* vbuf = reinterpret_cast<float2*>(smem_raw + Geo::XS_BYTES);   // [OT][LD]
@@ -82,22 +84,22 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
 
     // one elected thread streams the input: NG contiguous blocks of KT rows per iteration
     auto issue = [&](int it) {
+        auto rows_of = [&](int g, long long& r0) {
+            r0 = cta0 + (long long)g * region + (long long)it * KT + T;
+            const long long nv = nrows - r0;
+            return (unsigned)((nv < 0 ? 0 : (nv > KT ? KT : nv)) * M * 8);
+        };
         unsigned total = 0;
-        unsigned bytes[NG];
-#pragma unroll
-        for (int g = 0; g < NG; g++) {
-            const long long r0 = cta0 + (long long)g * region + (long long)it * KT + T;
-            long long nv = nrows - r0;
-            nv = nv < 0 ? 0 : (nv > KT ? KT : nv);
-            bytes[g] = (unsigned)(nv * M * 8);
-            total += bytes[g];
-        }
+        long long r0;
+#pragma unroll 1
+        for (int g = 0; g < NG; g++)
+            total += rows_of(g, r0);
         mbar_expect_tx(bar, total);
-#pragma unroll
+#pragma unroll 1
         for (int g = 0; g < NG; g++) {
-            const long long r0 = cta0 + (long long)g * region + (long long)it * KT + T;
-            if (bytes[g])
-                bulk_g2s(xs + g * KT * M, x + r0 * M, bytes[g], bar);
+            const unsigned bytes = rows_of(g, r0);
+            if (bytes)
+                bulk_g2s(xs + g * KT * M, x + r0 * M, bytes, bar);
         }
     };
     if (tid == 0)
@@ -121,40 +123,40 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
         __syncthreads(); // vbuf complete; xs drained
         if (tid == 0 && it + 1 < iters)
             issue(it + 1);
-        // ---------------- inverse DFT pass 1 (in place): y[j][k1] -> slot j + RDX*k1 ----------------
+        // ---------------- inverse DFT pass 1 (in place): y[j][k1] -> slot j + R2*k1 ----------------
 #pragma unroll
-        for (int n = 0; n < NI; n++) {
+        for (int n = 0; n < Geo::NI1; n++) {
             const int idx = tid + n * NT;
             const int o = idx % OT, j = idx / OT;
-            float2 v[RDX];
+            float2 v[R1];
 #pragma unroll
-            for (int q = 0; q < RDX; q++)
-                v[q] = vbuf[o * LD + j + q * RDX];
-            dft_r<RDX, false>(v);
+            for (int q = 0; q < R1; q++)
+                v[q] = vbuf[o * LD + j + q * R2];
+            dft_r<R1, false>(v);
 #pragma unroll
-            for (int q = 0; q < RDX; q++)
-                vbuf[o * LD + j + q * RDX] = v[q];
+            for (int q = 0; q < R1; q++)
+                vbuf[o * LD + j + q * R2] = v[q];
         }
         __syncthreads();
         // ---------------- pass 2: twiddle, DFT over j, channel-major stores ----------------
 #pragma unroll
-        for (int n = 0; n < NI; n++) {
+        for (int n = 0; n < Geo::NI2; n++) {
             const int idx = tid + n * NT;
             const int o = idx % OT, k1 = idx / OT;
-            float2 a[RDX];
+            float2 a[R2];
 #pragma unroll
-            for (int j = 0; j < RDX; j++) {
-                a[j] = vbuf[o * LD + k1 * RDX + j];
+            for (int j = 0; j < R2; j++) {
+                a[j] = vbuf[o * LD + k1 * R2 + j];
                 if (j > 0)
                     a[j] = cmul(a[j], wtab[j * k1]);
             }
-            dft_r<RDX, false>(a);
+            dft_r<R2, false>(a);
             const int g = o / KT, k = o % KT;
             const long long t = cta0 + (long long)g * region + (long long)it * KT + k;
             if (t < noutput) {
 #pragma unroll
-                for (int k2 = 0; k2 < RDX; k2++) {
-                    const int c = k1 + RDX * k2;
+                for (int k2 = 0; k2 < R2; k2++) {
+                    const int c = k1 + R1 * k2;
                     if (c < nouts)
                         out[(long long)c * out_stride + t] = a[k2];
                 }
@@ -222,7 +224,7 @@ static int launch_stream_tp(int T, const void* x, void* out, long long out_strid
 
 bool pfb_stream_supported(int M, int T, int R, const void* x)
 {
-    return R == M && T >= 1 && T <= 32 && (M == 16 || M == 64 || M == 256) && ((uintptr_t)x & 15) == 0;
+    return R == M && T >= 1 && T <= 32 && M >= 8 && M <= 256 && (M & (M - 1)) == 0 && ((uintptr_t)x & 15) == 0;
 }
 
 // x: interleaved input with T*M history items in front (16-byte aligned); identity channel map.
@@ -242,6 +244,14 @@ int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stri
     if (M == 64)
         return nt_small == 128 ? launch_stream_tp<64, 128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo)
                                : launch_stream_tp<64, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+    switch (M) {
+    case 8:
+        return launch_stream_tp<8, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+    case 32:
+        return launch_stream_tp<32, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+    case 128:
+        return launch_stream_tp<128, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+    }
     return launch_stream_tp<256, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
 }
 

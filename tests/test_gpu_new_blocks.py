@@ -372,7 +372,7 @@ def test_filterbank_fixtures_and_qa(grb):
                                      # the TMA-staged streaming kernel (nf in 16/64/256, <= 32 taps, >= 4096 vectors): all three
                                      # ring depths, one tap, ragged last block, a partial last CTA
                                      (16, 8, 10001), (64, 32, 9000), (256, 4, 5000), (64, 1, 4096), (16, 17, 33333),
-                                     (256, 32, 6000), (64, 9, 4097), (256, 16, 20011)])
+                                     (256, 32, 6000), (64, 9, 4097), (256, 16, 20011), (8, 16, 9000), (32, 11, 7001), (128, 20, 5003)])
 def test_filterbank_sweep(grb, orc, nf, nt, n):
     rng = np.random.default_rng(nf * 100 + nt)
     taps = rng.uniform(-1, 1, (nf, nt)).astype(np.float32)

@@ -54,7 +54,10 @@ def test_pfb_ctor_contract_and_errors(grb):
 
 
 @pytest.mark.parametrize("M,ntaps,osr", [(64, 1024, 1.0), (16, 200, 1.0), (256, 2048, 1.0), (64, 1024, 2.0),
-                                          (5, 43, 1.0), (6, 31, 1.5), (64, 130, 1.0), (64, 2048, 1.0), (3, 2, 3.0)])
+                                          (5, 43, 1.0), (6, 31, 1.5), (64, 130, 1.0), (64, 2048, 1.0), (3, 2, 3.0),
+                                          # the streaming kernel's other channel counts (M = R1 x R2 with R1 != R2, and M = 8)
+                                          (8, 100, 1.0), (32, 500, 1.0), (128, 2048, 1.0), (32, 1024, 1.0), (128, 700, 1.0),
+                                          (8, 256, 1.0)])
 def test_pfb_against_oracle(grb, orc, M, ntaps, osr):
     rng = np.random.default_rng(M * 1000 + ntaps)
     taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
