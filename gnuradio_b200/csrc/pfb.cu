@@ -12,7 +12,7 @@
 //     fin[q] = v_i  with  q = (i - (oo+2)*R) mod M            (the idxlut rotation; identity when R == M)
 //     out_n[oo] = sum_q fin[q] * e^{+j 2 pi q c / M},  c = channel_map[n]
 //
-// Fast path (M in {16, 64, 256}, oversample_rate 1, T <= 32): persistent CTAs of 256 threads; a tile is
+// First-generation fast path (M in {16, 64, 256}, oversample_rate 1, T <= 32; pfb_stream.cu now takes every power of two 8..256): persistent CTAs of 256 threads; a tile is
 // OT = 256*G/M output times.  Phase 1: thread (branch i, group g) slides a register window down its
 // branch's time axis -- G outputs from G+TP-1 coalesced 8-byte loads (lanes run over i, i.e. over
 // consecutive interleaved samples) with its TP taps held in registers -- and drops v into shared memory

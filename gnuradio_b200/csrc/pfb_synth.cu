@@ -7,7 +7,7 @@
 //                     i, the one with the even taps reads the half of the IFFT that alternates with n)
 // (checked against the reference's own classes in tests/test_oracle.py).
 //
-// pfb_synth_kernel (1x, M in {16, 64, 256}, up to 32 taps per branch, any channel map, any number of connected inputs):
+// pfb_synth_kernel (1x, M a power of two 8..256, up to 32 taps per branch, any channel map, any number of connected inputs):
 // pfb_stream_kernel read right to left.  A persistent CTA owns NG contiguous runs of input times; per iteration ONE 2-D TMA
 // tensor copy per run (cp.async.bulk.tensor: box = KT times x M streams out of the stream-major input, rows beyond the
 // connected inputs and items beyond the end arrive as zeros) lands the next KT columns; the M-point backward DFT runs over
@@ -56,16 +56,18 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
 
 template <int M, int NT>
 struct SynthGeom {
-    static constexpr int RDX = M == 16 ? 4 : (M == 64 ? 8 : 16);
+    // M = R1 * R2: pass 1 runs radix-R1 transforms over the bins j + R2 q, pass 2 radix-R2 ones over j (R2 = 1: none)
+    static constexpr int R1 = M >= 128 ? 16 : (M >= 32 ? 8 : (M == 16 ? 4 : M));
+    static constexpr int R2 = M / R1;
     static constexpr int NG = NT / M;     // runs per CTA
     static constexpr int KT = 16;         // input times per run per iteration
     static constexpr int OT = NG * KT;    // times per CTA per iteration
     static constexpr int LD = M + 1;      // padded row of the [time][branch] buffer
-    static constexpr int NI = OT * RDX / NT;
+    static constexpr int NI1 = OT * R2 / NT, NI2 = OT * R1 / NT;
     static constexpr int XS_BYTES = OT * M * 8;
     static constexpr int VB_BYTES = OT * LD * 8;
     static constexpr int SMEM = XS_BYTES + VB_BYTES + M * 8 + M * 4 + 16;
-    static_assert(NT % M == 0 && (OT * RDX) % NT == 0, "geometry");
+    static_assert(NT % M == 0 && (OT * R2) % NT == 0 && (OT * R1) % NT == 0 && R1 * R2 == M && R2 <= 16, "geometry");
 };
 
 // x is described by `tmap`: [nin streams][items] floats (2 per item), T-1 history items in front of every stream.
@@ -77,7 +79,7 @@ pfb_synth_kernel(const __grid_constant__ CUtensorMap tmap, float2* __restrict__ 
                  const int* __restrict__ inv /* [M]: stream feeding FFT bin c, or -1 */, long long region, int iters)
 {
     using Geo = SynthGeom<M, NT>;
-    constexpr int NG = Geo::NG, KT = Geo::KT, OT = Geo::OT, LD = Geo::LD, RDX = Geo::RDX, NI = Geo::NI;
+    constexpr int NG = Geo::NG, KT = Geo::KT, OT = Geo::OT, LD = Geo::LD, R1 = Geo::R1, R2 = Geo::R2, NI1 = Geo::NI1, NI2 = Geo::NI2;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float2* xs = reinterpret_cast<float2*>(smem_raw);                    // [NG][M][KT]
     float2* vbuf = reinterpret_cast<float2*>(smem_raw + Geo::XS_BYTES);  // [OT][LD]
@@ -122,48 +124,48 @@ pfb_synth_kernel(const __grid_constant__ CUtensorMap tmap, float2* __restrict__ 
     auto iteration = [&](int it, auto phc) {
         constexpr int PH = decltype(phc)::value;
         mbar_wait(bar, it & 1);
-        // ---------------- backward DFT over the channels, pass 1: gather through the map, y[j][k1] -> slot j + RDX*k1 ---
+        // ---------------- backward DFT over the channels, pass 1: gather through the map, y[j][k1] -> slot j + R2*k1 ---
 #pragma unroll
-        for (int n = 0; n < NI; n++) {
+        for (int n = 0; n < NI1; n++) {
             const int idx = tid + n * NT;
             const int o = idx % OT, j = idx / OT;
             const int g = o / KT, k = o % KT;
-            float2 v[RDX];
+            float2 v[R1];
 #pragma unroll
-            for (int q = 0; q < RDX; q++) {
-                const int s = sinv[j + q * RDX];
+            for (int q = 0; q < R1; q++) {
+                const int s = sinv[j + q * R2];
                 v[q] = s >= 0 ? xs[(g * M + s) * KT + k] : make_float2(0.f, 0.f);
             }
-            dft_r<RDX, false>(v);
+            dft_r<R1, false>(v);
 #pragma unroll
-            for (int q = 0; q < RDX; q++)
-                vbuf[o * LD + j + q * RDX] = v[q];
+            for (int q = 0; q < R1; q++)
+                vbuf[o * LD + j + q * R2] = v[q];
         }
         __syncthreads(); // xs drained, pass-1 results visible
         if (tid == 0 && it + 1 < iters)
             issue(it + 1);
         // ---------------- pass 2: twiddle, DFT over j; results back in natural branch order ----------------
-        float2 a[NI][RDX];
+        float2 a[NI2][R2];
 #pragma unroll
-        for (int n = 0; n < NI; n++) {
+        for (int n = 0; n < NI2; n++) {
             const int idx = tid + n * NT;
             const int o = idx % OT, k1 = idx / OT;
 #pragma unroll
-            for (int j = 0; j < RDX; j++) {
-                a[n][j] = vbuf[o * LD + k1 * RDX + j];
+            for (int j = 0; j < R2; j++) {
+                a[n][j] = vbuf[o * LD + k1 * R2 + j];
                 if (j > 0)
                     a[n][j] = cmul(a[n][j], wtab[j * k1]);
             }
-            dft_r<RDX, false>(a[n]);
+            dft_r<R2, false>(a[n]);
         }
         __syncthreads(); // every slot has been read before any is overwritten
 #pragma unroll
-        for (int n = 0; n < NI; n++) {
+        for (int n = 0; n < NI2; n++) {
             const int idx = tid + n * NT;
             const int o = idx % OT, k1 = idx / OT;
 #pragma unroll
-            for (int k2 = 0; k2 < RDX; k2++)
-                vbuf[o * LD + k1 + RDX * k2] = a[n][k2];
+            for (int k2 = 0; k2 < R2; k2++)
+                vbuf[o * LD + k1 + R1 * k2] = a[n][k2];
         }
         __syncthreads();
         // ---------------- branch FIRs along time: one new transform output per step, TP packed FMAs ----------------
@@ -239,7 +241,7 @@ static int launch_synth_tp(int T, const CUtensorMap& tmap, void* out, long long 
 
 bool pfb_synth_fast_supported(int M, int T, int twox, const void* x, long long stride, int nin)
 {
-    return twox == 1 && T >= 1 && T <= 32 && (M == 16 || M == 64 || M == 256) && nin >= 1 && nin <= M &&
+    return twox == 1 && T >= 1 && T <= 32 && M >= 8 && M <= 256 && (M & (M - 1)) == 0 && nin >= 1 && nin <= M &&
            ((uintptr_t)x & 15) == 0 && (stride & 1) == 0 && tmap_encoder() != nullptr;
 }
 
@@ -261,8 +263,14 @@ int pfb_synth_fast_launch(int M, int T, const void* x, long long stride, int nin
                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
         return fail(GRB200_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    if (M == 8)
+        return launch_synth_tp<8, 256>(T, tmap, out, ntimes, h, wM, inv, nsm, st);
     if (M == 16)
         return launch_synth_tp<16, 256>(T, tmap, out, ntimes, h, wM, inv, nsm, st);
+    if (M == 32)
+        return launch_synth_tp<32, 256>(T, tmap, out, ntimes, h, wM, inv, nsm, st);
+    if (M == 128)
+        return launch_synth_tp<128, 256>(T, tmap, out, ntimes, h, wM, inv, nsm, st);
     if (M == 64)
         return launch_synth_tp<64, 256>(T, tmap, out, ntimes, h, wM, inv, nsm, st);
     return launch_synth_tp<256, 256>(T, tmap, out, ntimes, h, wM, inv, nsm, st);

@@ -238,7 +238,10 @@ def test_pfb_synthesizer_fixtures_and_qa(grb):
                                             (256, 16, False, 256, 700), (64, 32, False, 64, 1000), (64, 5, False, 64, 1000),
                                             (64, 1, False, 64, 300), (64, 16, True, 64, 2001), (64, 16, True, 128, 500),
                                             (5, 9, False, 5, 1000), (6, 4, True, 9, 999), (100, 3, False, 7, 200),
-                                            (64, 40, False, 64, 400)])
+                                            (64, 40, False, 64, 400),
+                                            # channel counts M = R1 x R2 with R1 != R2, and M = 8, on the fast path
+                                            (8, 12, False, 8, 9000), (32, 16, False, 32, 4001), (128, 10, False, 128, 1500),
+                                            (32, 7, False, 20, 3000), (128, 32, False, 77, 900)])
 def test_pfb_synthesizer_sweep(grb, orc, M, T, twox, nin, n):
     """tensor-map TMA fast path (1x; M = 16 / 64 / 256; up to 32 taps per branch; fewer inputs than channels; random channel
     map) and the general path (2x, other channel counts, more than 32 taps per branch)."""
