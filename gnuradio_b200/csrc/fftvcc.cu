@@ -109,7 +109,7 @@ fft_vcc_kernel(const VccArgs a)
     }
 }
 
-// ---- streaming variant (1024 <= N <= 8192) ----------------------------------------------------------
+// ---- streaming variant (32 <= N <= 8192; below 1024 several vectors per CTA share one bulk copy) ----------------------------------------------------------
 // ncu on the kernel above (profiles/r1_fftvcc_ncu.txt): 2 CTAs/SM at 127 registers, long-scoreboard stalls
 // 2.9 per issue -- every vector's loads are exposed, and window + twiddle lookups add 2.7x the input's L1
 // sectors.  Here a persistent CTA keeps ONE TMA bulk copy (its next VPC vectors, contiguous in the stream)
@@ -365,7 +365,7 @@ static int launch_vcc_stream(const VccArgs& a, int nsm, cudaStream_t st)
 template <int N, bool REAL>
 static int launch_vcc_dir(bool fwd, const VccArgs& a, int nsm, cudaStream_t st)
 {
-    if constexpr (N >= 1024 && N <= 8192) {
+    if constexpr (N >= 32 && N <= 8192) { // (two passes at least: the prefetch is issued after the first exchange)
         static const bool use_stream = [] {
             const char* e = getenv("GRB200_FFT_STREAM");
             return !(e && e[0] == '0');

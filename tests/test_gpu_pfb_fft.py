@@ -168,12 +168,12 @@ def test_fft_vcc_sizes(grb, orc, N):
             assert_parity(got, po.f64_fft_vcc(N, fwd, w, sh, x), "f64 N=%d f%d s%d" % (N, fwd, sh))
 
 
-@pytest.mark.parametrize("N", [1024, 2048, 4096, 8192])
+@pytest.mark.parametrize("N", [32, 64, 128, 256, 512, 1024, 2048, 4096, 8192])
 def test_fft_vcc_streaming_kernel(grb, orc, N):
     """>= 64 vectors per work() call take the persistent TMA-prefetch kernel (fft_vcc_stream_kernel);
     odd vector counts exercise the clipped last bulk copy."""
     rng = np.random.default_rng(1000 + N)
-    nvec = 701 if N <= 2048 else 333
+    nvec = 701 if N <= 2048 else 333  # (odd: below 1024 several vectors share a bulk copy, the last one is clipped)
     x = crand(rng, N * nvec)
     w = rng.uniform(0.1, 1, N).astype(np.float32)
     for fwd in (True, False):
