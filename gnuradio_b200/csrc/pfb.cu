@@ -89,6 +89,154 @@ pfb_generic_kernel(const float2* __restrict__ x, float2* __restrict__ out, long 
     }
 }
 
+// ---- any rate ratio, any channel map, any tap count -- power-of-two channel counts 8 .. 256 --------------------------
+// The generic kernel above evaluates the DFT directly, M multiply-adds per output: 11 - 17 Gsps where the streaming kernel
+// does 300+ (an oversampled channelizer, more than 32 taps per branch).  Same tile structure, but the branches go through
+// the two in-place passes of pfb_stream.cu (M = R1 x R2, lanes over time) and the channel map is a gather at the end:
+//   FIR   thread (time ol, branch i): T loads through L1 (lanes over i: consecutive interleaved samples), taps of its branch in
+//         registers (its branch never changes: 256 % M == 0); the idxlut rotation q = (i - (oo+2) R) mod M is the scatter
+//   DFT   pass 1 radix R1 over q = j + R2 q', pass 2 twiddle + radix R2 over j, results back in natural order
+//   out   out_n[oo] = X[channel_map[n]], lanes over time (128-byte runs per channel)
+template <int M, int TP>
+__global__ void __launch_bounds__(256)
+pfb_fftgen_kernel(const float2* __restrict__ x, float2* __restrict__ out, long long out_stride, int nouts,
+                  const int* __restrict__ cmap, long long noutput, int T, int R, const float* __restrict__ h,
+                  const float2* __restrict__ wtab_g)
+{
+    constexpr int NT = 256, OT = 32, LD = M + 1;
+    constexpr int R1 = M >= 128 ? 16 : (M >= 32 ? 8 : (M == 16 ? 4 : M)), R2 = M / R1;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float2* vbuf = reinterpret_cast<float2*>(smem_raw); // [OT][LD]
+    float2* wtab = vbuf + OT * LD;                      // [M]
+    int* smap = reinterpret_cast<int*>(wtab + M);       // [nouts]
+    const int tid = threadIdx.x;
+    for (int k = tid; k < M; k += NT)
+        wtab[k] = wtab_g[k];
+    for (int k = tid; k < nouts; k += NT)
+        smap[k] = cmap[k];
+    const int i = tid % M; // this thread's branch in every FIR item it owns
+    float taps[TP > 0 ? TP : 1];
+    if (TP > 0) {
+#pragma unroll
+        for (int u = 0; u < TP; u++)
+            taps[u] = u < T ? __ldg(h + u * M + i) : 0.f;
+    }
+    const long long ntiles = (noutput + OT - 1) / OT;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long o0 = tile * OT;
+        __syncthreads(); // the previous tile's gather is done (and the tables are written)
+        // ---------------- branch FIRs ----------------
+        for (int ol = tid / M; ol < OT; ol += NT / M) {
+            const long long oo = o0 + ol;
+            if (oo < noutput) {
+                const long long P = (oo + 1) * R - 1;
+                const float2* xp = x + (P - i + (long long)T * M);
+                float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+                if (TP > 0) {
+#pragma unroll
+                    for (int u = 0; u < TP; u += 2) {
+                        if (u < T)
+                            a0 = __ffma2_rn(make_float2(taps[u], taps[u]), __ldg(xp - (long long)u * M), a0);
+                        if (u + 1 < T)
+                            a1 = __ffma2_rn(make_float2(taps[u + 1], taps[u + 1]), __ldg(xp - (long long)(u + 1) * M), a1);
+                    }
+                } else {
+                    for (int u = 0; u < T; u++) {
+                        const float hh = __ldg(h + u * M + i);
+                        a0 = __ffma2_rn(make_float2(hh, hh), __ldg(xp - (long long)u * M), a0);
+                    }
+                }
+                int q = (int)((i - (oo + 2) * R) % M);
+                if (q < 0)
+                    q += M;
+                vbuf[ol * LD + q] = __fadd2_rn(a0, a1);
+            }
+        }
+        __syncthreads();
+        // ---------------- inverse DFT pass 1 (in place): y[j][k1] -> slot j + R2*k1 ----------------
+        for (int idx = tid; idx < OT * R2; idx += NT) {
+            const int o = idx % OT, j = idx / OT;
+            float2 v[R1];
+#pragma unroll
+            for (int q = 0; q < R1; q++)
+                v[q] = vbuf[o * LD + j + q * R2];
+            dft_r<R1, false>(v);
+#pragma unroll
+            for (int q = 0; q < R1; q++)
+                vbuf[o * LD + j + q * R2] = v[q];
+        }
+        __syncthreads();
+        // ---------------- pass 2: twiddle, DFT over j; natural order back into the buffer ----------------
+        constexpr int NI2 = (OT * R1 + NT - 1) / NT;
+        float2 a[NI2][R2];
+#pragma unroll
+        for (int n = 0; n < NI2; n++) {
+            const int idx = tid + n * NT;
+            if (idx < OT * R1) {
+                const int o = idx % OT, k1 = idx / OT;
+#pragma unroll
+                for (int j = 0; j < R2; j++) {
+                    a[n][j] = vbuf[o * LD + k1 * R2 + j];
+                    if (j > 0)
+                        a[n][j] = cmul(a[n][j], wtab[j * k1]);
+                }
+                dft_r<R2, false>(a[n]);
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int n = 0; n < NI2; n++) {
+            const int idx = tid + n * NT;
+            if (idx < OT * R1) {
+                const int o = idx % OT, k1 = idx / OT;
+#pragma unroll
+                for (int k2 = 0; k2 < R2; k2++)
+                    vbuf[o * LD + k1 + R1 * k2] = a[n][k2];
+            }
+        }
+        __syncthreads();
+        // ---------------- channel map gather, lanes over time ----------------
+        for (int idx = tid; idx < OT * nouts; idx += NT) {
+            const int ol = idx % OT, n = idx / OT;
+            const long long oo = o0 + ol;
+            if (oo < noutput)
+                out[(long long)n * out_stride + oo] = vbuf[ol * LD + smap[n]];
+        }
+    }
+}
+
+template <int M, int TP>
+static int launch_fftgen(const void* x, void* out, long long out_stride, int nouts, const int* cmap, long long noutput,
+                         int T, int R, const float* h, const float2* wM, int nsm, cudaStream_t st)
+{
+    const size_t smem = ((size_t)32 * (M + 1) + M) * 8 + (size_t)nouts * 4;
+    auto kern = pfb_fftgen_kernel<M, TP>;
+    if (smem > 48 * 1024)
+        GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, smem));
+    if (occ < 1)
+        occ = 1;
+    const long long ntiles = (noutput + 31) / 32;
+    long long grid = (long long)nsm * occ;
+    if (grid > ntiles)
+        grid = ntiles;
+    kern<<<(unsigned)grid, 256, smem, st>>>((const float2*)x, (float2*)out, out_stride, nouts, cmap, noutput, T, R, h, wM);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+template <int M>
+static int launch_fftgen_tp(const void* x, void* out, long long out_stride, int nouts, const int* cmap, long long noutput,
+                            int T, int R, const float* h, const float2* wM, int nsm, cudaStream_t st)
+{
+    if (T <= 16)
+        return launch_fftgen<M, 16>(x, out, out_stride, nouts, cmap, noutput, T, R, h, wM, nsm, st);
+    if (T <= 32)
+        return launch_fftgen<M, 32>(x, out, out_stride, nouts, cmap, noutput, T, R, h, wM, nsm, st);
+    return launch_fftgen<M, 0>(x, out, out_stride, nouts, cmap, noutput, T, R, h, wM, nsm, st);
+}
+
 // ---- fast kernel --------------------------------------------------------------------------------------
 template <int M>
 struct PfbGeom {
@@ -315,6 +463,22 @@ int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stri
         if (M == 64)
             return launch_fast_tp<64>(T, x, out, out_stride, nouts, cmap, identity, noutput, nrows, h, wM, nsm, st);
         return launch_fast_tp<256>(T, x, out, out_stride, nouts, cmap, identity, noutput, nrows, h, wM, nsm, st);
+    }
+    if (allow_fast && M >= 8 && M <= 256 && (M & (M - 1)) == 0 && nouts <= 4096 && !GRB_GETENV_ONCE("GRB200_PFB_GENERIC")) {
+        switch (M) {
+        case 8:
+            return launch_fftgen_tp<8>(x, out, out_stride, nouts, cmap, noutput, T, R, h, wM, nsm, st);
+        case 16:
+            return launch_fftgen_tp<16>(x, out, out_stride, nouts, cmap, noutput, T, R, h, wM, nsm, st);
+        case 32:
+            return launch_fftgen_tp<32>(x, out, out_stride, nouts, cmap, noutput, T, R, h, wM, nsm, st);
+        case 64:
+            return launch_fftgen_tp<64>(x, out, out_stride, nouts, cmap, noutput, T, R, h, wM, nsm, st);
+        case 128:
+            return launch_fftgen_tp<128>(x, out, out_stride, nouts, cmap, noutput, T, R, h, wM, nsm, st);
+        case 256:
+            return launch_fftgen_tp<256>(x, out, out_stride, nouts, cmap, noutput, T, R, h, wM, nsm, st);
+        }
     }
     // generic path
     int OT = 32;

@@ -57,7 +57,10 @@ def test_pfb_ctor_contract_and_errors(grb):
                                           (5, 43, 1.0), (6, 31, 1.5), (64, 130, 1.0), (64, 2048, 1.0), (3, 2, 3.0),
                                           # the streaming kernel's other channel counts (M = R1 x R2 with R1 != R2, and M = 8)
                                           (8, 100, 1.0), (32, 500, 1.0), (128, 2048, 1.0), (32, 1024, 1.0), (128, 700, 1.0),
-                                          (8, 256, 1.0)])
+                                          (8, 256, 1.0),
+                                          # pfb_fftgen_kernel: oversampled, more than 32 taps per branch, R1 != R2
+                                          (64, 64 * 40, 1.0), (32, 512, 2.0), (128, 640, 4.0 / 3.0), (16, 100, 4.0), (8, 64, 8.0),
+                                          (256, 256 * 3, 2.0), (32, 32 * 33, 1.0)])
 def test_pfb_against_oracle(grb, orc, M, ntaps, osr):
     rng = np.random.default_rng(M * 1000 + ntaps)
     taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
@@ -75,6 +78,24 @@ def test_pfb_against_oracle(grb, orc, M, ntaps, osr):
     if M * nout <= 64 * 3000:
         f64 = po.f64_channelizer(M, hp, srcs.T.reshape(-1), nout, osr)
         assert_parity(np.array(outs), f64, "f64")
+
+
+@pytest.mark.parametrize("M,osr", [(32, 1.0), (128, 2.0), (8, 1.0)])
+def test_pfb_channel_map_other_channel_counts(grb, orc, M, osr):
+    """A permuted channel map with fewer outputs than channels on the FFT-based general kernel."""
+    rng = np.random.default_rng(M + 5)
+    ntaps, nout = M * 9 - 3, 1200
+    taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
+    blk = grb.filter.pfb_channelizer_ccf(M, taps, osr)
+    T = blk.taps_per_filter()
+    rows = int(nout / osr) + 2
+    ins = np.concatenate([np.zeros((M, T), np.complex64), crand(rng, M * rows).reshape(M, rows)], axis=1)
+    cmap = rng.permutation(M).astype(np.int32)
+    blk.set_channel_map(cmap)
+    nouts = max(1, M // 3)
+    got = blk.process(ins, nout, nouts)
+    ref, _ = orc.pfb_channelizer(M, taps, osr, ins, nout, channel_map=cmap, nouts=nouts)
+    assert_parity(got, ref, "mapped M=%d osr=%g" % (M, osr))
 
 
 def test_pfb_channel_map_and_fewer_outputs_fast_path(grb, orc):
