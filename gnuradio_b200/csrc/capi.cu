@@ -125,6 +125,12 @@ struct grb200_fir {
     const void* halo_src = nullptr; // left neighbour's newest ntaps-1 items (peer memory), see grb200_fir_set_halo_source
     bool real = false; // fir_filter_fff: float stream, float taps (fir_fff.cu)
     int isz() const { return real ? 4 : 8; }
+    // Long filters run on the overlap-save kernels of fft_filter (fftfilt.cu) -- same linear convolution, ~3e-7 NRMS from the
+    // time-domain sum: past ~72 real (40 complex) taps per decimation step the CUDA-core FIR is FP32-bound below their rate.
+    int fft_pref = -1; // GRB200_FIR_FFT as it stood when the handle was made: 0 never, 1 whenever a plan exists, unset = auto
+    bool fft_route = false;
+    DevBuf fH, ftw;
+    int fL = 0, fK = 1;
     Stager sg;
     std::mutex mu;
 };
@@ -160,7 +166,38 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
     if (rc)
         return rc;
     h->ntaps = ntaps;
+    // route to the overlap-save kernels?  (not where a tensor-core mode applies: <= 64 taps at decimation 1, real taps <= 1024
+    // at decimation 8)
+    h->fft_route = false;
+    const bool tc_case = h->tc_pref != 0 && ((D == 1 && ntaps <= 64) || (!h->ct && D == 8 && ntaps <= 1024));
+    const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && !tc_case && ntaps > (h->ct ? 40 : 72) * (long long)D);
+    if (want && fftfilt_device_plan(ntaps, nullptr) > 0) {
+        std::vector<float> tc((size_t)2 * ntaps, 0.f);
+        for (int t = 0; t < ntaps; t++) {
+            tc[2 * (size_t)t] = taps[(size_t)t * es];
+            if (h->ct)
+                tc[2 * (size_t)t + 1] = taps[(size_t)t * es + 1];
+        }
+        if ((rc = fftfilt_plan_build(tc.data(), ntaps, h->device, h->sg.s_exec, h->fH, h->ftw, &h->fL, &h->fK)))
+            return rc;
+        h->fft_route = true;
+    }
     return 0;
+}
+
+// the FIR of one device-resident call: overlap-save when the handle routes there, else the FIR kernels
+static int fir_run_dev(grb200_fir* h, const void* in_dev, void* out_dev, long long noutput, cudaStream_t st, const void* halo)
+{
+    if (h->fft_route) {
+        if (halo) { // the overlap-save kernels read their history in place: bring the neighbour's items over first
+            int rc = halo_fetch_launch(const_cast<void*>(in_dev), halo, (size_t)(h->ntaps - 1) * 8, st);
+            if (rc)
+                return rc;
+        }
+        return fftfilt_launch(h->fL, h->fK, in_dev, out_dev, noutput, h->ntaps, h->decim, (const float2*)h->fH.p,
+                              (const float2*)h->ftw.p, sm_count(h->device), st);
+    }
+    return fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput, h->tc_pref, st, halo);
 }
 
 static int fir_create(bool ct, int decim, const float* taps, int ntaps, int device, grb200_fir** out, bool real = false)
@@ -177,6 +214,8 @@ static int fir_create(bool ct, int decim, const float* taps, int ntaps, int devi
     h->ct = ct;
     h->decim = decim;
     h->tc_pref = fir_tc_env();
+    if (const char* e = getenv("GRB200_FIR_FFT")) // (per handle, at create: tests flip it between handles)
+        h->fft_pref = atoi(e) ? 1 : 0;
     h->real = real;
     grb::DeviceScope _ds_create(device); // the caller keeps its own current device
     int rc = h->sg.init(device);
@@ -247,7 +286,7 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
             return rc;
     }
     rc = h->real ? fir_fff_launch(h->decim, h->ntaps, (const float*)h->rev.p, in_dev, out_dev, noutput, sm_count(h->device), st)
-                 : fir_launch(h->ct, h->decim, h->ntaps, h->gtaps.p, h->rev.p, in_dev, out_dev, noutput, h->tc_pref, st, halo);
+                 : fir_run_dev(h, in_dev, out_dev, noutput, st, halo);
     if (!rc && h->rot) {
         rc = rotate_launch(out_dev, noutput, h->theta, h->delta, st);
         h->theta = rotate_advance(h->theta, h->delta, noutput);
@@ -318,7 +357,7 @@ static int fir_work_host(grb200_fir* h, const void* in_host, void* out_host, lon
             const long long o0 = c * chunk, n = std::min(chunk, noutput - o0);
             int r2 = h->real ? fir_fff_launch(D, nt, (const float*)h->rev.p, sg.dev[slot][0], sg.dev[slot][1], n,
                                               sm_count(h->device), st)
-                             : fir_launch(h->ct, D, nt, h->gtaps.p, h->rev.p, sg.dev[slot][0], sg.dev[slot][1], n, h->tc_pref, st);
+                             : fir_run_dev(h, sg.dev[slot][0], sg.dev[slot][1], n, st, nullptr);
             if (!r2 && h->rot)
                 r2 = rotate_launch(sg.dev[slot][1], n, rotate_advance(h->theta, h->delta, o0), h->delta, st);
             return r2;
@@ -366,6 +405,8 @@ void grb200_fir_destroy(grb200_fir* h)
     h->sg.destroy();
     h->gtaps.release();
     h->rev.release();
+    h->fH.release();
+    h->ftw.release();
     delete h;
 }
 

@@ -124,6 +124,10 @@ struct DevBuf {
         cap = 0;
     }
 };
+// capi_fftfilt.cu: device plan + filter spectra of the overlap-save kernels for `ntaps` complex taps
+int fftfilt_plan_build(const float* taps_re_im, int ntaps, int device, cudaStream_t st, DevBuf& H, DevBuf& tw, int* L_io,
+                       int* K_out);
+
 
 // forward twiddle table e^{-j 2 pi k / N} (or e^{+...} with sign=+1), evaluated in double
 inline std::vector<float2> make_roots(int N, int sign)

@@ -24,7 +24,12 @@ static int ref_nsamples(int ntaps)
     return fftsize - ntaps + 1;
 }
 
-static int fftfilt_prepare(grb200_fftfilt* h, const float* taps_re_im, int ntaps)
+namespace grb {
+// Device plan + filter spectra for `ntaps` complex taps (also used by the FIR handle when it routes a long filter here):
+// H_p = FFT_L(taps of partition p / L), scale on the host like fft_filter.cc:184-189, transform on the device.
+// *L_io: the length `tw` currently holds roots for (0 = none); updated.  Returns GRB200_ERANGE when no plan exists.
+int fftfilt_plan_build(const float* taps_re_im, int ntaps, int device, cudaStream_t st, DevBuf& H, DevBuf& tw, int* L_io,
+                       int* K_out)
 {
     int K = 1;
     const int L = fftfilt_device_plan(ntaps, &K);
@@ -32,13 +37,13 @@ static int fftfilt_prepare(grb200_fftfilt* h, const float* taps_re_im, int ntaps
         return fail(GRB200_ERANGE, "fft_filter_ccc: %d taps exceed the single-CTA transform (max %d)", ntaps,
                     16384 * 3 / 4 + 1);
     int rc;
-    if (L != h->L) {
+    if (L != *L_io) {
         std::vector<float2> roots = make_roots(L, -1);
-        if ((rc = h->tw.upload(roots.data(), roots.size() * sizeof(float2))))
+        if ((rc = tw.upload(roots.data(), roots.size() * sizeof(float2))))
             return rc;
+        *L_io = L;
     }
-    // H_p = FFT_L(taps of partition p / L): scale on the host like fft_filter.cc:184-189, transform on the device.
-    // One partition holds all taps; two hold taps [0, L/2) and [L/2, ntaps).
+    // One partition holds all taps; K hold taps [p L/2, (p+1) L/2).
     const int P = K == 1 ? ntaps : L / 2;
     std::vector<float2> padded((size_t)L * K, make_float2(0.f, 0.f));
     const float scale = 1.0f / (float)L;
@@ -47,21 +52,30 @@ static int fftfilt_prepare(grb200_fftfilt* h, const float* taps_re_im, int ntaps
     DevBuf tmp;
     if ((rc = tmp.upload(padded.data(), padded.size() * sizeof(float2))))
         return rc;
-    if ((rc = h->H.upload(padded.data(), padded.size() * sizeof(float2)))) { // sized; overwritten below
+    if ((rc = H.upload(padded.data(), padded.size() * sizeof(float2)))) { // sized; overwritten below
         tmp.release();
         return rc;
     }
-    rc = fft_vcc_launch(L, true, tmp.p, h->H.p, K, nullptr, 0, 0, (const float2*)h->tw.p, sm_count(h->device),
-                        h->sg.s_exec);
+    rc = fft_vcc_launch(L, true, tmp.p, H.p, K, nullptr, 0, 0, (const float2*)tw.p, sm_count(device), st);
     if (!rc) {
-        cudaError_t e = cudaStreamSynchronize(h->sg.s_exec);
+        cudaError_t e = cudaStreamSynchronize(st);
         if (e != cudaSuccess)
             rc = fail(GRB200_ECUDA, "fft_filter_ccc::set_taps: %s", cudaGetErrorString(e));
     }
     tmp.release();
     if (rc)
         return rc;
-    h->L = L;
+    *K_out = K;
+    return 0;
+}
+} // namespace grb
+
+static int fftfilt_prepare(grb200_fftfilt* h, const float* taps_re_im, int ntaps)
+{
+    int K = 1;
+    int rc = fftfilt_plan_build(taps_re_im, ntaps, h->device, h->sg.s_exec, h->H, h->tw, &h->L, &K);
+    if (rc)
+        return rc;
     h->parts = K;
     h->ntaps = ntaps;
     h->nsamples = ref_nsamples(ntaps);

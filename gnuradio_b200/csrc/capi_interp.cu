@@ -34,21 +34,25 @@ __global__ void __launch_bounds__(256) interp_fir_kernel(const float2* __restric
 #pragma unroll
             for (int t = 0; t < TT; t++)
                 w[t] = __ldg(x + t);
+            // (summation order = interp_stream_kernel's: taps from the newest item backwards, even and odd ones in separate
+            // accumulators -- a stream cut into calls of any length gives the same bits whichever kernel a call takes)
             auto phase = [&](int p) {
                 const float* h = sh + (size_t)p * TT * ES;
-                float2 a = make_float2(0.f, 0.f);
+                float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
 #pragma unroll
-                for (int t = 0; t < TT; t++) {
+                for (int u = 0; u < TT; u++) {
+                    const int t = TT - 1 - u;
                     if (CT) {
                         const float hr = h[2 * t], hi = h[2 * t + 1];
-                        a.x = fmaf(w[t].x, hr, fmaf(-w[t].y, hi, a.x));
-                        a.y = fmaf(w[t].x, hi, fmaf(w[t].y, hr, a.y));
+                        a0 = __ffma2_rn(make_float2(hr, hr), w[t], a0);
+                        a1 = __ffma2_rn(make_float2(-hi, hi), make_float2(w[t].y, w[t].x), a1);
+                    } else if (u & 1) {
+                        a1 = __ffma2_rn(make_float2(h[t], h[t]), w[t], a1);
                     } else {
-                        a.x = fmaf(w[t].x, h[t], a.x);
-                        a.y = fmaf(w[t].y, h[t], a.y);
+                        a0 = __ffma2_rn(make_float2(h[t], h[t]), w[t], a0);
                     }
                 }
-                return a;
+                return __fadd2_rn(a0, a1);
             };
             if ((L & 1) == 0 && pair_ok) { // two phases per 16-byte store: item i*L + p is even
                 for (int p = 0; p < L; p += 2) {
@@ -62,19 +66,21 @@ __global__ void __launch_bounds__(256) interp_fir_kernel(const float2* __restric
         } else {
             for (int p = 0; p < L; p++) {
                 const float* h = sh + (size_t)p * T * ES;
-                float2 a = make_float2(0.f, 0.f);
-                for (int t = 0; t < T; t++) {
+                float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+                for (int u = 0; u < T; u++) {
+                    const int t = T - 1 - u;
                     const float2 v = __ldg(x + t);
                     if (CT) {
                         const float hr = h[2 * t], hi = h[2 * t + 1];
-                        a.x = fmaf(v.x, hr, fmaf(-v.y, hi, a.x));
-                        a.y = fmaf(v.x, hi, fmaf(v.y, hr, a.y));
+                        a0 = __ffma2_rn(make_float2(hr, hr), v, a0);
+                        a1 = __ffma2_rn(make_float2(-hi, hi), make_float2(v.y, v.x), a1);
+                    } else if (u & 1) {
+                        a1 = __ffma2_rn(make_float2(h[t], h[t]), v, a1);
                     } else {
-                        a.x = fmaf(v.x, h[t], a.x);
-                        a.y = fmaf(v.y, h[t], a.y);
+                        a0 = __ffma2_rn(make_float2(h[t], h[t]), v, a0);
                     }
                 }
-                y[p] = a;
+                y[p] = __fadd2_rn(a0, a1);
             }
         }
     }

@@ -18,6 +18,16 @@
 
 namespace grb {
 
+// Decimation on store: output n = nb + e is kept when D divides it.  The 64-bit division is done once per block (nb = qb D +
+// rb); an element costs a 32-bit one.
+__device__ __forceinline__ void store_decimated(float2* __restrict__ out, long long qb, unsigned rb, unsigned D, unsigned e,
+                                                float2 v)
+{
+    const unsigned s = rb + e, q = s / D;
+    if (s == q * D)
+        out[qb + q] = v;
+}
+
 template <int L>
 __global__ void __launch_bounds__(L / 16)
 fftfilt_ols_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin,
@@ -54,21 +64,28 @@ fftfilt_ols_kernel(const float2* __restrict__ in, float2* __restrict__ out, long
             }
         __syncthreads(); // forward transform's last gather is done before the inverse reuses S
         cta_fft<L, false, true>(v, S, t, tw);
+        if (D == 1) {
 #pragma unroll
-        for (int b = 0; b < E / RL; b++)
+            for (int b = 0; b < E / RL; b++)
 #pragma unroll
-            for (int q = 0; q < RL; q++) {
-                const int m = (t + b * TPV) + q * (L / RL);
-                if (m >= ntaps - 1) {
+                for (int q = 0; q < RL; q++) {
+                    const int m = (t + b * TPV) + q * (L / RL);
                     const long long n = base + m - (ntaps - 1);
-                    if (n < ny) {
-                        if (D == 1)
-                            out[n] = v[b * RL + q];
-                        else if (n % D == 0)
-                            out[n / D] = v[b * RL + q];
-                    }
+                    if (m >= ntaps - 1 && n < ny)
+                        out[n] = v[b * RL + q];
                 }
-            }
+        } else {
+            const long long dec_q = base / D;
+            const unsigned dec_r = (unsigned)(base - dec_q * D);
+#pragma unroll
+            for (int b = 0; b < E / RL; b++)
+#pragma unroll
+                for (int q = 0; q < RL; q++) {
+                    const int m = (t + b * TPV) + q * (L / RL);
+                    if (m >= ntaps - 1 && base + m - (ntaps - 1) < ny)
+                        store_decimated(out, dec_q, dec_r, (unsigned)D, (unsigned)(m - (ntaps - 1)), v[b * RL + q]);
+                }
+        }
         __syncthreads();
     }
 }
@@ -189,21 +206,28 @@ fftfilt_ols_stream_kernel(const float2* __restrict__ in, float2* __restrict__ ou
             }
         __syncthreads(); // forward transform's last gather is done before the inverse reuses S
         cta_fft_tws<L, false, true>(v, S, t, TWR, tw, []() {});
+        if (D == 1) {
 #pragma unroll
-        for (int b = 0; b < E / RL; b++)
+            for (int b = 0; b < E / RL; b++)
 #pragma unroll
-            for (int q = 0; q < RL; q++) {
-                const int m = (t + b * TPV) + q * (L / RL);
-                if (m >= ntaps - 1) {
+                for (int q = 0; q < RL; q++) {
+                    const int m = (t + b * TPV) + q * (L / RL);
                     const long long n = base + m - (ntaps - 1);
-                    if (n < ny) {
-                        if (D == 1)
-                            out[n] = v[b * RL + q];
-                        else if (n % D == 0)
-                            out[n / D] = v[b * RL + q];
-                    }
+                    if (m >= ntaps - 1 && n < ny)
+                        out[n] = v[b * RL + q];
                 }
-            }
+        } else {
+            const long long dec_q = base / D;
+            const unsigned dec_r = (unsigned)(base - dec_q * D);
+#pragma unroll
+            for (int b = 0; b < E / RL; b++)
+#pragma unroll
+                for (int q = 0; q < RL; q++) {
+                    const int m = (t + b * TPV) + q * (L / RL);
+                    if (m >= ntaps - 1 && base + m - (ntaps - 1) < ny)
+                        store_decimated(out, dec_q, dec_r, (unsigned)D, (unsigned)(m - (ntaps - 1)), v[b * RL + q]);
+                }
+        }
         __syncthreads();
     }
 }
@@ -514,21 +538,28 @@ fftfilt_upols_kernel(const float2* __restrict__ in, float2* __restrict__ out, lo
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             __syncthreads(); // forward transform's last gather is done before the inverse reuses S
             cta_fft_tws<L, false, true>(v, S, t, TWR, tw, []() {});
+            if (D == 1) {
 #pragma unroll
-            for (int b = 0; b < E / RL; b++)
+                for (int b = 0; b < E / RL; b++)
 #pragma unroll
-                for (int q = 0; q < RL; q++) {
-                    const int m = (t + b * TPV) + q * (L / RL);
-                    if (m >= V) {
+                    for (int q = 0; q < RL; q++) {
+                        const int m = (t + b * TPV) + q * (L / RL);
                         const long long n = blk * V + (m - V);
-                        if (n < ny) {
-                            if (D == 1)
-                                out[n] = v[b * RL + q];
-                            else if (n % D == 0)
-                                out[n / D] = v[b * RL + q];
-                        }
+                        if (m >= V && n < ny)
+                            out[n] = v[b * RL + q];
                     }
-                }
+            } else {
+                const long long dec_q = (blk * V) / D;
+                const unsigned dec_r = (unsigned)(blk * V - dec_q * D);
+#pragma unroll
+                for (int b = 0; b < E / RL; b++)
+#pragma unroll
+                    for (int q = 0; q < RL; q++) {
+                        const int m = (t + b * TPV) + q * (L / RL);
+                        if (m >= V && blk * V + (m - V) < ny)
+                            store_decimated(out, dec_q, dec_r, (unsigned)D, (unsigned)(m - V), v[b * RL + q]);
+                    }
+            }
             __syncthreads();
         }
     }
@@ -856,14 +887,16 @@ fftfilt_upols2_kernel(const float2* __restrict__ in, float2* __restrict__ out, l
                     o[256 * (q - 8)] = v[q];
             } else {
                 const long long n0 = (b0 + i) * V + t;
+                const long long dec_q = D == 1 ? 0 : ((b0 + i) * V) / D;
+                const unsigned dec_r = D == 1 ? 0u : (unsigned)((b0 + i) * V - dec_q * D);
 #pragma unroll
                 for (int q = 8; q < 16; q++) {
                     const long long n = n0 + 256 * (q - 8);
                     if (n < ny) {
                         if (D == 1)
                             out[n] = v[q];
-                        else if (n % D == 0)
-                            out[n / D] = v[q];
+                        else
+                            store_decimated(out, dec_q, dec_r, (unsigned)D, (unsigned)(t + 256 * (q - 8)), v[q]);
                     }
                 }
             }
@@ -911,8 +944,8 @@ int fftfilt_device_plan(int ntaps, int* parts)
     // 2050..10240 taps: K = ceil(ntaps / 2048) partitions on the 4096-point kernel (K-1 <= 4 parked spectra fit in the
     // 512 TMEM columns of an SM at two CTAs) beat the 16384-point transform; below 2050 plain overlap-save is faster.
     const int kneed = (ntaps + 2047) / 2048;
-    if (upols != 0 && L == 16384 && kneed <= 5) {
-        L = 4096;
+    if (upols != 0 && (L == 16384 || ntaps >= 1400) && kneed <= 5) { // (measured: plain overlap-save 129 Gsps at 1400 taps and
+        L = 4096;                                                      // falling, the two-partition kernel 129 at any count)
         K = kneed < 2 ? 2 : kneed;
     } else if (upols == 1 && ntaps > 1025 && kneed <= 5) {
         L = 4096;

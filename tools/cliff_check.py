@@ -8,7 +8,8 @@ import gnuradio_b200 as g
 
 rng = np.random.default_rng(0)
 ts = torch.cuda.Stream()
-what = sys.argv[1:] or ["fir", "fft", "pfb", "fftfilt"]
+what = [a for a in sys.argv[1:] if "=" not in a] or ["fir", "fft", "pfb", "fftfilt"]
+opts = dict(a.split("=") for a in sys.argv[1:] if "=" in a)
 
 
 def timed(fn, reps=5):
@@ -52,7 +53,7 @@ if "pfb" in what:
         nin = nout / osr * M
         print("pfb M=%3d T=%2d osr=%.2f map=%d  %.3f ms  %6.1f Gsps (input)" % (M, T, osr, remap, ms, nin / ms / 1e6), flush=True)
 if "fftfilt" in what:
-    for ntaps in (16, 64, 256, 1024, 2049, 4096, 6000, 12000):
+    for ntaps in [int(v) for v in opts.get("taps", "16,64,256,1024,2049,4096,6000,12000").split(",")]:
         taps = (rng.uniform(-1, 1, ntaps) + 1j * rng.uniform(-1, 1, ntaps)).astype(np.complex64)
         blk = g.filter.fft_filter_ccc(1, taps)
         ns = blk.nsamples()
