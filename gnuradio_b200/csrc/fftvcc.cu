@@ -9,7 +9,11 @@
 // so a vector crosses HBM exactly once in each direction: 16 B per complex sample (12 B with the fused
 // magnitude-squared), the figure the HBM roofline is taken against.  Persistent CTAs loop over vectors.
 #include <cstdint>
+#include <cmath>
 #include <cstdlib>
+#include <mutex>
+#include <utility>
+#include <vector>
 #include "fft.cuh"
 #include "tma.cuh"
 #include "capi_common.cuh"
@@ -309,6 +313,189 @@ magsq_kernel(const float2* __restrict__ in, float* __restrict__ out, long long n
 }
 
 // ---- host dispatch --------------------------------------------------------------------------------
+// ---- sizes that are not a power of two (128 <= N <= 8192): Bluestein over the power-of-two transform ---------------------
+// FFTW takes any size at N log N; the direct kernel above is O(N^2) (1.2 Gsps at N = 1000).  With c[n] = e^{-j pi n^2 / N}:
+//     X[k] = c[k] * sum_n (x[n] c[n]) * conj(c)[k - n]           (n k = (n^2 + k^2 - (k - n)^2) / 2)
+// -- a convolution, done circularly at a power of two L >= 2N - 1 exactly like fftfilt.cu's overlap-save block: load
+// (+ window, + swap) * chirp, zero padded to L -> cta_fft -> * B (the transformed chirp, 1/L folded in) in registers -> inverse
+// with the reversed radix schedule -> * chirp -> the first N values (+ rotate, + |.|^2 / log).  One vector per CTA; the
+// backward transform conjugates both tables (the chirp is even in n).  Tables per (device, N) are built at the first launch.
+template <int L, bool REAL>
+__global__ void __launch_bounds__(L / 16, L <= 8192 ? 8192 / L : 1) // 128 registers: 512 resident threads per SM
+fft_bluestein_kernel(const VccArgs a, int N, int forward, const float2* __restrict__ chirp, const float2* __restrict__ Bhat,
+                     const float2* __restrict__ twL)
+{
+    constexpr int E = 16, TPV = L / 16;
+    constexpr int R0 = fft_first_radix(L, false), RM = fft_last_radix(L, false), RL = fft_last_radix(L, true);
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float2* S = reinterpret_cast<float2*>(smem_raw);
+    const int t = threadIdx.x;
+    const float* __restrict__ window = a.window;
+    const bool in_swap = (!forward) && a.shift, out_rot = forward && a.shift;
+    const int len_in = N / 2, len_out = (N + 1) / 2; // fft_vcc_fftw.cc:79,93,107
+    for (long long vec = blockIdx.x; vec < a.nvec; vec += gridDim.x) {
+        const long long sv = (vec * a.vstride + a.voff) * N;
+        float2 v[E];
+#pragma unroll
+        for (int b = 0; b < E / R0; b++)
+#pragma unroll
+            for (int q = 0; q < R0; q++) {
+                const int m = (t + b * TPV) + q * (L / R0);
+                float2 x = make_float2(0.f, 0.f);
+                if (m < N) {
+                    int s = m;
+                    if (in_swap) {
+                        s += len_in;
+                        s -= s >= N ? N : 0;
+                    }
+                    x = REAL ? make_float2(reinterpret_cast<const float*>(a.in)[sv + s], 0.f)
+                             : reinterpret_cast<const float2*>(a.in)[sv + s];
+                    if (window != nullptr) {
+                        const float w = __ldg(window + s);
+                        x = __fmul2_rn(x, make_float2(w, w));
+                    }
+                    float2 c = __ldg(chirp + m);
+                    if (!forward)
+                        c.y = -c.y;
+                    x = cmul(x, c);
+                }
+                v[b * R0 + q] = x;
+            }
+        cta_fft<L, true, false>(v, S, t, twL);
+#pragma unroll
+        for (int b = 0; b < E / RM; b++)
+#pragma unroll
+            for (int q = 0; q < RM; q++) {
+                const int k = (t + b * TPV) + q * (L / RM);
+                float2 h = __ldg(Bhat + k);
+                if (!forward)
+                    h.y = -h.y;
+                v[b * RM + q] = cmul(v[b * RM + q], h);
+            }
+        __syncthreads(); // the forward transform's last gather is done before the inverse reuses S
+        cta_fft<L, false, true>(v, S, t, twL);
+#pragma unroll
+        for (int b = 0; b < E / RL; b++)
+#pragma unroll
+            for (int q = 0; q < RL; q++) {
+                const int k = (t + b * TPV) + q * (L / RL);
+                if (k < N) {
+                    float2 c = __ldg(chirp + k);
+                    if (!forward)
+                        c.y = -c.y;
+                    int o = k;
+                    if (out_rot) {
+                        o += N - len_out;
+                        o -= o >= N ? N : 0;
+                    }
+                    vcc_store(a, vec, N, o, cmul(v[b * RL + q], c));
+                }
+            }
+        __syncthreads(); // the next vector's first pass overwrites S
+    }
+}
+
+struct BluesteinPlan {
+    int L = 0;
+    float2 *chirp = nullptr, *Bhat = nullptr, *twL = nullptr;
+};
+
+int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st);
+
+// tables of (current device, N); built on `st` at the first use (the launch that follows is ordered behind them)
+static int bluestein_plan(int N, int nsm, cudaStream_t st, BluesteinPlan* out)
+{
+    static std::mutex mu;
+    static std::vector<std::pair<std::pair<int, int>, BluesteinPlan>> plans;
+    int dev = 0;
+    GRB_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(mu);
+    for (auto& p : plans)
+        if (p.first.first == dev && p.first.second == N) {
+            *out = p.second;
+            return 0;
+        }
+    BluesteinPlan pl;
+    pl.L = 1024;
+    while (pl.L < 2 * N - 1)
+        pl.L *= 2;
+    const int L = pl.L;
+    const double pi = 3.14159265358979323846;
+    std::vector<float2> c((size_t)N), b((size_t)L, make_float2(0.f, 0.f)), roots((size_t)L);
+    for (int n = 0; n < N; n++) {
+        const long long r = ((long long)n * n) % (2LL * N); // n^2 mod 2N: the angle stays small, the table exact to fp32
+        const double ang = pi * (double)r / (double)N;
+        c[n] = make_float2((float)cos(ang), (float)-sin(ang));
+        const float2 bn = make_float2((float)(cos(ang) / L), (float)(sin(ang) / L)); // conj(c) / L
+        b[n] = bn;
+        if (n)
+            b[L - n] = bn;
+    }
+    for (int i = 0; i < L; i++) {
+        const double ang = -2.0 * pi * (double)i / (double)L;
+        roots[i] = make_float2((float)cos(ang), (float)sin(ang));
+    }
+    float2* tmp = nullptr;
+    GRB_CUDA(cudaMalloc(&pl.chirp, (size_t)N * 8));
+    GRB_CUDA(cudaMalloc(&pl.Bhat, (size_t)L * 8));
+    GRB_CUDA(cudaMalloc(&pl.twL, (size_t)L * 8));
+    GRB_CUDA(cudaMalloc(&tmp, (size_t)L * 8));
+    GRB_CUDA(cudaMemcpyAsync(pl.chirp, c.data(), (size_t)N * 8, cudaMemcpyHostToDevice, st));
+    GRB_CUDA(cudaMemcpyAsync(pl.twL, roots.data(), (size_t)L * 8, cudaMemcpyHostToDevice, st));
+    GRB_CUDA(cudaMemcpyAsync(tmp, b.data(), (size_t)L * 8, cudaMemcpyHostToDevice, st));
+    VccArgs fa{ tmp, pl.Bhat, 1, nullptr, pl.twL, 0, 0, 1, 0, 0.f, 0.f, nullptr };
+    int rc = fft_vcc_launch_ex(L, true, false, fa, nsm, st);
+    if (rc)
+        return rc;
+    GRB_CUDA(cudaStreamSynchronize(st)); // the pageable staging vectors and tmp go away
+    cudaFree(tmp);
+    plans.push_back({ { dev, N }, pl });
+    *out = pl;
+    return 0;
+}
+
+template <int L>
+static int launch_bluestein(const BluesteinPlan& pl, int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st)
+{
+    const size_t smem = (size_t)fft_smem_elems(L) * 8;
+    auto go = [&](auto kern) -> int {
+        if (smem > 48 * 1024)
+            GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int occ = 1;
+        GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, L / 16, smem));
+        if (occ < 1)
+            occ = 1;
+        long long grid = (long long)nsm * occ;
+        if (grid > a.nvec)
+            grid = a.nvec;
+        kern<<<(unsigned)grid, L / 16, smem, st>>>(a, N, fwd ? 1 : 0, pl.chirp, pl.Bhat, pl.twL);
+        GRB_LAUNCH_CHECK();
+        return 0;
+    };
+    return real_in ? go(fft_bluestein_kernel<L, true>) : go(fft_bluestein_kernel<L, false>);
+}
+
+static int bluestein_launch(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st)
+{
+    BluesteinPlan pl;
+    int rc = bluestein_plan(N, nsm, st, &pl);
+    if (rc)
+        return rc;
+    switch (pl.L) {
+    case 1024:
+        return launch_bluestein<1024>(pl, N, fwd, real_in, a, nsm, st);
+    case 2048:
+        return launch_bluestein<2048>(pl, N, fwd, real_in, a, nsm, st);
+    case 4096:
+        return launch_bluestein<4096>(pl, N, fwd, real_in, a, nsm, st);
+    case 8192:
+        return launch_bluestein<8192>(pl, N, fwd, real_in, a, nsm, st);
+    case 16384:
+        return launch_bluestein<16384>(pl, N, fwd, real_in, a, nsm, st);
+    }
+    return fail(GRB200_ERANGE, "fft_vcc: no transform for size %d", N);
+}
+
 template <int N, bool FWD, bool REAL>
 static int launch_vcc(const VccArgs& a, int nsm, cudaStream_t st)
 {
@@ -410,6 +597,12 @@ int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, 
     if (N > fft_direct_max())
         return fail(GRB200_ERANGE, "fft_vcc: fft_size %d is not supported (powers of two up to 16384, any size up to %d)",
                     N, fft_direct_max());
+    static const bool use_bluestein = [] {
+        const char* e = GRB_GETENV_ONCE("GRB200_FFT_BLUESTEIN"); // 0 = the O(N^2) kernel for every size
+        return !(e && e[0] == '0');
+    }();
+    if (use_bluestein && N >= 128) // (below that the direct sum is cheaper than two 1024-point transforms)
+        return bluestein_launch(N, fwd, real_in, a, nsm, st);
     const size_t smem = (size_t)N * 16;
     if (smem > 48 * 1024)
         GRB_CUDA(cudaFuncSetAttribute(dft_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -176,7 +176,8 @@ def test_fft_vcc_reference_fixtures(grb):
         assert_parity(got, fx["vcc15_f%d_s1" % fwd], "odd size shift f%d" % fwd)
 
 
-@pytest.mark.parametrize("N", [1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096, 8192, 16384, 12, 100, 1000])
+@pytest.mark.parametrize("N", [1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096, 8192, 16384, 12, 100, 1000,
+                               129, 600, 1536, 2049, 5000, 8191])  # (sizes that are not powers of two: Bluestein from 128 on)
 def test_fft_vcc_sizes(grb, orc, N):
     rng = np.random.default_rng(N)
     nvec = 37 if N <= 4096 else 5
