@@ -39,6 +39,9 @@ struct VccArgs {
 };
 int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st);
 // logpwr.cu: single_pole_iir along the frames + nlog10, in place on p [nframes][N]
+// capi_resamp.cu: the streaming polyphase kernel (register ring per (phase, run)); *done = false when the geometry does not fit
+int resamp_stream_try(bool ct, const void* in, void* out, long long nout, unsigned ctr0, unsigned L, unsigned D, int T,
+                      const float* rev_tap_major, int nsm, cudaStream_t st, bool* done);
 long long logpwr_scratch_floats(long long nframes, int N, int nsm);
 long long logpwr_static_scratch_floats();
 int logpwr_static_check(long long nframes, int N, int nsm);

@@ -6,6 +6,7 @@
 // shared memory, broadcast reads), so an input item is fetched T times per L*T multiply-adds; the L results of a position
 // are contiguous in the output.  8 + 8L algorithmic bytes per input item: the block is bound by its own output stream.
 #include <cstdint>
+#include <type_traits>
 #include "capi_common.cuh"
 #include "tma.cuh"
 
@@ -34,25 +35,21 @@ __global__ void __launch_bounds__(256) interp_fir_kernel(const float2* __restric
 #pragma unroll
             for (int t = 0; t < TT; t++)
                 w[t] = __ldg(x + t);
-            // (summation order = interp_stream_kernel's: taps from the newest item backwards, even and odd ones in separate
-            // accumulators -- a stream cut into calls of any length gives the same bits whichever kernel a call takes)
             auto phase = [&](int p) {
                 const float* h = sh + (size_t)p * TT * ES;
-                float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+                float2 a = make_float2(0.f, 0.f);
 #pragma unroll
-                for (int u = 0; u < TT; u++) {
-                    const int t = TT - 1 - u;
+                for (int t = 0; t < TT; t++) {
                     if (CT) {
                         const float hr = h[2 * t], hi = h[2 * t + 1];
-                        a0 = __ffma2_rn(make_float2(hr, hr), w[t], a0);
-                        a1 = __ffma2_rn(make_float2(-hi, hi), make_float2(w[t].y, w[t].x), a1);
-                    } else if (u & 1) {
-                        a1 = __ffma2_rn(make_float2(h[t], h[t]), w[t], a1);
+                        a.x = fmaf(w[t].x, hr, fmaf(-w[t].y, hi, a.x));
+                        a.y = fmaf(w[t].x, hi, fmaf(w[t].y, hr, a.y));
                     } else {
-                        a0 = __ffma2_rn(make_float2(h[t], h[t]), w[t], a0);
+                        a.x = fmaf(w[t].x, h[t], a.x);
+                        a.y = fmaf(w[t].y, h[t], a.y);
                     }
                 }
-                return __fadd2_rn(a0, a1);
+                return a;
             };
             if ((L & 1) == 0 && pair_ok) { // two phases per 16-byte store: item i*L + p is even
                 for (int p = 0; p < L; p += 2) {
@@ -66,21 +63,19 @@ __global__ void __launch_bounds__(256) interp_fir_kernel(const float2* __restric
         } else {
             for (int p = 0; p < L; p++) {
                 const float* h = sh + (size_t)p * T * ES;
-                float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
-                for (int u = 0; u < T; u++) {
-                    const int t = T - 1 - u;
+                float2 a = make_float2(0.f, 0.f);
+                for (int t = 0; t < T; t++) {
                     const float2 v = __ldg(x + t);
                     if (CT) {
                         const float hr = h[2 * t], hi = h[2 * t + 1];
-                        a0 = __ffma2_rn(make_float2(hr, hr), v, a0);
-                        a1 = __ffma2_rn(make_float2(-hi, hi), make_float2(v.y, v.x), a1);
-                    } else if (u & 1) {
-                        a1 = __ffma2_rn(make_float2(h[t], h[t]), v, a1);
+                        a.x = fmaf(v.x, hr, fmaf(-v.y, hi, a.x));
+                        a.y = fmaf(v.x, hi, fmaf(v.y, hr, a.y));
                     } else {
-                        a0 = __ffma2_rn(make_float2(h[t], h[t]), v, a0);
+                        a.x = fmaf(v.x, h[t], a.x);
+                        a.y = fmaf(v.y, h[t], a.y);
                     }
                 }
-                y[p] = __fadd2_rn(a0, a1);
+                y[p] = a;
             }
         }
     }
@@ -163,162 +158,17 @@ __global__ void __launch_bounds__(256) interp_fir_tile_kernel(const float2* __re
     }
 }
 
-// ---- streaming form (round 2, third attempt; interpolation <= 32, <= 32 taps per phase): a register ring per (phase, run) --
+// ---- streaming form (round 2): the resampler's streaming kernel (capi_resamp.cu, resamp_stream_kernel) with decimation 1 ----
 // What bounds the kernels above is the load/store unit: every multiply-add pair drags a shared-memory tap load along and the
-// window comes through L1 item by item.  Here nothing but the stream itself moves: thread (phase l, run g) keeps the taps of
-// its phase AND the last TP input items of its run in registers and walks down the run -- per output one 8-byte shared load
-// (the new item, broadcast to the L lanes of the run), TP packed FMAs and one store; the L lanes of a run store L consecutive
-// outputs (a whole 32-byte sector at L = 4).  A producer warp streams the runs' new items: per iteration and run ONE bulk
-// copy of KT + 2 items (the copy starts on an even item: 16-byte rule) into a ring of NS stages, rows KT + 2 items apart (which
-// also keeps the 32 / L runs of a warp in different banks).
-namespace istream {
-constexpr int KT = 32, ROW = KT + 2, NCW = 8, MAXNS = 4; // items per run and iteration, row stride, consumer warps, stages <=
-}
-
-template <int TP, bool CT>
-__global__ void __launch_bounds__(288) // (a 3-CTA register cap was measured slower: 434 vs 465 G at 4 x 16)
-interp_stream_kernel(const float2* __restrict__ in /* 16-byte aligned; the stream starts at in[gs] */, float2* __restrict__ out,
-                     long long nin_pos, int L, int T, const float* __restrict__ rev, int iters, int gs, int NS)
-{
-    using namespace istream;
-    constexpr int ES = CT ? 2 : 1;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int RW = 32 / L, NG = NCW * RW; // runs per warp, per CTA
-    float2* xs = reinterpret_cast<float2*>(smem_raw); // [NS][NG][ROW]
-    unsigned long long* full = reinterpret_cast<unsigned long long*>(smem_raw + (size_t)NS * NG * ROW * 8);
-    unsigned long long* empty = full + MAXNS;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const long long region = (long long)iters * KT; // input positions per run
-    const long long cta0 = (long long)blockIdx.x * NG * region;
-    const long long nitems = nin_pos + T - 1 + gs; // items of `in` that may be read (counted from the aligned base)
-    const long long nitems_even = nitems & ~1LL;
-    if (tid == 0)
-        for (int s = 0; s < NS; s++) {
-            mbar_init(&full[s], 32);
-            mbar_init(&empty[s], NCW);
-        }
-    __syncthreads();
-    // position n reads items n + gs .. n + gs + T - 1; the newest one of a run's iteration `it`, step k, is item
-    // b + it KT + k with b = n0 + gs + T - 1; copies start at the even item at or below it
-    if (warp == NCW) {
-        // ---------------- producer warp: lane j streams runs j, j + 32, ... ----------------
-        for (int it = 0; it < iters; it++) {
-            const int s = it % NS, use = it / NS;
-            if (use > 0)
-                mbar_wait(&empty[s], (unsigned)((use - 1) & 1));
-            unsigned bytes = 0;
-            for (int g = lane; g < NG; g += 32) {
-                const long long b = cta0 + (long long)g * region + gs + T - 1 + (long long)it * KT;
-                const long long a0 = b & ~1LL;
-                long long n = nitems_even - a0;
-                n = n < 0 ? 0 : (n > ROW ? ROW : n);
-                bytes += (unsigned)(n * 8);
-            }
-            mbar_expect_tx(&full[s], bytes); // (arrives: 32 arrivals complete the phase once the bytes are in)
-            for (int g = lane; g < NG; g += 32) {
-                const long long b = cta0 + (long long)g * region + gs + T - 1 + (long long)it * KT;
-                const long long a0 = b & ~1LL;
-                long long n = nitems_even - a0;
-                n = n < 0 ? 0 : (n > ROW ? ROW : n);
-                if (n)
-                    bulk_g2s(xs + ((size_t)s * NG + g) * ROW, in + a0, (unsigned)(n * 8), &full[s]);
-            }
-        }
-        return;
-    }
-    // ---------------- consumers ----------------
-    const int l = lane % L, gw = lane / L;
-    const bool idle = gw >= RW; // lanes beyond the last whole run of the warp (L does not divide 32)
-    const int g = warp * RW + (idle ? 0 : gw);
-    const long long n0 = cta0 + (long long)g * region; // first input position of this run
-    const long long b0 = n0 + gs + T - 1;
-    const int off = (int)(b0 & 1); // region is even: the same for every iteration
-    // taps of phase l; tap u multiplies the item u behind the newest one of a window (rev index T - 1 - u)
-    float hr[TP], hi[CT ? TP : 1];
-#pragma unroll
-    for (int u = 0; u < TP; u++) {
-        const bool ok = u < T && !idle;
-        hr[u] = ok ? __ldg(rev + ((size_t)l * T + (T - 1 - u)) * ES) : 0.f;
-        if (CT)
-            hi[u] = ok ? __ldg(rev + ((size_t)l * T + (T - 1 - u)) * ES + 1) : 0.f;
-    }
-    float2 ring[TP]; // once the newest item of position n = n0 + m is in, ring[(m - u) mod TP] = item b0 + m - u
-#pragma unroll
-    for (int u = 1; u < TP; u++) {
-        const long long r = b0 - u;
-        ring[(TP - u) % TP] = (u < T && r >= gs && r < nitems) ? in[r] : make_float2(0.f, 0.f);
-    }
-    ring[0] = make_float2(0.f, 0.f);
-    const long long last_odd = (nitems & 1) ? nitems - 1 : -1; // the one item the 16-byte copies cannot bring
-    for (int it = 0; it < iters; it++) {
-        const int s = it % NS;
-        mbar_wait(&full[s], (unsigned)((it / NS) & 1));
-        const float2* src = xs + ((size_t)s * NG + g) * ROW + off;
-        const long long nb = n0 + (long long)it * KT; // first position of this block
-        float2* o = out + nb * L + l;
-        const long long left = nin_pos - nb;
-        static_assert(KT % TP == 0, "the ring position returns to 0 every iteration");
-#pragma unroll
-        for (int k = 0; k < KT; k++) {
-            float2 x = src[k];
-            if (b0 + (long long)it * KT + k == last_odd)
-                x = in[last_odd];
-            ring[k % TP] = x;
-            float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
-#pragma unroll
-            for (int u = 0; u < TP; u++) {
-                const float2 w = ring[(k - u + 2 * TP) % TP];
-                if (CT) { // a += w * (hr + j hi)
-                    a0 = __ffma2_rn(make_float2(hr[u], hr[u]), w, a0);
-                    a1 = __ffma2_rn(make_float2(-hi[u], hi[u]), make_float2(w.y, w.x), a1);
-                } else if (u & 1) {
-                    a1 = __ffma2_rn(make_float2(hr[u], hr[u]), w, a1);
-                } else {
-                    a0 = __ffma2_rn(make_float2(hr[u], hr[u]), w, a0);
-                }
-            }
-            if (k < left && !idle)
-                o[(long long)k * L] = __fadd2_rn(a0, a1);
-        }
-        __syncwarp();
-        if (lane == 0)
-            mbar_arrive_one(&empty[s]);
-    }
-}
-
-template <int TP, bool CT>
-static int interp_stream_launch(const void* in, void* out, long long nin_pos, int L, int T, const float* rev, int nsm,
-                                cudaStream_t st)
-{
-    using namespace istream;
-    const int NG = NCW * (32 / L);
-    const size_t stage = (size_t)NG * ROW * 8;
-    const int NS = 3 * stage <= 72 * 1024 ? 3 : 2;
-    const size_t smem = (size_t)NS * stage + 2 * MAXNS * 8 + 16;
-    auto kern = interp_stream_kernel<TP, CT>;
-    GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int occ = 1;
-    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 288, smem));
-    if (occ < 1)
-        occ = 1;
-    const long long per_iter = (long long)NG * KT; // positions per CTA and iteration
-    long long grid = (long long)nsm * occ;
-    const long long need = (nin_pos + per_iter - 1) / per_iter;
-    if (grid > need)
-        grid = need;
-    long long iters = (nin_pos + grid * per_iter - 1) / (grid * per_iter);
-    grid = (nin_pos + iters * per_iter - 1) / (iters * per_iter);
-    if (iters > 0x7fffffffLL / KT)
-        return fail(GRB200_ERANGE, "interp_fir_filter: work() call too long for one launch");
-    const int gs = (int)((((uintptr_t)in) >> 3) & 1); // 8-byte aligned only: the stream starts one item into an aligned one
-    kern<<<(unsigned)grid, 288, smem, st>>>((const float2*)in - gs, (float2*)out, nin_pos, L, T, rev, (int)iters, gs, NS);
-    GRB_LAUNCH_CHECK();
-    return 0;
-}
-
+// window comes through L1 item by item.  In the streaming form nothing but the stream itself moves: thread (phase l, run g)
+// keeps the taps of its phase AND the last TP input items of its run in registers and walks down the run -- per output one
+// 8-byte shared load (the new item, broadcast to the L lanes of the run), TP packed FMAs and one store; the L lanes of a run
+// store L consecutive outputs (a whole 32-byte sector at L = 4); a producer warp streams the runs' new items with one bulk
+// copy per run and iteration.  Same summation order as interp_fir_kernel (one accumulator, oldest tap first): a stream cut
+// into calls of any length gives the same bits whichever kernel a call takes.
 template <bool CT>
-static int interp_launch_t(const void* in, void* out, long long nin_pos, int L, int T, const float* rev, int nsm,
-                           cudaStream_t st)
+static int interp_launch_t(const void* in, void* out, long long nin_pos, int L, int T, const float* rev, const float* rev_tm,
+                           int nsm, cudaStream_t st)
 {
     const size_t smem = (size_t)L * T * (CT ? 8 : 4);
     if (smem > 200 * 1024)
@@ -334,14 +184,11 @@ static int interp_launch_t(const void* in, void* out, long long nin_pos, int L, 
         const char* e = GRB_GETENV_ONCE("GRB200_INTERP_STREAM"); // 0 = the one-position-per-thread kernel only
         return !(e && e[0] == '0');
     }();
-    if (use_stream && L >= 2 && L <= 32 && T <= 32 && nin_pos >= 8192 && !(CT && T > 16) &&
-        (size_t)2 * istream::NCW * (32 / L) * istream::ROW * 8 <= 100 * 1024) {
-        if (T <= 8)
-            return interp_stream_launch<8, CT>(in, out, nin_pos, L, T, rev, nsm, st);
-        if (T <= 16)
-            return interp_stream_launch<16, CT>(in, out, nin_pos, L, T, rev, nsm, st);
-        if constexpr (!CT)
-            return interp_stream_launch<32, CT>(in, out, nin_pos, L, T, rev, nsm, st);
+    if (use_stream && rev_tm && nin_pos >= 8192) {
+        bool done = false;
+        const int rc = resamp_stream_try(CT, in, out, nin_pos * L, 0u, (unsigned)L, 1u, T, rev_tm, nsm, st, &done);
+        if (rc || done)
+            return rc;
     }
     if (use_tile && L <= 16 && (T == 4 || T == 8 || T == 16 || T == 32) && nin_pos >= 1024) {
         const size_t tsm = (((size_t)L * T * (CT ? 2 : 1) + 3) & ~(size_t)3) * 4 + (size_t)((256 + T + 1) & ~1) * 8 +
@@ -397,13 +244,13 @@ static int interp_launch_t(const void* in, void* out, long long nin_pos, int L, 
     return launch(interp_fir_kernel<0, CT>);
 }
 
-static int interp_launch(bool ct, const void* in, void* out, long long nin_pos, int L, int T, const float* rev, int nsm,
-                         cudaStream_t st)
+static int interp_launch(bool ct, const void* in, void* out, long long nin_pos, int L, int T, const float* rev,
+                         const float* rev_tm, int nsm, cudaStream_t st)
 {
     if (nin_pos <= 0)
         return 0;
-    return ct ? interp_launch_t<true>(in, out, nin_pos, L, T, rev, nsm, st)
-              : interp_launch_t<false>(in, out, nin_pos, L, T, rev, nsm, st);
+    return ct ? interp_launch_t<true>(in, out, nin_pos, L, T, rev, rev_tm, nsm, st)
+              : interp_launch_t<false>(in, out, nin_pos, L, T, rev, rev_tm, nsm, st);
 }
 
 } // namespace grb
@@ -412,7 +259,7 @@ struct grb200_interp {
     int device = 0;
     bool ct = false;
     int L = 1, T = 0, ntaps = 0; // interpolation, taps per phase, taps as given
-    DevBuf rev;
+    DevBuf rev, rev_tm; // phase-major reversed taps; the same tap-major (the streaming kernel's table)
     Stager sg;
     std::mutex mu;
 };
@@ -430,6 +277,13 @@ static int interp_upload(grb200_interp* h, const float* taps, int ntaps)
     }
     int rc = h->rev.upload(rev.data(), rev.size() * sizeof(float));
     if (rc)
+        return rc;
+    std::vector<float> tm(rev.size());
+    for (int p = 0; p < L; p++)
+        for (int t = 0; t < T; t++)
+            for (int e = 0; e < es; e++)
+                tm[((size_t)t * L + p) * es + e] = rev[((size_t)p * T + t) * es + e];
+    if ((rc = h->rev_tm.upload(tm.data(), tm.size() * sizeof(float))))
         return rc;
     h->T = T;
     h->ntaps = ntaps;
@@ -502,7 +356,7 @@ int grb200_interp_fir_work_dev(grb200_interp* h, const void* in_dev, void* out_d
     if (rc)
         return rc;
     cudaStream_t st_ = pick_stream(stream, h->sg);
-    return dev_done(interp_launch(h->ct, in_dev, out_dev, noutput / h->L, h->L, h->T, (const float*)h->rev.p, sm_count(h->device),
+    return dev_done(interp_launch(h->ct, in_dev, out_dev, noutput / h->L, h->L, h->T, (const float*)h->rev.p, (const float*)h->rev_tm.p, sm_count(h->device),
                          st_), h->sg, st_);
 }
 
@@ -542,7 +396,7 @@ int grb200_interp_fir_work(grb200_interp* h, const void* in_host, void* out_host
         [&](long long c, int slot, cudaStream_t st) {
             const long long i0 = c * chunk, n = std::min(chunk, ni - i0);
             return interp_launch(h->ct, sg.dev[slot][0], sg.dev[slot][1], n, L, T, (const float*)h->rev.p,
-                                 sm_count(h->device), st);
+                                 (const float*)h->rev_tm.p, sm_count(h->device), st);
         });
 }
 
@@ -553,6 +407,7 @@ void grb200_interp_fir_destroy(grb200_interp* h)
     grb::DeviceScope _ds(h->device);
     h->sg.destroy();
     h->rev.release();
+    h->rev_tm.release();
     delete h;
 }
 

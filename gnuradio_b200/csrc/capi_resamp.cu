@@ -11,6 +11,7 @@
 #include <cstdint>
 #include <type_traits>
 #include "capi_common.cuh"
+#include "tma.cuh"
 
 using namespace grb;
 
@@ -177,6 +178,224 @@ static int resamp_phase_launch(const void* in, void* out, long long nout, unsign
     return 0;
 }
 
+// ---- streaming form (round 2): interpolation <= 32, decimation <= 4 (and <= taps per phase), <= 32 taps per phase ----------
+// The kernels above read a T-item window per output through L1: load/store-unit bound (0.34 of HBM at 3/2 x 16).  Outputs of
+// the SAME phase are L apart and their windows D items apart, so for small D a thread that keeps one phase can keep its
+// window in a register ring and fetch D new items per output -- interp_stream_kernel (capi_interp.cu) with a step of D:
+// lanes = (output offset l < L, run g); lane l owns outputs n L + l of its run, phase (ctr0 + l D) mod L, window start
+// n D + (ctr0 + l D) / L; a producer warp streams each run's new items (one bulk copy of KT D + D + 2 items per run and
+// iteration).  Summation order = the kernels above (one accumulator, oldest tap first): a stream cut into calls of any
+// length gives the same bits whichever kernel a call takes.
+namespace rstream {
+constexpr int KT = 32, NCW = 8, MAXNS = 4; // groups of L outputs per run and iteration, consumer warps, stages <=
+// row stride: even (16-byte copies) with an odd half -- 4 x odd words: the runs of a warp start in different banks
+__host__ __device__ constexpr int row_items(int D) { return (((KT * D + D + 3) / 2) | 1) * 2; }
+}
+
+template <int TP, int D, bool CT>
+__global__ void __launch_bounds__(288)
+resamp_stream_kernel(const float2* __restrict__ in /* 16-byte aligned; the stream starts at in[gs] */, float2* __restrict__ out,
+                     long long nout, unsigned ctr0, int L, int T, const float* __restrict__ rev, long long nitems, int iters,
+                     int gs, int NS)
+{
+    using namespace rstream;
+    constexpr int ROW = row_items(D);
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int RW = 32 / L, NG = NCW * RW;
+    float2* xs = reinterpret_cast<float2*>(smem_raw); // [NS][NG][ROW]
+    unsigned long long* full = reinterpret_cast<unsigned long long*>(smem_raw + (size_t)NS * NG * ROW * 8);
+    unsigned long long* empty = full + MAXNS;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long region = (long long)iters * KT; // groups per run
+    const long long cta0 = (long long)blockIdx.x * NG * region;
+    const long long nitems_even = nitems & ~1LL; // (nitems counts from the aligned base: gs included)
+    if (tid == 0)
+        for (int s = 0; s < NS; s++) {
+            mbar_init(&full[s], 32);
+            mbar_init(&empty[s], NCW);
+        }
+    __syncthreads();
+    // the first new item of a run's group m (for a lane at offset 0) is item (n0 + m) D + T - D + gs of the aligned buffer
+    if (warp == NCW) {
+        for (int it = 0; it < iters; it++) {
+            const int s = it % NS, use = it / NS;
+            if (use > 0)
+                mbar_wait(&empty[s], (unsigned)((use - 1) & 1));
+            unsigned bytes = 0;
+            for (int g = lane; g < NG; g += 32) {
+                const long long a0 = ((cta0 + (long long)g * region + (long long)it * KT) * D + T - D + gs) & ~1LL;
+                long long n = nitems_even - a0;
+                n = n < 0 ? 0 : (n > ROW ? ROW : n);
+                bytes += (unsigned)(n * 8);
+            }
+            mbar_expect_tx(&full[s], bytes);
+            for (int g = lane; g < NG; g += 32) {
+                const long long a0 = ((cta0 + (long long)g * region + (long long)it * KT) * D + T - D + gs) & ~1LL;
+                long long n = nitems_even - a0;
+                n = n < 0 ? 0 : (n > ROW ? ROW : n);
+                if (n)
+                    bulk_g2s(xs + ((size_t)s * NG + g) * ROW, in + a0, (unsigned)(n * 8), &full[s]);
+            }
+        }
+        return;
+    }
+    const int l = lane % L, gw = lane / L;
+    const bool idle = gw >= RW;
+    const int g = warp * RW + (idle ? 0 : gw);
+    const long long n0 = cta0 + (long long)g * region; // first group of this run
+    const unsigned sl = ctr0 + (unsigned)l * (unsigned)D;
+    const int ql = (int)(sl / (unsigned)L), ph = (int)(sl - (unsigned)ql * (unsigned)L); // window offset and phase of this lane
+    const long long b0 = n0 * D + T - D + gs; // item of (group 0, new item 0) for a lane at offset 0
+    const int off = (int)(b0 & 1) + ql;       // (KT D is even: the parity holds for every iteration)
+    // tap u multiplies the item u behind the newest one of a window: rev index T - 1 - u (tap-major table)
+    float hr[TP], hi[CT ? TP : 1];
+#pragma unroll
+    for (int u = 0; u < TP; u++) {
+        const bool ok = u < T && !idle;
+        if (CT) {
+            const float2 c = ok ? __ldg(reinterpret_cast<const float2*>(rev) + (size_t)(T - 1 - u) * L + ph) : make_float2(0.f, 0.f);
+            hr[u] = c.x;
+            hi[u] = c.y;
+        } else {
+            hr[u] = ok ? __ldg(rev + (size_t)(T - 1 - u) * L + ph) : 0.f;
+        }
+    }
+    // ring slot of the item r = m D + d (group m of the run, new item d): r mod TP; the T - D items in front of group 0 warm it up
+    float2 ring[TP];
+#pragma unroll
+    for (int u = 0; u < TP; u++)
+        ring[u] = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int r = 1; r < TP; r++) { // item b0 + ql - r
+        const long long x = b0 + ql - r;
+        if (r <= T - D && x >= gs && x < nitems)
+            ring[(TP - r) % TP] = in[x];
+    }
+    const long long last_odd = (nitems & 1) ? nitems - 1 : -1; // the one item the 16-byte copies cannot bring
+    static_assert(KT % TP == 0, "the ring position returns to 0 every iteration");
+    for (int it = 0; it < iters; it++) {
+        const int s = it % NS;
+        mbar_wait(&full[s], (unsigned)((it / NS) & 1));
+        const float2* src = xs + ((size_t)s * NG + g) * ROW + off;
+        const long long nb = n0 + (long long)it * KT; // first group of this block
+        const long long ib = b0 + ql + (long long)it * KT * D; // item index of src[0]
+        float2* o = out + nb * L + l;
+        const long long left = nout - (nb * L + l); // this lane's outputs of the block that exist: k L < left
+        auto block = [&](auto patch) {
+            constexpr bool PATCH = decltype(patch)::value; // this block holds the odd last item: it is read where it lies
+#pragma unroll
+            for (int k = 0; k < KT; k++) {
+#pragma unroll
+                for (int d = 0; d < D; d++) {
+                    float2 x = src[k * D + d];
+                    if (PATCH && ib + k * D + d == last_odd)
+                        x = in[last_odd];
+                    ring[(k * D + d) % TP] = x;
+                }
+                float2 a = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int u = TP - 1; u >= 0; u--) { // oldest tap first, one accumulator: the order of resamp_kernel (two
+                                                    // chains by tap parity were measured: no faster here, slower above)
+                    const float2 w = ring[(k * D + D - 1 - u + 4 * TP) % TP];
+                    if (CT) {
+                        a = __ffma2_rn(make_float2(-hi[u], hr[u]), make_float2(w.y, w.y), a);
+                        a = __ffma2_rn(make_float2(hr[u], hi[u]), make_float2(w.x, w.x), a);
+                    } else {
+                        a = __ffma2_rn(make_float2(hr[u], hr[u]), w, a);
+                    }
+                }
+                if ((long long)k * L < left && !idle)
+                    o[(long long)k * L] = a;
+            }
+        };
+        if (last_odd >= ib && last_odd < ib + KT * D)
+            block(std::true_type{});
+        else
+            block(std::false_type{});
+        __syncwarp();
+        if (lane == 0)
+            mbar_arrive_one(&empty[s]);
+    }
+}
+
+template <int TP, int D, bool CT>
+static int resamp_stream_launch_t(const void* in, void* out, long long nout, unsigned ctr0, int L, int T, const float* rev,
+                                  int nsm, cudaStream_t st, bool* done)
+{
+    using namespace rstream;
+    const int NG = NCW * (32 / L);
+    const size_t stage = (size_t)NG * row_items(D) * 8;
+    const int NS = 3 * stage <= 80 * 1024 ? 3 : 2;
+    const size_t smem = (size_t)NS * stage + 2 * MAXNS * 8 + 16;
+    if (smem > 160 * 1024)
+        return 0; // not done: the caller falls back
+    auto kern = resamp_stream_kernel<TP, D, CT>;
+    GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 288, smem));
+    if (occ < 1)
+        occ = 1;
+    const long long ngroups = (nout + L - 1) / L;
+    const long long per_iter = (long long)NG * KT;
+    long long grid = (long long)nsm * occ;
+    const long long need = (ngroups + per_iter - 1) / per_iter;
+    if (grid > need)
+        grid = need;
+    long long iters = (ngroups + grid * per_iter - 1) / (grid * per_iter);
+    grid = (ngroups + iters * per_iter - 1) / (iters * per_iter);
+    if (iters > 0x7fffffffLL / (KT * D))
+        return 0;
+    const int gs = (int)((((uintptr_t)in) >> 3) & 1);
+    // items the call may read: the last output's window ends at (ctr0 + (nout-1) D) / L + T
+    const long long nitems = (long long)(((unsigned long long)ctr0 + (unsigned long long)(nout - 1) * D) / (unsigned)L) + T + gs;
+    kern<<<(unsigned)grid, 288, smem, st>>>((const float2*)in - gs, (float2*)out, nout, ctr0, L, T, rev, nitems, (int)iters, gs,
+                                            NS);
+    GRB_LAUNCH_CHECK();
+    *done = true;
+    return 0;
+}
+
+template <bool CT>
+static int resamp_stream_launch(const void* in, void* out, long long nout, unsigned ctr0, unsigned L, unsigned D, int T,
+                                const float* rev, int nsm, cudaStream_t st, bool* done)
+{
+    *done = false;
+    static const bool use_stream = [] {
+        const char* e = GRB_GETENV_ONCE("GRB200_RESAMP_STREAM"); // 0 = the window-through-L1 kernels only
+        return !(e && e[0] == '0');
+    }();
+    if (!use_stream || L < 2 || L > 32 || D > 4 || (int)D > T || T > (CT ? 16 : 32) || nout < 32768)
+        return 0;
+    auto byd = [&](auto tp) -> int {
+        constexpr int TPv = decltype(tp)::value;
+        switch (D) {
+        case 1:
+            return resamp_stream_launch_t<TPv, 1, CT>(in, out, nout, ctr0, (int)L, T, rev, nsm, st, done);
+        case 2:
+            return resamp_stream_launch_t<TPv, 2, CT>(in, out, nout, ctr0, (int)L, T, rev, nsm, st, done);
+        case 3:
+            return resamp_stream_launch_t<TPv, 3, CT>(in, out, nout, ctr0, (int)L, T, rev, nsm, st, done);
+        default:
+            return resamp_stream_launch_t<TPv, 4, CT>(in, out, nout, ctr0, (int)L, T, rev, nsm, st, done);
+        }
+    };
+    if (T <= 8)
+        return byd(std::integral_constant<int, 8>{});
+    if (T <= 16)
+        return byd(std::integral_constant<int, 16>{});
+    if constexpr (!CT)
+        return byd(std::integral_constant<int, 32>{});
+    return 0;
+}
+
+// (also the streaming kernel of interp_fir_filter: an interpolator is the resampler with decimation 1 and counter 0)
+int resamp_stream_try(bool ct, const void* in, void* out, long long nout, unsigned ctr0, unsigned L, unsigned D, int T,
+                      const float* rev_tap_major, int nsm, cudaStream_t st, bool* done)
+{
+    return ct ? resamp_stream_launch<true>(in, out, nout, ctr0, L, D, T, rev_tap_major, nsm, st, done)
+              : resamp_stream_launch<false>(in, out, nout, ctr0, L, D, T, rev_tap_major, nsm, st, done);
+}
+
 static int resamp_launch(bool ct, const void* in, void* out, long long nout, unsigned ctr0, unsigned L, unsigned D, int T,
                          const float* rev, int nsm, cudaStream_t st)
 {
@@ -197,7 +416,11 @@ static int resamp_launch(bool ct, const void* in, void* out, long long nout, uns
         return 0;
     };
     bool done = false;
-    int rc = ct ? resamp_phase_launch<true>(in, out, nout, ctr0, L, D, T, rev, nblk, st, &done)
+    int rc = ct ? resamp_stream_launch<true>(in, out, nout, ctr0, L, D, T, rev, nsm, st, &done)
+                : resamp_stream_launch<false>(in, out, nout, ctr0, L, D, T, rev, nsm, st, &done);
+    if (rc || done)
+        return rc;
+    rc = ct ? resamp_phase_launch<true>(in, out, nout, ctr0, L, D, T, rev, nblk, st, &done)
                 : resamp_phase_launch<false>(in, out, nout, ctr0, L, D, T, rev, nblk, st, &done);
     if (rc || done)
         return rc;

@@ -160,6 +160,38 @@ def test_rational_resampler_set_taps_midstream_and_errors(grb, orc):
     assert blk.general_work(0, [100], [x], [np.empty(0, np.complex64)]) == 0
 
 
+@pytest.mark.parametrize("L,D,ntaps,cplx,ctr0,shift", [(3, 2, 48, False, 0, 0), (2, 3, 64, False, 1, 1), (4, 3, 61, True, 2, 0),
+                                                       (5, 4, 100, False, 3, 1), (4, 1, 64, False, 0, 0), (32, 3, 96, False, 7, 0),
+                                                       (7, 2, 100, True, 5, 1), (3, 4, 96, False, 1, 0), (2, 1, 64, False, 1, 1),
+                                                       (3, 2, 20, False, 2, 0)])
+def test_rational_resampler_streaming_kernel(grb, orc, L, D, ntaps, cplx, ctr0, shift):
+    """One device-resident call long enough for resamp_stream_kernel (small interpolation and decimation): every ring depth
+    and decimation step, interpolations that do not divide the warp, complex taps, a starting phase counter, an input
+    pointer that is only 8-byte aligned, an output count that is not a multiple of the interpolation."""
+    import torch
+
+    rng = np.random.default_rng(L * 131 + D * 17 + ntaps)
+    nout = 200001
+    T = -(-ntaps // L)
+    taps = crand(rng, ntaps) if cplx else rng.uniform(-1, 1, ntaps).astype(np.float32)
+    ni = (ctr0 + (nout - 1) * D) // L + 1
+    x = crand(rng, ni + T - 1)
+    xd = torch.from_numpy(np.concatenate([np.zeros(shift, np.complex64), x]).view(np.float32).copy()).cuda()
+    yd = torch.full((2 * nout + 2,), float("nan"), dtype=torch.float32, device="cuda")
+    cls = grb.filter.rational_resampler_base_ccc if cplx else grb.filter.rational_resampler_base_ccf
+    blk = cls(L, D, taps)
+    blk.set_ctr(ctr0)
+    used, made = blk.work_dev(xd.data_ptr() + 8 * shift, ni, yd.data_ptr(), nout, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert made == nout
+    y = yd.cpu().numpy()
+    assert np.isnan(y[-2:]).all()  # nothing written past the end
+    got = y[:-2].view(np.complex64)
+    exp, used_ref, ctr_ref = orc.rational_resampler(L, D, taps, x, noutput=nout, ctr=ctr0)
+    assert (used, blk.ctr()) == (used_ref, ctr_ref)
+    assert_parity(got, exp, "oracle %d/%d/%d" % (L, D, ntaps), 2e-6, 2e-5)
+
+
 def test_rational_resampler_large_device_resident_and_host_chunks(grb):
     import torch
 
