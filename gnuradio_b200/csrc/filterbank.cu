@@ -179,11 +179,12 @@ filterbank_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out,
         };
         unsigned total = 0;
         long long r0;
-#pragma unroll 1
+        constexpr int UNR = NG <= 16 ? NG : 1;
+#pragma unroll UNR
         for (int g = 0; g < NG; g++)
             total += rows_of(g, r0);
         mbar_expect_tx(b, total);
-#pragma unroll 1
+#pragma unroll UNR
         for (int g = 0; g < NG; g++) {
             const unsigned bytes = rows_of(g, r0);
             if (bytes)

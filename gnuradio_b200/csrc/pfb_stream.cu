@@ -91,11 +91,12 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
         };
         unsigned total = 0;
         long long r0;
-#pragma unroll 1
+        constexpr int UNR = NG <= 16 ? NG : 1; // (M = 8 has 32 groups: rolled there, straight-line code elsewhere)
+#pragma unroll UNR
         for (int g = 0; g < NG; g++)
             total += rows_of(g, r0);
         mbar_expect_tx(bar, total);
-#pragma unroll 1
+#pragma unroll UNR
         for (int g = 0; g < NG; g++) {
             const unsigned bytes = rows_of(g, r0);
             if (bytes)
