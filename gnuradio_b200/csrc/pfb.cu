@@ -33,17 +33,22 @@ int halo_fetch_launch(void* dst, const void* src, size_t bytes, cudaStream_t st)
 __global__ void __launch_bounds__(256)
 pfb_generic_kernel(const float2* __restrict__ x, float2* __restrict__ out, long long out_stride, int nouts,
                    const int* __restrict__ cmap, long long noutput, int M, int T, int R,
-                   const float* __restrict__ h, const float2* __restrict__ wtab, int OT)
+                   const float* __restrict__ h, const float2* __restrict__ wtab, int OT, int R1)
 {
+    // R1 > 1: M = R1 * R2 and the DFT runs in two stages through a second buffer (M (R1 + R2) multiply-adds per output time
+    // instead of M^2): y[j][k1] = sum_q v[j + R2 q] W^(R2 q k1), then X[c] = sum_j y[j][c mod R1] W^(j c) for the mapped channels
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2* v = reinterpret_cast<float2*>(smem_raw); // [OT][M+1]
     float2* W = v + (size_t)OT * (M + 1);            // [M]
+    float2* v2 = W + M;                              // [OT][M+1] when R1 > 1
+    const int R2 = R1 > 1 ? M / R1 : 1;
     const int NT = blockDim.x, tid = threadIdx.x;
     for (int k = tid; k < M; k += NT)
         W[k] = wtab[k];
     const long long ntiles = (noutput + OT - 1) / OT;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const long long o0 = tile * OT;
+        const int rot0 = (int)(((o0 + 2) * R) % M), Rm = R % M;
         __syncthreads();
         for (int idx = tid; idx < OT * M; idx += NT) {
             const int ol = idx / M, i = idx % M;
@@ -52,19 +57,67 @@ pfb_generic_kernel(const float2* __restrict__ x, float2* __restrict__ out, long 
                 const long long P = (oo + 1) * R - 1;
                 const float2* xp = x + (P - i + (long long)T * M);
                 float2 acc = make_float2(0.f, 0.f);
-                for (int u = 0; u < T; u++) {
-                    const float hh = __ldg(h + u * M + i);
-                    const float2 a = xp[-(long long)u * M];
-                    acc.x = fmaf(hh, a.x, acc.x);
-                    acc.y = fmaf(hh, a.y, acc.y);
+                int u = 0;
+                for (; u + 4 <= T; u += 4) { // four independent loads of each kind in flight, then the dependent chain
+                    float hh[4];
+                    float2 a[4];
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        hh[e] = __ldg(h + (u + e) * M + i);
+                        a[e] = __ldg(xp - (long long)(u + e) * M);
+                    }
+#pragma unroll
+                    for (int e = 0; e < 4; e++)
+                        acc = __ffma2_rn(make_float2(hh[e], hh[e]), a[e], acc);
                 }
-                int q = (int)((i - (oo + 2) * R) % M);
+                for (; u < T; u++) {
+                    const float hh = __ldg(h + u * M + i);
+                    acc = __ffma2_rn(make_float2(hh, hh), __ldg(xp - (long long)u * M), acc);
+                }
+                int q = (i - rot0 - ol * Rm) % M; // (i - (oo + 2) R) mod M, the 64-bit part taken once per tile
                 if (q < 0)
                     q += M;
                 v[ol * (M + 1) + q] = acc;
             }
         }
         __syncthreads();
+        if (R1 > 1) {
+            for (int idx = tid; idx < OT * M; idx += NT) { // (ol, k1, j): lanes over j, then k1
+                const int ol = idx / M, r = idx % M, j = r % R2, k1 = r / R2;
+                const float2* vr = v + ol * (M + 1) + j;
+                float2 acc = make_float2(0.f, 0.f);
+                int widx = 0;
+                const int wstep = (R2 * k1) % M;
+                for (int q = 0; q < R1; q++) {
+                    acc = __ffma2_rn(make_float2(W[widx].x, W[widx].x), vr[q * R2], acc);
+                    acc = __ffma2_rn(make_float2(-W[widx].y, W[widx].y), make_float2(vr[q * R2].y, vr[q * R2].x), acc);
+                    widx += wstep;
+                    if (widx >= M)
+                        widx -= M;
+                }
+                v2[ol * (M + 1) + k1 * R2 + j] = acc;
+            }
+            __syncthreads();
+            for (int idx = tid; idx < OT * nouts; idx += NT) {
+                const int ol = idx % OT, n = idx / OT;
+                const long long oo = o0 + ol;
+                if (oo < noutput) {
+                    const int c = cmap[n];
+                    const float2* yr = v2 + ol * (M + 1) + (c % R1) * R2;
+                    float2 acc = make_float2(0.f, 0.f);
+                    int widx = 0;
+                    for (int j = 0; j < R2; j++) {
+                        acc = __ffma2_rn(make_float2(W[widx].x, W[widx].x), yr[j], acc);
+                        acc = __ffma2_rn(make_float2(-W[widx].y, W[widx].y), make_float2(yr[j].y, yr[j].x), acc);
+                        widx += c;
+                        if (widx >= M)
+                            widx -= M;
+                    }
+                    out[(long long)n * out_stride + oo] = acc;
+                }
+            }
+            continue;
+        }
         for (int idx = tid; idx < OT * nouts; idx += NT) {
             const int ol = idx % OT, n = idx / OT;
             const long long oo = o0 + ol;
@@ -480,12 +533,17 @@ int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stri
             return launch_fftgen_tp<256>(x, out, out_stride, nouts, cmap, noutput, T, R, h, wM, nsm, st);
         }
     }
-    // generic path
+    // generic path: the DFT in two stages when the channel count has a divisor (the one nearest its square root)
+    int R1 = 1;
+    for (int d = 2; d * d <= M; d++)
+        if (M % d == 0)
+            R1 = d;
     int OT = 32;
-    size_t smem = ((size_t)OT * (M + 1) + M) * 8;
+    const int nbuf = R1 > 1 ? 2 : 1;
+    size_t smem = ((size_t)nbuf * OT * (M + 1) + M) * 8;
     while (smem > 200 * 1024 && OT > 1) {
         OT /= 2;
-        smem = ((size_t)OT * (M + 1) + M) * 8;
+        smem = ((size_t)nbuf * OT * (M + 1) + M) * 8;
     }
     if (smem > 200 * 1024)
         return fail(GRB200_ERANGE, "pfb_channelizer: %d channels exceed the device tile", M);
@@ -496,7 +554,7 @@ int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stri
     if (grid > ntiles)
         grid = ntiles;
     pfb_generic_kernel<<<(unsigned)grid, 256, smem, st>>>((const float2*)x, (float2*)out, out_stride, nouts, cmap,
-                                                          noutput, M, T, R, h, wM, OT);
+                                                          noutput, M, T, R, h, wM, OT, R1);
     GRB_LAUNCH_CHECK();
     return 0;
 }
