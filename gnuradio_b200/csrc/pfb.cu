@@ -28,6 +28,9 @@ bool pfb_stream_supported(int M, int T, int R, const void* x);
 int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
                       const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo);
 int halo_fetch_launch(void* dst, const void* src, size_t bytes, cudaStream_t st);
+bool pfb_stream_os2_supported(int M, int T, int R, const void* x);
+int pfb_stream_os2_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                          const float* h, const float2* wM, int nsm, cudaStream_t st);
 
 // ---- generic kernel: any M, T, rate ratio, channel map -------------------------------------------------
 __global__ void __launch_bounds__(256)
@@ -510,6 +513,8 @@ int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stri
         if (rc)
             return rc;
     }
+    if (allow_fast && identity && pfb_stream_os2_supported(M, T, R, x) && !GRB_GETENV_ONCE("GRB200_PFB_V1"))
+        return pfb_stream_os2_launch(M, T, x, out, out_stride, nouts, noutput, h, wM, nsm, st);
     if (allow_fast && R == M && T <= 32 && (M == 16 || M == 64 || M == 256)) {
         if (M == 16)
             return launch_fast_tp<16>(T, x, out, out_stride, nouts, cmap, identity, noutput, nrows, h, wM, nsm, st);

@@ -38,7 +38,12 @@ struct PfbStreamGeom {
     static_assert(NT % M == 0 && (OT * R2) % NT == 0 && (OT * R1) % NT == 0 && R1 * R2 == M && R2 <= 16, "geometry");
 };
 
-template <int M, int TP, int NT>
+// OS = 2: oversample_rate 2 (R = M/2).  Output time t = 2 m + p uses the samples x[(m - u) M + (p + 1) R - 1 - i] and the
+// rotation q = (i - p R) mod M (pfb.cu's closed form with (t + 2) R = (m + 1) M + p R): the odd times are the plain channelizer
+// on x, the even ones the plain channelizer on x delayed by R samples, and the rotation by M/2 of the odd ones is a factor
+// (-1)^c on channel c.  So half of a CTA's groups walk the stream and half walk it R samples earlier; lanes 0-15 / 16-31 of a
+// warp's channel store hold the even / odd times of the same 32 consecutive output times.
+template <int M, int TP, int NT, int OS>
 __global__ void __launch_bounds__(NT)
 pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long long out_stride, int nouts,
                   long long noutput, int T, long long nrows, const float* __restrict__ h,
@@ -55,9 +60,15 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
     const int tid = threadIdx.x;
     const int bi = tid % M, bg = tid / M;
     const int col = M - 1 - bi;                       // input stream feeding branch bi
-    const long long region = (long long)iters * KT;   // output times per group run
-    const long long cta0 = (long long)blockIdx.x * NG * region;
-    const long long gs = cta0 + (long long)bg * region; // this thread's first output time
+    const long long region = (long long)iters * KT;   // output times (OS = 2: pairs of them) per group run
+    const long long cta0 = (long long)blockIdx.x * (NG / OS) * region;
+    const long long gs = cta0 + (long long)(bg / OS) * region; // this thread's first output time (pair)
+    static_assert(NG % OS == 0, "an oversampled CTA needs both parities");
+    // OS = 2: the groups of even output times read the stream R = M/2 samples earlier; their last pair may lack its odd time
+    const int delay = (OS == 2 && (bg % OS) == 0) ? M / 2 : 0;
+    x -= delay;
+    if (OS == 2)
+        nrows = T + (noutput + 1 - (bg % OS)) / 2;
 
     for (int k = tid; k < M; k += NT)
         wtab[k] = wM[k];
@@ -77,16 +88,19 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
         // the T history rows of a time-sharded segment are the left neighbour's newest rows: with a halo source they are
         // read where they are -- the neighbour GPU's memory, plain loads over NVLink -- instead of being copied in first
         const float2* src = (halo != nullptr && r < T) ? halo : x;
-        ring[(TP - u) % TP] = (r >= 0 && r < nrows) ? src[r * M + col] : make_float2(0.f, 0.f);
+        ring[(TP - u) % TP] = (r >= (delay ? 1 : 0) && r < nrows) ? src[r * M + col] : make_float2(0.f, 0.f);
     }
     ring[0] = make_float2(0.f, 0.f);
     __syncthreads(); // barrier initialised, twiddle table written
 
     // one elected thread streams the input: NG contiguous blocks of KT rows per iteration
     auto issue = [&](int it) {
+        // (the issuing thread belongs to group 0: its x is the EVEN groups' delayed one -- the odd groups add the delay back --
+        // and the row count is taken per parity here, not from its own nrows)
         auto rows_of = [&](int g, long long& r0) {
-            r0 = cta0 + (long long)g * region + (long long)it * KT + T;
-            const long long nv = nrows - r0;
+            r0 = cta0 + (long long)(g / OS) * region + (long long)it * KT + T;
+            const long long nr = OS == 2 ? T + (noutput + 1 - (g % OS)) / 2 : nrows;
+            const long long nv = nr - r0;
             return (unsigned)((nv < 0 ? 0 : (nv > KT ? KT : nv)) * M * 8);
         };
         unsigned total = 0;
@@ -100,7 +114,7 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
         for (int g = 0; g < NG; g++) {
             const unsigned bytes = rows_of(g, r0);
             if (bytes)
-                bulk_g2s(xs + g * KT * M, x + r0 * M, bytes, bar);
+                bulk_g2s(xs + g * KT * M, x + r0 * M + ((OS == 2 && (g % OS)) ? M / 2 : 0), bytes, bar);
         }
     };
     if (tid == 0)
@@ -153,13 +167,16 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
             }
             dft_r<R2, false>(a);
             const int g = o / KT, k = o % KT;
-            const long long t = cta0 + (long long)g * region + (long long)it * KT + k;
+            const long long t = OS * (cta0 + (long long)(g / OS) * region + (long long)it * KT + k) + (g % OS);
             if (t < noutput) {
 #pragma unroll
                 for (int k2 = 0; k2 < R2; k2++) {
                     const int c = k1 + R1 * k2;
+                    float2 y = a[k2];
+                    if (OS == 2 && (g % OS) && (c & 1)) // the rotation by M/2 of the odd output times
+                        y = make_float2(-y.x, -y.y);
                     if (c < nouts)
-                        out[(long long)c * out_stride + t] = a[k2];
+                        out[(long long)c * out_stride + t] = y;
                 }
             }
         }
@@ -179,12 +196,12 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
 }
 
 // ---- host launcher ------------------------------------------------------------------------------------
-template <int M, int TP, int NT>
+template <int M, int TP, int NT, int OS = 1>
 static int launch_stream(const void* x, void* out, long long out_stride, int nouts, long long noutput, int T,
                          long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo)
 {
     using Geo = PfbStreamGeom<M, NT>;
-    auto kern = pfb_stream_kernel<M, TP, NT>;
+    auto kern = pfb_stream_kernel<M, TP, NT, OS>;
     static thread_local bool configured[16] = {};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -197,19 +214,32 @@ static int launch_stream(const void* x, void* out, long long out_stride, int nou
     if (occ < 1)
         occ = 1;
     long long grid = (long long)nsm * occ;
-    const long long need = (noutput + Geo::OT - 1) / Geo::OT;
+    const long long steps = (noutput + OS - 1) / OS; // output times (OS = 2: pairs) ...
+    constexpr int OTS = Geo::OT / OS;                // ... and how many a CTA covers per iteration
+    const long long need = (steps + OTS - 1) / OTS;
     if (grid > need)
         grid = need;
-    long long iters = (noutput + grid * Geo::OT - 1) / (grid * Geo::OT);
+    long long iters = (steps + grid * OTS - 1) / (grid * OTS);
     if (TP > Geo::KT && (iters & 1))
         iters++;
-    grid = (noutput + iters * Geo::OT - 1) / (iters * Geo::OT); // drop CTAs the rounding left without work
+    grid = (steps + iters * OTS - 1) / (iters * OTS); // drop CTAs the rounding left without work
     if (iters > 0x7fffffffLL / Geo::KT)
         return fail(GRB200_ERANGE, "pfb_channelizer: work() call too long for one launch");
     kern<<<(unsigned)grid, NT, Geo::SMEM, st>>>((const float2*)x, (float2*)out, out_stride, nouts, noutput, T, nrows,
                                                  h, wM, (int)iters, (const float2*)halo);
     GRB_LAUNCH_CHECK();
     return 0;
+}
+
+template <int M>
+static int launch_stream_os2(int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                             long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st)
+{
+    if (T <= 8)
+        return launch_stream<M, 8, 256, 2>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, nullptr);
+    if (T <= 16)
+        return launch_stream<M, 16, 256, 2>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, nullptr);
+    return launch_stream<M, 32, 256, 2>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, nullptr);
 }
 
 template <int M, int NT>
@@ -221,6 +251,31 @@ static int launch_stream_tp(int T, const void* x, void* out, long long out_strid
     if (T <= 16)
         return launch_stream<M, 16, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo);
     return launch_stream<M, 32, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo);
+}
+
+// oversample_rate 2 (R = M/2): 8 .. 128 channels (a CTA needs groups of both parities)
+bool pfb_stream_os2_supported(int M, int T, int R, const void* x)
+{
+    return 2 * R == M && T >= 1 && T <= 32 && M >= 8 && M <= 128 && (M & (M - 1)) == 0 && ((uintptr_t)x & 15) == 0;
+}
+
+int pfb_stream_os2_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                          const float* h, const float2* wM, int nsm, cudaStream_t st)
+{
+    if (noutput <= 0)
+        return 0;
+    const long long nrows = T + (noutput + 1) / 2;
+    switch (M) {
+    case 8:
+        return launch_stream_os2<8>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+    case 16:
+        return launch_stream_os2<16>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+    case 32:
+        return launch_stream_os2<32>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+    case 64:
+        return launch_stream_os2<64>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+    }
+    return launch_stream_os2<128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
 }
 
 bool pfb_stream_supported(int M, int T, int R, const void* x)

@@ -62,7 +62,9 @@ def test_pfb_ctor_contract_and_errors(grb):
                                           (64, 64 * 40, 1.0), (32, 512, 2.0), (128, 640, 4.0 / 3.0), (16, 100, 4.0), (8, 64, 8.0),
                                           (256, 256 * 3, 2.0), (32, 32 * 33, 1.0),
                                           # channel counts that are not a power of two: the two-stage DFT of the generic kernel
-                                          (48, 48 * 7, 1.0), (100, 1000, 1.0), (12, 100, 1.5), (20, 200, 2.0), (7, 50, 1.0), (96, 960, 4.0 / 3.0)])
+                                          (48, 48 * 7, 1.0), (100, 1000, 1.0), (12, 100, 1.5), (20, 200, 2.0), (7, 50, 1.0), (96, 960, 4.0 / 3.0),
+                                          # oversample_rate 2 on the streaming kernel (8 .. 128 channels, every ring depth)
+                                          (8, 64, 2.0), (16, 100, 2.0), (128, 1024, 2.0), (32, 32 * 30, 2.0), (64, 64 * 5, 2.0)])
 def test_pfb_against_oracle(grb, orc, M, ntaps, osr):
     rng = np.random.default_rng(M * 1000 + ntaps)
     taps = rng.uniform(-1, 1, ntaps).astype(np.float32)
