@@ -54,10 +54,11 @@ int fftfilt_launch(int L, int parts, const void* in, void* out, long long nout, 
                    const float2* tw, int nsm, cudaStream_t st);
 int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stride, int nouts, const int* cmap,
                int identity, long long noutput, const float* h, const float2* wM, int nsm, bool allow_fast,
-               cudaStream_t st, const void* halo = nullptr);
+               cudaStream_t st, const void* halo = nullptr, const int* inv = nullptr);
 bool pfb_stream_supported(int M, int T, int R, const void* x);
 int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
-                      const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo = nullptr);
+                      const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo = nullptr,
+                      const int* inv = nullptr);
 // pfb_synthesizer_ccf (pfb_synth.cu)
 bool pfb_synth_fast_supported(int M, int T, int twox, const void* x, long long stride, int nin);
 int pfb_synth_fast_launch(int M, int T, const void* x, long long stride, int nin, void* out, long long ntimes, const float* h,

@@ -15,7 +15,8 @@ struct grb200_pfb {
     std::vector<int> cmap;     // d_channel_map
     bool identity = true;
     const void* halo_src = nullptr; // left neighbour's newest T rows (peer memory), see grb200_pfb_chan_set_halo_source
-    DevBuf h, wM, dmap;
+    DevBuf h, wM, dmap, dinv; // dinv: output stream of DFT bin c (-1 = none), when no two outputs share a channel
+    bool invertible = false;
     Stager sg;
     std::mutex mu;
 };
@@ -44,6 +45,18 @@ static int pfb_upload_map(grb200_pfb* p)
             p->identity = false;
     if ((int)p->cmap.size() != p->M)
         p->identity = false;
+    std::vector<int> inv((size_t)p->M, -1);
+    p->invertible = true;
+    for (size_t n = 0; n < p->cmap.size(); n++) {
+        const int c = p->cmap[n];
+        if (c < 0 || c >= p->M || inv[c] != -1)
+            p->invertible = false;
+        else
+            inv[c] = (int)n;
+    }
+    int rc = p->dinv.upload(inv.data(), inv.size() * sizeof(int));
+    if (rc)
+        return rc;
     return p->dmap.upload(p->cmap.data(), p->cmap.size() * sizeof(int));
 }
 
@@ -187,7 +200,7 @@ int grb200_pfb_chan_work_interleaved_dev(grb200_pfb* p, const void* in_dev, void
     cudaStream_t st_ = pick_stream(stream, p->sg);
     return dev_done(pfb_launch(p->M, p->T, p->R, in_dev, out_dev, out_stride, nout_streams, (const int*)p->dmap.p,
                       p->identity ? 1 : 0, noutput, (const float*)p->h.p, (const float2*)p->wM.p,
-                      sm_count(p->device), true, st_, p->halo_src), p->sg, st_);
+                      sm_count(p->device), true, st_, p->halo_src, p->invertible ? (const int*)p->dinv.p : nullptr), p->sg, st_);
 }
 
 // Shared host-staged driver.  `interleaved` selects the input form:
@@ -272,7 +285,7 @@ static int pfb_work_host(grb200_pfb* p, int interleaved, const void* const* in_s
             }
             return pfb_launch(M, T, R, sg.dev[slot][0], sg.dev[slot][1], chunk, nouts, (const int*)p->dmap.p,
                               p->identity ? 1 : 0, n, (const float*)p->h.p, (const float2*)p->wM.p,
-                              sm_count(p->device), true, st);
+                              sm_count(p->device), true, st, nullptr, p->invertible ? (const int*)p->dinv.p : nullptr);
         });
     if (!rc && lag)
         rc = sg.lag_collect(out_streams, nouts, produced);
@@ -324,6 +337,7 @@ void grb200_pfb_chan_destroy(grb200_pfb* p)
     p->h.release();
     p->wM.release();
     p->dmap.release();
+    p->dinv.release();
     delete p;
 }
 

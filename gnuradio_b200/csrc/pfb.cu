@@ -26,11 +26,11 @@ namespace grb {
 
 bool pfb_stream_supported(int M, int T, int R, const void* x);
 int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
-                      const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo);
+                      const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo, const int* inv);
 int halo_fetch_launch(void* dst, const void* src, size_t bytes, cudaStream_t st);
 bool pfb_stream_os2_supported(int M, int T, int R, const void* x);
 int pfb_stream_os2_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
-                          const float* h, const float2* wM, int nsm, cudaStream_t st);
+                          const float* h, const float2* wM, int nsm, cudaStream_t st, const int* inv);
 
 // ---- generic kernel: any M, T, rate ratio, channel map -------------------------------------------------
 __global__ void __launch_bounds__(256)
@@ -500,21 +500,24 @@ static int launch_fast_tp(int T, const void* x, void* out, long long out_stride,
 // wM: e^{+j 2 pi k / M}, k < M.  cmap: device int[nouts].
 int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stride, int nouts, const int* cmap,
                int identity, long long noutput, const float* h, const float2* wM, int nsm, bool allow_fast,
-               cudaStream_t st, const void* halo)
+               cudaStream_t st, const void* halo, const int* inv)
 {
+    // inv: the channel map inverted (output stream of DFT bin c, -1 = none) when no two outputs share a channel, else null
+    const bool mapped_ok = identity || inv != nullptr;
+    const int* use_inv = identity ? nullptr : inv;
     if (noutput <= 0)
         return 0;
     const long long nrows = T + (noutput * R) / M; // history rows + consumed rows
-    if (allow_fast && identity && pfb_stream_supported(M, T, R, x) && !GRB_GETENV_ONCE("GRB200_PFB_V1"))
-        return pfb_stream_launch(M, T, x, out, out_stride, nouts, noutput, h, wM, nsm, st, halo);
+    if (allow_fast && mapped_ok && pfb_stream_supported(M, T, R, x) && !GRB_GETENV_ONCE("GRB200_PFB_V1"))
+        return pfb_stream_launch(M, T, x, out, out_stride, nouts, noutput, h, wM, nsm, st, halo, use_inv);
     if (halo) // the other kernels read their history in place: bring the neighbour's rows over first (T*M items)
     {
         int rc = halo_fetch_launch(const_cast<void*>(x), halo, (size_t)T * M * 8, st);
         if (rc)
             return rc;
     }
-    if (allow_fast && identity && pfb_stream_os2_supported(M, T, R, x) && !GRB_GETENV_ONCE("GRB200_PFB_V1"))
-        return pfb_stream_os2_launch(M, T, x, out, out_stride, nouts, noutput, h, wM, nsm, st);
+    if (allow_fast && mapped_ok && pfb_stream_os2_supported(M, T, R, x) && !GRB_GETENV_ONCE("GRB200_PFB_V1"))
+        return pfb_stream_os2_launch(M, T, x, out, out_stride, nouts, noutput, h, wM, nsm, st, use_inv);
     if (allow_fast && R == M && T <= 32 && (M == 16 || M == 64 || M == 256)) {
         if (M == 16)
             return launch_fast_tp<16>(T, x, out, out_stride, nouts, cmap, identity, noutput, nrows, h, wM, nsm, st);

@@ -34,7 +34,7 @@ struct PfbStreamGeom {
     static constexpr int NI1 = OT * R2 / NT, NI2 = OT * R1 / NT; // DFT items per thread in pass 1 / pass 2
     static constexpr int XS_BYTES = NG * KT * M * 8;
     static constexpr int VB_BYTES = OT * LD * 8;
-    static constexpr int SMEM = XS_BYTES + VB_BYTES + M * 8 + 16;
+    static constexpr int SMEM = XS_BYTES + VB_BYTES + M * 8 + 16 + M * 4;
     static_assert(NT % M == 0 && (OT * R2) % NT == 0 && (OT * R1) % NT == 0 && R1 * R2 == M && R2 <= 16, "geometry");
 };
 
@@ -43,11 +43,12 @@ struct PfbStreamGeom {
 // on x, the even ones the plain channelizer on x delayed by R samples, and the rotation by M/2 of the odd ones is a factor
 // (-1)^c on channel c.  So half of a CTA's groups walk the stream and half walk it R samples earlier; lanes 0-15 / 16-31 of a
 // warp's channel store hold the even / odd times of the same 32 consecutive output times.
-template <int M, int TP, int NT, int OS>
+template <int M, int TP, int NT, int OS, bool MAPPED>
 __global__ void __launch_bounds__(NT)
 pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long long out_stride, int nouts,
                   long long noutput, int T, long long nrows, const float* __restrict__ h,
-                  const float2* __restrict__ wM, int iters, const float2* __restrict__ halo)
+                  const float2* __restrict__ wM, int iters, const float2* __restrict__ halo,
+                  const int* __restrict__ inv /* output stream of DFT bin c (-1: none), or null = identity */)
 {
     using Geo = PfbStreamGeom<M, NT>;
     constexpr int NG = Geo::NG, KT = Geo::KT, OT = Geo::OT, LD = Geo::LD, R1 = Geo::R1, R2 = Geo::R2;
@@ -56,6 +57,7 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
     float2* vbuf = reinterpret_cast<float2*>(smem_raw + Geo::XS_BYTES);   // [OT][LD]
     float2* wtab = vbuf + OT * LD;                                        // [M] e^{+j 2 pi k / M}
     unsigned long long* bar = reinterpret_cast<unsigned long long*>(wtab + M);
+    int* sinv = reinterpret_cast<int*>(bar + 2); // [M] when a channel map is in force
 
     const int tid = threadIdx.x;
     const int bi = tid % M, bg = tid / M;
@@ -72,6 +74,9 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
 
     for (int k = tid; k < M; k += NT)
         wtab[k] = wM[k];
+    if (MAPPED)
+        for (int k = tid; k < M; k += NT)
+            sinv[k] = inv[k];
     if (tid == 0)
         mbar_init(bar, 1);
 
@@ -175,8 +180,9 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
                     float2 y = a[k2];
                     if (OS == 2 && (g % OS) && (c & 1)) // the rotation by M/2 of the odd output times
                         y = make_float2(-y.x, -y.y);
-                    if (c < nouts)
-                        out[(long long)c * out_stride + t] = y;
+                    const int n = MAPPED ? sinv[c] : c; // the channel map, inverted on the host: a scatter here
+                    if (n >= 0 && n < nouts)
+                        out[(long long)n * out_stride + t] = y;
                 }
             }
         }
@@ -198,16 +204,17 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
 // ---- host launcher ------------------------------------------------------------------------------------
 template <int M, int TP, int NT, int OS = 1>
 static int launch_stream(const void* x, void* out, long long out_stride, int nouts, long long noutput, int T,
-                         long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo)
+                         long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo,
+                         const int* inv)
 {
     using Geo = PfbStreamGeom<M, NT>;
-    auto kern = pfb_stream_kernel<M, TP, NT, OS>;
-    static thread_local bool configured[16] = {};
+    auto kern = inv != nullptr ? pfb_stream_kernel<M, TP, NT, OS, true> : pfb_stream_kernel<M, TP, NT, OS, false>;
+    static thread_local bool configured[2][16] = {};
     int dev = 0;
     cudaGetDevice(&dev);
-    if (!configured[dev & 15]) {
+    if (!configured[inv != nullptr][dev & 15]) {
         GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo::SMEM));
-        configured[dev & 15] = true;
+        configured[inv != nullptr][dev & 15] = true;
     }
     int occ = 1;
     GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, Geo::SMEM));
@@ -226,31 +233,33 @@ static int launch_stream(const void* x, void* out, long long out_stride, int nou
     if (iters > 0x7fffffffLL / Geo::KT)
         return fail(GRB200_ERANGE, "pfb_channelizer: work() call too long for one launch");
     kern<<<(unsigned)grid, NT, Geo::SMEM, st>>>((const float2*)x, (float2*)out, out_stride, nouts, noutput, T, nrows,
-                                                 h, wM, (int)iters, (const float2*)halo);
+                                                 h, wM, (int)iters, (const float2*)halo, inv);
     GRB_LAUNCH_CHECK();
     return 0;
 }
 
 template <int M>
 static int launch_stream_os2(int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
-                             long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st)
+                             long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st,
+                             const int* inv)
 {
     if (T <= 8)
-        return launch_stream<M, 8, 256, 2>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, nullptr);
+        return launch_stream<M, 8, 256, 2>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, nullptr, inv);
     if (T <= 16)
-        return launch_stream<M, 16, 256, 2>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, nullptr);
-    return launch_stream<M, 32, 256, 2>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, nullptr);
+        return launch_stream<M, 16, 256, 2>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, nullptr, inv);
+    return launch_stream<M, 32, 256, 2>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, nullptr, inv);
 }
 
 template <int M, int NT>
 static int launch_stream_tp(int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
-                            long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo)
+                            long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo,
+                            const int* inv)
 {
     if (T <= 8)
-        return launch_stream<M, 8, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo);
+        return launch_stream<M, 8, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo, inv);
     if (T <= 16)
-        return launch_stream<M, 16, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo);
-    return launch_stream<M, 32, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo);
+        return launch_stream<M, 16, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo, inv);
+    return launch_stream<M, 32, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo, inv);
 }
 
 // oversample_rate 2 (R = M/2): 8 .. 128 channels (a CTA needs groups of both parities)
@@ -260,22 +269,22 @@ bool pfb_stream_os2_supported(int M, int T, int R, const void* x)
 }
 
 int pfb_stream_os2_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
-                          const float* h, const float2* wM, int nsm, cudaStream_t st)
+                          const float* h, const float2* wM, int nsm, cudaStream_t st, const int* inv)
 {
     if (noutput <= 0)
         return 0;
     const long long nrows = T + (noutput + 1) / 2;
     switch (M) {
     case 8:
-        return launch_stream_os2<8>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+        return launch_stream_os2<8>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, inv);
     case 16:
-        return launch_stream_os2<16>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+        return launch_stream_os2<16>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, inv);
     case 32:
-        return launch_stream_os2<32>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+        return launch_stream_os2<32>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, inv);
     case 64:
-        return launch_stream_os2<64>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+        return launch_stream_os2<64>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, inv);
     }
-    return launch_stream_os2<128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st);
+    return launch_stream_os2<128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, inv);
 }
 
 bool pfb_stream_supported(int M, int T, int R, const void* x)
@@ -285,30 +294,24 @@ bool pfb_stream_supported(int M, int T, int R, const void* x)
 
 // x: interleaved input with T*M history items in front (16-byte aligned); identity channel map.
 int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
-                      const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo)
+                      const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo, const int* inv)
 {
     if (noutput <= 0)
         return 0;
     const long long nrows = T + noutput;
-    static const int nt_small = [] {
-        const char* e = getenv("GRB200_PFB_NT");
-        return (e && atoi(e) == 128) ? 128 : 256;
-    }();
     if (M == 16)
-        return nt_small == 128 ? launch_stream_tp<16, 128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo)
-                               : launch_stream_tp<16, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+        return launch_stream_tp<16, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
     if (M == 64)
-        return nt_small == 128 ? launch_stream_tp<64, 128>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo)
-                               : launch_stream_tp<64, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+        return launch_stream_tp<64, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
     switch (M) {
     case 8:
-        return launch_stream_tp<8, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+        return launch_stream_tp<8, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
     case 32:
-        return launch_stream_tp<32, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+        return launch_stream_tp<32, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
     case 128:
-        return launch_stream_tp<128, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+        return launch_stream_tp<128, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
     }
-    return launch_stream_tp<256, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo);
+    return launch_stream_tp<256, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
 }
 
 } // namespace grb
