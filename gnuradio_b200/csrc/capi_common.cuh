@@ -21,6 +21,7 @@ int fir_upad(int D, int ntaps);
 int rotate_launch(void* y, long long n, double theta, double delta, cudaStream_t st);
 double rotate_advance(double theta, double delta, long long n);
 bool fft_size_is_fast(int N);
+bool fft_size_is_big(int N); // powers of two 32768 .. 262144: four-step over the single-CTA transform
 int fft_direct_max();
 int fft_vcc_launch(int N, bool fwd, const void* in, void* out, long long nvec, const float* window, int shift,
                    int magsq, const float2* tw, int nsm, cudaStream_t st);

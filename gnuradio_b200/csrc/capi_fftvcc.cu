@@ -84,7 +84,7 @@ static int vcc_create(int fft_size, int forward, const float* window, int nwindo
     *out = nullptr;
     if (fft_size <= 0) // fft_complex ctor, gr-fft/lib/fft.cc:161-163 -> std::out_of_range
         return fail(GRB200_ERANGE, "fft_impl_fftw: invalid fft_size");
-    if (!fft_size_is_fast(fft_size) && fft_size > fft_direct_max())
+    if (!fft_size_is_fast(fft_size) && !fft_size_is_big(fft_size) && fft_size > fft_direct_max())
         return fail(GRB200_ERANGE, "fft_vcc: fft_size %d is not supported by the device transform", fft_size);
     if (nwindow < 0)
         return fail(GRB200_EINVAL, "fft_vcc: negative window length");
@@ -275,7 +275,7 @@ int grb200_logpwrfft_create(int complex_input, double sample_rate, int fft_size,
     *out = nullptr;
     if (fft_size <= 0)
         return fail(GRB200_ERANGE, "fft_impl_fftw: invalid fft_size");
-    if (!fft_size_is_fast(fft_size) && fft_size > fft_direct_max())
+    if (!fft_size_is_fast(fft_size) && !fft_size_is_big(fft_size) && fft_size > fft_direct_max())
         return fail(GRB200_ERANGE, "logpwrfft: fft_size %d is not supported by the device transform", fft_size);
     if (nwindow != fft_size || !window)
         return fail(GRB200_EWINDOW, "fft_vcc: window not the same length as fft_size");

@@ -10,6 +10,7 @@
 // magnitude-squared), the figure the HBM roofline is taken against.  Persistent CTAs loop over vectors.
 #include <cstdint>
 #include <cmath>
+#include <type_traits>
 #include <cstdlib>
 #include <mutex>
 #include <utility>
@@ -565,6 +566,170 @@ static int launch_vcc_dir(bool fwd, const VccArgs& a, int nsm, cudaStream_t st)
     return fwd ? launch_vcc<N, true, REAL>(a, nsm, st) : launch_vcc<N, false, REAL>(a, nsm, st);
 }
 
+// ---- powers of two above 16384 (32768 .. 262144): four-step over the single-CTA transform -------------------------------
+// N = R * N2 (R = 8 or 16 columns, N2 = 4096 .. 16384), n = N2 n1 + n2, k = k1 + R k2:
+//     X[k1 + R k2] = sum_n2 W_N2^(n2 k2) * [ W_N^(n2 k1) * sum_n1 x[N2 n1 + n2] W_R^(n1 k1) ]
+// step 1 (big_cols_kernel): thread (vector, n2) loads its R items N2 apart (coalesced over n2; window and input swap here),
+//   radix-R transform in registers, twiddle from the N-entry table, Z[k1][n2] to scratch;   step 2: the batched N2-point
+//   kernel over the R rows of every vector, in place;   step 3 (big_rows_kernel): thread (vector, k2) gathers its R values
+//   and stores R consecutive outputs (+ rotate, + |.|^2 / log).  Three passes over HBM instead of one: ~48 B per sample.
+template <int R, bool FWD, bool REAL>
+__global__ void __launch_bounds__(256)
+big_cols_kernel(const VccArgs a, int N, int N2, long long vbase, long long nb, float2* __restrict__ Z)
+{
+    const long long total = nb * N2;
+    const bool in_swap = (!FWD) && a.shift;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+        const long long vec = e / N2;
+        const int n2 = (int)(e - vec * N2);
+        const long long sv = ((vbase + vec) * a.vstride + a.voff) * N;
+        float2 v[R];
+#pragma unroll
+        for (int n1 = 0; n1 < R; n1++) {
+            int d = n2 + N2 * n1;
+            if (in_swap)
+                d = (d + N / 2) & (N - 1);
+            float2 x = REAL ? make_float2(reinterpret_cast<const float*>(a.in)[sv + d], 0.f)
+                            : reinterpret_cast<const float2*>(a.in)[sv + d];
+            if (a.window != nullptr) {
+                const float w = __ldg(a.window + d);
+                x = __fmul2_rn(x, make_float2(w, w));
+            }
+            v[n1] = x;
+        }
+        dft_r<R, FWD>(v);
+#pragma unroll
+        for (int k1 = 0; k1 < R; k1++) {
+            float2 y = v[k1];
+            if (k1 > 0) {
+                float2 w = __ldg(a.tw + (((long long)n2 * k1) & (N - 1)));
+                if (!FWD)
+                    w.y = -w.y;
+                y = cmul(y, w);
+            }
+            Z[(vec * R + k1) * N2 + n2] = y;
+        }
+    }
+}
+
+template <int R>
+__global__ void __launch_bounds__(256)
+big_rows_kernel(const VccArgs a, int N, int N2, int forward, long long vbase, long long nb, const float2* __restrict__ Y)
+{
+    const long long total = nb * N2;
+    const bool out_rot = forward && a.shift;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+        const long long vec = e / N2;
+        const int k2 = (int)(e - vec * N2);
+#pragma unroll
+        for (int k1 = 0; k1 < R; k1++) {
+            int k = k1 + R * k2;
+            if (out_rot)
+                k = (k + N / 2) & (N - 1);
+            vcc_store(a, vbase + vec, N, k, Y[(vec * R + k1) * N2 + k2]);
+        }
+    }
+}
+
+__global__ void big_roots_kernel(const float2* __restrict__ twN, float2* __restrict__ tw2, int N2, int R)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N2)
+        tw2[i] = twN[(long long)i * R];
+}
+
+bool fft_size_is_big(int N) { return N >= 32768 && N <= 262144 && (N & (N - 1)) == 0; }
+
+int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st);
+
+// scratch of (current device): grow-only, shared by every big transform on the device (calls on different streams serialise
+// on the mutex only while launching; the buffer itself is used in stream order -- one stream at a time per device is assumed,
+// a second stream gets its own buffer)
+struct BigScratch {
+    int dev;
+    cudaStream_t st;
+    float2* p;
+    size_t cap;
+    float2* tw2;
+    int tw2_N;
+};
+
+static int big_launch(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st)
+{
+    static std::mutex mu;
+    static std::vector<BigScratch> pool;
+    int dev = 0;
+    GRB_CUDA(cudaGetDevice(&dev));
+    const int N2 = N <= 65536 ? 4096 : N / 16, R = N / N2;
+    const size_t per_vec = (size_t)N * 8;
+    long long batch = (long long)(((size_t)256 << 20) / per_vec);
+    batch = batch < 1 ? 1 : (batch > a.nvec ? a.nvec : batch);
+    std::lock_guard<std::mutex> lk(mu);
+    BigScratch* sc = nullptr;
+    for (auto& q : pool)
+        if (q.dev == dev && q.st == st)
+            sc = &q;
+    if (!sc) {
+        pool.push_back({ dev, st, nullptr, 0, nullptr, 0 });
+        sc = &pool.back();
+    }
+    if (sc->cap < (size_t)batch * per_vec) {
+        GRB_CUDA(cudaStreamSynchronize(st));
+        if (sc->p)
+            cudaFree(sc->p);
+        sc->p = nullptr;
+        sc->cap = 0;
+        cudaError_t e = cudaMalloc(&sc->p, (size_t)batch * per_vec);
+        if (e != cudaSuccess)
+            return fail(GRB200_ENOMEM, "cudaMalloc(%zu) failed: %s", (size_t)batch * per_vec, cudaGetErrorString(e));
+        sc->cap = (size_t)batch * per_vec;
+    }
+    if (sc->tw2_N != N) { // roots of the N2-point rows: every R-th root of N
+        GRB_CUDA(cudaStreamSynchronize(st));
+        if (sc->tw2)
+            cudaFree(sc->tw2);
+        sc->tw2 = nullptr;
+        GRB_CUDA(cudaMalloc(&sc->tw2, (size_t)N2 * 8));
+        big_roots_kernel<<<(N2 + 255) / 256, 256, 0, st>>>(a.tw, sc->tw2, N2, R);
+        GRB_LAUNCH_CHECK();
+        sc->tw2_N = N;
+    }
+    for (long long vbase = 0; vbase < a.nvec; vbase += batch) {
+        const long long nb = a.nvec - vbase < batch ? a.nvec - vbase : batch;
+        long long grid = (nb * N2 + 255) / 256;
+        if (grid > (long long)nsm * 16)
+            grid = (long long)nsm * 16;
+        auto cols = [&](auto r) -> int {
+            constexpr int Rv = decltype(r)::value;
+            if (fwd) {
+                if (real_in)
+                    big_cols_kernel<Rv, true, true><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, vbase, nb, sc->p);
+                else
+                    big_cols_kernel<Rv, true, false><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, vbase, nb, sc->p);
+            } else {
+                if (real_in)
+                    big_cols_kernel<Rv, false, true><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, vbase, nb, sc->p);
+                else
+                    big_cols_kernel<Rv, false, false><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, vbase, nb, sc->p);
+            }
+            GRB_LAUNCH_CHECK();
+            return 0;
+        };
+        int rc = R == 8 ? cols(std::integral_constant<int, 8>{}) : cols(std::integral_constant<int, 16>{});
+        if (rc)
+            return rc;
+        VccArgs ra{ sc->p, sc->p, nb * R, nullptr, sc->tw2, 0, 0, 1, 0, 0.f, 0.f, nullptr };
+        if ((rc = fft_vcc_launch_ex(N2, fwd, false, ra, nsm, st)))
+            return rc;
+        if (R == 8)
+            big_rows_kernel<8><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, fwd ? 1 : 0, vbase, nb, sc->p);
+        else
+            big_rows_kernel<16><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, fwd ? 1 : 0, vbase, nb, sc->p);
+        GRB_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
 bool fft_size_is_fast(int N) { return N >= 2 && N <= 16384 && (N & (N - 1)) == 0; }
 int fft_direct_max() { return 8192; }
 
@@ -594,8 +759,10 @@ int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, 
         }
     }
 #undef GRB_VCC_CASE
+    if (fft_size_is_big(N))
+        return big_launch(N, fwd, real_in, a, nsm, st);
     if (N > fft_direct_max())
-        return fail(GRB200_ERANGE, "fft_vcc: fft_size %d is not supported (powers of two up to 16384, any size up to %d)",
+        return fail(GRB200_ERANGE, "fft_vcc: fft_size %d is not supported (powers of two up to 262144, any size up to %d)",
                     N, fft_direct_max());
     static const bool use_bluestein = [] {
         const char* e = GRB_GETENV_ONCE("GRB200_FFT_BLUESTEIN"); // 0 = the O(N^2) kernel for every size

@@ -194,6 +194,24 @@ def test_fft_vcc_sizes(grb, orc, N):
             assert_parity(got, po.f64_fft_vcc(N, fwd, w, sh, x), "f64 N=%d f%d s%d" % (N, fwd, sh))
 
 
+@pytest.mark.parametrize("N,nvec", [(32768, 3), (65536, 5), (131072, 2), (262144, 3)])
+def test_fft_vcc_big_sizes_four_step(grb, N, nvec):
+    """Powers of two above the single-CTA transform: columns -> batched rows -> gather (fft_vcc, fused |.|^2, fft_vfc)."""
+    rng = np.random.default_rng(N + nvec)
+    x = crand(rng, N * nvec)
+    w = rng.uniform(0.1, 1, N).astype(np.float32)
+    for fwd in (True, False):
+        for sh in (False, True):
+            got = grb.fft.fft_vcc(N, fwd, w, sh).process(x)
+            assert_parity(got, po.f64_fft_vcc(N, fwd, w, sh, x), "f64 N=%d f%d s%d" % (N, fwd, sh))
+    P = grb.fft.fft_vcc(N, True, w, True).process(x, magsq=True)
+    ref = po.f64_fft_vcc(N, True, w, True, x)
+    assert_parity(P, (ref.real ** 2 + ref.imag ** 2), "fused mag^2 N=%d" % N)
+    xr = rng.uniform(-1, 1, N * nvec).astype(np.float32)
+    got = grb.fft.fft_vfc(N, True, w).process(xr)
+    assert_parity(got, po.f64_fft_vcc(N, True, w, False, xr.astype(np.complex64)), "vfc N=%d" % N)
+
+
 @pytest.mark.parametrize("N", [32, 64, 128, 256, 512, 1024, 2048, 4096, 8192])
 def test_fft_vcc_streaming_kernel(grb, orc, N):
     """>= 64 vectors per work() call take the persistent TMA-prefetch kernel (fft_vcc_stream_kernel);

@@ -37,7 +37,7 @@ if "fir" in what:
         print("fir_%s ntaps=%5d D=%2d  %.3f ms  %6.1f Gsps  %5.0f GB/s  %5.1f TFLOP/s" % ("ccc" if cplx else "ccf", ntaps, D, ms, n / ms / 1e6,
               n / ms / 1e6 * 8 * (1 + 1 / D), n / ms / 1e6 * ntaps / D * (8 if cplx else 4) / 1e3), flush=True)
 if "fft" in what:
-    for N in (16, 64, 256, 512, 1024, 2048, 4096, 8192, 16384, 1000, 1536):
+    for N in (16, 64, 256, 512, 1024, 2048, 4096, 8192, 16384, 32768, 65536, 262144, 1000, 1536):
         nv = n // N
         blk = g.fft.fft_vcc(N, True, np.ones(N, np.float32), False)
         ms = timed(lambda: blk.work_dev(xd.data_ptr(), yd.data_ptr(), nv, ts.cuda_stream))
