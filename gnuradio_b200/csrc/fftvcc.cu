@@ -577,11 +577,11 @@ template <int R, bool FWD, bool REAL>
 __global__ void __launch_bounds__(256)
 big_cols_kernel(const VccArgs a, int N, int N2, long long vbase, long long nb, float2* __restrict__ Z)
 {
-    const long long total = nb * N2;
     const bool in_swap = (!FWD) && a.shift;
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
-        const long long vec = e / N2;
-        const int n2 = (int)(e - vec * N2);
+    const int per = N2 / 256; // blocks of 256 consecutive n2 per vector (N2 is a multiple of 256)
+    for (long long blk = blockIdx.x; blk < nb * per; blk += gridDim.x) {
+        const long long vec = blk / per;
+        const int n2 = (int)(blk - vec * per) * 256 + threadIdx.x;
         const long long sv = ((vbase + vec) * a.vstride + a.voff) * N;
         float2 v[R];
 #pragma unroll
@@ -598,17 +598,16 @@ big_cols_kernel(const VccArgs a, int N, int N2, long long vbase, long long nb, f
             v[n1] = x;
         }
         dft_r<R, FWD>(v);
+        // v[k1] *= W_N^(n2 k1): the powers 1, 2, 4, 8 from the table (coalesced over n2), the rest are products
+        apply_twiddles_l<R>(v, [&](int j) {
+            float2 w = __ldg(a.tw + (((long long)n2 << j) & (N - 1)));
+            if (!FWD)
+                w.y = -w.y;
+            return w;
+        });
 #pragma unroll
-        for (int k1 = 0; k1 < R; k1++) {
-            float2 y = v[k1];
-            if (k1 > 0) {
-                float2 w = __ldg(a.tw + (((long long)n2 * k1) & (N - 1)));
-                if (!FWD)
-                    w.y = -w.y;
-                y = cmul(y, w);
-            }
-            Z[(vec * R + k1) * N2 + n2] = y;
-        }
+        for (int k1 = 0; k1 < R; k1++)
+            Z[(vec * R + k1) * N2 + n2] = v[k1];
     }
 }
 
@@ -616,17 +615,26 @@ template <int R>
 __global__ void __launch_bounds__(256)
 big_rows_kernel(const VccArgs a, int N, int N2, int forward, long long vbase, long long nb, const float2* __restrict__ Y)
 {
-    const long long total = nb * N2;
+    // a block owns 256 consecutive k2 of one vector = 256 R consecutive outputs k = k1 + R k2: gathered (coalesced over k2 for
+    // every k1) into shared memory, rows padded by one, then stored in output order (coalesced over k)
+    __shared__ float2 sh[256 * (R + 1)];
     const bool out_rot = forward && a.shift;
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
-        const long long vec = e / N2;
-        const int k2 = (int)(e - vec * N2);
+    const int per = N2 / 256, t = threadIdx.x;
+    for (long long blk = blockIdx.x; blk < nb * per; blk += gridDim.x) {
+        const long long vec = blk / per;
+        const int k20 = (int)(blk - vec * per) * 256;
+        __syncthreads();
 #pragma unroll
-        for (int k1 = 0; k1 < R; k1++) {
-            int k = k1 + R * k2;
+        for (int k1 = 0; k1 < R; k1++)
+            sh[t * (R + 1) + k1] = Y[(vec * R + k1) * N2 + k20 + t];
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int e = t + 256 * i; // k - R k20
+            int k = R * k20 + e;
             if (out_rot)
                 k = (k + N / 2) & (N - 1);
-            vcc_store(a, vbase + vec, N, k, Y[(vec * R + k1) * N2 + k2]);
+            vcc_store(a, vbase + vec, N, k, sh[(e / R) * (R + 1) + (e % R)]);
         }
     }
 }
