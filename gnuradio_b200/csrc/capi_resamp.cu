@@ -187,19 +187,20 @@ static int resamp_phase_launch(const void* in, void* out, long long nout, unsign
 // iteration).  Summation order = the kernels above (one accumulator, oldest tap first): a stream cut into calls of any
 // length gives the same bits whichever kernel a call takes.
 namespace rstream {
-constexpr int KT = 32, NCW = 8, MAXNS = 4; // groups of L outputs per run and iteration, consumer warps, stages <=
+constexpr int NCW = 8, MAXNS = 4; // consumer warps, stages <=  (KT = groups of L outputs per run and iteration: 32, or 16 when
+                                  // the stages of a long row -- small interpolation, decimation 3 or 4 -- would not fit)
 // row stride: even (16-byte copies) with an odd half -- 4 x odd words: the runs of a warp start in different banks
-__host__ __device__ constexpr int row_items(int D) { return (((KT * D + D + 3) / 2) | 1) * 2; }
+__host__ __device__ constexpr int row_items(int D, int KT) { return (((KT * D + D + 3) / 2) | 1) * 2; }
 }
 
-template <int TP, int D, bool CT>
+template <int TP, int D, bool CT, int KT>
 __global__ void __launch_bounds__(288)
 resamp_stream_kernel(const float2* __restrict__ in /* 16-byte aligned; the stream starts at in[gs] */, float2* __restrict__ out,
                      long long nout, unsigned ctr0, int L, int T, const float* __restrict__ rev, long long nitems, int iters,
                      int gs, int NS)
 {
     using namespace rstream;
-    constexpr int ROW = row_items(D);
+    constexpr int ROW = row_items(D, KT);
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int RW = 32 / L, NG = NCW * RW;
     float2* xs = reinterpret_cast<float2*>(smem_raw); // [NS][NG][ROW]
@@ -318,18 +319,18 @@ resamp_stream_kernel(const float2* __restrict__ in /* 16-byte aligned; the strea
     }
 }
 
-template <int TP, int D, bool CT>
-static int resamp_stream_launch_t(const void* in, void* out, long long nout, unsigned ctr0, int L, int T, const float* rev,
+template <int TP, int D, bool CT, int KT>
+static int resamp_stream_launch_k(const void* in, void* out, long long nout, unsigned ctr0, int L, int T, const float* rev,
                                   int nsm, cudaStream_t st, bool* done)
 {
     using namespace rstream;
     const int NG = NCW * (32 / L);
-    const size_t stage = (size_t)NG * row_items(D) * 8;
+    const size_t stage = (size_t)NG * row_items(D, KT) * 8;
     const int NS = 3 * stage <= 80 * 1024 ? 3 : 2;
     const size_t smem = (size_t)NS * stage + 2 * MAXNS * 8 + 16;
     if (smem > 160 * 1024)
         return 0; // not done: the caller falls back
-    auto kern = resamp_stream_kernel<TP, D, CT>;
+    auto kern = resamp_stream_kernel<TP, D, CT, KT>;
     GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 1;
     GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 288, smem));
@@ -352,6 +353,19 @@ static int resamp_stream_launch_t(const void* in, void* out, long long nout, uns
                                             NS);
     GRB_LAUNCH_CHECK();
     *done = true;
+    return 0;
+}
+
+template <int TP, int D, bool CT>
+static int resamp_stream_launch_t(const void* in, void* out, long long nout, unsigned ctr0, int L, int T, const float* rev,
+                                  int nsm, cudaStream_t st, bool* done)
+{
+    using namespace rstream;
+    const size_t stage32 = (size_t)NCW * (32 / L) * row_items(D, 32) * 8;
+    if (2 * stage32 + 128 <= 160 * 1024 || TP > 16)
+        return resamp_stream_launch_k<TP, D, CT, 32>(in, out, nout, ctr0, L, T, rev, nsm, st, done);
+    if constexpr (TP <= 16)
+        return resamp_stream_launch_k<TP, D, CT, 16>(in, out, nout, ctr0, L, T, rev, nsm, st, done);
     return 0;
 }
 
