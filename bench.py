@@ -590,9 +590,73 @@ class LogPwrFft(Workload):
         return self.name % self.log2n
 
 
+class Resampler(Workload):
+    """rational_resampler_base_ccf 3/2, 16 taps per phase; rates in OUTPUT items."""
+    name = "rational_resampler_base_ccf %d/%d, %d taps per phase, 2^%d output items per GPU (section 8(f) row; output items/s)"
+    block = "rational_resampler_base_ccf"
+    L, D, T = 3, 2, 16
+    log2n, seed = 28, 12
+    kernel = "resamp_stream_kernel"
+
+    def __init__(self, *a, **k):
+        super().__init__(*a, **k)
+        self.alg_bytes = 8.0 * (1 + self.D / self.L)  # per OUTPUT item
+        self.flops = 4.0 * self.T
+
+    def make(self, taps):
+        return self.grb.filter.rational_resampler_base_ccf(self.L, self.D, taps, device=self.device)
+
+    def setup(self):
+        L, D, T = self.L, self.D, self.T
+        self.taps = lowpass(L * T, 0.4 / max(L, D), blackman_harris(L * T)) * L
+        self.blk = self.make(self.taps)
+        self.nout = self.n
+        self.nin = ((self.nout - 1) * D) // L + 1
+        self.d_in = self.rand_c64(self.nin + T, self.seed)
+        self.d_out = self.torch.empty(2 * self.nout, dtype=self.torch.float32, device="cuda")
+        self.samples_per_step = self.nout
+
+    def step(self):
+        self.blk.set_ctr(0)
+        self.blk.work_dev(self.d_in.data_ptr(), self.nin, self.d_out.data_ptr(), self.nout, self.stream)
+
+    def describe(self):
+        return self.name % (self.L, self.D, self.T, self.log2n)
+
+    def parity(self, sc):
+        return sc.rational_resampler(self.fetch_c64(self.d_in), self.fetch_c64(self.d_out), self.L, self.D, self.taps, self.nout,
+                                     seed=self.seed)
+
+    def cpu_setup(self, lay, log2n):
+        rng = np.random.default_rng(self.seed)
+        n = 1 << log2n
+        self.cpu_lay = lay
+        self.cpu_nin = (n * self.D) // self.L
+        self.cpu_x = (rng.uniform(-1, 1, self.cpu_nin + self.T) + 1j * rng.uniform(-1, 1, self.cpu_nin + self.T)).astype(np.complex64)
+        self.cpu_taps = lowpass(self.L * self.T, 0.4 / max(self.L, self.D), blackman_harris(self.L * self.T)) * self.L
+        return n
+
+    def cpu_call(self):
+        self.cpu_lay.rational_resampler(self.L, self.D, self.cpu_taps, self.cpu_x, nin=self.cpu_nin)
+
+
+class Interpolator(Resampler):
+    """interp_fir_filter_ccf x4, 16 taps per phase; rates in OUTPUT items."""
+    name = "interp_fir_filter_ccf x%d (/%d), %d taps per phase, 2^%d output items per GPU (section 8(f) row; output items/s)"
+    block = "interp_fir_filter_ccf"
+    L, D, T = 4, 1, 16
+    seed = 13
+
+    def make(self, taps):
+        return self.grb.filter.interp_fir_filter_ccf(self.L, taps, device=self.device)
+
+    def step(self):
+        self.blk.work_dev(self.d_in.data_ptr(), self.d_out.data_ptr(), self.nout, self.stream)
+
+
 WORKLOADS = {"pfb": PfbChannelizer, "fir": FirCcf, "fftfilt": FftFilter, "firdec": FirLongDecim, "fftvcc": FftVccMagSq,
              "xlat": FreqXlating, "pfbdec": PfbDecimator, "firfff": FirFff, "pfbsynth": PfbSynthesizer, "fbank": Filterbank,
-             "logpwr": LogPwrFft}
+             "logpwr": LogPwrFft, "interp": Interpolator, "resamp": Resampler}
 
 
 # ---------------------------------------------------------------------------------------------------------

@@ -161,6 +161,26 @@ def fft_vcc(fetch_in, fetch_out, fft_size, forward, window, shift, nvec, magsq=F
     return acc.result()
 
 
+def rational_resampler(fetch_in, fetch_out, interpolation, decimation, taps, nout, ctr0=0, width=384, count=64, seed=0, orc=None):
+    """rational_resampler_base general_work() (gr-filter/lib/rational_resampler_base_impl.cc:151-173) in closed form:
+    out[i] = firs[(ctr0 + i D) % L].filter(&in[(ctr0 + i D) / L]); interp_fir_filter is the case D = 1, ctr0 = 0
+    (interp_fir_filter_impl.cc:139-147).  in[] starts at the first window item (no history in front)."""
+    orc = orc or po.best()
+    acc = _Acc(orc.kind)
+    L, D = interpolation, decimation
+    T = -(-len(taps) // L)
+    for o0 in window_starts(nout, width, count, seed):
+        w = min(width, nout - o0)
+        s0, s1 = ctr0 + o0 * D, ctr0 + (o0 + w - 1) * D
+        q0, q1 = s0 // L, s1 // L
+        xin = fetch_in(q0, q1 + T)
+        got = fetch_out(o0, o0 + w)
+        ref, _, _ = orc.rational_resampler(L, D, taps, xin, noutput=w, ctr=s0 % L)
+        f64 = po.f64_rational_resampler(L, D, taps, xin, w, ctr=s0 % L)
+        acc.add(got, ref[:w], f64)
+    return acc.result()
+
+
 def pfb_decimator(fetch_in, fetch_out, decim, taps, channel, nout, width=256, count=32, seed=0, orc=None):
     """pfb_decimator_ccf: fetch_in(s, a, b) -> items [a, b) of input stream s (T-1 history items in front)."""
     orc = orc or po.best()

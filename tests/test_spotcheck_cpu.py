@@ -89,6 +89,23 @@ def test_spotcheck_pfb_decimator(orc):
     assert res["windows"] >= 6 and sc.ok(res), res
 
 
+@pytest.mark.parametrize("L,D,ctr0", [(3, 2, 0), (4, 1, 0), (5, 7, 3)])
+def test_spotcheck_rational_resampler(orc, L, D, ctr0):
+    """The window checker against one whole-stream run of the oracle (a window restarts the phase counter where the
+    stream's closed form puts it); a corrupted output must fail."""
+    rng = np.random.default_rng(L * 10 + D)
+    T, nout = 9, 6000
+    taps = rng.uniform(-1, 1, L * T - 1).astype(np.float32)
+    nin = (ctr0 + (nout - 1) * D) // L + 1
+    x = crand(rng, nin + T - 1)
+    y, _, _ = orc.rational_resampler(L, D, taps, x, noutput=nout, ctr=ctr0)
+    assert len(y) == nout
+    res = sc.rational_resampler(_fetch(x), _fetch(y), L, D, taps, nout, ctr0=ctr0, width=90, count=8, seed=2, orc=orc)
+    assert res["windows"] >= 6 and sc.ok(res), res
+    y[0] += 1e-2
+    assert not sc.ok(sc.rational_resampler(_fetch(x), _fetch(y), L, D, taps, nout, ctr0=ctr0, width=90, count=8, seed=2, orc=orc))
+
+
 def test_window_starts_cover_ends_and_boundaries():
     s = sc.window_starts(1 << 30, 1024, 64, 0)
     assert s[0] == 0 and s[-1] == (1 << 30) - 1024 and len(s) >= 66
