@@ -447,9 +447,11 @@ class FirFff(Workload):
     (gnuradio-runtime/examples/mp-sched/perf-data/*.dat:2, BASELINE.md section 1: 14.2 - 18.4 Msps on 2007-8 CPUs)."""
     name = "fir_filter_fff 256 taps decim 1, 2^%d float samples per GPU (section 8(f) row; mp-sched perf-data shape)"
     block = "fir_filter_fff"
-    alg_bytes, flops, log2n, seed = 8.0, 512.0, 28, 8
-    kernel = "fir_fff_kernel"
-    bound = "fp32"
+    # 256 taps run on the overlap-save kernel (two halves of the call as re / im of one 4096-point complex block, 3841 new
+    # items each): (2 x 5 N log2 N + 6 N) / (2 x 3841) flops per real sample, N = 4096 (the time-domain sum would be 512)
+    alg_bytes, flops, log2n, seed = 8.0, (2 * 5 * 4096 * 12 + 6 * 4096) / (2.0 * 3841), 28, 8
+    kernel = "fftfilt_ols_kernel<4096, RP>"
+    bound = "hbm"
     ntaps = 256
 
     def setup(self):

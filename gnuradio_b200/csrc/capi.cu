@@ -145,6 +145,20 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
         if (rc)
             return rc;
         h->ntaps = ntaps;
+        // long real filters: the overlap-save kernel with the two halves of a call as re / im of one complex stream
+        h->fft_route = false;
+        const int L = fftfilt_realpair_L(ntaps);
+        // (measured, tools/fff_check.py: ~265 G samples/s at any tap count up to 2049 and any decimation; the FIR kernel falls
+        // below that from ~58 taps on, its decimating form much earlier)
+        const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && ntaps > (h->decim == 1 ? 56 : 24));
+        if (want && L > 0) {
+            std::vector<float> tc((size_t)2 * ntaps, 0.f);
+            for (int t = 0; t < ntaps; t++)
+                tc[2 * (size_t)t] = taps[t];
+            if ((rc = fftfilt_plan_build(tc.data(), ntaps, h->device, h->sg.s_exec, h->fH, h->ftw, &h->fL, &h->fK, L)))
+                return rc;
+            h->fft_route = true;
+        }
         return 0;
     }
     // reversed copy (fir_filter.cc:62-64) and its phase-major re-layout g_p[u] = rev[D*u + p]
@@ -183,6 +197,14 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
         h->fft_route = true;
     }
     return 0;
+}
+
+static int fir_fff_run_dev(grb200_fir* h, const void* in_dev, void* out_dev, long long noutput, cudaStream_t st)
+{
+    if (h->fft_route && noutput >= 65536)
+        return fftfilt_realpair_launch(h->fL, in_dev, out_dev, noutput, h->ntaps, h->decim, (const float2*)h->fH.p,
+                                       (const float2*)h->ftw.p, sm_count(h->device), st);
+    return fir_fff_launch(h->decim, h->ntaps, (const float*)h->rev.p, in_dev, out_dev, noutput, sm_count(h->device), st);
 }
 
 // the FIR of one device-resident call: overlap-save when the handle routes there, else the FIR kernels
@@ -285,8 +307,7 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
         if ((rc = halo_fetch_launch(const_cast<void*>(in_dev), halo, (size_t)(h->ntaps - 1) * isz, st)))
             return rc;
     }
-    rc = h->real ? fir_fff_launch(h->decim, h->ntaps, (const float*)h->rev.p, in_dev, out_dev, noutput, sm_count(h->device), st)
-                 : fir_run_dev(h, in_dev, out_dev, noutput, st, halo);
+    rc = h->real ? fir_fff_run_dev(h, in_dev, out_dev, noutput, st) : fir_run_dev(h, in_dev, out_dev, noutput, st, halo);
     if (!rc && h->rot) {
         rc = rotate_launch(out_dev, noutput, h->theta, h->delta, st);
         h->theta = rotate_advance(h->theta, h->delta, noutput);
@@ -355,8 +376,7 @@ static int fir_work_host(grb200_fir* h, const void* in_host, void* out_host, lon
         },
         [&](long long c, int slot, cudaStream_t st) {
             const long long o0 = c * chunk, n = std::min(chunk, noutput - o0);
-            int r2 = h->real ? fir_fff_launch(D, nt, (const float*)h->rev.p, sg.dev[slot][0], sg.dev[slot][1], n,
-                                              sm_count(h->device), st)
+            int r2 = h->real ? fir_fff_run_dev(h, sg.dev[slot][0], sg.dev[slot][1], n, st)
                              : fir_run_dev(h, sg.dev[slot][0], sg.dev[slot][1], n, st, nullptr);
             if (!r2 && h->rot)
                 r2 = rotate_launch(sg.dev[slot][1], n, rotate_advance(h->theta, h->delta, o0), h->delta, st);

@@ -131,7 +131,11 @@ struct DevBuf {
 };
 // capi_fftfilt.cu: device plan + filter spectra of the overlap-save kernels for `ntaps` complex taps
 int fftfilt_plan_build(const float* taps_re_im, int ntaps, int device, cudaStream_t st, DevBuf& H, DevBuf& tw, int* L_io,
-                       int* K_out);
+                       int* K_out, int force_L = 0);
+// fftfilt.cu: fir_filter_fff on the overlap-save kernel (two halves of a real call as re / im of one complex stream)
+int fftfilt_realpair_L(int ntaps);
+int fftfilt_realpair_launch(int L, const void* in, void* out, long long nout, int ntaps, int D, const float2* H,
+                            const float2* tw, int nsm, cudaStream_t st);
 
 
 // forward twiddle table e^{-j 2 pi k / N} (or e^{+...} with sign=+1), evaluated in double

@@ -29,10 +29,10 @@ namespace grb {
 // H_p = FFT_L(taps of partition p / L), scale on the host like fft_filter.cc:184-189, transform on the device.
 // *L_io: the length `tw` currently holds roots for (0 = none); updated.  Returns GRB200_ERANGE when no plan exists.
 int fftfilt_plan_build(const float* taps_re_im, int ntaps, int device, cudaStream_t st, DevBuf& H, DevBuf& tw, int* L_io,
-                       int* K_out)
+                       int* K_out, int force_L)
 {
     int K = 1;
-    const int L = fftfilt_device_plan(ntaps, &K);
+    const int L = force_L > 0 ? force_L : fftfilt_device_plan(ntaps, &K); // (a forced length is a one-partition plan)
     if (L < 0)
         return fail(GRB200_ERANGE, "fft_filter_ccc: %d taps exceed the single-CTA transform (max %d)", ntaps,
                     16384 * 3 / 4 + 1);

@@ -28,10 +28,13 @@ __device__ __forceinline__ void store_decimated(float2* __restrict__ out, long l
         out[qb + q] = v;
 }
 
-template <int L>
+// RP ("real pair", fir_filter_fff with a long filter): `in` / `out` are FLOAT streams.  A real filter acts on the real and the
+// imaginary part of a complex stream independently, so the two halves of the call -- outputs [0, half) and [half, nout) --
+// ride through the transform as re and im of one complex block: two coalesced float loads per item, two float stores.
+template <int L, bool RP>
 __global__ void __launch_bounds__(L / 16)
 fftfilt_ols_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin,
-                   int ntaps, int D, const float2* __restrict__ H, const float2* __restrict__ tw)
+                   int ntaps, int D, const float2* __restrict__ H, const float2* __restrict__ tw, long long half)
 {
     constexpr int E = 16, TPV = L / E;
     constexpr int R0 = fft_first_radix(L, false);
@@ -41,8 +44,11 @@ fftfilt_ols_kernel(const float2* __restrict__ in, float2* __restrict__ out, long
     float2* S = reinterpret_cast<float2*>(smem_raw);
     const int t = threadIdx.x;
     const int V = L - (ntaps - 1);
-    const long long ny = nout * D; // full-rate convolution outputs needed
+    const long long ny = (RP ? half : nout) * D; // full-rate convolution outputs needed (RP: of the longer, first half)
     const long long nblocks = (ny + V - 1) / V;
+    const float* __restrict__ inf = reinterpret_cast<const float*>(in);
+    float* __restrict__ outf = reinterpret_cast<float*>(out);
+    const long long nyB = RP ? (nout - half) * D : 0; // RP: outputs of the second half, whose stream starts half D items in
 
     for (long long blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const long long base = blk * V; // buffer index of the block's first input item
@@ -52,7 +58,12 @@ fftfilt_ols_kernel(const float2* __restrict__ in, float2* __restrict__ out, long
 #pragma unroll
             for (int q = 0; q < R0; q++) {
                 const long long g = base + (t + b * TPV) + q * (L / R0);
-                v[b * R0 + q] = (g < nin) ? in[g] : make_float2(0.f, 0.f);
+                if (RP) {
+                    const long long gb = g + half * D;
+                    v[b * R0 + q] = make_float2(g < nin ? inf[g] : 0.f, gb < nin ? inf[gb] : 0.f);
+                } else {
+                    v[b * R0 + q] = (g < nin) ? in[g] : make_float2(0.f, 0.f);
+                }
             }
         cta_fft<L, true, false>(v, S, t, tw);
 #pragma unroll
@@ -64,7 +75,25 @@ fftfilt_ols_kernel(const float2* __restrict__ in, float2* __restrict__ out, long
             }
         __syncthreads(); // forward transform's last gather is done before the inverse reuses S
         cta_fft<L, false, true>(v, S, t, tw);
-        if (D == 1) {
+        if (RP) {
+            const long long dec_q = base / D;
+            const unsigned dec_r = (unsigned)(base - dec_q * D);
+#pragma unroll
+            for (int b = 0; b < E / RL; b++)
+#pragma unroll
+                for (int q = 0; q < RL; q++) {
+                    const int m = (t + b * TPV) + q * (L / RL);
+                    const long long n = base + m - (ntaps - 1);
+                    if (m >= ntaps - 1 && n < ny) {
+                        const unsigned sdec = dec_r + (unsigned)(m - (ntaps - 1)), qd = sdec / (unsigned)D;
+                        if (sdec == qd * (unsigned)D) {
+                            outf[dec_q + qd] = v[b * RL + q].x;
+                            if (n < nyB)
+                                outf[half + dec_q + qd] = v[b * RL + q].y;
+                        }
+                    }
+                }
+        } else if (D == 1) {
 #pragma unroll
             for (int b = 0; b < E / RL; b++)
 #pragma unroll
@@ -94,7 +123,7 @@ template <int L>
 static int launch_ols(const void* in, void* out, long long nout, long long nin, int ntaps, int D, const float2* H,
                       const float2* tw, int nsm, cudaStream_t st)
 {
-    auto kern = fftfilt_ols_kernel<L>;
+    auto kern = fftfilt_ols_kernel<L, false>;
     constexpr int smem = fft_smem_elems(L) * 8;
     if (smem > 48 * 1024)
         GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -107,9 +136,58 @@ static int launch_ols(const void* in, void* out, long long nout, long long nin, 
     long long grid = (long long)nsm * occ;
     if (grid > nblocks)
         grid = nblocks;
-    kern<<<(unsigned)grid, L / 16, smem, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps, D, H, tw);
+    kern<<<(unsigned)grid, L / 16, smem, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps, D, H, tw, 0);
     GRB_LAUNCH_CHECK();
     return 0;
+}
+
+// fir_filter_fff through the overlap-save kernel: two halves of a real call as one complex stream (see RP above)
+template <int L>
+static int launch_ols_realpair(const void* in, void* out, long long nout, int ntaps, int D, const float2* H, const float2* tw,
+                               int nsm, cudaStream_t st)
+{
+    auto kern = fftfilt_ols_kernel<L, true>;
+    constexpr int smem = fft_smem_elems(L) * 8;
+    if (smem > 48 * 1024)
+        GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, L / 16, smem));
+    if (occ < 1)
+        occ = 1;
+    const long long half = (nout + 1) / 2, nin = nout * D + ntaps - 1; // (floats)
+    const int V = L - (ntaps - 1);
+    long long nblocks = (half * D + V - 1) / V;
+    long long grid = (long long)nsm * occ;
+    if (grid > nblocks)
+        grid = nblocks;
+    kern<<<(unsigned)grid, L / 16, smem, st>>>((const float2*)in, (float2*)out, nout, nin, ntaps, D, H, tw, half);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+// L for a real-pair plan (one partition, at least half of every block is output), or -1
+int fftfilt_realpair_L(int ntaps)
+{
+    for (int L = 4096; L <= 16384; L *= 2)
+        if (ntaps - 1 <= L / 2)
+            return L;
+    return -1;
+}
+
+int fftfilt_realpair_launch(int L, const void* in, void* out, long long nout, int ntaps, int D, const float2* H,
+                            const float2* tw, int nsm, cudaStream_t st)
+{
+    if (nout <= 0)
+        return 0;
+    switch (L) {
+    case 4096:
+        return launch_ols_realpair<4096>(in, out, nout, ntaps, D, H, tw, nsm, st);
+    case 8192:
+        return launch_ols_realpair<8192>(in, out, nout, ntaps, D, H, tw, nsm, st);
+    case 16384:
+        return launch_ols_realpair<16384>(in, out, nout, ntaps, D, H, tw, nsm, st);
+    }
+    return fail(GRB200_ERANGE, "fir_filter_fff: no overlap-save kernel for fft length %d", L);
 }
 
 // ---- streaming variant (L = 4096, 8192) --------------------------------------------------------------

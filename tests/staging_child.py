@@ -43,6 +43,7 @@ N = 1 << 20  # 8 MiB of complex64: 8 chunks at GRB200_CHUNK_MB=1
 
 # fir_filter_ccf (CUDA-core path: bit-reproducible under chunking), ccc with decimation, fff
 os.environ["GRB200_FIR_TC"] = "0"
+os.environ["GRB200_FIR_FFT"] = "0"  # (the overlap-save route of long filters re-blocks per chunk: parity, not bits)
 taps = rng.uniform(-1, 1, 37).astype(np.float32)
 x = put(cr(N + 36))
 y = buf(N, np.complex64)

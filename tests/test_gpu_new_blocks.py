@@ -52,6 +52,28 @@ def test_fir_fff_sweep(grb, orc, ntaps, decim):
     assert_parity(got, f64, "fff f64 %d/%d" % (ntaps, decim))
 
 
+@pytest.mark.parametrize("ntaps,decim,nout", [(97, 1, 200001), (256, 1, 131073), (1000, 3, 70001), (4097, 1, 66000), (8192, 2, 65537),
+                                              (300, 2, 65536)])
+def test_fir_fff_long_filters_on_the_overlap_save_kernel(grb, orc, ntaps, decim, nout):
+    """Long filters (> 56 taps, > 24 when decimating) and >= 65536 outputs: the two halves of the call go through fftfilt_ols_kernel as
+    re / im of one complex stream (odd output counts: the second half is one shorter)."""
+    import torch
+
+    rng = np.random.default_rng(ntaps + decim)
+    x = rng.uniform(-1, 1, nout * decim + ntaps - 1).astype(np.float32)
+    taps = (rng.uniform(-1, 1, ntaps) * (4.0 / ntaps)).astype(np.float32)
+    xd = torch.from_numpy(x).cuda()
+    yd = torch.full((nout + 2,), float("nan"), dtype=torch.float32, device="cuda")
+    blk = grb.filter.fir_filter_fff(decim, taps)
+    blk.work_dev(xd.data_ptr(), yd.data_ptr(), nout, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    y = yd.cpu().numpy()
+    assert np.isnan(y[-2:]).all() and np.isfinite(y[:-2]).all()
+    f64 = np.convolve(x.astype(np.float64), taps.astype(np.float64))[ntaps - 1: ntaps - 1 + nout * decim: decim]
+    assert_parity(y[:-2], f64, "fff f64 %d/%d" % (ntaps, decim))
+    assert_parity(y[:-2], orc.fir_fff(decim, taps, x, nout), "fff oracle %d/%d" % (ntaps, decim))
+
+
 def test_fir_fff_tiles_ragged_ends_and_unaligned(grb, orc):
     """Several tiles per CTA, an odd output count (half a pair at the end), 4-byte aligned input and output pointers."""
     import torch
