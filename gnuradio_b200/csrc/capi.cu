@@ -184,7 +184,7 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
     // at decimation 8)
     h->fft_route = false;
     const bool tc_case = h->tc_pref != 0 && ((D == 1 && ntaps <= 64) || (!h->ct && D == 8 && ntaps <= 1024));
-    const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && !tc_case && ntaps > (h->ct ? 40 : 72) * (long long)D);
+    const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && !tc_case && ntaps > (h->ct ? 40 : (D == 1 ? 64 : 72)) * (long long)D);
     if (want && fftfilt_device_plan(ntaps, nullptr) > 0) {
         std::vector<float> tc((size_t)2 * ntaps, 0.f);
         for (int t = 0; t < ntaps; t++) {
