@@ -8,49 +8,9 @@
 // One kernel per launch does load (+window, +input swap) -> cta_fft -> (+output rotate, +|.|^2) -> store,
 // so a vector crosses HBM exactly once in each direction: 16 B per complex sample (12 B with the fused
 // magnitude-squared), the figure the HBM roofline is taken against.  Persistent CTAs loop over vectors.
-#include <cstdint>
-#include <cmath>
-#include <type_traits>
-#include <cstdlib>
-#include <mutex>
-#include <utility>
-#include <vector>
-#include "fft.cuh"
-#include "tma.cuh"
-#include "capi_common.cuh"
+#include "fftvcc.cuh"
 
 namespace grb {
-
-// What one launch does besides the transform.  in: vectors of N complex64, or N float32 when REAL (fft_vfc_fftw.cc:70-80);
-// output vector j transforms input vector j*vstride + voff (keep_one_in_n in front of the FFT, logpwrfft.py:49-52);
-// mode 0: complex out; 1: |X|^2 (complex_to_mag_squared fused); 2: log_mul * log2(max(|X|^2, FLT_MIN) * log_scale) -- the
-// nlog10_ff at the end of logpwrfft without averaging (nlog10_ff_impl.cc:47-58) -- and the last vector's |X|^2 goes to ystate
-// (the single_pole_iir memory a later set_average(true) continues from).
-
-__device__ __forceinline__ void vcc_store(const VccArgs& a, long long vec, int N, int k, float2 X)
-{
-    if (a.mode == 0) {
-        reinterpret_cast<float2*>(a.out)[vec * N + k] = X;
-    } else {
-        const float p = fmaf(X.x, X.x, X.y * X.y);
-        if (a.mode == 1) {
-            reinterpret_cast<float*>(a.out)[vec * N + k] = p;
-        } else {
-            reinterpret_cast<float*>(a.out)[vec * N + k] = log2f(fmaxf(p, 1.17549435e-38f) * a.log_scale) * a.log_mul;
-            if (vec == a.nvec - 1)
-                a.ystate[k] = p;
-        }
-    }
-}
-
-template <int N>
-struct VccGeom {
-    static constexpr int E = fft_elems(N);
-    static constexpr int TPV = N / E;                        // threads per vector
-    static constexpr int VPC = TPV >= 128 ? 1 : 128 / TPV;   // vectors per CTA
-    static constexpr int NT = TPV * VPC;
-    static constexpr int SMEM = VPC * fft_smem_elems(N) * 8;
-};
 
 template <int N, bool FWD, bool REAL>
 __global__ void __launch_bounds__(VccGeom<N>::NT)
@@ -111,140 +71,6 @@ fft_vcc_kernel(const VccArgs a)
         }
         if (N > E)
             __syncthreads(); // the next iteration's first pass overwrites S
-    }
-}
-
-// ---- streaming variant (32 <= N <= 8192; below 1024 several vectors per CTA share one bulk copy) ----------------------------------------------------------
-// ncu on the kernel above (profiles/r1_fftvcc_ncu.txt): 2 CTAs/SM at 127 registers, long-scoreboard stalls
-// 2.9 per issue -- every vector's loads are exposed, and window + twiddle lookups add 2.7x the input's L1
-// sectors.  Here a persistent CTA keeps ONE TMA bulk copy (its next VPC vectors, contiguous in the stream)
-// in flight while it transforms the current ones: the copy is issued as soon as the first pass has drained
-// the landing buffer, and completes behind passes 2..n and the stores.  The window sits in shared memory,
-// the loop-invariant base twiddles too (cta_fft_tws), so the only global loads left are the bulk copies.
-template <int N>
-struct VccStreamGeom {
-    using G = VccGeom<N>;
-    static constexpr int XIN_BYTES = G::VPC * N * 8;
-    static constexpr int S_BYTES = G::VPC * fft_smem_elems(N) * 8;
-    static constexpr int TW_BYTES = fft_tws_slots(N) * G::TPV * 8;
-    static constexpr int WIN_BYTES = N * 4;
-    static constexpr int SMEM = XIN_BYTES + S_BYTES + TW_BYTES + WIN_BYTES + 16;
-};
-
-// MODE is a template parameter here (straight-line store code: the 16 stores of a thread issue back to back) -- the
-// per-element mode switch of vcc_store() cost the cfg5 kernel 17 % when it was first generalised.
-template <int N, bool FWD, bool REAL, int MODE>
-__global__ void __launch_bounds__(VccGeom<N>::NT)
-fft_vcc_stream_kernel(const VccArgs a)
-{
-    using G = VccGeom<N>;
-    using SG = VccStreamGeom<N>;
-    constexpr int ISZ = REAL ? 4 : 8; // bytes per input item
-    const long long nvec = a.nvec;
-    const float* __restrict__ window = a.window;
-    const float2* __restrict__ tw = a.tw;
-    const int shift = a.shift;
-    constexpr int E = G::E, TPV = G::TPV, VPC = G::VPC;
-    constexpr int R0 = fft_first_radix(N, false);
-    constexpr int RL = fft_last_radix(N, false);
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    float2* XIN = reinterpret_cast<float2*>(smem_raw);
-    float2* Sall = reinterpret_cast<float2*>(smem_raw + SG::XIN_BYTES);
-    float2* TW = reinterpret_cast<float2*>(smem_raw + SG::XIN_BYTES + SG::S_BYTES);
-    float* WIN = reinterpret_cast<float*>(smem_raw + SG::XIN_BYTES + SG::S_BYTES + SG::TW_BYTES);
-    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem_raw + SG::XIN_BYTES + SG::S_BYTES +
-                                                                    SG::TW_BYTES + SG::WIN_BYTES);
-    const int vl = threadIdx.x / TPV;
-    const int t = threadIdx.x % TPV;
-    float2* S = Sall + vl * fft_smem_elems(N);
-    const float2* X = XIN + vl * N;
-    const float* XR = reinterpret_cast<const float*>(XIN) + vl * N;
-    float2* __restrict__ outc = reinterpret_cast<float2*>(a.out);
-    float* __restrict__ outf = reinterpret_cast<float*>(a.out);
-    const float log_mul = a.log_mul, log_scale = a.log_scale;
-    const bool in_swap = (!FWD) && shift;
-    const bool out_rot = FWD && shift;
-    const bool has_win = window != nullptr;
-    const long long vstep = (long long)gridDim.x * VPC;
-
-    auto issue = [&](long long vbase) {
-        long long nv = nvec - vbase;
-        nv = nv > VPC ? VPC : nv;
-        mbar_expect_tx(bar, (unsigned)(nv * N * ISZ));
-        if (a.vstride == 1) { // the CTA's vectors are contiguous in the stream: one copy
-            bulk_g2s(XIN, reinterpret_cast<const char*>(a.in) + (vbase + a.voff) * N * ISZ, (unsigned)(nv * N * ISZ), bar);
-        } else {
-            for (int s = 0; s < (int)nv; s++)
-                bulk_g2s(reinterpret_cast<char*>(XIN) + (size_t)s * N * ISZ,
-                         reinterpret_cast<const char*>(a.in) + ((vbase + s) * a.vstride + a.voff) * N * ISZ, N * ISZ, bar);
-        }
-    };
-
-    if (threadIdx.x == 0)
-        mbar_init(bar, 1);
-    if (vl == 0)
-        cta_fft_tws_init<N, FWD>(TW, t, tw);
-    if (has_win)
-        for (int i = threadIdx.x; i < N; i += G::NT)
-            WIN[i] = window[i];
-    __syncthreads();
-    long long vbase = (long long)blockIdx.x * VPC;
-    if (threadIdx.x == 0 && vbase < nvec)
-        issue(vbase);
-
-    unsigned phase = 0;
-    for (; vbase < nvec; vbase += vstep, phase ^= 1) {
-        const long long vec = vbase + vl;
-        const bool valid = vec < nvec;
-        mbar_wait(bar, phase);
-        float2 v[E];
-#pragma unroll
-        for (int b = 0; b < E / R0; b++) {
-#pragma unroll
-            for (int q = 0; q < R0; q++) {
-                int d = (t + b * TPV) + q * (N / R0);
-                if (in_swap)
-                    d = (d + N / 2) & (N - 1);
-                float2 x = make_float2(0.f, 0.f);
-                if (valid)
-                    x = REAL ? make_float2(XR[d], 0.f) : X[d];
-                if (has_win) {
-                    const float w = WIN[d];
-                    x = __fmul2_rn(x, make_float2(w, w));
-                }
-                v[b * R0 + q] = x;
-            }
-        }
-        const long long vnext = vbase + vstep;
-        cta_fft_tws<N, FWD>(v, S, t, TW, tw, [&]() {
-            if (threadIdx.x == 0 && vnext < nvec)
-                issue(vnext); // every thread has read XIN (barrier after the first pass)
-        });
-        if (valid) {
-#pragma unroll
-            for (int b = 0; b < E / RL; b++) {
-#pragma unroll
-                for (int q = 0; q < RL; q++) {
-                    int k = (t + b * TPV) + q * (N / RL);
-                    if (out_rot)
-                        k = (k + N / 2) & (N - 1);
-                    const float2 Xk = v[b * RL + q];
-                    if constexpr (MODE == 0) {
-                        outc[vec * N + k] = Xk;
-                    } else {
-                        const float pw = fmaf(Xk.x, Xk.x, Xk.y * Xk.y);
-                        if constexpr (MODE == 1) {
-                            outf[vec * N + k] = pw;
-                        } else {
-                            outf[vec * N + k] = log2f(fmaxf(pw, 1.17549435e-38f) * log_scale) * log_mul;
-                            if (vec == nvec - 1)
-                                a.ystate[k] = pw;
-                        }
-                    }
-                }
-            }
-        }
-        __syncthreads(); // the next iteration's first pass overwrites S
     }
 }
 
@@ -314,189 +140,6 @@ magsq_kernel(const float2* __restrict__ in, float* __restrict__ out, long long n
 }
 
 // ---- host dispatch --------------------------------------------------------------------------------
-// ---- sizes that are not a power of two (128 <= N <= 8192): Bluestein over the power-of-two transform ---------------------
-// FFTW takes any size at N log N; the direct kernel above is O(N^2) (1.2 Gsps at N = 1000).  With c[n] = e^{-j pi n^2 / N}:
-//     X[k] = c[k] * sum_n (x[n] c[n]) * conj(c)[k - n]           (n k = (n^2 + k^2 - (k - n)^2) / 2)
-// -- a convolution, done circularly at a power of two L >= 2N - 1 exactly like fftfilt.cu's overlap-save block: load
-// (+ window, + swap) * chirp, zero padded to L -> cta_fft -> * B (the transformed chirp, 1/L folded in) in registers -> inverse
-// with the reversed radix schedule -> * chirp -> the first N values (+ rotate, + |.|^2 / log).  One vector per CTA; the
-// backward transform conjugates both tables (the chirp is even in n).  Tables per (device, N) are built at the first launch.
-template <int L, bool REAL>
-__global__ void __launch_bounds__(L / 16, L <= 8192 ? 8192 / L : 1) // 128 registers: 512 resident threads per SM
-fft_bluestein_kernel(const VccArgs a, int N, int forward, const float2* __restrict__ chirp, const float2* __restrict__ Bhat,
-                     const float2* __restrict__ twL)
-{
-    constexpr int E = 16, TPV = L / 16;
-    constexpr int R0 = fft_first_radix(L, false), RM = fft_last_radix(L, false), RL = fft_last_radix(L, true);
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    float2* S = reinterpret_cast<float2*>(smem_raw);
-    const int t = threadIdx.x;
-    const float* __restrict__ window = a.window;
-    const bool in_swap = (!forward) && a.shift, out_rot = forward && a.shift;
-    const int len_in = N / 2, len_out = (N + 1) / 2; // fft_vcc_fftw.cc:79,93,107
-    for (long long vec = blockIdx.x; vec < a.nvec; vec += gridDim.x) {
-        const long long sv = (vec * a.vstride + a.voff) * N;
-        float2 v[E];
-#pragma unroll
-        for (int b = 0; b < E / R0; b++)
-#pragma unroll
-            for (int q = 0; q < R0; q++) {
-                const int m = (t + b * TPV) + q * (L / R0);
-                float2 x = make_float2(0.f, 0.f);
-                if (m < N) {
-                    int s = m;
-                    if (in_swap) {
-                        s += len_in;
-                        s -= s >= N ? N : 0;
-                    }
-                    x = REAL ? make_float2(reinterpret_cast<const float*>(a.in)[sv + s], 0.f)
-                             : reinterpret_cast<const float2*>(a.in)[sv + s];
-                    if (window != nullptr) {
-                        const float w = __ldg(window + s);
-                        x = __fmul2_rn(x, make_float2(w, w));
-                    }
-                    float2 c = __ldg(chirp + m);
-                    if (!forward)
-                        c.y = -c.y;
-                    x = cmul(x, c);
-                }
-                v[b * R0 + q] = x;
-            }
-        cta_fft<L, true, false>(v, S, t, twL);
-#pragma unroll
-        for (int b = 0; b < E / RM; b++)
-#pragma unroll
-            for (int q = 0; q < RM; q++) {
-                const int k = (t + b * TPV) + q * (L / RM);
-                float2 h = __ldg(Bhat + k);
-                if (!forward)
-                    h.y = -h.y;
-                v[b * RM + q] = cmul(v[b * RM + q], h);
-            }
-        __syncthreads(); // the forward transform's last gather is done before the inverse reuses S
-        cta_fft<L, false, true>(v, S, t, twL);
-#pragma unroll
-        for (int b = 0; b < E / RL; b++)
-#pragma unroll
-            for (int q = 0; q < RL; q++) {
-                const int k = (t + b * TPV) + q * (L / RL);
-                if (k < N) {
-                    float2 c = __ldg(chirp + k);
-                    if (!forward)
-                        c.y = -c.y;
-                    int o = k;
-                    if (out_rot) {
-                        o += N - len_out;
-                        o -= o >= N ? N : 0;
-                    }
-                    vcc_store(a, vec, N, o, cmul(v[b * RL + q], c));
-                }
-            }
-        __syncthreads(); // the next vector's first pass overwrites S
-    }
-}
-
-struct BluesteinPlan {
-    int L = 0;
-    float2 *chirp = nullptr, *Bhat = nullptr, *twL = nullptr;
-};
-
-int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st);
-
-// tables of (current device, N); built on `st` at the first use (the launch that follows is ordered behind them)
-static int bluestein_plan(int N, int nsm, cudaStream_t st, BluesteinPlan* out)
-{
-    static std::mutex mu;
-    static std::vector<std::pair<std::pair<int, int>, BluesteinPlan>> plans;
-    int dev = 0;
-    GRB_CUDA(cudaGetDevice(&dev));
-    std::lock_guard<std::mutex> lk(mu);
-    for (auto& p : plans)
-        if (p.first.first == dev && p.first.second == N) {
-            *out = p.second;
-            return 0;
-        }
-    BluesteinPlan pl;
-    pl.L = 1024;
-    while (pl.L < 2 * N - 1)
-        pl.L *= 2;
-    const int L = pl.L;
-    const double pi = 3.14159265358979323846;
-    std::vector<float2> c((size_t)N), b((size_t)L, make_float2(0.f, 0.f)), roots((size_t)L);
-    for (int n = 0; n < N; n++) {
-        const long long r = ((long long)n * n) % (2LL * N); // n^2 mod 2N: the angle stays small, the table exact to fp32
-        const double ang = pi * (double)r / (double)N;
-        c[n] = make_float2((float)cos(ang), (float)-sin(ang));
-        const float2 bn = make_float2((float)(cos(ang) / L), (float)(sin(ang) / L)); // conj(c) / L
-        b[n] = bn;
-        if (n)
-            b[L - n] = bn;
-    }
-    for (int i = 0; i < L; i++) {
-        const double ang = -2.0 * pi * (double)i / (double)L;
-        roots[i] = make_float2((float)cos(ang), (float)sin(ang));
-    }
-    float2* tmp = nullptr;
-    GRB_CUDA(cudaMalloc(&pl.chirp, (size_t)N * 8));
-    GRB_CUDA(cudaMalloc(&pl.Bhat, (size_t)L * 8));
-    GRB_CUDA(cudaMalloc(&pl.twL, (size_t)L * 8));
-    GRB_CUDA(cudaMalloc(&tmp, (size_t)L * 8));
-    GRB_CUDA(cudaMemcpyAsync(pl.chirp, c.data(), (size_t)N * 8, cudaMemcpyHostToDevice, st));
-    GRB_CUDA(cudaMemcpyAsync(pl.twL, roots.data(), (size_t)L * 8, cudaMemcpyHostToDevice, st));
-    GRB_CUDA(cudaMemcpyAsync(tmp, b.data(), (size_t)L * 8, cudaMemcpyHostToDevice, st));
-    VccArgs fa{ tmp, pl.Bhat, 1, nullptr, pl.twL, 0, 0, 1, 0, 0.f, 0.f, nullptr };
-    int rc = fft_vcc_launch_ex(L, true, false, fa, nsm, st);
-    if (rc)
-        return rc;
-    GRB_CUDA(cudaStreamSynchronize(st)); // the pageable staging vectors and tmp go away
-    cudaFree(tmp);
-    plans.push_back({ { dev, N }, pl });
-    *out = pl;
-    return 0;
-}
-
-template <int L>
-static int launch_bluestein(const BluesteinPlan& pl, int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st)
-{
-    const size_t smem = (size_t)fft_smem_elems(L) * 8;
-    auto go = [&](auto kern) -> int {
-        if (smem > 48 * 1024)
-            GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        int occ = 1;
-        GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, L / 16, smem));
-        if (occ < 1)
-            occ = 1;
-        long long grid = (long long)nsm * occ;
-        if (grid > a.nvec)
-            grid = a.nvec;
-        kern<<<(unsigned)grid, L / 16, smem, st>>>(a, N, fwd ? 1 : 0, pl.chirp, pl.Bhat, pl.twL);
-        GRB_LAUNCH_CHECK();
-        return 0;
-    };
-    return real_in ? go(fft_bluestein_kernel<L, true>) : go(fft_bluestein_kernel<L, false>);
-}
-
-static int bluestein_launch(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st)
-{
-    BluesteinPlan pl;
-    int rc = bluestein_plan(N, nsm, st, &pl);
-    if (rc)
-        return rc;
-    switch (pl.L) {
-    case 1024:
-        return launch_bluestein<1024>(pl, N, fwd, real_in, a, nsm, st);
-    case 2048:
-        return launch_bluestein<2048>(pl, N, fwd, real_in, a, nsm, st);
-    case 4096:
-        return launch_bluestein<4096>(pl, N, fwd, real_in, a, nsm, st);
-    case 8192:
-        return launch_bluestein<8192>(pl, N, fwd, real_in, a, nsm, st);
-    case 16384:
-        return launch_bluestein<16384>(pl, N, fwd, real_in, a, nsm, st);
-    }
-    return fail(GRB200_ERANGE, "fft_vcc: no transform for size %d", N);
-}
-
 template <int N, bool FWD, bool REAL>
 static int launch_vcc(const VccArgs& a, int nsm, cudaStream_t st)
 {
@@ -517,39 +160,6 @@ static int launch_vcc(const VccArgs& a, int nsm, cudaStream_t st)
     return 0;
 }
 
-template <int N, bool FWD, bool REAL, int MODE>
-static int launch_vcc_stream_m(const VccArgs& a, int nsm, cudaStream_t st)
-{
-    using G = VccGeom<N>;
-    using SG = VccStreamGeom<N>;
-    auto kern = fft_vcc_stream_kernel<N, FWD, REAL, MODE>;
-    GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::SMEM));
-    int occ = 1;
-    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, G::NT, SG::SMEM));
-    if (occ < 1)
-        occ = 1;
-    long long need = (a.nvec + G::VPC - 1) / G::VPC;
-    long long grid = (long long)nsm * occ;
-    if (grid > need)
-        grid = need;
-    kern<<<(unsigned)grid, G::NT, SG::SMEM, st>>>(a);
-    GRB_LAUNCH_CHECK();
-    return 0;
-}
-
-template <int N, bool FWD, bool REAL>
-static int launch_vcc_stream(const VccArgs& a, int nsm, cudaStream_t st)
-{
-    if (a.mode == 0)
-        return launch_vcc_stream_m<N, FWD, REAL, 0>(a, nsm, st);
-    if (a.mode == 1)
-        return launch_vcc_stream_m<N, FWD, REAL, 1>(a, nsm, st);
-    if constexpr (FWD) // the log epilogue belongs to logpwrfft: forward transforms only
-        return launch_vcc_stream_m<N, FWD, REAL, 2>(a, nsm, st);
-    else
-        return fail(GRB200_EINVAL, "fft_vcc: the log epilogue needs a forward transform");
-}
-
 template <int N, bool REAL>
 static int launch_vcc_dir(bool fwd, const VccArgs& a, int nsm, cudaStream_t st)
 {
@@ -561,181 +171,9 @@ static int launch_vcc_dir(bool fwd, const VccArgs& a, int nsm, cudaStream_t st)
         // TMA sources must be 16-byte aligned (every vector start is, once the base is); a few vectors are not worth a
         // persistent pipeline
         if (use_stream && (((uintptr_t)a.in) & 15) == 0 && a.nvec >= 64)
-            return fwd ? launch_vcc_stream<N, true, REAL>(a, nsm, st) : launch_vcc_stream<N, false, REAL>(a, nsm, st);
+            return fft_vcc_stream_launch(N, fwd, REAL, a, nsm, st);
     }
     return fwd ? launch_vcc<N, true, REAL>(a, nsm, st) : launch_vcc<N, false, REAL>(a, nsm, st);
-}
-
-// ---- powers of two above 16384 (32768 .. 262144): four-step over the single-CTA transform -------------------------------
-// N = R * N2 (R = 8 or 16 columns, N2 = 4096 .. 16384), n = N2 n1 + n2, k = k1 + R k2:
-//     X[k1 + R k2] = sum_n2 W_N2^(n2 k2) * [ W_N^(n2 k1) * sum_n1 x[N2 n1 + n2] W_R^(n1 k1) ]
-// step 1 (big_cols_kernel): thread (vector, n2) loads its R items N2 apart (coalesced over n2; window and input swap here),
-//   radix-R transform in registers, twiddle from the N-entry table, Z[k1][n2] to scratch;   step 2: the batched N2-point
-//   kernel over the R rows of every vector, in place;   step 3 (big_rows_kernel): thread (vector, k2) gathers its R values
-//   and stores R consecutive outputs (+ rotate, + |.|^2 / log).  Three passes over HBM instead of one: ~48 B per sample.
-template <int R, bool FWD, bool REAL>
-__global__ void __launch_bounds__(256)
-big_cols_kernel(const VccArgs a, int N, int N2, long long vbase, long long nb, float2* __restrict__ Z)
-{
-    const bool in_swap = (!FWD) && a.shift;
-    const int per = N2 / 256; // blocks of 256 consecutive n2 per vector (N2 is a multiple of 256)
-    for (long long blk = blockIdx.x; blk < nb * per; blk += gridDim.x) {
-        const long long vec = blk / per;
-        const int n2 = (int)(blk - vec * per) * 256 + threadIdx.x;
-        const long long sv = ((vbase + vec) * a.vstride + a.voff) * N;
-        float2 v[R];
-#pragma unroll
-        for (int n1 = 0; n1 < R; n1++) {
-            int d = n2 + N2 * n1;
-            if (in_swap)
-                d = (d + N / 2) & (N - 1);
-            float2 x = REAL ? make_float2(reinterpret_cast<const float*>(a.in)[sv + d], 0.f)
-                            : reinterpret_cast<const float2*>(a.in)[sv + d];
-            if (a.window != nullptr) {
-                const float w = __ldg(a.window + d);
-                x = __fmul2_rn(x, make_float2(w, w));
-            }
-            v[n1] = x;
-        }
-        dft_r<R, FWD>(v);
-        // v[k1] *= W_N^(n2 k1): the powers 1, 2, 4, 8 from the table (coalesced over n2), the rest are products
-        apply_twiddles_l<R>(v, [&](int j) {
-            float2 w = __ldg(a.tw + (((long long)n2 << j) & (N - 1)));
-            if (!FWD)
-                w.y = -w.y;
-            return w;
-        });
-#pragma unroll
-        for (int k1 = 0; k1 < R; k1++)
-            Z[(vec * R + k1) * N2 + n2] = v[k1];
-    }
-}
-
-template <int R>
-__global__ void __launch_bounds__(256)
-big_rows_kernel(const VccArgs a, int N, int N2, int forward, long long vbase, long long nb, const float2* __restrict__ Y)
-{
-    // a block owns 256 consecutive k2 of one vector = 256 R consecutive outputs k = k1 + R k2: gathered (coalesced over k2 for
-    // every k1) into shared memory, rows padded by one, then stored in output order (coalesced over k)
-    __shared__ float2 sh[256 * (R + 1)];
-    const bool out_rot = forward && a.shift;
-    const int per = N2 / 256, t = threadIdx.x;
-    for (long long blk = blockIdx.x; blk < nb * per; blk += gridDim.x) {
-        const long long vec = blk / per;
-        const int k20 = (int)(blk - vec * per) * 256;
-        __syncthreads();
-#pragma unroll
-        for (int k1 = 0; k1 < R; k1++)
-            sh[t * (R + 1) + k1] = Y[(vec * R + k1) * N2 + k20 + t];
-        __syncthreads();
-#pragma unroll
-        for (int i = 0; i < R; i++) {
-            const int e = t + 256 * i; // k - R k20
-            int k = R * k20 + e;
-            if (out_rot)
-                k = (k + N / 2) & (N - 1);
-            vcc_store(a, vbase + vec, N, k, sh[(e / R) * (R + 1) + (e % R)]);
-        }
-    }
-}
-
-__global__ void big_roots_kernel(const float2* __restrict__ twN, float2* __restrict__ tw2, int N2, int R)
-{
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < N2)
-        tw2[i] = twN[(long long)i * R];
-}
-
-bool fft_size_is_big(int N) { return N >= 32768 && N <= 262144 && (N & (N - 1)) == 0; }
-
-int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st);
-
-// scratch of (current device): grow-only, shared by every big transform on the device (calls on different streams serialise
-// on the mutex only while launching; the buffer itself is used in stream order -- one stream at a time per device is assumed,
-// a second stream gets its own buffer)
-struct BigScratch {
-    int dev;
-    cudaStream_t st;
-    float2* p;
-    size_t cap;
-    float2* tw2;
-    int tw2_N;
-};
-
-static int big_launch(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st)
-{
-    static std::mutex mu;
-    static std::vector<BigScratch> pool;
-    int dev = 0;
-    GRB_CUDA(cudaGetDevice(&dev));
-    const int N2 = N <= 65536 ? 4096 : N / 16, R = N / N2;
-    const size_t per_vec = (size_t)N * 8;
-    long long batch = (long long)(((size_t)256 << 20) / per_vec);
-    batch = batch < 1 ? 1 : (batch > a.nvec ? a.nvec : batch);
-    std::lock_guard<std::mutex> lk(mu);
-    BigScratch* sc = nullptr;
-    for (auto& q : pool)
-        if (q.dev == dev && q.st == st)
-            sc = &q;
-    if (!sc) {
-        pool.push_back({ dev, st, nullptr, 0, nullptr, 0 });
-        sc = &pool.back();
-    }
-    if (sc->cap < (size_t)batch * per_vec) {
-        GRB_CUDA(cudaStreamSynchronize(st));
-        if (sc->p)
-            cudaFree(sc->p);
-        sc->p = nullptr;
-        sc->cap = 0;
-        cudaError_t e = cudaMalloc(&sc->p, (size_t)batch * per_vec);
-        if (e != cudaSuccess)
-            return fail(GRB200_ENOMEM, "cudaMalloc(%zu) failed: %s", (size_t)batch * per_vec, cudaGetErrorString(e));
-        sc->cap = (size_t)batch * per_vec;
-    }
-    if (sc->tw2_N != N) { // roots of the N2-point rows: every R-th root of N
-        GRB_CUDA(cudaStreamSynchronize(st));
-        if (sc->tw2)
-            cudaFree(sc->tw2);
-        sc->tw2 = nullptr;
-        GRB_CUDA(cudaMalloc(&sc->tw2, (size_t)N2 * 8));
-        big_roots_kernel<<<(N2 + 255) / 256, 256, 0, st>>>(a.tw, sc->tw2, N2, R);
-        GRB_LAUNCH_CHECK();
-        sc->tw2_N = N;
-    }
-    for (long long vbase = 0; vbase < a.nvec; vbase += batch) {
-        const long long nb = a.nvec - vbase < batch ? a.nvec - vbase : batch;
-        long long grid = (nb * N2 + 255) / 256;
-        if (grid > (long long)nsm * 16)
-            grid = (long long)nsm * 16;
-        auto cols = [&](auto r) -> int {
-            constexpr int Rv = decltype(r)::value;
-            if (fwd) {
-                if (real_in)
-                    big_cols_kernel<Rv, true, true><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, vbase, nb, sc->p);
-                else
-                    big_cols_kernel<Rv, true, false><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, vbase, nb, sc->p);
-            } else {
-                if (real_in)
-                    big_cols_kernel<Rv, false, true><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, vbase, nb, sc->p);
-                else
-                    big_cols_kernel<Rv, false, false><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, vbase, nb, sc->p);
-            }
-            GRB_LAUNCH_CHECK();
-            return 0;
-        };
-        int rc = R == 8 ? cols(std::integral_constant<int, 8>{}) : cols(std::integral_constant<int, 16>{});
-        if (rc)
-            return rc;
-        VccArgs ra{ sc->p, sc->p, nb * R, nullptr, sc->tw2, 0, 0, 1, 0, 0.f, 0.f, nullptr };
-        if ((rc = fft_vcc_launch_ex(N2, fwd, false, ra, nsm, st)))
-            return rc;
-        if (R == 8)
-            big_rows_kernel<8><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, fwd ? 1 : 0, vbase, nb, sc->p);
-        else
-            big_rows_kernel<16><<<(unsigned)grid, 256, 0, st>>>(a, N, N2, fwd ? 1 : 0, vbase, nb, sc->p);
-        GRB_LAUNCH_CHECK();
-    }
-    return 0;
 }
 
 bool fft_size_is_fast(int N) { return N >= 2 && N <= 16384 && (N & (N - 1)) == 0; }
@@ -808,3 +246,4 @@ int magsq_launch(const void* in, float* out, long long n, int nsm, cudaStream_t 
 }
 
 } // namespace grb
+
