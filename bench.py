@@ -368,9 +368,11 @@ class FreqXlating(FirCcf):
     """freq_xlating_fir_filter_ccf, 128-tap channel filter, decimate by 8 (not a BASELINE config)."""
     name = "freq_xlating_fir_filter_ccf 128 taps decim 8, 2^%d input samples per GPU x %d set(s) (section 8(f) row)"
     block = "freq_xlating_fir_filter_ccf"
-    alg_bytes, flops, log2n, seed = 8.0 + 8.0 / 8, 128.0, 28, 6  # one read per input item, one write per output item
-    kernel = "fir_tiled_kernel + rotate_kernel"
-    bound = "fp32"  # complex composite taps with decimation run on the CUDA cores
+    # one read per input item, one write per output item; 128 complex composite taps at decimation 8 take the overlap-save
+    # route (4096-point blocks, 3969 new items each: two transforms and the spectrum product per block), then the rotator
+    alg_bytes, flops, log2n, seed = 8.0 + 8.0 / 8, (2 * 5 * 4096 * 12 + 6 * 4096) / 3969.0, 28, 6
+    kernel = "fftfilt_ols3_kernel + rotate_kernel"
+    bound = "fp32"
     ntaps, decim, nsets = 128, 8, 1
 
     def setup(self):
@@ -450,7 +452,7 @@ class FirFff(Workload):
     # 256 taps run on the overlap-save kernel (two halves of the call as re / im of one 4096-point complex block, 3841 new
     # items each): (2 x 5 N log2 N + 6 N) / (2 x 3841) flops per real sample, N = 4096 (the time-domain sum would be 512)
     alg_bytes, flops, log2n, seed = 8.0, (2 * 5 * 4096 * 12 + 6 * 4096) / (2.0 * 3841), 28, 8
-    kernel = "fftfilt_ols_kernel<4096, RP>"
+    kernel = "fftfilt_ols3_kernel<RP>"
     bound = "hbm"
     ntaps = 256
 

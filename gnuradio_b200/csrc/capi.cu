@@ -126,7 +126,7 @@ struct grb200_fir {
     bool real = false; // fir_filter_fff: float stream, float taps (fir_fff.cu)
     int isz() const { return real ? 4 : 8; }
     // Long filters run on the overlap-save kernels of fft_filter (fftfilt.cu) -- same linear convolution, ~3e-7 NRMS from the
-    // time-domain sum: past ~72 real (40 complex) taps per decimation step the CUDA-core FIR is FP32-bound below their rate.
+    // time-domain sum: past ~48 real (16 complex) taps per decimation step the CUDA-core FIR is FP32-bound below their rate.
     int fft_pref = -1; // GRB200_FIR_FFT as it stood when the handle was made: 0 never, 1 whenever a plan exists, unset = auto
     bool fft_route = false;
     DevBuf fH, ftw;
@@ -148,9 +148,9 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
         // long real filters: the overlap-save kernel with the two halves of a call as re / im of one complex stream
         h->fft_route = false;
         const int L = fftfilt_realpair_L(ntaps);
-        // (measured, tools/fff_check.py: ~265 G samples/s at any tap count up to 2049 and any decimation; the FIR kernel falls
-        // below that from ~58 taps on, its decimating form much earlier)
-        const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && ntaps > (h->decim == 1 ? 56 : 24));
+        // (measured, tools/route_check.py: ~470 G samples/s at any tap count up to 2049, ~450 at decimations that divide 256,
+        // ~380 at others; the FIR kernel falls below that past 16 taps, at decimation 2 and 4 past 8)
+        const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && ntaps > (h->decim == 2 || h->decim == 4 ? 8 : 16));
         if (want && L > 0) {
             std::vector<float> tc((size_t)2 * ntaps, 0.f);
             for (int t = 0; t < ntaps; t++)
@@ -180,11 +180,18 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
     if (rc)
         return rc;
     h->ntaps = ntaps;
-    // route to the overlap-save kernels?  (not where a tensor-core mode applies: <= 64 taps at decimation 1, real taps <= 1024
-    // at decimation 8)
+    // route to the overlap-save kernels?  Measured crossovers (tools/route_check.py; the three-group kernel runs at ~245 G
+    // items/s, ~200 at decimations that do not divide 256): complex taps past 16 at decimation 1 -- that includes the
+    // tensor-core FIR of 17..64 complex taps (3 x 4 MMAs per tile: 205 G items/s) unless GRB200_FIR_TC=1 asks for it --, any
+    // complex filter at decimation 2, 4, 8.., past 16 per step at other decimations; real taps past 64 at decimation 1, past 32
+    // per step at decimation 2, 4, .., 48 per step otherwise; never where the real-tap tensor-core modes apply.  (Short filters
+    // take the route on large calls only: fir_run_dev.)
     h->fft_route = false;
-    const bool tc_case = h->tc_pref != 0 && ((D == 1 && ntaps <= 64) || (!h->ct && D == 8 && ntaps <= 1024));
-    const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && !tc_case && ntaps > (h->ct ? 40 : (D == 1 ? 64 : 72)) * (long long)D);
+    const bool tc_real = h->tc_pref != 0 && !h->ct && ((D == 1 && ntaps <= 64) || (D == 8 && ntaps <= 1024));
+    const bool tc_forced = h->tc_pref == 1 && h->ct && D == 1 && ntaps <= 64;
+    const bool p2 = D > 1 && D <= 256 && (D & (D - 1)) == 0;
+    const long long least = h->ct ? (p2 ? 0 : 16LL * D) : (D == 1 ? 64 : (p2 ? 32LL : 48LL) * D);
+    const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && !tc_real && !tc_forced && ntaps > least);
     if (want && fftfilt_device_plan(ntaps, nullptr) > 0) {
         std::vector<float> tc((size_t)2 * ntaps, 0.f);
         for (int t = 0; t < ntaps; t++) {
@@ -210,7 +217,8 @@ static int fir_fff_run_dev(grb200_fir* h, const void* in_dev, void* out_dev, lon
 // the FIR of one device-resident call: overlap-save when the handle routes there, else the FIR kernels
 static int fir_run_dev(grb200_fir* h, const void* in_dev, void* out_dev, long long noutput, cudaStream_t st, const void* halo)
 {
-    if (h->fft_route) {
+    // (a short filter on a scheduler-sized call: the direct kernels start faster than a 768-thread CTA per SM does)
+    if (h->fft_route && (h->fft_pref == 1 || h->ntaps > 64LL * h->decim || noutput * h->decim >= 32768)) {
         if (halo) { // the overlap-save kernels read their history in place: bring the neighbour's items over first
             int rc = halo_fetch_launch(const_cast<void*>(in_dev), halo, (size_t)(h->ntaps - 1) * 8, st);
             if (rc)
@@ -308,7 +316,8 @@ int grb200_fir_work_dev(grb200_fir* h, const void* in_dev, void* out_dev, long l
             return rc;
     }
     rc = h->real ? fir_fff_run_dev(h, in_dev, out_dev, noutput, st) : fir_run_dev(h, in_dev, out_dev, noutput, st, halo);
-    if (!rc && h->rot) {
+    if (!rc && h->rot) { // (a separate pass on purpose: rotating in the overlap-save kernel's stores was measured slower -- a
+        // decimating block keeps one lane in D, and the float64 angle sequence issues for the whole warp: 159 vs 221 G items/s)
         rc = rotate_launch(out_dev, noutput, h->theta, h->delta, st);
         h->theta = rotate_advance(h->theta, h->delta, noutput);
     }

@@ -174,11 +174,20 @@ int fftfilt_realpair_L(int ntaps)
     return -1;
 }
 
+static int ols3_realpair(const void* in, void* out, long long nout, int ntaps, int D, const float2* H, const float2* tw,
+                         int nsm, cudaStream_t st, bool* done); // (three-group kernel, below)
+
 int fftfilt_realpair_launch(int L, const void* in, void* out, long long nout, int ntaps, int D, const float2* H,
                             const float2* tw, int nsm, cudaStream_t st)
 {
     if (nout <= 0)
         return 0;
+    if (L == 4096) {
+        bool done = false;
+        const int rc = ols3_realpair(in, out, nout, ntaps, D, H, tw, nsm, st, &done);
+        if (rc || done)
+            return rc;
+    }
     switch (L) {
     case 4096:
         return launch_ols_realpair<4096>(in, out, nout, ntaps, D, H, tw, nsm, st);
@@ -1007,6 +1016,306 @@ static int launch_upols2(const void* in, void* out, long long nout, long long ni
     return 0;
 }
 
+// ---- plain overlap-save on the same three-group machinery (`fftfilt_ols3_kernel`, L = 4096, up to 2048 taps) ----------
+// The streaming kernel above (256-thread CTAs, generic radix schedule, H from L2) reaches a third of the FP32 peak; the
+// three-group CTA of the two-partition kernel reaches half.  This is that CTA without the delay line: every group owns a run
+// of blocks, block b's L (+2) items arrive by one bulk copy while block b-1 is transformed, H sits in 64 tensor-memory
+// columns shared by the groups.  RP = the real-pair form of fir_filter_fff (see fftfilt_ols_kernel): the two float streams
+// arrive by two bulk copies (16-byte aligned starts: up to three floats early each) and leave as two float stores.
+struct Ols3 {
+    static constexpr int L = 4096, TPV = 256, NG = 3;
+    static constexpr int XROW = L + 4;         // floats per real-pair row; (L + 2) complex items fit in the same bytes
+    static constexpr int XIN_BYTES = XROW * 8;
+    static constexpr int S_BYTES = Upols2::S_BYTES, T1_BYTES = Upols2::T1_BYTES, TW2_BYTES = Upols2::TW2_BYTES;
+    static constexpr int SMEM = NG * (XIN_BYTES + S_BYTES) + T1_BYTES + TW2_BYTES + NG * 8 + 16;
+    static constexpr int TMEM_COLS = 64;
+};
+
+template <bool RP>
+__global__ void __launch_bounds__(768, 1)
+fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int ntaps, int D,
+                    const float2* __restrict__ H, const float2* __restrict__ tw, long long run, int gs, long long half)
+{
+    using G = Ols3;
+    constexpr int L = G::L, TPV = G::TPV, NG = G::NG, XROW = G::XROW;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int grp = threadIdx.x >> 8, t = threadIdx.x & 255, warp = t >> 5, bid = grp + 1;
+    float2* XIN = reinterpret_cast<float2*>(smem_raw + grp * (G::XIN_BYTES + G::S_BYTES));
+    float* XF = reinterpret_cast<float*>(XIN);
+    float2* S = reinterpret_cast<float2*>(smem_raw + grp * (G::XIN_BYTES + G::S_BYTES) + G::XIN_BYTES);
+    float2* T1 = reinterpret_cast<float2*>(smem_raw + NG * (G::XIN_BYTES + G::S_BYTES));
+    float2* TW2 = reinterpret_cast<float2*>(smem_raw + NG * (G::XIN_BYTES + G::S_BYTES) + G::T1_BYTES);
+    unsigned long long* bar0 =
+        reinterpret_cast<unsigned long long*>(smem_raw + NG * (G::XIN_BYTES + G::S_BYTES) + G::T1_BYTES + G::TW2_BYTES);
+    unsigned long long* bar = bar0 + grp;
+    unsigned* tmem_slot = reinterpret_cast<unsigned*>(bar0 + NG);
+    const float* __restrict__ inf = reinterpret_cast<const float*>(in);
+    float* __restrict__ outf = reinterpret_cast<float*>(out);
+    const int nh = ntaps - 1, V = L - nh;
+    const long long ny = (RP ? half : nout) * D;      // full-rate outputs (RP: of the first, longer half)
+    const long long nyB = RP ? (nout - half) * D : 0; // RP: of the second half, whose stream starts hD floats in
+    const long long hD = half * D;
+    const long long nblocks = (ny + V - 1) / V;
+    const long long nin_al = RP ? (nin & ~3LL) : (nin & ~1LL); // what the bulk copies may touch; the rest is read directly
+    const long long b0 = ((long long)blockIdx.x * NG + grp) * run;
+    const long long b1 = (b0 + run < nblocks) ? b0 + run : nblocks;
+
+    auto issue = [&](long long blk) {
+        if constexpr (RP) {
+            const long long a0 = (blk * V) & ~3LL, c0 = (blk * V + hD) & ~3LL;
+            long long na = nin_al - a0, nc = nin_al - c0;
+            na = na < 0 ? 0 : (na > XROW ? XROW : na);
+            nc = nc < 0 ? 0 : (nc > XROW ? XROW : nc);
+            mbar_expect_tx(bar, (unsigned)((na + nc) * 4));
+            if (na)
+                bulk_g2s(XF, inf + a0, (unsigned)(na * 4), bar);
+            if (nc)
+                bulk_g2s(XF + XROW, inf + c0, (unsigned)(nc * 4), bar);
+        } else {
+            const long long e0 = (blk * V + gs) & ~1LL;
+            long long n = nin_al - e0;
+            n = n < 0 ? 0 : (n > L + 2 ? L + 2 : n);
+            mbar_expect_tx(bar, (unsigned)(n * 8));
+            if (n)
+                bulk_g2s(XIN, in + e0, (unsigned)(n * 8), bar);
+        }
+    };
+
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(G::TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (t == 0)
+        mbar_init(bar, 1);
+    if (grp == 0) { // the two twiddle tables of fft4096_3x16
+        const int r = t >> 4, q = t & 15;
+        T1[r * Upols2::T1_STRIDE + q] = tw[(16 * q * r) & (L - 1)];
+        if (q < 2)
+            T1[r * Upols2::T1_STRIDE + 16 + q] = make_float2(0.f, 0.f);
+        TW2[t] = tw[t];
+        TW2[TPV + t] = tw[2 * t];
+        TW2[2 * TPV + t] = tw[4 * t];
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const unsigned tmem = *tmem_slot;
+    const unsigned th0 = tmem + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)((warp >> 2) * 32);
+    if (grp == 0) { // bins k = t + 256 i, i = 0..15: columns 2 i, 2 i + 1 of this thread's lane
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+            float2 a[8];
+#pragma unroll
+            for (int e = 0; e < 8; e++)
+                a[e] = __ldg(H + t + 256 * (8 * c + e));
+            asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, "
+                         "%12, %13, %14, %15, %16};" ::"r"(th0 + c * 16),
+                         "f"(a[0].x), "f"(a[0].y), "f"(a[1].x), "f"(a[1].y), "f"(a[2].x), "f"(a[2].y), "f"(a[3].x),
+                         "f"(a[3].y), "f"(a[4].x), "f"(a[4].y), "f"(a[5].x), "f"(a[5].y), "f"(a[6].x), "f"(a[6].y),
+                         "f"(a[7].x), "f"(a[7].y)
+                         : "memory");
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads(); // H is in place for the other groups
+    asm volatile("tcgen05.fence::after_thread_sync;");
+
+    if (b0 < b1) {
+        if (t == 0)
+            issue(b0);
+        unsigned ph = 0;
+        for (long long blk = b0; blk < b1; blk++) {
+            const long long base = blk * V + gs; // buffer index of the block's first input item
+            mbar_wait(bar, ph);
+            ph ^= 1;
+            float2 v[16];
+            if constexpr (RP) {
+                const float* xa = XF + (int)(base & 3) + t;
+                const float* xc = XF + XROW + (int)((base + hD) & 3) + t;
+                if (base + hD + L <= nin_al) {
+#pragma unroll
+                    for (int q = 0; q < 16; q++)
+                        v[q] = make_float2(xa[256 * q], xc[256 * q]);
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 16; q++) {
+                        const long long ga = base + t + 256 * q, gc = ga + hD;
+                        v[q].x = ga < nin_al ? xa[256 * q] : (ga < nin ? inf[ga] : 0.f);
+                        v[q].y = gc < nin_al ? xc[256 * q] : (gc < nin ? inf[gc] : 0.f);
+                    }
+                }
+            } else {
+                const float2* x = XIN + (int)(base & 1) + t;
+                if (base + L <= nin_al) {
+#pragma unroll
+                    for (int q = 0; q < 16; q++)
+                        v[q] = x[256 * q];
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 16; q++) {
+                        const long long g = base + t + 256 * q;
+                        float2 c = make_float2(0.f, 0.f);
+                        if (g < nin_al)
+                            c = x[256 * q];
+                        else if (g < nin)
+                            c = in[g];
+                        v[q] = c;
+                    }
+                }
+            }
+            fft4096_3x16<true>(v, S, t, bid, T1, TW2, [&]() {
+                if (t == 0 && blk + 1 < b1)
+                    issue(blk + 1); // every thread of the group has read the block's items by now
+            });
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                float2 h[4];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                             : "=f"(h[0].x), "=f"(h[0].y), "=f"(h[1].x), "=f"(h[1].y), "=f"(h[2].x), "=f"(h[2].y),
+                               "=f"(h[3].x), "=f"(h[3].y)
+                             : "r"(th0 + c * 8));
+                asm volatile("tcgen05.wait::ld.sync.aligned;"
+                             : "+f"(h[0].x), "+f"(h[0].y), "+f"(h[1].x), "+f"(h[1].y), "+f"(h[2].x), "+f"(h[2].y),
+                               "+f"(h[3].x), "+f"(h[3].y));
+#pragma unroll
+                for (int e = 0; e < 4; e++)
+                    v[4 * c + e] = cmul(v[4 * c + e], h[e]);
+            }
+            group_sync(bid); // forward transform's last gather is done before the inverse reuses S
+            fft4096_3x16<false>(v, S, t, bid, T1, TW2, []() {});
+            // item m = t + 256 q of the block is output n = blk V + m - nh, for m >= nh
+            const long long n0 = blk * V - nh + t;
+            if constexpr (RP) {
+                if (D == 1 && (blk + 1) * V <= nyB) {
+                    float* oa = outf + n0;
+                    float* oc = oa + half;
+#pragma unroll
+                    for (int q = 0; q < 16; q++)
+                        if (t + 256 * q >= nh) {
+                            oa[256 * q] = v[q].x;
+                            oc[256 * q] = v[q].y;
+                        }
+                } else {
+                    const long long dec_q = (blk * V) / D;
+                    const unsigned dec_r = (unsigned)(blk * V - dec_q * D);
+                    if ((256 % D) == 0 && (blk + 1) * V <= nyB) { // D | 256: a thread's 16 items are kept or dropped together
+                        const int sg = (int)dec_r + t - nh;       // item m is decimated output dec_q + (sg + 256 q) / D
+                        if ((sg & (D - 1)) == 0) {
+                            const int step = 256 / D;
+                            float* oa = outf + dec_q + sg / D;
+                            float* oc = oa + half;
+#pragma unroll
+                            for (int q = 0; q < 16; q++)
+                                if (t + 256 * q >= nh) {
+                                    oa[step * q] = v[q].x;
+                                    oc[step * q] = v[q].y;
+                                }
+                        }
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 16; q++) {
+                            const int m = t + 256 * q;
+                            const long long n = n0 + 256 * q;
+                            if (m >= nh && n < ny) {
+                                const unsigned sdec = dec_r + (unsigned)(m - nh), qd = sdec / (unsigned)D;
+                                if (sdec == qd * (unsigned)D) {
+                                    outf[dec_q + qd] = v[q].x;
+                                    if (n < nyB)
+                                        outf[half + dec_q + qd] = v[q].y;
+                                }
+                            }
+                        }
+                    }
+                }
+            } else {
+                if (D == 1 && (blk + 1) * V <= ny) {
+                    float2* o = out + n0;
+#pragma unroll
+                    for (int q = 0; q < 16; q++)
+                        if (t + 256 * q >= nh)
+                            o[256 * q] = v[q];
+                } else if (D == 1) {
+#pragma unroll
+                    for (int q = 0; q < 16; q++)
+                        if (t + 256 * q >= nh && n0 + 256 * q < ny)
+                            out[n0 + 256 * q] = v[q];
+                } else {
+                    const long long dec_q = (blk * V) / D;
+                    const unsigned dec_r = (unsigned)(blk * V - dec_q * D);
+                    if ((256 % D) == 0 && (blk + 1) * V <= ny) { // D | 256: a thread's 16 items are kept or dropped together
+                        const int sg = (int)dec_r + t - nh;      // item m is decimated output dec_q + (sg + 256 q) / D
+                        if ((sg & (D - 1)) == 0) {
+                            const int step = 256 / D;
+                            float2* o = out + dec_q + sg / D;
+#pragma unroll
+                            for (int q = 0; q < 16; q++)
+                                if (t + 256 * q >= nh)
+                                    o[step * q] = v[q];
+                        }
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 16; q++) {
+                            const int m = t + 256 * q;
+                            if (m >= nh && n0 + 256 * q < ny)
+                                store_decimated(out, dec_q, dec_r, (unsigned)D, (unsigned)(m - nh), v[q]);
+                        }
+                    }
+                }
+            }
+            group_sync(bid); // the inverse transform's last gather is done before the next block's first scatter
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    if (threadIdx.x < 32)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(G::TMEM_COLS));
+}
+
+static bool ols3_enabled()
+{
+    static const bool on = [] {
+        const char* e = GRB_GETENV_ONCE("GRB200_FFTFILT_OLS3"); // 0 = the 256-thread kernels
+        return !(e && e[0] == '0');
+    }();
+    return on;
+}
+
+// RP: `nout` real outputs, `half` as in launch_ols_realpair; otherwise complex items.
+template <bool RP>
+static int launch_ols3(const void* in, void* out, long long nout, long long nin, int ntaps, int D, const float2* H,
+                       const float2* tw, int nsm, cudaStream_t st)
+{
+    using G = Ols3;
+    auto kern = fftfilt_ols3_kernel<RP>;
+    GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
+    const long long half = RP ? (nout + 1) / 2 : 0;
+    const int V = G::L - (ntaps - 1);
+    const long long nblocks = ((RP ? half : nout) * D + V - 1) / V;
+    long long groups = (long long)nsm * G::NG; // one CTA per SM, NG independent block runs each
+    if (groups > nblocks)
+        groups = nblocks;
+    const long long run = (nblocks + groups - 1) / groups;
+    groups = (nblocks + run - 1) / run;
+    const long long grid = (groups + G::NG - 1) / G::NG;
+    const int gs = RP ? 0 : (int)((((uintptr_t)in) >> 3) & 1);
+    kern<<<(unsigned)grid, G::NG * G::TPV, G::SMEM, st>>>((const float2*)in - gs, (float2*)out, nout, nin + gs, ntaps, D, H, tw,
+                                                          run, gs, half);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+static int ols3_realpair(const void* in, void* out, long long nout, int ntaps, int D, const float2* H, const float2* tw,
+                         int nsm, cudaStream_t st, bool* done)
+{
+    *done = false;
+    if (!ols3_enabled() || (((uintptr_t)in) & 15) != 0) // the bulk copies start on 16-byte boundaries of the float stream
+        return 0;
+    *done = true;
+    return launch_ols3<true>(in, out, nout, nout * D + ntaps - 1, ntaps, D, H, tw, nsm, st);
+}
+
 // Device plan for a tap count: FFT length L (at least the reference's 2*2^ceil(log2 ntaps), never below 4096) and
 // the number of tap partitions K (1 = plain overlap-save with hop L-ntaps+1, 2 = partitioned with hop L/2).  Runs at
 // create / set_taps time only (the developer knobs below are never read per work()).
@@ -1022,8 +1331,8 @@ int fftfilt_device_plan(int ntaps, int* parts)
     // 2050..10240 taps: K = ceil(ntaps / 2048) partitions on the 4096-point kernel (K-1 <= 4 parked spectra fit in the
     // 512 TMEM columns of an SM at two CTAs) beat the 16384-point transform; below 2050 plain overlap-save is faster.
     const int kneed = (ntaps + 2047) / 2048;
-    if (upols != 0 && (L == 16384 || ntaps >= 1400) && kneed <= 5) { // (measured: plain overlap-save 129 Gsps at 1400 taps and
-        L = 4096;                                                      // falling, the two-partition kernel 129 at any count)
+    if (upols != 0 && (L == 16384 || ntaps > 2048) && kneed <= 5) { // (measured: plain overlap-save on the three-group kernel 137
+        L = 4096;                                                     // Gsps at 2048 taps, the two-partition kernel 130 at any count)
         K = kneed < 2 ? 2 : kneed;
     } else if (upols == 1 && ntaps > 1025 && kneed <= 5) {
         L = 4096;
@@ -1075,6 +1384,8 @@ int fftfilt_launch(int L, int parts, const void* in, void* out, long long nout, 
         const char* e = GRB_GETENV_ONCE("GRB200_FFTFILT_STREAM");
         return !(e && e[0] == '0');
     }();
+    if (L == 4096 && ols3_enabled() && (((uintptr_t)in) & 7) == 0)
+        return launch_ols3<false>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
     if (use_stream && (((uintptr_t)in) & 15) == 0) { // TMA bulk copies need a 16-byte aligned stream
         if (L == 4096)
             return launch_ols_stream<4096>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);

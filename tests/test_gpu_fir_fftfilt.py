@@ -392,6 +392,49 @@ def test_fft_filter_partitioned_device_resident_unaligned(grb):
     assert_parity(a, ref, "f64")
 
 
+@pytest.mark.parametrize("ntaps,decim,shift", [(31, 1, 0), (128, 1, 1), (1025, 1, 0), (2048, 1, 1), (2047, 1, 0), (600, 2, 0),
+                                               (333, 3, 1), (100, 4, 1), (512, 8, 0), (77, 16, 0), (1, 1, 1), (2, 2, 0)])
+def test_fft_filter_three_group_kernel(grb, ntaps, decim, shift):
+    """fftfilt_ols3_kernel (plain overlap-save, up to 2048 taps): device resident, many blocks per group and a ragged last one,
+    16- and 8-byte aligned input, decimations that divide 256 (kept-or-dropped per thread) and that do not; nothing is written
+    past the last output."""
+    import scipy.signal
+    import torch
+
+    rng = np.random.default_rng(5 * ntaps + decim)
+    nout = ((1 << 21) + 777) // decim
+    x = crand(rng, nout * decim + ntaps - 1 + shift)
+    taps = crand(rng, ntaps) * np.float32(4.0 / max(ntaps, 4))
+    xd = torch.from_numpy(x.view(np.float32)).cuda()
+    yd = torch.full((2 * (nout + 2),), float("nan"), dtype=torch.float32, device="cuda")
+    blk = grb.filter.fft_filter_ccc(decim, taps)
+    blk.work_dev(xd.data_ptr() + 8 * shift, yd.data_ptr(), nout, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    y = yd.cpu().numpy()
+    assert np.isnan(y[-4:]).all() and np.isfinite(y[:-4]).all()
+    ref = scipy.signal.fftconvolve(x[shift:].astype(np.complex128), taps.astype(np.complex128))[ntaps - 1: ntaps - 1 + nout * decim: decim]
+    assert_parity(y[:-4].view(np.complex64), ref, "f64 %d/%d" % (ntaps, decim))
+
+
+@pytest.mark.parametrize("kind,ntaps,decim", [("ccf", 100, 1), ("ccf", 128, 2), ("ccf", 256, 4), ("ccc", 24, 1), ("ccc", 64, 1),
+                                              ("ccc", 48, 2), ("ccc", 100, 4), ("ccc", 200, 8)])
+@pytest.mark.parametrize("route", ["0", None])
+def test_fir_direct_kernels_and_the_overlap_save_route_agree(grb, orc, monkeypatch, kind, ntaps, decim, route):
+    """Tap counts the handle sends to the overlap-save kernels on its own (past 16 complex / 48..64 real taps per decimation
+    step): the direct FIR kernels (GRB200_FIR_FFT=0, read when the handle is made) and the routed call both meet the oracle."""
+    if route is None:
+        monkeypatch.delenv("GRB200_FIR_FFT", raising=False)
+    else:
+        monkeypatch.setenv("GRB200_FIR_FFT", route)
+    rng = np.random.default_rng(ntaps * 3 + decim)
+    x = crand(rng, 150000 + 7)
+    taps = crand(rng, ntaps) if kind == "ccc" else rng.uniform(-1, 1, ntaps).astype(np.float32)
+    cls = grb.filter.fir_filter_ccc if kind == "ccc" else grb.filter.fir_filter_ccf
+    got = sched_mock.run_sync(cls(decim, taps), x, max_noutput=1 << 20)
+    assert_parity(got, orc.fir_stream(decim, taps, x), "%s %d/%d oracle" % (kind, ntaps, decim))
+    assert_parity(got, po.f64_fir(decim, taps, x), "%s %d/%d f64" % (kind, ntaps, decim))
+
+
 def test_fft_filter_state_across_calls_and_set_taps(grb, orc):
     rng = np.random.default_rng(8)
     x, taps = crand(rng, 20000), crand(rng, 100)

@@ -110,6 +110,43 @@ def test_freq_xlating_long_run_device_resident(grb, cplx):
     assert_parity(got, po.f64_freq_xlating_fir(1, taps, fc, fs, data), "2^22 device-resident vs f64")
 
 
+@pytest.mark.parametrize("ntaps,decim", [(128, 8), (40, 4), (100, 3), (33, 1), (2000, 16)])
+def test_freq_xlating_on_the_overlap_save_route(grb, monkeypatch, ntaps, decim):
+    """Composite taps past the FIR kernels' crossover run on the overlap-save kernels (every store form of fftfilt_ols3_kernel:
+    full-rate, decimation dividing 256, any other decimation, the ragged last block; 2000 taps: the same), rotate_kernel
+    behind them; the same calls on the direct kernels (GRB200_FIR_FFT=0) and float64 agree, across two uneven device-resident
+    calls."""
+    import torch
+
+    rng = np.random.default_rng(ntaps + decim)
+    nout = ((1 << 21) + 12345) // decim
+    data = crand(rng, nout * decim)
+    x = np.concatenate([np.zeros(ntaps - 1, np.complex64), data])
+    taps = (rng.uniform(-1, 1, ntaps) * (4.0 / ntaps)).astype(np.float32)
+    fc, fs = 0.0731, 1.0
+    xd = torch.from_numpy(x.view(np.float32)).cuda()
+    st = torch.cuda.current_stream().cuda_stream
+    res = []
+    for route in (None, "0"):
+        if route is None:
+            monkeypatch.delenv("GRB200_FIR_FFT", raising=False)
+        else:
+            monkeypatch.setenv("GRB200_FIR_FFT", route)
+        blk = grb.filter.freq_xlating_fir_filter_ccf(decim, taps, fc, fs)
+        yd = torch.full((2 * (nout + 1),), float("nan"), dtype=torch.float32, device="cuda")
+        cut = 70001
+        blk.work_dev(xd.data_ptr(), yd.data_ptr(), cut, st)
+        blk.work_dev(xd.data_ptr() + 8 * cut * decim, yd.data_ptr() + 8 * cut, nout - cut, st)
+        torch.cuda.synchronize()
+        y = yd.cpu().numpy()
+        assert np.isnan(y[-2:]).all() and np.isfinite(y[:-2]).all()
+        res.append(y[:-2].view(np.complex64))
+    ref = po.f64_freq_xlating_fir(decim, taps, fc, fs, data)
+    assert_parity(res[0], ref, "overlap-save route vs f64", 2e-6, 2e-5)
+    assert_parity(res[1], ref, "direct kernels vs f64", 2e-6, 2e-5)
+    assert_parity(res[0], res[1], "one against the other", 2e-6, 2e-5)
+
+
 def test_freq_xlating_host_chunking_is_invisible(grb):
     """The host-staged path cuts a large work() into pipeline chunks; the rotator angle of each chunk comes from the
     closed form, so one big call equals many scheduler-sized ones bit for bit on the CUDA-core FIR."""

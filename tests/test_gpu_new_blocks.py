@@ -52,20 +52,25 @@ def test_fir_fff_sweep(grb, orc, ntaps, decim):
     assert_parity(got, f64, "fff f64 %d/%d" % (ntaps, decim))
 
 
-@pytest.mark.parametrize("ntaps,decim,nout", [(97, 1, 200001), (256, 1, 131073), (1000, 3, 70001), (4097, 1, 66000), (8192, 2, 65537),
-                                              (300, 2, 65536)])
-def test_fir_fff_long_filters_on_the_overlap_save_kernel(grb, orc, ntaps, decim, nout):
-    """Long filters (> 56 taps, > 24 when decimating) and >= 65536 outputs: the two halves of the call go through fftfilt_ols_kernel as
-    re / im of one complex stream (odd output counts: the second half is one shorter)."""
+@pytest.mark.parametrize("ntaps,decim,nout,shift", [(97, 1, 200001, 0), (256, 1, 131073, 0), (1000, 3, 70001, 0), (4097, 1, 66000, 0),
+                                                    (8192, 2, 65537, 0), (300, 2, 65536, 0), (17, 1, 1 << 21, 0), (24, 4, 300001, 0),
+                                                    (2049, 1, 400003, 0), (9, 2, 500002, 0), (64, 8, 100000, 0), (130, 1, 300000, 1),
+                                                    (130, 5, 99999, 2), (40, 1, 65536, 3)])
+def test_fir_fff_long_filters_on_the_overlap_save_kernel(grb, orc, ntaps, decim, nout, shift):
+    """More than 16 taps (8 at decimation 2) and >= 65536 outputs: the two halves of the call go through the overlap-save kernels
+    as re / im of one complex stream (odd output counts: the second half is one shorter) -- fftfilt_ols3_kernel<RP> up to 2049
+    taps when the float stream is 16-byte aligned (two bulk copies per block, each up to three floats early), else
+    fftfilt_ols_kernel<L, RP>."""
     import torch
 
     rng = np.random.default_rng(ntaps + decim)
-    x = rng.uniform(-1, 1, nout * decim + ntaps - 1).astype(np.float32)
+    x = rng.uniform(-1, 1, nout * decim + ntaps - 1 + shift).astype(np.float32)
     taps = (rng.uniform(-1, 1, ntaps) * (4.0 / ntaps)).astype(np.float32)
     xd = torch.from_numpy(x).cuda()
+    x = x[shift:]
     yd = torch.full((nout + 2,), float("nan"), dtype=torch.float32, device="cuda")
     blk = grb.filter.fir_filter_fff(decim, taps)
-    blk.work_dev(xd.data_ptr(), yd.data_ptr(), nout, torch.cuda.current_stream().cuda_stream)
+    blk.work_dev(xd.data_ptr() + 4 * shift, yd.data_ptr(), nout, torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
     y = yd.cpu().numpy()
     assert np.isnan(y[-2:]).all() and np.isfinite(y[:-2]).all()
