@@ -576,8 +576,8 @@ class LogPwrFft(Workload):
     name = "logpwrfft_c 4096 Blackman-Harris, decimation 1, avg_alpha 0.1, 2^%d samples per GPU (section 8(f) row)"
     block = "logpwrfft_c"
     alg_bytes, flops, log2n, seed = 12.0, 70.0, 28, 11
-    kernel = "fft_vcc_stream_kernel + logpwr_local/carry/fixup"
-    launches_per_step = 4
+    kernel = "fft_vcc_stream_kernel<mode 3: run-local IIR> + logpwr_carry/fixup"
+    launches_per_step = 3
     N = 4096
 
     def setup(self):

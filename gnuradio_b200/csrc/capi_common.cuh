@@ -37,6 +37,11 @@ struct VccArgs {
     long long vstride, voff;
     float log_mul, log_scale;
     float* ystate;
+    // mode 3 (streaming kernel only, fft_vcc_stream_iir_launch): |X|^2 through the single-pole IIR along the frames, CTA r
+    // filtering its run of run_len consecutive frames from a zero state and leaving the run's last value in agg[r][bin]
+    double alpha = 0.0;
+    float* agg = nullptr;
+    long long run_len = 0;
 };
 int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st);
 // logpwr.cu: single_pole_iir along the frames + nlog10, in place on p [nframes][N]
@@ -44,6 +49,13 @@ int fft_vcc_launch_ex(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, 
 int resamp_stream_try(bool ct, const void* in, void* out, long long nout, unsigned ctr0, unsigned L, unsigned D, int T,
                       const float* rev_tap_major, int nsm, cudaStream_t st, bool* done);
 long long logpwr_scratch_floats(long long nframes, int N, int nsm);
+// the FFT kernel with the run-local IIR in its epilogue (sizes whose vectors take a CTA each: 2048, 4096, 8192); *done = false
+// when the call does not fit (then nothing was launched).  agg: *nruns x N floats, at most logpwr_fused_scratch_floats().
+int fft_vcc_stream_iir_launch(int N, bool real_in, VccArgs a, double alpha, float* agg, int nsm, cudaStream_t st,
+                              long long* run_len, long long* nruns, bool* done);
+long long logpwr_fused_scratch_floats(int N, int nsm);
+int logpwr_carry_fixup_launch(float* p, long long nframes, int N, long long run_len, long long nruns, double alpha, float* agg,
+                              float* ystate, float log_mul, float log_scale, cudaStream_t st);
 long long logpwr_static_scratch_floats();
 int logpwr_static_check(long long nframes, int N, int nsm);
 int logpwr_iir_log_launch_static(float* p, long long nframes, int N, double alpha, float* ystate, float log_mul,

@@ -395,6 +395,22 @@ static void logpwr_plan(const grb200_logpwr* h, long long nvec_in, long long max
     *count_after = cnt;
 }
 
+// the handle's averaging scratch, grown on demand (grb200_logpwrfft_work_dev_static exists for callers that must not allocate)
+static int logpwr_reserve_scratch(grb200_logpwr* h, long long floats, cudaStream_t st)
+{
+    if ((size_t)floats * 4 <= h->scratch.cap)
+        return 0;
+    GRB_CUDA(cudaStreamSynchronize(st)); // an earlier call on this stream may still use the old scratch
+    h->scratch.release();
+    void* pnew = nullptr;
+    cudaError_t e = cudaMalloc(&pnew, (size_t)floats * 4 + 256);
+    if (e != cudaSuccess)
+        return fail(GRB200_ENOMEM, "cudaMalloc(%lld) failed: %s", floats * 4, cudaGetErrorString(e));
+    h->scratch.p = pnew;
+    h->scratch.cap = (size_t)floats * 4 + 256;
+    return 0;
+}
+
 // output frame j transforms input vector first + j*vstride of in_dev
 static int logpwr_run_dev(grb200_logpwr* h, const void* in_dev, long long first, long long vstride, long long nkeep,
                           float* out_dev, cudaStream_t st)
@@ -405,23 +421,33 @@ static int logpwr_run_dev(grb200_logpwr* h, const void* in_dev, long long first,
     const bool avg = h->average && h->avg_alpha != 1.0;
     VccArgs a{ in_dev, out_dev, nkeep, (const float*)h->window.p, (const float2*)h->tw.p, 0, avg ? 1 : 2, vstride, first,
                h->log_mul, h->log_scale, (float*)h->ystate.p };
-    int rc = fft_vcc_launch_ex(h->N, true, !h->complex_input, a, nsm, st);
+    int rc;
+    // Long averaging calls at 2048 / 4096 / 8192 bins: the FFT kernel filters its own runs of frames (mode 3), two small
+    // kernels finish.  (Only past what grb200_logpwrfft_work_dev_static accepts: up to there both entry points run the same
+    // kernels and give the same bits.)
+    const long long fused_need = logpwr_fused_scratch_floats(h->N, nsm);
+    if (avg && (h->N == 2048 || h->N == 4096 || h->N == 8192) && nkeep > 8 * (logpwr_static_scratch_floats() / h->N)) {
+        if ((rc = logpwr_reserve_scratch(h, fused_need, st)))
+            return rc;
+        long long run_len = 0, nruns = 0;
+        bool done = false;
+        if ((rc = fft_vcc_stream_iir_launch(h->N, !h->complex_input, a, h->avg_alpha, (float*)h->scratch.p, nsm, st, &run_len,
+                                            &nruns, &done)))
+            return rc;
+        if (done)
+            return logpwr_carry_fixup_launch(out_dev, nkeep, h->N, run_len, nruns, h->avg_alpha, (float*)h->scratch.p,
+                                             (float*)h->ystate.p, h->log_mul, h->log_scale, st);
+    }
+    rc = fft_vcc_launch_ex(h->N, true, !h->complex_input, a, nsm, st);
     if (rc || !avg)
         return rc;
     const long long need = logpwr_scratch_floats(nkeep, h->N, nsm);
-    if ((size_t)need * 4 > h->scratch.cap) {
-        GRB_CUDA(cudaStreamSynchronize(st)); // an earlier call on this stream may still use the old scratch
-        h->scratch.release();
-        void* pnew = nullptr;
-        cudaError_t e = cudaMalloc(&pnew, (size_t)need * 4 + 256);
-        if (e != cudaSuccess)
-            return fail(GRB200_ENOMEM, "cudaMalloc(%lld) failed: %s", need * 4, cudaGetErrorString(e));
-        h->scratch.p = pnew;
-        h->scratch.cap = (size_t)need * 4 + 256;
-    }
+    if ((rc = logpwr_reserve_scratch(h, need, st)))
+        return rc;
     return logpwr_iir_log_launch(out_dev, nkeep, h->N, h->avg_alpha, (float*)h->ystate.p, need ? (float*)h->scratch.p : nullptr,
                                  h->log_mul, h->log_scale, nsm, st);
 }
+
 
 extern "C" {
 

@@ -54,7 +54,15 @@ fft_vcc_stream_kernel(const VccArgs a)
     const bool in_swap = (!FWD) && shift;
     const bool out_rot = FWD && shift;
     const bool has_win = window != nullptr;
-    const long long vstep = (long long)gridDim.x * VPC;
+    // MODE 3: CTA r walks its own run of consecutive frames (the recurrence runs along them); else CTAs interleave
+    const long long vstep = MODE == 3 ? 1 : (long long)gridDim.x * VPC;
+    const long long vfirst = MODE == 3 ? (long long)blockIdx.x * a.run_len : (long long)blockIdx.x * VPC;
+    const long long vend = MODE == 3 ? (vfirst + a.run_len < nvec ? vfirst + a.run_len : nvec) : nvec;
+    const double alpha = a.alpha, beta = 1.0 - a.alpha;
+    float ys[MODE == 3 ? E : 1]; // the filter memory of this thread's bins
+#pragma unroll
+    for (int i = 0; i < (MODE == 3 ? E : 1); i++)
+        ys[i] = 0.f;
 
     auto issue = [&](long long vbase) {
         long long nv = nvec - vbase;
@@ -77,12 +85,12 @@ fft_vcc_stream_kernel(const VccArgs a)
         for (int i = threadIdx.x; i < N; i += G::NT)
             WIN[i] = window[i];
     __syncthreads();
-    long long vbase = (long long)blockIdx.x * VPC;
-    if (threadIdx.x == 0 && vbase < nvec)
+    long long vbase = vfirst;
+    if (threadIdx.x == 0 && vbase < vend)
         issue(vbase);
 
     unsigned phase = 0;
-    for (; vbase < nvec; vbase += vstep, phase ^= 1) {
+    for (; vbase < vend; vbase += vstep, phase ^= 1) {
         const long long vec = vbase + vl;
         const bool valid = vec < nvec;
         mbar_wait(bar, phase);
@@ -106,7 +114,7 @@ fft_vcc_stream_kernel(const VccArgs a)
         }
         const long long vnext = vbase + vstep;
         cta_fft_tws<N, FWD>(v, S, t, TW, tw, [&]() {
-            if (threadIdx.x == 0 && vnext < nvec)
+            if (threadIdx.x == 0 && vnext < vend)
                 issue(vnext); // every thread has read XIN (barrier after the first pass)
         });
         if (valid) {
@@ -124,6 +132,10 @@ fft_vcc_stream_kernel(const VccArgs a)
                         const float pw = fmaf(Xk.x, Xk.x, Xk.y * Xk.y);
                         if constexpr (MODE == 1) {
                             outf[vec * N + k] = pw;
+                        } else if constexpr (MODE == 3) { // single_pole_iir.h:82 (double arithmetic, float state), as logpwr.cu
+                            const float y = (float)(alpha * (double)pw + beta * (double)ys[b * RL + q]);
+                            ys[b * RL + q] = y;
+                            outf[vec * N + k] = y;
                         } else {
                             outf[vec * N + k] = log2f(fmaxf(pw, 1.17549435e-38f) * log_scale) * log_mul;
                             if (vec == nvec - 1)
@@ -134,6 +146,19 @@ fft_vcc_stream_kernel(const VccArgs a)
             }
         }
         __syncthreads(); // the next iteration's first pass overwrites S
+    }
+    if constexpr (MODE == 3) {
+        if (vfirst < vend) {
+#pragma unroll
+            for (int b = 0; b < E / RL; b++)
+#pragma unroll
+                for (int q = 0; q < RL; q++) {
+                    int k = (t + b * TPV) + q * (N / RL);
+                    if (out_rot)
+                        k = (k + N / 2) & (N - 1);
+                    a.agg[(long long)blockIdx.x * N + k] = ys[b * RL + q];
+                }
+        }
     }
 }
 
@@ -170,6 +195,63 @@ static int launch_vcc_stream(const VccArgs& a, int nsm, cudaStream_t st)
         return fail(GRB200_EINVAL, "fft_vcc: the log epilogue needs a forward transform");
 }
 
+
+// ---- mode 3: the run-local single-pole IIR of logpwrfft in the FFT kernel's epilogue ------------------------------------------
+// (logpwr.cu's first pass -- read |X|^2, filter, write -- folded into the kernel that produces |X|^2: 8 B per bin less HBM
+// traffic.)  One run per CTA, so the carries / fix-up kernels of logpwr.cu see nruns = the grid.
+template <int N, bool REAL>
+static int launch_vcc_stream_iir(VccArgs a, int nsm, cudaStream_t st, long long* run_len, long long* nruns, bool* done)
+{
+    using G = VccGeom<N>;
+    using SG = VccStreamGeom<N>;
+    static_assert(G::VPC == 1, "one vector per CTA");
+    auto kern = fft_vcc_stream_kernel<N, true, REAL, 3>;
+    GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::SMEM));
+    int occ = 1;
+    GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, G::NT, SG::SMEM));
+    if (occ < 1)
+        occ = 1;
+    const long long grid = (long long)nsm * (occ > 4 ? 4 : occ); // (logpwr_fused_scratch_floats: room for 4 runs per SM)
+    if (a.nvec < 4 * grid) // (short calls: the three-kernel form spreads a few frames over the machine better)
+        return 0;
+    const long long len = (a.nvec + grid - 1) / grid, runs = (a.nvec + len - 1) / len;
+    a.run_len = len;
+    a.mode = 3;
+    kern<<<(unsigned)runs, G::NT, SG::SMEM, st>>>(a);
+    GRB_LAUNCH_CHECK();
+    *run_len = len;
+    *nruns = runs;
+    *done = true;
+    return 0;
+}
+
+long long logpwr_fused_scratch_floats(int N, int nsm) { return (long long)nsm * 4 * N; }
+
+int fft_vcc_stream_iir_launch(int N, bool real_in, VccArgs a, double alpha, float* agg, int nsm, cudaStream_t st,
+                              long long* run_len, long long* nruns, bool* done)
+{
+    *done = false;
+    static const bool on = [] {
+        const char* e = GRB_GETENV_ONCE("GRB200_LOGPWR_FUSED"); // 0 = FFT kernel, then the three kernels of logpwr.cu
+        return !(e && e[0] == '0');
+    }();
+    if (!on || (((uintptr_t)a.in) & 15) != 0)
+        return 0;
+    a.alpha = alpha;
+    a.agg = agg;
+    switch (N) {
+    case 2048:
+        return real_in ? launch_vcc_stream_iir<2048, true>(a, nsm, st, run_len, nruns, done)
+                       : launch_vcc_stream_iir<2048, false>(a, nsm, st, run_len, nruns, done);
+    case 4096:
+        return real_in ? launch_vcc_stream_iir<4096, true>(a, nsm, st, run_len, nruns, done)
+                       : launch_vcc_stream_iir<4096, false>(a, nsm, st, run_len, nruns, done);
+    case 8192:
+        return real_in ? launch_vcc_stream_iir<8192, true>(a, nsm, st, run_len, nruns, done)
+                       : launch_vcc_stream_iir<8192, false>(a, nsm, st, run_len, nruns, done);
+    }
+    return 0;
+}
 
 int fft_vcc_stream_launch(int N, bool fwd, bool real_in, const VccArgs& a, int nsm, cudaStream_t st)
 {

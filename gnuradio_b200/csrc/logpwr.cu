@@ -68,41 +68,88 @@ logpwr_carry_kernel(float* __restrict__ agg, long long nruns, long long nframes,
         return;
     const double bfull = pow(beta, (double)run_len);
     double c = (double)ystate[bin];
-    for (long long r = 0; r < nruns; r++) {
-        const float a = agg[r * N + bin];
-        agg[r * N + bin] = (float)c;
-        const long long len = (r + 1) * run_len <= nframes ? run_len : nframes - r * run_len;
-        const double b = len == run_len ? bfull : pow(beta, (double)len);
-        c = (double)a + b * c;
+    for (long long r0 = 0; r0 < nruns; r0 += 8) { // eight loads in flight, then the dependent chain (as the other two kernels)
+        float a[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+            a[u] = r0 + u < nruns ? agg[(r0 + u) * N + bin] : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const long long r = r0 + u;
+            if (r < nruns) {
+                agg[r * N + bin] = (float)c;
+                const long long len = (r + 1) * run_len <= nframes ? run_len : nframes - r * run_len;
+                const double b = len == run_len ? bfull : pow(beta, (double)len);
+                c = (double)a[u] + b * c;
+            }
+        }
     }
     ystate[bin] = (float)c;
 }
 
+// VEC = 4: a thread takes four neighbouring bins (16-byte accesses; N a multiple of 4 and p 16-byte aligned), same arithmetic
+// per bin.
+template <int VEC>
 __global__ void __launch_bounds__(256)
 logpwr_fixup_kernel(float* __restrict__ p, long long nframes, int N, int run_len, double beta,
                     const float* __restrict__ carry, float log_mul, float log_scale)
 {
-    const int bin = blockIdx.x * blockDim.x + threadIdx.x;
+    const int bin = (blockIdx.x * blockDim.x + threadIdx.x) * VEC;
     const long long run = blockIdx.y;
     if (bin >= N)
         return;
     const long long j0 = run * run_len;
     long long j1 = j0 + run_len;
     j1 = j1 > nframes ? nframes : j1;
-    const double c = (double)carry[run * N + bin];
+    double c[VEC];
+#pragma unroll
+    for (int e = 0; e < VEC; e++)
+        c[e] = (double)carry[run * N + bin + e];
     double m = beta;
-    for (long long j = j0; j < j1; j += 8) {
-        float z[8];
+    constexpr int U = VEC == 4 ? 4 : 8; // frames in flight per thread
+    for (long long j = j0; j < j1; j += U) {
+        float z[U][VEC];
 #pragma unroll
-        for (int u = 0; u < 8; u++)
-            z[u] = j + u < j1 ? p[(j + u) * N + bin] : 0.f;
-#pragma unroll
-        for (int u = 0; u < 8; u++) {
+        for (int u = 0; u < U; u++) {
             if (j + u < j1) {
-                p[(j + u) * N + bin] = logpwr_log(z[u] + (float)(m * c), log_mul, log_scale);
+                if constexpr (VEC == 4) {
+                    const float4 q = *reinterpret_cast<const float4*>(p + (j + u) * N + bin);
+                    z[u][0] = q.x, z[u][1] = q.y, z[u][2] = q.z, z[u][3] = q.w;
+                } else {
+                    z[u][0] = p[(j + u) * N + bin];
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < VEC; e++)
+                    z[u][e] = 0.f;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (j + u < j1) {
+                float o[VEC];
+#pragma unroll
+                for (int e = 0; e < VEC; e++)
+                    o[e] = logpwr_log(z[u][e] + (float)(m * c[e]), log_mul, log_scale);
+                if constexpr (VEC == 4)
+                    *reinterpret_cast<float4*>(p + (j + u) * N + bin) = make_float4(o[0], o[1], o[2], o[3]);
+                else
+                    p[(j + u) * N + bin] = o[0];
                 m *= beta;
             }
         }
+    }
+}
+
+static void logpwr_fixup_launch(float* p, long long nframes, int N, int run_len, long long nruns, double beta, const float* carry,
+                                float log_mul, float log_scale, cudaStream_t st)
+{
+    if ((N & 3) == 0 && (((uintptr_t)p) & 15) == 0 && (((uintptr_t)carry) & 15) == 0) {
+        const unsigned gx = (unsigned)((N / 4 + 255) / 256);
+        logpwr_fixup_kernel<4><<<dim3(gx, (unsigned)nruns), 256, 0, st>>>(p, nframes, N, run_len, beta, carry, log_mul, log_scale);
+    } else {
+        const unsigned gx = (unsigned)((N + 255) / 256);
+        logpwr_fixup_kernel<1><<<dim3(gx, (unsigned)nruns), 256, 0, st>>>(p, nframes, N, run_len, beta, carry, log_mul, log_scale);
     }
 }
 
@@ -151,7 +198,25 @@ int logpwr_iir_log_launch(float* p, long long nframes, int N, double alpha, floa
     GRB_LAUNCH_CHECK();
     logpwr_carry_kernel<<<gx, 256, 0, st>>>(scratch, nruns, nframes, N, (int)len, beta, ystate);
     GRB_LAUNCH_CHECK();
-    logpwr_fixup_kernel<<<dim3(gx, (unsigned)nruns), 256, 0, st>>>(p, nframes, N, (int)len, beta, scratch, log_mul, log_scale);
+    logpwr_fixup_launch(p, nframes, N, (int)len, nruns, beta, scratch, log_mul, log_scale, st);
+    GRB_LAUNCH_CHECK();
+    return 0;
+}
+
+// The second half of the above for a caller whose FFT kernel already filtered the runs (fft_vcc_stream_kernel mode 3: run r =
+// frames [r run_len, (r+1) run_len), local results in p, last values in agg): carries, then fix-up + logarithm.
+int logpwr_carry_fixup_launch(float* p, long long nframes, int N, long long run_len, long long nruns, double alpha, float* agg,
+                              float* ystate, float log_mul, float log_scale, cudaStream_t st)
+{
+    if (nframes <= 0)
+        return 0;
+    if (nruns > 65535 || run_len > 0x7fffffffLL)
+        return fail(GRB200_ERANGE, "logpwrfft: too many frames in one call");
+    const double beta = 1.0 - alpha;
+    const unsigned gx = (unsigned)((N + 255) / 256);
+    logpwr_carry_kernel<<<gx, 256, 0, st>>>(agg, nruns, nframes, N, (int)run_len, beta, ystate);
+    GRB_LAUNCH_CHECK();
+    logpwr_fixup_launch(p, nframes, N, (int)run_len, nruns, beta, agg, log_mul, log_scale, st);
     GRB_LAUNCH_CHECK();
     return 0;
 }

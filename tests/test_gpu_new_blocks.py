@@ -214,6 +214,47 @@ def test_logpwrfft_against_oracle(grb, orc, cin, N, dec, avg, alpha, nvec):
     assert np.abs(got2 - got)[strong].max() < 2e-3
 
 
+@pytest.mark.parametrize("cin,N,dec,nvec,first", [(True, 4096, 1, 1500, 1450), (True, 4096, 1, 1500, 37), (False, 4096, 2, 1300, 1250),
+                                                  (True, 2048, 1, 2600, 2550), (True, 8192, 1, 700, 650), (False, 2048, 3, 2500, 60),
+                                                  (False, 8192, 1, 700, 652)])
+def test_logpwrfft_long_averaging_calls_filter_in_the_fft_kernel(grb, orc, cin, N, dec, nvec, first):
+    """Calls of >= 4 frames per resident CTA at 2048 / 4096 / 8192 bins: fft_vcc_stream_kernel mode 3 filters each CTA's run of
+    consecutive frames in its epilogue, logpwr_carry_kernel / logpwr_fixup_kernel finish.  Device resident, two calls in a row
+    -- a long one and a short one that takes the three-kernel form, in either order; the second continues the first's filter
+    memory and decimator phase --, against float64 and the oracle."""
+    import torch
+
+    rng = np.random.default_rng(N + dec + nvec)
+    w = _ref_win(orc, N)
+    n = N * nvec * dec
+    x = crand(rng, n) if cin else rng.uniform(-1, 1, n).astype(np.float32)
+    tone = np.exp(2j * np.pi * 0.0731 * np.arange(n)) * (3 + 2 * np.sin(np.arange(n) * 1e-5))
+    x = (x + tone).astype(np.complex64) if cin else (x + tone.real).astype(np.float32)
+    alpha = 0.07
+    cls = grb.fft.logpwrfft_c if cin else grb.fft.logpwrfft_f
+    blk = cls(float(N * dec), N, 2.0, 1.0, alpha, True, lambda k: w)
+    xd = torch.from_numpy(x.view(np.float32) if cin else x).cuda()
+    yd = torch.full((nvec + 1, N), float("nan"), dtype=torch.float32, device="cuda")
+    isz = 8 if cin else 4
+    cut = first * dec * N  # items in the first call
+    u1, m1 = blk.work_dev(xd.data_ptr(), cut, yd.data_ptr(), nvec)
+    u2, m2 = blk.work_dev(xd.data_ptr() + u1 * isz, n - u1, yd.data_ptr() + m1 * N * 4, nvec - m1)
+    torch.cuda.synchronize()
+    assert m1 + m2 == nvec and u1 + u2 == n
+    got = yd.cpu().numpy()
+    assert np.isnan(got[-1]).all() and np.isfinite(got[:-1]).all()
+    got = got[:-1]
+    f64 = po.f64_logpwrfft(cin, N, 2.0, dec, alpha, True, w, x)
+    assert got.shape == f64.shape
+    pw = lambda d: 10.0 ** (np.asarray(d, np.float64) / 10.0)
+    assert_parity(pw(got), pw(f64), "power vs f64", 1e-5, 2e-4)
+    strong = f64 > f64.max() - 60.0
+    assert np.abs(got - f64)[strong].max() < 2e-3
+    k = 200  # the C oracle on the first frames
+    ref, cnt, st = orc.logpwrfft(cin, N, 2.0, dec, alpha, True, w, x[: k * dec * N])
+    assert_parity(pw(got[:k]), pw(ref), "power vs oracle", 1e-5, 2e-4)
+
+
 def test_logpwrfft_setters_and_limits(grb, orc):
     N = 256
     w = _ref_win(orc, N)
