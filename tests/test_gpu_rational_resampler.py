@@ -164,7 +164,11 @@ def test_rational_resampler_set_taps_midstream_and_errors(grb, orc):
                                                        (5, 4, 100, False, 3, 1), (4, 1, 64, False, 0, 0), (32, 3, 96, False, 7, 0),
                                                        (7, 2, 100, True, 5, 1), (3, 4, 96, False, 1, 0), (2, 1, 64, False, 1, 1),
                                                        (3, 2, 20, False, 2, 0), (2, 3, 32, False, 0, 0), (3, 4, 40, True, 1, 1),
-                                                       (2, 4, 30, False, 1, 0)])  # (the last three: 16-group rows)
+                                                       (2, 4, 30, False, 1, 0),  # (the last three: 16-group rows)
+                                                       # interpolation 1 = a decimating FIR: the FIR handle's kernels (direct,
+                                                       # tensor cores, overlap-save)
+                                                       (1, 4, 64, False, 0, 0), (1, 1, 48, False, 0, 1), (1, 8, 700, False, 0, 0),
+                                                       (1, 3, 200, True, 0, 1), (1, 2, 9, True, 0, 0)])
 def test_rational_resampler_streaming_kernel(grb, orc, L, D, ntaps, cplx, ctr0, shift):
     """One device-resident call long enough for resamp_stream_kernel (small interpolation and decimation): every ring depth
     and decimation step, interpolations that do not divide the warp, complex taps, a starting phase counter, an input
