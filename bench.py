@@ -369,9 +369,10 @@ class FreqXlating(FirCcf):
     name = "freq_xlating_fir_filter_ccf 128 taps decim 8, 2^%d input samples per GPU x %d set(s) (section 8(f) row)"
     block = "freq_xlating_fir_filter_ccf"
     # one read per input item, one write per output item; 128 complex composite taps at decimation 8 take the overlap-save
-    # route (4096-point blocks, 3969 new items each: two transforms and the spectrum product per block), then the rotator
-    alg_bytes, flops, log2n, seed = 8.0 + 8.0 / 8, (2 * 5 * 4096 * 12 + 6 * 4096) / 3969.0, 28, 6
-    kernel = "fftfilt_ols3_kernel + rotate_kernel"
+    # route (4096-point blocks, 3969 new items each: a 4096-point forward transform, the spectrum product, the fold to 512 bins
+    # and a 512-point inverse per block), then the rotator
+    alg_bytes, flops, log2n, seed = 8.0 + 8.0 / 8, (5 * 4096 * 12 + 5 * 512 * 9 + 6 * 4096 + 2 * 4096) / 3969.0, 28, 6
+    kernel = "fftfilt_ols3_kernel<DEC 8> + rotate_kernel"
     bound = "fp32"
     ntaps, decim, nsets = 128, 8, 1
 

@@ -1031,12 +1031,21 @@ struct Ols3 {
     static constexpr int TMEM_COLS = 64;
 };
 
-template <bool RP>
+// DEC = 4 or 8 (= D): only every DEC-th result of a block is wanted, item m = DEC i + r with r = (ntaps-1 - b V) mod DEC for block
+// b.  Decimating in time is aliasing in frequency: with Z_r[k] = X[k] H[k] e^{+j 2 pi k r / L},
+//     y[DEC i + r] = sum_{k' < L/DEC} ( sum_j Z_r[k' + j L/DEC] ) e^{+j 2 pi k' i / (L/DEC)},
+// an inverse transform of L/DEC points instead of L.  The DEC rotated filter spectra H_r sit side by side in tensor memory (64
+// columns each: all 512 at DEC = 8), so the rotation costs nothing per block; L/DEC = 256 Q with Q = 16 / DEC, so the fold adds
+// a thread's own registers (bins t + 256 q: q, q + Q, q + 2 Q, ... alias); then a radix-Q step in registers, a twiddle, and Q
+// 256-point inverse transforms done by the first 16 Q threads of the group (two radix-16 passes) while the rest wait -- the
+// other two groups of the CTA use the pipes meanwhile.  Forward transform and loads as before.
+template <bool RP, int DEC>
 __global__ void __launch_bounds__(768, 1)
 fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, long long nout, long long nin, int ntaps, int D,
                     const float2* __restrict__ H, const float2* __restrict__ tw, long long run, int gs, long long half)
 {
     using G = Ols3;
+    constexpr int NROT = DEC ? DEC : 1, TMEM_COLS = 64 * NROT;
     constexpr int L = G::L, TPV = G::TPV, NG = G::NG, XROW = G::XROW;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int grp = threadIdx.x >> 8, t = threadIdx.x & 255, warp = t >> 5, bid = grp + 1;
@@ -1083,7 +1092,7 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
 
     if (threadIdx.x < 32) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"(G::TMEM_COLS));
+                     "r"(TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     if (t == 0)
@@ -1102,15 +1111,20 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
     asm volatile("tcgen05.fence::after_thread_sync;");
     const unsigned tmem = *tmem_slot;
     const unsigned th0 = tmem + ((unsigned)((warp & 3) * 32) << 16) + (unsigned)((warp >> 2) * 32);
-    if (grp == 0) { // bins k = t + 256 i, i = 0..15: columns 2 i, 2 i + 1 of this thread's lane
-#pragma unroll
-        for (int c = 0; c < 2; c++) {
+    if (grp == 0) { // bins k = t + 256 i, i = 0..15: columns 2 i, 2 i + 1 of this thread's lane (+ 64 r: rotated by r items)
+#pragma unroll 1
+        for (int rc = 0; rc < 2 * NROT; rc++) {
+            const int r = rc >> 1, c = rc & 1;
             float2 a[8];
 #pragma unroll
-            for (int e = 0; e < 8; e++)
-                a[e] = __ldg(H + t + 256 * (8 * c + e));
+            for (int e = 0; e < 8; e++) {
+                const int k = t + 256 * (8 * c + e);
+                a[e] = __ldg(H + k);
+                if (DEC) // e^{+j 2 pi k r / L} = conj(W_L^{k r})
+                    a[e] = cmul_dir<false>(a[e], __ldg(tw + ((k * r) & (L - 1))));
+            }
             asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, "
-                         "%12, %13, %14, %15, %16};" ::"r"(th0 + c * 16),
+                         "%12, %13, %14, %15, %16};" ::"r"(th0 + 64 * r + c * 16),
                          "f"(a[0].x), "f"(a[0].y), "f"(a[1].x), "f"(a[1].y), "f"(a[2].x), "f"(a[2].y), "f"(a[3].x),
                          "f"(a[3].y), "f"(a[4].x), "f"(a[4].y), "f"(a[5].x), "f"(a[5].y), "f"(a[6].x), "f"(a[6].y),
                          "f"(a[7].x), "f"(a[7].y)
@@ -1169,13 +1183,16 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
                 if (t == 0 && blk + 1 < b1)
                     issue(blk + 1); // every thread of the group has read the block's items by now
             });
+            // DEC: this block keeps items m = DEC i + rb (output blk V + m - nh is a multiple of DEC)
+            const int rb = DEC ? (int)((((long long)nh - blk * V) % NROT + NROT) % NROT) : 0;
+            const unsigned thr = th0 + 64u * (unsigned)rb;
 #pragma unroll
             for (int c = 0; c < 4; c++) {
                 float2 h[4];
                 asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                              : "=f"(h[0].x), "=f"(h[0].y), "=f"(h[1].x), "=f"(h[1].y), "=f"(h[2].x), "=f"(h[2].y),
                                "=f"(h[3].x), "=f"(h[3].y)
-                             : "r"(th0 + c * 8));
+                             : "r"(thr + c * 8));
                 asm volatile("tcgen05.wait::ld.sync.aligned;"
                              : "+f"(h[0].x), "+f"(h[0].y), "+f"(h[1].x), "+f"(h[1].y), "+f"(h[2].x), "+f"(h[2].y),
                                "+f"(h[3].x), "+f"(h[3].y));
@@ -1184,6 +1201,77 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
                     v[4 * c + e] = cmul(v[4 * c + e], h[e]);
             }
             group_sync(bid); // forward transform's last gather is done before the inverse reuses S
+            if constexpr (DEC != 0) {
+                constexpr int Q = 16 / DEC;
+                float2 f[Q];
+#pragma unroll
+                for (int qq = 0; qq < Q; qq++) {
+                    f[qq] = v[qq];
+#pragma unroll
+                    for (int j = 1; j < DEC; j++)
+                        f[qq] = __fadd2_rn(f[qq], v[qq + Q * j]);
+                }
+                // a_{i0}[t] = e^{+j 2 pi t i0 / (256 Q)} sum_q' f[q'] e^{+j 2 pi q' i0 / Q}; the twiddle is conj(W_L^{DEC t i0})
+                float2 w4 = TW2[2 * TPV + t]; // W_L^{4 t}
+                const float2 w8 = cmul(w4, w4);
+                if constexpr (Q == 2) {
+                    dft2<false>(f[0], f[1]);
+                    f[1] = cmul_dir<false>(f[1], w8);
+                } else {
+                    dft4<false>(f[0], f[1], f[2], f[3]);
+                    f[1] = cmul_dir<false>(f[1], w4);
+                    f[2] = cmul_dir<false>(f[2], w8);
+                    f[3] = cmul_dir<false>(f[3], cmul(w4, w8));
+                }
+                float2* S1 = S;        // [Q][256]
+                float2* S2 = S + 1024; // [Q][16 x 17]
+#pragma unroll
+                for (int i0 = 0; i0 < Q; i0++)
+                    S1[i0 * 256 + t] = f[i0];
+                group_sync(bid);
+                const bool act = t < 16 * Q;
+                const int i0 = t >> 4, c = t & 15; // pass A: (i0, c) sums over h, t' = c + 16 h; pass B: (i0, g = c) sums over c
+                float2 x[16];
+                if (act) {
+#pragma unroll
+                    for (int h = 0; h < 16; h++)
+                        x[h] = S1[i0 * 256 + c + 16 * h];
+                    dft16<false>(x);
+                    const float2* trow = T1 + c * Upols2::T1_STRIDE; // W256^{c g}
+#pragma unroll
+                    for (int g = 1; g < 16; g++)
+                        x[g] = cmul_dir<false>(x[g], trow[g]);
+#pragma unroll
+                    for (int g = 0; g < 16; g++)
+                        S2[i0 * 272 + g * 17 + c] = x[g];
+                }
+                group_sync(bid);
+                if (act) {
+#pragma unroll
+                    for (int cc = 0; cc < 16; cc++)
+                        x[cc] = S2[i0 * 272 + c * 17 + cc];
+                    dft16<false>(x);
+                    // x[d] = result i = i0 + Q (c + 16 d) of the block = item m = DEC i + rb = decimated output ob + i
+                    const long long ob = (blk * V + rb - nh) / DEC; // (exact)
+                    const long long lim = RP ? half : nout, limB = RP ? nout - half : 0;
+#pragma unroll
+                    for (int d = 0; d < 16; d++) {
+                        const int i = i0 + Q * (c + 16 * d);
+                        const long long o = ob + i;
+                        if (DEC * i + rb >= nh && o < lim) {
+                            if constexpr (RP) {
+                                outf[o] = x[d].x;
+                                if (o < limB)
+                                    outf[half + o] = x[d].y;
+                            } else {
+                                out[o] = x[d];
+                            }
+                        }
+                    }
+                }
+                group_sync(bid); // S is free for the next block's first scatter
+                continue;
+            }
             fft4096_3x16<false>(v, S, t, bid, T1, TW2, []() {});
             // item m = t + 256 q of the block is output n = blk V + m - nh, for m >= nh
             const long long n0 = blk * V - nh + t;
@@ -1270,7 +1358,7 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
     if (threadIdx.x < 32)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(G::TMEM_COLS));
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS));
 }
 
 static bool ols3_enabled()
@@ -1283,12 +1371,12 @@ static bool ols3_enabled()
 }
 
 // RP: `nout` real outputs, `half` as in launch_ols_realpair; otherwise complex items.
-template <bool RP>
-static int launch_ols3(const void* in, void* out, long long nout, long long nin, int ntaps, int D, const float2* H,
-                       const float2* tw, int nsm, cudaStream_t st)
+template <bool RP, int DEC>
+static int launch_ols3_d(const void* in, void* out, long long nout, long long nin, int ntaps, int D, const float2* H,
+                         const float2* tw, int nsm, cudaStream_t st)
 {
     using G = Ols3;
-    auto kern = fftfilt_ols3_kernel<RP>;
+    auto kern = fftfilt_ols3_kernel<RP, DEC>;
     GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
     const long long half = RP ? (nout + 1) / 2 : 0;
     const int V = G::L - (ntaps - 1);
@@ -1304,6 +1392,21 @@ static int launch_ols3(const void* in, void* out, long long nout, long long nin,
                                                           run, gs, half);
     GRB_LAUNCH_CHECK();
     return 0;
+}
+
+template <bool RP>
+static int launch_ols3(const void* in, void* out, long long nout, long long nin, int ntaps, int D, const float2* H,
+                       const float2* tw, int nsm, cudaStream_t st)
+{
+    static const bool fold = [] {
+        const char* e = GRB_GETENV_ONCE("GRB200_FFTFILT_FOLD"); // 0 = full-length inverse transform, decimation on store
+        return !(e && e[0] == '0');
+    }();
+    if (fold && D == 8)
+        return launch_ols3_d<RP, 8>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+    if (fold && D == 4)
+        return launch_ols3_d<RP, 4>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+    return launch_ols3_d<RP, 0>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
 }
 
 static int ols3_realpair(const void* in, void* out, long long nout, int ntaps, int D, const float2* H, const float2* tw,
