@@ -148,11 +148,11 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
         // long real filters: the overlap-save kernel with the two halves of a call as re / im of one complex stream
         h->fft_route = false;
         const int L = fftfilt_realpair_L(ntaps);
-        // (measured, tools/route_check.py: ~470 G samples/s at any tap count up to 2049, ~640 at decimation 4 and 8 (folded
-        // inverse transform), ~450 at other decimations that divide 256, ~380 at the rest; the FIR kernel falls below that past
-        // 16 taps, at decimation 2, 4 and 8 past 8)
+        // (measured, tools/route_check.py: ~470 G samples/s at any tap count up to 2049, ~590 / 635 / 645 at decimation 2 / 4 / 8
+        // (folded inverse transform), ~450 at other decimations that divide 256, ~380 at the rest; the FIR kernel falls below
+        // that past 16 taps, at decimation 4 and 8 past 8, at decimation 2 it is below at 8 taps already)
         const bool want =
-            h->fft_pref == 1 || (h->fft_pref < 0 && ntaps > (h->decim == 2 || h->decim == 4 || h->decim == 8 ? 8 : 16));
+            h->fft_pref == 1 || (h->fft_pref < 0 && ntaps > (h->decim == 2 ? 4 : (h->decim == 4 || h->decim == 8 ? 8 : 16)));
         if (want && L > 0) {
             std::vector<float> tc((size_t)2 * ntaps, 0.f);
             for (int t = 0; t < ntaps; t++)
@@ -189,13 +189,13 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
     // per step at decimation 2, 4, .., 48 per step otherwise; never where the real-tap tensor-core modes apply.  (Short filters
     // take the route on large calls only: fir_run_dev.)
     h->fft_route = false;
-    // (decimation 4 and 8: the overlap-save kernel folds the spectrum and inverts L/D points -- ~350 G items/s; the tensor-core
+    // (decimation 2, 4 and 8: the overlap-save kernel folds the spectrum and inverts L/D points -- 330 - 360 G items/s; the tensor-core
     // decimate-by-8 mode holds 345 - 357 from 256 taps up, 292 below)
     const bool tc_real = h->tc_pref != 0 && !h->ct && ((D == 1 && ntaps <= 64) || (D == 8 && ntaps >= 256 && ntaps <= 1024));
     const bool tc_forced = h->tc_pref == 1 && ((h->ct && D == 1 && ntaps <= 64) || (!h->ct && D == 8 && ntaps <= 1024));
     const bool p2 = D > 1 && D <= 256 && (D & (D - 1)) == 0;
     const long long least =
-        h->ct ? (p2 ? 0 : 16LL * D) : (D == 1 ? 64 : (D == 8 ? 0 : (D == 4 ? 64 : (p2 ? 32LL : 48LL) * D)));
+        h->ct ? (p2 ? 0 : 16LL * D) : (D == 1 ? 64 : (D == 8 ? 0 : (D == 4 ? 64 : (D == 2 ? 32 : (p2 ? 32LL : 48LL) * D))));
     const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && !tc_real && !tc_forced && ntaps > least);
     if (want && fftfilt_device_plan(ntaps, nullptr) > 0) {
         std::vector<float> tc((size_t)2 * ntaps, 0.f);

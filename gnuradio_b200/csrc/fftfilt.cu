@@ -1031,7 +1031,7 @@ struct Ols3 {
     static constexpr int TMEM_COLS = 64;
 };
 
-// DEC = 4 or 8 (= D): only every DEC-th result of a block is wanted, item m = DEC i + r with r = (ntaps-1 - b V) mod DEC for block
+// DEC = 2, 4 or 8 (= D): only every DEC-th result of a block is wanted, item m = DEC i + r with r = (ntaps-1 - b V) mod DEC for block
 // b.  Decimating in time is aliasing in frequency: with Z_r[k] = X[k] H[k] e^{+j 2 pi k r / L},
 //     y[DEC i + r] = sum_{k' < L/DEC} ( sum_j Z_r[k' + j L/DEC] ) e^{+j 2 pi k' i / (L/DEC)},
 // an inverse transform of L/DEC points instead of L.  The DEC rotated filter spectra H_r sit side by side in tensor memory (64
@@ -1217,20 +1217,32 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
                 if constexpr (Q == 2) {
                     dft2<false>(f[0], f[1]);
                     f[1] = cmul_dir<false>(f[1], w8);
-                } else {
+                } else if constexpr (Q == 4) {
                     dft4<false>(f[0], f[1], f[2], f[3]);
                     f[1] = cmul_dir<false>(f[1], w4);
                     f[2] = cmul_dir<false>(f[2], w8);
                     f[3] = cmul_dir<false>(f[3], cmul(w4, w8));
+                } else { // Q == 8: conj(W_L^{2 t i0}), i0 = 1..7, from W^{2t}, W^{4t}, W^{8t}
+                    dft8<false>(f);
+                    const float2 w2 = TW2[TPV + t], w6 = cmul(w2, w4), w12 = cmul(w4, w8);
+                    f[1] = cmul_dir<false>(f[1], w2);
+                    f[2] = cmul_dir<false>(f[2], w4);
+                    f[3] = cmul_dir<false>(f[3], w6);
+                    f[4] = cmul_dir<false>(f[4], w8);
+                    f[5] = cmul_dir<false>(f[5], cmul(w2, w8));
+                    f[6] = cmul_dir<false>(f[6], w12);
+                    f[7] = cmul_dir<false>(f[7], cmul(w2, w12));
                 }
+                constexpr int P2 = 272 + DEC; // rows of S2 start DEC float2-banks apart: pass B's half-warps read without conflicts
                 float2* S1 = S;        // [Q][256]
-                float2* S2 = S + 1024; // [Q][16 x 17]
+                float2* S2 = S + 2048; // [Q][16 x 17 (+ DEC)]
 #pragma unroll
                 for (int i0 = 0; i0 < Q; i0++)
                     S1[i0 * 256 + t] = f[i0];
                 group_sync(bid);
                 const bool act = t < 16 * Q;
-                const int i0 = t >> 4, c = t & 15; // pass A: (i0, c) sums over h, t' = c + 16 h; pass B: (i0, g = c) sums over c
+                const int i0 = t >> 4, c = t & 15; // pass A: thread (i0, c) sums over h, t' = c + 16 h
+                const int j0 = t % Q, g = t / Q;   // pass B: thread (j0, g) sums over c: its results are i = t + 16 Q d
                 float2 x[16];
                 if (act) {
 #pragma unroll
@@ -1239,24 +1251,24 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
                     dft16<false>(x);
                     const float2* trow = T1 + c * Upols2::T1_STRIDE; // W256^{c g}
 #pragma unroll
-                    for (int g = 1; g < 16; g++)
-                        x[g] = cmul_dir<false>(x[g], trow[g]);
+                    for (int gg = 1; gg < 16; gg++)
+                        x[gg] = cmul_dir<false>(x[gg], trow[gg]);
 #pragma unroll
-                    for (int g = 0; g < 16; g++)
-                        S2[i0 * 272 + g * 17 + c] = x[g];
+                    for (int gg = 0; gg < 16; gg++)
+                        S2[i0 * P2 + gg * 17 + c] = x[gg];
                 }
                 group_sync(bid);
                 if (act) {
 #pragma unroll
                     for (int cc = 0; cc < 16; cc++)
-                        x[cc] = S2[i0 * 272 + c * 17 + cc];
+                        x[cc] = S2[j0 * P2 + g * 17 + cc];
                     dft16<false>(x);
-                    // x[d] = result i = i0 + Q (c + 16 d) of the block = item m = DEC i + rb = decimated output ob + i
+                    // x[d] = result i = j0 + Q (g + 16 d) = t + 16 Q d of the block = item m = DEC i + rb = decimated output ob + i
                     const long long ob = (blk * V + rb - nh) / DEC; // (exact)
                     const long long lim = RP ? half : nout, limB = RP ? nout - half : 0;
 #pragma unroll
                     for (int d = 0; d < 16; d++) {
-                        const int i = i0 + Q * (c + 16 * d);
+                        const int i = t + 16 * Q * d;
                         const long long o = ob + i;
                         if (DEC * i + rb >= nh && o < lim) {
                             if constexpr (RP) {
@@ -1406,6 +1418,8 @@ static int launch_ols3(const void* in, void* out, long long nout, long long nin,
         return launch_ols3_d<RP, 8>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
     if (fold && D == 4)
         return launch_ols3_d<RP, 4>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+    if (fold && D == 2)
+        return launch_ols3_d<RP, 2>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
     return launch_ols3_d<RP, 0>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
 }
 
