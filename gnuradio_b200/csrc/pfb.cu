@@ -25,6 +25,9 @@
 namespace grb {
 
 bool pfb_stream_supported(int M, int T, int R, const void* x);
+bool pfb_stream_split_supported(int M, int T, int R, const void* x);
+int pfb_stream_split_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                            const float* h, const float2* wM, int nsm, cudaStream_t st);
 int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
                       const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo, const int* inv);
 int halo_fetch_launch(void* dst, const void* src, size_t bytes, cudaStream_t st);
@@ -516,6 +519,9 @@ int pfb_launch(int M, int T, int R, const void* x, void* out, long long out_stri
         if (rc)
             return rc;
     }
+    if (allow_fast && identity && pfb_stream_split_supported(M, T, R, x) && !GRB_GETENV_ONCE("GRB200_PFB_V1") &&
+        !GRB_GETENV_ONCE("GRB200_PFB_GENERIC"))
+        return pfb_stream_split_launch(M, T, x, out, out_stride, nouts, noutput, h, wM, nsm, st);
     if (allow_fast && mapped_ok && pfb_stream_os2_supported(M, T, R, x) && !GRB_GETENV_ONCE("GRB200_PFB_V1"))
         return pfb_stream_os2_launch(M, T, x, out, out_stride, nouts, noutput, h, wM, nsm, st, use_inv);
     if (allow_fast && R == M && T <= 32 && (M == 16 || M == 64 || M == 256)) {

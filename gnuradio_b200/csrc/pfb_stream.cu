@@ -43,7 +43,9 @@ struct PfbStreamGeom {
 // on x, the even ones the plain channelizer on x delayed by R samples, and the rotation by M/2 of the odd ones is a factor
 // (-1)^c on channel c.  So half of a CTA's groups walk the stream and half walk it R samples earlier; lanes 0-15 / 16-31 of a
 // warp's channel store hold the even / odd times of the same 32 consecutive output times.
-template <int M, int TP, int NT, int OS, bool MAPPED>
+// ACCUM: the results are ADDED to what `out` holds -- the second launch of a filter with 33 .. 64 taps per branch, whose older
+// taps run as a second channelizer on the same stream (the DFT is linear: pfb_stream_split_launch).
+template <int M, int TP, int NT, int OS, bool MAPPED, bool ACCUM = false>
 __global__ void __launch_bounds__(NT)
 pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long long out_stride, int nouts,
                   long long noutput, int T, long long nrows, const float* __restrict__ h,
@@ -163,6 +165,16 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
         for (int n = 0; n < Geo::NI2; n++) {
             const int idx = tid + n * NT;
             const int o = idx % OT, k1 = idx / OT;
+            const int g = o / KT, k = o % KT;
+            const long long t = OS * (cta0 + (long long)(g / OS) * region + (long long)it * KT + k) + (g % OS);
+            float2 prev[ACCUM ? R2 : 1]; // what the first launch left: all R2 loads in flight behind the transform below
+            if constexpr (ACCUM) {
+#pragma unroll
+                for (int k2 = 0; k2 < R2; k2++) {
+                    const int c = k1 + R1 * k2;
+                    prev[k2] = (t < noutput && c < nouts) ? out[(long long)c * out_stride + t] : make_float2(0.f, 0.f);
+                }
+            }
             float2 a[R2];
 #pragma unroll
             for (int j = 0; j < R2; j++) {
@@ -171,8 +183,6 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
                     a[j] = cmul(a[j], wtab[j * k1]);
             }
             dft_r<R2, false>(a);
-            const int g = o / KT, k = o % KT;
-            const long long t = OS * (cta0 + (long long)(g / OS) * region + (long long)it * KT + k) + (g % OS);
             if (t < noutput) {
 #pragma unroll
                 for (int k2 = 0; k2 < R2; k2++) {
@@ -181,8 +191,11 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
                     if (OS == 2 && (g % OS) && (c & 1)) // the rotation by M/2 of the odd output times
                         y = make_float2(-y.x, -y.y);
                     const int n = MAPPED ? sinv[c] : c; // the channel map, inverted on the host: a scatter here
-                    if (n >= 0 && n < nouts)
+                    if (n >= 0 && n < nouts) {
+                        if (ACCUM) // (identity map only)
+                            y = make_float2(prev[k2].x + y.x, prev[k2].y + y.y);
                         out[(long long)n * out_stride + t] = y;
+                    }
                 }
             }
         }
@@ -205,16 +218,24 @@ pfb_stream_kernel(const float2* __restrict__ x, float2* __restrict__ out, long l
 template <int M, int TP, int NT, int OS = 1>
 static int launch_stream(const void* x, void* out, long long out_stride, int nouts, long long noutput, int T,
                          long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo,
-                         const int* inv)
+                         const int* inv, bool accum = false)
 {
     using Geo = PfbStreamGeom<M, NT>;
     auto kern = inv != nullptr ? pfb_stream_kernel<M, TP, NT, OS, true> : pfb_stream_kernel<M, TP, NT, OS, false>;
-    static thread_local bool configured[2][16] = {};
+    if constexpr (OS == 1) {
+        if (accum) {
+            if (inv != nullptr)
+                return fail(GRB200_EINVAL, "pfb_channelizer: no accumulating kernel under a channel map");
+            kern = pfb_stream_kernel<M, TP, NT, 1, false, true>;
+        }
+    }
+    static thread_local bool configured[3][16] = {};
     int dev = 0;
     cudaGetDevice(&dev);
-    if (!configured[inv != nullptr][dev & 15]) {
+    const int which = accum ? 2 : (inv != nullptr ? 1 : 0);
+    if (!configured[which][dev & 15]) {
         GRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo::SMEM));
-        configured[inv != nullptr][dev & 15] = true;
+        configured[which][dev & 15] = true;
     }
     int occ = 1;
     GRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, Geo::SMEM));
@@ -253,13 +274,13 @@ static int launch_stream_os2(int T, const void* x, void* out, long long out_stri
 template <int M, int NT>
 static int launch_stream_tp(int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
                             long long nrows, const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo,
-                            const int* inv)
+                            const int* inv, bool accum = false)
 {
     if (T <= 8)
-        return launch_stream<M, 8, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo, inv);
+        return launch_stream<M, 8, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo, inv, accum);
     if (T <= 16)
-        return launch_stream<M, 16, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo, inv);
-    return launch_stream<M, 32, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo, inv);
+        return launch_stream<M, 16, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo, inv, accum);
+    return launch_stream<M, 32, NT>(x, out, out_stride, nouts, noutput, T, nrows, h, wM, nsm, st, halo, inv, accum);
 }
 
 // oversample_rate 2 (R = M/2): 8 .. 128 channels (a CTA needs groups of both parities)
@@ -293,25 +314,52 @@ bool pfb_stream_supported(int M, int T, int R, const void* x)
 }
 
 // x: interleaved input with T*M history items in front (16-byte aligned); identity channel map.
-int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
-                      const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo, const int* inv)
+static int stream_launch_any(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                             const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo, const int* inv,
+                             bool accum)
 {
     if (noutput <= 0)
         return 0;
     const long long nrows = T + noutput;
     if (M == 16)
-        return launch_stream_tp<16, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
+        return launch_stream_tp<16, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv, accum);
     if (M == 64)
-        return launch_stream_tp<64, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
+        return launch_stream_tp<64, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv, accum);
     switch (M) {
     case 8:
-        return launch_stream_tp<8, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
+        return launch_stream_tp<8, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv, accum);
     case 32:
-        return launch_stream_tp<32, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
+        return launch_stream_tp<32, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv, accum);
     case 128:
-        return launch_stream_tp<128, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
+        return launch_stream_tp<128, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv, accum);
     }
-    return launch_stream_tp<256, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv);
+    return launch_stream_tp<256, 256>(T, x, out, out_stride, nouts, noutput, nrows, h, wM, nsm, st, halo, inv, accum);
+}
+
+int pfb_stream_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                      const float* h, const float2* wM, int nsm, cudaStream_t st, const void* halo, const int* inv)
+{
+    return stream_launch_any(M, T, x, out, out_stride, nouts, noutput, h, wM, nsm, st, halo, inv, false);
+}
+
+// 33 .. 64 taps per branch (a register ring holds 32): two channelizers on the same stream, the newest 32 taps first, then
+// the older T - 32 on the rows 32 earlier, added to the first one's output (the DFT is linear).  Output time o of the kernel
+// reads rows o + T - u for tap u: the first launch's stream starts T - 32 rows in, the second one's where the call's does.
+// Identity channel map, history in place (no halo source).
+bool pfb_stream_split_supported(int M, int T, int R, const void* x)
+{
+    return R == M && T > 32 && T <= 64 && M >= 8 && M <= 256 && (M & (M - 1)) == 0 && ((uintptr_t)x & 15) == 0;
+}
+
+int pfb_stream_split_launch(int M, int T, const void* x, void* out, long long out_stride, int nouts, long long noutput,
+                            const float* h, const float2* wM, int nsm, cudaStream_t st)
+{
+    const float2* xa = (const float2*)x + (long long)(T - 32) * M;
+    int rc = stream_launch_any(M, 32, xa, out, out_stride, nouts, noutput, h, wM, nsm, st, nullptr, nullptr, false);
+    if (rc)
+        return rc;
+    return stream_launch_any(M, T - 32, x, out, out_stride, nouts, noutput, h + (size_t)32 * M, wM, nsm, st, nullptr, nullptr,
+                             true);
 }
 
 } // namespace grb

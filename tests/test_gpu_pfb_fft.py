@@ -61,6 +61,10 @@ def test_pfb_ctor_contract_and_errors(grb):
                                           # pfb_fftgen_kernel: oversampled, more than 32 taps per branch, R1 != R2
                                           (64, 64 * 40, 1.0), (32, 512, 2.0), (128, 640, 4.0 / 3.0), (16, 100, 4.0), (8, 64, 8.0),
                                           (256, 256 * 3, 2.0), (32, 32 * 33, 1.0),
+                                          # 33 .. 64 taps per branch at rate 1: two launches of the streaming kernel, the second
+                                          # one (the older taps, 1 .. 32 of them: every ring depth) adding to the first
+                                          (8, 8 * 64, 1.0), (256, 256 * 48, 1.0), (16, 16 * 33 - 5, 1.0), (128, 128 * 41, 1.0),
+                                          (64, 64 * 56, 1.0),
                                           # channel counts that are not a power of two: the two-stage DFT of the generic kernel
                                           (48, 48 * 7, 1.0), (100, 1000, 1.0), (12, 100, 1.5), (20, 200, 2.0), (7, 50, 1.0), (96, 960, 4.0 / 3.0),
                                           # oversample_rate 2 on the streaming kernel (8 .. 128 channels, every ring depth)
