@@ -189,13 +189,15 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
     // per step at decimation 2, 4, .., 48 per step otherwise; never where the real-tap tensor-core modes apply.  (Short filters
     // take the route on large calls only: fir_run_dev.)
     h->fft_route = false;
-    // (decimation 2, 4 and 8: the overlap-save kernel folds the spectrum and inverts L/D points -- 330 - 360 G items/s; the tensor-core
+    // (decimation 2, 4, 8 and 16 .. 256: the overlap-save kernel folds the spectrum and inverts L/D (L/8) points -- 320 - 360 G
+    // items/s, against 319 of the direct kernel up to 256 real taps at decimation 16 and 149 at decimation 32; the tensor-core
     // decimate-by-8 mode holds 345 - 357 from 256 taps up, 292 below)
     const bool tc_real = h->tc_pref != 0 && !h->ct && ((D == 1 && ntaps <= 64) || (D == 8 && ntaps >= 256 && ntaps <= 1024));
     const bool tc_forced = h->tc_pref == 1 && ((h->ct && D == 1 && ntaps <= 64) || (!h->ct && D == 8 && ntaps <= 1024));
     const bool p2 = D > 1 && D <= 256 && (D & (D - 1)) == 0;
     const long long least =
-        h->ct ? (p2 ? 0 : 16LL * D) : (D == 1 ? 64 : (D == 8 ? 0 : (D == 4 ? 64 : (D == 2 ? 32 : (p2 ? 32LL : 48LL) * D))));
+        h->ct ? (p2 ? 0 : 16LL * D)
+              : (D == 1 ? 64 : (D == 2 ? 32 : (D == 4 ? 64 : (D == 8 ? 0 : (D == 16 ? 256 : (p2 ? 0 : 48LL * D))))));
     const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && !tc_real && !tc_forced && ntaps > least);
     if (want && fftfilt_device_plan(ntaps, nullptr) > 0) {
         std::vector<float> tc((size_t)2 * ntaps, 0.f);

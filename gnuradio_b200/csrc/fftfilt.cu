@@ -1031,7 +1031,7 @@ struct Ols3 {
     static constexpr int TMEM_COLS = 64;
 };
 
-// DEC = 2, 4 or 8 (= D): only every DEC-th result of a block is wanted, item m = DEC i + r with r = (ntaps-1 - b V) mod DEC for block
+// DEC = 2, 4 or 8 (= D, or D = 8 E with DEC = 8 and E = 2 .. 32 of the results dropped on store): only every DEC-th result of a block is wanted, item m = DEC i + r with r = (ntaps-1 - b V) mod DEC for block
 // b.  Decimating in time is aliasing in frequency: with Z_r[k] = X[k] H[k] e^{+j 2 pi k r / L},
 //     y[DEC i + r] = sum_{k' < L/DEC} ( sum_j Z_r[k' + j L/DEC] ) e^{+j 2 pi k' i / (L/DEC)},
 // an inverse transform of L/DEC points instead of L.  The DEC rotated filter spectra H_r sit side by side in tensor memory (64
@@ -1263,14 +1263,20 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
                     for (int cc = 0; cc < 16; cc++)
                         x[cc] = S2[j0 * P2 + g * 17 + cc];
                     dft16<false>(x);
-                    // x[d] = result i = j0 + Q (g + 16 d) = t + 16 Q d of the block = item m = DEC i + rb = decimated output ob + i
-                    const long long ob = (blk * V + rb - nh) / DEC; // (exact)
+                    // x[d] = result i = j0 + Q (g + 16 d) = t + 16 Q d of the block = item m = DEC i + rb.  D = DEC: decimated
+                    // output ob + i.  D = DEC E (DEC = 8, E = 2 .. 32): every E-th of them is wanted, i = ifirst + E j -- a thread
+                    // keeps all of its results or none (16 Q = 32 is a multiple of E) -- and is output ob + j.
+                    const int E = D / DEC, lgE = 31 - __clz(E);
+                    const int rD = E == 1 ? rb : (int)((((long long)nh - blk * V) % D + D) % D);
+                    const int ifirst = (rD - rb) / DEC;
+                    const long long ob = (blk * V + rD - nh) / D; // (exact)
                     const long long lim = RP ? half : nout, limB = RP ? nout - half : 0;
+                    const bool keep = ((t - ifirst) & (E - 1)) == 0;
 #pragma unroll
                     for (int d = 0; d < 16; d++) {
                         const int i = t + 16 * Q * d;
-                        const long long o = ob + i;
-                        if (DEC * i + rb >= nh && o < lim) {
+                        const long long o = ob + ((i - ifirst) >> lgE);
+                        if (keep && DEC * i + rb >= nh && o < lim) {
                             if constexpr (RP) {
                                 outf[o] = x[d].x;
                                 if (o < limB)
@@ -1414,7 +1420,7 @@ static int launch_ols3(const void* in, void* out, long long nout, long long nin,
         const char* e = GRB_GETENV_ONCE("GRB200_FFTFILT_FOLD"); // 0 = full-length inverse transform, decimation on store
         return !(e && e[0] == '0');
     }();
-    if (fold && D == 8)
+    if (fold && (D == 8 || D == 16 || D == 32 || D == 64 || D == 128 || D == 256)) // (beyond 8: fold by 8, every D/8-th kept)
         return launch_ols3_d<RP, 8>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
     if (fold && D == 4)
         return launch_ols3_d<RP, 4>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);

@@ -55,7 +55,7 @@ def test_fir_fff_sweep(grb, orc, ntaps, decim):
 @pytest.mark.parametrize("ntaps,decim,nout,shift", [(97, 1, 200001, 0), (256, 1, 131073, 0), (1000, 3, 70001, 0), (4097, 1, 66000, 0),
                                                     (8192, 2, 65537, 0), (300, 2, 65536, 0), (17, 1, 1 << 21, 0), (24, 4, 300001, 0),
                                                     (2049, 1, 400003, 0), (9, 2, 500002, 0), (64, 8, 100000, 0), (130, 1, 300000, 1),
-                                                    (130, 5, 99999, 2), (40, 1, 65536, 3)])
+                                                    (130, 5, 99999, 2), (40, 1, 65536, 3), (200, 16, 70000, 0), (33, 32, 65536, 0)])
 def test_fir_fff_long_filters_on_the_overlap_save_kernel(grb, orc, ntaps, decim, nout, shift):
     """More than 16 taps (8 at decimation 2) and >= 65536 outputs: the two halves of the call go through the overlap-save kernels
     as re / im of one complex stream (odd output counts: the second half is one shorter) -- fftfilt_ols3_kernel<RP> up to 2049

@@ -26,9 +26,9 @@ def timed(fn, reps=3):
     return e0.elapsed_time(e1) / reps
 
 
-kinds = sys.argv[1:] or ["ccf", "ccc", "fff"]
+kinds = [a for a in sys.argv[1:] if "=" not in a] or ["ccf", "ccc", "fff"]
 for kind in kinds:
-    for D in (1, 2, 4, 8):
+    for D in [int(a[2:]) for a in sys.argv[1:] if a.startswith('D=')] or (1, 2, 4, 8):
         for ntaps in (8, 16, 24, 32, 40, 48, 64, 96, 128, 192, 256, 384, 512):
             if kind == "ccc":
                 taps = (rng.uniform(-1, 1, ntaps) + 1j * rng.uniform(-1, 1, ntaps)).astype(np.complex64)
