@@ -1266,17 +1266,36 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
                     // x[d] = result i = j0 + Q (g + 16 d) = t + 16 Q d of the block = item m = DEC i + rb.  D = DEC: decimated
                     // output ob + i.  D = DEC E (DEC = 8, E = 2 .. 32): every E-th of them is wanted, i = ifirst + E j -- a thread
                     // keeps all of its results or none (16 Q = 32 is a multiple of E) -- and is output ob + j.
+                    // (E not a power of two -- decimation 10 = 2 x 5, 20 = 4 x 5, 24 = 8 x 3 ..: one 32-bit division per result)
                     const int E = D / DEC, lgE = 31 - __clz(E);
+                    const bool p2 = (E & (E - 1)) == 0;
                     const int rD = E == 1 ? rb : (int)((((long long)nh - blk * V) % D + D) % D);
                     const int ifirst = (rD - rb) / DEC;
                     const long long ob = (blk * V + rD - nh) / D; // (exact)
                     const long long lim = RP ? half : nout, limB = RP ? nout - half : 0;
                     const bool keep = ((t - ifirst) & (E - 1)) == 0;
+                    // not a power of two: (i - ifirst) = jj E + mm, carried from one result to the next (one division per thread)
+                    const unsigned uE = (unsigned)E, qE = (16u * Q) / uE, rE = 16u * Q - qE * uE;
+                    const unsigned r0 = (unsigned)(t - ifirst + E); // (ifirst < E: not negative)
+                    int jj = (int)(r0 / uE) - 1;
+                    unsigned mm = r0 - (r0 / uE) * uE;
 #pragma unroll
                     for (int d = 0; d < 16; d++) {
-                        const int i = t + 16 * Q * d;
-                        const long long o = ob + ((i - ifirst) >> lgE);
-                        if (keep && DEC * i + rb >= nh && o < lim) {
+                        const int i = t + 16 * Q * d, rel = i - ifirst;
+                        int j = rel >> lgE;
+                        bool kept = keep;
+                        if (!p2) {
+                            j = jj;
+                            kept = mm == 0;
+                            mm += rE;
+                            jj += (int)qE;
+                            if (mm >= uE) {
+                                mm -= uE;
+                                jj++;
+                            }
+                        }
+                        const long long o = ob + j;
+                        if (kept && DEC * i + rb >= nh && o < lim) {
                             if constexpr (RP) {
                                 outf[o] = x[d].x;
                                 if (o < limB)
@@ -1420,12 +1439,17 @@ static int launch_ols3(const void* in, void* out, long long nout, long long nin,
         const char* e = GRB_GETENV_ONCE("GRB200_FFTFILT_FOLD"); // 0 = full-length inverse transform, decimation on store
         return !(e && e[0] == '0');
     }();
-    if (fold && (D == 8 || D == 16 || D == 32 || D == 64 || D == 128 || D == 256)) // (beyond 8: fold by 8, every D/8-th kept)
-        return launch_ols3_d<RP, 8>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
-    if (fold && D == 4)
-        return launch_ols3_d<RP, 4>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
-    if (fold && D == 2)
-        return launch_ols3_d<RP, 2>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+    // fold by the largest of 8, 4, 2 that divides the decimation; what is left of it (powers of two up to 32: whole threads;
+    // anything else: per result) is dropped on store.  Odd decimations: full-length inverse.
+    if (fold && D > 1 && D <= (1 << 20)) {
+        const int rest8 = D / 8;
+        if (D % 8 == 0 && ((rest8 & (rest8 - 1)) != 0 || rest8 <= 32))
+            return launch_ols3_d<RP, 8>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+        if (D % 8 != 0 && D % 4 == 0)
+            return launch_ols3_d<RP, 4>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+        if (D % 4 != 0 && D % 2 == 0)
+            return launch_ols3_d<RP, 2>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
+    }
     return launch_ols3_d<RP, 0>(in, out, nout, nin, ntaps, D, H, tw, nsm, st);
 }
 

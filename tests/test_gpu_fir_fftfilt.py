@@ -394,11 +394,14 @@ def test_fft_filter_partitioned_device_resident_unaligned(grb):
 
 @pytest.mark.parametrize("ntaps,decim,shift", [(31, 1, 0), (128, 1, 1), (1025, 1, 0), (2048, 1, 1), (2047, 1, 0), (600, 2, 0),
                                                (333, 3, 1), (100, 4, 1), (512, 8, 0), (77, 16, 0), (1, 1, 1), (2, 2, 0),
-                                               (300, 32, 1), (1000, 64, 0), (40, 256, 0), (2048, 16, 1), (129, 128, 0)])
+                                               (300, 32, 1), (1000, 64, 0), (40, 256, 0), (2048, 16, 1), (129, 128, 0),
+                                               (100, 10, 0), (333, 20, 1), (64, 24, 0), (500, 6, 1), (50, 100, 0), (700, 40, 1),
+                                               (90, 512, 0)])
 def test_fft_filter_three_group_kernel(grb, ntaps, decim, shift):
     """fftfilt_ols3_kernel (plain overlap-save, up to 2048 taps): device resident, many blocks per group and a ragged last one,
     16- and 8-byte aligned input, decimations 2 / 4 / 8 (spectrum folded, L/D-point inverse), 16 .. 256 (folded by 8, every
-    D/8-th result kept) and others (full inverse, decimated on store); nothing is written past the last output."""
+    D/8-th result kept), other even decimations (folded by their largest factor 2 / 4 / 8, the rest dropped per result) and odd
+    ones (full inverse, decimated on store); nothing is written past the last output."""
     import scipy.signal
     import torch
 
