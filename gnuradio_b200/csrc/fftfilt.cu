@@ -1267,41 +1267,59 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
                     // output ob + i.  D = DEC E (DEC = 8, E = 2 .. 32): every E-th of them is wanted, i = ifirst + E j -- a thread
                     // keeps all of its results or none (16 Q = 32 is a multiple of E) -- and is output ob + j.
                     // (E not a power of two -- decimation 10 = 2 x 5, 20 = 4 x 5, 24 = 8 x 3 ..: one 32-bit division per result)
-                    const int E = D / DEC, lgE = 31 - __clz(E);
-                    const bool p2 = (E & (E - 1)) == 0;
-                    const int rD = E == 1 ? rb : (int)((((long long)nh - blk * V) % D + D) % D);
-                    const int ifirst = (rD - rb) / DEC;
-                    const long long ob = (blk * V + rD - nh) / D; // (exact)
+                    const long long nb = (long long)nh - blk * V;
                     const long long lim = RP ? half : nout, limB = RP ? nout - half : 0;
-                    const bool keep = ((t - ifirst) & (E - 1)) == 0;
-                    // not a power of two: (i - ifirst) = jj E + mm, carried from one result to the next (one division per thread)
-                    const unsigned uE = (unsigned)E, qE = (16u * Q) / uE, rE = 16u * Q - qE * uE;
-                    const unsigned r0 = (unsigned)(t - ifirst + E); // (ifirst < E: not negative)
-                    int jj = (int)(r0 / uE) - 1;
-                    unsigned mm = r0 - (r0 / uE) * uE;
-#pragma unroll
-                    for (int d = 0; d < 16; d++) {
-                        const int i = t + 16 * Q * d, rel = i - ifirst;
-                        int j = rel >> lgE;
-                        bool kept = keep;
-                        if (!p2) {
-                            j = jj;
-                            kept = mm == 0;
-                            mm += rE;
-                            jj += (int)qE;
-                            if (mm >= uE) {
-                                mm -= uE;
-                                jj++;
-                            }
+                    auto put = [&](long long o, float2 y) {
+                        if constexpr (RP) {
+                            outf[o] = y.x;
+                            if (o < limB)
+                                outf[half + o] = y.y;
+                        } else {
+                            out[o] = y;
                         }
-                        const long long o = ob + j;
-                        if (kept && DEC * i + rb >= nh && o < lim) {
-                            if constexpr (RP) {
-                                outf[o] = x[d].x;
-                                if (o < limB)
-                                    outf[half + o] = x[d].y;
-                            } else {
-                                out[o] = x[d];
+                    };
+                    if (D == DEC) { // the plain case, kept apart: this warp is the tail of the block, every instruction counts
+                        const long long ob = (rb - nb) / DEC; // = (blk V + rb - nh) / DEC, exact
+#pragma unroll
+                        for (int d = 0; d < 16; d++) {
+                            const int i = t + 16 * Q * d;
+                            if (DEC * i + rb >= nh && ob + i < lim)
+                                put(ob + i, x[d]);
+                        }
+                    } else {
+                        const int E = D / DEC, lgE = 31 - __clz(E);
+                        const bool p2 = (E & (E - 1)) == 0;
+                        const int rD = p2 ? (int)(nb & (D - 1)) : (int)((nb % D + D) % D);
+                        const int ifirst = (rD - rb) / DEC;
+                        const long long num = rD - nb; // = blk V + rD - nh, a multiple of D
+                        const long long ob = p2 ? (num >> (lgE + (DEC == 8 ? 3 : (DEC == 4 ? 2 : 1)))) : num / D;
+                        if (p2) {
+                            if (((t - ifirst) & (E - 1)) == 0) {
+#pragma unroll
+                                for (int d = 0; d < 16; d++) {
+                                    const int i = t + 16 * Q * d;
+                                    const long long o = ob + ((i - ifirst) >> lgE);
+                                    if (DEC * i + rb >= nh && o < lim)
+                                        put(o, x[d]);
+                                }
+                            }
+                        } else { // (i - ifirst) = jj E + mm, carried from one result to the next: one division per thread
+                            const unsigned uE = (unsigned)E, qE = (16u * Q) / uE, rE = 16u * Q - qE * uE;
+                            const unsigned r0 = (unsigned)(t - ifirst + E); // (ifirst < E: not negative)
+                            int jj = (int)(r0 / uE) - 1;
+                            unsigned mm = r0 - (r0 / uE) * uE;
+#pragma unroll
+                            for (int d = 0; d < 16; d++) {
+                                const int i = t + 16 * Q * d;
+                                const long long o = ob + jj;
+                                if (mm == 0 && DEC * i + rb >= nh && o < lim)
+                                    put(o, x[d]);
+                                mm += rE;
+                                jj += (int)qE;
+                                if (mm >= uE) {
+                                    mm -= uE;
+                                    jj++;
+                                }
                             }
                         }
                     }
