@@ -208,7 +208,7 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
     const long long least =
         h->ct ? ((even || D >= 24) ? 0 : 16LL * D)
               : (D == 1 ? 64
-                        : (D == 2 ? 32 : (D == 4 ? 64 : (D == 8 || D == 16 ? 0 : (D >= 24 ? 0 : (even ? 13LL : 48LL) * D))))));
+                        : (D == 2 ? 32 : (D == 4 ? 64 : (D == 8 || D == 16 ? 0 : (D >= 24 ? 0 : (even ? 13LL : 48LL) * D)))));
     const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && !tc_real && !tc_forced && ntaps > least);
     if (want && fftfilt_device_plan(ntaps, nullptr) > 0) {
         std::vector<float> tc((size_t)2 * ntaps, 0.f);
