@@ -726,6 +726,19 @@ __device__ __forceinline__ float2 cmul_dir(float2 a, float2 w) // a * w forward,
 
 __device__ __forceinline__ void group_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
 
+// The two twiddle tables of fft4096_3x16, written by one 256-thread group (thread t): T1[r][q] = W256^{q r} = W4096^{16 q r}
+// (rows padded to T1_STRIDE), TW2[j][t] = W4096^{2^j t}, j = 0, 1, 2.  tw: the 4096 roots.
+__device__ __forceinline__ void fft4096_3x16_tables(float2* T1, float2* TW2, const float2* __restrict__ tw, int t)
+{
+    const int r = t >> 4, q = t & 15;
+    T1[r * Upols2::T1_STRIDE + q] = tw[(16 * q * r) & (Upols2::L - 1)];
+    if (q < 2)
+        T1[r * Upols2::T1_STRIDE + 16 + q] = make_float2(0.f, 0.f);
+    TW2[t] = tw[t];
+    TW2[Upols2::TPV + t] = tw[2 * t];
+    TW2[2 * Upols2::TPV + t] = tw[4 * t];
+}
+
 // Register convention as cta_fft: in v[q] = x[t + 256 q], out v[q] = X[t + 256 q]; `bid` = the group's barrier.
 template <bool FWD, class After>
 __device__ __forceinline__ void fft4096_3x16(float2 (&v)[16], float2* S, int t, int bid, const float2* T1,
@@ -832,15 +845,8 @@ fftfilt_upols2_kernel(const float2* __restrict__ in, float2* __restrict__ out, l
         mbar_init(&bar[0], 1);
         mbar_init(&bar[1], 1);
     }
-    if (grp == 0) {
-        const int r = t >> 4, q = t & 15; // T1[r][q] = W256^{q r} = W4096^{16 q r}
-        T1[r * G::T1_STRIDE + q] = tw[(16 * q * r) & (L - 1)];
-        if (q < 2)
-            T1[r * G::T1_STRIDE + 16 + q] = make_float2(0.f, 0.f);
-        TW2[t] = tw[t];
-        TW2[TPV + t] = tw[2 * t];
-        TW2[2 * TPV + t] = tw[4 * t];
-    }
+    if (grp == 0)
+        fft4096_3x16_tables(T1, TW2, tw, t);
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;");
@@ -1097,15 +1103,8 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
     }
     if (t == 0)
         mbar_init(bar, 1);
-    if (grp == 0) { // the two twiddle tables of fft4096_3x16
-        const int r = t >> 4, q = t & 15;
-        T1[r * Upols2::T1_STRIDE + q] = tw[(16 * q * r) & (L - 1)];
-        if (q < 2)
-            T1[r * Upols2::T1_STRIDE + 16 + q] = make_float2(0.f, 0.f);
-        TW2[t] = tw[t];
-        TW2[TPV + t] = tw[2 * t];
-        TW2[2 * TPV + t] = tw[4 * t];
-    }
+    if (grp == 0)
+        fft4096_3x16_tables(T1, TW2, tw, t);
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;");
