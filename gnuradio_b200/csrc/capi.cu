@@ -153,11 +153,11 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
         // that past 16 taps, at decimation 4 and 8 past 8, at decimation 2 it is below at 8 taps already)
         // At decimations that are not powers of two the one-output-per-thread FIR kernel reads ntaps floats per output whatever
         // the decimation: ~15 - 27 T floats/s, so it holds against the overlap-save kernels (430 - 530 G samples/s at even
-        // decimations, 370 at odd ones) up to 28 - 72 taps (profiles/r2_route_check.txt).
+        // decimations, 425 at odd ones) up to 24 - 64 taps (profiles/r2_route_check.txt).
         const int D = h->decim;
         const bool dp2 = (D & (D - 1)) == 0;
         const int least = dp2 ? (D == 1 ? 16 : (D == 2 ? 4 : 8))
-                              : ((D & 1) == 0 ? (D < 16 ? 40 : 48) : (D < 8 ? 28 : (D < 16 ? 48 : 72)));
+                              : ((D & 1) == 0 ? (D < 16 ? 40 : 48) : (D < 8 ? 24 : (D < 16 ? 44 : 64)));
         const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && ntaps > least);
         if (want && L > 0) {
             std::vector<float> tc((size_t)2 * ntaps, 0.f);
@@ -208,7 +208,7 @@ static int fir_upload_taps(grb200_fir* h, const float* taps, int ntaps)
     const long long least =
         h->ct ? ((even || D >= 24) ? 0 : 16LL * D)
               : (D == 1 ? 64
-                        : (D == 2 ? 32 : (D == 4 ? 64 : (D == 8 || D == 16 ? 0 : (D >= 24 ? 0 : (even ? 13LL : 48LL) * D)))));
+                        : (D == 2 ? 32 : (D == 4 ? 64 : (D == 8 || D == 16 ? 0 : (D >= 24 ? 0 : (even ? 13LL : 40LL) * D)))));
     const bool want = h->fft_pref == 1 || (h->fft_pref < 0 && !tc_real && !tc_forced && ntaps > least);
     if (want && fftfilt_device_plan(ntaps, nullptr) > 0) {
         std::vector<float> tc((size_t)2 * ntaps, 0.f);

@@ -1355,6 +1355,27 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
                                     oc[step * q] = v[q].y;
                                 }
                         }
+                    } else if ((blk + 1) * V <= nyB) { // any other decimation, whole block inside (see the complex form below)
+                        const unsigned uD = (unsigned)D, qD = 256u / uD, rD = 256u - qD * uD;
+                        const unsigned lift = ((unsigned)nh + uD - 1) / uD;
+                        const unsigned r0 = dec_r + (unsigned)t + lift * uD - (unsigned)nh;
+                        int jj = (int)(r0 / uD) - (int)lift;
+                        unsigned mm = r0 - (r0 / uD) * uD;
+                        float* oa = outf + dec_q;
+                        float* oc = oa + half;
+#pragma unroll
+                        for (int q = 0; q < 16; q++) {
+                            if (mm == 0 && t + 256 * q >= nh) {
+                                oa[jj] = v[q].x;
+                                oc[jj] = v[q].y;
+                            }
+                            mm += rD;
+                            jj += (int)qD;
+                            if (mm >= uD) {
+                                mm -= uD;
+                                jj++;
+                            }
+                        }
                     } else {
 #pragma unroll
                         for (int q = 0; q < 16; q++) {
@@ -1395,6 +1416,25 @@ fftfilt_ols3_kernel(const float2* __restrict__ in, float2* __restrict__ out, lon
                             for (int q = 0; q < 16; q++)
                                 if (t + 256 * q >= nh)
                                     o[step * q] = v[q];
+                        }
+                    } else if ((blk + 1) * V <= ny) { // any other decimation, whole block inside: dec_r + m - nh = jj D + mm,
+                                                      // carried from one item of the thread to the next (256 = qD D + rD)
+                        const unsigned uD = (unsigned)D, qD = 256u / uD, rD = 256u - qD * uD;
+                        const unsigned lift = ((unsigned)nh + uD - 1) / uD; // (so that the first dividend is not negative)
+                        const unsigned r0 = dec_r + (unsigned)t + lift * uD - (unsigned)nh;
+                        int jj = (int)(r0 / uD) - (int)lift;
+                        unsigned mm = r0 - (r0 / uD) * uD;
+                        float2* o = out + dec_q;
+#pragma unroll
+                        for (int q = 0; q < 16; q++) {
+                            if (mm == 0 && t + 256 * q >= nh)
+                                o[jj] = v[q];
+                            mm += rD;
+                            jj += (int)qD;
+                            if (mm >= uD) {
+                                mm -= uD;
+                                jj++;
+                            }
                         }
                     } else {
 #pragma unroll
